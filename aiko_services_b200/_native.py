@@ -1,0 +1,88 @@
+"""Loader for libaiko_b200.so -- the C-ABI boundary (include/aiko_b200.h).
+
+There is no CPU fallback: if the library is missing, or no B200 is visible when a
+compute entry point is called, the product path raises.
+"""
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libaiko_b200.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+OK = 0
+ERR_INVALID_ARGUMENT = -1
+ERR_UNSUPPORTED = -2
+ERR_CUDA = -3
+ERR_WORKSPACE = -4
+
+
+class NativeError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"libaiko_b200 error {code}: {message}")
+        self.code = code
+
+
+class OverlayOp(ctypes.Structure):
+    _fields_ = [("kind", ctypes.c_int32), ("x0", ctypes.c_int32), ("y0", ctypes.c_int32),
+                ("x1", ctypes.c_int32), ("y1", ctypes.c_int32), ("p0", ctypes.c_uint32),
+                ("p1", ctypes.c_uint32), ("p2", ctypes.c_uint32)]
+
+
+class Overlay(ctypes.Structure):
+    _fields_ = [("ops", ctypes.c_void_p), ("op_offsets", ctypes.c_void_p),
+                ("patch_ids", ctypes.c_void_p), ("luts", ctypes.c_void_p),
+                ("patch_w", ctypes.c_int32), ("patch_h", ctypes.c_int32),
+                ("n_patches", ctypes.c_int32)]
+
+
+_vp, _i, _i64, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t
+_ovp = ctypes.POINTER(Overlay)
+
+# name -> argtypes.  Every symbol declared in include/aiko_b200.h must be listed here;
+# tests/test_abi.py checks the two against each other.
+SIGNATURES = {
+    "aiko_b200_abi_version": [],
+    "aiko_b200_last_error": [],
+    "aiko_b200_device_info": [ctypes.c_char_p, _sz, ctypes.POINTER(_i), ctypes.POINTER(_i)],
+    "aiko_b200_resize_linear_u8": [_vp, _i, _i, _i, _i, _i64, _i64, _vp, _i, _i, _i64, _i64, _i, _ovp, _vp],
+    "aiko_b200_overlay_u8": [_vp, _vp, _i, _i, _i, _i, _i64, _i64, _ovp, _vp],
+    "aiko_b200_swap_rb_u8": [_vp, _vp, _i64, _vp],
+    "aiko_b200_bgr2gray_u8": [_vp, _vp, _i64, _i, _vp],
+    "aiko_b200_gray2bgr_u8": [_vp, _vp, _i64, _vp],
+    "aiko_b200_flip_u8": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "aiko_b200_crop_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _vp],
+}
+
+_lib = None
+
+
+def build(verbose=False):
+    """Compile libaiko_b200.so in-tree with nvcc for sm_100a (cross-compiles without a GPU)."""
+    out = None if verbose else subprocess.DEVNULL
+    subprocess.check_call(["make", "-C", CSRC, "-j8"], stdout=out, stderr=None if verbose else subprocess.STDOUT)
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(aiko_services_b200 has no CPU fallback)")
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, argtypes in SIGNATURES.items():
+            fn = getattr(handle, name)  # AttributeError = header/library mismatch: fail loudly
+            fn.argtypes = argtypes
+            fn.restype = ctypes.c_char_p if name == "aiko_b200_last_error" else ctypes.c_int
+        _lib = handle
+    return _lib
+
+
+def check(code):
+    if code != OK:
+        msg = lib().aiko_b200_last_error()
+        raise NativeError(code, msg.decode() if msg else "")
+    return code

@@ -1,0 +1,264 @@
+// Colour conversion, flip and crop call sites of the reference's media elements
+// (R/elements/media/video_io.py:129,299; webcam_io.py:122-129; image_io.py:115-117,158-160).
+// All are single-pass HBM-bound byte shuffles: each thread owns 16 pixels = 48 bytes =
+// three 128-bit vectors (lcm of the 3-byte pixel and the 16-byte vector), so every global
+// access is a full uint8x16 load or store.
+#include "common.cuh"
+
+namespace aiko {
+
+__device__ __forceinline__ uint32_t bp(uint32_t a, uint32_t b, uint32_t sel) { return __byte_perm(a, b, sel); }
+
+// 12 bytes (4 pixels) in words a,b,c:  a = p0c0 p0c1 p0c2 p1c0 ; b = p1c1 p1c2 p2c0 p2c1 ; c = p2c2 p3c0 p3c1 p3c2
+__device__ __forceinline__ void swap12(uint32_t a, uint32_t b, uint32_t c, uint32_t* oa, uint32_t* ob, uint32_t* oc) {
+  // out bytes: p0c2 p0c1 p0c0 p1c2 | p1c1 p1c0 p2c2 p2c1 | p2c0 p3c2 p3c1 p3c0
+  *oa = bp(a, b, 0x5012);                // a2 a1 a0 b1
+  const uint32_t t = bp(a, c, 0x4003);   // a3 a0(dummy) a0(dummy) c0 -> bytes: [a3, a0, a0, c0]
+  *ob = bp(b, t, 0x3740);                // b0 t0(a3) t3(c0) b3   => p1c1 p1c0 p2c2 p2c1
+  *oc = bp(c, b, 0x1236);                // b2 c3 c2 c1           => p2c0 p3c2 p3c1 p3c0
+}
+
+__global__ void __launch_bounds__(kThreads) swap_rb_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                                           long long n_groups, long long n_pixels, int vec_ok) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < n_groups; g += stride) {
+    if (vec_ok && (g + 1) * 16 <= n_pixels) {
+      const uint4* s = reinterpret_cast<const uint4*>(src) + g * 3;
+      uint4 v0 = ldg_stream(s), v1 = ldg_stream(s + 1), v2 = ldg_stream(s + 2);
+      uint4 o0, o1, o2;
+      swap12(v0.x, v0.y, v0.z, &o0.x, &o0.y, &o0.z);
+      swap12(v0.w, v1.x, v1.y, &o0.w, &o1.x, &o1.y);
+      swap12(v1.z, v1.w, v2.x, &o1.z, &o1.w, &o2.x);
+      swap12(v2.y, v2.z, v2.w, &o2.y, &o2.z, &o2.w);
+      uint4* d = reinterpret_cast<uint4*>(dst) + g * 3;
+      stg_stream(d, o0); stg_stream(d + 1, o1); stg_stream(d + 2, o2);
+    } else {
+      const long long pe = min((g + 1) * 16, n_pixels);
+      for (long long px = g * 16; px < pe; px++) {
+        const uint8_t a = src[3 * px], b = src[3 * px + 1], c = src[3 * px + 2];
+        dst[3 * px] = c; dst[3 * px + 1] = b; dst[3 * px + 2] = a;
+      }
+    }
+  }
+}
+
+// cv2 BGR2GRAY, 15-bit fixed point
+__device__ __forceinline__ uint32_t gray_of(uint32_t c0, uint32_t c1, uint32_t c2, int rgb_order) {
+  const uint32_t b = rgb_order ? c2 : c0, r = rgb_order ? c0 : c2;
+  return (b * 3735u + c1 * 19235u + r * 9798u + 16384u) >> 15;
+}
+__device__ __forceinline__ uint32_t gray4(uint32_t a, uint32_t b, uint32_t c, int rgb) {
+  const uint32_t g0 = gray_of(a & 0xff, (a >> 8) & 0xff, (a >> 16) & 0xff, rgb);
+  const uint32_t g1 = gray_of(a >> 24, b & 0xff, (b >> 8) & 0xff, rgb);
+  const uint32_t g2 = gray_of((b >> 16) & 0xff, b >> 24, c & 0xff, rgb);
+  const uint32_t g3 = gray_of((c >> 8) & 0xff, (c >> 16) & 0xff, c >> 24, rgb);
+  return g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+}
+
+__global__ void __launch_bounds__(kThreads) bgr2gray_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                                            long long n_groups, long long n_pixels, int rgb_order,
+                                                            int vec_ok) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < n_groups; g += stride) {
+    if (vec_ok && (g + 1) * 16 <= n_pixels) {
+      const uint4* s = reinterpret_cast<const uint4*>(src) + g * 3;
+      const uint4 v0 = ldg_stream(s), v1 = ldg_stream(s + 1), v2 = ldg_stream(s + 2);
+      uint4 o;
+      o.x = gray4(v0.x, v0.y, v0.z, rgb_order);
+      o.y = gray4(v0.w, v1.x, v1.y, rgb_order);
+      o.z = gray4(v1.z, v1.w, v2.x, rgb_order);
+      o.w = gray4(v2.y, v2.z, v2.w, rgb_order);
+      stg_stream(reinterpret_cast<uint4*>(dst) + g, o);
+    } else {
+      const long long pe = min((g + 1) * 16, n_pixels);
+      for (long long px = g * 16; px < pe; px++)
+        dst[px] = (uint8_t)gray_of(src[3 * px], src[3 * px + 1], src[3 * px + 2], rgb_order);
+    }
+  }
+}
+
+__device__ __forceinline__ void rep4(uint32_t g, uint32_t* a, uint32_t* b, uint32_t* c) {
+  *a = bp(g, g, 0x1000);  // g0 g0 g0 g1
+  *b = bp(g, g, 0x2211);  // g1 g1 g2 g2
+  *c = bp(g, g, 0x3332);  // g2 g3 g3 g3
+}
+
+__global__ void __launch_bounds__(kThreads) gray2bgr_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                                            long long n_groups, long long n_pixels, int vec_ok) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < n_groups; g += stride) {
+    if (vec_ok && (g + 1) * 16 <= n_pixels) {
+      const uint4 v = ldg_stream(reinterpret_cast<const uint4*>(src) + g);
+      uint4 o0, o1, o2;
+      rep4(v.x, &o0.x, &o0.y, &o0.z);
+      rep4(v.y, &o0.w, &o1.x, &o1.y);
+      rep4(v.z, &o1.z, &o1.w, &o2.x);
+      rep4(v.w, &o2.y, &o2.z, &o2.w);
+      uint4* d = reinterpret_cast<uint4*>(dst) + g * 3;
+      stg_stream(d, o0); stg_stream(d + 1, o1); stg_stream(d + 2, o2);
+    } else {
+      const long long pe = min((g + 1) * 16, n_pixels);
+      for (long long px = g * 16; px < pe; px++) dst[3 * px] = dst[3 * px + 1] = dst[3 * px + 2] = src[px];
+    }
+  }
+}
+
+// Flip / crop: one CTA per output row; the source row (segment) goes through shared memory
+// so both the global read and the global write are coalesced vectors.
+__global__ void __launch_bounds__(kThreads) flip_rows_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                                             long long n_rows, int h, int w, int ch, int flip_code) {
+  extern __shared__ __align__(16) uint8_t srow[];
+  const int rb = w * ch;
+  for (long long r = blockIdx.x; r < n_rows; r += gridDim.x) {
+    const long long n = r / h;
+    const int y = (int)(r - n * h);
+    const int sy = (flip_code <= 0) ? h - 1 - y : y;
+    const uint8_t* s = src + (n * h + sy) * (long long)rb;
+    uint8_t* d = dst + r * (long long)rb;
+    if (flip_code == 0) {  // vertical only: straight row copy
+      if ((((uintptr_t)s | (uintptr_t)d | (uintptr_t)rb) & 15) == 0) {
+        for (int i = threadIdx.x; i < (rb >> 4); i += kThreads)
+          stg_stream(reinterpret_cast<uint4*>(d) + i, ldg_stream(reinterpret_cast<const uint4*>(s) + i));
+      } else {
+        for (int i = threadIdx.x; i < rb; i += kThreads) d[i] = s[i];
+      }
+      continue;
+    }
+    // stage the source row, then emit pixels in reverse order
+    const int head = (int)((uintptr_t)s & 15);
+    const uint8_t* sa = s - head;  // aligned down; bytes before s are never used
+    const int nv = (head + rb + 15) >> 4;
+    for (int i = threadIdx.x; i < nv; i += kThreads) {
+      // first / last vector may straddle the allocation edge: fall back to bytes there
+      if (i == 0 || i == nv - 1) {
+        for (int b = 0; b < 16; b++) {
+          const int o = i * 16 + b - head;
+          srow[i * 16 + b] = (o >= 0 && o < rb) ? s[o] : 0;
+        }
+      } else {
+        reinterpret_cast<uint4*>(srow)[i] = ldg_stream(reinterpret_cast<const uint4*>(sa) + i);
+      }
+    }
+    __syncthreads();
+    const uint8_t* sp = srow + head;
+    const bool dvec = (((uintptr_t)d | (uintptr_t)rb) & 15) == 0;
+    if (dvec) {
+      for (int i = threadIdx.x; i < (rb >> 4); i += kThreads) {
+        uint32_t wds[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          uint32_t v = 0;
+#pragma unroll
+          for (int b = 0; b < 4; b++) {
+            const int o = i * 16 + k * 4 + b;  // output byte index
+            const int px = o / ch, c = o - px * ch;
+            v |= (uint32_t)sp[(w - 1 - px) * ch + c] << (8 * b);
+          }
+          wds[k] = v;
+        }
+        stg_stream(reinterpret_cast<uint4*>(d) + i, make_uint4(wds[0], wds[1], wds[2], wds[3]));
+      }
+    } else {
+      for (int o = threadIdx.x; o < rb; o += kThreads) {
+        const int px = o / ch, c = o - px * ch;
+        d[o] = sp[(w - 1 - px) * ch + c];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) crop_rows_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                                             long long n_rows, int h, int w, int ch, int x0, int y0,
+                                                             int cw, int chh) {
+  const int rb = cw * ch;
+  for (long long r = blockIdx.x; r < n_rows; r += gridDim.x) {
+    const long long n = r / chh;
+    const int y = (int)(r - n * chh);
+    const uint8_t* s = src + ((n * h + y0 + y) * (long long)w + x0) * ch;
+    uint8_t* d = dst + r * (long long)rb;
+    if ((((uintptr_t)s | (uintptr_t)d | (uintptr_t)rb) & 15) == 0) {
+      for (int i = threadIdx.x; i < (rb >> 4); i += kThreads)
+        stg_stream(reinterpret_cast<uint4*>(d) + i, ldg_stream(reinterpret_cast<const uint4*>(s) + i));
+    } else {
+      for (int i = threadIdx.x; i < rb; i += kThreads) d[i] = s[i];
+    }
+  }
+}
+
+static unsigned stream_grid(long long work_items) {
+  long long blocks = (work_items + kThreads - 1) / kThreads;
+  const long long cap = (long long)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (unsigned)blocks;
+}
+
+}  // namespace aiko
+
+using namespace aiko;
+
+extern "C" int aiko_b200_swap_rb_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, void* stream) {
+  AIKO_CHECK_ARG(n_pixels >= 0, "swap_rb: n_pixels < 0");
+  if (n_pixels == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(src && dst, "swap_rb: null pointer");
+  const long long groups = (n_pixels + 15) / 16;
+  const int vec_ok = ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0;
+  swap_rb_kernel<<<stream_grid(groups), kThreads, 0, (cudaStream_t)stream>>>(src, dst, groups, n_pixels, vec_ok);
+  return cuda_status(cudaGetLastError(), "swap_rb launch");
+}
+
+extern "C" int aiko_b200_bgr2gray_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, int rgb_order,
+                                     void* stream) {
+  AIKO_CHECK_ARG(n_pixels >= 0, "bgr2gray: n_pixels < 0");
+  if (n_pixels == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(src && dst, "bgr2gray: null pointer");
+  const long long groups = (n_pixels + 15) / 16;
+  const int vec_ok = ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0;
+  bgr2gray_kernel<<<stream_grid(groups), kThreads, 0, (cudaStream_t)stream>>>(src, dst, groups, n_pixels,
+                                                                               rgb_order ? 1 : 0, vec_ok);
+  return cuda_status(cudaGetLastError(), "bgr2gray launch");
+}
+
+extern "C" int aiko_b200_gray2bgr_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, void* stream) {
+  AIKO_CHECK_ARG(n_pixels >= 0, "gray2bgr: n_pixels < 0");
+  if (n_pixels == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(src && dst, "gray2bgr: null pointer");
+  const long long groups = (n_pixels + 15) / 16;
+  const int vec_ok = ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0;
+  gray2bgr_kernel<<<stream_grid(groups), kThreads, 0, (cudaStream_t)stream>>>(src, dst, groups, n_pixels, vec_ok);
+  return cuda_status(cudaGetLastError(), "gray2bgr launch");
+}
+
+extern "C" int aiko_b200_flip_u8(const uint8_t* src, uint8_t* dst, int n_frames, int h, int w, int channels,
+                                 int flip_code, void* stream) {
+  AIKO_CHECK_ARG(n_frames >= 0 && h >= 0 && w >= 0, "flip: negative size");
+  if (n_frames == 0 || h == 0 || w == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(src && dst && src != dst, "flip: null or aliased pointers");
+  AIKO_CHECK_ARG(channels >= 1 && channels <= 4, "flip: channels %d not in 1..4", channels);
+  const size_t smem = (size_t)w * channels + 48;
+  AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "flip: row of %zu bytes exceeds shared memory", smem);
+  AIKO_CUDA(cudaFuncSetAttribute(flip_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const long long rows = (long long)n_frames * h;
+  long long grid = (long long)sm_count() * 8;
+  if (grid > rows) grid = rows;
+  flip_rows_kernel<<<(unsigned)grid, kThreads, smem, (cudaStream_t)stream>>>(src, dst, rows, h, w, channels,
+                                                                            flip_code);
+  return cuda_status(cudaGetLastError(), "flip launch");
+}
+
+extern "C" int aiko_b200_crop_u8(const uint8_t* src, int n_frames, int h, int w, int channels, uint8_t* dst, int x0,
+                                 int y0, int crop_w, int crop_h, void* stream) {
+  AIKO_CHECK_ARG(n_frames >= 0, "crop: n_frames < 0");
+  AIKO_CHECK_ARG(channels >= 1 && channels <= 4, "crop: channels %d not in 1..4", channels);
+  AIKO_CHECK_ARG(x0 >= 0 && y0 >= 0 && crop_w >= 0 && crop_h >= 0 && x0 + crop_w <= w && y0 + crop_h <= h,
+                 "crop: window %d,%d %dx%d outside %dx%d", x0, y0, crop_w, crop_h, w, h);
+  if (n_frames == 0 || crop_w == 0 || crop_h == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(src && dst, "crop: null pointer");
+  const long long rows = (long long)n_frames * crop_h;
+  long long grid = (long long)sm_count() * 8;
+  if (grid > rows) grid = rows;
+  crop_rows_kernel<<<(unsigned)grid, kThreads, 0, (cudaStream_t)stream>>>(src, dst, rows, h, w, channels, x0, y0,
+                                                                          crop_w, crop_h);
+  return cuda_status(cudaGetLastError(), "crop launch");
+}

@@ -1,0 +1,161 @@
+"""Python-facing operators over the C ABI.
+
+torch is used here for device memory and streams only (``tensor.data_ptr()``,
+``torch.cuda.current_stream()``); the arithmetic is in libaiko_b200.so.  Each function
+mirrors the library call the reference element makes (cited in include/aiko_b200.h) but
+takes a whole batch ``uint8[N, H, W, C]`` (or ``[N, H, W]`` for grayscale) resident on the GPU.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _native
+from ._native import Overlay, OverlayOp, check
+
+
+def _stream_ptr(stream=None):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return ctypes.c_void_p(s.cuda_stream)
+
+
+def _require_cuda(t, name, dtype=torch.uint8):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f"{name}: expected a CUDA tensor (aiko_services_b200 has no CPU path)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name}: expected {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name}: expected a contiguous tensor")
+    return t
+
+
+def _nhwc(t):
+    """-> (n, h, w, c, gray_input)"""
+    if t.dim() == 4:
+        return t.shape[0], t.shape[1], t.shape[2], t.shape[3], False
+    if t.dim() == 3:
+        return t.shape[0], t.shape[1], t.shape[2], 1, True
+    raise ValueError(f"expected [N,H,W,C] or [N,H,W], got {tuple(t.shape)}")
+
+
+def _out(out, shape, device, name, dtype=torch.uint8):
+    if out is None:
+        return torch.empty(shape, dtype=dtype, device=device)
+    _require_cuda(out, name, dtype)
+    if tuple(out.shape) != tuple(shape):
+        raise ValueError(f"{name}: expected shape {tuple(shape)}, got {tuple(out.shape)}")
+    return out
+
+
+class DeviceOverlay:
+    """A draw list resident on the GPU (see aiko_b200_overlay in include/aiko_b200.h)."""
+
+    def __init__(self, ops, op_offsets, atlas=None):
+        self.ops, self.op_offsets, self.atlas = ops, op_offsets, atlas
+        self.struct = Overlay()
+        self.struct.ops = ops.data_ptr()
+        self.struct.op_offsets = op_offsets.data_ptr()
+        if atlas is not None:
+            self.struct.patch_ids = atlas.patch_ids.data_ptr()
+            self.struct.luts = atlas.luts.data_ptr()
+            self.struct.patch_w, self.struct.patch_h = atlas.patch_w, atlas.patch_h
+            self.struct.n_patches = atlas.patch_ids.shape[0]
+
+    @staticmethod
+    def pack_host(ops_per_frame):
+        """-> (uint8 ndarray of packed ops, int32 ndarray of offsets)"""
+        flat = [op for ops in ops_per_frame for op in ops]
+        offsets = np.zeros(len(ops_per_frame) + 1, np.int32)
+        if ops_per_frame:
+            np.cumsum([len(o) for o in ops_per_frame], out=offsets[1:])
+        count = max(len(flat), 1)
+        arr = (OverlayOp * count)(*flat)
+        raw = np.frombuffer(arr, dtype=np.uint8, count=ctypes.sizeof(OverlayOp) * count).copy()
+        return raw, offsets
+
+    @staticmethod
+    def from_host(ops_per_frame, device, atlas=None):
+        """ops_per_frame: list (one entry per frame) of lists of OverlayOp."""
+        raw, offsets = DeviceOverlay.pack_host(ops_per_frame)
+        return DeviceOverlay(torch.from_numpy(raw).to(device), torch.from_numpy(offsets).to(device), atlas)
+
+    def pointer(self):
+        return ctypes.pointer(self.struct)
+
+
+def resize_linear(src, width, height, *, swap_rb=False, overlay=None, out=None, stream=None):
+    """cv2.resize(image, (width, height)) for every frame of ``src``; optional fused overlay / swap."""
+    _require_cuda(src, "resize_linear src")
+    n, h, w, c, gray = _nhwc(src)
+    shape = (n, height, width) if gray else (n, height, width, c)
+    out = _out(out, shape, src.device, "resize_linear out")
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_resize_linear_u8(
+            src.data_ptr(), n, h, w, c, w * c, h * w * c, out.data_ptr(), height, width, width * c,
+            height * width * c, int(bool(swap_rb)), overlay.pointer() if overlay is not None else None,
+            _stream_ptr(stream)))
+    return out
+
+
+def overlay_draw(src, overlay, *, out=None, stream=None):
+    """ImageOverlay's drawing on frames already resident on the GPU."""
+    _require_cuda(src, "overlay src")
+    n, h, w, c, _ = _nhwc(src)
+    out = _out(out, src.shape, src.device, "overlay out")
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_overlay_u8(src.data_ptr(), out.data_ptr(), n, h, w, c, w * c, h * w * c,
+                                                 overlay.pointer(), _stream_ptr(stream)))
+    return out
+
+
+def swap_rb(src, *, out=None, stream=None):
+    _require_cuda(src, "swap_rb src")
+    if src.shape[-1] != 3:
+        raise ValueError("swap_rb: last dimension must be 3")
+    out = _out(out, src.shape, src.device, "swap_rb out")
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_swap_rb_u8(src.data_ptr(), out.data_ptr(), src.numel() // 3,
+                                                 _stream_ptr(stream)))
+    return out
+
+
+def bgr2gray(src, *, rgb_order=False, out=None, stream=None):
+    _require_cuda(src, "bgr2gray src")
+    if src.shape[-1] != 3:
+        raise ValueError("bgr2gray: last dimension must be 3")
+    out = _out(out, src.shape[:-1], src.device, "bgr2gray out")
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_bgr2gray_u8(src.data_ptr(), out.data_ptr(), src.numel() // 3,
+                                                  int(bool(rgb_order)), _stream_ptr(stream)))
+    return out
+
+
+def gray2bgr(src, *, out=None, stream=None):
+    _require_cuda(src, "gray2bgr src")
+    out = _out(out, tuple(src.shape) + (3,), src.device, "gray2bgr out")
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_gray2bgr_u8(src.data_ptr(), out.data_ptr(), src.numel(),
+                                                  _stream_ptr(stream)))
+    return out
+
+
+def flip(src, flip_code, *, out=None, stream=None):
+    """cv2.flip semantics: 0 vertical, >0 horizontal, <0 both."""
+    _require_cuda(src, "flip src")
+    n, h, w, c, _ = _nhwc(src)
+    out = _out(out, src.shape, src.device, "flip out")
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_flip_u8(src.data_ptr(), out.data_ptr(), n, h, w, c, int(flip_code),
+                                              _stream_ptr(stream)))
+    return out
+
+
+def crop(src, x0, y0, width, height, *, out=None, stream=None):
+    _require_cuda(src, "crop src")
+    n, h, w, c, gray = _nhwc(src)
+    shape = (n, height, width) if gray else (n, height, width, c)
+    out = _out(out, shape, src.device, "crop out")
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_crop_u8(src.data_ptr(), n, h, w, c, out.data_ptr(), int(x0), int(y0),
+                                              int(width), int(height), _stream_ptr(stream)))
+    return out

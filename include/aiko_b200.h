@@ -1,0 +1,123 @@
+/*
+ * aiko_b200.h -- C ABI of libaiko_b200.so: the B200 (sm_100a) implementation of
+ * aiko_services' per-frame media hot path.
+ *
+ * The reference is pure Python; it has no FFI of its own.  Each entry point
+ * below replaces the third-party library call made at the cited line of the
+ * reference element (R/ = src/aiko_services/ in rskew/aiko_services), batched
+ * over the frames of one process_frame() call.  INTEGRATION.md shows the ctypes
+ * binding a maintainer would add to those elements.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - images are uint8, interleaved channels (HWC), batched as N frames with an
+ *     explicit row stride and frame stride in bytes (tight: row = W*C,
+ *     frame = H*W*C);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); all
+ *     work is enqueued asynchronously on it;
+ *   - nothing here allocates or frees device memory: the caller passes outputs
+ *     and, where stated, a workspace;
+ *   - the return value is 0 (AIKO_B200_OK) or a negative AIKO_B200_ERR_* code;
+ *     aiko_b200_last_error() gives a thread-local message.  Errors never
+ *     abort() or throw across the ABI, so an element can map them to
+ *     StreamEvent.ERROR (R/main/pipeline.py:1057-1066).
+ */
+#ifndef AIKO_B200_H_
+#define AIKO_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AIKO_B200_OK 0
+#define AIKO_B200_ERR_INVALID_ARGUMENT (-1)
+#define AIKO_B200_ERR_UNSUPPORTED (-2)
+#define AIKO_B200_ERR_CUDA (-3)
+#define AIKO_B200_ERR_WORKSPACE (-4)
+
+#define AIKO_B200_ABI_VERSION 1
+
+int aiko_b200_abi_version(void);
+const char* aiko_b200_last_error(void);
+/* Name of the device the library would launch on, compute capability major*10+minor
+ * in *cc (must be 100 for the kernels to load).  Returns ERR_CUDA without a GPU. */
+int aiko_b200_device_info(char* name_host, size_t name_len, int* cc_host, int* sm_count_host);
+
+/* ---------------------------------------------------------------------- */
+/* Overlay draw list (ImageOverlay, R/elements/media/image_io.py:107-163). */
+/* One op = one cv2.rectangle or one rendered glyph of a cv2.putText label; */
+/* ops are applied in array order, per frame.                               */
+
+#define AIKO_B200_OP_RECT 0
+#define AIKO_B200_OP_GLYPH 1
+
+typedef struct aiko_b200_overlay_op {
+  int32_t kind;           /* AIKO_B200_OP_* */
+  int32_t x0, y0, x1, y1; /* RECT: corner points as given to cv2.rectangle (x0<=x1, y0<=y1);
+                             GLYPH: inclusive bounding box of touched pixels, image coordinates */
+  uint32_t p0;            /* RECT: colour, byte c = value stored to memory channel c;
+                             GLYPH: patch index for channel 0 | channel 1 << 16 */
+  uint32_t p1;            /* GLYPH: patch index for channel 2 */
+  uint32_t p2;            /* GLYPH: (x0 - patch_origin_x) | (y0 - patch_origin_y) << 16 */
+} aiko_b200_overlay_op;
+
+/* Glyph atlas: patch_ids[patch][patch_h][patch_w] are uint16 indices into
+ * luts[index][256] (index 0 = identity); a touched pixel becomes
+ * luts[id][old_value], which replays cv2.putText(..., LINE_AA) exactly. */
+typedef struct aiko_b200_overlay {
+  const aiko_b200_overlay_op* ops; /* device */
+  const int32_t* op_offsets;       /* device, [n_frames + 1]: frame i uses ops[op_offsets[i] .. op_offsets[i+1]) */
+  const uint16_t* patch_ids;       /* device, may be NULL when no GLYPH ops */
+  const uint8_t* luts;             /* device */
+  int32_t patch_w, patch_h;
+  int32_t n_patches;
+} aiko_b200_overlay;
+
+/* ---------------------------------------------------------------------- */
+/* ImageResize, ndarray branch: cv2.resize(image, (W, H)), INTER_LINEAR,   */
+/* bit-exact fixed-point arithmetic -- R/elements/media/image_io.py:216.   */
+/* Optionally fused with what the reference runs next on the same frames:  */
+/*   overlay  != NULL : ImageOverlay's drawing (image_io.py:107-163)       */
+/*   swap_rb  != 0    : cv2.cvtColor RGB<->BGR (video_io.py:129,299)       */
+/*                      applied to the stored pixels (op colours refer to   */
+/*                      the stored channel order).                          */
+/* channels in {1, 3, 4}.                                                   */
+int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int src_h, int src_w, int channels,
+                               int64_t src_row_stride, int64_t src_frame_stride, uint8_t* dst, int dst_h,
+                               int dst_w, int64_t dst_row_stride, int64_t dst_frame_stride, int swap_rb,
+                               const aiko_b200_overlay* overlay_host, void* stream);
+
+/* ImageOverlay alone on already-resident frames (image_io.py:107-163).     */
+/* channels == 3: frames are drawn in place of a copy src -> dst (src may   */
+/* equal dst).  channels == 1: the GRAY -> BGR -> draw -> BGR2GRAY round     */
+/* trip of image_io.py:115,158.                                             */
+int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_frames, int h, int w, int channels,
+                         int64_t row_stride, int64_t frame_stride, const aiko_b200_overlay* overlay_host,
+                         void* stream);
+
+/* ---------------------------------------------------------------------- */
+/* Colour conversion / flip / crop call sites.                              */
+
+/* cv2.cvtColor(.., COLOR_RGB2BGR / COLOR_BGR2RGB): image_io.py:117,160;   */
+/* video_io.py:129,214-216,299; webcam_io.py:122.  n_pixels 3-byte pixels.  */
+int aiko_b200_swap_rb_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, void* stream);
+/* cv2.cvtColor(.., COLOR_BGR2GRAY) (rgb_order=0) / COLOR_RGB2GRAY (1):      */
+/* webcam_io.py:124, image_io.py:158.                                        */
+int aiko_b200_bgr2gray_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, int rgb_order, void* stream);
+/* cv2.cvtColor(.., COLOR_GRAY2BGR): image_io.py:115.                        */
+int aiko_b200_gray2bgr_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, void* stream);
+/* cv2.flip(image, flip_code): webcam_io.py:127 (1, horizontal), :129 (0,    */
+/* vertical); flip_code < 0 flips both.  Tight frames [n, h, w, channels].   */
+int aiko_b200_flip_u8(const uint8_t* src, uint8_t* dst, int n_frames, int h, int w, int channels,
+                      int flip_code, void* stream);
+/* image[y0:y0+ch, x0:x0+cw] (numpy slicing as used on frames; north_star).  */
+int aiko_b200_crop_u8(const uint8_t* src, int n_frames, int h, int w, int channels, uint8_t* dst, int x0,
+                      int y0, int crop_w, int crop_h, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AIKO_B200_H_ */

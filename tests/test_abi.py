@@ -1,0 +1,41 @@
+"""CPU: the C-ABI library loads and exports every symbol include/aiko_b200.h declares."""
+import ctypes
+import os
+import re
+
+from aiko_services_b200 import _native
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "aiko_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(aiko_b200_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_and_bindings_agree():
+    assert declared_symbols() == sorted(_native.SIGNATURES)
+
+
+def test_library_exports_every_declared_symbol():
+    handle = ctypes.CDLL(_native.LIB_PATH)
+    for name in declared_symbols():
+        assert getattr(handle, name) is not None
+
+
+def test_version_and_error_string_without_gpu():
+    lib = _native.lib()
+    assert lib.aiko_b200_abi_version() == 1
+    # argument validation happens before any CUDA call, so it is testable on CPU
+    rc = lib.aiko_b200_swap_rb_u8(None, None, -1, None)
+    assert rc == _native.ERR_INVALID_ARGUMENT
+    assert b"n_pixels" in lib.aiko_b200_last_error()
+    rc = lib.aiko_b200_resize_linear_u8(1, 1, 4, 4, 2, 8, 32, 1, 2, 2, 4, 8, 0, None, None)
+    assert rc == _native.ERR_INVALID_ARGUMENT and b"channels" in lib.aiko_b200_last_error()
+    assert lib.aiko_b200_resize_linear_u8(None, 0, 4, 4, 3, 12, 48, None, 2, 2, 6, 12, 0, None, None) == 0
+
+
+def test_overlay_op_struct_layout():
+    assert ctypes.sizeof(_native.OverlayOp) == 32
+    assert ctypes.sizeof(_native.Overlay) == 48

@@ -1,0 +1,199 @@
+"""GPU parity: the CUDA path through the C ABI against the CPU oracle (bit-exact), the golden
+vectors of the reference, and size-independent properties at BASELINE's full sizes."""
+import numpy as np
+import pytest
+import torch
+
+from aiko_services_b200 import ops
+from aiko_services_b200.overlay_plan import build_ops
+from aiko_services_b200.text_atlas import TextAtlas
+from golden import cases
+from oracle import image as O
+from util import check_golden, overlay_cpu, random_overlay
+
+pytestmark = pytest.mark.gpu
+
+
+def dev(arr, cuda):
+    return torch.from_numpy(np.ascontiguousarray(arr)).to(cuda)
+
+
+def host(t):
+    return t.cpu().numpy()
+
+
+@pytest.fixture(scope="module")
+def atlas():
+    return TextAtlas()
+
+
+# ---------------------------------------------------------------- resize (a-1)
+@pytest.mark.parametrize("case", cases.RESIZE_NDARRAY, ids=lambda c: c[0])
+def test_resize_linear_golden(golden, cuda, case):
+    name, seed, sh, sw, c, dw, dh = case
+    img = cases.frame(seed, sh, sw, c)
+    out = host(ops.resize_linear(dev(img[None], cuda), dw, dh))[0]
+    check_golden(golden, "resize/" + name, out)
+
+
+def test_resize_linear_random_shapes_vs_oracle(cuda):
+    rng = np.random.default_rng(101)
+    for i in range(60):
+        h, w, H, W = (int(v) for v in rng.integers(1, 260, 4))
+        c = int(rng.choice([1, 3, 4]))
+        if i % 3 == 0:
+            w = 16 * int(rng.integers(1, 20))      # 16-byte aligned rows take the TMA-staged kernel
+        n = int(rng.integers(1, 4))
+        frames = np.stack([cases.frame(1000 * i + k, h, w, c) for k in range(n)])
+        out = host(ops.resize_linear(dev(frames, cuda), W, H))
+        for k in range(n):
+            np.testing.assert_array_equal(out[k], O.resize_linear(frames[k], W, H), err_msg=f"{(h, w, c)}->{(H, W)}")
+
+
+def test_resize_linear_unaligned_base_pointer(cuda):
+    frames = np.stack([cases.frame(77, 48, 64, 3)])
+    buf = torch.empty(frames.size + 1, dtype=torch.uint8, device=cuda)
+    view = buf[1:].view(frames.shape)
+    view.copy_(dev(frames, cuda))
+    assert view.data_ptr() % 16 != 0
+    # a view is contiguous in the sense the ABI needs (tight strides)
+    out = host(ops.resize_linear(view, 20, 30))
+    np.testing.assert_array_equal(out[0], O.resize_linear(frames[0], 20, 30))
+
+
+def test_resize_linear_edge_values(cuda):
+    for v in (0, 255):
+        img = np.full((2, 90, 160, 3), v, np.uint8)
+        assert (host(ops.resize_linear(dev(img, cuda), 37, 41)) == v).all()
+    grad = np.tile(np.arange(256, dtype=np.uint8)[None, None, :, None], (1, 64, 1, 3))
+    np.testing.assert_array_equal(host(ops.resize_linear(dev(grad, cuda), 100, 30))[0], O.resize_linear(grad[0], 100, 30))
+
+
+def test_resize_linear_empty_batch_and_bad_args(cuda):
+    empty = torch.empty((0, 8, 8, 3), dtype=torch.uint8, device=cuda)
+    assert ops.resize_linear(empty, 4, 4).shape == (0, 4, 4, 3)
+    with pytest.raises(RuntimeError):
+        ops.resize_linear(torch.zeros((1, 8, 8, 3), dtype=torch.uint8), 4, 4)       # host tensor: no CPU path
+    with pytest.raises(Exception):
+        ops.resize_linear(torch.zeros((1, 8, 8, 2), dtype=torch.uint8, device=cuda), 4, 4)
+
+
+def test_resize_cfg2_batch_properties(cuda):
+    """BASELINE config 2 size (32 x 1080p -> 640x480): every frame equals the oracle; identical
+    inputs give identical outputs wherever they sit in the batch; swap_rb commutes."""
+    frames = np.stack([cases.frame(2000 + (i % 4), 1080, 1920, 3) for i in range(32)])
+    d = dev(frames, cuda)
+    out = host(ops.resize_linear(d, 640, 480))
+    refs = [O.resize_linear(frames[i], 640, 480) for i in range(4)]
+    for i in range(32):
+        np.testing.assert_array_equal(out[i], refs[i % 4])
+    swapped = host(ops.resize_linear(d, 640, 480, swap_rb=True))
+    np.testing.assert_array_equal(swapped, out[..., ::-1])
+
+
+# ---------------------------------------------------------------- convert / flip / crop (a-4)
+@pytest.mark.parametrize("n_pixels", [0, 1, 15, 16, 17, 4097, 640 * 480, 1920 * 1080 + 5])
+def test_convert_ops_vs_oracle(cuda, n_pixels):
+    rng = np.random.default_rng(n_pixels)
+    rgb = rng.integers(0, 256, (1, 1, n_pixels, 3), dtype=np.uint8)
+    gray = rng.integers(0, 256, (1, 1, n_pixels), dtype=np.uint8)
+    d = dev(rgb, cuda)
+    if n_pixels == 0:
+        assert ops.swap_rb(d).numel() == 0 and ops.bgr2gray(d).numel() == 0
+        return
+    np.testing.assert_array_equal(host(ops.swap_rb(d)), rgb[..., ::-1])
+    np.testing.assert_array_equal(host(ops.bgr2gray(d))[0], O.bgr2gray(rgb[0]))
+    np.testing.assert_array_equal(host(ops.bgr2gray(d, rgb_order=True))[0], O.bgr2gray(rgb[0], True))
+    np.testing.assert_array_equal(host(ops.gray2bgr(dev(gray, cuda)))[0], O.gray2bgr(gray[0]))
+
+
+def test_swap_is_involution_full_size(cuda):
+    frames = dev(np.stack([cases.frame(9, 1080, 1920, 3)] * 2), cuda)
+    assert torch.equal(ops.swap_rb(ops.swap_rb(frames)), frames)
+
+
+@pytest.mark.parametrize("shape", [(2, 37, 53, 3), (1, 48, 64, 3), (3, 20, 33, 1), (1, 9, 16, 4), (1, 1080, 1920, 3)])
+@pytest.mark.parametrize("code", [0, 1, -1])
+def test_flip_vs_oracle(cuda, shape, code):
+    n, h, w, c = shape
+    frames = np.stack([cases.frame(50 + k, h, w, c) for k in range(n)])
+    out = host(ops.flip(dev(frames, cuda), code))
+    for k in range(n):
+        np.testing.assert_array_equal(out[k], O.flip(frames[k], code))
+
+
+def test_crop_vs_numpy(cuda):
+    frames = np.stack([cases.frame(60 + k, 70, 90, 3) for k in range(3)])
+    d = dev(frames, cuda)
+    for (x0, y0, w, h) in [(0, 0, 90, 70), (16, 8, 32, 40), (5, 3, 17, 11), (89, 69, 1, 1), (10, 10, 0, 5)]:
+        np.testing.assert_array_equal(host(ops.crop(d, x0, y0, w, h)), frames[:, y0:y0 + h, x0:x0 + w])
+    with pytest.raises(Exception):
+        ops.crop(d, 80, 0, 20, 10)
+
+
+# ---------------------------------------------------------------- overlay (a-3)
+def device_overlay(overlays, w, h, layout, atlas, cuda):
+    per_frame = [build_ops(o, w, h, layout, atlas) for o in overlays]
+    return ops.DeviceOverlay.from_host(per_frame, cuda, atlas.device(cuda))
+
+
+@pytest.mark.parametrize("case", cases.OVERLAY, ids=lambda c: c[0])
+def test_overlay_golden(golden, cuda, atlas, case):
+    name, seed, h, w, c, overlay = case
+    img = cases.frame(seed, h, w, c)
+    ov = device_overlay([overlay], w, h, "rgb" if c == 3 else "bgr", atlas, cuda)
+    out = host(ops.overlay_draw(dev(img[None], cuda), ov))[0]
+    check_golden(golden, "overlay/" + name, out)
+
+
+def test_overlay_random_vs_oracle_replay(cuda, atlas):
+    rng = np.random.default_rng(202)
+    for i in range(12):
+        h, w = int(rng.integers(40, 200)), int(rng.integers(60, 320))
+        c = 1 if i % 4 == 0 else 3
+        n = 3
+        frames = np.stack([cases.frame(300 + 10 * i + k, h, w, c) for k in range(n)])
+        overlays = [random_overlay(rng, w, h, n=int(rng.integers(0, 9))) for _ in range(n)]
+        ov = device_overlay(overlays, w, h, "rgb" if c == 3 else "bgr", atlas, cuda)
+        out = host(ops.overlay_draw(dev(frames, cuda), ov))
+        for k in range(n):
+            np.testing.assert_array_equal(out[k], overlay_cpu(frames[k], overlays[k], atlas))
+
+
+def test_overlay_many_ops_per_frame(cuda, atlas):
+    rng = np.random.default_rng(203)
+    h, w = 240, 320
+    overlay = random_overlay(rng, w, h, n=70)     # > 256 ops: several cull passes per row
+    img = cases.frame(204, h, w, 3)
+    ov = device_overlay([overlay], w, h, "rgb", atlas, cuda)
+    assert int(ov.op_offsets[-1]) > 256
+    np.testing.assert_array_equal(host(ops.overlay_draw(dev(img[None], cuda), ov))[0], overlay_cpu(img, overlay, atlas))
+
+
+# ---------------------------------------------------------------- fused chain (config 2)
+def test_fused_chain_golden(golden, cuda, atlas):
+    frames = np.stack([cases.frame(2000 + i, 1080, 1920, 3) for i in range(2)])
+    ov = device_overlay([cases.OVERLAY_4] * 2, 640, 480, "rgb", atlas, cuda)
+    out = host(ops.resize_linear(dev(frames, cuda), 640, 480, overlay=ov))
+    for i in range(2):
+        check_golden(golden, f"chain/cfg2_{i}", out[i])
+    # ... and with the encoder-side RGB->BGR folded in (video_io.py:299)
+    ov_bgr = device_overlay([cases.OVERLAY_4] * 2, 640, 480, "bgr", atlas, cuda)
+    out_bgr = host(ops.resize_linear(dev(frames, cuda), 640, 480, swap_rb=True, overlay=ov_bgr))
+    np.testing.assert_array_equal(out_bgr, out[..., ::-1])
+
+
+def test_fused_equals_unfused_random(cuda, atlas):
+    rng = np.random.default_rng(205)
+    for i in range(6):
+        h, w = int(rng.integers(60, 300)), 16 * int(rng.integers(4, 30))
+        H, W = int(rng.integers(40, 200)), int(rng.integers(60, 320))
+        frames = np.stack([cases.frame(400 + 10 * i + k, h, w, 3) for k in range(3)])
+        overlays = [random_overlay(rng, W, H) for _ in range(3)]
+        ov = device_overlay(overlays, W, H, "rgb", atlas, cuda)
+        d = dev(frames, cuda)
+        fused = ops.resize_linear(d, W, H, overlay=ov)
+        unfused = ops.overlay_draw(ops.resize_linear(d, W, H), ov)
+        assert torch.equal(fused, unfused)
+        for k in range(3):
+            np.testing.assert_array_equal(host(fused)[k], overlay_cpu(O.resize_linear(frames[k], W, H), overlays[k], atlas))

@@ -1,0 +1,87 @@
+"""CPU: the C oracle against the golden vectors produced by the reference's own elements,
+and directly against cv2 / Pillow where they are installed."""
+import numpy as np
+import pytest
+
+from golden import cases
+from oracle import image as O
+from util import check_golden
+
+
+@pytest.mark.parametrize("case", cases.RESIZE_NDARRAY, ids=lambda c: c[0])
+def test_resize_linear_golden(golden, case):
+    name, seed, sh, sw, c, dw, dh = case
+    check_golden(golden, "resize/" + name, O.resize_linear(cases.frame(seed, sh, sw, c), dw, dh))
+
+
+@pytest.mark.parametrize("case", cases.RESIZE_PIL, ids=lambda c: c[0])
+def test_resize_bicubic_golden(golden, case):
+    name, seed, sh, sw, dw, dh = case
+    check_golden(golden, "resize_pil/" + name, O.resize_bicubic_aa(cases.frame(seed, sh, sw, 3), dw, dh))
+
+
+def test_resize_linear_vs_cv2_random_shapes():
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(7)
+    for _ in range(120):
+        h, w, H, W = (int(v) for v in rng.integers(1, 200, 4))
+        c = int(rng.choice([1, 3, 4]))
+        img = cases.frame(int(rng.integers(1 << 30)), h, w, c)
+        np.testing.assert_array_equal(O.resize_linear(img, W, H), cv2.resize(img, (W, H)))
+
+
+def test_resize_bicubic_vs_pillow_random_shapes():
+    Image = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(8)
+    for _ in range(40):
+        h, w, H, W = (int(v) for v in rng.integers(1, 150, 4))
+        img = cases.frame(int(rng.integers(1 << 30)), h, w, 3)
+        ref = np.asarray(Image.fromarray(img, "RGB").resize((W, H)))
+        np.testing.assert_array_equal(O.resize_bicubic_aa(img, W, H), ref)
+
+
+def test_saturation_edges():
+    cv2 = pytest.importorskip("cv2")
+    for v in (0, 255):
+        img = np.full((40, 50, 3), v, np.uint8)
+        assert (O.resize_linear(img, 23, 17) == v).all()
+        assert (O.resize_bicubic_aa(img, 23, 17) == v).all()
+    grad = np.tile(np.arange(256, dtype=np.uint8)[None, :, None], (64, 1, 3))
+    np.testing.assert_array_equal(O.resize_linear(grad, 100, 30), cv2.resize(grad, (100, 30)))
+
+
+def test_convert_flip_vs_cv2():
+    cv2 = pytest.importorskip("cv2")
+    img = cases.frame(5, 67, 93, 3)
+    gray = cases.frame(6, 67, 93, 1)
+    np.testing.assert_array_equal(O.swap_rb(img), cv2.cvtColor(img, cv2.COLOR_RGB2BGR))
+    np.testing.assert_array_equal(O.swap_rb(img), img[..., ::-1])
+    np.testing.assert_array_equal(O.bgr2gray(img), cv2.cvtColor(img, cv2.COLOR_BGR2GRAY))
+    np.testing.assert_array_equal(O.bgr2gray(img, True), cv2.cvtColor(img, cv2.COLOR_RGB2GRAY))
+    np.testing.assert_array_equal(O.gray2bgr(gray), cv2.cvtColor(gray, cv2.COLOR_GRAY2BGR))
+    for code in (0, 1, -1):
+        np.testing.assert_array_equal(O.flip(img, code), cv2.flip(img, code))
+        np.testing.assert_array_equal(O.flip(gray, code), cv2.flip(gray, code))
+
+
+def test_rectangle_vs_cv2_random():
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(9)
+    for _ in range(1500):
+        h, w = (int(v) for v in rng.integers(4, 80, 2))
+        a = cases.frame(int(rng.integers(1 << 30)), h, w, 3)
+        b = a.copy()
+        x0, x1 = (int(v) for v in rng.integers(-20, w + 20, 2))
+        y0, y1 = (int(v) for v in rng.integers(-20, h + 20, 2))
+        cv2.rectangle(a, (x0, y0), (x1, y1), (0, 255, 255), 2)
+        O.rectangle(b, x0, y0, x1, y1, (0, 255, 255))
+        np.testing.assert_array_equal(a, b)
+
+
+def test_resize_norm_f32_matches_numpy():
+    img = cases.frame(3, 120, 160, 3)
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    u8 = O.resize_linear(img, 56, 56)
+    ref = ((u8.astype(np.float32) / np.float32(255) - np.asarray(mean, np.float32)) /
+           np.asarray(std, np.float32)).transpose(2, 0, 1)
+    np.testing.assert_array_equal(O.resize_norm_f32(img, 56, 56, mean, std), ref)
