@@ -47,18 +47,30 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity, uint32_t suspend_ns) {
+  uint32_t ok;
   asm volatile(
       "{\n\t"
       ".reg .pred p;\n\t"
-      "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE_%=;\n\t"
-      "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t"
-      "}" ::"r"(smem_u32(bar)),
-      "r"(parity)
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(suspend_ns)
       : "memory");
+  return ok != 0;
+}
+// Blocks until the phase with the given parity completes.  The hardware suspends the thread
+// for up to `suspend_ns` per probe and failed probes back off with nanosleep, so a waiting
+// warp does not compete with working warps for issue slots.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t suspend_ns = 1000,
+                                          uint32_t backoff_ns = 0) {
+  while (!mbar_try_wait(bar, parity, suspend_ns)) {
+    if (backoff_ns) __nanosleep(backoff_ns);
+  }
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 // 1-D bulk async copy global -> shared (TMA engine), completion on an mbarrier.
 // dst, src 16-byte aligned; bytes a multiple of 16.

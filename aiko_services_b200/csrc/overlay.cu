@@ -16,8 +16,7 @@ struct OverlayParams {
 
 __global__ void __launch_bounds__(kThreads) overlay_rows_kernel(const OverlayParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
-  uint32_t* mask = reinterpret_cast<uint32_t*>(smem);
-  uint8_t* row = smem + 32;
+  uint8_t* row = smem;
   const long long rows = (long long)p.n * p.h;
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
     const int n = (int)(r / p.h), y = (int)(r - (long long)n * p.h);
@@ -35,7 +34,9 @@ __global__ void __launch_bounds__(kThreads) overlay_rows_kernel(const OverlayPar
       for (int x = threadIdx.x; x < p.w; x += kThreads) row[3 * x] = row[3 * x + 1] = row[3 * x + 2] = s[x];
     }
     __syncthreads();
-    overlay_apply_row(p.ov, n, y, p.w, row, mask);
+    const int ob = p.ov.op_offsets[n];
+    overlay_apply_row(p.ov.ops + ob, p.ov.op_offsets[n + 1] - ob, p.ov, y, p.w, row, kThreads);
+    __syncthreads();
     if (p.channels == 3) {
       store_row(p.dst + o, row, p.w * 3);
     } else {
@@ -66,7 +67,7 @@ extern "C" int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_fram
   p.row_stride = row_stride; p.frame_stride = frame_stride;
   p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
                     overlay->patch_h};
-  const size_t smem = 32 + (((size_t)w * 3 + 15) & ~(size_t)15);
+  const size_t smem = ((size_t)w * 3 + 15) & ~(size_t)15;
   AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "overlay: row of %zu bytes exceeds shared memory", smem);
   AIKO_CUDA(cudaFuncSetAttribute(overlay_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long rows = (long long)n_frames * h;

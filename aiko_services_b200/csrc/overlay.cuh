@@ -6,6 +6,7 @@
 
 namespace aiko {
 
+
 struct OverlayDev {
   const aiko_b200_overlay_op* ops;
   const int32_t* op_offsets;
@@ -22,68 +23,126 @@ __device__ __forceinline__ bool rect_covers(int x, int y, int xa, int ya, int xb
   return true;
 }
 
-// Applies, in order, every op of frame `frame` that touches image row `y` to
-// `row` (w pixels x 3 bytes, shared memory).  Must be called by all threads of
-// the CTA with CTA-uniform arguments; `mask` is kThreads/32 words of shared
-// scratch.  Ends with the row consistent for all threads (__syncthreads).
-__device__ __forceinline__ void overlay_apply_row(const OverlayDev& ov, int frame, int y, int w, uint8_t* row,
-                                                  uint32_t* mask) {
-  const int ob = ov.op_offsets[frame], oe = ov.op_offsets[frame + 1];
-  for (int base = ob; base < oe; base += kThreads) {
-    // parallel cull by row range, order preserved through the bit position
-    const int i = base + threadIdx.x;
-    bool hit = false;
-    if (i < oe) {
-      const aiko_b200_overlay_op* op = ov.ops + i;
-      const int kind = op->kind;
-      const int ylo = op->y0 - (kind == AIKO_B200_OP_RECT ? 1 : 0);
-      const int yhi = op->y1 + (kind == AIKO_B200_OP_RECT ? 1 : 0);
-      hit = (y >= ylo) && (y <= yhi);
+__device__ __forceinline__ void put_rgb(uint8_t* row, int x, uint32_t colour) {
+  row[3 * x + 0] = colour & 0xff;
+  row[3 * x + 1] = (colour >> 8) & 0xff;
+  row[3 * x + 2] = (colour >> 16) & 0xff;
+}
+
+// ---------------------------------------------------------------------------------------
+// Ownership: pixels 4g .. 4g+3 ("group" g) belong to worker thread g % nthreads -- the same
+// mapping the resize kernels use when they produce the row -- so a thread only ever
+// read-modify-writes its own pixels and the replay needs no barrier: draw order is kept per
+// pixel by program order.
+
+// Columns of row y that op can touch: two intervals [a0,a1] and [b0,b1] (equal for glyphs and
+// for the top / bottom bands of a rectangle; the two 3-pixel side bands otherwise).
+struct OpSpan {
+  int a0, a1, b0, b1;
+  bool row_hit;
+};
+__device__ __forceinline__ OpSpan op_span(const aiko_b200_overlay_op* op, int y) {
+  OpSpan s;
+  const int kind = op->kind, x0 = op->x0, y0 = op->y0, x1 = op->x1, y1 = op->y1;
+  if (kind == AIKO_B200_OP_RECT) {
+    s.row_hit = (y >= y0 - 1) && (y <= y1 + 1);
+    const bool band = (y <= y0 + 1) || (y >= y1 - 1);
+    s.a0 = x0 - 1;
+    s.b1 = x1 + 1;
+    s.a1 = band ? x1 + 1 : x0 + 1;
+    s.b0 = band ? x0 - 1 : x1 - 1;
+  } else {
+    s.row_hit = (y >= y0) && (y <= y1);
+    s.a0 = s.b0 = x0;
+    s.a1 = s.b1 = x1;
+  }
+  return s;
+}
+__device__ __forceinline__ bool span_meets(const OpSpan& s, int lo, int hi) {
+  return (s.a0 <= hi && s.a1 >= lo) || (s.b0 <= hi && s.b1 >= lo);
+}
+
+// One lane applies one op to its pixels [mlo, mhi] of row y.
+__device__ __forceinline__ void apply_op_to_pixels(const aiko_b200_overlay_op* op, const OverlayDev& ov, int y,
+                                                   int mlo, int mhi, uint8_t* row) {
+  if (op->kind == AIKO_B200_OP_RECT) {
+    const int x0 = op->x0, x1 = op->x1, y0 = op->y0, y1 = op->y1;
+    const uint32_t colour = op->p0;
+    for (int x = max(mlo, x0 - 1); x <= min(mhi, x1 + 1); x++)
+      if (rect_covers(x, y, x0, y0, x1, y1)) put_rgb(row, x, colour);
+  } else {
+    const int xs = max(mlo, op->x0), xe = min(mhi, op->x1);
+    const int psize = ov.patch_w * ov.patch_h;
+    const uint32_t p0 = op->p0, p1 = op->p1, p2 = op->p2;
+    const int px = op->x0 - int(p2 & 0xffff), py = op->y0 - int(p2 >> 16);
+    const uint16_t* q = ov.patch_ids + (y - py) * ov.patch_w - px;
+    const uint16_t* q0 = q + (size_t)(p0 & 0xffff) * psize;
+    const uint16_t* q1 = q + (size_t)(p0 >> 16) * psize;
+    const uint16_t* q2 = q + (size_t)(p1 & 0xffff) * psize;
+    uint16_t id[4][3];
+    uint8_t val[4][3];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {          // all id look-ups first ...
+      const int x = min(xs + k, xe);
+      id[k][0] = __ldg(q0 + x); id[k][1] = __ldg(q1 + x); id[k][2] = __ldg(q2 + x);
     }
-    const uint32_t m = __ballot_sync(0xffffffffu, hit);
-    if ((threadIdx.x & 31) == 0) mask[threadIdx.x >> 5] = m;
-    __syncthreads();
-#pragma unroll 1
-    for (int wd = 0; wd < kThreads / 32; wd++) {
-      uint32_t bits = mask[wd];
-      while (bits) {
-        const int b = __ffs(bits) - 1;
-        bits &= bits - 1;
-        const aiko_b200_overlay_op op = ov.ops[base + wd * 32 + b];
-        if (op.kind == AIKO_B200_OP_RECT) {
-          const int xs = max(op.x0 - 1, 0), xe = min(op.x1 + 1, w - 1);
-          const bool full = (y <= op.y0 + 1) || (y >= op.y1 - 1);  // top / bottom band: whole span
-          if (full || op.x1 - op.x0 < 6) {
-            for (int x = xs + threadIdx.x; x <= xe; x += kThreads)
-              if (rect_covers(x, y, op.x0, op.y0, op.x1, op.y1)) {
-                row[3 * x + 0] = op.p0 & 0xff;
-                row[3 * x + 1] = (op.p0 >> 8) & 0xff;
-                row[3 * x + 2] = (op.p0 >> 16) & 0xff;
-              }
-          } else if (threadIdx.x < 6) {  // side bands: 3 pixels at each side
-            const int x = (threadIdx.x < 3) ? op.x0 - 1 + threadIdx.x : op.x1 - 1 + (threadIdx.x - 3);
-            if (x >= 0 && x < w) {
-              row[3 * x + 0] = op.p0 & 0xff;
-              row[3 * x + 1] = (op.p0 >> 8) & 0xff;
-              row[3 * x + 2] = (op.p0 >> 16) & 0xff;
-            }
-          }
-        } else {
-          const int px = op.x0 - int(op.p2 & 0xffff), py = op.y0 - int(op.p2 >> 16);
-          const int xs = max(op.x0, 0), xe = min(op.x1, w - 1);
-          const int prow = (y - py) * ov.patch_w - px;
-          const int span = xe - xs + 1;
-          for (int t = threadIdx.x; t < span * 3; t += kThreads) {
-            const int x = xs + t / 3, c = t - (t / 3) * 3;
-            const uint32_t pid = (c == 0) ? (op.p0 & 0xffff) : (c == 1) ? (op.p0 >> 16) : (op.p1 & 0xffff);
-            const uint16_t id = ov.patch_ids[(size_t)pid * (ov.patch_w * ov.patch_h) + prow + x];
-            if (id) row[3 * x + c] = ov.luts[(size_t)id * 256 + row[3 * x + c]];
-          }
-        }
-        __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 4; k++) {          // ... then all transfer-table look-ups
+      const uint8_t* d = row + 3 * min(xs + k, xe);
+#pragma unroll
+      for (int c = 0; c < 3; c++) val[k][c] = id[k][c] ? __ldg(ov.luts + (size_t)id[k][c] * 256 + d[c]) : d[c];
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+      if (xs + k <= xe) {
+        uint8_t* d = row + 3 * (xs + k);
+        d[0] = val[k][0]; d[1] = val[k][1]; d[2] = val[k][2];
       }
+  }
+}
+
+// The warp applies the ops flagged in `hits` (bit b = ops32[b], in order) to the pixels its
+// lanes own.  Every lane walks the list for the next op that touches ITS pixels, then the lanes
+// apply their (different) ops together, so the two dependent atlas look-ups of a glyph are
+// paid once per round rather than once per op.
+__device__ __forceinline__ void overlay_apply_hits(const aiko_b200_overlay_op* ops32, uint32_t hits,
+                                                   const OverlayDev& ov, int y, int mlo, int mhi, uint8_t* row) {
+  uint32_t rem = hits;   // every lane keeps its own cursor into the hit list
+  while (true) {
+    const aiko_b200_overlay_op* op = nullptr;
+    while (rem) {
+      const int b = __ffs(rem) - 1;
+      rem &= rem - 1;
+      const aiko_b200_overlay_op* cand = ops32 + b;
+      if (span_meets(op_span(cand, y), mlo, mhi)) { op = cand; break; }
     }
-    __syncthreads();  // mask is rewritten by the next batch of ops
+    if (!__any_sync(0xffffffffu, op != nullptr)) break;
+    if (op != nullptr) apply_op_to_pixels(op, ov, y, mlo, mhi, row);
+  }
+}
+
+// Self-contained replay for a CTA of `nthreads` worker threads: applies, in order, every op of
+// ops[0 .. nops) that touches image row `y` to `row` (w pixels x 3 bytes, shared memory).
+// Culling is warp-local (32 ops per ballot).  Callers order the row's producers before, and
+// its consumers after, with __syncthreads().
+__device__ __forceinline__ void overlay_apply_row(const aiko_b200_overlay_op* ops, int nops, const OverlayDev& ov,
+                                                  int y, int w, uint8_t* row, int nthreads) {
+  if (nops == 0) return;
+  const int lane = threadIdx.x & 31;
+  const int groups = (w + 3) >> 2;
+  for (int gbase = (threadIdx.x & ~31); gbase < groups; gbase += nthreads) {   // warp-uniform
+    const int wlo = gbase * 4, whi = min(wlo + 127, w - 1);                    // the warp's pixel span
+    const int mlo = (gbase + lane) * 4, mhi = min(mlo + 3, w - 1);             // this lane's pixels
+    for (int base = 0; base < nops; base += 32) {
+      const int i = base + lane;
+      bool hit = false;
+      if (i < nops) {
+        const OpSpan s = op_span(ops + i, y);
+        hit = s.row_hit && span_meets(s, wlo, whi);
+      }
+      const uint32_t hits = __ballot_sync(0xffffffffu, hit);
+      if (hits) overlay_apply_hits(ops + base, hits, ov, y, mlo, mhi, row);
+    }
   }
 }
 

@@ -3,13 +3,18 @@
 // fused with ImageOverlay's drawing (image_io.py:127-155) and an RGB<->BGR swap
 // (R/elements/media/video_io.py:299).
 //
-// Work item = one output row of one frame.  Persistent CTAs stride over the items.  In the
-// staged variant the two source rows an output row needs are pulled into shared memory by
-// the TMA engine (1-D cp.async.bulk, mbarrier completion) through a ring of `stages`
-// slots, so every 32-byte sector of a needed source row crosses HBM exactly once and the
-// SM's load/store units only see shared memory.  The gather variant (unaligned rows, or
-// horizontal scale > 4 where most sectors of a row carry no weight) reads taps directly
-// from global memory.
+// Work item = one output row of one frame; each CTA owns a contiguous run of items.
+//
+// resize3_staged (RGB frames with 16-byte aligned rows, horizontal scale <= 4): the two
+// source rows an output row needs are pulled into shared memory by the TMA engine (1-D
+// cp.async.bulk, mbarrier completion) through a ring of stages, so every 32-byte sector of
+// a needed source row crosses HBM exactly once and the SM's load/store units only see shared
+// memory.  A thread produces 4 consecutive output pixels: taps are fetched as aligned words,
+// the horizontal pass is one dp2a per channel (two 11-bit weights x two 8-bit taps), the
+// vertical pass one mad.hi per source row.
+//
+// resize_rows_generic (1/4 channels, unaligned rows, or scale > 4 where most sectors of a
+// source row carry no weight): same row structure, taps read straight from global memory.
 #include "overlay.cuh"
 
 namespace aiko {
@@ -23,7 +28,7 @@ struct ResizeParams {
   int swap_rb, has_overlay;
   OverlayDev ov;
   int stages, seg_stride, row_bytes;
-  long long items;
+  int items, items_per_cta;
 };
 
 // cv2's coefficient derivation (float32 phase from a double position, 11-bit weights).
@@ -38,164 +43,389 @@ __device__ __forceinline__ void linear_coef(int d, double scale, int* s_out, flo
 }
 __device__ __forceinline__ int coef_q11(float f) { return __float2int_rn(__fmul_rn(f, 2048.f)); }
 
-__device__ __forceinline__ int vblend(int r0, int r1, int b0, int b1) {
-  const int v = (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2;
-  return min(max(v, 0), 255);
+__device__ __forceinline__ void horizontal_coef(int dx, double scale, int sw, int* s_out, uint32_t* packed) {
+  int s;
+  float f;
+  linear_coef(dx, scale, &s, &f);
+  if (s < 0) { s = 0; f = 0.f; }
+  if (s >= sw - 1) { s = sw - 1; f = 0.f; }
+  const int a0 = coef_q11(__fsub_rn(1.f, f)), a1 = coef_q11(f);
+  *s_out = s;
+  *packed = (uint32_t)(a0 & 0xffff) | ((uint32_t)a1 << 16);
 }
 
-template <int C, bool STAGED>
-__global__ void __launch_bounds__(kThreads) resize_linear_rows(const ResizeParams p) {
+struct RowCoef {
+  int y0, y1, b0, b1;
+};
+__device__ __forceinline__ RowCoef vertical_coef(int dy, double scale, int sh) {
+  int sy;
+  float fy;
+  linear_coef(dy, scale, &sy, &fy);
+  RowCoef r;
+  r.b0 = coef_q11(__fsub_rn(1.f, fy));
+  r.b1 = coef_q11(fy);
+  r.y0 = min(max(sy, 0), sh - 1);
+  r.y1 = min(max(sy + 1, 0), sh - 1);
+  return r;
+}
+
+// ((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2 with b pre-shifted by 16.
+// The sum never exceeds 1020, so no saturation is needed.
+__device__ __forceinline__ uint32_t vblend_hi(uint32_t r0, uint32_t r1, uint32_t b0s, uint32_t b1s) {
+  return (__umulhi(b0s, r0 >> 4) + __umulhi(b1s, r1 >> 4) + 2u) >> 2;
+}
+
+// ---------------------------------------------------------------------------------------
+// Row scheduling shared by the producer warp and the consumer warps of resize3_staged: CTA c
+// takes chunks c, c + G, c + 2G, ... of `chunk` consecutive output rows, so rows being read at
+// the same time are neighbours in memory and label rows (slow) are spread over many CTAs.
+constexpr int kMaskWords = 4;   // producer-side culling handles frames with up to 128 draw-list entries
+constexpr int kRecHeader = 8;   // ints: n, dy, b0 << 16, b1 << 16, first op, op count, -, -
+
+// Row scheduling of resize3_staged: CTA c takes chunks c, c + G, c + 2G, ... of `chunk`
+// consecutive output rows, so rows being read at the same time are neighbours in memory and
+// label rows (slow) are spread over many CTAs.
+struct RowIter {
+  int item, left, n, dy;
+  __device__ __forceinline__ void start(int first_item, int items, int chunk, int dh) {
+    item = first_item;
+    left = min(chunk, items - first_item);
+    n = first_item / dh;
+    dy = first_item - n * dh;
+  }
+  __device__ __forceinline__ bool valid(int items) const { return item < items; }
+  __device__ __forceinline__ void next(int items, int chunk, int stride_items, int dh) {
+    if (--left > 0) {
+      ++item;
+      if (++dy == dh) { dy = 0; ++n; }
+    } else {
+      item += stride_items - chunk + 1;
+      if (item < items) start(item, items, chunk, dh);
+    }
+  }
+};
+
+// One RGB output pixel from the 2x2 taps around it.  lo/hi hold the 6 source bytes of a row
+// (t0c0 t0c1 t0c2 t1c0 | t1c1 t1c2 . .), coef = a0 | a1 << 16.
+__device__ __forceinline__ void pixel_general(uint32_t ulo, uint32_t uhi, uint32_t vlo, uint32_t vhi, uint32_t coef,
+                                              uint32_t b0s, uint32_t b1s, uint32_t* c0, uint32_t* c1, uint32_t* c2) {
+  const uint32_t up01 = __byte_perm(ulo, uhi, 0x4130), up2 = __byte_perm(ulo, uhi, 0x0052);
+  const uint32_t vp01 = __byte_perm(vlo, vhi, 0x4130), vp2 = __byte_perm(vlo, vhi, 0x0052);
+  *c0 = vblend_hi(__dp2a_lo(coef, up01, 0u), __dp2a_lo(coef, vp01, 0u), b0s, b1s);
+  *c1 = vblend_hi(__dp2a_hi(coef, up01, 0u), __dp2a_hi(coef, vp01, 0u), b0s, b1s);
+  *c2 = vblend_hi(__dp2a_lo(coef, up2, 0u), __dp2a_lo(coef, vp2, 0u), b0s, b1s);
+}
+// Same arithmetic when every horizontal weight pair is (2048, 0) -- an odd integer scale such
+// as 1920 -> 640: R = 2048 * tap, so (b * (R >> 4)) >> 16 == (b * tap) >> 9, computed as
+// umulhi(b << 15, tap << 8) (b <= 2048 keeps b << 15 inside 32 bits).
+__device__ __forceinline__ uint32_t vblend_decim(uint32_t t0, uint32_t t1, uint32_t b0d, uint32_t b1d) {
+  return (__umulhi(b0d, t0) + __umulhi(b1d, t1) + 2u) >> 2;
+}
+
+// DECIM: horizontal pass degenerates to picking one source pixel (all weights 2048, 0).
+template <bool DECIM>
+__device__ __forceinline__ void consume_row(const uint8_t* r0, const uint8_t* r1, const int* xw, const int* xs,
+                                            const uint32_t* xcoef, uint8_t* orow, int g_first, int g_step, int groups,
+                                            uint32_t b0, uint32_t b1, uint32_t sel_rgb) {
+  const uint32_t b0s = DECIM ? (b0 << 15) : (b0 << 16), b1s = DECIM ? (b1 << 15) : (b1 << 16);
+  for (int g = g_first; g < groups; g += g_step) {
+    const int4 w4 = reinterpret_cast<const int4*>(xw)[g];
+    const int4 s4 = reinterpret_cast<const int4*>(xs)[g];
+    const int wo[4] = {w4.x, w4.y, w4.z, w4.w};
+    const int sh[4] = {s4.x, s4.y, s4.z, s4.w};
+    uint32_t cs[4] = {0, 0, 0, 0};
+    if (!DECIM) {
+      const uint4 c4 = reinterpret_cast<const uint4*>(xcoef)[g];
+      cs[0] = c4.x; cs[1] = c4.y; cs[2] = c4.z; cs[3] = c4.w;
+    }
+    uint32_t px[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t* w0 = reinterpret_cast<const uint32_t*>(r0 + wo[k]);
+      const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1 + wo[k]);
+      uint32_t c0, c1, c2;
+      if (DECIM) {
+        const uint32_t u = __funnelshift_r(w0[0], w0[1], sh[k]), v = __funnelshift_r(w1[0], w1[1], sh[k]);
+        c0 = vblend_decim(__byte_perm(u, 0, 0x4404), __byte_perm(v, 0, 0x4404), b0s, b1s);   // tap << 8
+        c1 = vblend_decim(__byte_perm(u, 0, 0x4414), __byte_perm(v, 0, 0x4414), b0s, b1s);
+        c2 = vblend_decim(__byte_perm(u, 0, 0x4424), __byte_perm(v, 0, 0x4424), b0s, b1s);
+      } else {
+        const uint32_t u0 = w0[0], u1 = w0[1], u2 = w0[2];
+        const uint32_t v0 = w1[0], v1 = w1[1], v2 = w1[2];
+        pixel_general(__funnelshift_r(u0, u1, sh[k]), __funnelshift_r(u1, u2, sh[k]), __funnelshift_r(v0, v1, sh[k]),
+                      __funnelshift_r(v1, v2, sh[k]), cs[k], b0s, b1s, &c0, &c1, &c2);
+      }
+      // c0 c1 c2 -> 24-bit pixel in stored channel order (sel_rgb swaps R and B when asked)
+      px[k] = __byte_perm(__byte_perm(c0, c1, 0x0040), c2, sel_rgb);
+    }
+    uint32_t* o = reinterpret_cast<uint32_t*>(orow) + 3 * g;
+    o[0] = __byte_perm(px[0], px[1], 0x4210);
+    o[1] = __byte_perm(px[1], px[2], 0x5421);
+    o[2] = __byte_perm(px[2], px[3], 0x6542);
+  }
+}
+
+__global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int groups = (p.dw + 3) >> 2;  // 4 output pixels per group
+  const int dwp = groups * 4;
+  int* xw = reinterpret_cast<int*>(smem);                               // word-aligned byte offset of tap 0
+  int* xs = reinterpret_cast<int*>(smem + (size_t)dwp * 4);             // 8 * (offset & 3): funnel shift
+  uint32_t* xcoef = reinterpret_cast<uint32_t*>(smem + (size_t)dwp * 8);  // a0 | a1 << 16
+  size_t off = (size_t)dwp * 12;
+  uint8_t* orow = smem + off;                      // one output row; each warp owns 384-byte segments
+  off += ((size_t)groups * 12 + 15) & ~(size_t)15;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + off);
+  uint64_t* empty = full + 8;
+  off += 128;
+  // per-row records written by the producer warp (ring of 2 * stages: a consumer may still be
+  // drawing row i - stages when row i is prepared): header + draw-list hit masks per segment
+  const int nseg = (groups + 31) >> 5;
+  const int mrec = kRecHeader + (p.has_overlay ? nseg * kMaskWords : 0);
+  int* mring = reinterpret_cast<int*>(smem + off);
+  off += ((size_t)2 * p.stages * mrec * 4 + 15) & ~(size_t)15;
+  uint8_t* stage = smem + off;
+
+  const int ncons = (int)blockDim.x / 32 - 1;      // consumer warps; the last warp is the TMA producer
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  bool not_decim = false;
+  for (int dx = threadIdx.x; dx < dwp; dx += blockDim.x) {
+    int s;
+    uint32_t c;
+    horizontal_coef(min(dx, p.dw - 1), p.scale_x, p.sw, &s, &c);
+    xw[dx] = (s * 3) & ~3;
+    xs[dx] = ((s * 3) & 3) * 8;
+    xcoef[dx] = c;
+    not_decim |= (c != 2048u);
+  }
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; s++) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], ncons);
+    }
+    fence_mbar_init();
+  }
+  const bool decim = !__syncthreads_or(not_decim);
+
+  const int chunk = p.items_per_cta;               // rows per chunk
+  const int stride_items = (int)gridDim.x * chunk;
+  // rows this CTA handles (chunks blockIdx, blockIdx + G, ...; the globally last chunk may be short)
+  const int total_chunks = (p.items + chunk - 1) / chunk;
+  const int my_chunks = ((int)blockIdx.x < total_chunks) ? (total_chunks - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  int my_items = my_chunks * chunk;
+  if (my_chunks > 0 && ((int)blockIdx.x + (my_chunks - 1) * (int)gridDim.x) == total_chunks - 1)
+    my_items -= total_chunks * chunk - p.items;
+
+  if (warp == ncons) {
+    // ---- producer warp: prepares the row record (coefficients, culled draw list), then lane 0
+    //      feeds the TMA ring -----------------------------------------------------------------
+    RowIter ri;
+    ri.start(blockIdx.x * chunk, p.items, chunk, p.dh);
+    int slot = 0, rslot = 0, round = 0;
+    for (int it = 0; it < my_items; ++it, ri.next(p.items, chunk, stride_items, p.dh)) {
+      if (round > 0) mbar_wait(&empty[slot], (uint32_t)((round - 1) & 1), 2000, 200);
+      const RowCoef rc = vertical_coef(ri.dy, p.scale_y, p.sh);
+      uint8_t* s0 = stage + (size_t)slot * 2 * p.seg_stride;
+      if (lane == 0) {   // data first: the barrier only completes after expect_tx below
+        const uint8_t* f = p.src + (long long)ri.n * p.src_frame_stride;
+        bulk_g2s(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
+        bulk_g2s(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
+      }
+      int* rec = mring + rslot * mrec;
+      int ob = 0, nops = 0;
+      if (p.has_overlay) {
+        ob = __ldg(p.ov.op_offsets + ri.n);
+        nops = __ldg(p.ov.op_offsets + ri.n + 1) - ob;
+        if (nops <= 32 * kMaskWords) {
+          for (int wi = 0; wi * 32 < nops; wi++) {
+            const int i = wi * 32 + lane;
+            OpSpan sp;
+            sp.row_hit = false;
+            if (i < nops) sp = op_span(p.ov.ops + ob + i, ri.dy);
+            for (int seg = 0; seg < nseg; seg++) {
+              const int lo = seg * 128, hi = min(lo + 127, p.dw - 1);
+              const uint32_t m = __ballot_sync(0xffffffffu, sp.row_hit && span_meets(sp, lo, hi));
+              if (lane == 0) rec[kRecHeader + seg * kMaskWords + wi] = (int)m;
+            }
+          }
+        }
+      }
+      if (lane == 0) {
+        *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
+        rec[4] = ob;
+        rec[5] = nops;
+        mbar_expect_tx(&full[slot], 2u * (uint32_t)p.row_bytes);   // release: record + masks visible
+      }
+      __syncwarp();
+      if (++slot == p.stages) { slot = 0; ++round; }
+      if (++rslot == 2 * p.stages) rslot = 0;
+    }
+    return;
+  }
+
+  // ---- consumers: each warp produces, overlays and stores its own 128-pixel segments --------
+  const int row_bytes_out = p.dw * 3;
+  const uint32_t sel_rgb = p.swap_rb ? 0x7014u : 0x7410u;   // (c0 c1 . .),(c2) -> c0 c1 c2 0 | c2 c1 c0 0
+  int slot = 0, rslot = 0, round = 0;
+  for (int it = 0; it < my_items; ++it) {
+    mbar_wait(&full[slot], (uint32_t)(round & 1), 500, 0);
+    const int* rec = mring + rslot * mrec;
+    const int4 hdr = *reinterpret_cast<const int4*>(rec);   // n, dy, b0, b1
+    const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
+    const uint8_t* r1 = r0 + p.seg_stride;
+    if (decim)
+      consume_row<true>(r0, r1, xw, xs, xcoef, orow, warp * 32 + lane, ncons * 32, groups, (uint32_t)hdr.z,
+                        (uint32_t)hdr.w, sel_rgb);
+    else
+      consume_row<false>(r0, r1, xw, xs, xcoef, orow, warp * 32 + lane, ncons * 32, groups, (uint32_t)hdr.z,
+                         (uint32_t)hdr.w, sel_rgb);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[slot]);      // this warp no longer reads the stage
+    if (p.has_overlay) {
+      const int ob = rec[4], nops = rec[5];
+      if (nops > 32 * kMaskWords) {
+        overlay_apply_row(p.ov.ops + ob, nops, p.ov, hdr.y, p.dw, orow, ncons * 32);
+      } else if (nops > 0) {
+        for (int gbase = warp * 32; gbase < groups; gbase += ncons * 32) {
+          const int mlo = (gbase + lane) * 4, mhi = min(mlo + 3, p.dw - 1);
+          for (int wi = 0; wi * 32 < nops; wi++) {
+            const uint32_t hits = (uint32_t)rec[kRecHeader + (gbase >> 5) * kMaskWords + wi];
+            if (hits) overlay_apply_hits(p.ov.ops + ob + wi * 32, hits, p.ov, hdr.y, mlo, mhi, orow);
+          }
+        }
+      }
+      __syncwarp();
+    }
+    uint8_t* drow = p.dst + (long long)hdr.x * p.dst_frame_stride + (long long)hdr.y * p.dst_row_stride;
+    for (int gbase = warp * 32; gbase < groups; gbase += ncons * 32) {
+      const int b0 = gbase * 12, b1 = min(b0 + 384, row_bytes_out);   // this warp's bytes of the row
+      if ((reinterpret_cast<uintptr_t>(drow) & 15) == 0) {
+        const int nvec = (b1 - b0) >> 4;
+        if (lane < nvec)
+          stg_stream(reinterpret_cast<uint4*>(drow + b0) + lane, reinterpret_cast<const uint4*>(orow + b0)[lane]);
+        for (int i = b0 + (nvec << 4) + lane; i < b1; i += 32) drow[i] = orow[i];
+      } else {
+        for (int i = b0 + lane; i < b1; i += 32) drow[i] = orow[i];
+      }
+    }
+    __syncwarp();                                  // the segment is rewritten by the next row
+    if (++slot == p.stages) { slot = 0; ++round; }
+    if (++rslot == 2 * p.stages) rslot = 0;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+template <int C>
+__global__ void __launch_bounds__(kThreads) resize_rows_generic(const ResizeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   int2* xtab = reinterpret_cast<int2*>(smem);
   size_t off = ((size_t)p.dw * 8 + 15) & ~(size_t)15;
   uint8_t* orow = smem + off;
-  off += ((size_t)p.dw * C + 15) & ~(size_t)15;
-  uint32_t* mask = reinterpret_cast<uint32_t*>(smem + off);
-  off += 32;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + off);
-  off += 64;
-  uint8_t* stage = smem + off;
 
-  // horizontal taps and weights, once per CTA
   for (int dx = threadIdx.x; dx < p.dw; dx += kThreads) {
     int s;
-    float f;
-    linear_coef(dx, p.scale_x, &s, &f);
-    if (s < 0) { s = 0; f = 0.f; }
-    if (s >= p.sw - 1) { s = p.sw - 1; f = 0.f; }
-    const int a0 = coef_q11(__fsub_rn(1.f, f)), a1 = coef_q11(f);
-    xtab[dx] = make_int2(s * C, (a0 & 0xffff) | (a1 << 16));
-  }
-  if (STAGED && threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; s++) mbar_init(&bars[s], 1);
-    fence_mbar_init();
+    uint32_t c;
+    horizontal_coef(dx, p.scale_x, p.sw, &s, &c);
+    xtab[dx] = make_int2(s * C, (int)c);
   }
   __syncthreads();
 
-  const long long G = gridDim.x;
-  auto rows_of = [&](long long item, int* n, int* dy, int* y0, int* y1, int* b0, int* b1) {
-    *n = (int)(item / p.dh);
-    *dy = (int)(item - (long long)(*n) * p.dh);
-    int sy;
-    float fy;
-    linear_coef(*dy, p.scale_y, &sy, &fy);
-    *b0 = coef_q11(__fsub_rn(1.f, fy));
-    *b1 = coef_q11(fy);
-    *y0 = min(max(sy, 0), p.sh - 1);
-    *y1 = min(max(sy + 1, 0), p.sh - 1);
-  };
-  auto issue = [&](long long item, int slot) {
-    int n, dy, y0, y1, b0, b1;
-    rows_of(item, &n, &dy, &y0, &y1, &b0, &b1);
+  const int i0 = blockIdx.x * p.items_per_cta;
+  const int i1 = min(p.items, i0 + p.items_per_cta);
+  if (i0 >= i1) return;
+  int n = i0 / p.dh, dy = i0 - n * p.dh;
+  const int last_off = (p.sw - 1) * C;
+  for (int item = i0; item < i1; ++item) {
+    const RowCoef rc = vertical_coef(dy, p.scale_y, p.sh);
+    const uint32_t b0s = (uint32_t)rc.b0 << 16, b1s = (uint32_t)rc.b1 << 16;
     const uint8_t* f = p.src + (long long)n * p.src_frame_stride;
-    uint8_t* s0 = stage + (size_t)slot * 2 * p.seg_stride;
-    mbar_expect_tx(&bars[slot], 2u * (uint32_t)p.row_bytes);
-    bulk_g2s(s0, f + (long long)y0 * p.src_row_stride, (uint32_t)p.row_bytes, &bars[slot]);
-    bulk_g2s(s0 + p.seg_stride, f + (long long)y1 * p.src_row_stride, (uint32_t)p.row_bytes, &bars[slot]);
-  };
-
-  if (STAGED && threadIdx.x == 0) {
-    for (int s = 0; s < p.stages - 1; s++) {
-      const long long item = blockIdx.x + (long long)s * G;
-      if (item < p.items) issue(item, s);
-    }
-  }
-
-  int it = 0;
-  for (long long item = blockIdx.x; item < p.items; item += G, ++it) {
-    int n, dy, y0, y1, b0, b1;
-    rows_of(item, &n, &dy, &y0, &y1, &b0, &b1);
-    const uint8_t *r0, *r1;
-    if (STAGED) {
-      const int slot = it % p.stages;
-      if (threadIdx.x == 0) {
-        const long long nxt = item + (long long)(p.stages - 1) * G;
-        if (nxt < p.items) issue(nxt, (it + p.stages - 1) % p.stages);
-      }
-      mbar_wait(&bars[slot], (uint32_t)((it / p.stages) & 1));
-      r0 = stage + (size_t)slot * 2 * p.seg_stride;
-      r1 = r0 + p.seg_stride;
-    } else {
-      const uint8_t* f = p.src + (long long)n * p.src_frame_stride;
-      r0 = f + (long long)y0 * p.src_row_stride;
-      r1 = f + (long long)y1 * p.src_row_stride;
-    }
-
-    const int last_off = (p.sw - 1) * C;
+    const uint8_t* r0 = f + (long long)rc.y0 * p.src_row_stride;
+    const uint8_t* r1 = f + (long long)rc.y1 * p.src_row_stride;
     for (int dx = threadIdx.x; dx < p.dw; dx += kThreads) {
       const int2 e = xtab[dx];
-      const int a0 = (int)(short)(e.y & 0xffff), a1 = e.y >> 16;
-      if (STAGED && C == 3) {
-        // 6 source bytes per row (two adjacent RGB taps) from three aligned words
-        const int sh8 = (e.x & 3) * 8;
-        const uint32_t* w0 = reinterpret_cast<const uint32_t*>(r0 + (e.x & ~3));
-        const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1 + (e.x & ~3));
-        const uint32_t u0 = w0[0], u1 = w0[1], u2 = w0[2];
-        const uint32_t v0 = w1[0], v1 = w1[1], v2 = w1[2];
-        const uint32_t ulo = __funnelshift_r(u0, u1, sh8), uhi = __funnelshift_r(u1, u2, sh8);
-        const uint32_t vlo = __funnelshift_r(v0, v1, sh8), vhi = __funnelshift_r(v1, v2, sh8);
-        // lo = t0c0 t0c1 t0c2 t1c0 ; hi = t1c1 t1c2 ..
-        int o[3];
-        o[0] = vblend((ulo & 0xff) * a0 + (ulo >> 24) * a1, (vlo & 0xff) * a0 + (vlo >> 24) * a1, b0, b1);
-        o[1] = vblend(((ulo >> 8) & 0xff) * a0 + (uhi & 0xff) * a1, ((vlo >> 8) & 0xff) * a0 + (vhi & 0xff) * a1,
-                      b0, b1);
-        o[2] = vblend(((ulo >> 16) & 0xff) * a0 + ((uhi >> 8) & 0xff) * a1,
-                      ((vlo >> 16) & 0xff) * a0 + ((vhi >> 8) & 0xff) * a1, b0, b1);
-        uint8_t* q = orow + dx * 3;
-        if (p.swap_rb) { q[0] = o[2]; q[1] = o[1]; q[2] = o[0]; }
-        else { q[0] = o[0]; q[1] = o[1]; q[2] = o[2]; }
-      } else {
-        const int o0 = e.x, o1 = min(e.x + C, last_off);
+      const uint32_t a0 = (uint32_t)e.y & 0xffff, a1 = (uint32_t)e.y >> 16;
+      const int o0 = e.x, o1 = min(e.x + C, last_off);
 #pragma unroll
-        for (int c = 0; c < C; c++) {
-          int t00, t01, t10, t11;
-          if (STAGED) {
-            t00 = r0[o0 + c]; t01 = r0[o1 + c]; t10 = r1[o0 + c]; t11 = r1[o1 + c];
-          } else {
-            t00 = __ldg(r0 + o0 + c); t01 = __ldg(r0 + o1 + c);
-            t10 = __ldg(r1 + o0 + c); t11 = __ldg(r1 + o1 + c);
-          }
-          const int v = vblend(t00 * a0 + t01 * a1, t10 * a0 + t11 * a1, b0, b1);
-          const int cc = (p.swap_rb && C >= 3 && c < 3) ? 2 - c : c;
-          orow[dx * C + cc] = (uint8_t)v;
-        }
+      for (int c = 0; c < C; c++) {
+        const uint32_t t00 = __ldg(r0 + o0 + c), t01 = __ldg(r0 + o1 + c);
+        const uint32_t t10 = __ldg(r1 + o0 + c), t11 = __ldg(r1 + o1 + c);
+        const uint32_t v = vblend_hi(t00 * a0 + t01 * a1, t10 * a0 + t11 * a1, b0s, b1s);
+        const int cc = (p.swap_rb && C >= 3 && c < 3) ? 2 - c : c;
+        orow[dx * C + cc] = (uint8_t)v;
       }
     }
     __syncthreads();
-    if (C == 3 && p.has_overlay) overlay_apply_row(p.ov, n, dy, p.dw, orow, mask);
+    if (C == 3 && p.has_overlay) {
+      const int ob = p.ov.op_offsets[n];
+      overlay_apply_row(p.ov.ops + ob, p.ov.op_offsets[n + 1] - ob, p.ov, dy, p.dw, orow, kThreads);
+      __syncthreads();
+    }
     store_row(p.dst + (long long)n * p.dst_frame_stride + (long long)dy * p.dst_row_stride, orow, p.dw * C);
-    __syncthreads();  // orow and the consumed stage slot are free again
+    __syncthreads();  // orow is rewritten by the next item
+    if (++dy == p.dh) { dy = 0; ++n; }
   }
 }
 
+static int env_int(const char* name, int fallback) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : fallback;
+}
+
+static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
+  *done = false;
+  const int groups = (p.dw + 3) / 4;
+  int ncons = (groups + 31) / 32;
+  if (ncons > 8) ncons = 8;
+  ncons = env_int("AIKO_B200_RESIZE_WARPS", ncons);
+  if (ncons < 1) ncons = 1;
+  if (ncons > 8) ncons = 8;
+  const int threads = (ncons + 1) * 32;            // + the TMA producer warp
+  const size_t fixed = (size_t)groups * 48 + (((size_t)groups * 12 + 15) & ~(size_t)15) + 128;
+  p.row_bytes = p.sw * 3;
+  p.seg_stride = p.row_bytes + 16;                 // tap reads may run a few bytes past the row end
+  int stages = env_int("AIKO_B200_RESIZE_STAGES", 3);
+  if (stages > 8) stages = 8;
+  const size_t max_smem = (size_t)device_max_smem_optin();
+  const size_t mrec = (size_t)(kRecHeader + (p.has_overlay ? ((groups + 31) / 32) * kMaskWords : 0)) * 4;
+  auto need = [&](int st) { return fixed + ((2 * st * mrec + 15) & ~(size_t)15) + (size_t)st * 2 * p.seg_stride; };
+  while (stages > 2 && need(stages) > max_smem) stages--;
+  if (stages < 2 || need(stages) > max_smem) return AIKO_B200_OK;  // not staged
+  p.stages = stages;
+  const size_t smem = need(stages);
+  AIKO_CUDA(cudaFuncSetAttribute(resize3_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resize3_staged, threads, smem));
+  if (per_sm < 1) per_sm = 1;
+  int chunk = env_int("AIKO_B200_RESIZE_CHUNK", 4);
+  if (chunk < 1) chunk = 1;
+  long long grid = (long long)sm_count() * per_sm;
+  const long long chunks = ((long long)p.items + chunk - 1) / chunk;
+  if (grid > chunks) grid = chunks;
+  p.items_per_cta = chunk;
+  resize3_staged<<<(unsigned)grid, threads, smem, stream>>>(p);
+  *done = true;
+  return cuda_status(cudaGetLastError(), "resize3_staged launch");
+}
+
 template <int C>
-static int launch_resize(const ResizeParams& p0, bool staged, cudaStream_t stream) {
-  ResizeParams p = p0;
-  size_t smem = (((size_t)p.dw * 8 + 15) & ~(size_t)15) + (((size_t)p.dw * C + 15) & ~(size_t)15) + 32 + 64;
+static int launch_generic(ResizeParams p, cudaStream_t stream) {
+  const size_t smem = (((size_t)p.dw * 8 + 15) & ~(size_t)15) + (((size_t)p.dw * C + 15) & ~(size_t)15);
   const int max_smem = device_max_smem_optin();
-  if (staged) {
-    p.row_bytes = p.sw * C;
-    p.seg_stride = p.row_bytes + 16;  // tap reads may run a few bytes past the row end
-    int stages = 4;
-    while (stages > 2 && smem + (size_t)stages * 2 * p.seg_stride > (size_t)56 * 1024) stages--;
-    p.stages = stages;
-    if (smem + (size_t)stages * 2 * p.seg_stride > (size_t)max_smem) staged = false;
-    else smem += (size_t)stages * 2 * p.seg_stride;
-  }
   if (smem > (size_t)max_smem) {
     set_last_error("resize_linear: destination width %d needs %zu bytes of shared memory (max %d)", p.dw, smem,
                    max_smem);
     return AIKO_B200_ERR_UNSUPPORTED;
   }
-  auto kern = staged ? resize_linear_rows<C, true> : resize_linear_rows<C, false>;
-  AIKO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  AIKO_CUDA(cudaFuncSetAttribute(resize_rows_generic<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem));
+  AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resize_rows_generic<C>, kThreads, smem));
   if (per_sm < 1) per_sm = 1;
   long long grid = (long long)sm_count() * per_sm;
   if (grid > p.items) grid = p.items;
-  kern<<<(unsigned)grid, kThreads, smem, stream>>>(p);
-  return cuda_status(cudaGetLastError(), "resize_linear launch");
+  p.items_per_cta = (int)((p.items + grid - 1) / grid);
+  grid = (p.items + p.items_per_cta - 1) / p.items_per_cta;
+  resize_rows_generic<C><<<(unsigned)grid, kThreads, smem, stream>>>(p);
+  return cuda_status(cudaGetLastError(), "resize_rows_generic launch");
 }
 
 }  // namespace aiko
@@ -217,6 +447,7 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
                  "resize_linear: row stride smaller than a row");
   AIKO_CHECK_ARG(!overlay || channels == 3, "resize_linear: fused overlay needs 3-channel frames");
   AIKO_CHECK_ARG(!swap_rb || channels >= 3, "resize_linear: swap_rb needs colour frames");
+  AIKO_CHECK_ARG((int64_t)n_frames * dst_h < (int64_t)1 << 31, "resize_linear: more than 2^31 output rows");
   ResizeParams p{};
   p.src = src; p.dst = dst;
   p.n = n_frames; p.sh = src_h; p.sw = src_w; p.dh = dst_h; p.dw = dst_w;
@@ -232,14 +463,18 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
     p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
                       overlay->patch_h};
   }
-  p.items = (long long)n_frames * dst_h;
+  p.items = n_frames * dst_h;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)src_row_stride | (uintptr_t)src_frame_stride |
                          (uintptr_t)((int64_t)src_w * channels)) & 15) == 0;
-  const bool staged = aligned && p.scale_x <= 4.0;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (channels == 3 && aligned && p.scale_x <= 4.0) {
+    bool done = false;
+    const int rc = launch_staged3(p, st, &done);
+    if (rc != AIKO_B200_OK || done) return rc;
+  }
   switch (channels) {
-    case 1: return launch_resize<1>(p, staged, st);
-    case 3: return launch_resize<3>(p, staged, st);
-    default: return launch_resize<4>(p, staged, st);
+    case 1: return launch_generic<1>(p, st);
+    case 3: return launch_generic<3>(p, st);
+    default: return launch_generic<4>(p, st);
   }
 }

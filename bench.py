@@ -170,8 +170,10 @@ def run_gpu_arm(args):
     out = torch.empty((BATCH, DST_H, DST_W, 3), dtype=torch.uint8, device=device)
     stream = torch.cuda.current_stream()
 
+    exp_ov = None if os.environ.get("AIKO_BENCH_EXPERIMENT_NO_OVERLAY") else ov   # experiments only
+
     def step(i):
-        ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=ov, out=out)
+        ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=exp_ov, out=out)
 
     def barrier():
         if world > 1:
