@@ -13,6 +13,7 @@ struct OverlayDev {
   const uint16_t* patch_ids;
   const uint8_t* luts;
   int patch_w, patch_h;
+  int max_ops;   // host hint: largest per-frame op count (0 = unknown)
 };
 
 // cv2.rectangle(.., thickness=2) coverage, closed form.
@@ -65,16 +66,21 @@ __device__ __forceinline__ bool span_meets(const OpSpan& s, int lo, int hi) {
 // One lane applies one op to its pixels [mlo, mhi] of row y.
 __device__ __forceinline__ void apply_op_to_pixels(const aiko_b200_overlay_op* op, const OverlayDev& ov, int y,
                                                    int mlo, int mhi, uint8_t* row) {
-  if (op->kind == AIKO_B200_OP_RECT) {
-    const int x0 = op->x0, x1 = op->x1, y0 = op->y0, y1 = op->y1;
-    const uint32_t colour = op->p0;
-    for (int x = max(mlo, x0 - 1); x <= min(mhi, x1 + 1); x++)
-      if (rect_covers(x, y, x0, y0, x1, y1)) put_rgb(row, x, colour);
+  const int4 lo4 = reinterpret_cast<const int4*>(op)[0];   // kind, x0, y0, x1
+  const int4 hi4 = reinterpret_cast<const int4*>(op)[1];   // y1, p0, p1, p2
+  const int x0 = lo4.y, y0 = lo4.z, x1 = lo4.w, y1 = hi4.x;
+  if (lo4.x == AIKO_B200_OP_RECT) {
+    const uint32_t colour = (uint32_t)hi4.y;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int x = mlo + k;
+      if (x <= mhi && rect_covers(x, y, x0, y0, x1, y1)) put_rgb(row, x, colour);
+    }
   } else {
-    const int xs = max(mlo, op->x0), xe = min(mhi, op->x1);
+    const int xs = max(mlo, x0), xe = min(mhi, x1);
     const int psize = ov.patch_w * ov.patch_h;
-    const uint32_t p0 = op->p0, p1 = op->p1, p2 = op->p2;
-    const int px = op->x0 - int(p2 & 0xffff), py = op->y0 - int(p2 >> 16);
+    const uint32_t p0 = (uint32_t)hi4.y, p1 = (uint32_t)hi4.z, p2 = (uint32_t)hi4.w;
+    const int px = x0 - int(p2 & 0xffff), py = y0 - int(p2 >> 16);
     const uint16_t* q = ov.patch_ids + (y - py) * ov.patch_w - px;
     const uint16_t* q0 = q + (size_t)(p0 & 0xffff) * psize;
     const uint16_t* q1 = q + (size_t)(p0 >> 16) * psize;

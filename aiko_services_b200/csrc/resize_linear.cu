@@ -29,6 +29,7 @@ struct ResizeParams {
   OverlayDev ov;
   int stages, seg_stride, row_bytes;
   int items, items_per_cta;
+  int ops_cap;   // draw-list entries per ring slot staged in shared memory (0: read ops from global)
 };
 
 // cv2's coefficient derivation (float32 phase from a double position, 11-bit weights).
@@ -165,7 +166,11 @@ __device__ __forceinline__ void consume_row(const uint8_t* r0, const uint8_t* r1
   }
 }
 
-__global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
+// Warp roles: warps [0, ncons) consume rows; warp ncons is the TMA producer; with an overlay,
+// warp ncons + 1 culls the frame's draw list (staged next to the row) into per-segment hit
+// masks.  Barriers per ring slot: full (TMA bytes landed), ready (masks written), empty
+// (consumers are done reading the slot).
+__global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int groups = (p.dw + 3) >> 2;  // 4 output pixels per group
   const int dwp = groups * 4;
@@ -177,16 +182,23 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
   off += ((size_t)groups * 12 + 15) & ~(size_t)15;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + off);
   uint64_t* empty = full + 8;
-  off += 128;
-  // per-row records written by the producer warp (ring of 2 * stages: a consumer may still be
-  // drawing row i - stages when row i is prepared): header + draw-list hit masks per segment
+  uint64_t* ready = full + 16;
+  off += 192;
+  // per-row records, ring of stages + 1 (a consumer may still be drawing row i - stages - 1
+  // when row i is prepared): header, then for every 128-pixel segment and every 32 draw-list
+  // entries one word per consumer lane: the entries that touch that lane's 4 pixels
   const int nseg = (groups + 31) >> 5;
-  const int mrec = kRecHeader + (p.has_overlay ? nseg * kMaskWords : 0);
+  const int rdepth = p.stages + 1;
+  const int mwords = (p.ops_cap + 31) >> 5;
+  const int mrec = kRecHeader + nseg * mwords * 32;
   int* mring = reinterpret_cast<int*>(smem + off);
-  off += ((size_t)2 * p.stages * mrec * 4 + 15) & ~(size_t)15;
+  off += ((size_t)rdepth * mrec * 4 + 15) & ~(size_t)15;
+  // the frame's draw list, copied next to each row by the TMA engine (same ring as the records)
+  aiko_b200_overlay_op* opsring = reinterpret_cast<aiko_b200_overlay_op*>(smem + off);
+  off += (size_t)rdepth * p.ops_cap * sizeof(aiko_b200_overlay_op);
   uint8_t* stage = smem + off;
 
-  const int ncons = (int)blockDim.x / 32 - 1;      // consumer warps; the last warp is the TMA producer
+  const int ncons = (int)blockDim.x / 32 - (p.has_overlay ? 2 : 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   bool not_decim = false;
   for (int dx = threadIdx.x; dx < dwp; dx += blockDim.x) {
@@ -202,6 +214,7 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
     for (int s = 0; s < p.stages; s++) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], ncons);
+      mbar_init(&ready[s], 1);
     }
     fence_mbar_init();
   }
@@ -217,48 +230,82 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
     my_items -= total_chunks * chunk - p.items;
 
   if (warp == ncons) {
-    // ---- producer warp: prepares the row record (coefficients, culled draw list), then lane 0
-    //      feeds the TMA ring -----------------------------------------------------------------
-    RowIter ri;
+    // ---- producer: one lane feeds the TMA ring (rows + the frame's draw list) ----------------
+    if (lane != 0 || my_items == 0) return;
+    RowIter ri, rn;                                // current row, next row (for prefetching its list offsets)
     ri.start(blockIdx.x * chunk, p.items, chunk, p.dh);
+    rn = ri;
+    int ob = 0, oe = 0, ob_next = 0, oe_next = 0;
+    if (p.has_overlay) { ob = __ldg(p.ov.op_offsets + ri.n); oe = __ldg(p.ov.op_offsets + ri.n + 1); }
     int slot = 0, rslot = 0, round = 0;
-    for (int it = 0; it < my_items; ++it, ri.next(p.items, chunk, stride_items, p.dh)) {
-      if (round > 0) mbar_wait(&empty[slot], (uint32_t)((round - 1) & 1), 2000, 200);
+    for (int it = 0; it < my_items; ++it) {
+      if (round > 0) mbar_wait(&empty[slot], (uint32_t)((round - 1) & 1), 1000, 100);
       const RowCoef rc = vertical_coef(ri.dy, p.scale_y, p.sh);
       uint8_t* s0 = stage + (size_t)slot * 2 * p.seg_stride;
-      if (lane == 0) {   // data first: the barrier only completes after expect_tx below
-        const uint8_t* f = p.src + (long long)ri.n * p.src_frame_stride;
-        bulk_g2s(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
-        bulk_g2s(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
+      const uint8_t* f = p.src + (long long)ri.n * p.src_frame_stride;
+      bulk_g2s(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
+      bulk_g2s(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
+      const int nops = oe - ob;
+      uint32_t ops_bytes = 0;
+      if (nops > 0 && nops <= p.ops_cap) {
+        ops_bytes = (uint32_t)nops * (uint32_t)sizeof(aiko_b200_overlay_op);
+        bulk_g2s(opsring + (size_t)rslot * p.ops_cap, p.ov.ops + ob, ops_bytes, &full[slot]);
+      }
+      if (p.has_overlay && it + 1 < my_items) {    // next row's offsets: in flight while this row is consumed
+        rn.next(p.items, chunk, stride_items, p.dh);
+        ob_next = __ldg(p.ov.op_offsets + rn.n);
+        oe_next = __ldg(p.ov.op_offsets + rn.n + 1);
       }
       int* rec = mring + rslot * mrec;
-      int ob = 0, nops = 0;
-      if (p.has_overlay) {
-        ob = __ldg(p.ov.op_offsets + ri.n);
-        nops = __ldg(p.ov.op_offsets + ri.n + 1) - ob;
-        if (nops <= 32 * kMaskWords) {
-          for (int wi = 0; wi * 32 < nops; wi++) {
-            const int i = wi * 32 + lane;
-            OpSpan sp;
-            sp.row_hit = false;
-            if (i < nops) sp = op_span(p.ov.ops + ob + i, ri.dy);
-            for (int seg = 0; seg < nseg; seg++) {
-              const int lo = seg * 128, hi = min(lo + 127, p.dw - 1);
-              const uint32_t m = __ballot_sync(0xffffffffu, sp.row_hit && span_meets(sp, lo, hi));
-              if (lane == 0) rec[kRecHeader + seg * kMaskWords + wi] = (int)m;
+      *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
+      rec[4] = ob;
+      rec[5] = nops;
+      mbar_expect_tx(&full[slot], 2u * (uint32_t)p.row_bytes + ops_bytes);   // release: record visible
+      ri.next(p.items, chunk, stride_items, p.dh);
+      ob = ob_next; oe = oe_next;
+      if (++slot == p.stages) { slot = 0; ++round; }
+      if (++rslot == rdepth) rslot = 0;
+    }
+    return;
+  }
+
+  if (warp == ncons + 1) {
+    // ---- cull warp: per row, which draw-list entries touch which 128-pixel segment -----------
+    int slot = 0, rslot = 0, round = 0;
+    for (int it = 0; it < my_items; ++it) {
+      mbar_wait(&full[slot], (uint32_t)(round & 1), 500, 0);
+      int* rec = mring + rslot * mrec;
+      const int dy = rec[1], ob = rec[4], nops = rec[5];
+      if (nops > 0 && nops <= p.ops_cap) {
+        const aiko_b200_overlay_op* fops = opsring + (size_t)rslot * p.ops_cap;
+        for (int wi = 0; wi * 32 < nops; wi++) {
+          const int i = wi * 32 + lane;
+          OpSpan sp;
+          sp.row_hit = false;
+          sp.a0 = sp.b0 = 1; sp.a1 = sp.b1 = 0;
+          if (i < nops) sp = op_span(fops + i, dy);
+          for (int seg = 0; seg < nseg; seg++) {
+            const int lo = seg * 128, hi = min(lo + 127, p.dw - 1);
+            uint32_t m = __ballot_sync(0xffffffffu, sp.row_hit && span_meets(sp, lo, hi));
+            // this lane now plays consumer lane `lane` of the segment: which hits touch its pixels?
+            const int mlo = lo + 4 * lane, mhi = min(mlo + 3, p.dw - 1);
+            uint32_t mine = 0;
+            while (m) {
+              const int b = __ffs(m) - 1;
+              m &= m - 1;
+              OpSpan o;
+              o.a0 = __shfl_sync(0xffffffffu, sp.a0, b); o.a1 = __shfl_sync(0xffffffffu, sp.a1, b);
+              o.b0 = __shfl_sync(0xffffffffu, sp.b0, b); o.b1 = __shfl_sync(0xffffffffu, sp.b1, b);
+              if (span_meets(o, mlo, mhi)) mine |= 1u << b;
             }
+            rec[kRecHeader + (seg * mwords + wi) * 32 + lane] = (int)mine;
           }
         }
       }
-      if (lane == 0) {
-        *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
-        rec[4] = ob;
-        rec[5] = nops;
-        mbar_expect_tx(&full[slot], 2u * (uint32_t)p.row_bytes);   // release: record + masks visible
-      }
       __syncwarp();
+      if (lane == 0) mbar_arrive(&ready[slot]);
       if (++slot == p.stages) { slot = 0; ++round; }
-      if (++rslot == 2 * p.stages) rslot = 0;
+      if (++rslot == rdepth) rslot = 0;
     }
     return;
   }
@@ -266,9 +313,10 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
   // ---- consumers: each warp produces, overlays and stores its own 128-pixel segments --------
   const int row_bytes_out = p.dw * 3;
   const uint32_t sel_rgb = p.swap_rb ? 0x7014u : 0x7410u;   // (c0 c1 . .),(c2) -> c0 c1 c2 0 | c2 c1 c0 0
+  uint64_t* go = p.has_overlay ? ready : full;
   int slot = 0, rslot = 0, round = 0;
   for (int it = 0; it < my_items; ++it) {
-    mbar_wait(&full[slot], (uint32_t)(round & 1), 500, 0);
+    mbar_wait(&go[slot], (uint32_t)(round & 1), 500, 0);
     const int* rec = mring + rslot * mrec;
     const int4 hdr = *reinterpret_cast<const int4*>(rec);   // n, dy, b0, b1
     const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
@@ -283,14 +331,21 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
     if (lane == 0) mbar_arrive(&empty[slot]);      // this warp no longer reads the stage
     if (p.has_overlay) {
       const int ob = rec[4], nops = rec[5];
-      if (nops > 32 * kMaskWords) {
+      if (nops > p.ops_cap) {                      // list too long for the staged path: cull here
         overlay_apply_row(p.ov.ops + ob, nops, p.ov, hdr.y, p.dw, orow, ncons * 32);
       } else if (nops > 0) {
+        const aiko_b200_overlay_op* fops = opsring + (size_t)rslot * p.ops_cap;
         for (int gbase = warp * 32; gbase < groups; gbase += ncons * 32) {
           const int mlo = (gbase + lane) * 4, mhi = min(mlo + 3, p.dw - 1);
           for (int wi = 0; wi * 32 < nops; wi++) {
-            const uint32_t hits = (uint32_t)rec[kRecHeader + (gbase >> 5) * kMaskWords + wi];
-            if (hits) overlay_apply_hits(p.ov.ops + ob + wi * 32, hits, p.ov, hdr.y, mlo, mhi, orow);
+            uint32_t rem = (uint32_t)rec[kRecHeader + ((gbase >> 5) * mwords + wi) * 32 + lane];
+            while (__any_sync(0xffffffffu, rem != 0)) {   // lanes apply their own (different) entries together
+              if (rem) {
+                const int b = __ffs(rem) - 1;
+                rem &= rem - 1;
+                apply_op_to_pixels(fops + wi * 32 + b, p.ov, hdr.y, mlo, mhi, orow);
+              }
+            }
           }
         }
       }
@@ -310,7 +365,7 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
     }
     __syncwarp();                                  // the segment is rewritten by the next row
     if (++slot == p.stages) { slot = 0; ++round; }
-    if (++rslot == 2 * p.stages) rslot = 0;
+    if (++rslot == rdepth) rslot = 0;
   }
 }
 
@@ -379,15 +434,19 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   ncons = env_int("AIKO_B200_RESIZE_WARPS", ncons);
   if (ncons < 1) ncons = 1;
   if (ncons > 8) ncons = 8;
-  const int threads = (ncons + 1) * 32;            // + the TMA producer warp
-  const size_t fixed = (size_t)groups * 48 + (((size_t)groups * 12 + 15) & ~(size_t)15) + 128;
+  const int threads = (ncons + (p.has_overlay ? 2 : 1)) * 32;   // + TMA producer warp (+ cull warp)
+  const size_t fixed = (size_t)groups * 48 + (((size_t)groups * 12 + 15) & ~(size_t)15) + 192;
   p.row_bytes = p.sw * 3;
   p.seg_stride = p.row_bytes + 16;                 // tap reads may run a few bytes past the row end
   int stages = env_int("AIKO_B200_RESIZE_STAGES", 3);
   if (stages > 8) stages = 8;
   const size_t max_smem = (size_t)device_max_smem_optin();
-  const size_t mrec = (size_t)(kRecHeader + (p.has_overlay ? ((groups + 31) / 32) * kMaskWords : 0)) * 4;
-  auto need = [&](int st) { return fixed + ((2 * st * mrec + 15) & ~(size_t)15) + (size_t)st * 2 * p.seg_stride; };
+  p.ops_cap = (p.has_overlay && p.ov.max_ops > 0 && p.ov.max_ops <= 32 * kMaskWords) ? p.ov.max_ops : 0;
+  const size_t mrec = (size_t)(kRecHeader + ((groups + 31) / 32) * ((p.ops_cap + 31) / 32) * 32) * 4;
+  auto need = [&](int st) {
+    return fixed + (((st + 1) * mrec + 15) & ~(size_t)15) + (size_t)(st + 1) * p.ops_cap * sizeof(aiko_b200_overlay_op) +
+           (size_t)st * 2 * p.seg_stride;
+  };
   while (stages > 2 && need(stages) > max_smem) stages--;
   if (stages < 2 || need(stages) > max_smem) return AIKO_B200_OK;  // not staged
   p.stages = stages;
@@ -396,7 +455,7 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   int per_sm = 0;
   AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resize3_staged, threads, smem));
   if (per_sm < 1) per_sm = 1;
-  int chunk = env_int("AIKO_B200_RESIZE_CHUNK", 4);
+  int chunk = env_int("AIKO_B200_RESIZE_CHUNK", 1);
   if (chunk < 1) chunk = 1;
   long long grid = (long long)sm_count() * per_sm;
   const long long chunks = ((long long)p.items + chunk - 1) / chunk;
@@ -461,7 +520,7 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
   if (overlay) {
     AIKO_CHECK_ARG(overlay->ops && overlay->op_offsets, "resize_linear: overlay without ops/op_offsets");
     p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
-                      overlay->patch_h};
+                      overlay->patch_h, overlay->max_ops_per_frame};
   }
   p.items = n_frames * dst_h;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

@@ -50,9 +50,10 @@ def _out(out, shape, device, name, dtype=torch.uint8):
 class DeviceOverlay:
     """A draw list resident on the GPU (see aiko_b200_overlay in include/aiko_b200.h)."""
 
-    def __init__(self, ops, op_offsets, atlas=None):
+    def __init__(self, ops, op_offsets, atlas=None, max_ops_per_frame=0):
         self.ops, self.op_offsets, self.atlas = ops, op_offsets, atlas
         self.struct = Overlay()
+        self.struct.max_ops_per_frame = int(max_ops_per_frame)
         self.struct.ops = ops.data_ptr()
         self.struct.op_offsets = op_offsets.data_ptr()
         if atlas is not None:
@@ -77,7 +78,8 @@ class DeviceOverlay:
     def from_host(ops_per_frame, device, atlas=None):
         """ops_per_frame: list (one entry per frame) of lists of OverlayOp."""
         raw, offsets = DeviceOverlay.pack_host(ops_per_frame)
-        return DeviceOverlay(torch.from_numpy(raw).to(device), torch.from_numpy(offsets).to(device), atlas)
+        most = max((len(o) for o in ops_per_frame), default=0)
+        return DeviceOverlay(torch.from_numpy(raw).to(device), torch.from_numpy(offsets).to(device), atlas, most)
 
     def pointer(self):
         return ctypes.pointer(self.struct)

@@ -163,6 +163,9 @@ def run_gpu_arm(args):
 
     atlas = TextAtlas.shared()
     frame_ops = build_ops(OVERLAY, DST_W, DST_H, "bgr", atlas)
+    exp = os.environ.get("AIKO_BENCH_EXPERIMENT_OPS")          # experiments only: "rects" | "glyphs"
+    if exp:
+        frame_ops = [] if exp == "none" else [o for o in frame_ops if (o.kind == 0) == (exp == "rects")]
     ov = ops.DeviceOverlay.from_host([frame_ops] * BATCH, device, atlas.device(device))
 
     # device-resident inputs: N_ROTATING_BATCHES distinct batches (streams sharded by rank for N>1)

@@ -74,6 +74,8 @@ typedef struct aiko_b200_overlay {
   const uint8_t* luts;             /* device */
   int32_t patch_w, patch_h;
   int32_t n_patches;
+  int32_t max_ops_per_frame;       /* largest op count of any frame, or 0 if unknown (a hint: kernels size
+                                      their shared-memory copy of a frame's list with it) */
 } aiko_b200_overlay;
 
 /* ---------------------------------------------------------------------- */
