@@ -47,6 +47,9 @@ SIGNATURES = {
     "aiko_b200_last_error": [],
     "aiko_b200_device_info": [ctypes.c_char_p, _sz, ctypes.POINTER(_i), ctypes.POINTER(_i)],
     "aiko_b200_resize_linear_u8": [_vp, _i, _i, _i, _i, _i64, _i64, _vp, _i, _i, _i64, _i64, _i, _ovp, _vp],
+    "aiko_b200_resize_bicubic_workspace_bytes": [_i, _i, _i, _i],
+    "aiko_b200_resize_bicubic_prepare": [_vp, _sz, _i, _i, _i, _i, _vp],
+    "aiko_b200_resize_bicubic_aa_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp, _sz, _vp],
     "aiko_b200_overlay_u8": [_vp, _vp, _i, _i, _i, _i, _i64, _i64, _ovp, _vp],
     "aiko_b200_swap_rb_u8": [_vp, _vp, _i64, _vp],
     "aiko_b200_bgr2gray_u8": [_vp, _vp, _i64, _i, _vp],
@@ -54,6 +57,8 @@ SIGNATURES = {
     "aiko_b200_flip_u8": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "aiko_b200_crop_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _vp],
 }
+
+RESTYPES = {"aiko_b200_last_error": ctypes.c_char_p, "aiko_b200_resize_bicubic_workspace_bytes": ctypes.c_size_t}
 
 _lib = None
 
@@ -76,7 +81,7 @@ def lib():
         for name, argtypes in SIGNATURES.items():
             fn = getattr(handle, name)  # AttributeError = header/library mismatch: fail loudly
             fn.argtypes = argtypes
-            fn.restype = ctypes.c_char_p if name == "aiko_b200_last_error" else ctypes.c_int
+            fn.restype = RESTYPES.get(name, ctypes.c_int)
         _lib = handle
     return _lib
 

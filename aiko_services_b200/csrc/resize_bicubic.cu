@@ -1,0 +1,277 @@
+// Batched antialiased bicubic resize, bit-exact with PIL.Image.resize((W, H)) for 8-bit
+// images (default BICUBIC filter) as called by the reference's ImageResize on PIL inputs
+// (R/elements/media/image_io.py:218).  Pillow's algorithm: per axis, a table of 22-bit
+// fixed-point weights over a support of 2 * max(scale, 1) source pixels; a horizontal pass
+// into a uint8 intermediate image, then a vertical pass.
+//
+//   bicubic_coeffs_kernel  fills the two weight tables in a caller-provided workspace using
+//                          explicitly rounded IEEE double operations (same results as the C
+//                          library on the host, no FMA contraction);
+//   resize_bicubic_rows    one CTA per band of output rows of one frame: source rows stream
+//                          through the horizontal pass into a shared-memory ring of uint8
+//                          intermediate rows, and each output row is produced from that ring,
+//                          so a source byte is read from HBM once per band it belongs to and the
+//                          intermediate image never exists in global memory.
+#include "common.cuh"
+
+namespace aiko {
+
+constexpr int kPrecisionBits = 32 - 8 - 2;
+
+struct AxisTable {
+  int ksize;  // taps per output index (row stride of k)
+  int off_bounds;
+  int off_k;
+};
+struct BicubicLayout {
+  AxisTable x, y;
+  size_t ints;
+};
+
+__host__ __device__ inline int bicubic_ksize(int in_size, int out_size) {
+  double scale = (double)in_size / out_size;
+  if (scale < 1.0) scale = 1.0;
+  const double support = 2.0 * scale;
+  int c = (int)support;
+  if ((double)c < support) c++;
+  return c * 2 + 1;
+}
+
+static BicubicLayout bicubic_layout(int sh, int sw, int dh, int dw) {
+  BicubicLayout l;
+  l.x.ksize = (bicubic_ksize(sw, dw) + 3) & ~3;  // rows of k padded to 16 bytes
+  l.y.ksize = (bicubic_ksize(sh, dh) + 3) & ~3;
+  size_t o = 4;
+  l.x.off_bounds = (int)o; o += 2 * (size_t)dw;
+  o = (o + 3) & ~(size_t)3;
+  l.x.off_k = (int)o; o += (size_t)dw * l.x.ksize;
+  l.y.off_bounds = (int)o; o += 2 * (size_t)dh;
+  o = (o + 3) & ~(size_t)3;
+  l.y.off_k = (int)o; o += (size_t)dh * l.y.ksize;
+  l.ints = o;
+  return l;
+}
+
+__device__ __forceinline__ double bicubic_filter(double x) {
+  // a = -0.5: ((a + 2) x - (a + 3)) x x + 1   |   (((x - 5) x + 8) x - 4) a
+  if (x < 0.0) x = -x;
+  if (x < 1.0) return __dadd_rn(__dmul_rn(__dmul_rn(__dadd_rn(__dmul_rn(1.5, x), -2.5), x), x), 1.0);
+  if (x < 2.0)
+    return __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(x, -5.0), x), 8.0), x), -4.0), -0.5);
+  return 0.0;
+}
+
+// one thread per output index of one axis
+__global__ void bicubic_coeffs_kernel(int* ws, int in_size, int out_size, int ksize, int off_bounds, int off_k) {
+  const int xx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (xx >= out_size) return;
+  int* bounds = ws + off_bounds;
+  int* k = ws + off_k + (size_t)xx * ksize;
+  if (in_size == out_size) {  // Pillow skips the pass: identity weights reproduce the copy exactly
+    bounds[2 * xx] = xx;
+    bounds[2 * xx + 1] = 1;
+    k[0] = 1 << kPrecisionBits;
+    for (int t = 1; t < ksize; t++) k[t] = 0;
+    return;
+  }
+  const double scale = __ddiv_rn((double)in_size, (double)out_size);
+  const double filterscale = scale < 1.0 ? 1.0 : scale;
+  const double support = __dmul_rn(2.0, filterscale);
+  const double center = __dmul_rn(__dadd_rn((double)xx, 0.5), scale);
+  const double ss = __ddiv_rn(1.0, filterscale);
+  int xmin = __double2int_rz(__dadd_rn(__dsub_rn(center, support), 0.5));
+  if (xmin < 0) xmin = 0;
+  int xmax = __double2int_rz(__dadd_rn(__dadd_rn(center, support), 0.5));
+  if (xmax > in_size) xmax = in_size;
+  xmax -= xmin;
+  double ww = 0.0;
+  for (int x = 0; x < xmax; x++)
+    ww = __dadd_rn(ww, bicubic_filter(__dmul_rn(__dadd_rn(__dsub_rn((double)(x + xmin), center), 0.5), ss)));
+  for (int x = 0; x < ksize; x++) {
+    int v = 0;
+    if (x < xmax) {
+      double w = bicubic_filter(__dmul_rn(__dadd_rn(__dsub_rn((double)(x + xmin), center), 0.5), ss));
+      if (ww != 0.0) w = __ddiv_rn(w, ww);
+      const double f = __dmul_rn(w, (double)(1 << kPrecisionBits));
+      v = f < 0 ? __double2int_rz(__dadd_rn(-0.5, f)) : __double2int_rz(__dadd_rn(0.5, f));
+    }
+    k[x] = v;
+  }
+  bounds[2 * xx] = xmin;
+  bounds[2 * xx + 1] = xmax;
+}
+
+__device__ __forceinline__ uint8_t clip8_q22(int v) {
+  v >>= kPrecisionBits;
+  return (uint8_t)min(max(v, 0), 255);
+}
+
+struct BicubicParams {
+  const uint8_t* src;
+  uint8_t* dst;
+  const int* ws;
+  int n, sh, sw, dh, dw, ch;
+  int ksx, ksy, off_bx, off_kx, off_by, off_ky;
+  int band, bands_per_frame, ring_rows;
+  int kx_in_smem;
+};
+
+__global__ void __launch_bounds__(kThreads) resize_bicubic_rows(const BicubicParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int src_row_bytes = p.sw * p.ch, mid_row_bytes = p.dw * p.ch;
+  const int src_stride = (src_row_bytes + 31) & ~15, mid_stride = (mid_row_bytes + 15) & ~15;
+  uint8_t* srow = smem;                               // one staged source row (+ 16 bytes of head room)
+  uint8_t* ring = srow + src_stride;                  // ring_rows intermediate rows
+  int* bx_s = reinterpret_cast<int*>(ring + (size_t)p.ring_rows * mid_stride);   // xmin, count per dx
+  int* kx_s = bx_s + 2 * p.dw;                        // weights, when they fit
+
+  const int* bx = p.ws + p.off_bx;
+  const int* kx = p.ws + p.off_kx;
+  const int* by = p.ws + p.off_by;
+  const int* ky = p.ws + p.off_ky;
+  for (int i = threadIdx.x; i < 2 * p.dw; i += kThreads) bx_s[i] = bx[i];
+  if (p.kx_in_smem)
+    for (int i = threadIdx.x; i < p.dw * p.ksx; i += kThreads) kx_s[i] = kx[i];
+  const int* kxt = p.kx_in_smem ? kx_s : kx;
+  __syncthreads();
+
+  const int frame = blockIdx.x / p.bands_per_frame;
+  const int dy0 = (blockIdx.x - frame * p.bands_per_frame) * p.band;
+  const int dy1 = min(dy0 + p.band, p.dh);
+  const uint8_t* fsrc = p.src + (size_t)frame * p.sh * src_row_bytes;
+  uint8_t* fdst = p.dst + (size_t)frame * p.dh * mid_row_bytes;
+
+  int next_src = by[2 * dy0];
+  for (int dy = dy0; dy < dy1; dy++) {
+    const int ymin = by[2 * dy], ycnt = by[2 * dy + 1];
+    // horizontal pass for every source row this output row still needs
+    for (; next_src < ymin + ycnt; next_src++) {
+      const uint8_t* g = fsrc + (size_t)next_src * src_row_bytes;
+      const int head = (int)(reinterpret_cast<uintptr_t>(g) & 15);
+      if (head == 0 && (src_row_bytes & 15) == 0) {
+        for (int i = threadIdx.x; i < (src_row_bytes >> 4); i += kThreads)
+          reinterpret_cast<uint4*>(srow)[i] = ldg_stream(reinterpret_cast<const uint4*>(g) + i);
+      } else {
+        for (int i = threadIdx.x; i < src_row_bytes; i += kThreads) srow[i] = g[i];
+      }
+      __syncthreads();
+      uint8_t* mid = ring + (size_t)(next_src % p.ring_rows) * mid_stride;
+      for (int dx = threadIdx.x; dx < p.dw; dx += kThreads) {
+        const int xmin = bx_s[2 * dx], cnt = bx_s[2 * dx + 1];
+        const int* k = kxt + (size_t)dx * p.ksx;
+        const uint8_t* s = srow + xmin * p.ch;
+        if (p.ch == 3) {
+          int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
+          for (int t = 0; t < cnt; t++) {
+            const int w = k[t];
+            a0 += s[3 * t] * w; a1 += s[3 * t + 1] * w; a2 += s[3 * t + 2] * w;
+          }
+          mid[3 * dx] = clip8_q22(a0); mid[3 * dx + 1] = clip8_q22(a1); mid[3 * dx + 2] = clip8_q22(a2);
+        } else {
+          for (int c = 0; c < p.ch; c++) {
+            int a = 1 << (kPrecisionBits - 1);
+            for (int t = 0; t < cnt; t++) a += s[t * p.ch + c] * k[t];
+            mid[dx * p.ch + c] = clip8_q22(a);
+          }
+        }
+      }
+      __syncthreads();
+    }
+    // vertical pass: one output row from ycnt intermediate rows
+    const int* k = ky + (size_t)dy * p.ksy;
+    uint8_t* o = fdst + (size_t)dy * mid_row_bytes;
+    for (int i4 = threadIdx.x * 4; i4 < mid_row_bytes; i4 += kThreads * 4) {
+      int a[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) a[j] = 1 << (kPrecisionBits - 1);
+      for (int t = 0; t < ycnt; t++) {
+        const int w = __ldg(k + t);
+        const uint32_t v = *reinterpret_cast<const uint32_t*>(ring + (size_t)((ymin + t) % p.ring_rows) * mid_stride + i4);
+        a[0] += (int)(v & 0xff) * w; a[1] += (int)((v >> 8) & 0xff) * w;
+        a[2] += (int)((v >> 16) & 0xff) * w; a[3] += (int)(v >> 24) * w;
+      }
+      if (i4 + 3 < mid_row_bytes && (reinterpret_cast<uintptr_t>(o) & 3) == 0) {
+        *reinterpret_cast<uint32_t*>(o + i4) = (uint32_t)clip8_q22(a[0]) | ((uint32_t)clip8_q22(a[1]) << 8) |
+                                               ((uint32_t)clip8_q22(a[2]) << 16) | ((uint32_t)clip8_q22(a[3]) << 24);
+      } else {
+        for (int j = 0; j < 4 && i4 + j < mid_row_bytes; j++) o[i4 + j] = clip8_q22(a[j]);
+      }
+    }
+    // the next output row's horizontal pass starts with a barrier after staging, which also
+    // orders these ring reads before the ring rows they no longer need are overwritten
+  }
+}
+
+}  // namespace aiko
+
+using namespace aiko;
+
+extern "C" size_t aiko_b200_resize_bicubic_workspace_bytes(int src_h, int src_w, int dst_h, int dst_w) {
+  if (src_h <= 0 || src_w <= 0 || dst_h <= 0 || dst_w <= 0) return 0;
+  return bicubic_layout(src_h, src_w, dst_h, dst_w).ints * sizeof(int);
+}
+
+extern "C" int aiko_b200_resize_bicubic_prepare(void* workspace, size_t workspace_bytes, int src_h, int src_w,
+                                                int dst_h, int dst_w, void* stream) {
+  AIKO_CHECK_ARG(src_h > 0 && src_w > 0 && dst_h > 0 && dst_w > 0, "resize_bicubic_prepare: bad size");
+  const BicubicLayout l = bicubic_layout(src_h, src_w, dst_h, dst_w);
+  if (!workspace || workspace_bytes < l.ints * sizeof(int)) {
+    set_last_error("resize_bicubic_prepare: workspace of %zu bytes, need %zu", workspace_bytes, l.ints * sizeof(int));
+    return AIKO_B200_ERR_WORKSPACE;
+  }
+  AIKO_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "resize_bicubic_prepare: workspace not 16-byte aligned");
+  int* ws = static_cast<int*>(workspace);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  bicubic_coeffs_kernel<<<(dst_w + 127) / 128, 128, 0, st>>>(ws, src_w, dst_w, l.x.ksize, l.x.off_bounds, l.x.off_k);
+  bicubic_coeffs_kernel<<<(dst_h + 127) / 128, 128, 0, st>>>(ws, src_h, dst_h, l.y.ksize, l.y.off_bounds, l.y.off_k);
+  return cuda_status(cudaGetLastError(), "bicubic_coeffs launch");
+}
+
+extern "C" int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, int src_h, int src_w, int channels,
+                                              uint8_t* dst, int dst_h, int dst_w, const void* workspace,
+                                              size_t workspace_bytes, void* stream) {
+  AIKO_CHECK_ARG(n_frames >= 0, "resize_bicubic: n_frames < 0");
+  if (n_frames == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(src && dst, "resize_bicubic: null frame pointer");
+  AIKO_CHECK_ARG(src_h > 0 && src_w > 0 && dst_h > 0 && dst_w > 0, "resize_bicubic: bad size");
+  AIKO_CHECK_ARG(channels == 1 || channels == 3 || channels == 4, "resize_bicubic: channels %d not in {1,3,4}",
+                 channels);
+  const BicubicLayout l = bicubic_layout(src_h, src_w, dst_h, dst_w);
+  if (!workspace || workspace_bytes < l.ints * sizeof(int)) {
+    set_last_error("resize_bicubic: workspace of %zu bytes, need %zu (and it must have been prepared)", workspace_bytes,
+                   l.ints * sizeof(int));
+    return AIKO_B200_ERR_WORKSPACE;
+  }
+  BicubicParams p{};
+  p.src = src; p.dst = dst; p.ws = static_cast<const int*>(workspace);
+  p.n = n_frames; p.sh = src_h; p.sw = src_w; p.dh = dst_h; p.dw = dst_w; p.ch = channels;
+  p.ksx = l.x.ksize; p.ksy = l.y.ksize;
+  p.off_bx = l.x.off_bounds; p.off_kx = l.x.off_k; p.off_by = l.y.off_bounds; p.off_ky = l.y.off_k;
+  p.ring_rows = l.y.ksize + 1;
+  // bands: enough CTAs to fill the machine, long enough that the vertical halo stays small
+  const double scale_y = (double)src_h / dst_h;
+  int band = (int)(4.0 * l.y.ksize / (scale_y < 1.0 ? 1.0 : scale_y)) + 1;  // halo <= ~25 % of the rows read
+  const long long want_ctas = (long long)sm_count() * 4;
+  while (band > 8 && (long long)n_frames * ((dst_h + band - 1) / band) < want_ctas) band /= 2;
+  if (band > dst_h) band = dst_h;
+  if (band < 1) band = 1;
+  p.band = band;
+  p.bands_per_frame = (dst_h + band - 1) / band;
+  const size_t src_stride = ((size_t)src_w * channels + 31) & ~(size_t)15;
+  const size_t mid_stride = ((size_t)dst_w * channels + 15) & ~(size_t)15;
+  size_t smem = src_stride + (size_t)p.ring_rows * mid_stride + (size_t)2 * dst_w * sizeof(int);
+  const size_t kx_bytes = (size_t)dst_w * l.x.ksize * sizeof(int);
+  const size_t max_smem = (size_t)device_max_smem_optin();
+  p.kx_in_smem = (smem + kx_bytes <= 100 * 1024) ? 1 : 0;
+  if (p.kx_in_smem) smem += kx_bytes;
+  if (smem > max_smem) {
+    set_last_error("resize_bicubic: %dx%d -> %dx%d needs %zu bytes of shared memory (max %zu)", src_w, src_h, dst_w,
+                   dst_h, smem, max_smem);
+    return AIKO_B200_ERR_UNSUPPORTED;
+  }
+  AIKO_CUDA(cudaFuncSetAttribute(resize_bicubic_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const long long grid = (long long)n_frames * p.bands_per_frame;
+  AIKO_CHECK_ARG(grid < ((long long)1 << 31), "resize_bicubic: too many bands");
+  resize_bicubic_rows<<<(unsigned)grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  return cuda_status(cudaGetLastError(), "resize_bicubic launch");
+}

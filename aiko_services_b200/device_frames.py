@@ -1,0 +1,182 @@
+"""Device-resident frames handed between consecutive GPU elements.
+
+The reference passes ``images`` -- a Python list of ndarrays / PIL images -- from element to
+element through ``frame.swag`` (R/main/pipeline.py:1071).  Here a GPU element returns a list
+of ``DeviceImage`` items instead: each is a view of one frame of a ``DeviceBatch`` that lives
+in HBM.  A ``DeviceImage`` turns into an ndarray on demand (``np.asarray(image)``,
+``image.to_pil()``), so elements that were not ported keep working, at the price of one
+device-to-host copy of the batch.
+
+A ``DeviceBatch`` is lazy: ImageResize, ImageOverlay and colour conversion only append to its
+recipe.  When the pixels are needed, consecutive steps that the library can run as one kernel
+(bilinear resize -> overlay -> channel swap) are launched as one.
+"""
+import numpy as np
+import torch
+
+from . import ops
+from .overlay_plan import build_ops
+from .text_atlas import TextAtlas
+
+
+class DeviceBatch:
+    def __init__(self, tensor, stream=None, recipe=None):
+        self._source = tensor            # uint8 [N, H, W, C] or [N, H, W] on a CUDA device
+        self._recipe = list(recipe or [])
+        self._tensor = tensor if not self._recipe else None
+        self._host = None
+        self.stream = stream             # torch.cuda.Stream the batch's work is ordered on
+
+    # ---- geometry of the result, known without running anything
+    @property
+    def device(self):
+        return self._source.device
+
+    def __len__(self):
+        return self._source.shape[0]
+
+    @property
+    def frame_shape(self):
+        h, w = self._source.shape[1:3]
+        c = self._source.shape[3] if self._source.dim() == 4 else 1
+        for step in self._recipe:
+            if step[0] in ("resize_linear", "resize_bicubic"):
+                w, h = step[1], step[2]
+            elif step[0] == "convert":
+                c = {"RGB2BGR": 3, "BGR2RGB": 3, "RGB2GRAY": 1, "BGR2GRAY": 1, "GRAY2BGR": 3}[step[1]]
+        return (h, w) if c == 1 else (h, w, c)
+
+    def then(self, *step):
+        return DeviceBatch(self._source if self._tensor is None else self._tensor, self.stream,
+                           (self._recipe if self._tensor is None else []) + [tuple(step)])
+
+    # ---- materialisation
+    @property
+    def tensor(self):
+        if self._tensor is None:
+            ctx = torch.cuda.stream(self.stream) if self.stream is not None else _NullContext()
+            with ctx:
+                self._tensor = self._run(self._source, self._recipe)
+        return self._tensor
+
+    def _overlay(self, overlays, width, height, gray, swapped, n):
+        atlas = TextAtlas.shared()
+        layout = "bgr" if (gray or swapped) else "rgb"
+        if isinstance(overlays, dict):
+            per_frame = [build_ops(overlays, width, height, layout, atlas)] * n
+        else:
+            per_frame = [build_ops(o, width, height, layout, atlas) for o in overlays]
+        return ops.DeviceOverlay.from_host(per_frame, self.device, atlas.device(self.device))
+
+    def _run(self, t, recipe):
+        i = 0
+        while i < len(recipe):
+            step = recipe[i]
+            kind = step[0]
+            n = t.shape[0]
+            colour = t.dim() == 4 and t.shape[3] == 3
+            if kind == "resize_linear":
+                w, h = step[1], step[2]
+                ov, swap, used = None, False, 1
+                # fuse what the library runs in the same pass: [overlay] [RGB<->BGR]
+                if colour and i + used < len(recipe) and recipe[i + used][0] == "overlay":
+                    ov_spec = recipe[i + used][1]
+                    used += 1
+                    if i + used < len(recipe) and recipe[i + used] in (("convert", "RGB2BGR"), ("convert", "BGR2RGB")):
+                        swap = True
+                        used += 1
+                    ov = self._overlay(ov_spec, w, h, False, swap, n)
+                elif colour and i + used < len(recipe) and recipe[i + used] in (("convert", "RGB2BGR"),
+                                                                                 ("convert", "BGR2RGB")):
+                    swap = True
+                    used += 1
+                t = ops.resize_linear(t, w, h, swap_rb=swap, overlay=ov)
+                i += used
+                continue
+            if kind == "resize_bicubic":
+                t = ops.resize_bicubic_aa(t, step[1], step[2])
+            elif kind == "overlay":
+                gray = t.dim() == 3
+                h, w = t.shape[1:3]
+                t = ops.overlay_draw(t, self._overlay(step[1], w, h, gray, False, n))
+            elif kind == "convert":
+                code = step[1]
+                if code in ("RGB2BGR", "BGR2RGB"):
+                    t = ops.swap_rb(t)
+                elif code in ("RGB2GRAY", "BGR2GRAY"):
+                    t = ops.bgr2gray(t, rgb_order=(code == "RGB2GRAY"))
+                elif code == "GRAY2BGR":
+                    t = ops.gray2bgr(t)
+                else:
+                    raise ValueError(f"unknown conversion {code}")
+            elif kind == "flip":
+                t = ops.flip(t, step[1])
+            elif kind == "crop":
+                t = ops.crop(t, *step[1:])
+            else:
+                raise ValueError(f"unknown step {kind}")
+            i += 1
+        return t
+
+    def host(self, out=None):
+        """The whole batch as one ndarray (one device-to-host copy, cached)."""
+        if self._host is None:
+            t = self.tensor
+            if self.stream is not None:
+                with torch.cuda.stream(self.stream):
+                    h = t.to("cpu", non_blocking=False) if out is None else out.copy_(t, non_blocking=True)
+                self.stream.synchronize()
+            else:
+                h = t.cpu() if out is None else out.copy_(t)
+            self._host = h.numpy()
+        return self._host
+
+    def images(self):
+        return [DeviceImage(self, i) for i in range(len(self))]
+
+
+class _NullContext:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+class DeviceImage:
+    """One frame of a DeviceBatch; stands in for the ndarray the reference would pass."""
+
+    def __init__(self, batch, index):
+        self.batch, self.index = batch, index
+
+    @property
+    def shape(self):
+        return self.batch.frame_shape
+
+    @property
+    def ndim(self):
+        return len(self.shape)
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.batch.host()[self.index]
+        return a.astype(dtype) if dtype is not None and dtype != a.dtype else a
+
+    def numpy(self):
+        return np.asarray(self)
+
+    def astype(self, dtype):
+        return np.asarray(self).astype(dtype)
+
+    def to_pil(self):
+        from PIL import Image
+        a = np.asarray(self)
+        return Image.fromarray(a, "L" if a.ndim == 2 else "RGB")
+
+
+def group_device_images(images):
+    """If ``images`` is exactly the frames of one DeviceBatch, in order, return that batch."""
+    if images and all(isinstance(im, DeviceImage) for im in images):
+        b = images[0].batch
+        if len(images) == len(b) and all(im.batch is b and im.index == i for i, im in enumerate(images)):
+            return b
+    return None

@@ -99,6 +99,42 @@ def resize_linear(src, width, height, *, swap_rb=False, overlay=None, out=None, 
     return out
 
 
+_bicubic_plans = {}   # (device, sh, sw, dh, dw) -> prepared workspace tensor
+
+
+def bicubic_workspace(device, sh, sw, dh, dw, stream=None):
+    """Prepared weight tables for PIL-style resizing of sh x sw frames to dh x dw (cached per device)."""
+    key = (str(device), sh, sw, dh, dw)
+    ws = _bicubic_plans.get(key)
+    if ws is None:
+        nbytes = _native.lib().aiko_b200_resize_bicubic_workspace_bytes(sh, sw, dh, dw)
+        if nbytes == 0:
+            raise ValueError(f"resize_bicubic_aa: bad size {sw}x{sh} -> {dw}x{dh}")
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        with torch.cuda.device(device):
+            check(_native.lib().aiko_b200_resize_bicubic_prepare(ws.data_ptr(), nbytes, sh, sw, dh, dw,
+                                                                 _stream_ptr(stream)))
+        # later calls may come from other streams: make the tables visible to all of them
+        (stream or torch.cuda.current_stream()).synchronize()
+        _bicubic_plans[key] = ws
+    return ws
+
+
+def resize_bicubic_aa(src, width, height, *, out=None, stream=None):
+    """PIL.Image.resize((width, height)) (default bicubic, antialiased) for every frame of ``src``."""
+    _require_cuda(src, "resize_bicubic_aa src")
+    n, h, w, c, gray = _nhwc(src)
+    shape = (n, height, width) if gray else (n, height, width, c)
+    out = _out(out, shape, src.device, "resize_bicubic_aa out")
+    if n == 0:
+        return out
+    ws = bicubic_workspace(src.device, h, w, height, width, stream)
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_resize_bicubic_aa_u8(src.data_ptr(), n, h, w, c, out.data_ptr(), height, width,
+                                                           ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
+    return out
+
+
 def overlay_draw(src, overlay, *, out=None, stream=None):
     """ImageOverlay's drawing on frames already resident on the GPU."""
     _require_cuda(src, "overlay src")

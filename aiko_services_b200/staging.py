@@ -1,0 +1,85 @@
+"""Host -> device staging of frames: pinned buffers and cudaMemcpyAsync on a per-stream CUDA stream.
+
+One ``FrameStager`` per aiko stream (kept in ``stream.variables``, the place the reference gives
+elements for per-stream state, R/main/stream.py:81).  ``upload`` packs a list of equally shaped
+frames into a pinned buffer and enqueues one asynchronous copy; buffers rotate so the host can
+fill the next batch while the previous copy is in flight.
+"""
+import numpy as np
+import torch
+
+from .device_frames import DeviceBatch, DeviceImage, group_device_images
+
+
+class FrameStager:
+    def __init__(self, device, slots=2):
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(self.device)
+        self.slots = slots
+        self._pinned = [None] * slots
+        self._events = [None] * slots
+        self._next = 0
+
+    def _slot(self, nbytes):
+        i = self._next
+        self._next = (i + 1) % self.slots
+        if self._events[i] is not None:
+            self._events[i].synchronize()          # the copy out of this buffer has finished
+        if self._pinned[i] is None or self._pinned[i].numel() < nbytes:
+            self._pinned[i] = torch.empty(max(nbytes, 1), dtype=torch.uint8).pin_memory()
+        return i, self._pinned[i]
+
+    def upload_array(self, frames):
+        """frames: uint8 ndarray [N, H, W, C] or [N, H, W] (pageable or pinned) -> DeviceBatch"""
+        frames = np.ascontiguousarray(frames, dtype=np.uint8)
+        i, pinned = self._slot(frames.nbytes)
+        view = pinned[:frames.nbytes].view(frames.shape)
+        view.numpy()[...] = frames
+        return self.upload_pinned(view, i)
+
+    def upload_pinned(self, pinned_tensor, slot=None):
+        """A tensor already in pinned host memory -> DeviceBatch (one cudaMemcpyAsync)."""
+        with torch.cuda.stream(self.stream):
+            dev = torch.empty(pinned_tensor.shape, dtype=torch.uint8, device=self.device)
+            dev.copy_(pinned_tensor, non_blocking=True)
+            if slot is not None:
+                ev = torch.cuda.Event()
+                ev.record(self.stream)
+                self._events[slot] = ev
+        return DeviceBatch(dev, self.stream)
+
+    def upload(self, images):
+        """list of ndarray / PIL.Image / DeviceImage -> list of (DeviceBatch, positions).
+
+        Frames of equal shape are batched together; ``positions`` are their indices in ``images``.
+        """
+        whole = group_device_images(images)
+        if whole is not None:
+            return [(whole, list(range(len(images))))]
+        groups = {}
+        for pos, im in enumerate(images):
+            if isinstance(im, DeviceImage):
+                groups.setdefault(("dev", id(im.batch)), []).append(pos)
+            else:
+                a = im if isinstance(im, np.ndarray) else np.asarray(im)
+                groups.setdefault(("host", a.shape), []).append(pos)
+        out = []
+        for (where, _), positions in groups.items():
+            if where == "dev":
+                b = images[positions[0]].batch
+                idx = [images[p].index for p in positions]
+                if idx == list(range(len(b))):
+                    out.append((b, positions))
+                else:
+                    sel = torch.as_tensor(idx, device=b.device)
+                    out.append((DeviceBatch(b.tensor.index_select(0, sel).contiguous(), b.stream), positions))
+            else:
+                arrs = [images[p] if isinstance(images[p], np.ndarray) else np.asarray(images[p]) for p in positions]
+                nbytes = sum(a.nbytes for a in arrs)
+                i, pinned = self._slot(nbytes)
+                view = pinned[:nbytes].view((len(arrs),) + arrs[0].shape)
+                host = view.numpy()
+                for k, a in enumerate(arrs):
+                    host[k] = a
+                out.append((self.upload_pinned(view, i), positions))
+        return out

@@ -92,6 +92,21 @@ int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int src_h, int 
                                int dst_w, int64_t dst_row_stride, int64_t dst_frame_stride, int swap_rb,
                                const aiko_b200_overlay* overlay_host, void* stream);
 
+/* ImageResize, PIL branch: PIL.Image.resize((W, H)) -- default BICUBIC filter   */
+/* with antialiasing, 8 bits per channel, horizontal pass then vertical pass on a  */
+/* uint8 intermediate -- R/elements/media/image_io.py:218.  Bit-exact.             */
+/* The two fixed-point weight tables live in a caller-provided device workspace:   */
+/*   bytes   = aiko_b200_resize_bicubic_workspace_bytes(...)  (0 for bad sizes)    */
+/*   prepare = fills it for one (src, dst) size pair; reusable for any number of   */
+/*             resize calls with that size pair, on any stream ordered after it.   */
+/* Frames are tight: [n, h, w, channels], channels in {1, 3, 4}.                    */
+size_t aiko_b200_resize_bicubic_workspace_bytes(int src_h, int src_w, int dst_h, int dst_w);
+int aiko_b200_resize_bicubic_prepare(void* workspace, size_t workspace_bytes, int src_h, int src_w, int dst_h,
+                                     int dst_w, void* stream);
+int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, int src_h, int src_w, int channels,
+                                   uint8_t* dst, int dst_h, int dst_w, const void* workspace,
+                                   size_t workspace_bytes, void* stream);
+
 /* ImageOverlay alone on already-resident frames (image_io.py:107-163).     */
 /* channels == 3: frames are drawn in place of a copy src -> dst (src may   */
 /* equal dst).  channels == 1: the GRAY -> BGR -> draw -> BGR2GRAY round     */

@@ -91,6 +91,49 @@ def test_resize_cfg2_batch_properties(cuda):
     np.testing.assert_array_equal(swapped, out[..., ::-1])
 
 
+# ---------------------------------------------------------------- PIL bicubic resize (a-2)
+@pytest.mark.parametrize("case", cases.RESIZE_PIL, ids=lambda c: c[0])
+def test_resize_bicubic_golden(golden, cuda, case):
+    name, seed, sh, sw, dw, dh = case
+    img = cases.frame(seed, sh, sw, 3)
+    out = host(ops.resize_bicubic_aa(dev(img[None], cuda), dw, dh))[0]
+    check_golden(golden, "resize_pil/" + name, out)
+
+
+def test_resize_bicubic_random_shapes_vs_oracle(cuda):
+    rng = np.random.default_rng(111)
+    for i in range(40):
+        h, w, H, W = (int(v) for v in rng.integers(1, 200, 4))
+        c = int(rng.choice([1, 3, 4]))
+        n = int(rng.integers(1, 4))
+        frames = np.stack([cases.frame(5000 + 10 * i + k, h, w, c) for k in range(n)])
+        out = host(ops.resize_bicubic_aa(dev(frames, cuda), W, H))
+        for k in range(n):
+            np.testing.assert_array_equal(out[k], O.resize_bicubic_aa(frames[k], W, H), err_msg=f"{(h, w, c)}->{(H, W)}")
+
+
+def test_resize_bicubic_cfg1_batch(cuda):
+    """BASELINE config 1 size: every frame of a 1080p batch equals the oracle; edge values saturate."""
+    frames = np.stack([cases.frame(1000 + (i % 2), 1080, 1920, 3) for i in range(8)])
+    out = host(ops.resize_bicubic_aa(dev(frames, cuda), 640, 480))
+    refs = [O.resize_bicubic_aa(frames[i], 640, 480) for i in range(2)]
+    for i in range(8):
+        np.testing.assert_array_equal(out[i], refs[i % 2])
+    for v in (0, 255):
+        img = np.full((1, 200, 300, 3), v, np.uint8)
+        assert (host(ops.resize_bicubic_aa(dev(img, cuda), 77, 51)) == v).all()
+
+
+def test_resize_bicubic_workspace_errors(cuda):
+    from aiko_services_b200 import _native
+    lib = _native.lib()
+    assert lib.aiko_b200_resize_bicubic_workspace_bytes(0, 10, 10, 10) == 0
+    src = torch.zeros((1, 8, 8, 3), dtype=torch.uint8, device=cuda)
+    dst = torch.zeros((1, 4, 4, 3), dtype=torch.uint8, device=cuda)
+    rc = lib.aiko_b200_resize_bicubic_aa_u8(src.data_ptr(), 1, 8, 8, 3, dst.data_ptr(), 4, 4, None, 0, None)
+    assert rc == _native.ERR_WORKSPACE
+
+
 # ---------------------------------------------------------------- convert / flip / crop (a-4)
 @pytest.mark.parametrize("n_pixels", [0, 1, 15, 16, 17, 4097, 640 * 480, 1920 * 1080 + 5])
 def test_convert_ops_vs_oracle(cuda, n_pixels):
