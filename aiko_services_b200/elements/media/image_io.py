@@ -1,0 +1,264 @@
+"""GPU image elements with the reference's names, inputs, outputs and parameters
+(R/elements/media/image_io.py).  ``process_frame`` only enqueues work: frames are staged to the
+GPU once (pinned memory + cudaMemcpyAsync on the stream's CUDA stream), stay device-resident
+between consecutive elements as lazy ``DeviceImage`` items, and consecutive resize / overlay /
+colour-convert steps run as one fused kernel when the pixels are finally needed.
+
+``logic_*`` functions hold the behaviour; the classes below bind them to this package's
+runtime, and ``aiko_services_b200.reference_adapter`` binds the same functions to the
+reference's own ``aiko.PipelineElement`` so unmodified pipelines pick them up.
+"""
+import numpy as np
+
+from ...device_frames import DeviceImage
+from ...pipeline import PipelineElement
+from ...staging import FrameStager
+from ...stream import StreamEvent
+from .common_io import DataSource, DataTarget, contains_all
+
+__all__ = ["ImageConvert", "ImageOutput", "ImageOverlay", "ImageReadFile", "ImageResize", "ImageWriteFile"]
+
+_CONVERSIONS = ("RGB2BGR", "BGR2RGB", "RGB2GRAY", "BGR2GRAY", "GRAY2BGR")
+_FLIPS = {"vertical": 0, "horizontal": 1, "both": -1}
+
+
+def device_for(stream_id, n_devices=None):
+    """Streams are pinned to one GPU for their lifetime: stable hash of stream_id."""
+    import torch
+    import zlib
+    n = n_devices or torch.cuda.device_count()
+    if n <= 0:
+        raise RuntimeError("aiko_services_b200 needs a CUDA device (there is no CPU fallback)")
+    current = torch.cuda.current_device()
+    if n_devices is None and "LOCAL_RANK" in __import__("os").environ:
+        return current          # one process per GPU: the launcher already chose
+    return zlib.crc32(str(stream_id).encode()) % n
+
+
+def stager_for(stream):
+    """Per-stream CUDA stream + pinned staging ring, kept where the reference keeps per-stream
+    state (stream.variables, R/main/stream.py:81)."""
+    stager = stream.variables.get("_b200_stager")
+    if stager is None:
+        import torch
+        stager = FrameStager(torch.device("cuda", device_for(stream.stream_id)))
+        stream.variables["_b200_stager"] = stager
+    return stager
+
+
+def _apply(stream, images, step):
+    """Append one recipe step to every batch behind ``images`` -> new list, same order."""
+    if not images:
+        return []
+    out = [None] * len(images)
+    for batch, positions in stager_for(stream).upload(images):
+        result = batch.then(*step).images()
+        for k, pos in enumerate(positions):
+            out[pos] = result[k]
+    return out
+
+
+# ---- behaviour shared by both bindings ------------------------------------------------------
+def logic_image_resize(element, stream, images):
+    """ImageResize.process_frame (image_io.py:208-220): ndarray frames take cv2's bilinear
+    arithmetic, PIL frames take Pillow's antialiased bicubic arithmetic."""
+    resolution, _ = element.get_parameter("resolution")
+    width, height = resolution.split("x")
+    width, height = int(width), int(height)
+    arrays = [i for i, im in enumerate(images) if isinstance(im, (np.ndarray, DeviceImage))]
+    pil = [i for i in range(len(images)) if i not in set(arrays)]
+    out = [None] * len(images)
+    for idx, kind in ((arrays, "resize_linear"), (pil, "resize_bicubic")):
+        if idx:
+            for i, r in zip(idx, _apply(stream, [images[i] for i in idx], (kind, width, height))):
+                out[i] = r
+    if pil:   # the reference returns PIL images for PIL inputs
+        for i in pil:
+            out[i] = _LazyPil(out[i])
+    return StreamEvent.OKAY, {"images": out}
+
+
+class _LazyPil(DeviceImage):
+    """A DeviceImage that came from a PIL input: ``save`` / ``size`` like the PIL image the
+    reference would have produced, pixels still on the GPU until asked for."""
+
+    def __init__(self, image):
+        super().__init__(image.batch, image.index)
+
+    @property
+    def size(self):
+        return (self.shape[1], self.shape[0])
+
+    def save(self, path, *a, **k):
+        return self.to_pil().save(path, *a, **k)
+
+
+def logic_image_overlay(element, stream, images, overlay):
+    """ImageOverlay.process_frame (image_io.py:107-163)."""
+    for image in images:
+        if not isinstance(image, (np.ndarray, DeviceImage)) or isinstance(image, _LazyPil):
+            # the reference indexes image.shape, which PIL images lack -> its frame errors out
+            return StreamEvent.ERROR, {"diagnostic": "ImageOverlay: images must be numpy arrays"}
+    return StreamEvent.OKAY, {"images": _apply(stream, images, ("overlay", overlay))}
+
+
+def logic_image_convert(element, stream, images):
+    conversion, found = element.get_parameter("conversion", default=None)
+    flip, flip_found = element.get_parameter("flip", default=None)
+    if found:
+        if conversion not in _CONVERSIONS:
+            return StreamEvent.ERROR, {"diagnostic": f"ImageConvert: unknown conversion {conversion}"}
+        images = _apply(stream, images, ("convert", conversion))
+    if flip_found:
+        if flip not in _FLIPS:
+            return StreamEvent.ERROR, {"diagnostic": f"ImageConvert: unknown flip {flip}"}
+        images = _apply(stream, images, ("flip", _FLIPS[flip]))
+    return StreamEvent.OKAY, {"images": images}
+
+
+def logic_image_read_file(element, stream, paths):
+    """ImageReadFile.process_frame (image_io.py:180-191): lazy PIL open, decode deferred."""
+    from PIL import Image
+    images = []
+    for path in paths:
+        try:
+            images.append(Image.open(path))
+        except Exception as exception:
+            return StreamEvent.ERROR, {"diagnostic": f"Error loading image: {exception}"}
+    return StreamEvent.OKAY, {"images": images}
+
+
+def logic_image_write_file(element, stream, images):
+    """ImageWriteFile.process_frame (image_io.py:234-255)."""
+    from PIL import Image
+    for image in images:
+        path = stream.variables["target_path"]
+        if contains_all(path, "{}"):
+            path = path.format(stream.variables["target_file_id"])
+            stream.variables["target_file_id"] += 1
+        if isinstance(image, DeviceImage):
+            image = image.to_pil()
+        elif not isinstance(image, Image.Image):
+            if isinstance(image, np.ndarray):
+                image = Image.fromarray(image.astype("uint8"), "RGB")
+            else:
+                return StreamEvent.ERROR, {"diagnostic": "UNKNOWN IMAGE TYPE"}
+        try:
+            image.save(path)
+        except Exception as exception:
+            return StreamEvent.ERROR, {"diagnostic": f"Error saving image: {exception}"}
+    return StreamEvent.OKAY, {}
+
+
+def _pipeline_stager(pipeline, device_index):
+    """Stager shared by the streams of one GPU, used when frames of many streams travel together."""
+    import torch
+    stagers = pipeline.__dict__.setdefault("_b200_stagers", {})
+    if device_index not in stagers:
+        stagers[device_index] = FrameStager(torch.device("cuda", device_index), slots=3)
+    return stagers[device_index]
+
+
+def _cross_stream(prepare):
+    """Build ``process_frame_batch`` for an element whose work is one recipe step per frame.
+
+    ``prepare(element, stream, **inputs)`` returns either ``(StreamEvent.ERROR, diagnostic)`` or
+    ``(images, step, merge_key)``.  Frames of all calls that share a GPU and a merge key (and a
+    shape) are staged together and extended by ONE step, so the kernel that eventually runs
+    covers every concurrent stream -- batching keyed by stream_id as the frames' owners.
+    ``step`` may end in a per-call argument (ImageOverlay's dict); it is expanded per frame.
+    """
+    def process_frame_batch(self, calls, pipeline):
+        results = [None] * len(calls)
+        buckets = {}                       # (device, merge_key) -> [(call index, images, step)]
+        for ci, (stream, inputs) in enumerate(calls):
+            pipeline._enable_thread_local(stream, stream.frame_id)
+            try:
+                prepared = prepare(self, stream, **inputs)
+            except Exception as exception:      # same containment as a per-frame call
+                prepared = (StreamEvent.ERROR, {"diagnostic": repr(exception)})
+            finally:
+                pipeline._disable_thread_local()
+            if len(prepared) == 2:
+                results[ci] = prepared
+                continue
+            images, step, merge_key = prepared
+            buckets.setdefault((device_for(stream.stream_id), merge_key), []).append((ci, images, step))
+        for (device_index, _), members in buckets.items():
+            flat, owner = [], []
+            for ci, images, step in members:
+                for k, image in enumerate(images):
+                    flat.append(image)
+                    owner.append((ci, k, step))
+            outputs = {ci: [None] * len(images) for ci, images, _ in members}
+            if flat:
+                for batch, positions in _pipeline_stager(pipeline, device_index).upload(flat):
+                    step = owner[positions[0]][2]
+                    if step[0] == "overlay":   # one overlay dict per frame, in batch order
+                        step = ("overlay", [owner[p][2][1] for p in positions])
+                    for image, pos in zip(batch.then(*step).images(), positions):
+                        ci, k, _ = owner[pos]
+                        outputs[ci][k] = image
+            for ci, _, _ in members:
+                results[ci] = (StreamEvent.OKAY, {"images": outputs[ci]})
+        return results
+    return process_frame_batch
+
+
+def _prepare_resize(element, stream, images):
+    if any(not isinstance(im, (np.ndarray, DeviceImage)) for im in images):
+        return logic_image_resize(element, stream, images)       # PIL frames: per-stream path
+    resolution, _ = element.get_parameter("resolution")
+    width, height = (int(v) for v in resolution.split("x"))
+    return images, ("resize_linear", width, height), ("resize_linear", width, height)
+
+
+def _prepare_overlay(element, stream, images, overlay):
+    for image in images:
+        if not isinstance(image, (np.ndarray, DeviceImage)) or isinstance(image, _LazyPil):
+            return StreamEvent.ERROR, {"diagnostic": "ImageOverlay: images must be numpy arrays"}
+    return images, ("overlay", overlay), "overlay"
+
+
+def _prepare_convert(element, stream, images):
+    conversion, found = element.get_parameter("conversion", default=None)
+    flip, flip_found = element.get_parameter("flip", default=None)
+    if flip_found or not found or conversion not in _CONVERSIONS:
+        return logic_image_convert(element, stream, images)      # rare combinations: per-stream path
+    return images, ("convert", conversion), ("convert", conversion)
+
+
+# ---- this package's runtime bindings -------------------------------------------------------------
+class ImageOutput(PipelineElement):
+    def process_frame(self, stream, images):
+        return StreamEvent.OKAY, {"images": images}
+
+
+class ImageResize(PipelineElement):
+    batch_across_streams = True
+    process_frame = logic_image_resize
+    process_frame_batch = _cross_stream(_prepare_resize)
+
+
+class ImageOverlay(PipelineElement):
+    batch_across_streams = True
+    process_frame = logic_image_overlay
+    process_frame_batch = _cross_stream(_prepare_overlay)
+
+
+class ImageConvert(PipelineElement):
+    """GPU home of the colour-conversion / flip call sites of R/elements/media/video_io.py:129,299
+    and webcam_io.py:122-129 (those elements' capture and codec parts are out of scope).
+    Parameters: ``conversion`` in RGB2BGR | BGR2RGB | RGB2GRAY | BGR2GRAY | GRAY2BGR and / or
+    ``flip`` in horizontal | vertical | both."""
+    batch_across_streams = True
+    process_frame = logic_image_convert
+    process_frame_batch = _cross_stream(_prepare_convert)
+
+
+class ImageReadFile(DataSource):
+    process_frame = logic_image_read_file
+
+
+class ImageWriteFile(DataTarget):
+    process_frame = logic_image_write_file

@@ -15,7 +15,10 @@ import sys
 import threading
 import types
 
-REFERENCE_SRC = "/root/reference/src"
+_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# the read-only mount in the build container, else the git-ignored copy that travels to the GPU box
+_CANDIDATES = ["/root/reference/src", os.path.join(_ROOT, "baseline", "_ref")]
+REFERENCE_SRC = next((c for c in _CANDIDATES if os.path.isdir(os.path.join(c, "aiko_services"))), _CANDIDATES[0])
 
 
 def available():
@@ -110,7 +113,7 @@ def load_reference():
     global _aiko
     if _aiko is None:
         if not available():
-            raise RuntimeError("/root/reference is not present on this machine")
+            raise RuntimeError("the reference is not present on this machine (see baseline/install_ref.sh)")
         os.environ.setdefault("AIKO_LOG_MQTT", "false")
         os.environ.setdefault("AIKO_LOG_LEVEL", "WARNING")
         sys.dont_write_bytecode = True

@@ -1,0 +1,160 @@
+"""GPU: the reference-facing element / pipeline layer.  Existing pipeline-definition JSON
+(module names of the reference) runs on this package's runtime, frames stay device-resident
+between elements, frames of many streams are batched into one launch, and -- where the
+reference package is present -- the same GPU elements run inside the reference's own,
+unmodified PipelineImpl.  Results are compared with the reference elements' cv2 / Pillow calls
+(oracle/reference_port.py) and the C oracle."""
+import json
+import os
+import queue
+
+import numpy as np
+import pytest
+import torch
+
+from aiko_services_b200.device_frames import DeviceImage
+from aiko_services_b200.pipeline import Pipeline
+from golden import cases
+from oracle import image as O
+from oracle import ref_harness, reference_port
+
+pytestmark = pytest.mark.gpu
+
+IMAGE_IO = "aiko_services.elements.media.image_io"     # what existing definitions name
+
+SOURCE = '''
+from aiko_services_b200.pipeline import PipelineElement
+from aiko_services_b200.stream import StreamEvent
+
+class Feed(PipelineElement):
+    def process_frame(self, stream, **inputs):
+        return StreamEvent.OKAY, inputs
+'''
+
+
+def definition(tmp_path, names, resolution="64x48", extra=None):
+    src = tmp_path / "feed.py"
+    src.write_text(SOURCE)
+    io = {"Feed": (["images", "overlay"], ["images", "overlay"]), "ImageResize": (["images"], ["images"]),
+          "ImageOverlay": (["images", "overlay"], ["images"]), "ImageConvert": (["images"], ["images"]),
+          "ImageOutput": (["images"], ["images"])}
+    elements = []
+    for name in names:
+        i, o = io[name]
+        e = {"name": name, "input": [{"name": k, "type": "any"} for k in i],
+             "output": [{"name": k, "type": "any"} for k in o],
+             "deploy": {"local": {"module": str(src) if name == "Feed" else IMAGE_IO}}}
+        if extra and name in extra:
+            e["parameters"] = extra[name]
+        elements.append(e)
+    return {"version": 0, "name": "p_gpu", "runtime": "python", "graph": ["(" + " ".join(names) + ")"],
+            "parameters": {"resolution": resolution}, "elements": elements}
+
+
+def test_chain_device_resident_and_fused(cuda, tmp_path):
+    names = ["Feed", "ImageResize", "ImageOverlay", "ImageConvert", "ImageOutput"]
+    p = Pipeline(definition(tmp_path, names, "160x120", {"ImageConvert": {"conversion": "RGB2BGR"}}))
+    frames = [cases.frame(700 + k, 270, 480, 3) for k in range(4)]
+    q = queue.Queue()
+    assert p.create_stream("s1", queue_response=q)
+    okay, swag = p.process_frame({"stream_id": "s1", "frame_id": 0}, {"images": frames, "overlay": cases.OVERLAY_SMALL})
+    assert okay
+    images = swag["images"]
+    assert all(isinstance(im, DeviceImage) for im in images)
+    batch = images[0].batch
+    assert batch._tensor is None and [s[0] for s in batch._recipe] == ["resize_linear", "overlay", "convert"]
+    ref = reference_port.chain_resize_overlay_bgr(frames, "160x120", cases.OVERLAY_SMALL)
+    for im, r in zip(images, ref):
+        np.testing.assert_array_equal(np.asarray(im), r)          # D2H on demand, like an ndarray
+    assert images[0].shape == (120, 160, 3)
+
+
+def test_cross_stream_batching_one_launch(cuda, tmp_path):
+    p = Pipeline(definition(tmp_path, ["Feed", "ImageResize", "ImageOverlay", "ImageOutput"], "96x64"))
+    rng = np.random.default_rng(1)
+    work, expect = [], []
+    for k in range(12):
+        sid = f"s{k:02d}"
+        assert p.create_stream(sid)
+        frame = cases.frame(800 + k, 128, 192, 3)
+        overlay = {"objects": [{"name": f"id{k}", "confidence": 0.5 + k / 100}],
+                   "rectangles": [{"x": 5 + k, "y": 30, "w": 40, "h": 20}]}
+        work.append(({"stream_id": sid, "frame_id": 0}, {"images": [frame], "overlay": overlay}))
+        expect.append(reference_port.image_overlay(reference_port.image_resize([frame], "96x64"), overlay)[0])
+    results = p.process_frames(work)
+    batches = {id(swag["images"][0].batch) for okay, swag in results}
+    assert len(batches) == 1                      # 12 streams -> one DeviceBatch -> one fused launch
+    for (okay, swag), ref in zip(results, expect):
+        assert okay
+        np.testing.assert_array_equal(np.asarray(swag["images"][0]), ref)
+
+
+def test_pil_branch_read_resize_write(cuda, tmp_path):
+    from PIL import Image
+    for k in range(3):
+        Image.fromarray(cases.frame(900 + k, 120, 160, 3), "RGB").save(tmp_path / f"in_{k:02d}.png")
+    d = {"version": 0, "name": "p_image_0", "runtime": "python",
+         "graph": ["(ImageReadFile ImageResize ImageWriteFile)"], "parameters": {"resolution": "80x60"},
+         "elements": [
+             {"name": "ImageReadFile", "parameters": {"data_sources": f"(file://{tmp_path}/in_{{}}.png)",
+                                                      "data_batch_size": 2},
+              "input": [{"name": "paths", "type": "[Path]"}], "output": [{"name": "images", "type": "[image]"}],
+              "deploy": {"local": {"module": IMAGE_IO}}},
+             {"name": "ImageResize", "input": [{"name": "images", "type": "[image]"}],
+              "output": [{"name": "images", "type": "[image]"}], "deploy": {"local": {"module": IMAGE_IO}}},
+             {"name": "ImageWriteFile", "parameters": {"data_targets": f"file://{tmp_path}/out_{{:02d}}.png"},
+              "input": [{"name": "images", "type": "[image]"}], "output": [],
+              "deploy": {"local": {"module": IMAGE_IO}}}]}
+    p = Pipeline(d)
+    assert p.create_stream("1")
+    p.run()
+    for k in range(3):
+        got = np.asarray(Image.open(tmp_path / f"out_{k:02d}.png"))
+        ref = np.asarray(Image.open(tmp_path / f"in_{k:02d}.png").resize((80, 60)))
+        np.testing.assert_array_equal(got, ref)
+
+
+def test_errors_become_stream_events(cuda, tmp_path):
+    from PIL import Image
+    p = Pipeline(definition(tmp_path, ["Feed", "ImageOverlay", "ImageOutput"]))
+    assert p.create_stream("e")
+    pil = Image.fromarray(cases.frame(1, 32, 32, 3), "RGB")
+    okay, _ = p.process_frame({"stream_id": "e"}, {"images": [pil], "overlay": {}})
+    assert not okay and "e" not in p.streams          # ERROR destroys the stream, as in the reference
+    p = Pipeline(definition(tmp_path, ["Feed", "ImageResize", "ImageOutput"], resolution="bogus"))
+    assert p.create_stream("f")
+    okay, _ = p.process_frame({"stream_id": "f"}, {"images": [cases.frame(1, 32, 32, 3)], "overlay": {}})
+    assert not okay and "f" not in p.streams
+
+
+def test_gray_and_mixed_shapes(cuda, tmp_path):
+    p = Pipeline(definition(tmp_path, ["Feed", "ImageResize", "ImageOverlay", "ImageOutput"], "64x48"))
+    assert p.create_stream("g")
+    frames = [cases.frame(1, 96, 128, 3), cases.frame(2, 96, 128, 1), cases.frame(3, 50, 70, 3)]
+    okay, swag = p.process_frame({"stream_id": "g"}, {"images": frames, "overlay": cases.OVERLAY_RECTS_ONLY})
+    assert okay
+    ref = reference_port.image_overlay(reference_port.image_resize(frames, "64x48"), cases.OVERLAY_RECTS_ONLY)
+    for im, r in zip(swag["images"], ref):
+        np.testing.assert_array_equal(np.asarray(im), r)
+
+
+@pytest.mark.skipif(not ref_harness.available(), reason="reference package not present (baseline/install_ref.sh)")
+def test_drop_in_inside_the_unmodified_reference_runtime(cuda):
+    """The reference's own PipelineImpl, its own JSON module names, GPU elements underneath."""
+    ref_harness.load_reference()
+    from aiko_services_b200 import reference_adapter
+    module = reference_adapter.install()
+    try:
+        frames = [cases.frame(2000 + i, 1080, 1920, 3) for i in range(2)]
+        out = ref_harness.run_reference_pipeline(
+            [("ImageResize", IMAGE_IO, ["images"], ["images"], {"resolution": "640x480"}),
+             ("ImageOverlay", IMAGE_IO, ["images", "overlay"], ["images"], None),
+             ("ImageOutput", IMAGE_IO, ["images"], ["images"], None)],
+            [{"images": frames, "overlay": cases.OVERLAY_4}])
+        images = out[0]["images"]
+        assert type(images[0]).__name__ == "DeviceImage"          # the GPU classes were the ones loaded
+        ref = reference_port.image_overlay(reference_port.image_resize(frames, "640x480"), cases.OVERLAY_4)
+        for im, r in zip(images, ref):
+            np.testing.assert_array_equal(np.asarray(im), r)
+    finally:
+        reference_adapter.uninstall()
