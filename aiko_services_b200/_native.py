@@ -50,6 +50,7 @@ SIGNATURES = {
     "aiko_b200_resize_bicubic_workspace_bytes": [_i, _i, _i, _i],
     "aiko_b200_resize_bicubic_prepare": [_vp, _sz, _i, _i, _i, _i, _vp],
     "aiko_b200_resize_bicubic_aa_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp, _sz, _vp],
+    "aiko_b200_resize_bicubic_aa_u8_noalloc": [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp],
     "aiko_b200_overlay_u8": [_vp, _vp, _i, _i, _i, _i, _i64, _i64, _ovp, _vp],
     "aiko_b200_swap_rb_u8": [_vp, _vp, _i64, _vp],
     "aiko_b200_bgr2gray_u8": [_vp, _vp, _i64, _i, _vp],

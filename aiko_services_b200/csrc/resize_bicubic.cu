@@ -275,3 +275,64 @@ extern "C" int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, 
   resize_bicubic_rows<<<(unsigned)grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
   return cuda_status(cudaGetLastError(), "resize_bicubic launch");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant.
+//
+// Some users of this library cannot give the bicubic resize a workspace because they cannot
+// allocate device memory at the point where they call it: an element whose process_frame runs
+// on the pipeline's single event-loop thread (a cudaMalloc there synchronises the device and
+// holds up every other stream's frames), a service that handed all device memory to its own
+// pool at start-up, or a thin foreign-language binding that can only pass the frame buffers it
+// was given.  For them the weight tables live in the fixed array below instead.
+//
+// The array is part of the loaded library image: every GPU that loads libaiko_b200.so holds
+// these kStaticScratchBytes until the process exits, whether or not this entry point is used.
+constexpr size_t kStaticScratchBytes = 256 * 1024;
+static __device__ __align__(256) int g_bicubic_static_scratch[kStaticScratchBytes / sizeof(int)];
+
+// In host code `g_bicubic_static_scratch` is only a handle for the symbol, not an address a
+// kernel could use; the device address is looked up once per device (with that device
+// current) and remembered.
+static int* g_static_scratch_ptr[64];
+
+static int static_scratch_for_current_device(int** out) {
+  int dev = 0;
+  AIKO_CUDA(cudaGetDevice(&dev));
+  AIKO_CHECK_ARG(dev >= 0 && dev < 64, "resize_bicubic_noalloc: device index %d out of range", dev);
+  int* p = __atomic_load_n(&g_static_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    void* addr = nullptr;
+    AIKO_CUDA(cudaGetSymbolAddress(&addr, g_bicubic_static_scratch));
+    p = static_cast<int*>(addr);
+    __atomic_store_n(&g_static_scratch_ptr[dev], p, __ATOMIC_RELEASE);  // same value from any thread
+  }
+  *out = p;
+  return AIKO_B200_OK;
+}
+
+extern "C" int aiko_b200_resize_bicubic_aa_u8_noalloc(const uint8_t* src, int n_frames, int src_h, int src_w,
+                                                      int channels, uint8_t* dst, int dst_h, int dst_w,
+                                                      void* stream) {
+  AIKO_CHECK_ARG(n_frames >= 0, "resize_bicubic_noalloc: n_frames < 0");
+  AIKO_CHECK_ARG(src_h > 0 && src_w > 0 && dst_h > 0 && dst_w > 0, "resize_bicubic_noalloc: bad size");
+  const size_t need = aiko_b200_resize_bicubic_workspace_bytes(src_h, src_w, dst_h, dst_w);
+  if (need > kStaticScratchBytes) {
+    set_last_error(
+        "resize_bicubic_noalloc: %dx%d -> %dx%d needs %zu bytes of weight tables but the built-in scratch holds %zu; "
+        "use aiko_b200_resize_bicubic_aa_u8 with a workspace of your own",
+        src_w, src_h, dst_w, dst_h, need, kStaticScratchBytes);
+    return AIKO_B200_ERR_UNSUPPORTED;
+  }
+  if (n_frames == 0) return AIKO_B200_OK;
+  int* scratch = nullptr;
+  const int rc = static_scratch_for_current_device(&scratch);
+  if (rc != AIKO_B200_OK) return rc;
+  // Both tables are rewritten in full (every bound, every weight, padding weights as zero)
+  // before the resize reads them, on the same stream: nothing left by an earlier call is ever
+  // read, so there is nothing that has to be cleared first.
+  const int prc = aiko_b200_resize_bicubic_prepare(scratch, kStaticScratchBytes, src_h, src_w, dst_h, dst_w, stream);
+  if (prc != AIKO_B200_OK) return prc;
+  return aiko_b200_resize_bicubic_aa_u8(src, n_frames, src_h, src_w, channels, dst, dst_h, dst_w, scratch,
+                                        kStaticScratchBytes, stream);
+}

@@ -107,6 +107,20 @@ int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, int src_h, 
                                    uint8_t* dst, int dst_h, int dst_w, const void* workspace,
                                    size_t workspace_bytes, void* stream);
 
+/* Same resize for callers that cannot allocate device memory where they call it    */
+/* (an element running on the pipeline's one event-loop thread, where cudaMalloc     */
+/* would stall every stream; a process whose device memory is all owned by a pool;   */
+/* a minimal binding that only has the frame buffers).  No counterpart in the        */
+/* reference.  The weight tables go into a 256 KiB array built into the library      */
+/* (resident on every GPU that loads it); size pairs needing more are refused with   */
+/* AIKO_B200_ERR_UNSUPPORTED (1080p -> 640x480 needs 73 KB).  The first call on a    */
+/* device looks up that array's device address (cudaGetSymbolAddress): make it       */
+/* before any stream capture.  All calls share the one array and each rewrites it:   */
+/* calls that can overlap on the GPU (different streams, no ordering) race -- give   */
+/* such callers the workspace variant above.  Allocates and frees nothing.           */
+int aiko_b200_resize_bicubic_aa_u8_noalloc(const uint8_t* src, int n_frames, int src_h, int src_w, int channels,
+                                           uint8_t* dst, int dst_h, int dst_w, void* stream);
+
 /* ImageOverlay alone on already-resident frames (image_io.py:107-163).     */
 /* channels == 3: frames are drawn in place of a copy src -> dst (src may   */
 /* equal dst).  channels == 1: the GRAY -> BGR -> draw -> BGR2GRAY round     */
