@@ -275,7 +275,7 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
     for (int it = 0; it < my_items; ++it) {
       mbar_wait(&full[slot], (uint32_t)(round & 1), 500, 0);
       int* rec = mring + rslot * mrec;
-      const int dy = rec[1], ob = rec[4], nops = rec[5];
+      const int dy = rec[1], nops = rec[5];
       if (nops > 0 && nops <= p.ops_cap) {
         const aiko_b200_overlay_op* fops = opsring + (size_t)rslot * p.ops_cap;
         for (int wi = 0; wi * 32 < nops; wi++) {

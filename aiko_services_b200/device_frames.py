@@ -26,6 +26,7 @@ class DeviceBatch:
         self._tensor = tensor if not self._recipe else None
         self._host = None
         self.stream = stream             # torch.cuda.Stream the batch's work is ordered on
+        self.stager = None               # FrameStager that brought the frames in (pinned result buffers)
 
     # ---- geometry of the result, known without running anything
     @property
@@ -47,8 +48,10 @@ class DeviceBatch:
         return (h, w) if c == 1 else (h, w, c)
 
     def then(self, *step):
-        return DeviceBatch(self._source if self._tensor is None else self._tensor, self.stream,
-                           (self._recipe if self._tensor is None else []) + [tuple(step)])
+        nxt = DeviceBatch(self._source if self._tensor is None else self._tensor, self.stream,
+                          (self._recipe if self._tensor is None else []) + [tuple(step)])
+        nxt.stager = self.stager
+        return nxt
 
     # ---- materialisation
     @property
@@ -118,17 +121,26 @@ class DeviceBatch:
             i += 1
         return t
 
-    def host(self, out=None):
-        """The whole batch as one ndarray (one device-to-host copy, cached)."""
-        if self._host is None:
-            t = self.tensor
+    def host_view(self):
+        """The whole batch as one ndarray over PINNED memory: one asynchronous device-to-host
+        copy, no further host copy.  The stager reuses that buffer for the next result of the
+        same shape on this stream, so the view is only valid until then."""
+        t = self.tensor
+        if self.stager is None:
             if self.stream is not None:
-                with torch.cuda.stream(self.stream):
-                    h = t.to("cpu", non_blocking=False) if out is None else out.copy_(t, non_blocking=True)
                 self.stream.synchronize()
-            else:
-                h = t.cpu() if out is None else out.copy_(t)
-            self._host = h.numpy()
+            return t.cpu().numpy()
+        out = self.stager.pinned_out(t.shape)
+        with torch.cuda.stream(self.stream):
+            out.copy_(t, non_blocking=True)
+        self.stream.synchronize()
+        return out.numpy()
+
+    def host(self):
+        """The whole batch as one ndarray that the caller may keep (cached)."""
+        if self._host is None:
+            view = self.host_view()
+            self._host = np.array(view, copy=True) if self.stager is not None else view
         return self._host
 
     def images(self):

@@ -19,6 +19,8 @@ class FrameStager:
         self._pinned = [None] * slots
         self._events = [None] * slots
         self._next = 0
+        self._owned = {}          # pinned blocks handed out by allocate(): base address -> tensor
+        self._out = {}            # pinned result buffers by (shape): reused for device-to-host copies
 
     def _slot(self, nbytes):
         i = self._next
@@ -28,6 +30,31 @@ class FrameStager:
         if self._pinned[i] is None or self._pinned[i].numel() < nbytes:
             self._pinned[i] = torch.empty(max(nbytes, 1), dtype=torch.uint8).pin_memory()
         return i, self._pinned[i]
+
+    def allocate(self, n, frame_shape):
+        """-> list of ``n`` uint8 ndarray views, each of ``frame_shape``, over one pinned buffer.
+
+        A source element (decoder, camera reader, test generator) writes its frames here; ``upload``
+        recognises such frames and issues the cudaMemcpyAsync straight from this memory, with no
+        intermediate host copy.  The buffer belongs to the caller until it is uploaded.
+        """
+        count = int(np.prod(frame_shape))
+        pinned = torch.empty(max(n * count, 1), dtype=torch.uint8).pin_memory()
+        block = pinned[:n * count].view((n,) + tuple(frame_shape))
+        self._owned[block.data_ptr()] = block
+        return [block[i].numpy() for i in range(n)]
+
+    def _owned_block(self, arrays):
+        """If ``arrays`` are all the frames of one ``allocate`` block, in order, return its tensor."""
+        block = self._owned.get(arrays[0].ctypes.data)
+        if block is None or block.shape[0] != len(arrays) or tuple(block.shape[1:]) != arrays[0].shape:
+            return None
+        step = block[0].numel()
+        base = block.data_ptr()
+        for i, a in enumerate(arrays):
+            if a.ctypes.data != base + i * step or not a.flags.c_contiguous or a.dtype != np.uint8:
+                return None
+        return block
 
     def upload_array(self, frames):
         """frames: uint8 ndarray [N, H, W, C] or [N, H, W] (pageable or pinned) -> DeviceBatch"""
@@ -75,11 +102,28 @@ class FrameStager:
                     out.append((DeviceBatch(b.tensor.index_select(0, sel).contiguous(), b.stream), positions))
             else:
                 arrs = [images[p] if isinstance(images[p], np.ndarray) else np.asarray(images[p]) for p in positions]
+                block = self._owned_block(arrs)
+                if block is not None:                 # frames were produced in our pinned memory: no host copy
+                    batch = self.upload_pinned(block)
+                    batch.stager = self
+                    out.append((batch, positions))
+                    continue
                 nbytes = sum(a.nbytes for a in arrs)
                 i, pinned = self._slot(nbytes)
                 view = pinned[:nbytes].view((len(arrs),) + arrs[0].shape)
                 host = view.numpy()
                 for k, a in enumerate(arrs):
                     host[k] = a
-                out.append((self.upload_pinned(view, i), positions))
+                batch = self.upload_pinned(view, i)
+                batch.stager = self
+                out.append((batch, positions))
         return out
+
+    def pinned_out(self, shape):
+        """A pinned host buffer for results of ``shape`` (reused between batches of that shape)."""
+        key = tuple(shape)
+        buf = self._out.get(key)
+        if buf is None:
+            buf = torch.empty(key, dtype=torch.uint8).pin_memory()
+            self._out[key] = buf
+        return buf
