@@ -51,6 +51,12 @@ SIGNATURES = {
     "aiko_b200_resize_bicubic_prepare": [_vp, _sz, _i, _i, _i, _i, _vp],
     "aiko_b200_resize_bicubic_aa_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp, _sz, _vp],
     "aiko_b200_resize_bicubic_aa_u8_noalloc": [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp],
+    "aiko_b200_resize_norm_f32_nchw": [_vp, _i, _i, _i, _vp, _i, _i, ctypes.POINTER(ctypes.c_float),
+                                       ctypes.POINTER(ctypes.c_float), _vp],
+    "aiko_b200_audio_workspace_bytes": [_i],
+    "aiko_b200_audio_prepare": [_vp, _sz, _i, _vp],
+    "aiko_b200_audio_chain": [_vp, _i, _i, _i, ctypes.c_double, _vp, _vp, ctypes.POINTER(_i), _vp, _vp, _vp, _i, _i,
+                              _vp, _sz, _vp],
     "aiko_b200_overlay_u8": [_vp, _vp, _i, _i, _i, _i, _i64, _i64, _ovp, _vp],
     "aiko_b200_swap_rb_u8": [_vp, _vp, _i64, _vp],
     "aiko_b200_bgr2gray_u8": [_vp, _vp, _i64, _i, _vp],
@@ -59,7 +65,8 @@ SIGNATURES = {
     "aiko_b200_crop_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _vp],
 }
 
-RESTYPES = {"aiko_b200_last_error": ctypes.c_char_p, "aiko_b200_resize_bicubic_workspace_bytes": ctypes.c_size_t}
+RESTYPES = {"aiko_b200_last_error": ctypes.c_char_p, "aiko_b200_resize_bicubic_workspace_bytes": ctypes.c_size_t,
+            "aiko_b200_audio_workspace_bytes": ctypes.c_size_t}
 
 _lib = None
 

@@ -1,0 +1,84 @@
+"""Python-facing audio chain over the C ABI (PE_FFT -> PE_AudioResampler -> PE_AudioFilter,
+R/elements/media/audio_io.py:202-320), batched over windows resident on the GPU."""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _native
+from ._native import check
+from .ops import _require_cuda, _stream_ptr
+
+AF_FREQUENCY_MINIMUM, AF_FREQUENCY_MAXIMUM = 10, 9000     # audio_io.py:204-205
+AR_BAND_COUNT = 8                                         # audio_io.py:237
+
+_plans = {}
+
+
+class AudioPlan:
+    """Per (device, window length, sample rate): twiddle workspace and the float64-evaluated
+    constants of the chain (fftfreq, band edges, frequency gate)."""
+
+    def __init__(self, device, n, sample_rate):
+        self.n, self.sample_rate = n, float(sample_rate)
+        lib = _native.lib()
+        nbytes = lib.aiko_b200_audio_workspace_bytes(n)
+        if nbytes == 0:
+            raise ValueError(f"audio window length {n} must be even and >= 4")
+        self.workspace = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        with torch.cuda.device(device):
+            check(lib.aiko_b200_audio_prepare(self.workspace.data_ptr(), nbytes, n, _stream_ptr()))
+        torch.cuda.current_stream(device).synchronize()
+        self.frequencies = np.fft.fftfreq(n, 1 / self.sample_rate)             # PE_FFT, :312-313
+        half = self.frequencies[0:n // 2]                                      # PE_AudioResampler, :253-257
+        band_width = (half[-1] - half[0]) / AR_BAND_COUNT / 10
+        ranges = []
+        for band in range(AR_BAND_COUNT):
+            start, end = band * band_width, band * band_width + band_width
+            idx = np.nonzero((half >= start) & (half < end))[0]
+            ranges += [int(idx[0]), int(idx[-1]) + 1] if len(idx) else [0, 0]
+        self.band_ranges = (ctypes.c_int * 16)(*ranges)
+        self.band_frequencies = np.array([(b * band_width + b * band_width + band_width) / 2
+                                          for b in range(AR_BAND_COUNT)])
+        folded = np.abs(self.frequencies[:n // 2 + 1])                         # |f| of bins k = 0 .. n/2
+        ok = np.nonzero((folded >= AF_FREQUENCY_MINIMUM) & (folded <= AF_FREQUENCY_MAXIMUM))[0]
+        self.gate = (int(ok[0]), int(ok[-1])) if len(ok) else (1, 0)
+
+
+def plan(device, n, sample_rate):
+    key = (str(device), n, float(sample_rate))
+    if key not in _plans:
+        _plans[key] = AudioPlan(device, n, sample_rate)
+    return _plans[key]
+
+
+def audio_chain(audio, sample_rate, *, bands=True, top=True, stream=None):
+    """audio: int16 or float32 CUDA tensor [windows, n].  Returns a dict with ``amplitudes``
+    [windows, n] float32, ``frequencies`` (numpy float64 [n], the same for every window),
+    and, when asked, ``band_frequencies`` [8], ``band_amplitudes`` [windows, 8],
+    ``top_frequencies`` / ``top_amplitudes`` [windows, 100], ``top_count`` [windows]."""
+    if audio.dtype not in (torch.int16, torch.float32):
+        raise TypeError(f"audio_chain: int16 or float32 expected, got {audio.dtype}")
+    _require_cuda(audio, "audio_chain audio", audio.dtype)
+    if audio.dim() != 2:
+        raise ValueError("audio_chain: expected [windows, samples]")
+    b, n = audio.shape
+    pl = plan(audio.device, n, sample_rate)
+    dev = audio.device
+    out = {"frequencies": pl.frequencies,
+           "amplitudes": torch.empty((b, n), dtype=torch.float32, device=dev)}
+    band = torch.empty((b, 8), dtype=torch.float32, device=dev) if bands else None
+    tf = torch.empty((b, 100), dtype=torch.float32, device=dev) if top else None
+    ta = torch.empty((b, 100), dtype=torch.float32, device=dev) if top else None
+    tc = torch.empty((b,), dtype=torch.int32, device=dev) if top else None
+    with torch.cuda.device(dev):
+        check(_native.lib().aiko_b200_audio_chain(
+            audio.data_ptr(), 0 if audio.dtype == torch.int16 else 1, b, n, pl.sample_rate,
+            out["amplitudes"].data_ptr(), band.data_ptr() if bands else None, pl.band_ranges,
+            tf.data_ptr() if top else None, ta.data_ptr() if top else None, tc.data_ptr() if top else None,
+            pl.gate[0], pl.gate[1], pl.workspace.data_ptr(), pl.workspace.numel(), _stream_ptr(stream)))
+    if bands:
+        out["band_frequencies"], out["band_amplitudes"] = pl.band_frequencies, band
+    if top:
+        out["top_frequencies"], out["top_amplitudes"], out["top_count"] = tf, ta, tc
+    return out

@@ -1,0 +1,347 @@
+// The reference's audio chain, batched over windows: PE_FFT -> PE_AudioResampler (8 band sums)
+// -> PE_AudioFilter (spectral gate + 100 loudest bins), R/elements/media/audio_io.py:202-320
+// (dead code in the reference: it sits inside a string literal; oracle = oracle/audio.py).
+//
+// One CTA per window.  A real window of N samples is packed into N/2 complex points
+// (z[n] = x[2n] + i x[2n+1]), transformed in shared memory by a mixed-radix (4/5/3/2) Stockham
+// autosort FFT that ping-pongs between two buffers, and unpacked to the N-point spectrum;
+// magnitudes / 1e6 go to HBM once, and the band sums and the gate + top-100 selection run on
+// the copy that is still in shared memory.  Twiddles come from a table generated in double
+// precision (aiko_b200_audio_prepare); all arithmetic is fp32 (tolerance 1e-4).
+// Per window HBM sees 2N bytes in (int16) and 4N bytes out: the path is HBM-bound.
+#include "common.cuh"
+
+namespace aiko {
+
+constexpr int kAudioThreads = 1024;
+constexpr int kMaxStages = 16;
+constexpr int kMaxHalf = 8192;       // N/2 complex points must fit twice in shared memory
+constexpr int kTopK = 100;           // AF_SAMPLES_MAXIMUM, audio_io.py:206
+constexpr int kBands = 8;            // AR_BAND_COUNT, audio_io.py:237
+constexpr int kHistBins = 4096;
+
+struct AudioParams {
+  const void* audio;
+  int dtype;  // 0 = int16, 1 = float32
+  int n_windows, n, half;
+  int n_stages, radix[kMaxStages];
+  const float2* tw_half;  // exp(-2 pi i j / half), j < half
+  const float2* tw_full;  // exp(-2 pi i k / n),    k <= half
+  float* amplitudes;      // [windows, n]
+  float* band_sums;       // [windows, 8] or null
+  int band_lo[kBands], band_hi[kBands];
+  float* top_freq;        // [windows, 100] or null
+  float* top_amp;
+  int* top_count;
+  int gate_lo, gate_hi;   // bins k (folded: min(i, n - i)) passing the frequency gate
+  float amp_min, amp_max, hz_per_bin;
+};
+
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+  return make_float2(__fmaf_rn(a.x, b.x, -a.y * b.y), __fmaf_rn(a.x, b.y, a.y * b.x));
+}
+__device__ __forceinline__ float2 mul_mi(float2 a) { return make_float2(a.y, -a.x); }  // a * (-i)
+__device__ __forceinline__ float2 cscale(float2 a, float s) { return make_float2(a.x * s, a.y * s); }
+
+template <int R>
+__device__ __forceinline__ void dft_small(float2* a) {
+  if (R == 2) {
+    const float2 t = a[1];
+    a[1] = csub(a[0], t);
+    a[0] = cadd(a[0], t);
+  } else if (R == 3) {
+    const float2 t1 = cadd(a[1], a[2]);
+    const float2 t2 = make_float2(a[0].x - 0.5f * t1.x, a[0].y - 0.5f * t1.y);
+    const float2 t3 = mul_mi(cscale(csub(a[1], a[2]), 0.86602540378443864676f));
+    a[0] = cadd(a[0], t1);
+    a[1] = cadd(t2, t3);
+    a[2] = csub(t2, t3);
+  } else if (R == 4) {
+    const float2 t0 = cadd(a[0], a[2]), t1 = csub(a[0], a[2]);
+    const float2 t2 = cadd(a[1], a[3]), t3 = mul_mi(csub(a[1], a[3]));
+    a[0] = cadd(t0, t2);
+    a[1] = cadd(t1, t3);
+    a[2] = csub(t0, t2);
+    a[3] = csub(t1, t3);
+  } else {  // 5
+    const float c1 = 0.30901699437494742410f, c2 = -0.80901699437494742410f;
+    const float s1 = 0.95105651629515357212f, s2 = 0.58778525229247312917f;
+    const float2 t1 = cadd(a[1], a[4]), t2 = cadd(a[2], a[3]);
+    const float2 t3 = csub(a[1], a[4]), t4 = csub(a[2], a[3]);
+    const float2 m1 = make_float2(a[0].x + c1 * t1.x + c2 * t2.x, a[0].y + c1 * t1.y + c2 * t2.y);
+    const float2 m2 = make_float2(a[0].x + c2 * t1.x + c1 * t2.x, a[0].y + c2 * t1.y + c1 * t2.y);
+    const float2 n1 = mul_mi(make_float2(s1 * t3.x + s2 * t4.x, s1 * t3.y + s2 * t4.y));
+    const float2 n2 = mul_mi(make_float2(s2 * t3.x - s1 * t4.x, s2 * t3.y - s1 * t4.y));
+    a[0] = cadd(a[0], cadd(t1, t2));
+    a[1] = cadd(m1, n1);
+    a[4] = csub(m1, n1);
+    a[2] = cadd(m2, n2);
+    a[3] = csub(m2, n2);
+  }
+}
+
+// One Stockham pass: length-n sub-transforms interleaved with stride s; reads x, writes y.
+template <int R>
+__device__ __forceinline__ void stockham_pass(const float2* __restrict__ x, float2* __restrict__ y, int n, int s,
+                                              const float2* __restrict__ tw, int half) {
+  const int m = n / R, total = m * s, tw_step = half / n;
+  for (int b = threadIdx.x; b < total; b += kAudioThreads) {
+    const int p = b / s, q = b - p * s;
+    float2 a[R];
+#pragma unroll
+    for (int k = 0; k < R; k++) a[k] = x[q + s * (p + m * k)];
+    dft_small<R>(a);
+    y[q + s * (R * p)] = a[0];
+#pragma unroll
+    for (int j = 1; j < R; j++) y[q + s * (R * p + j)] = cmul(a[j], __ldg(tw + p * j * tw_step));
+  }
+}
+
+__global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const AudioParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  float2* buf0 = reinterpret_cast<float2*>(smem);
+  float2* buf1 = buf0 + p.half;
+  __shared__ int s_count, s_threshold_bin, s_above;
+  __shared__ int hist[kHistBins];
+  const int half = p.half, n = p.n;
+
+  for (int w = blockIdx.x; w < p.n_windows; w += gridDim.x) {
+    // ---- pack the real window into half complex points
+    if (p.dtype == 0) {
+      const short2* in = reinterpret_cast<const short2*>(static_cast<const int16_t*>(p.audio) + (size_t)w * n);
+      for (int i = threadIdx.x; i < half; i += kAudioThreads) {
+        const short2 v = __ldg(in + i);
+        buf0[i] = make_float2((float)v.x, (float)v.y);
+      }
+    } else {
+      const float2* in = reinterpret_cast<const float2*>(static_cast<const float*>(p.audio) + (size_t)w * n);
+      for (int i = threadIdx.x; i < half; i += kAudioThreads) buf0[i] = __ldg(in + i);
+    }
+    __syncthreads();
+    // ---- half-length complex FFT
+    float2 *x = buf0, *y = buf1;
+    int len = half, stride = 1;
+    for (int st = 0; st < p.n_stages; st++) {
+      const int r = p.radix[st];
+      if (r == 4) stockham_pass<4>(x, y, len, stride, p.tw_half, half);
+      else if (r == 5) stockham_pass<5>(x, y, len, stride, p.tw_half, half);
+      else if (r == 3) stockham_pass<3>(x, y, len, stride, p.tw_half, half);
+      else stockham_pass<2>(x, y, len, stride, p.tw_half, half);
+      len /= r;
+      stride *= r;
+      float2* t = x; x = y; y = t;
+      __syncthreads();
+    }
+    // ---- unpack to the spectrum of the real window, magnitudes / 1e6 (audio_io.py:299,309)
+    float* amp = reinterpret_cast<float*>(y);          // half + 1 magnitudes, in the idle buffer
+    float* out = p.amplitudes + (size_t)w * n;
+    for (int k = threadIdx.x; k <= half; k += kAudioThreads) {
+      const float2 zk = x[k == half ? 0 : k];
+      const float2 zr = x[k == 0 ? 0 : half - k];
+      const float2 zc = make_float2(zr.x, -zr.y);
+      const float2 e = cscale(cadd(zk, zc), 0.5f);
+      const float2 o = cscale(mul_mi(csub(zk, zc)), 0.5f);
+      const float2 xk = cadd(e, cmul(__ldg(p.tw_full + k), o));
+      const float a = sqrtf(__fmaf_rn(xk.x, xk.x, xk.y * xk.y)) * 1e-6f;
+      amp[k] = a;
+      out[k] = a;
+      if (k != 0 && k != half) out[n - k] = a;         // |X[n-k]| = |X[k]| for real input
+    }
+    __syncthreads();
+    // ---- PE_AudioResampler: 8 band sums over the first half of the spectrum (audio_io.py:250-277)
+    if (p.band_sums != nullptr) {
+      const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+      if (warp < kBands) {
+        float sum = 0.f;
+        for (int k = p.band_lo[warp] + lane; k < p.band_hi[warp]; k += 32) sum += amp[k];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+        if (lane == 0) p.band_sums[(size_t)w * kBands + warp] = sum;
+      }
+    }
+    // ---- PE_AudioFilter: gate on amplitude and |frequency|, then the 100 largest by amplitude,
+    //      ties in original index order (a stable descending sort, audio_io.py:213-230)
+    if (p.top_amp != nullptr) {
+      unsigned long long* list = reinterpret_cast<unsigned long long*>(x);     // the spectrum is no longer needed
+      const int list_cap = half;                                               // half * 8 bytes = one buffer
+      for (int i = threadIdx.x; i < kHistBins; i += kAudioThreads) hist[i] = 0;
+      if (threadIdx.x == 0) { s_count = 0; s_threshold_bin = 0; s_above = 0; }
+      __syncthreads();
+      const int klo = max(p.gate_lo, 0), khi = min(p.gate_hi, half);
+      for (int k = klo + threadIdx.x; k <= khi; k += kAudioThreads) {
+        const float a = amp[k];
+        if (a >= p.amp_min && a <= p.amp_max)
+          atomicAdd(&hist[__float_as_uint(a) >> 20], (k != 0 && k != half) ? 2 : 1);
+      }
+      __syncthreads();
+      if (threadIdx.x < 32) {   // highest bin T with count(bins >= T) >= 100 (or 0 if fewer pass the gate)
+        int running = 0, found = -1, above = 0;
+        for (int base = kHistBins - 32; base >= 0 && found < 0; base -= 32) {
+          const int c = hist[base + 31 - threadIdx.x];            // lane 0 = highest bin of the chunk
+          int incl = c;
+#pragma unroll
+          for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if ((int)threadIdx.x >= d) incl += t;
+          }
+          const unsigned hit = __ballot_sync(0xffffffffu, running + incl >= kTopK);
+          if (hit) {
+            const int l = __ffs(hit) - 1;
+            found = base + 31 - l;
+            above = running + __shfl_sync(0xffffffffu, incl - c, l);
+          }
+          running += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (threadIdx.x == 0) { s_threshold_bin = max(found, 0); s_above = above; }
+      }
+      __syncthreads();
+      const unsigned tbin = (unsigned)s_threshold_bin;
+      for (int k = klo + threadIdx.x; k <= khi; k += kAudioThreads) {
+        const float a = amp[k];
+        if (a >= p.amp_min && a <= p.amp_max && (__float_as_uint(a) >> 20) >= tbin) {
+          const int copies = (k != 0 && k != half) ? 2 : 1;
+          const int at = atomicAdd(&s_count, copies);
+          const unsigned long long hi = (unsigned long long)__float_as_uint(a) << 32;
+          if (at < list_cap) list[at] = hi | (0xffffffffu - (unsigned)k);
+          if (copies == 2 && at + 1 < list_cap) list[at + 1] = hi | (0xffffffffu - (unsigned)(n - k));
+        }
+      }
+      __syncthreads();
+      const int count = min(s_count, list_cap);
+      int padded = 1;
+      while (padded < count) padded <<= 1;
+      for (int i = count + threadIdx.x; i < padded; i += kAudioThreads) list[i] = 0ull;   // sorts last
+      __syncthreads();
+      for (int size = 2; size <= padded; size <<= 1) {       // bitonic sort, descending
+        for (int strd = size >> 1; strd > 0; strd >>= 1) {
+          for (int i = threadIdx.x; i < padded; i += kAudioThreads) {
+            const int j = i ^ strd;
+            if (j > i) {
+              const bool desc = (i & size) == 0;
+              const unsigned long long a = list[i], b = list[j];
+              if ((a < b) == desc) { list[i] = b; list[j] = a; }
+            }
+          }
+          __syncthreads();
+        }
+      }
+      const int take = min(count, kTopK);
+      for (int i = threadIdx.x; i < kTopK; i += kAudioThreads) {
+        float a = 0.f, f = 0.f;
+        if (i < take) {
+          const unsigned long long e = list[i];
+          const unsigned idx = 0xffffffffu - (unsigned)(e & 0xffffffffu);
+          a = __uint_as_float((unsigned)(e >> 32));
+          f = (float)min(idx, (unsigned)n - idx) * p.hz_per_bin;
+        }
+        p.top_amp[(size_t)w * kTopK + i] = a;
+        p.top_freq[(size_t)w * kTopK + i] = f;
+      }
+      if (threadIdx.x == 0) p.top_count[w] = take;
+    }
+    __syncthreads();   // shared buffers are reused by the next window
+  }
+}
+
+__global__ void audio_twiddles_kernel(float2* tw_half, float2* tw_full, int half) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double s, c;
+  if (i < half) {
+    sincospi(-2.0 * (double)i / (double)half, &s, &c);
+    tw_half[i] = make_float2((float)c, (float)s);
+  }
+  if (i <= half) {
+    sincospi(-(double)i / (double)half, &s, &c);   // exp(-2 pi i k / n), n = 2 * half
+    tw_full[i] = make_float2((float)c, (float)s);
+  }
+}
+
+static int factorize(int m, int* radix) {
+  int count = 0;
+  const int order[4] = {4, 5, 3, 2};
+  for (int r : order)
+    while (m % r == 0 && count < kMaxStages) { radix[count++] = r; m /= r; }
+  return m == 1 ? count : -1;
+}
+
+}  // namespace aiko
+
+using namespace aiko;
+
+extern "C" size_t aiko_b200_audio_workspace_bytes(int n_samples) {
+  if (n_samples < 4 || (n_samples & 1)) return 0;
+  const size_t half = (size_t)n_samples / 2;
+  return (half + (half + 1) + 1) * sizeof(float2);
+}
+
+extern "C" int aiko_b200_audio_prepare(void* workspace, size_t workspace_bytes, int n_samples, void* stream) {
+  const size_t need = aiko_b200_audio_workspace_bytes(n_samples);
+  AIKO_CHECK_ARG(need != 0, "audio_prepare: window length %d must be even and >= 4", n_samples);
+  if (!workspace || workspace_bytes < need) {
+    set_last_error("audio_prepare: workspace of %zu bytes, need %zu", workspace_bytes, need);
+    return AIKO_B200_ERR_WORKSPACE;
+  }
+  const int half = n_samples / 2;
+  float2* tw_half = static_cast<float2*>(workspace);
+  audio_twiddles_kernel<<<(half + 1 + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(tw_half, tw_half + half,
+                                                                                               half);
+  return cuda_status(cudaGetLastError(), "audio_twiddles launch");
+}
+
+extern "C" int aiko_b200_audio_chain(const void* audio, int dtype, int n_windows, int n_samples, double sample_rate,
+                                     float* amplitudes, float* band_sums, const int* band_ranges_host,
+                                     float* top_freq, float* top_amp, int* top_count, int gate_lo, int gate_hi,
+                                     const void* workspace, size_t workspace_bytes, void* stream) {
+  AIKO_CHECK_ARG(n_windows >= 0, "audio_chain: n_windows < 0");
+  if (n_windows == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(audio && amplitudes, "audio_chain: null pointer");
+  AIKO_CHECK_ARG(dtype == 0 || dtype == 1, "audio_chain: dtype %d (0 = int16, 1 = float32)", dtype);
+  const size_t need = aiko_b200_audio_workspace_bytes(n_samples);
+  AIKO_CHECK_ARG(need != 0, "audio_chain: window length %d must be even and >= 4", n_samples);
+  if (!workspace || workspace_bytes < need) {
+    set_last_error("audio_chain: workspace of %zu bytes, need %zu (and it must have been prepared)", workspace_bytes,
+                   need);
+    return AIKO_B200_ERR_WORKSPACE;
+  }
+  AIKO_CHECK_ARG(!band_sums || band_ranges_host, "audio_chain: band_sums without band ranges");
+  AIKO_CHECK_ARG((top_freq != nullptr) == (top_amp != nullptr) && (top_amp != nullptr) == (top_count != nullptr),
+                 "audio_chain: top_freq, top_amp and top_count go together");
+  AudioParams p{};
+  p.audio = audio; p.dtype = dtype; p.n_windows = n_windows; p.n = n_samples; p.half = n_samples / 2;
+  if (p.half > kMaxHalf) {
+    set_last_error("audio_chain: window of %d samples exceeds the %d this kernel keeps in shared memory", n_samples,
+                   2 * kMaxHalf);
+    return AIKO_B200_ERR_UNSUPPORTED;
+  }
+  p.n_stages = factorize(p.half, p.radix);
+  if (p.n_stages < 0) {
+    set_last_error("audio_chain: %d / 2 has a prime factor other than 2, 3, 5", n_samples);
+    return AIKO_B200_ERR_UNSUPPORTED;
+  }
+  p.tw_half = static_cast<const float2*>(workspace);
+  p.tw_full = p.tw_half + p.half;
+  p.amplitudes = amplitudes;
+  p.band_sums = band_sums;
+  for (int b = 0; b < kBands; b++) {
+    p.band_lo[b] = band_sums ? band_ranges_host[2 * b] : 0;
+    p.band_hi[b] = band_sums ? band_ranges_host[2 * b + 1] : 0;
+    AIKO_CHECK_ARG(p.band_lo[b] >= 0 && p.band_hi[b] <= p.half && p.band_lo[b] <= p.band_hi[b],
+                   "audio_chain: band %d range outside the first half of the spectrum", b);
+  }
+  p.top_freq = top_freq; p.top_amp = top_amp; p.top_count = top_count;
+  p.gate_lo = gate_lo; p.gate_hi = gate_hi;
+  p.amp_min = 0.1f;   // AF_AMPLITUDE_MINIMUM / MAXIMUM, audio_io.py:202-203
+  p.amp_max = 12.0f;
+  p.hz_per_bin = (float)(sample_rate / (double)n_samples);
+  const size_t smem = (size_t)2 * p.half * sizeof(float2);
+  AIKO_CUDA(cudaFuncSetAttribute(audio_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, audio_chain_kernel, kAudioThreads, smem));
+  if (per_sm < 1) per_sm = 1;
+  long long grid = (long long)sm_count() * per_sm;
+  if (grid > n_windows) grid = n_windows;
+  audio_chain_kernel<<<(unsigned)grid, kAudioThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  return cuda_status(cudaGetLastError(), "audio_chain launch");
+}

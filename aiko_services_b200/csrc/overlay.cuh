@@ -44,7 +44,8 @@ struct OpSpan {
 };
 __device__ __forceinline__ OpSpan op_span(const aiko_b200_overlay_op* op, int y) {
   OpSpan s;
-  const int kind = op->kind, x0 = op->x0, y0 = op->y0, x1 = op->x1, y1 = op->y1;
+  const int4 lo4 = reinterpret_cast<const int4*>(op)[0];   // kind, x0, y0, x1
+  const int kind = lo4.x, x0 = lo4.y, y0 = lo4.z, x1 = lo4.w, y1 = op->y1;
   if (kind == AIKO_B200_OP_RECT) {
     s.row_hit = (y >= y0 - 1) && (y <= y1 + 1);
     const bool band = (y <= y0 + 1) || (y >= y1 - 1);

@@ -183,7 +183,8 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + off);
   uint64_t* empty = full + 8;
   uint64_t* ready = full + 16;
-  off += 192;
+  uint64_t* listed = full + 24;                    // the frame's draw list (and the row record) landed
+  off += 256;
   // per-row records, ring of stages + 1 (a consumer may still be drawing row i - stages - 1
   // when row i is prepared): header, then for every 128-pixel segment and every 32 draw-list
   // entries one word per consumer lane: the entries that touch that lane's 4 pixels
@@ -213,8 +214,9 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; s++) {
       mbar_init(&full[s], 1);
-      mbar_init(&empty[s], ncons);
+      mbar_init(&empty[s], ncons + (p.has_overlay ? 1 : 0));   // every reader of the row: consumers (+ cull warp)
       mbar_init(&ready[s], 1);
+      mbar_init(&listed[s], 1);
     }
     fence_mbar_init();
   }
@@ -246,21 +248,26 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
       bulk_g2s(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
       bulk_g2s(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
       const int nops = oe - ob;
-      uint32_t ops_bytes = 0;
-      if (nops > 0 && nops <= p.ops_cap) {
-        ops_bytes = (uint32_t)nops * (uint32_t)sizeof(aiko_b200_overlay_op);
-        bulk_g2s(opsring + (size_t)rslot * p.ops_cap, p.ov.ops + ob, ops_bytes, &full[slot]);
+      int* rec = mring + rslot * mrec;
+      *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
+      rec[4] = ob;
+      rec[5] = nops;
+      if (p.has_overlay) {
+        // the draw list is tiny and comes from L2: it completes its own barrier long before the
+        // rows land, so the cull warp works while the rows are still in flight
+        uint32_t ops_bytes = 0;
+        if (nops > 0 && nops <= p.ops_cap) {
+          ops_bytes = (uint32_t)nops * (uint32_t)sizeof(aiko_b200_overlay_op);
+          bulk_g2s(opsring + (size_t)rslot * p.ops_cap, p.ov.ops + ob, ops_bytes, &listed[slot]);
+        }
+        mbar_expect_tx(&listed[slot], ops_bytes);          // release: record visible to the cull warp
       }
       if (p.has_overlay && it + 1 < my_items) {    // next row's offsets: in flight while this row is consumed
         rn.next(p.items, chunk, stride_items, p.dh);
         ob_next = __ldg(p.ov.op_offsets + rn.n);
         oe_next = __ldg(p.ov.op_offsets + rn.n + 1);
       }
-      int* rec = mring + rslot * mrec;
-      *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
-      rec[4] = ob;
-      rec[5] = nops;
-      mbar_expect_tx(&full[slot], 2u * (uint32_t)p.row_bytes + ops_bytes);   // release: record visible
+      mbar_expect_tx(&full[slot], 2u * (uint32_t)p.row_bytes);   // release: record visible to the consumers
       ri.next(p.items, chunk, stride_items, p.dh);
       ob = ob_next; oe = oe_next;
       if (++slot == p.stages) { slot = 0; ++round; }
@@ -273,7 +280,7 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
     // ---- cull warp: per row, which draw-list entries touch which 128-pixel segment -----------
     int slot = 0, rslot = 0, round = 0;
     for (int it = 0; it < my_items; ++it) {
-      mbar_wait(&full[slot], (uint32_t)(round & 1), 500, 0);
+      mbar_wait(&listed[slot], (uint32_t)(round & 1), 500, 0);
       int* rec = mring + rslot * mrec;
       const int dy = rec[1], nops = rec[5];
       if (nops > 0 && nops <= p.ops_cap) {
@@ -303,7 +310,10 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
         }
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(&ready[slot]);
+      if (lane == 0) {
+        mbar_arrive(&ready[slot]);
+        mbar_arrive(&empty[slot]);     // done with this slot's `listed` phase
+      }
       if (++slot == p.stages) { slot = 0; ++round; }
       if (++rslot == rdepth) rslot = 0;
     }
@@ -313,10 +323,9 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
   // ---- consumers: each warp produces, overlays and stores its own 128-pixel segments --------
   const int row_bytes_out = p.dw * 3;
   const uint32_t sel_rgb = p.swap_rb ? 0x7014u : 0x7410u;   // (c0 c1 . .),(c2) -> c0 c1 c2 0 | c2 c1 c0 0
-  uint64_t* go = p.has_overlay ? ready : full;
   int slot = 0, rslot = 0, round = 0;
   for (int it = 0; it < my_items; ++it) {
-    mbar_wait(&go[slot], (uint32_t)(round & 1), 500, 0);
+    mbar_wait(&full[slot], (uint32_t)(round & 1), 500, 0);
     const int* rec = mring + rslot * mrec;
     const int4 hdr = *reinterpret_cast<const int4*>(rec);   // n, dy, b0, b1
     const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
@@ -328,8 +337,8 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
       consume_row<false>(r0, r1, xw, xs, xcoef, orow, warp * 32 + lane, ncons * 32, groups, (uint32_t)hdr.z,
                          (uint32_t)hdr.w, sel_rgb);
     __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[slot]);      // this warp no longer reads the stage
     if (p.has_overlay) {
+      mbar_wait(&ready[slot], (uint32_t)(round & 1), 200, 0);   // hit masks (normally long since written)
       const int ob = rec[4], nops = rec[5];
       if (nops > p.ops_cap) {                      // list too long for the staged path: cull here
         overlay_apply_row(p.ov.ops + ob, nops, p.ov, hdr.y, p.dw, orow, ncons * 32);
@@ -364,6 +373,9 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
       }
     }
     __syncwarp();                                  // the segment is rewritten by the next row
+    // Release the slot only now: no barrier of this slot may advance a second phase while any
+    // warp could still be waiting on the first (a parity wait cannot tell phases 2 apart).
+    if (lane == 0) mbar_arrive(&empty[slot]);
     if (++slot == p.stages) { slot = 0; ++round; }
     if (++rslot == rdepth) rslot = 0;
   }
@@ -435,7 +447,7 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   if (ncons < 1) ncons = 1;
   if (ncons > 8) ncons = 8;
   const int threads = (ncons + (p.has_overlay ? 2 : 1)) * 32;   // + TMA producer warp (+ cull warp)
-  const size_t fixed = (size_t)groups * 48 + (((size_t)groups * 12 + 15) & ~(size_t)15) + 192;
+  const size_t fixed = (size_t)groups * 48 + (((size_t)groups * 12 + 15) & ~(size_t)15) + 256;
   p.row_bytes = p.sw * 3;
   p.seg_stride = p.row_bytes + 16;                 // tap reads may run a few bytes past the row end
   int stages = env_int("AIKO_B200_RESIZE_STAGES", 3);

@@ -135,6 +135,21 @@ def resize_bicubic_aa(src, width, height, *, out=None, stream=None):
     return out
 
 
+def resize_norm_f32(src, width, height, mean, std, *, out=None, stream=None):
+    """cv2-exact bilinear resize of RGB frames, then ((x / 255) - mean) / std as float32 [N, 3, H, W]."""
+    _require_cuda(src, "resize_norm_f32 src")
+    n, h, w, c, _ = _nhwc(src)
+    if c != 3:
+        raise ValueError("resize_norm_f32: RGB frames expected")
+    out = _out(out, (n, 3, height, width), src.device, "resize_norm_f32 out", torch.float32)
+    m = (ctypes.c_float * 3)(*[float(v) for v in mean])
+    s = (ctypes.c_float * 3)(*[float(v) for v in std])
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_resize_norm_f32_nchw(src.data_ptr(), n, h, w, out.data_ptr(), height, width,
+                                                           m, s, _stream_ptr(stream)))
+    return out
+
+
 def overlay_draw(src, overlay, *, out=None, stream=None):
     """ImageOverlay's drawing on frames already resident on the GPU."""
     _require_cuda(src, "overlay src")

@@ -129,6 +129,14 @@ int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_frames, int h, 
                          int64_t row_stride, int64_t frame_stride, const aiko_b200_overlay* overlay_host,
                          void* stream);
 
+/* BASELINE config 4 (extension, no reference element: the closest consumer is  */
+/* R/examples/yolo/yolo.py:62-64 handing resized frames to a torch model):        */
+/* cv2-exact bilinear resize of RGB frames [n, src_h, src_w, 3], then             */
+/* out[n][c][y][x] = ((float)u8 / 255 - mean[c]) / std[c] as fp32 NCHW.           */
+/* mean_host / std_host: 3 floats each in HOST memory.                            */
+int aiko_b200_resize_norm_f32_nchw(const uint8_t* src, int n_frames, int src_h, int src_w, float* dst, int dst_h,
+                                   int dst_w, const float* mean_host, const float* std_host, void* stream);
+
 /* ---------------------------------------------------------------------- */
 /* Colour conversion / flip / crop call sites.                              */
 
@@ -147,6 +155,27 @@ int aiko_b200_flip_u8(const uint8_t* src, uint8_t* dst, int n_frames, int h, int
 /* image[y0:y0+ch, x0:x0+cw] (numpy slicing as used on frames; north_star).  */
 int aiko_b200_crop_u8(const uint8_t* src, int n_frames, int h, int w, int channels, uint8_t* dst, int x0,
                       int y0, int crop_w, int crop_h, void* stream);
+
+/* ---------------------------------------------------------------------- */
+/* Audio chain, batched over windows (the reference code is dead -- inside a    */
+/* string literal, R/elements/media/audio_io.py:162-642 -- so parity is against */
+/* a numpy restatement, oracle/audio.py):                                        */
+/*   PE_FFT            :306-320  amplitudes = |fft(window)| / 1e6, all n bins    */
+/*   PE_AudioResampler :250-277  sums of 8 bands of the first half of the bins   */
+/*   PE_AudioFilter    :213-230  0.1 <= amplitude <= 12, 10 <= |f| <= 9000 Hz,   */
+/*                               100 largest by amplitude (stable order)         */
+/* audio: [n_windows, n_samples] int16 (dtype 0) or float32 (dtype 1);           */
+/* n_samples even, n_samples / 2 = 2^a 3^b 5^c <= 8192.  The workspace holds the */
+/* twiddle tables (generated in double precision by _prepare).  band_ranges_host */
+/* (16 ints: lo, hi per band) and gate_lo / gate_hi (folded bin range passing    */
+/* the frequency gate) are evaluated by the caller in float64 as numpy would.    */
+/* band_sums and the three top_* outputs may be NULL to skip those stages.       */
+size_t aiko_b200_audio_workspace_bytes(int n_samples);
+int aiko_b200_audio_prepare(void* workspace, size_t workspace_bytes, int n_samples, void* stream);
+int aiko_b200_audio_chain(const void* audio, int dtype, int n_windows, int n_samples, double sample_rate,
+                          float* amplitudes, float* band_sums, const int* band_ranges_host, float* top_freq,
+                          float* top_amp, int* top_count, int gate_lo, int gate_hi, const void* workspace,
+                          size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

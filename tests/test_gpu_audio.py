@@ -1,0 +1,91 @@
+"""GPU: the audio chain (PE_FFT -> PE_AudioResampler -> PE_AudioFilter) against the numpy float64
+restatement of the reference's (dead) code, oracle/audio.py.  Tolerances (SURVEY.md 8c, fp32 FFT):
+magnitudes abs(gpu - ref) <= 1e-4 * max|ref| per window, and per bin rtol 1e-4 with
+atol 1e-4 * median|ref|; band sums rtol 1e-4; selected bins compared as values."""
+import numpy as np
+import pytest
+import torch
+
+from aiko_services_b200 import audio_ops
+from oracle import audio as A
+
+pytestmark = pytest.mark.gpu
+
+
+def windows_cfg5(count, n=16000, fs=16000):
+    t = np.arange(n) / fs
+    freqs = np.geomspace(50, 7000, count)
+    out = np.empty((count, n), np.int16)
+    for k in range(count):
+        rng = np.random.default_rng(5000 + k)
+        out[k] = np.clip(3000 * np.sin(2 * np.pi * freqs[k] * t) + rng.normal(0, 200, n), -32768, 32767).astype(np.int16)
+    return out
+
+
+def check_window(res, k, window, fs):
+    amp, freq = A.pe_fft(window, fs)
+    got = res["amplitudes"][k].cpu().numpy().astype(np.float64)
+    assert np.abs(got - amp).max() <= 1e-4 * np.abs(amp).max()
+    np.testing.assert_allclose(got, amp, rtol=1e-4, atol=1e-4 * np.median(np.abs(amp)))
+    np.testing.assert_array_equal(res["frequencies"], freq)
+    bf, ba = A.pe_audio_resampler(amp, freq)
+    np.testing.assert_allclose(res["band_frequencies"], bf, rtol=1e-12)
+    np.testing.assert_allclose(res["band_amplitudes"][k].cpu().numpy(), ba, rtol=1e-4, atol=1e-4 * np.abs(ba).max())
+    tf, ta = A.pe_audio_filter(amp, freq)
+    count = int(res["top_count"][k])
+    gf = res["top_frequencies"][k].cpu().numpy()[:count]
+    ga = res["top_amplitudes"][k].cpu().numpy()[:count]
+    # bins within 1e-4 of a gate edge or of the 100th value may legitimately differ in fp32
+    lo_edge = np.sum((np.abs(amp - 0.1) < 2e-5) | (np.abs(amp - 12) < 2e-3))
+    if lo_edge == 0 and (len(ta) < 100 or ta[99] - np.sort(amp[(amp <= 12) & (amp >= 0.1)])[::-1][100:101].sum() > 1e-4):
+        assert count == len(ta)
+        np.testing.assert_allclose(np.sort(ga)[::-1], ta, rtol=1e-4)
+        np.testing.assert_allclose(np.sort(gf), np.sort(tf), rtol=1e-6, atol=1e-3)
+    assert (np.diff(ga) <= 0).all()                      # sorted by amplitude, descending
+    assert ((ga >= 0.1 - 1e-5) & (ga <= 12 + 1e-3)).all() and ((gf >= 10) & (gf <= 9000)).all()
+
+
+def test_audio_chain_cfg5_windows(cuda):
+    fs = 16000
+    w = windows_cfg5(24)
+    res = audio_ops.audio_chain(torch.from_numpy(w).to(cuda), fs)
+    for k in range(24):
+        check_window(res, k, w[k], fs)
+
+
+def test_audio_chain_float_input_and_other_lengths(cuda):
+    rng = np.random.default_rng(7)
+    for n, fs in ((16000, 16000), (9600, 48000), (8192, 8000), (4000, 16000), (1000, 8000)):
+        x = (rng.standard_normal((3, n)) * 4000).astype(np.float32)
+        x[1] += 30000 * np.sin(2 * np.pi * 440 * np.arange(n) / fs).astype(np.float32)
+        res = audio_ops.audio_chain(torch.from_numpy(x).to(cuda), fs)
+        for k in range(3):
+            amp, _ = A.pe_fft(x[k], fs)
+            got = res["amplitudes"][k].cpu().numpy().astype(np.float64)
+            assert np.abs(got - amp).max() <= 1e-4 * np.abs(amp).max(), (n, k)
+
+
+def test_audio_chain_properties_full_batch(cuda):
+    """1024 windows (BASELINE config 5): linearity of the spectrum, Parseval, symmetry."""
+    fs, n = 16000, 16000
+    w = windows_cfg5(64)
+    batch = np.tile(w, (16, 1))                                       # 1024 windows
+    res = audio_ops.audio_chain(torch.from_numpy(batch).to(cuda), fs)
+    amp = res["amplitudes"]
+    assert torch.equal(amp[:64], amp[64:128])                         # same window, same result, anywhere in the batch
+    a = amp[:64].double().cpu().numpy()
+    np.testing.assert_allclose(a[:, 1:n // 2], a[:, :n // 2:-1], rtol=0, atol=0)      # |X[k]| == |X[n-k]| exactly
+    energy_time = (w.astype(np.float64) ** 2).sum(1)
+    energy_freq = ((a * 1e6) ** 2).sum(1) / n
+    np.testing.assert_allclose(energy_freq, energy_time, rtol=1e-4)
+
+
+def test_audio_chain_empty_and_errors(cuda):
+    empty = torch.empty((0, 16000), dtype=torch.int16, device=cuda)
+    assert audio_ops.audio_chain(empty, 16000)["amplitudes"].shape == (0, 16000)
+    with pytest.raises(Exception):
+        audio_ops.audio_chain(torch.zeros((1, 16001), dtype=torch.int16, device=cuda), 16000)      # odd length
+    with pytest.raises(Exception):
+        audio_ops.audio_chain(torch.zeros((1, 2 * 7 * 100), dtype=torch.int16, device=cuda), 16000)  # factor 7
+    with pytest.raises(Exception):
+        audio_ops.audio_chain(torch.zeros((1, 32000), dtype=torch.int16, device=cuda), 16000)      # too long

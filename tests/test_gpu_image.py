@@ -134,6 +134,32 @@ def test_resize_bicubic_workspace_errors(cuda):
     assert rc == _native.ERR_WORKSPACE
 
 
+# ---------------------------------------------------------------- config 4: resize + normalise -> fp32 NCHW
+IMAGENET_MEAN, IMAGENET_STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+
+
+def test_resize_norm_f32_vs_oracle(cuda):
+    rng = np.random.default_rng(121)
+    for i in range(8):
+        h, w, H, W = (int(v) for v in rng.integers(8, 300, 4))
+        frames = np.stack([cases.frame(6000 + 10 * i + k, h, w, 3) for k in range(2)])
+        out = host(ops.resize_norm_f32(dev(frames, cuda), W, H, IMAGENET_MEAN, IMAGENET_STD))
+        for k in range(2):
+            np.testing.assert_array_equal(out[k], O.resize_norm_f32(frames[k], W, H, IMAGENET_MEAN, IMAGENET_STD))
+
+
+def test_resize_norm_f32_cfg4_size(cuda):
+    """4K -> 224x224: bit-identical to cv2-exact resize followed by the numpy float32 transform."""
+    frames = np.stack([cases.frame(4000 + k, 2160, 3840, 3) for k in range(2)])
+    out = host(ops.resize_norm_f32(dev(frames, cuda), 224, 224, IMAGENET_MEAN, IMAGENET_STD))
+    assert out.shape == (2, 3, 224, 224) and out.dtype == np.float32
+    for k in range(2):
+        u8 = O.resize_linear(frames[k], 224, 224)
+        ref = ((u8.astype(np.float32) / np.float32(255) - np.asarray(IMAGENET_MEAN, np.float32)) /
+               np.asarray(IMAGENET_STD, np.float32)).transpose(2, 0, 1)
+        np.testing.assert_array_equal(out[k], ref)      # tolerance 0: every step is a correctly rounded fp32 op
+
+
 # ---------------------------------------------------------------- convert / flip / crop (a-4)
 @pytest.mark.parametrize("n_pixels", [0, 1, 15, 16, 17, 4097, 640 * 480, 1920 * 1080 + 5])
 def test_convert_ops_vs_oracle(cuda, n_pixels):
