@@ -264,10 +264,10 @@ def run_gpu_arm(args):
     h2d = BATCH * SRC_H * SRC_W * 3
     d2h = BATCH * DST_H * DST_W * 3
 
-    if world > 1:
-        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_s = float(t[0]), float(t[1])
+    # max over ranks of the device / wall timings, sum over ranks of the frames processed
+    from aiko_services_b200 import sharding
+    (ms, e2e_s), (frames_timed, frames_e2e) = sharding.combine([ms, e2e_s], [BATCH * args.steps, BATCH * e2e_steps],
+                                                               device=device)
 
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -277,7 +277,7 @@ def run_gpu_arm(args):
             peak, peak_src = FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
         achieved = ALGO_BYTES_PER_FRAME * BATCH / (kernel_ms * 1e-3) / 1e9
         line = {
-            "metric": "1080p frames/sec through resize+convert+overlay", "value": world * BATCH * args.steps / (ms * 1e-3),
+            "metric": "1080p frames/sec through resize+convert+overlay", "value": frames_timed / (ms * 1e-3),
             "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
@@ -287,7 +287,7 @@ def run_gpu_arm(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "kernel": "resize3_staged",
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_FRAME * BATCH, "kernel_ms": kernel_ms},
-            "e2e": {"value": world * BATCH * e2e_steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
+            "e2e": {"value": frames_e2e / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                     "note": "Pipeline.process_frame over ImageResize -> ImageOverlay -> ImageConvert(RGB2BGR) -> "
                             "ImageOutput; pinned host frames -> cudaMemcpyAsync -> fused kernel -> D2H, 2 aiko streams "

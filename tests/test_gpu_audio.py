@@ -89,3 +89,28 @@ def test_audio_chain_empty_and_errors(cuda):
         audio_ops.audio_chain(torch.zeros((1, 2 * 7 * 100), dtype=torch.int16, device=cuda), 16000)  # factor 7
     with pytest.raises(Exception):
         audio_ops.audio_chain(torch.zeros((1, 32000), dtype=torch.int16, device=cuda), 16000)      # too long
+
+
+def test_audio_elements_in_pipeline(cuda, tmp_path):
+    """The reference's graph (PE_FFT PE_AudioResampler PE_AudioFilter), 6 concurrent streams batched."""
+    from aiko_services_b200.pipeline import Pipeline
+    mod = "aiko_services.elements.media.audio_io"
+    io3 = [{"name": "amplitudes", "type": "any"}, {"name": "frequencies", "type": "any"}, {"name": "spectrum", "type": "any"}]
+    d = {"version": 0, "name": "p_audio", "runtime": "python", "graph": ["(PE_FFT PE_AudioFilter)"],
+         "parameters": {"sample_rate": 16000},
+         "elements": [{"name": "PE_FFT", "input": [{"name": "audio", "type": "any"}], "output": io3,
+                       "deploy": {"local": {"module": mod}}},
+                      {"name": "PE_AudioFilter", "input": io3, "output": io3[:2], "deploy": {"local": {"module": mod}}}]}
+    p = Pipeline(d)
+    w = windows_cfg5(6)
+    work = []
+    for k in range(6):
+        assert p.create_stream(f"a{k}")
+        work.append(({"stream_id": f"a{k}", "frame_id": 0}, {"audio": w[k]}))
+    results = p.process_frames(work)
+    for k, (okay, swag) in enumerate(results):
+        assert okay
+        amp, freq = A.pe_fft(w[k], 16000)
+        tf, ta = A.pe_audio_filter(amp, freq)
+        assert len(swag["amplitudes"]) == len(ta)
+        np.testing.assert_allclose(np.sort(swag["amplitudes"])[::-1], ta, rtol=1e-4)
