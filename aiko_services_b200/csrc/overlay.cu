@@ -66,7 +66,9 @@ extern "C" int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_fram
   p.src = src; p.dst = dst; p.n = n_frames; p.h = h; p.w = w; p.channels = channels;
   p.row_stride = row_stride; p.frame_stride = frame_stride;
   p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
-                    overlay->patch_h, overlay->max_ops_per_frame};
+                    overlay->patch_h, overlay->max_ops_per_frame, overlay->index,
+                      overlay->index_width, overlay->index_segments, overlay->index_words,
+                      overlay->index_frame_words};
   const size_t smem = ((size_t)w * 3 + 15) & ~(size_t)15;
   AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "overlay: row of %zu bytes exceeds shared memory", smem);
   AIKO_CUDA(cudaFuncSetAttribute(overlay_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -14,6 +14,8 @@ struct OverlayDev {
   const uint8_t* luts;
   int patch_w, patch_h;
   int max_ops;   // host hint: largest per-frame op count (0 = unknown)
+  const uint32_t* index;   // optional spatial index (include/aiko_b200.h), or null
+  int index_width, index_segments, index_words, index_frame_words;
 };
 
 // cv2.rectangle(.., thickness=2) coverage, closed form.

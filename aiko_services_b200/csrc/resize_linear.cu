@@ -29,7 +29,8 @@ struct ResizeParams {
   OverlayDev ov;
   int stages, seg_stride, row_bytes;
   int items, items_per_cta;
-  int ops_cap;   // draw-list entries per ring slot staged in shared memory (0: read ops from global)
+  int index_words_per_frame;   // uint32 words of the overlay's spatial index staged per ring slot (0: none)
+  int ops_cap;                 // draw-list entries staged per ring slot next to the index (0: read from global)
 };
 
 // cv2's coefficient derivation (float32 phase from a double position, 11-bit weights).
@@ -80,7 +81,6 @@ __device__ __forceinline__ uint32_t vblend_hi(uint32_t r0, uint32_t r1, uint32_t
 // Row scheduling shared by the producer warp and the consumer warps of resize3_staged: CTA c
 // takes chunks c, c + G, c + 2G, ... of `chunk` consecutive output rows, so rows being read at
 // the same time are neighbours in memory and label rows (slow) are spread over many CTAs.
-constexpr int kMaskWords = 4;   // producer-side culling handles frames with up to 128 draw-list entries
 constexpr int kRecHeader = 8;   // ints: n, dy, b0 << 16, b1 << 16, first op, op count, -, -
 
 // Row scheduling of resize3_staged: CTA c takes chunks c, c + G, c + 2G, ... of `chunk`
@@ -166,11 +166,11 @@ __device__ __forceinline__ void consume_row(const uint8_t* r0, const uint8_t* r1
   }
 }
 
-// Warp roles: warps [0, ncons) consume rows; warp ncons is the TMA producer; with an overlay,
-// warp ncons + 1 culls the frame's draw list (staged next to the row) into per-segment hit
-// masks.  Barriers per ring slot: full (TMA bytes landed), ready (masks written), empty
-// (consumers are done reading the slot).
-__global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
+// Warp roles: warps [0, ncons) consume rows; warp ncons is the TMA producer.  Per ring slot the
+// producer brings in the two source rows and, with an overlay, the frame's spatial index of its
+// draw list; `full` completes when the bytes have landed, `empty` when every consumer warp is
+// done with the slot.
+__global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int groups = (p.dw + 3) >> 2;  // 4 output pixels per group
   const int dwp = groups * 4;
@@ -182,24 +182,16 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
   off += ((size_t)groups * 12 + 15) & ~(size_t)15;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + off);
   uint64_t* empty = full + 8;
-  uint64_t* ready = full + 16;
-  uint64_t* listed = full + 24;                    // the frame's draw list (and the row record) landed
-  off += 256;
-  // per-row records, ring of stages + 1 (a consumer may still be drawing row i - stages - 1
-  // when row i is prepared): header, then for every 128-pixel segment and every 32 draw-list
-  // entries one word per consumer lane: the entries that touch that lane's 4 pixels
-  const int nseg = (groups + 31) >> 5;
-  const int rdepth = p.stages + 1;
-  const int mwords = (p.ops_cap + 31) >> 5;
-  const int mrec = kRecHeader + nseg * mwords * 32;
-  int* mring = reinterpret_cast<int*>(smem + off);
-  off += ((size_t)rdepth * mrec * 4 + 15) & ~(size_t)15;
-  // the frame's draw list, copied next to each row by the TMA engine (same ring as the records)
-  aiko_b200_overlay_op* opsring = reinterpret_cast<aiko_b200_overlay_op*>(smem + off);
-  off += (size_t)rdepth * p.ops_cap * sizeof(aiko_b200_overlay_op);
+  off += 128;
+  int* recs = reinterpret_cast<int*>(smem + off);  // per slot: n, dy, b0, b1, first op, op count, -, -
+  off += (size_t)p.stages * kRecHeader * 4;
+  uint32_t* idxring = reinterpret_cast<uint32_t*>(smem + off);          // per slot: the frame's index block
+  off += (size_t)p.stages * p.index_words_per_frame * 4;
+  aiko_b200_overlay_op* opsring = reinterpret_cast<aiko_b200_overlay_op*>(smem + off);   // ... and its draw list
+  off += (size_t)p.stages * p.ops_cap * sizeof(aiko_b200_overlay_op);
   uint8_t* stage = smem + off;
 
-  const int ncons = (int)blockDim.x / 32 - (p.has_overlay ? 2 : 1);
+  const int ncons = (int)blockDim.x / 32 - 1;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   bool not_decim = false;
   for (int dx = threadIdx.x; dx < dwp; dx += blockDim.x) {
@@ -214,9 +206,7 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; s++) {
       mbar_init(&full[s], 1);
-      mbar_init(&empty[s], ncons + (p.has_overlay ? 1 : 0));   // every reader of the row: consumers (+ cull warp)
-      mbar_init(&ready[s], 1);
-      mbar_init(&listed[s], 1);
+      mbar_init(&empty[s], ncons);
     }
     fence_mbar_init();
   }
@@ -232,14 +222,14 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
     my_items -= total_chunks * chunk - p.items;
 
   if (warp == ncons) {
-    // ---- producer: one lane feeds the TMA ring (rows + the frame's draw list) ----------------
+    // ---- producer: one lane feeds the TMA ring ---------------------------------------------
     if (lane != 0 || my_items == 0) return;
-    RowIter ri, rn;                                // current row, next row (for prefetching its list offsets)
+    RowIter ri, rn;                                // current row, next row (to prefetch its list offsets)
     ri.start(blockIdx.x * chunk, p.items, chunk, p.dh);
     rn = ri;
     int ob = 0, oe = 0, ob_next = 0, oe_next = 0;
     if (p.has_overlay) { ob = __ldg(p.ov.op_offsets + ri.n); oe = __ldg(p.ov.op_offsets + ri.n + 1); }
-    int slot = 0, rslot = 0, round = 0;
+    int slot = 0, round = 0;
     for (int it = 0; it < my_items; ++it) {
       if (round > 0) mbar_wait(&empty[slot], (uint32_t)((round - 1) & 1), 1000, 100);
       const RowCoef rc = vertical_coef(ri.dy, p.scale_y, p.sh);
@@ -248,74 +238,30 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
       bulk_g2s(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
       bulk_g2s(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
       const int nops = oe - ob;
-      int* rec = mring + rslot * mrec;
-      *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
-      rec[4] = ob;
-      rec[5] = nops;
-      if (p.has_overlay) {
-        // the draw list is tiny and comes from L2: it completes its own barrier long before the
-        // rows land, so the cull warp works while the rows are still in flight
-        uint32_t ops_bytes = 0;
-        if (nops > 0 && nops <= p.ops_cap) {
-          ops_bytes = (uint32_t)nops * (uint32_t)sizeof(aiko_b200_overlay_op);
-          bulk_g2s(opsring + (size_t)rslot * p.ops_cap, p.ov.ops + ob, ops_bytes, &listed[slot]);
+      uint32_t idx_bytes = 0;
+      if (p.index_words_per_frame > 0 && nops > 0) {
+        idx_bytes = (uint32_t)p.index_words_per_frame * 4u;
+        bulk_g2s(idxring + (size_t)slot * p.index_words_per_frame,
+                 p.ov.index + (size_t)ri.n * p.ov.index_frame_words, idx_bytes, &full[slot]);
+        if (nops <= p.ops_cap) {
+          const uint32_t ops_bytes = (uint32_t)nops * (uint32_t)sizeof(aiko_b200_overlay_op);
+          bulk_g2s(opsring + (size_t)slot * p.ops_cap, p.ov.ops + ob, ops_bytes, &full[slot]);
+          idx_bytes += ops_bytes;
         }
-        mbar_expect_tx(&listed[slot], ops_bytes);          // release: record visible to the cull warp
       }
       if (p.has_overlay && it + 1 < my_items) {    // next row's offsets: in flight while this row is consumed
         rn.next(p.items, chunk, stride_items, p.dh);
         ob_next = __ldg(p.ov.op_offsets + rn.n);
         oe_next = __ldg(p.ov.op_offsets + rn.n + 1);
       }
-      mbar_expect_tx(&full[slot], 2u * (uint32_t)p.row_bytes);   // release: record visible to the consumers
+      int* rec = recs + slot * kRecHeader;
+      *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
+      rec[4] = ob;
+      rec[5] = nops;
+      mbar_expect_tx(&full[slot], 2u * (uint32_t)p.row_bytes + idx_bytes);   // release: record visible
       ri.next(p.items, chunk, stride_items, p.dh);
       ob = ob_next; oe = oe_next;
       if (++slot == p.stages) { slot = 0; ++round; }
-      if (++rslot == rdepth) rslot = 0;
-    }
-    return;
-  }
-
-  if (warp == ncons + 1) {
-    // ---- cull warp: per row, which draw-list entries touch which 128-pixel segment -----------
-    int slot = 0, rslot = 0, round = 0;
-    for (int it = 0; it < my_items; ++it) {
-      mbar_wait(&listed[slot], (uint32_t)(round & 1), 500, 0);
-      int* rec = mring + rslot * mrec;
-      const int dy = rec[1], nops = rec[5];
-      if (nops > 0 && nops <= p.ops_cap) {
-        const aiko_b200_overlay_op* fops = opsring + (size_t)rslot * p.ops_cap;
-        for (int wi = 0; wi * 32 < nops; wi++) {
-          const int i = wi * 32 + lane;
-          OpSpan sp;
-          sp.row_hit = false;
-          sp.a0 = sp.b0 = 1; sp.a1 = sp.b1 = 0;
-          if (i < nops) sp = op_span(fops + i, dy);
-          for (int seg = 0; seg < nseg; seg++) {
-            const int lo = seg * 128, hi = min(lo + 127, p.dw - 1);
-            uint32_t m = __ballot_sync(0xffffffffu, sp.row_hit && span_meets(sp, lo, hi));
-            // this lane now plays consumer lane `lane` of the segment: which hits touch its pixels?
-            const int mlo = lo + 4 * lane, mhi = min(mlo + 3, p.dw - 1);
-            uint32_t mine = 0;
-            while (m) {
-              const int b = __ffs(m) - 1;
-              m &= m - 1;
-              OpSpan o;
-              o.a0 = __shfl_sync(0xffffffffu, sp.a0, b); o.a1 = __shfl_sync(0xffffffffu, sp.a1, b);
-              o.b0 = __shfl_sync(0xffffffffu, sp.b0, b); o.b1 = __shfl_sync(0xffffffffu, sp.b1, b);
-              if (span_meets(o, mlo, mhi)) mine |= 1u << b;
-            }
-            rec[kRecHeader + (seg * mwords + wi) * 32 + lane] = (int)mine;
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(&ready[slot]);
-        mbar_arrive(&empty[slot]);     // done with this slot's `listed` phase
-      }
-      if (++slot == p.stages) { slot = 0; ++round; }
-      if (++rslot == rdepth) rslot = 0;
     }
     return;
   }
@@ -323,10 +269,11 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
   // ---- consumers: each warp produces, overlays and stores its own 128-pixel segments --------
   const int row_bytes_out = p.dw * 3;
   const uint32_t sel_rgb = p.swap_rb ? 0x7014u : 0x7410u;   // (c0 c1 . .),(c2) -> c0 c1 c2 0 | c2 c1 c0 0
-  int slot = 0, rslot = 0, round = 0;
+  const int nseg = p.ov.index_segments, nw = p.ov.index_words;
+  int slot = 0, round = 0;
   for (int it = 0; it < my_items; ++it) {
     mbar_wait(&full[slot], (uint32_t)(round & 1), 500, 0);
-    const int* rec = mring + rslot * mrec;
+    const int* rec = recs + slot * kRecHeader;
     const int4 hdr = *reinterpret_cast<const int4*>(rec);   // n, dy, b0, b1
     const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
     const uint8_t* r1 = r0 + p.seg_stride;
@@ -338,21 +285,33 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
                          (uint32_t)hdr.w, sel_rgb);
     __syncwarp();
     if (p.has_overlay) {
-      mbar_wait(&ready[slot], (uint32_t)(round & 1), 200, 0);   // hit masks (normally long since written)
       const int ob = rec[4], nops = rec[5];
-      if (nops > p.ops_cap) {                      // list too long for the staged path: cull here
+      if (nops > 0 && p.index_words_per_frame == 0) {        // no index from the host: cull here
         overlay_apply_row(p.ov.ops + ob, nops, p.ov, hdr.y, p.dw, orow, ncons * 32);
       } else if (nops > 0) {
-        const aiko_b200_overlay_op* fops = opsring + (size_t)rslot * p.ops_cap;
-        for (int gbase = warp * 32; gbase < groups; gbase += ncons * 32) {
-          const int mlo = (gbase + lane) * 4, mhi = min(mlo + 3, p.dw - 1);
-          for (int wi = 0; wi * 32 < nops; wi++) {
-            uint32_t rem = (uint32_t)rec[kRecHeader + ((gbase >> 5) * mwords + wi) * 32 + lane];
+        const uint32_t* idx = idxring + (size_t)slot * p.index_words_per_frame;
+        const uint32_t* yinfo = idx + 2 * nseg * nw * 32;
+        const aiko_b200_overlay_op* fops = (nops <= p.ops_cap) ? opsring + (size_t)slot * p.ops_cap : p.ov.ops + ob;
+        const int y = hdr.y;
+        for (int wi = 0; wi < nw; wi++) {
+          // which of these 32 ops touch this row, and which rectangles are in their band rows
+          const uint2 yi = reinterpret_cast<const uint2*>(yinfo)[wi * 32 + lane];
+          const int first = (int)(short)(yi.x & 0xffff), last = (int)(short)(yi.x >> 16);
+          const int band0 = (int)(short)(yi.y & 0xffff), band1 = (int)(short)(yi.y >> 16);
+          const uint32_t rowmask = __ballot_sync(0xffffffffu, y >= first && y <= last);
+          if (rowmask == 0) continue;
+          const uint32_t bandmask = __ballot_sync(0xffffffffu, y <= band0 || y >= band1);
+          for (int gbase = warp * 32; gbase < groups; gbase += ncons * 32) {
+            const int seg = gbase >> 5;
+            const int mlo = (gbase + lane) * 4, mhi = min(mlo + 3, p.dw - 1);
+            const uint32_t side = idx[(seg * nw + wi) * 32 + lane];
+            const uint32_t band = idx[((nseg + seg) * nw + wi) * 32 + lane];
+            uint32_t rem = rowmask & ((side & ~bandmask) | (band & bandmask));
             while (__any_sync(0xffffffffu, rem != 0)) {   // lanes apply their own (different) entries together
               if (rem) {
                 const int b = __ffs(rem) - 1;
                 rem &= rem - 1;
-                apply_op_to_pixels(fops + wi * 32 + b, p.ov, hdr.y, mlo, mhi, orow);
+                apply_op_to_pixels(fops + wi * 32 + b, p.ov, y, mlo, mhi, orow);
               }
             }
           }
@@ -373,11 +332,8 @@ __global__ void __launch_bounds__(320) resize3_staged(const ResizeParams p) {
       }
     }
     __syncwarp();                                  // the segment is rewritten by the next row
-    // Release the slot only now: no barrier of this slot may advance a second phase while any
-    // warp could still be waiting on the first (a parity wait cannot tell phases 2 apart).
-    if (lane == 0) mbar_arrive(&empty[slot]);
+    if (lane == 0) mbar_arrive(&empty[slot]);      // rows, record and index of this slot are free again
     if (++slot == p.stages) { slot = 0; ++round; }
-    if (++rslot == rdepth) rslot = 0;
   }
 }
 
@@ -446,19 +402,26 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   ncons = env_int("AIKO_B200_RESIZE_WARPS", ncons);
   if (ncons < 1) ncons = 1;
   if (ncons > 8) ncons = 8;
-  const int threads = (ncons + (p.has_overlay ? 2 : 1)) * 32;   // + TMA producer warp (+ cull warp)
-  const size_t fixed = (size_t)groups * 48 + (((size_t)groups * 12 + 15) & ~(size_t)15) + 256;
+  const int threads = (ncons + 1) * 32;            // + the TMA producer warp
   p.row_bytes = p.sw * 3;
   p.seg_stride = p.row_bytes + 16;                 // tap reads may run a few bytes past the row end
-  int stages = env_int("AIKO_B200_RESIZE_STAGES", 3);
+  // the host-built index is usable when it was made for this output width
+  const bool indexed = p.has_overlay && p.ov.index != nullptr && p.ov.index_width == p.dw &&
+                       p.ov.index_segments == (groups + 31) / 32 && p.ov.index_words > 0 &&
+                       p.ov.index_frame_words == 2 * p.ov.index_segments * p.ov.index_words * 32 + p.ov.index_words * 64;
+  p.index_words_per_frame = indexed ? p.ov.index_frame_words : 0;
+  // Staging the op records next to the index was measured slower (more shared memory per CTA, fewer
+  // CTAs per SM) than letting hit lanes fetch their record through L2: off unless asked for.
+  p.ops_cap = (env_int("AIKO_B200_RESIZE_STAGE_OPS", 0) && indexed && p.ov.max_ops > 0 &&
+               p.ov.max_ops <= 32 * p.ov.index_words) ? p.ov.max_ops : 0;
+  const size_t fixed = (size_t)groups * 48 + (((size_t)groups * 12 + 15) & ~(size_t)15) + 128;
+  auto need = [&](int st) {
+    return fixed + (size_t)st * (kRecHeader * 4 + (size_t)p.index_words_per_frame * 4 +
+                                 (size_t)p.ops_cap * sizeof(aiko_b200_overlay_op) + 2 * (size_t)p.seg_stride);
+  };
+  int stages = env_int("AIKO_B200_RESIZE_STAGES", 2);
   if (stages > 8) stages = 8;
   const size_t max_smem = (size_t)device_max_smem_optin();
-  p.ops_cap = (p.has_overlay && p.ov.max_ops > 0 && p.ov.max_ops <= 32 * kMaskWords) ? p.ov.max_ops : 0;
-  const size_t mrec = (size_t)(kRecHeader + ((groups + 31) / 32) * ((p.ops_cap + 31) / 32) * 32) * 4;
-  auto need = [&](int st) {
-    return fixed + (((st + 1) * mrec + 15) & ~(size_t)15) + (size_t)(st + 1) * p.ops_cap * sizeof(aiko_b200_overlay_op) +
-           (size_t)st * 2 * p.seg_stride;
-  };
   while (stages > 2 && need(stages) > max_smem) stages--;
   if (stages < 2 || need(stages) > max_smem) return AIKO_B200_OK;  // not staged
   p.stages = stages;
@@ -532,7 +495,9 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
   if (overlay) {
     AIKO_CHECK_ARG(overlay->ops && overlay->op_offsets, "resize_linear: overlay without ops/op_offsets");
     p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
-                      overlay->patch_h, overlay->max_ops_per_frame};
+                      overlay->patch_h, overlay->max_ops_per_frame, overlay->index,
+                      overlay->index_width, overlay->index_segments, overlay->index_words,
+                      overlay->index_frame_words};
   }
   p.items = n_frames * dst_h;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

@@ -69,7 +69,7 @@ class DeviceBatch:
             per_frame = [build_ops(overlays, width, height, layout, atlas)] * n
         else:
             per_frame = [build_ops(o, width, height, layout, atlas) for o in overlays]
-        return ops.DeviceOverlay.from_host(per_frame, self.device, atlas.device(self.device))
+        return ops.DeviceOverlay.from_host(per_frame, self.device, atlas.device(self.device), width=width)
 
     def _run(self, t, recipe):
         i = 0

@@ -47,13 +47,74 @@ def _out(out, shape, device, name, dtype=torch.uint8):
     return out
 
 
+INDEX_MAX_OPS = 128      # frames with longer draw lists are culled on the device instead
+
+
+def build_overlay_index(ops_per_frame, width):
+    """Spatial index of a draw list for frames ``width`` pixels wide (layout: include/aiko_b200.h).
+    -> (uint32 ndarray [frames, frame_words], segments, words) or None when a list is too long."""
+    most = max((len(o) for o in ops_per_frame), default=0)
+    if most == 0 or most > INDEX_MAX_OPS:
+        return None
+    words = (most + 31) // 32
+    segments = ((width + 3) // 4 + 31) // 32
+    lane_lo = (np.arange(segments)[:, None] * 128 + np.arange(32)[None, :] * 4)          # [seg, lane]
+    lane_hi = lane_lo + 3
+    frame_words = 2 * segments * words * 32 + words * 32 * 2
+    out = np.zeros((len(ops_per_frame), frame_words), np.uint32)
+    cache = {}
+    for f, frame_ops in enumerate(ops_per_frame):
+        key = id(frame_ops)
+        if key in cache:                     # the same list object for many frames (one overlay per batch)
+            out[f] = out[cache[key]]
+            continue
+        cache[key] = f
+        n = len(frame_ops)
+        if n == 0:
+            continue
+        kind = np.array([o.kind for o in frame_ops])
+        x0 = np.array([o.x0 for o in frame_ops]); x1 = np.array([o.x1 for o in frame_ops])
+        y0 = np.array([o.y0 for o in frame_ops]); y1 = np.array([o.y1 for o in frame_ops])
+        rect = kind == 0
+        grow = rect.astype(np.int64)
+        # side variant: two intervals A, B (equal for glyphs); band variant: the whole span
+        a0 = x0 - grow; a1 = np.where(rect, x0 + 1, x1); b0 = np.where(rect, x1 - 1, x0); b1 = x1 + grow
+        full0, full1 = x0 - grow, x1 + grow
+
+        def touches(lo, hi):                 # [op, seg, lane]
+            return (lo[:, None, None] <= lane_hi[None]) & (hi[:, None, None] >= lane_lo[None])
+
+        side = touches(a0, a1) | touches(b0, b1)
+        band = touches(full0, full1)
+        xm = np.zeros((2, segments, words, 32), np.uint32)
+        for b in range(n):
+            w, bit = divmod(b, 32)
+            xm[0, :, w, :] |= (side[b].astype(np.uint32) << np.uint32(bit))
+            xm[1, :, w, :] |= (band[b].astype(np.uint32) << np.uint32(bit))
+        clip = lambda v: np.clip(v, -32768, 32767).astype(np.int64) & 0xffff
+        yinfo = np.zeros((words * 32, 2), np.uint32)
+        yinfo[:, 0] = 1                      # unused slots: first_row 1 > last_row 0 -> never hit
+        yinfo[:n, 0] = (clip(y0 - grow) | (clip(y1 + grow) << 16)).astype(np.uint32)
+        yb0 = np.where(rect, y0 + 1, 32767); yb1 = np.where(rect, y1 - 1, -32768)
+        yinfo[:n, 1] = (clip(yb0) | (clip(yb1) << 16)).astype(np.uint32)
+        out[f] = np.concatenate([xm.reshape(-1), yinfo.reshape(-1)])
+    return out, segments, words
+
+
 class DeviceOverlay:
     """A draw list resident on the GPU (see aiko_b200_overlay in include/aiko_b200.h)."""
 
-    def __init__(self, ops, op_offsets, atlas=None, max_ops_per_frame=0):
+    def __init__(self, ops, op_offsets, atlas=None, max_ops_per_frame=0, index=None, index_width=0):
         self.ops, self.op_offsets, self.atlas = ops, op_offsets, atlas
         self.struct = Overlay()
         self.struct.max_ops_per_frame = int(max_ops_per_frame)
+        self.index = None
+        if index is not None:
+            table, segments, words = index
+            self.index = table
+            self.struct.index = table.data_ptr()
+            self.struct.index_width, self.struct.index_segments = int(index_width), int(segments)
+            self.struct.index_words, self.struct.index_frame_words = int(words), int(table.shape[1])
         self.struct.ops = ops.data_ptr()
         self.struct.op_offsets = op_offsets.data_ptr()
         if atlas is not None:
@@ -75,11 +136,18 @@ class DeviceOverlay:
         return raw, offsets
 
     @staticmethod
-    def from_host(ops_per_frame, device, atlas=None):
-        """ops_per_frame: list (one entry per frame) of lists of OverlayOp."""
+    def from_host(ops_per_frame, device, atlas=None, width=None):
+        """ops_per_frame: list (one entry per frame) of lists of OverlayOp; ``width``: frame width
+        the ops were built for (enables the spatial index the fused resize kernel uses)."""
         raw, offsets = DeviceOverlay.pack_host(ops_per_frame)
         most = max((len(o) for o in ops_per_frame), default=0)
-        return DeviceOverlay(torch.from_numpy(raw).to(device), torch.from_numpy(offsets).to(device), atlas, most)
+        index = None
+        if width:
+            built = build_overlay_index(ops_per_frame, width)
+            if built is not None:
+                index = (torch.from_numpy(built[0]).to(device), built[1], built[2])
+        return DeviceOverlay(torch.from_numpy(raw).to(device), torch.from_numpy(offsets).to(device), atlas, most,
+                             index, width or 0)
 
     def pointer(self):
         return ctypes.pointer(self.struct)

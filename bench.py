@@ -184,8 +184,12 @@ def run_gpu_arm(args):
     frame_ops = build_ops(OVERLAY, DST_W, DST_H, "bgr", atlas)
     exp = os.environ.get("AIKO_BENCH_EXPERIMENT_OPS")          # experiments only: "rects" | "glyphs"
     if exp:
-        frame_ops = [] if exp == "none" else [o for o in frame_ops if (o.kind == 0) == (exp == "rects")]
-    ov = ops.DeviceOverlay.from_host([frame_ops] * BATCH, device, atlas.device(device))
+        if exp == "faraway":                # four rectangles that touch no row of the frame
+            from aiko_services_b200._native import OverlayOp
+            frame_ops = [OverlayOp(0, 100 + 50 * k, 10000, 300 + 50 * k, 10100, 0xffff, 0, 0) for k in range(4)]
+        else:
+            frame_ops = [] if exp == "none" else [o for o in frame_ops if (o.kind == 0) == (exp == "rects")]
+    ov = ops.DeviceOverlay.from_host([frame_ops] * BATCH, device, atlas.device(device), width=DST_W)
 
     # device-resident inputs: N_ROTATING_BATCHES distinct batches (streams sharded by rank for N>1)
     batches = [torch.from_numpy(synthetic_batch(1000 * rank + i)).to(device) for i in range(N_ROTATING_BATCHES)]
@@ -292,7 +296,7 @@ def run_gpu_arm(args):
                     "note": "Pipeline.process_frame over ImageResize -> ImageOverlay -> ImageConvert(RGB2BGR) -> "
                             "ImageOutput; pinned host frames -> cudaMemcpyAsync -> fused kernel -> D2H, 2 aiko streams "
                             "alternating"},
-            "gpu_launches": args.steps,
+            "gpu_launches": args.steps * world,
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -1,0 +1,94 @@
+#!/usr/bin/env python
+"""Secondary measurements: the other BASELINE.json configs and the stand-alone kernels, each as
+units/s and as a fraction of the measured HBM roofline (algorithmic bytes of SURVEY.md 8(d)).
+Device-resident inputs, CUDA events, rotating inputs larger than L2.  One JSON line per kernel.
+
+    python benchmarks/configs.py [--steps 50]
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from aiko_services_b200 import audio_ops, ops  # noqa: E402
+
+
+def peak_gbs():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    return (float(json.load(open(path))["hbm_gbs"]), "measured") if os.path.exists(path) else (6650.0, "fallback")
+
+
+def timed(fn, steps, warmup=5):
+    for i in range(warmup):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def report(name, units, unit_name, algo_bytes_per_unit, ms, extra=None):
+    peak, src = peak_gbs()
+    achieved = units * algo_bytes_per_unit / (ms * 1e-3) / 1e9
+    line = {"kernel": name, "value": units / (ms * 1e-3), "unit": f"{unit_name}/s", "ms_per_launch": ms,
+            "units_per_launch": units, "algorithmic_bytes_per_unit": algo_bytes_per_unit,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "peak_source": src}}
+    line.update(extra or {})
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=50)
+    args = ap.parse_args()
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(1)
+    rot = 4
+
+    hd = [torch.randint(0, 256, (32, 1080, 1920, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+    out = torch.empty((32, 480, 640, 3), dtype=torch.uint8, device=dev)
+    ms = timed(lambda i: ops.resize_linear(hd[i % rot], 640, 480, out=out), args.steps)
+    report("resize_linear 1080p->640x480 (no overlay)", 32, "frames", 6_451_200, ms)
+    ms = timed(lambda i: ops.resize_bicubic_aa(hd[i % rot], 640, 480, out=out), max(args.steps // 5, 5))
+    report("resize_bicubic_aa 1080p->640x480 (config 1, codecs excluded)", 32, "frames", 7_142_400, ms)
+
+    sw = torch.empty_like(hd[0])
+    ms = timed(lambda i: ops.swap_rb(hd[i % rot], out=sw), args.steps)
+    report("swap_rb 1080p", 32, "frames", 2 * 6_220_800, ms)
+    gray = torch.empty((32, 1080, 1920), dtype=torch.uint8, device=dev)
+    ms = timed(lambda i: ops.bgr2gray(hd[i % rot], out=gray), args.steps)
+    report("bgr2gray 1080p", 32, "frames", 6_220_800 + 2_073_600, ms)
+    ms = timed(lambda i: ops.flip(hd[i % rot], 1, out=sw), args.steps)
+    report("flip horizontal 1080p", 32, "frames", 2 * 6_220_800, ms)
+    del sw, gray
+
+    uhd = [torch.randint(0, 256, (8, 2160, 3840, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+    nchw = torch.empty((8, 3, 224, 224), dtype=torch.float32, device=dev)
+    ms = timed(lambda i: ops.resize_norm_f32(uhd[i % rot], 224, 224, (0.485, 0.456, 0.406), (0.229, 0.224, 0.225),
+                                             out=nchw), args.steps)
+    report("resize_norm_f32 4K->224x224 NCHW (config 4, batch 8)", 8, "frames", 4_272_128, ms)
+    del uhd
+
+    t = np.arange(16000) / 16000.0
+    freqs = np.geomspace(50, 7000, 1024)
+    rng = np.random.default_rng(5000)
+    win = (3000 * np.sin(2 * np.pi * freqs[:, None] * t[None, :]) + rng.normal(0, 200, (1024, 16000))).astype(np.int16)
+    aud = [torch.from_numpy(np.roll(win, k, axis=0)).to(dev) for k in range(rot)]
+    ms = timed(lambda i: audio_ops.audio_chain(aud[i % rot], 16000), args.steps)
+    report("audio_chain 1024 x 16000 int16 (config 5: FFT + bands + gate/top-100)", 1024, "windows", 96_832, ms)
+    ms = timed(lambda i: audio_ops.audio_chain(aud[i % rot], 16000, bands=False, top=False), args.steps)
+    report("audio_chain, FFT magnitudes only", 1024, "windows", 96_000, ms)
+
+
+if __name__ == "__main__":
+    main()

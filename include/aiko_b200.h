@@ -74,8 +74,18 @@ typedef struct aiko_b200_overlay {
   const uint8_t* luts;             /* device */
   int32_t patch_w, patch_h;
   int32_t n_patches;
-  int32_t max_ops_per_frame;       /* largest op count of any frame, or 0 if unknown (a hint: kernels size
-                                      their shared-memory copy of a frame's list with it) */
+  int32_t max_ops_per_frame;       /* largest op count of any frame, or 0 if unknown */
+  /* Optional spatial index of the draw list for frames `index_width` pixels wide (NULL = kernels
+   * cull the list themselves).  Per frame, index_frame_words uint32:
+   *   xmask[2][index_segments][index_words][32]  bit b of word [v][s][w][l] = op 32*w + b can touch
+   *       pixels 128*s + 4*l .. +3; v = 0: rows where a rectangle only has its two side bands,
+   *       v = 1: rows inside a rectangle's top / bottom band (glyph ops: same in both);
+   *   yinfo[index_words][32][2]  per op: (first_row | last_row << 16), (band_row_0 | band_row_1 << 16)
+   *       as int16: the op touches rows first..last; a rectangle is in its band variant on rows
+   *       <= band_row_0 or >= band_row_1.
+   * Built by aiko_services_b200.ops.build_overlay_index (numpy). */
+  const uint32_t* index;
+  int32_t index_width, index_segments, index_words, index_frame_words;
 } aiko_b200_overlay;
 
 /* ---------------------------------------------------------------------- */
