@@ -19,6 +19,7 @@ constexpr int kMaxHalf = 8192;       // N/2 complex points must fit twice in sha
 constexpr int kTopK = 100;           // AF_SAMPLES_MAXIMUM, audio_io.py:206
 constexpr int kBands = 8;            // AR_BAND_COUNT, audio_io.py:237
 constexpr int kHistBins = 4096;
+constexpr int kDirectSort = 1024;    // up to this many gated bins are sorted directly
 
 struct AudioParams {
   const void* audio;
@@ -103,7 +104,7 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
   extern __shared__ __align__(16) uint8_t smem[];
   float2* buf0 = reinterpret_cast<float2*>(smem);
   float2* buf1 = buf0 + p.half;
-  __shared__ int s_count, s_threshold_bin, s_above;
+  __shared__ int s_count, s_threshold_bin;
   __shared__ int hist[kHistBins];
   const int half = p.half, n = p.n;
 
@@ -166,49 +167,73 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
     if (p.top_amp != nullptr) {
       unsigned long long* list = reinterpret_cast<unsigned long long*>(x);     // the spectrum is no longer needed
       const int list_cap = half;                                               // half * 8 bytes = one buffer
-      for (int i = threadIdx.x; i < kHistBins; i += kAudioThreads) hist[i] = 0;
-      if (threadIdx.x == 0) { s_count = 0; s_threshold_bin = 0; s_above = 0; }
-      __syncthreads();
       const int klo = max(p.gate_lo, 0), khi = min(p.gate_hi, half);
-      for (int k = klo + threadIdx.x; k <= khi; k += kAudioThreads) {
-        const float a = amp[k];
-        if (a >= p.amp_min && a <= p.amp_max)
-          atomicAdd(&hist[__float_as_uint(a) >> 20], (k != 0 && k != half) ? 2 : 1);
-      }
-      __syncthreads();
-      if (threadIdx.x < 32) {   // highest bin T with count(bins >= T) >= 100 (or 0 if fewer pass the gate)
-        int running = 0, found = -1, above = 0;
-        for (int base = kHistBins - 32; base >= 0 && found < 0; base -= 32) {
-          const int c = hist[base + 31 - threadIdx.x];            // lane 0 = highest bin of the chunk
-          int incl = c;
+      const int lane = threadIdx.x & 31;
+      // Appends every bin that passes the gates and whose key bin is >= min_bin (each bin k stands
+      // for spectrum indices k and n - k).  One atomic per warp; order in the list is irrelevant.
+      auto collect = [&](unsigned min_bin) {
+        for (int base = klo; base <= khi; base += kAudioThreads) {
+          const int k = base + (int)threadIdx.x;
+          float a = 0.f;
+          int copies = 0;
+          if (k <= khi) {
+            a = amp[k];
+            if (a >= p.amp_min && a <= p.amp_max && (__float_as_uint(a) >> 20) >= min_bin)
+              copies = (k != 0 && k != half) ? 2 : 1;
+          }
+          if (__ballot_sync(0xffffffffu, copies != 0) == 0) continue;
+          int incl = copies;
 #pragma unroll
           for (int d = 1; d < 32; d <<= 1) {
             const int t = __shfl_up_sync(0xffffffffu, incl, d);
-            if ((int)threadIdx.x >= d) incl += t;
+            if (lane >= d) incl += t;
           }
-          const unsigned hit = __ballot_sync(0xffffffffu, running + incl >= kTopK);
-          if (hit) {
-            const int l = __ffs(hit) - 1;
-            found = base + 31 - l;
-            above = running + __shfl_sync(0xffffffffu, incl - c, l);
+          int start = 0;
+          if (lane == 31) start = atomicAdd(&s_count, incl);
+          start = __shfl_sync(0xffffffffu, start, 31) + incl - copies;
+          if (copies) {
+            const unsigned long long hi = (unsigned long long)__float_as_uint(a) << 32;
+            if (start < list_cap) list[start] = hi | (0xffffffffu - (unsigned)k);
+            if (copies == 2 && start + 1 < list_cap) list[start + 1] = hi | (0xffffffffu - (unsigned)(n - k));
           }
-          running += __shfl_sync(0xffffffffu, incl, 31);
         }
-        if (threadIdx.x == 0) { s_threshold_bin = max(found, 0); s_above = above; }
-      }
+      };
+      if (threadIdx.x == 0) s_count = 0;
       __syncthreads();
-      const unsigned tbin = (unsigned)s_threshold_bin;
-      for (int k = klo + threadIdx.x; k <= khi; k += kAudioThreads) {
-        const float a = amp[k];
-        if (a >= p.amp_min && a <= p.amp_max && (__float_as_uint(a) >> 20) >= tbin) {
-          const int copies = (k != 0 && k != half) ? 2 : 1;
-          const int at = atomicAdd(&s_count, copies);
-          const unsigned long long hi = (unsigned long long)__float_as_uint(a) << 32;
-          if (at < list_cap) list[at] = hi | (0xffffffffu - (unsigned)k);
-          if (copies == 2 && at + 1 < list_cap) list[at + 1] = hi | (0xffffffffu - (unsigned)(n - k));
+      collect(0u);
+      __syncthreads();
+      if (s_count > kDirectSort) {
+        // Many bins pass the gates (noise-like input): keep only key bins that can reach the top 100.
+        __syncthreads();
+        for (int i = threadIdx.x; i < kHistBins; i += kAudioThreads) hist[i] = 0;
+        if (threadIdx.x == 0) { s_count = 0; s_threshold_bin = 0; }
+        __syncthreads();
+        for (int k = klo + threadIdx.x; k <= khi; k += kAudioThreads) {
+          const float a = amp[k];
+          if (a >= p.amp_min && a <= p.amp_max)
+            atomicAdd(&hist[__float_as_uint(a) >> 20], (k != 0 && k != half) ? 2 : 1);
         }
+        __syncthreads();
+        if (threadIdx.x < 32) {   // highest bin T with count(bins >= T) >= 100
+          int running = 0, found = -1;
+          for (int base = kHistBins - 32; base >= 0 && found < 0; base -= 32) {
+            const int c = hist[base + 31 - threadIdx.x];            // lane 0 = highest bin of the chunk
+            int incl = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+              const int t = __shfl_up_sync(0xffffffffu, incl, d);
+              if ((int)threadIdx.x >= d) incl += t;
+            }
+            const unsigned hit = __ballot_sync(0xffffffffu, running + incl >= kTopK);
+            if (hit) found = base + 31 - (__ffs(hit) - 1);
+            running += __shfl_sync(0xffffffffu, incl, 31);
+          }
+          if (threadIdx.x == 0) s_threshold_bin = max(found, 0);
+        }
+        __syncthreads();
+        collect((unsigned)s_threshold_bin);
+        __syncthreads();
       }
-      __syncthreads();
       const int count = min(s_count, list_cap);
       int padded = 1;
       while (padded < count) padded <<= 1;

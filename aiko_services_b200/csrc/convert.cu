@@ -106,7 +106,8 @@ __global__ void __launch_bounds__(kThreads) gray2bgr_kernel(const uint8_t* __res
 // Flip / crop: one CTA per output row; the source row (segment) goes through shared memory
 // so both the global read and the global write are coalesced vectors.
 __global__ void __launch_bounds__(kThreads) flip_rows_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
-                                                             long long n_rows, int h, int w, int ch, int flip_code) {
+                                                             long long n_rows, int h, int w, int ch, int flip_code,
+                                                             int rev_offset) {
   extern __shared__ __align__(16) uint8_t srow[];
   const int rb = w * ch;
   for (long long r = blockIdx.x; r < n_rows; r += gridDim.x) {
@@ -141,29 +142,21 @@ __global__ void __launch_bounds__(kThreads) flip_rows_kernel(const uint8_t* __re
     }
     __syncthreads();
     const uint8_t* sp = srow + head;
-    const bool dvec = (((uintptr_t)d | (uintptr_t)rb) & 15) == 0;
-    if (dvec) {
-      for (int i = threadIdx.x; i < (rb >> 4); i += kThreads) {
-        uint32_t wds[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-          uint32_t v = 0;
-#pragma unroll
-          for (int b = 0; b < 4; b++) {
-            const int o = i * 16 + k * 4 + b;  // output byte index
-            const int px = o / ch, c = o - px * ch;
-            v |= (uint32_t)sp[(w - 1 - px) * ch + c] << (8 * b);
-          }
-          wds[k] = v;
-        }
-        stg_stream(reinterpret_cast<uint4*>(d) + i, make_uint4(wds[0], wds[1], wds[2], wds[3]));
+    // reversed row, pixel by pixel, into a second shared buffer; then one coalesced copy out
+    uint8_t* rrow = srow + rev_offset;
+    if (ch == 3) {
+      for (int px = threadIdx.x; px < w; px += kThreads) {
+        const uint8_t* q = sp + 3 * (w - 1 - px);
+        rrow[3 * px] = q[0]; rrow[3 * px + 1] = q[1]; rrow[3 * px + 2] = q[2];
       }
+    } else if (ch == 1) {
+      for (int px = threadIdx.x; px < w; px += kThreads) rrow[px] = sp[w - 1 - px];
     } else {
-      for (int o = threadIdx.x; o < rb; o += kThreads) {
-        const int px = o / ch, c = o - px * ch;
-        d[o] = sp[(w - 1 - px) * ch + c];
-      }
+      for (int px = threadIdx.x; px < w; px += kThreads)
+        for (int c = 0; c < ch; c++) rrow[px * ch + c] = sp[(w - 1 - px) * ch + c];
     }
+    __syncthreads();
+    store_row(d, rrow, rb);
     __syncthreads();
   }
 }
@@ -236,14 +229,15 @@ extern "C" int aiko_b200_flip_u8(const uint8_t* src, uint8_t* dst, int n_frames,
   if (n_frames == 0 || h == 0 || w == 0) return AIKO_B200_OK;
   AIKO_CHECK_ARG(src && dst && src != dst, "flip: null or aliased pointers");
   AIKO_CHECK_ARG(channels >= 1 && channels <= 4, "flip: channels %d not in 1..4", channels);
-  const size_t smem = (size_t)w * channels + 48;
-  AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "flip: row of %zu bytes exceeds shared memory", smem);
+  const int rev_offset = (int)((((size_t)w * channels + 48) + 15) & ~(size_t)15);   // staged row, then reversed row
+  const size_t smem = (size_t)rev_offset + (((size_t)w * channels + 15) & ~(size_t)15);
+  AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "flip: row of %d bytes exceeds shared memory", w * channels);
   AIKO_CUDA(cudaFuncSetAttribute(flip_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long rows = (long long)n_frames * h;
   long long grid = (long long)sm_count() * 8;
   if (grid > rows) grid = rows;
   flip_rows_kernel<<<(unsigned)grid, kThreads, smem, (cudaStream_t)stream>>>(src, dst, rows, h, w, channels,
-                                                                            flip_code);
+                                                                            flip_code, rev_offset);
   return cuda_status(cudaGetLastError(), "flip launch");
 }
 

@@ -116,22 +116,25 @@ struct BicubicParams {
   int kx_in_smem;
 };
 
-__global__ void __launch_bounds__(kThreads) resize_bicubic_rows(const BicubicParams p) {
+constexpr int kBicubicThreads = 512;
+constexpr int kRowsPerRound = 4;   // source rows staged and filtered between two barriers
+
+__global__ void __launch_bounds__(kBicubicThreads) resize_bicubic_rows(const BicubicParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int src_row_bytes = p.sw * p.ch, mid_row_bytes = p.dw * p.ch;
   const int src_stride = (src_row_bytes + 31) & ~15, mid_stride = (mid_row_bytes + 15) & ~15;
-  uint8_t* srow = smem;                               // one staged source row (+ 16 bytes of head room)
-  uint8_t* ring = srow + src_stride;                  // ring_rows intermediate rows
+  uint8_t* srow = smem;                               // kRowsPerRound staged source rows
+  uint8_t* ring = srow + (size_t)kRowsPerRound * src_stride;   // ring_rows intermediate rows
   int* bx_s = reinterpret_cast<int*>(ring + (size_t)p.ring_rows * mid_stride);   // xmin, count per dx
-  int* kx_s = bx_s + 2 * p.dw;                        // weights, when they fit
+  int* kx_s = bx_s + ((2 * p.dw + 3) & ~3);           // weights, when they fit (16-byte aligned rows)
 
   const int* bx = p.ws + p.off_bx;
   const int* kx = p.ws + p.off_kx;
   const int* by = p.ws + p.off_by;
   const int* ky = p.ws + p.off_ky;
-  for (int i = threadIdx.x; i < 2 * p.dw; i += kThreads) bx_s[i] = bx[i];
+  for (int i = threadIdx.x; i < 2 * p.dw; i += kBicubicThreads) bx_s[i] = bx[i];
   if (p.kx_in_smem)
-    for (int i = threadIdx.x; i < p.dw * p.ksx; i += kThreads) kx_s[i] = kx[i];
+    for (int i = threadIdx.x; i < p.dw * p.ksx; i += kBicubicThreads) kx_s[i] = kx[i];
   const int* kxt = p.kx_in_smem ? kx_s : kx;
   __syncthreads();
 
@@ -140,47 +143,61 @@ __global__ void __launch_bounds__(kThreads) resize_bicubic_rows(const BicubicPar
   const int dy1 = min(dy0 + p.band, p.dh);
   const uint8_t* fsrc = p.src + (size_t)frame * p.sh * src_row_bytes;
   uint8_t* fdst = p.dst + (size_t)frame * p.dh * mid_row_bytes;
+  const int band_last = by[2 * (dy1 - 1)] + by[2 * (dy1 - 1) + 1] - 1;   // last source row this band needs
 
   int next_src = by[2 * dy0];
   for (int dy = dy0; dy < dy1; dy++) {
     const int ymin = by[2 * dy], ycnt = by[2 * dy + 1];
-    // horizontal pass for every source row this output row still needs
-    for (; next_src < ymin + ycnt; next_src++) {
-      const uint8_t* g = fsrc + (size_t)next_src * src_row_bytes;
-      const int head = (int)(reinterpret_cast<uintptr_t>(g) & 15);
-      if (head == 0 && (src_row_bytes & 15) == 0) {
-        for (int i = threadIdx.x; i < (src_row_bytes >> 4); i += kThreads)
-          reinterpret_cast<uint4*>(srow)[i] = ldg_stream(reinterpret_cast<const uint4*>(g) + i);
-      } else {
-        for (int i = threadIdx.x; i < src_row_bytes; i += kThreads) srow[i] = g[i];
+    // horizontal pass for the source rows this output row still needs (and up to
+    // kRowsPerRound - 1 rows ahead, which the ring is sized for)
+    while (next_src < ymin + ycnt) {
+      const int nrows = min(kRowsPerRound, band_last - next_src + 1);
+      const bool vec = ((reinterpret_cast<uintptr_t>(fsrc) | (uintptr_t)src_row_bytes) & 15) == 0;
+      for (int r = 0; r < nrows; r++) {
+        const uint8_t* g = fsrc + (size_t)(next_src + r) * src_row_bytes;
+        uint8_t* s = srow + (size_t)r * src_stride;
+        if (vec) {
+          for (int i = threadIdx.x; i < (src_row_bytes >> 4); i += kBicubicThreads)
+            reinterpret_cast<uint4*>(s)[i] = ldg_stream(reinterpret_cast<const uint4*>(g) + i);
+        } else {
+          for (int i = threadIdx.x; i < src_row_bytes; i += kBicubicThreads) s[i] = g[i];
+        }
       }
       __syncthreads();
-      uint8_t* mid = ring + (size_t)(next_src % p.ring_rows) * mid_stride;
-      for (int dx = threadIdx.x; dx < p.dw; dx += kThreads) {
-        const int xmin = bx_s[2 * dx], cnt = bx_s[2 * dx + 1];
-        const int* k = kxt + (size_t)dx * p.ksx;
-        const uint8_t* s = srow + xmin * p.ch;
-        if (p.ch == 3) {
-          int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
-          for (int t = 0; t < cnt; t++) {
-            const int w = k[t];
-            a0 += s[3 * t] * w; a1 += s[3 * t + 1] * w; a2 += s[3 * t + 2] * w;
-          }
-          mid[3 * dx] = clip8_q22(a0); mid[3 * dx + 1] = clip8_q22(a1); mid[3 * dx + 2] = clip8_q22(a2);
-        } else {
-          for (int c = 0; c < p.ch; c++) {
-            int a = 1 << (kPrecisionBits - 1);
-            for (int t = 0; t < cnt; t++) a += s[t * p.ch + c] * k[t];
-            mid[dx * p.ch + c] = clip8_q22(a);
+      for (int r = 0; r < nrows; r++) {
+        const uint8_t* srcrow = srow + (size_t)r * src_stride;
+        uint8_t* mid = ring + (size_t)((next_src + r) % p.ring_rows) * mid_stride;
+        for (int dx = threadIdx.x; dx < p.dw; dx += kBicubicThreads) {
+          const int xmin = bx_s[2 * dx], cnt = bx_s[2 * dx + 1];
+          const int4* k4 = reinterpret_cast<const int4*>(kxt + (size_t)dx * p.ksx);   // rows of 4-padded weights
+          const uint8_t* s = srcrow + xmin * p.ch;
+          if (p.ch == 3) {
+            int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
+            for (int t = 0; t < cnt; t += 4) {       // padding weights are zero; staged rows have slack bytes
+              const int4 w = k4[t >> 2];
+              const uint8_t* q = s + 3 * t;
+              a0 += q[0] * w.x + q[3] * w.y + q[6] * w.z + q[9] * w.w;
+              a1 += q[1] * w.x + q[4] * w.y + q[7] * w.z + q[10] * w.w;
+              a2 += q[2] * w.x + q[5] * w.y + q[8] * w.z + q[11] * w.w;
+            }
+            mid[3 * dx] = clip8_q22(a0); mid[3 * dx + 1] = clip8_q22(a1); mid[3 * dx + 2] = clip8_q22(a2);
+          } else {
+            const int* k = reinterpret_cast<const int*>(k4);
+            for (int c = 0; c < p.ch; c++) {
+              int a = 1 << (kPrecisionBits - 1);
+              for (int t = 0; t < cnt; t++) a += s[t * p.ch + c] * k[t];
+              mid[dx * p.ch + c] = clip8_q22(a);
+            }
           }
         }
       }
       __syncthreads();
+      next_src += nrows;
     }
     // vertical pass: one output row from ycnt intermediate rows
     const int* k = ky + (size_t)dy * p.ksy;
     uint8_t* o = fdst + (size_t)dy * mid_row_bytes;
-    for (int i4 = threadIdx.x * 4; i4 < mid_row_bytes; i4 += kThreads * 4) {
+    for (int i4 = threadIdx.x * 4; i4 < mid_row_bytes; i4 += kBicubicThreads * 4) {
       int a[4];
 #pragma unroll
       for (int j = 0; j < 4; j++) a[j] = 1 << (kPrecisionBits - 1);
@@ -197,8 +214,8 @@ __global__ void __launch_bounds__(kThreads) resize_bicubic_rows(const BicubicPar
         for (int j = 0; j < 4 && i4 + j < mid_row_bytes; j++) o[i4 + j] = clip8_q22(a[j]);
       }
     }
-    // the next output row's horizontal pass starts with a barrier after staging, which also
-    // orders these ring reads before the ring rows they no longer need are overwritten
+    // the next staging round starts with a barrier before any ring row is rewritten, which
+    // orders these ring reads before it
   }
 }
 
@@ -247,7 +264,7 @@ extern "C" int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, 
   p.n = n_frames; p.sh = src_h; p.sw = src_w; p.dh = dst_h; p.dw = dst_w; p.ch = channels;
   p.ksx = l.x.ksize; p.ksy = l.y.ksize;
   p.off_bx = l.x.off_bounds; p.off_kx = l.x.off_k; p.off_by = l.y.off_bounds; p.off_ky = l.y.off_k;
-  p.ring_rows = l.y.ksize + 1;
+  p.ring_rows = l.y.ksize + kRowsPerRound;
   // bands: enough CTAs to fill the machine, long enough that the vertical halo stays small
   const double scale_y = (double)src_h / dst_h;
   int band = (int)(4.0 * l.y.ksize / (scale_y < 1.0 ? 1.0 : scale_y)) + 1;  // halo <= ~25 % of the rows read
@@ -259,7 +276,8 @@ extern "C" int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, 
   p.bands_per_frame = (dst_h + band - 1) / band;
   const size_t src_stride = ((size_t)src_w * channels + 31) & ~(size_t)15;
   const size_t mid_stride = ((size_t)dst_w * channels + 15) & ~(size_t)15;
-  size_t smem = src_stride + (size_t)p.ring_rows * mid_stride + (size_t)2 * dst_w * sizeof(int);
+  size_t smem = (size_t)kRowsPerRound * src_stride + 16 + (size_t)p.ring_rows * mid_stride +
+                (size_t)((2 * dst_w + 3) & ~3) * sizeof(int);
   const size_t kx_bytes = (size_t)dst_w * l.x.ksize * sizeof(int);
   const size_t max_smem = (size_t)device_max_smem_optin();
   p.kx_in_smem = (smem + kx_bytes <= 100 * 1024) ? 1 : 0;
@@ -272,7 +290,7 @@ extern "C" int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, 
   AIKO_CUDA(cudaFuncSetAttribute(resize_bicubic_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long grid = (long long)n_frames * p.bands_per_frame;
   AIKO_CHECK_ARG(grid < ((long long)1 << 31), "resize_bicubic: too many bands");
-  resize_bicubic_rows<<<(unsigned)grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  resize_bicubic_rows<<<(unsigned)grid, kBicubicThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
   return cuda_status(cudaGetLastError(), "resize_bicubic launch");
 }
 

@@ -65,6 +65,23 @@ def test_audio_chain_float_input_and_other_lengths(cuda):
             assert np.abs(got - amp).max() <= 1e-4 * np.abs(amp).max(), (n, k)
 
 
+def test_audio_filter_when_thousands_of_bins_pass_the_gate(cuda):
+    """Noise-like windows: far more than 100 bins pass the gates, so the pruning path runs."""
+    rng = np.random.default_rng(11)
+    fs, n = 16000, 16000
+    x = (rng.standard_normal((4, n)) * 9000).astype(np.float32)
+    res = audio_ops.audio_chain(torch.from_numpy(x).to(cuda), fs)
+    for k in range(4):
+        amp, freq = A.pe_fft(x[k], fs)
+        tf, ta = A.pe_audio_filter(amp, freq)
+        assert ((amp >= 0.1) & (amp <= 12)).sum() > 2000 and len(ta) == 100
+        assert int(res["top_count"][k]) == 100
+        ga = res["top_amplitudes"][k].cpu().numpy()
+        np.testing.assert_allclose(ga, ta, rtol=1e-4)             # same 100 values, same (descending) order
+        gf = res["top_frequencies"][k].cpu().numpy()
+        np.testing.assert_allclose(np.sort(gf), np.sort(tf), rtol=1e-6, atol=1e-3)
+
+
 def test_audio_chain_properties_full_batch(cuda):
     """1024 windows (BASELINE config 5): linearity of the spectrum, Parseval, symmetry."""
     fs, n = 16000, 16000
