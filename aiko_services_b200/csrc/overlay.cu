@@ -49,6 +49,250 @@ __global__ void __launch_bounds__(kThreads) overlay_rows_kernel(const OverlayPar
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tile-parallel overlay, in place.  Used right after the resize kernel wrote the frames, while
+// they are still in L2: one CTA per 64 x 16 pixel tile that the frame's draw list touches (the
+// host lists those tiles with the ops that can touch each).  Every thread owns 4 pixels, holds
+// them in registers, applies the tile's ops to them in list order and writes them back once;
+// ownership makes barriers between ops unnecessary.  Without a tile list from the host the
+// kernel runs over every tile of every frame and culls the draw list itself.
+constexpr int kTileW = 64, kTileH = 16;     // 16 groups of 4 pixels x 16 rows = 256 threads
+
+struct TileParams {
+  uint8_t* frames;
+  int n, h, w;
+  long long row_stride, frame_stride;
+  int tiles_x, tiles_y;
+  int listed;            // 1: one CTA per record of ov.tiles; 0: one CTA per tile of every frame
+  OverlayDev ov;
+};
+
+struct Pixels4 {         // 12 bytes = 4 RGB pixels of one thread
+  uint32_t w0, w1, w2;
+};
+
+__device__ __forceinline__ Pixels4 load_pixels(const uint8_t* pix, bool words, int count) {
+  Pixels4 r{0, 0, 0};
+  if (words) {
+    r.w0 = reinterpret_cast<const uint32_t*>(pix)[0];
+    r.w1 = reinterpret_cast<const uint32_t*>(pix)[1];
+    r.w2 = reinterpret_cast<const uint32_t*>(pix)[2];
+  } else {
+    uint32_t v[3] = {0, 0, 0};
+    for (int q = 0; q < count * 3; q++) v[q >> 2] |= (uint32_t)pix[q] << (8 * (q & 3));
+    r.w0 = v[0]; r.w1 = v[1]; r.w2 = v[2];
+  }
+  return r;
+}
+
+// Applies one op to the thread's pixels mlo .. mhi of row y.  Returns true if anything changed.
+__device__ __forceinline__ bool apply_op_regs(const int4 lo4, const int4 hi4, const OverlayDev& ov, int psize, int y,
+                                              int mlo, int mhi, Pixels4& px) {
+  const int kind = lo4.x, x0 = lo4.y, y0 = lo4.z, x1 = lo4.w, y1 = hi4.x;
+  const int grow = (kind == AIKO_B200_OP_RECT) ? 1 : 0;
+  if (y < y0 - grow || y > y1 + grow || mhi < x0 - grow || mlo > x1 + grow) return false;
+  if (kind == AIKO_B200_OP_RECT) {
+    bool cover[4], any = false;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      cover[k] = (mlo + k <= mhi) && rect_covers(mlo + k, y, x0, y0, x1, y1);
+      any |= cover[k];
+    }
+    if (!any) return false;
+    const uint32_t c = (uint32_t)hi4.y & 0xffffffu;     // colour bytes 0..2; pixel k = bytes 3k .. 3k+2
+    if (cover[0]) px.w0 = (px.w0 & 0xff000000u) | c;
+    if (cover[1]) { px.w0 = (px.w0 & 0x00ffffffu) | (c << 24); px.w1 = (px.w1 & 0xffff0000u) | (c >> 8); }
+    if (cover[2]) { px.w1 = (px.w1 & 0x0000ffffu) | (c << 16); px.w2 = (px.w2 & 0xffffff00u) | (c >> 16); }
+    if (cover[3]) px.w2 = (px.w2 & 0x000000ffu) | (c << 8);
+    return true;
+  }
+  const int xs = max(mlo, x0), xe = min(mhi, x1);
+  const uint32_t p0 = (uint32_t)hi4.y, p1 = (uint32_t)hi4.z, p2 = (uint32_t)hi4.w;
+  const int opx = x0 - int(p2 & 0xffff), opy = y0 - int(p2 >> 16);
+  const uint16_t* q = ov.patch_ids + (y - opy) * ov.patch_w - opx;
+  const uint16_t* qc[3] = {q + (size_t)(p0 & 0xffff) * psize, q + (size_t)(p0 >> 16) * psize,
+                           q + (size_t)(p1 & 0xffff) * psize};
+  uint16_t id[4][3];
+  bool any = false;
+#pragma unroll
+  for (int k = 0; k < 4; k++)
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const int x = mlo + k;
+      id[k][c] = (x >= xs && x <= xe) ? __ldg(qc[c] + x) : (uint16_t)0;
+      any |= id[k][c] != 0;
+    }
+  if (!any) return false;
+  uint32_t v[3] = {px.w0, px.w1, px.w2};
+#pragma unroll
+  for (int k = 0; k < 4; k++)
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const int byte = 3 * k + c;                       // compile-time after unrolling
+      if (id[k][c]) {
+        const uint32_t old = (v[byte >> 2] >> (8 * (byte & 3))) & 0xffu;
+        const uint32_t nv = __ldg(ov.luts + (size_t)id[k][c] * 256 + old);
+        v[byte >> 2] = (v[byte >> 2] & ~(0xffu << (8 * (byte & 3)))) | (nv << (8 * (byte & 3)));
+      }
+    }
+  px.w0 = v[0]; px.w1 = v[1]; px.w2 = v[2];
+  return true;
+}
+
+__global__ void __launch_bounds__(kThreads, 6) overlay_tiles_kernel(const TileParams p) {
+  __shared__ uint32_t hitmask[kThreads / 32];
+  __shared__ int4 sops[kThreads * 2];         // staged op records (32 bytes each), one batch
+  int frame, tx, ty, ob, nops, nframes = 1;
+  const uint32_t* record = nullptr;
+  if (p.listed) {
+    record = p.ov.tiles + (size_t)blockIdx.x * (4 + p.ov.tile_words);
+    const uint32_t rx = __ldg(record), ry = __ldg(record + 1), rz = __ldg(record + 2), rw = __ldg(record + 3);
+    frame = (int)rx;
+    nframes = (int)ry;                        // consecutive frames with this same draw list
+    tx = (int)(rz & 0xffff);
+    ty = (int)(rz >> 16);
+    ob = (int)rw;
+    nops = p.ov.tile_words * 32;              // bits beyond the frame's list are zero
+  } else {
+    const int tiles_per_frame = p.tiles_x * p.tiles_y;
+    frame = blockIdx.x / tiles_per_frame;
+    const int t = blockIdx.x - frame * tiles_per_frame;
+    ty = t / p.tiles_x;
+    tx = t - ty * p.tiles_x;
+    ob = __ldg(p.ov.op_offsets + frame);
+    nops = __ldg(p.ov.op_offsets + frame + 1) - ob;
+  }
+  const int tile_x0 = tx * kTileW, tile_y0 = ty * kTileH;
+  const int tile_x1 = min(tile_x0 + kTileW, p.w) - 1, tile_y1 = min(tile_y0 + kTileH, p.h) - 1;
+  const aiko_b200_overlay_op* ops = p.ov.ops + ob;
+
+  // this thread's pixels
+  const int y = tile_y0 + (threadIdx.x >> 4);
+  const int mlo = tile_x0 + (threadIdx.x & 15) * 4, mhi = min(mlo + 3, p.w - 1);
+  const bool mine = y <= tile_y1 && mlo <= tile_x1;
+  uint8_t* pix = p.frames + (long long)frame * p.frame_stride + (long long)y * p.row_stride + (long long)mlo * 3;
+  const bool words = mine && mlo + 3 < p.w && ((reinterpret_cast<uintptr_t>(pix) & 3) == 0) &&
+                     (nframes == 1 || (p.frame_stride & 3) == 0);
+  Pixels4 px{0, 0, 0};
+  bool loaded = false, dirty = false;
+  if (p.listed && mine) {       // start the (L2) pixel fetch now; it overlaps the op and atlas look-ups
+    px = load_pixels(pix, words, mhi - mlo + 1);
+    loaded = true;
+  }
+  const int psize = p.ov.patch_w * p.ov.patch_h;
+
+  for (int base = 0; base < nops; base += kThreads) {
+    // ---- which ops of this batch touch the tile
+    if (p.listed) {
+      if (threadIdx.x < kThreads / 32) {
+        const int wd = base / 32 + threadIdx.x;
+        hitmask[threadIdx.x] = (wd < p.ov.tile_words) ? __ldg(record + 4 + wd) : 0u;
+      }
+      __syncthreads();
+    } else {
+      const int i = base + threadIdx.x;
+      bool hit = false;
+      if (i < nops) {
+        const int4 lo4 = __ldg(reinterpret_cast<const int4*>(ops + i));      // kind, x0, y0, x1
+        const int y1 = __ldg(&ops[i].y1);
+        const int grow = (lo4.x == AIKO_B200_OP_RECT) ? 1 : 0;
+        hit = lo4.y - grow <= tile_x1 && lo4.w + grow >= tile_x0 && lo4.z - grow <= tile_y1 && y1 + grow >= tile_y0;
+      }
+      const uint32_t m = __ballot_sync(0xffffffffu, hit);
+      if ((threadIdx.x & 31) == 0) hitmask[threadIdx.x >> 5] = m;
+      if (!__syncthreads_or(hit)) continue;               // nothing in this batch touches the tile
+    }
+    // ---- stage the hit ops, in list order, in shared memory: thread t fetches the t-th hit
+    int total = 0, my_word = -1, before = 0;
+#pragma unroll
+    for (int wd = 0; wd < kThreads / 32; wd++) {
+      const int c = __popc(hitmask[wd]);
+      if (my_word < 0 && (int)threadIdx.x < total + c) { my_word = wd; before = total; }
+      total += c;
+    }
+    if ((int)threadIdx.x < total) {
+      uint32_t bits = hitmask[my_word];
+      for (int k = (int)threadIdx.x - before; k > 0; k--) bits &= bits - 1;
+      const int4* src = reinterpret_cast<const int4*>(ops + base + my_word * 32 + (__ffs(bits) - 1));
+      sops[2 * threadIdx.x] = __ldg(src);
+      sops[2 * threadIdx.x + 1] = __ldg(src + 1);
+    }
+    __syncthreads();
+    if (mine && nframes == 1) {
+      for (int i = 0; i < total; i++) {
+        const int4 lo4 = sops[2 * i], hi4 = sops[2 * i + 1];
+        const int grow = (lo4.x == AIKO_B200_OP_RECT) ? 1 : 0;
+        if (y < lo4.z - grow || y > hi4.x + grow || mhi < lo4.y - grow || mlo > lo4.w + grow) continue;
+        if (!loaded) { px = load_pixels(pix, words, mhi - mlo + 1); loaded = true; }
+        dirty |= apply_op_regs(lo4, hi4, p.ov, psize, y, mlo, mhi, px);
+      }
+    } else if (mine) {
+      // several frames share this list (listed mode, at most 256 ops: a single batch): the ops stay
+      // staged, the glyph tables warm up in L1, and the next frame's pixels are fetched early
+      int first_hit = total;
+      for (int i = 0; i < total && first_hit == total; i++) {
+        const int4 lo4 = sops[2 * i], hi4 = sops[2 * i + 1];
+        const int grow = (lo4.x == AIKO_B200_OP_RECT) ? 1 : 0;
+        if (!(y < lo4.z - grow || y > hi4.x + grow || mhi < lo4.y - grow || mlo > lo4.w + grow)) first_hit = i;
+      }
+      if (first_hit < total) {                    // some op can touch this thread's pixels
+        Pixels4 cur = px;                         // frame `frame`, already in flight
+        for (int f = 0; f < nframes; f++) {
+          uint8_t* fp = pix + (long long)f * p.frame_stride;
+          Pixels4 nxt{0, 0, 0};
+          if (f + 1 < nframes) nxt = load_pixels(fp + p.frame_stride, words, mhi - mlo + 1);
+          bool changed = false;
+          for (int i = first_hit; i < total; i++) {
+            const int4 lo4 = sops[2 * i], hi4 = sops[2 * i + 1];
+            changed |= apply_op_regs(lo4, hi4, p.ov, psize, y, mlo, mhi, cur);
+          }
+          if (changed) {
+            if (words) {
+              reinterpret_cast<uint32_t*>(fp)[0] = cur.w0;
+              reinterpret_cast<uint32_t*>(fp)[1] = cur.w1;
+              reinterpret_cast<uint32_t*>(fp)[2] = cur.w2;
+            } else {
+              const uint32_t v[3] = {cur.w0, cur.w1, cur.w2};
+              for (int q = 0; q < (mhi - mlo + 1) * 3; q++) fp[q] = (uint8_t)(v[q >> 2] >> (8 * (q & 3)));
+            }
+          }
+          cur = nxt;
+        }
+      }
+    }
+    __syncthreads();                              // hitmask / sops are rewritten by the next batch
+  }
+  if (dirty) {
+    if (words) {
+      reinterpret_cast<uint32_t*>(pix)[0] = px.w0;
+      reinterpret_cast<uint32_t*>(pix)[1] = px.w1;
+      reinterpret_cast<uint32_t*>(pix)[2] = px.w2;
+    } else {
+      const uint32_t v[3] = {px.w0, px.w1, px.w2};
+      for (int q = 0; q < (mhi - mlo + 1) * 3; q++) pix[q] = (uint8_t)(v[q >> 2] >> (8 * (q & 3)));
+    }
+  }
+}
+
+// frames: uint8 [n, h, w, 3] with the given strides, modified in place
+int launch_overlay_tiles(uint8_t* frames, int n, int h, int w, long long row_stride, long long frame_stride,
+                         const OverlayDev& ov, cudaStream_t stream) {
+  TileParams p{};
+  p.frames = frames; p.n = n; p.h = h; p.w = w; p.row_stride = row_stride; p.frame_stride = frame_stride;
+  p.tiles_x = (w + kTileW - 1) / kTileW;
+  p.tiles_y = (h + kTileH - 1) / kTileH;
+  p.ov = ov;
+  p.listed = (ov.tiles != nullptr && ov.index_width == w && ov.tile_height == h && ov.tile_words > 0) ? 1 : 0;
+  if (p.listed && ov.n_tiles == 0) return AIKO_B200_OK;
+  const long long grid = p.listed ? (long long)ov.n_tiles : (long long)n * p.tiles_x * p.tiles_y;
+  if (grid >= ((long long)1 << 31)) {
+    set_last_error("overlay: too many tiles (%lld)", grid);
+    return AIKO_B200_ERR_UNSUPPORTED;
+  }
+  overlay_tiles_kernel<<<(unsigned)grid, kThreads, 0, stream>>>(p);
+  return cuda_status(cudaGetLastError(), "overlay_tiles launch");
+}
+
 }  // namespace aiko
 
 using namespace aiko;
@@ -68,7 +312,8 @@ extern "C" int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_fram
   p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
                     overlay->patch_h, overlay->max_ops_per_frame, overlay->index,
                       overlay->index_width, overlay->index_segments, overlay->index_words,
-                      overlay->index_frame_words};
+                      overlay->index_frame_words, overlay->tiles, overlay->n_tiles, overlay->tile_words,
+                      overlay->tile_height};
   const size_t smem = ((size_t)w * 3 + 15) & ~(size_t)15;
   AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "overlay: row of %zu bytes exceeds shared memory", smem);
   AIKO_CUDA(cudaFuncSetAttribute(overlay_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -16,6 +16,8 @@ struct OverlayDev {
   int max_ops;   // host hint: largest per-frame op count (0 = unknown)
   const uint32_t* index;   // optional spatial index (include/aiko_b200.h), or null
   int index_width, index_segments, index_words, index_frame_words;
+  const uint32_t* tiles;   // optional list of touched tiles (include/aiko_b200.h), or null
+  int n_tiles, tile_words, tile_height;
 };
 
 // cv2.rectangle(.., thickness=2) coverage, closed form.
@@ -154,5 +156,9 @@ __device__ __forceinline__ void overlay_apply_row(const aiko_b200_overlay_op* op
     }
   }
 }
+
+// Host: apply the draw list in place to frames [n, h, w, 3] (overlay.cu, tile-parallel kernel).
+int launch_overlay_tiles(uint8_t* frames, int n, int h, int w, long long row_stride, long long frame_stride,
+                         const OverlayDev& ov, cudaStream_t stream);
 
 }  // namespace aiko

@@ -497,16 +497,25 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
     p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
                       overlay->patch_h, overlay->max_ops_per_frame, overlay->index,
                       overlay->index_width, overlay->index_segments, overlay->index_words,
-                      overlay->index_frame_words};
+                      overlay->index_frame_words, overlay->tiles, overlay->n_tiles, overlay->tile_words,
+                      overlay->tile_height};
   }
   p.items = n_frames * dst_h;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)src_row_stride | (uintptr_t)src_frame_stride |
                          (uintptr_t)((int64_t)src_w * channels)) & 15) == 0;
   if (channels == 3 && aligned && p.scale_x <= 4.0) {
+    // Default: resize (+ swap) with the row pipeline, then the draw list in a second, tile-parallel
+    // kernel while the output frames are still in L2 -- measured faster than replaying the list
+    // inside the row loop (AIKO_B200_OVERLAY_FUSED=1 selects that single-kernel variant).
+    const bool two_pass = p.has_overlay && !env_int("AIKO_B200_OVERLAY_FUSED", 0);
+    ResizeParams q = p;
+    if (two_pass) q.has_overlay = 0;
     bool done = false;
-    const int rc = launch_staged3(p, st, &done);
-    if (rc != AIKO_B200_OK || done) return rc;
+    const int rc = launch_staged3(q, st, &done);
+    if (rc != AIKO_B200_OK) return rc;
+    if (done) return two_pass ? launch_overlay_tiles(dst, n_frames, dst_h, dst_w, dst_row_stride, dst_frame_stride, p.ov, st)
+                              : AIKO_B200_OK;
   }
   switch (channels) {
     case 1: return launch_generic<1>(p, st);

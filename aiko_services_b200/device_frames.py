@@ -11,12 +11,17 @@ A ``DeviceBatch`` is lazy: ImageResize, ImageOverlay and colour conversion only 
 recipe.  When the pixels are needed, consecutive steps that the library can run as one kernel
 (bilinear resize -> overlay -> channel swap) are launched as one.
 """
+from collections import OrderedDict
+
 import numpy as np
 import torch
 
 from . import ops
 from .overlay_plan import build_ops
 from .text_atlas import TextAtlas
+
+
+_overlay_cache = OrderedDict()       # (overlay content, size, layout, frames, device) -> DeviceOverlay
 
 
 class DeviceBatch:
@@ -65,11 +70,29 @@ class DeviceBatch:
     def _overlay(self, overlays, width, height, gray, swapped, n):
         atlas = TextAtlas.shared()
         layout = "bgr" if (gray or swapped) else "rgb"
-        if isinstance(overlays, dict):
+        # Detections change from frame to frame but often repeat (a static scene, a benchmark): keep
+        # the most recent draw lists on the device, keyed by content.
+        shared = isinstance(overlays, dict)
+        key = (repr(overlays), width, height, layout, n, str(self.device), atlas.version)
+        cached = _overlay_cache.get(key)
+        if cached is not None:
+            _overlay_cache.move_to_end(key)
+            return cached
+        if shared:
             per_frame = [build_ops(overlays, width, height, layout, atlas)] * n
         else:
-            per_frame = [build_ops(o, width, height, layout, atlas) for o in overlays]
-        return ops.DeviceOverlay.from_host(per_frame, self.device, atlas.device(self.device), width=width)
+            built = {}
+            per_frame = []
+            for o in overlays:          # streams that carry the same overlay share one list object
+                k = repr(o)
+                if k not in built:
+                    built[k] = build_ops(o, width, height, layout, atlas)
+                per_frame.append(built[k])
+        dev = ops.DeviceOverlay.from_host(per_frame, self.device, atlas.device(self.device), width=width, height=height)
+        _overlay_cache[key] = dev
+        if len(_overlay_cache) > 64:
+            _overlay_cache.popitem(last=False)
+        return dev
 
     def _run(self, t, recipe):
         i = 0

@@ -6,6 +6,7 @@ mirrors the library call the reference element makes (cited in include/aiko_b200
 takes a whole batch ``uint8[N, H, W, C]`` (or ``[N, H, W]`` for grayscale) resident on the GPU.
 """
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -101,10 +102,70 @@ def build_overlay_index(ops_per_frame, width):
     return out, segments, words
 
 
+TILE_W, TILE_H = 64, 16
+
+
+FRAMES_PER_TILE_CTA = 1      # grouping frames that share a list was measured slower (fewer, longer CTAs)
+
+
+def build_tile_list(ops_per_frame, width, height):
+    """Tiles (64 x 16 pixels) touched by the draw lists, with the ops that can touch them (layout:
+    include/aiko_b200.h).  Consecutive frames that share one list object -- the usual case: the
+    reference applies one ``overlay`` to every image of a call -- are grouped, up to
+    FRAMES_PER_TILE_CTA per record.  -> (uint32 ndarray [n_records, 4 + words], words) or None."""
+    most = max((len(o) for o in ops_per_frame), default=0)
+    if most == 0 or most > INDEX_MAX_OPS:
+        return None
+    words = (most + 31) // 32
+    tiles_x, tiles_y = (width + TILE_W - 1) // TILE_W, (height + TILE_H - 1) // TILE_H
+    cache, records = {}, []
+    first_ops = np.concatenate([[0], np.cumsum([len(o) for o in ops_per_frame])])
+    f = 0
+    while f < len(ops_per_frame):
+        frame_ops = ops_per_frame[f]
+        run = 1
+        while f + run < len(ops_per_frame) and ops_per_frame[f + run] is frame_ops:
+            run += 1
+        key = id(frame_ops)
+        if key not in cache:
+            masks = np.zeros((tiles_y, tiles_x, words), np.uint32)
+            for b, o in enumerate(frame_ops):
+                grow = 1 if o.kind == 0 else 0
+                bx0, by0, bx1, by1 = o.x0 - grow, o.y0 - grow, o.x1 + grow, o.y1 + grow
+                if bx1 < 0 or by1 < 0 or bx0 >= width or by0 >= height:
+                    continue
+                tx0, tx1 = max(bx0, 0) // TILE_W, min(bx1, width - 1) // TILE_W
+                ty0, ty1 = max(by0, 0) // TILE_H, min(by1, height - 1) // TILE_H
+                sel = np.ones((ty1 - ty0 + 1, tx1 - tx0 + 1), bool)
+                if o.kind == 0:      # a rectangle only touches tiles its 3-pixel outline crosses
+                    ix0, iy0, ix1, iy1 = o.x0 + 2, o.y0 + 2, o.x1 - 2, o.y1 - 2       # untouched interior
+                    txs, tys = np.arange(tx0, tx1 + 1) * TILE_W, np.arange(ty0, ty1 + 1) * TILE_H
+                    in_x = (txs >= ix0) & (txs + TILE_W - 1 <= ix1)
+                    in_y = (tys >= iy0) & (tys + TILE_H - 1 <= iy1)
+                    sel = ~(in_y[:, None] & in_x[None, :])
+                w, bit = divmod(b, 32)
+                masks[ty0:ty1 + 1, tx0:tx1 + 1, w] |= (sel.astype(np.uint32) << np.uint32(bit))
+            ty, tx = np.nonzero(masks.any(axis=2))
+            rec = np.zeros((len(ty), 4 + words), np.uint32)
+            rec[:, 2] = tx.astype(np.uint32) | (ty.astype(np.uint32) << 16)
+            rec[:, 4:] = masks[ty, tx]
+            cache[key] = rec
+        for g0 in range(f, f + run, FRAMES_PER_TILE_CTA):
+            rec = cache[key].copy()
+            rec[:, 0] = g0
+            rec[:, 1] = min(FRAMES_PER_TILE_CTA, f + run - g0)
+            rec[:, 3] = first_ops[g0]
+            records.append(rec)
+        f += run
+    table = np.concatenate(records) if records else np.zeros((0, 4 + words), np.uint32)
+    return table, words
+
+
 class DeviceOverlay:
     """A draw list resident on the GPU (see aiko_b200_overlay in include/aiko_b200.h)."""
 
-    def __init__(self, ops, op_offsets, atlas=None, max_ops_per_frame=0, index=None, index_width=0):
+    def __init__(self, ops, op_offsets, atlas=None, max_ops_per_frame=0, index=None, index_width=0, tiles=None,
+                 tile_height=0):
         self.ops, self.op_offsets, self.atlas = ops, op_offsets, atlas
         self.struct = Overlay()
         self.struct.max_ops_per_frame = int(max_ops_per_frame)
@@ -115,6 +176,14 @@ class DeviceOverlay:
             self.struct.index = table.data_ptr()
             self.struct.index_width, self.struct.index_segments = int(index_width), int(segments)
             self.struct.index_words, self.struct.index_frame_words = int(words), int(table.shape[1])
+        self.tiles = None
+        if tiles is not None and index_width:
+            table, words = tiles
+            self.tiles = table
+            self.struct.index_width = int(index_width)
+            self.struct.tiles = table.data_ptr()
+            self.struct.n_tiles, self.struct.tile_words = int(table.shape[0]), int(words)
+            self.struct.tile_height = int(tile_height)
         self.struct.ops = ops.data_ptr()
         self.struct.op_offsets = op_offsets.data_ptr()
         if atlas is not None:
@@ -136,18 +205,23 @@ class DeviceOverlay:
         return raw, offsets
 
     @staticmethod
-    def from_host(ops_per_frame, device, atlas=None, width=None):
-        """ops_per_frame: list (one entry per frame) of lists of OverlayOp; ``width``: frame width
-        the ops were built for (enables the spatial index the fused resize kernel uses)."""
+    def from_host(ops_per_frame, device, atlas=None, width=None, height=None):
+        """ops_per_frame: list (one entry per frame) of lists of OverlayOp; ``width`` / ``height``:
+        frame size the ops were built for (enables the spatial indices the kernels use)."""
         raw, offsets = DeviceOverlay.pack_host(ops_per_frame)
         most = max((len(o) for o in ops_per_frame), default=0)
         index = None
-        if width:
+        if width and os.environ.get("AIKO_B200_OVERLAY_FUSED"):      # only the single-kernel variant uses it
             built = build_overlay_index(ops_per_frame, width)
             if built is not None:
                 index = (torch.from_numpy(built[0]).to(device), built[1], built[2])
+        tiles = None
+        if width and height:
+            built = build_tile_list(ops_per_frame, width, height)
+            if built is not None and len(built[0]):
+                tiles = (torch.from_numpy(built[0]).to(device), built[1])
         return DeviceOverlay(torch.from_numpy(raw).to(device), torch.from_numpy(offsets).to(device), atlas, most,
-                             index, width or 0)
+                             index, width or 0, tiles, height or 0)
 
     def pointer(self):
         return ctypes.pointer(self.struct)

@@ -86,6 +86,13 @@ typedef struct aiko_b200_overlay {
    * Built by aiko_services_b200.ops.build_overlay_index (numpy). */
   const uint32_t* index;
   int32_t index_width, index_segments, index_words, index_frame_words;
+  /* Optional list of the 64 x 16 pixel tiles (of frames index_width x tile_height pixels) that
+   * the draw lists touch: n_tiles records of (4 + tile_words) uint32:
+   *   first_frame, frame_count, tile_x | tile_y << 16, op_offsets[first_frame], then tile_words
+   *   words: bit b of word w = op 32*w + b of the list can touch the tile.  frame_count > 1 only
+   *   for consecutive frames whose draw lists are identical.  NULL = not provided. */
+  const uint32_t* tiles;
+  int32_t n_tiles, tile_words, tile_height;
 } aiko_b200_overlay;
 
 /* ---------------------------------------------------------------------- */

@@ -203,7 +203,7 @@ def test_crop_vs_numpy(cuda):
 # ---------------------------------------------------------------- overlay (a-3)
 def device_overlay(overlays, w, h, layout, atlas, cuda):
     per_frame = [build_ops(o, w, h, layout, atlas) for o in overlays]
-    return ops.DeviceOverlay.from_host(per_frame, cuda, atlas.device(cuda), width=w)
+    return ops.DeviceOverlay.from_host(per_frame, cuda, atlas.device(cuda), width=w, height=h)
 
 
 @pytest.mark.parametrize("case", cases.OVERLAY, ids=lambda c: c[0])
