@@ -266,3 +266,41 @@ def test_fused_equals_unfused_random(cuda, atlas):
         assert torch.equal(fused, unfused)
         for k in range(3):
             np.testing.assert_array_equal(host(fused)[k], overlay_cpu(O.resize_linear(frames[k], W, H), overlays[k], atlas))
+
+
+def test_fused_resize_with_long_draw_list_uses_device_side_culling(cuda, atlas):
+    """More ops than the host-built tile list carries (128): the tile kernel culls by itself."""
+    rng = np.random.default_rng(206)
+    H, W = 120, 160
+    frames = np.stack([cases.frame(500 + k, 270, 480, 3) for k in range(2)])
+    overlays = [random_overlay(rng, W, H, n=60) for _ in range(2)]
+    ov = device_overlay(overlays, W, H, "rgb", atlas, cuda)
+    assert ov.tiles is None and int(ov.op_offsets[-1]) > 256
+    out = host(ops.resize_linear(dev(frames, cuda), W, H, overlay=ov))
+    for k in range(2):
+        np.testing.assert_array_equal(out[k], overlay_cpu(O.resize_linear(frames[k], W, H), overlays[k], atlas))
+
+
+def test_overlay_variants_agree(cuda, atlas, monkeypatch):
+    """Two-launch (default) and single-kernel (AIKO_B200_OVERLAY_FUSED=1) overlays are bit-identical."""
+    frames = dev(np.stack([cases.frame(2000 + i, 1080, 1920, 3) for i in range(3)]), cuda)
+    two_pass = ops.resize_linear(frames, 640, 480, swap_rb=True,
+                                 overlay=device_overlay([cases.OVERLAY_4] * 3, 640, 480, "bgr", atlas, cuda))
+    monkeypatch.setenv("AIKO_B200_OVERLAY_FUSED", "1")
+    fused = ops.resize_linear(frames, 640, 480, swap_rb=True,
+                              overlay=device_overlay([cases.OVERLAY_4] * 3, 640, 480, "bgr", atlas, cuda))
+    assert torch.equal(two_pass, fused)
+
+
+def test_resize_rgba_swap_and_widths_not_multiple_of_four(cuda, atlas):
+    rgba = np.stack([cases.frame(70, 45, 64, 4)])
+    out = host(ops.resize_linear(dev(rgba, cuda), 31, 17, swap_rb=True))[0]
+    ref = O.resize_linear(rgba[0], 31, 17)
+    np.testing.assert_array_equal(out, ref[..., [2, 1, 0, 3]])
+    rng = np.random.default_rng(207)
+    for W in (61, 62, 63, 130):
+        frames = np.stack([cases.frame(71 + W, 96, 128, 3)])
+        overlay = random_overlay(rng, W, 50)
+        ov = device_overlay([overlay], W, 50, "rgb", atlas, cuda)
+        out = host(ops.resize_linear(dev(frames, cuda), W, 50, overlay=ov))[0]
+        np.testing.assert_array_equal(out, overlay_cpu(O.resize_linear(frames[0], W, 50), overlay, atlas))
