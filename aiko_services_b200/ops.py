@@ -181,7 +181,7 @@ class DeviceOverlay:
             table, words = tiles
             self.tiles = table
             self.struct.index_width = int(index_width)
-            self.struct.tiles = table.data_ptr()
+            self.struct.tiles = table.data_ptr() if table.shape[0] else self.ops.data_ptr()   # non-null marks "listed"
             self.struct.n_tiles, self.struct.tile_words = int(table.shape[0]), int(words)
             self.struct.tile_height = int(tile_height)
         self.struct.ops = ops.data_ptr()
@@ -218,7 +218,9 @@ class DeviceOverlay:
         tiles = None
         if width and height:
             built = build_tile_list(ops_per_frame, width, height)
-            if built is not None and len(built[0]):
+            if most == 0:                       # nothing to draw at all: an empty list, so no kernel is launched
+                tiles = (torch.zeros((1, 5), dtype=torch.int32, device=device)[:0], 1)
+            elif built is not None and len(built[0]):
                 tiles = (torch.from_numpy(built[0]).to(device), built[1])
         return DeviceOverlay(torch.from_numpy(raw).to(device), torch.from_numpy(offsets).to(device), atlas, most,
                              index, width or 0, tiles, height or 0)
