@@ -36,6 +36,7 @@ struct AudioParams {
   int* top_count;
   int gate_lo, gate_hi;   // bins k (folded: min(i, n - i)) passing the frequency gate
   float amp_min, amp_max, hz_per_bin;
+  int tw_in_smem;
 };
 
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
@@ -84,26 +85,64 @@ __device__ __forceinline__ void dft_small(float2* a) {
 }
 
 // One Stockham pass: length-n sub-transforms interleaved with stride s; reads x, writes y.
+// b = p * s + q enumerates the n / R * s butterflies; p = floor(b / s) comes from a float divide
+// that is exact here ((b + 0.5) / s is never within rounding of an integer for b, s < 2^20).
+// Each thread runs two butterflies at a time so their shared-memory latencies overlap.
+// Complex points live in shared memory with one pad element after every 16, so the strided
+// writes of the early Stockham passes (stride 4 and 16 elements) spread over all banks.
+__device__ __forceinline__ int pidx(int i) { return i + (i >> 4); }
+__host__ __device__ inline size_t padded_points(size_t n) { return n + (n >> 4) + 1; }
+
+template <int R>
+__device__ __forceinline__ void butterfly_load(const float2* __restrict__ x, int b, int m, int s, float inv_s,
+                                               float2* a, int* p_out, int* q_out) {
+  const int p = __float2int_rd(((float)b + 0.5f) * inv_s), q = b - p * s;
+#pragma unroll
+  for (int k = 0; k < R; k++) a[k] = x[pidx(q + s * (p + m * k))];
+  *p_out = p;
+  *q_out = q;
+}
+template <int R>
+__device__ __forceinline__ void butterfly_store(float2* __restrict__ y, float2* a, int p, int q, int s,
+                                                const float2* __restrict__ tw, int tw_step) {
+  dft_small<R>(a);
+  y[pidx(q + s * (R * p))] = a[0];
+#pragma unroll
+  for (int j = 1; j < R; j++) y[pidx(q + s * (R * p + j))] = cmul(a[j], tw[p * j * tw_step]);
+}
 template <int R>
 __device__ __forceinline__ void stockham_pass(const float2* __restrict__ x, float2* __restrict__ y, int n, int s,
                                               const float2* __restrict__ tw, int half) {
   const int m = n / R, total = m * s, tw_step = half / n;
-  for (int b = threadIdx.x; b < total; b += kAudioThreads) {
-    const int p = b / s, q = b - p * s;
-    float2 a[R];
-#pragma unroll
-    for (int k = 0; k < R; k++) a[k] = x[q + s * (p + m * k)];
-    dft_small<R>(a);
-    y[q + s * (R * p)] = a[0];
-#pragma unroll
-    for (int j = 1; j < R; j++) y[q + s * (R * p + j)] = cmul(a[j], __ldg(tw + p * j * tw_step));
+  const float inv_s = 1.0f / (float)s;
+  int b = threadIdx.x;
+  for (; b + kAudioThreads < total; b += 2 * kAudioThreads) {
+    float2 a0[R], a1[R];
+    int p0, q0, p1, q1;
+    butterfly_load<R>(x, b, m, s, inv_s, a0, &p0, &q0);
+    butterfly_load<R>(x, b + kAudioThreads, m, s, inv_s, a1, &p1, &q1);
+    butterfly_store<R>(y, a0, p0, q0, s, tw, tw_step);
+    butterfly_store<R>(y, a1, p1, q1, s, tw, tw_step);
+  }
+  if (b < total) {
+    float2 a0[R];
+    int p0, q0;
+    butterfly_load<R>(x, b, m, s, inv_s, a0, &p0, &q0);
+    butterfly_store<R>(y, a0, p0, q0, s, tw, tw_step);
   }
 }
 
 __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const AudioParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
   float2* buf0 = reinterpret_cast<float2*>(smem);
-  float2* buf1 = buf0 + p.half;
+  float2* buf1 = buf0 + padded_points(p.half);
+  const float2* tw = p.tw_half;
+  if (p.tw_in_smem) {           // the pass twiddles next to the data: one copy per CTA, reused for every window
+    float2* tws = buf1 + padded_points(p.half);
+    for (int i = threadIdx.x; i < p.half; i += kAudioThreads) tws[i] = __ldg(p.tw_half + i);
+    tw = tws;
+    __syncthreads();
+  }
   __shared__ int s_count, s_threshold_bin;
   __shared__ int hist[kHistBins];
   const int half = p.half, n = p.n;
@@ -114,11 +153,11 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
       const short2* in = reinterpret_cast<const short2*>(static_cast<const int16_t*>(p.audio) + (size_t)w * n);
       for (int i = threadIdx.x; i < half; i += kAudioThreads) {
         const short2 v = __ldg(in + i);
-        buf0[i] = make_float2((float)v.x, (float)v.y);
+        buf0[pidx(i)] = make_float2((float)v.x, (float)v.y);
       }
     } else {
       const float2* in = reinterpret_cast<const float2*>(static_cast<const float*>(p.audio) + (size_t)w * n);
-      for (int i = threadIdx.x; i < half; i += kAudioThreads) buf0[i] = __ldg(in + i);
+      for (int i = threadIdx.x; i < half; i += kAudioThreads) buf0[pidx(i)] = __ldg(in + i);
     }
     __syncthreads();
     // ---- half-length complex FFT
@@ -126,10 +165,10 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
     int len = half, stride = 1;
     for (int st = 0; st < p.n_stages; st++) {
       const int r = p.radix[st];
-      if (r == 4) stockham_pass<4>(x, y, len, stride, p.tw_half, half);
-      else if (r == 5) stockham_pass<5>(x, y, len, stride, p.tw_half, half);
-      else if (r == 3) stockham_pass<3>(x, y, len, stride, p.tw_half, half);
-      else stockham_pass<2>(x, y, len, stride, p.tw_half, half);
+      if (r == 4) stockham_pass<4>(x, y, len, stride, tw, half);
+      else if (r == 5) stockham_pass<5>(x, y, len, stride, tw, half);
+      else if (r == 3) stockham_pass<3>(x, y, len, stride, tw, half);
+      else stockham_pass<2>(x, y, len, stride, tw, half);
       len /= r;
       stride *= r;
       float2* t = x; x = y; y = t;
@@ -139,8 +178,8 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
     float* amp = reinterpret_cast<float*>(y);          // half + 1 magnitudes, in the idle buffer
     float* out = p.amplitudes + (size_t)w * n;
     for (int k = threadIdx.x; k <= half; k += kAudioThreads) {
-      const float2 zk = x[k == half ? 0 : k];
-      const float2 zr = x[k == 0 ? 0 : half - k];
+      const float2 zk = x[pidx(k == half ? 0 : k)];
+      const float2 zr = x[pidx(k == 0 ? 0 : half - k)];
       const float2 zc = make_float2(zr.x, -zr.y);
       const float2 e = cscale(cadd(zk, zc), 0.5f);
       const float2 o = cscale(mul_mi(csub(zk, zc)), 0.5f);
@@ -239,19 +278,30 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
       while (padded < count) padded <<= 1;
       for (int i = count + threadIdx.x; i < padded; i += kAudioThreads) list[i] = 0ull;   // sorts last
       __syncthreads();
-      for (int size = 2; size <= padded; size <<= 1) {       // bitonic sort, descending
-        for (int strd = size >> 1; strd > 0; strd >>= 1) {
-          for (int i = threadIdx.x; i < padded; i += kAudioThreads) {
-            const int j = i ^ strd;
-            if (j > i) {
-              const bool desc = (i & size) == 0;
-              const unsigned long long a = list[i], b = list[j];
-              if ((a < b) == desc) { list[i] = b; list[j] = a; }
+      // Bitonic sort, descending.  Only the warps that hold elements take part; exchanges with
+      // a stride below 32 stay inside a warp (__syncwarp), wider ones use a named barrier over
+      // the participating threads.
+      const int sorters = min(max(padded, 32), kAudioThreads);
+      if ((int)threadIdx.x < sorters) {
+        for (int size = 2; size <= padded; size <<= 1) {
+          for (int strd = size >> 1; strd > 0; strd >>= 1) {
+            for (int i = threadIdx.x; i < padded; i += sorters) {
+              const int j = i ^ strd;
+              if (j > i) {
+                const bool desc = (i & size) == 0;
+                const unsigned long long a = list[i], b = list[j];
+                if ((a < b) == desc) { list[i] = b; list[j] = a; }
+              }
             }
+            // the next step crosses warps if its stride is >= 32
+            const int next = (strd > 1) ? (strd >> 1) : size;
+            const bool more = (strd > 1) || (size < padded);
+            if (more && (strd >= 32 || next >= 32)) asm volatile("bar.sync 1, %0;" ::"r"(sorters) : "memory");
+            else __syncwarp();
           }
-          __syncthreads();
         }
       }
+      __syncthreads();
       const int take = min(count, kTopK);
       for (int i = threadIdx.x; i < kTopK; i += kAudioThreads) {
         float a = 0.f, f = 0.f;
@@ -360,7 +410,10 @@ extern "C" int aiko_b200_audio_chain(const void* audio, int dtype, int n_windows
   p.amp_min = 0.1f;   // AF_AMPLITUDE_MINIMUM / MAXIMUM, audio_io.py:202-203
   p.amp_max = 12.0f;
   p.hz_per_bin = (float)(sample_rate / (double)n_samples);
-  const size_t smem = (size_t)2 * p.half * sizeof(float2);
+  size_t smem = (size_t)2 * padded_points(p.half) * sizeof(float2);
+  // static shared memory: 16 KB histogram + a few words; keep the twiddles on chip when there is room
+  p.tw_in_smem = (smem + (size_t)p.half * sizeof(float2) + 17 * 1024 <= (size_t)device_max_smem_optin()) ? 1 : 0;
+  if (p.tw_in_smem) smem += (size_t)p.half * sizeof(float2);
   AIKO_CUDA(cudaFuncSetAttribute(audio_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, audio_chain_kernel, kAudioThreads, smem));

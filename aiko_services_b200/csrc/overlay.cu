@@ -174,7 +174,11 @@ __global__ void __launch_bounds__(kThreads, 6) overlay_tiles_kernel(const TilePa
   const bool words = mine && mlo + 3 < p.w && ((reinterpret_cast<uintptr_t>(pix) & 3) == 0) &&
                      (nframes == 1 || (p.frame_stride & 3) == 0);
   Pixels4 px{0, 0, 0};
-  bool loaded = false, dirty = false, waited = false;
+  bool loaded = false, dirty = false;
+  if (p.listed && mine) {       // start the (L2) pixel fetch now; it overlaps the op and atlas look-ups
+    px = load_pixels(pix, words, mhi - mlo + 1);
+    loaded = true;
+  }
   const int psize = p.ov.patch_w * p.ov.patch_h;
 
   for (int base = 0; base < nops; base += kThreads) {
@@ -212,13 +216,6 @@ __global__ void __launch_bounds__(kThreads, 6) overlay_tiles_kernel(const TilePa
       const int4* src = reinterpret_cast<const int4*>(ops + base + my_word * 32 + (__ffs(bits) - 1));
       sops[2 * threadIdx.x] = __ldg(src);
       sops[2 * threadIdx.x + 1] = __ldg(src + 1);
-    }
-    if (!waited) {
-      waited = true;
-      if (p.listed && mine) {   // start the (L2) pixel fetch; it overlaps the atlas look-ups
-        px = load_pixels(pix, words, mhi - mlo + 1);
-        loaded = true;
-      }
     }
     __syncthreads();
     if (mine && nframes == 1) {
