@@ -37,8 +37,8 @@ class Overlay(ctypes.Structure):
                 ("n_patches", ctypes.c_int32), ("max_ops_per_frame", ctypes.c_int32),
                 ("index", ctypes.c_void_p), ("index_width", ctypes.c_int32), ("index_segments", ctypes.c_int32),
                 ("index_words", ctypes.c_int32), ("index_frame_words", ctypes.c_int32),
-                ("tiles", ctypes.c_void_p), ("n_tiles", ctypes.c_int32), ("tile_words", ctypes.c_int32),
-                ("tile_height", ctypes.c_int32)]
+                ("index_height", ctypes.c_int32), ("group_records", ctypes.c_void_p),
+                ("group_ctas", ctypes.c_void_p), ("n_group_ctas", ctypes.c_int32), ("group_words", ctypes.c_int32)]
 
 
 _vp, _i, _i64, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t

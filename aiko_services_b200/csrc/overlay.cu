@@ -63,7 +63,6 @@ struct TileParams {
   int n, h, w;
   long long row_stride, frame_stride;
   int tiles_x, tiles_y;
-  int listed;            // 1: one CTA per record of ov.tiles; 0: one CTA per tile of every frame
   OverlayDev ov;
 };
 
@@ -142,26 +141,12 @@ __device__ __forceinline__ bool apply_op_regs(const int4 lo4, const int4 hi4, co
 __global__ void __launch_bounds__(kThreads, 6) overlay_tiles_kernel(const TileParams p) {
   __shared__ uint32_t hitmask[kThreads / 32];
   __shared__ int4 sops[kThreads * 2];         // staged op records (32 bytes each), one batch
-  int frame, tx, ty, ob, nops, nframes = 1;
-  const uint32_t* record = nullptr;
-  if (p.listed) {
-    record = p.ov.tiles + (size_t)blockIdx.x * (4 + p.ov.tile_words);
-    const uint32_t rx = __ldg(record), ry = __ldg(record + 1), rz = __ldg(record + 2), rw = __ldg(record + 3);
-    frame = (int)rx;
-    nframes = (int)ry;                        // consecutive frames with this same draw list
-    tx = (int)(rz & 0xffff);
-    ty = (int)(rz >> 16);
-    ob = (int)rw;
-    nops = p.ov.tile_words * 32;              // bits beyond the frame's list are zero
-  } else {
-    const int tiles_per_frame = p.tiles_x * p.tiles_y;
-    frame = blockIdx.x / tiles_per_frame;
-    const int t = blockIdx.x - frame * tiles_per_frame;
-    ty = t / p.tiles_x;
-    tx = t - ty * p.tiles_x;
-    ob = __ldg(p.ov.op_offsets + frame);
-    nops = __ldg(p.ov.op_offsets + frame + 1) - ob;
-  }
+  const int tiles_per_frame = p.tiles_x * p.tiles_y;
+  const int frame = blockIdx.x / tiles_per_frame;
+  const int t = blockIdx.x - frame * tiles_per_frame;
+  const int ty = t / p.tiles_x, tx = t - ty * p.tiles_x;
+  const int ob = __ldg(p.ov.op_offsets + frame);
+  const int nops = __ldg(p.ov.op_offsets + frame + 1) - ob;
   const int tile_x0 = tx * kTileW, tile_y0 = ty * kTileH;
   const int tile_x1 = min(tile_x0 + kTileW, p.w) - 1, tile_y1 = min(tile_y0 + kTileH, p.h) - 1;
   const aiko_b200_overlay_op* ops = p.ov.ops + ob;
@@ -171,25 +156,14 @@ __global__ void __launch_bounds__(kThreads, 6) overlay_tiles_kernel(const TilePa
   const int mlo = tile_x0 + (threadIdx.x & 15) * 4, mhi = min(mlo + 3, p.w - 1);
   const bool mine = y <= tile_y1 && mlo <= tile_x1;
   uint8_t* pix = p.frames + (long long)frame * p.frame_stride + (long long)y * p.row_stride + (long long)mlo * 3;
-  const bool words = mine && mlo + 3 < p.w && ((reinterpret_cast<uintptr_t>(pix) & 3) == 0) &&
-                     (nframes == 1 || (p.frame_stride & 3) == 0);
+  const bool words = mine && mlo + 3 < p.w && ((reinterpret_cast<uintptr_t>(pix) & 3) == 0);
   Pixels4 px{0, 0, 0};
   bool loaded = false, dirty = false;
-  if (p.listed && mine) {       // start the (L2) pixel fetch now; it overlaps the op and atlas look-ups
-    px = load_pixels(pix, words, mhi - mlo + 1);
-    loaded = true;
-  }
   const int psize = p.ov.patch_w * p.ov.patch_h;
 
   for (int base = 0; base < nops; base += kThreads) {
     // ---- which ops of this batch touch the tile
-    if (p.listed) {
-      if (threadIdx.x < kThreads / 32) {
-        const int wd = base / 32 + threadIdx.x;
-        hitmask[threadIdx.x] = (wd < p.ov.tile_words) ? __ldg(record + 4 + wd) : 0u;
-      }
-      __syncthreads();
-    } else {
+    {
       const int i = base + threadIdx.x;
       bool hit = false;
       if (i < nops) {
@@ -218,7 +192,7 @@ __global__ void __launch_bounds__(kThreads, 6) overlay_tiles_kernel(const TilePa
       sops[2 * threadIdx.x + 1] = __ldg(src + 1);
     }
     __syncthreads();
-    if (mine && nframes == 1) {
+    if (mine) {
       for (int i = 0; i < total; i++) {
         const int4 lo4 = sops[2 * i], hi4 = sops[2 * i + 1];
         const int grow = (lo4.x == AIKO_B200_OP_RECT) ? 1 : 0;
@@ -226,41 +200,62 @@ __global__ void __launch_bounds__(kThreads, 6) overlay_tiles_kernel(const TilePa
         if (!loaded) { px = load_pixels(pix, words, mhi - mlo + 1); loaded = true; }
         dirty |= apply_op_regs(lo4, hi4, p.ov, psize, y, mlo, mhi, px);
       }
-    } else if (mine) {
-      // several frames share this list (listed mode, at most 256 ops: a single batch): the ops stay
-      // staged, the glyph tables warm up in L1, and the next frame's pixels are fetched early
-      int first_hit = total;
-      for (int i = 0; i < total && first_hit == total; i++) {
-        const int4 lo4 = sops[2 * i], hi4 = sops[2 * i + 1];
-        const int grow = (lo4.x == AIKO_B200_OP_RECT) ? 1 : 0;
-        if (!(y < lo4.z - grow || y > hi4.x + grow || mhi < lo4.y - grow || mlo > lo4.w + grow)) first_hit = i;
-      }
-      if (first_hit < total) {                    // some op can touch this thread's pixels
-        Pixels4 cur = px;                         // frame `frame`, already in flight
-        for (int f = 0; f < nframes; f++) {
-          uint8_t* fp = pix + (long long)f * p.frame_stride;
-          Pixels4 nxt{0, 0, 0};
-          if (f + 1 < nframes) nxt = load_pixels(fp + p.frame_stride, words, mhi - mlo + 1);
-          bool changed = false;
-          for (int i = first_hit; i < total; i++) {
-            const int4 lo4 = sops[2 * i], hi4 = sops[2 * i + 1];
-            changed |= apply_op_regs(lo4, hi4, p.ov, psize, y, mlo, mhi, cur);
-          }
-          if (changed) {
-            if (words) {
-              reinterpret_cast<uint32_t*>(fp)[0] = cur.w0;
-              reinterpret_cast<uint32_t*>(fp)[1] = cur.w1;
-              reinterpret_cast<uint32_t*>(fp)[2] = cur.w2;
-            } else {
-              const uint32_t v[3] = {cur.w0, cur.w1, cur.w2};
-              for (int q = 0; q < (mhi - mlo + 1) * 3; q++) fp[q] = (uint8_t)(v[q >> 2] >> (8 * (q & 3)));
-            }
-          }
-          cur = nxt;
-        }
-      }
     }
     __syncthreads();                              // hitmask / sops are rewritten by the next batch
+  }
+  if (dirty) {
+    if (words) {
+      reinterpret_cast<uint32_t*>(pix)[0] = px.w0;
+      reinterpret_cast<uint32_t*>(pix)[1] = px.w1;
+      reinterpret_cast<uint32_t*>(pix)[2] = px.w2;
+    } else {
+      const uint32_t v[3] = {px.w0, px.w1, px.w2};
+      for (int q = 0; q < (mhi - mlo + 1) * 3; q++) pix[q] = (uint8_t)(v[q >> 2] >> (8 * (q & 3)));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Overlay by touched groups: the host lists, per draw list, the 4-pixel groups the list can touch
+// with the ops per group (aiko_b200_overlay.group_records / group_ctas).  One thread per
+// (frame, touched group): it loads its 12 bytes, applies its ops in list order from the copy of the
+// list staged in shared memory, and stores them.  No thread idles, nothing is culled on the
+// device, and the dependent chain is record -> {pixels, glyph ids} -> transfer table -> store.
+constexpr int kGroupOps = 128;             // the host only builds group lists for lists up to this long
+
+__global__ void __launch_bounds__(kThreads) overlay_groups_kernel(const TileParams p) {
+  __shared__ int4 sops[kGroupOps * 2];
+  const uint4 cta = __ldg(reinterpret_cast<const uint4*>(p.ov.group_ctas) + blockIdx.x);
+  const int first = (int)cta.x, count = (int)cta.y, frame = (int)cta.z;
+  const int ob = (int)(cta.w & 0xffffffu), nops = (int)(cta.w >> 24);
+  const int rec_words = 1 + p.ov.group_words;
+  // this thread's group record (issued before the list is staged, so both fetches overlap)
+  uint32_t yx = 0, m[4] = {0, 0, 0, 0};
+  if ((int)threadIdx.x < count) {
+    const uint32_t* rec = p.ov.group_records + (size_t)(first + threadIdx.x) * rec_words;
+    yx = __ldg(rec);
+    for (int w = 0; w < p.ov.group_words && w < 4; w++) m[w] = __ldg(rec + 1 + w);
+  }
+  const int4* src = reinterpret_cast<const int4*>(p.ov.ops + ob);
+  for (int i = threadIdx.x; i < nops * 2; i += kThreads) sops[i] = __ldg(src + i);
+  const int y = (int)(yx >> 16), mlo = (int)(yx & 0xffff) * 4, mhi = min(mlo + 3, p.w - 1);
+  uint8_t* pix = p.frames + (long long)frame * p.frame_stride + (long long)y * p.row_stride + (long long)mlo * 3;
+  const bool active = (int)threadIdx.x < count;
+  const bool words = active && mlo + 3 < p.w && ((reinterpret_cast<uintptr_t>(pix) & 3) == 0);
+  Pixels4 px{0, 0, 0};
+  if (active) px = load_pixels(pix, words, mhi - mlo + 1);
+  __syncthreads();
+  if (!active) return;
+  const int psize = p.ov.patch_w * p.ov.patch_h;
+  bool dirty = false;
+#pragma unroll 1
+  for (int w = 0; w < p.ov.group_words && w < 4; w++) {
+    uint32_t bits = m[w];
+    while (bits) {
+      const int b = __ffs(bits) - 1;
+      bits &= bits - 1;
+      dirty |= apply_op_regs(sops[2 * (w * 32 + b)], sops[2 * (w * 32 + b) + 1], p.ov, psize, y, mlo, mhi, px);
+    }
   }
   if (dirty) {
     if (words) {
@@ -282,9 +277,14 @@ int launch_overlay_tiles(uint8_t* frames, int n, int h, int w, long long row_str
   p.tiles_x = (w + kTileW - 1) / kTileW;
   p.tiles_y = (h + kTileH - 1) / kTileH;
   p.ov = ov;
-  p.listed = (ov.tiles != nullptr && ov.index_width == w && ov.tile_height == h && ov.tile_words > 0) ? 1 : 0;
-  if (p.listed && ov.n_tiles == 0) return AIKO_B200_OK;
-  const long long grid = p.listed ? (long long)ov.n_tiles : (long long)n * p.tiles_x * p.tiles_y;
+  const bool grouped = ov.group_records != nullptr && ov.group_ctas != nullptr && ov.index_width == w &&
+                       ov.index_height == h && ov.group_words >= 1 && ov.group_words <= 4;
+  if (grouped) {
+    if (ov.n_group_ctas == 0) return AIKO_B200_OK;       // nothing is drawn
+    overlay_groups_kernel<<<(unsigned)ov.n_group_ctas, kThreads, 0, stream>>>(p);
+    return cuda_status(cudaGetLastError(), "overlay_groups launch");
+  }
+  const long long grid = (long long)n * p.tiles_x * p.tiles_y;
   if (grid >= ((long long)1 << 31)) {
     set_last_error("overlay: too many tiles (%lld)", grid);
     return AIKO_B200_ERR_UNSUPPORTED;
@@ -314,8 +314,8 @@ extern "C" int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_fram
   p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
                     overlay->patch_h, overlay->max_ops_per_frame, overlay->index,
                       overlay->index_width, overlay->index_segments, overlay->index_words,
-                      overlay->index_frame_words, overlay->tiles, overlay->n_tiles, overlay->tile_words,
-                      overlay->tile_height};
+                      overlay->index_frame_words, overlay->index_height, overlay->group_records,
+                      overlay->group_ctas, overlay->n_group_ctas, overlay->group_words};
   const size_t smem = ((size_t)w * 3 + 15) & ~(size_t)15;
   AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "overlay: row of %zu bytes exceeds shared memory", smem);
   AIKO_CUDA(cudaFuncSetAttribute(overlay_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

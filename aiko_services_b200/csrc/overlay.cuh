@@ -16,8 +16,10 @@ struct OverlayDev {
   int max_ops;   // host hint: largest per-frame op count (0 = unknown)
   const uint32_t* index;   // optional spatial index (include/aiko_b200.h), or null
   int index_width, index_segments, index_words, index_frame_words;
-  const uint32_t* tiles;   // optional list of touched tiles (include/aiko_b200.h), or null
-  int n_tiles, tile_words, tile_height;
+  int index_height;
+  const uint32_t* group_records;   // optional list of touched 4-pixel groups (include/aiko_b200.h), or null
+  const uint32_t* group_ctas;
+  int n_group_ctas, group_words;
 };
 
 // cv2.rectangle(.., thickness=2) coverage, closed form.

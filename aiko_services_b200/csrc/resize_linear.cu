@@ -497,8 +497,8 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
     p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
                       overlay->patch_h, overlay->max_ops_per_frame, overlay->index,
                       overlay->index_width, overlay->index_segments, overlay->index_words,
-                      overlay->index_frame_words, overlay->tiles, overlay->n_tiles, overlay->tile_words,
-                      overlay->tile_height};
+                      overlay->index_frame_words, overlay->index_height, overlay->group_records,
+                      overlay->group_ctas, overlay->n_group_ctas, overlay->group_words};
   }
   p.items = n_frames * dst_h;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

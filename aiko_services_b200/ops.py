@@ -102,70 +102,60 @@ def build_overlay_index(ops_per_frame, width):
     return out, segments, words
 
 
-TILE_W, TILE_H = 64, 16
+GROUPS_PER_CTA = 256
 
 
-FRAMES_PER_TILE_CTA = 1      # grouping frames that share a list was measured slower (fewer, longer CTAs)
-
-
-def build_tile_list(ops_per_frame, width, height):
-    """Tiles (64 x 16 pixels) touched by the draw lists, with the ops that can touch them (layout:
-    include/aiko_b200.h).  Consecutive frames that share one list object -- the usual case: the
-    reference applies one ``overlay`` to every image of a call -- are grouped, up to
-    FRAMES_PER_TILE_CTA per record.  -> (uint32 ndarray [n_records, 4 + words], words) or None."""
+def build_group_list(ops_per_frame, width, height):
+    """The 4-pixel groups (pixels 4g .. 4g+3 of a row) that each frame's draw list can touch, with
+    a bit mask of the ops per group, arranged for one thread per (frame, touched group)
+    (layout: include/aiko_b200.h).  Frames that share one list object share their records.
+    -> (records uint32 [n_records, 1 + words], ctas uint32 [n_ctas, 4], words) or None."""
     most = max((len(o) for o in ops_per_frame), default=0)
-    if most == 0 or most > INDEX_MAX_OPS:
+    if most == 0 or most > INDEX_MAX_OPS or sum(len(o) for o in ops_per_frame) >= (1 << 24):
         return None
     words = (most + 31) // 32
-    tiles_x, tiles_y = (width + TILE_W - 1) // TILE_W, (height + TILE_H - 1) // TILE_H
-    cache, records = {}, []
+    groups = (width + 3) // 4
     first_ops = np.concatenate([[0], np.cumsum([len(o) for o in ops_per_frame])])
-    f = 0
-    while f < len(ops_per_frame):
-        frame_ops = ops_per_frame[f]
-        run = 1
-        while f + run < len(ops_per_frame) and ops_per_frame[f + run] is frame_ops:
-            run += 1
+    cache, records, ctas, n_records = {}, [], [], 0
+    for f, frame_ops in enumerate(ops_per_frame):
         key = id(frame_ops)
         if key not in cache:
-            masks = np.zeros((tiles_y, tiles_x, words), np.uint32)
-            for b, o in enumerate(frame_ops):
-                grow = 1 if o.kind == 0 else 0
-                bx0, by0, bx1, by1 = o.x0 - grow, o.y0 - grow, o.x1 + grow, o.y1 + grow
-                if bx1 < 0 or by1 < 0 or bx0 >= width or by0 >= height:
-                    continue
-                tx0, tx1 = max(bx0, 0) // TILE_W, min(bx1, width - 1) // TILE_W
-                ty0, ty1 = max(by0, 0) // TILE_H, min(by1, height - 1) // TILE_H
-                sel = np.ones((ty1 - ty0 + 1, tx1 - tx0 + 1), bool)
-                if o.kind == 0:      # a rectangle only touches tiles its 3-pixel outline crosses
-                    ix0, iy0, ix1, iy1 = o.x0 + 2, o.y0 + 2, o.x1 - 2, o.y1 - 2       # untouched interior
-                    txs, tys = np.arange(tx0, tx1 + 1) * TILE_W, np.arange(ty0, ty1 + 1) * TILE_H
-                    in_x = (txs >= ix0) & (txs + TILE_W - 1 <= ix1)
-                    in_y = (tys >= iy0) & (tys + TILE_H - 1 <= iy1)
-                    sel = ~(in_y[:, None] & in_x[None, :])
-                w, bit = divmod(b, 32)
-                masks[ty0:ty1 + 1, tx0:tx1 + 1, w] |= (sel.astype(np.uint32) << np.uint32(bit))
-            ty, tx = np.nonzero(masks.any(axis=2))
-            rec = np.zeros((len(ty), 4 + words), np.uint32)
-            rec[:, 2] = tx.astype(np.uint32) | (ty.astype(np.uint32) << 16)
-            rec[:, 4:] = masks[ty, tx]
-            cache[key] = rec
-        for g0 in range(f, f + run, FRAMES_PER_TILE_CTA):
-            rec = cache[key].copy()
-            rec[:, 0] = g0
-            rec[:, 1] = min(FRAMES_PER_TILE_CTA, f + run - g0)
-            rec[:, 3] = first_ops[g0]
+            mask = np.zeros((height, groups, words), np.uint32)
+
+            def mark(ya, yb, xa, xb, w, bit):
+                ya, yb, xa, xb = max(ya, 0), min(yb, height - 1), max(xa, 0), min(xb, width - 1)
+                if ya <= yb and xa <= xb:
+                    mask[ya:yb + 1, xa // 4:xb // 4 + 1, w] |= np.uint32(1 << bit)
+
+            for b_, o in enumerate(frame_ops):
+                w, bit = divmod(b_, 32)
+                if o.kind == 0:        # rectangle outline: top / bottom bands, then the two side bands
+                    mark(o.y0 - 1, o.y0 + 1, o.x0 - 1, o.x1 + 1, w, bit)
+                    mark(o.y1 - 1, o.y1 + 1, o.x0 - 1, o.x1 + 1, w, bit)
+                    mark(o.y0 + 2, o.y1 - 2, o.x0 - 1, o.x0 + 1, w, bit)
+                    mark(o.y0 + 2, o.y1 - 2, o.x1 - 1, o.x1 + 1, w, bit)
+                else:
+                    mark(o.y0, o.y1, o.x0, o.x1, w, bit)
+            ys, gs = np.nonzero(mask.any(axis=2))
+            rec = np.empty((len(ys), 1 + words), np.uint32)
+            rec[:, 0] = gs.astype(np.uint32) | (ys.astype(np.uint32) << 16)
+            rec[:, 1:] = mask[ys, gs]
+            cache[key] = (n_records, len(ys))
             records.append(rec)
-        f += run
-    table = np.concatenate(records) if records else np.zeros((0, 4 + words), np.uint32)
-    return table, words
+            n_records += len(ys)
+        offset, count = cache[key]
+        for start in range(0, count, GROUPS_PER_CTA):
+            ctas.append((offset + start, min(GROUPS_PER_CTA, count - start), f, first_ops[f] | (len(frame_ops) << 24)))
+    if not ctas:
+        return None
+    return np.concatenate(records), np.array(ctas, np.uint32), words
 
 
 class DeviceOverlay:
     """A draw list resident on the GPU (see aiko_b200_overlay in include/aiko_b200.h)."""
 
-    def __init__(self, ops, op_offsets, atlas=None, max_ops_per_frame=0, index=None, index_width=0, tiles=None,
-                 tile_height=0):
+    def __init__(self, ops, op_offsets, atlas=None, max_ops_per_frame=0, index=None, index_width=0, groups=None,
+                 index_height=0):
         self.ops, self.op_offsets, self.atlas = ops, op_offsets, atlas
         self.struct = Overlay()
         self.struct.max_ops_per_frame = int(max_ops_per_frame)
@@ -176,14 +166,15 @@ class DeviceOverlay:
             self.struct.index = table.data_ptr()
             self.struct.index_width, self.struct.index_segments = int(index_width), int(segments)
             self.struct.index_words, self.struct.index_frame_words = int(words), int(table.shape[1])
-        self.tiles = None
-        if tiles is not None and index_width:
-            table, words = tiles
-            self.tiles = table
-            self.struct.index_width = int(index_width)
-            self.struct.tiles = table.data_ptr() if table.shape[0] else self.ops.data_ptr()   # non-null marks "listed"
-            self.struct.n_tiles, self.struct.tile_words = int(table.shape[0]), int(words)
-            self.struct.tile_height = int(tile_height)
+        self.groups = None
+        if groups is not None and index_width:
+            records, ctas, words = groups
+            self.groups = (records, ctas)
+            self.struct.index_width, self.struct.index_height = int(index_width), int(index_height)
+            self.struct.group_records, self.struct.group_ctas = records.data_ptr(), ctas.data_ptr()
+            self.struct.n_group_ctas, self.struct.group_words = int(ctas.shape[0]), int(words)
+            if ctas.shape[0] == 0:             # "nothing is drawn": the pointers only need to be non-null
+                self.struct.group_ctas = records.data_ptr()
         self.struct.ops = ops.data_ptr()
         self.struct.op_offsets = op_offsets.data_ptr()
         if atlas is not None:
@@ -215,15 +206,18 @@ class DeviceOverlay:
             built = build_overlay_index(ops_per_frame, width)
             if built is not None:
                 index = (torch.from_numpy(built[0]).to(device), built[1], built[2])
-        tiles = None
+        groups = None
         if width and height:
-            built = build_tile_list(ops_per_frame, width, height)
-            if most == 0:                       # nothing to draw at all: an empty list, so no kernel is launched
-                tiles = (torch.zeros((1, 5), dtype=torch.int32, device=device)[:0], 1)
-            elif built is not None and len(built[0]):
-                tiles = (torch.from_numpy(built[0]).to(device), built[1])
+            if most == 0:                       # nothing to draw at all: no kernel is launched
+                empty = torch.zeros((1, 4), dtype=torch.int32, device=device)
+                groups = (empty, empty[:0], 1)
+            else:
+                built = build_group_list(ops_per_frame, width, height)
+                if built is not None:
+                    groups = (torch.from_numpy(built[0].view(np.int32)).to(device),
+                              torch.from_numpy(built[1].view(np.int32)).to(device), built[2])
         return DeviceOverlay(torch.from_numpy(raw).to(device), torch.from_numpy(offsets).to(device), atlas, most,
-                             index, width or 0, tiles, height or 0)
+                             index, width or 0, groups, height or 0)
 
     def pointer(self):
         return ctypes.pointer(self.struct)

@@ -223,7 +223,7 @@ def run_gpu_arm(args):
     ms = ev0.elapsed_time(ev1)
     clocks = sampler.stop(wall0, wall1)
     # A step launches two kernels: resize3_staged (resize + swap: reads every weighted source
-    # sector and writes every output byte -- the algorithmic bytes) and overlay_tiles (the draw
+    # sector and writes every output byte -- the algorithmic bytes) and overlay_groups (the draw
     # list, in place on the L2-resident output).  The dominant kernel's own duration is measured
     # live with the same inputs and launch configuration, overlay off.
     barrier()
@@ -306,7 +306,7 @@ def run_gpu_arm(args):
                          "peak_source": peak_src, "kernel": "resize3_staged",
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_FRAME * BATCH, "kernel_ms": kernel_ms,
                          "step_ms": step_ms, "step_frac": ALGO_BYTES_PER_FRAME * BATCH / (step_ms * 1e-3) / 1e9 / peak,
-                         "kernels_per_step": ["resize3_staged", "overlay_tiles_kernel"]},
+                         "kernels_per_step": ["resize3_staged", "overlay_groups_kernel"]},
             "e2e": {"value": frames_e2e / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                     "note": "Pipeline.process_frame over ImageResize -> ImageOverlay -> ImageConvert(RGB2BGR) -> "

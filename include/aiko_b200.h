@@ -86,13 +86,19 @@ typedef struct aiko_b200_overlay {
    * Built by aiko_services_b200.ops.build_overlay_index (numpy). */
   const uint32_t* index;
   int32_t index_width, index_segments, index_words, index_frame_words;
-  /* Optional list of the 64 x 16 pixel tiles (of frames index_width x tile_height pixels) that
-   * the draw lists touch: n_tiles records of (4 + tile_words) uint32:
-   *   first_frame, frame_count, tile_x | tile_y << 16, op_offsets[first_frame], then tile_words
-   *   words: bit b of word w = op 32*w + b of the list can touch the tile.  frame_count > 1 only
-   *   for consecutive frames whose draw lists are identical.  NULL = not provided. */
-  const uint32_t* tiles;
-  int32_t n_tiles, tile_words, tile_height;
+  int32_t index_height;
+  /* Optional list of the 4-pixel groups (pixels 4g .. 4g+3 of row y) that the draw lists can touch,
+   * for frames index_width x index_height, arranged for one thread per (frame, touched group):
+   *   group_records[r] = (1 + group_words) uint32: g | y << 16, then bit b of word w = op 32*w + b
+   *       of the frame's list can touch the group;
+   *   group_ctas[c]    = 4 uint32: first record, record count (<= 256), frame,
+   *       op_offsets[frame] | op count << 24  -- one CTA's share.
+   * Frames with identical lists may share records.  n_group_ctas == 0 with non-NULL pointers means
+   * nothing is drawn.  NULL = not provided (the kernel then culls the list per 64 x 16 tile).
+   * Built by aiko_services_b200.ops.build_group_list (numpy). */
+  const uint32_t* group_records;
+  const uint32_t* group_ctas;
+  int32_t n_group_ctas, group_words;
 } aiko_b200_overlay;
 
 /* ---------------------------------------------------------------------- */

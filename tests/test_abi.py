@@ -38,4 +38,4 @@ def test_version_and_error_string_without_gpu():
 
 def test_overlay_op_struct_layout():
     assert ctypes.sizeof(_native.OverlayOp) == 32
-    assert ctypes.sizeof(_native.Overlay) == 96   # 6 pointers + 11 int32 (+ padding)
+    assert ctypes.sizeof(_native.Overlay) == 104   # 7 pointers + 11 int32 (+ padding)

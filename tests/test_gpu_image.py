@@ -269,13 +269,13 @@ def test_fused_equals_unfused_random(cuda, atlas):
 
 
 def test_fused_resize_with_long_draw_list_uses_device_side_culling(cuda, atlas):
-    """More ops than the host-built tile list carries (128): the tile kernel culls by itself."""
+    """More ops than the host-built group list carries (128): the tile kernel culls by itself."""
     rng = np.random.default_rng(206)
     H, W = 120, 160
     frames = np.stack([cases.frame(500 + k, 270, 480, 3) for k in range(2)])
     overlays = [random_overlay(rng, W, H, n=60) for _ in range(2)]
     ov = device_overlay(overlays, W, H, "rgb", atlas, cuda)
-    assert ov.tiles is None and int(ov.op_offsets[-1]) > 256
+    assert ov.groups is None and int(ov.op_offsets[-1]) > 256
     out = host(ops.resize_linear(dev(frames, cuda), W, H, overlay=ov))
     for k in range(2):
         np.testing.assert_array_equal(out[k], overlay_cpu(O.resize_linear(frames[k], W, H), overlays[k], atlas))
