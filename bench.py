@@ -301,8 +301,8 @@ def run_gpu_arm(args):
                        "l2": f"{N_ROTATING_BATCHES} rotating input batches of 199 MB each (> 126 MB L2), no flush",
                        "sharding": "independent streams per rank, no collective" if world > 1 else "single GPU"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": 198_900_000, "traffic_source": "ncu --set full, profiles/ncu_resize3_staged_r01_summary.csv "
-                                                                   "(dram read 178.0 MB + write 20.9 MB per launch)",
+                         "traffic": 197_457_408, "traffic_source": "ncu --set full, profiles/ncu_final_r01_summary.csv "
+                                                                   "(dram read 176.99 MB + write 20.47 MB per launch)",
                          "peak_source": peak_src, "kernel": "resize3_staged",
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_FRAME * BATCH, "kernel_ms": kernel_ms,
                          "step_ms": step_ms, "step_frac": ALGO_BYTES_PER_FRAME * BATCH / (step_ms * 1e-3) / 1e9 / peak,
