@@ -72,3 +72,35 @@ def test_skips_and_empty(atlas):
     ops = build_ops({"objects": [{"name": "a", "confidence": 0.0}], "rectangles": [{"x": 1, "y": 1, "w": 5, "h": 5}]},
                     64, 48)
     assert ops == []      # confidence must exceed the threshold (image_io.py:131)
+
+
+def test_group_list_covers_every_pixel_an_op_changes(atlas):
+    """The GPU applies an op only to the 4-pixel groups the host flagged for it: for random
+    overlays (clipped boxes, labels at the border), every pixel that op changes when replayed
+    alone must lie in a flagged group, and frames sharing a list must share its records."""
+    from aiko_services_b200.ops import build_group_list
+    from util import replay_ops_cpu
+    rng = np.random.default_rng(6)
+    for trial in range(12):
+        h, w = int(rng.integers(40, 140)), int(rng.integers(60, 260))
+        overlay = random_overlay(rng, w, h, n=int(rng.integers(1, 7)))
+        ops = build_ops(overlay, w, h, "rgb", atlas)
+        if not ops:
+            continue
+        records, ctas, words = build_group_list([ops, ops, list(ops)], w, h)
+        n_rec = len(records) // 2                      # frames 0 and 1 share one list object, frame 2 has a copy
+        assert [int(c[2]) for c in ctas] == sorted(int(c[2]) for c in ctas)
+        first_of_frame = {f: min(int(c[0]) for c in ctas if int(c[2]) == f) for f in (0, 1, 2)}
+        assert first_of_frame[0] == first_of_frame[1] != first_of_frame[2]
+        flagged = {}                                    # (y, g) -> mask words
+        for r in records[:n_rec]:
+            flagged[(int(r[0] >> 16), int(r[0] & 0xffff))] = [int(v) for v in r[1:]]
+        for b, op in enumerate(ops):
+            probes = [np.zeros((h, w, 3), np.uint8), np.full((h, w, 3), 255, np.uint8),
+                      rng.integers(0, 256, (h, w, 3), dtype=np.uint8)]
+            changed = np.zeros((h, w), bool)
+            for base in probes:
+                changed |= (replay_ops_cpu(base.copy(), [op], atlas) != base).any(axis=2)
+            for y, x in zip(*np.nonzero(changed)):
+                mask = flagged.get((int(y), int(x) // 4))
+                assert mask is not None and (mask[b // 32] >> (b % 32)) & 1, (trial, b, int(x), int(y))
