@@ -304,3 +304,22 @@ def test_resize_rgba_swap_and_widths_not_multiple_of_four(cuda, atlas):
         ov = device_overlay([overlay], W, 50, "rgb", atlas, cuda)
         out = host(ops.resize_linear(dev(frames, cuda), W, 50, overlay=ov))[0]
         np.testing.assert_array_equal(out, overlay_cpu(O.resize_linear(frames[0], W, 50), overlay, atlas))
+
+
+def test_sizes_beyond_on_chip_limits_are_refused_not_mangled(cuda):
+    """Rows that cannot be staged in shared memory give AIKO_B200_ERR_UNSUPPORTED with a message."""
+    from aiko_services_b200 import _native
+    tiny = torch.zeros((1, 2, 4, 3), dtype=torch.uint8, device=cuda)
+    with pytest.raises(_native.NativeError) as e:
+        ops.resize_linear(tiny, 40000, 2)                 # 40000-pixel output rows: tables exceed shared memory
+    assert e.value.code == _native.ERR_UNSUPPORTED and "shared memory" in str(e.value)
+    with pytest.raises(_native.NativeError) as e:
+        ops.resize_bicubic_aa(tiny, 60000, 2)
+    assert e.value.code == _native.ERR_UNSUPPORTED
+    with pytest.raises(_native.NativeError) as e:
+        ops.flip(torch.zeros((1, 1, 100000, 3), dtype=torch.uint8, device=cuda), 1)
+    assert e.value.code == _native.ERR_INVALID_ARGUMENT
+    # the widest rows the staged kernel takes still resize exactly (8K frames)
+    frames = np.stack([cases.frame(81, 24, 7680, 3)])
+    out = host(ops.resize_linear(dev(frames, cuda), 3840, 12))
+    np.testing.assert_array_equal(out[0], O.resize_linear(frames[0], 3840, 12))
