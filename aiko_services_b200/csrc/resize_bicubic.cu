@@ -265,13 +265,20 @@ extern "C" int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, 
   p.ksx = l.x.ksize; p.ksy = l.y.ksize;
   p.off_bx = l.x.off_bounds; p.off_kx = l.x.off_k; p.off_by = l.y.off_bounds; p.off_ky = l.y.off_k;
   p.ring_rows = l.y.ksize + kRowsPerRound;
-  // bands: enough CTAs to fill the machine, long enough that the vertical halo stays small
+  // bands: long enough that the vertical halo (ksize source rows re-filtered per band) stays small,
+  // and a CTA count that fills whole waves of the machine (2 CTAs per SM fit by shared memory)
   const double scale_y = (double)src_h / dst_h;
-  int band = (int)(4.0 * l.y.ksize / (scale_y < 1.0 ? 1.0 : scale_y)) + 1;  // halo <= ~25 % of the rows read
-  const long long want_ctas = (long long)sm_count() * 4;
-  while (band > 8 && (long long)n_frames * ((dst_h + band - 1) / band) < want_ctas) band /= 2;
-  if (band > dst_h) band = dst_h;
-  if (band < 1) band = 1;
+  const double rows_per_out = scale_y < 1.0 ? 1.0 : scale_y;
+  const long long slots = (long long)sm_count() * 2;
+  int band = 1;
+  double best = -1.0;
+  for (int cand = 4; cand <= 64 && cand <= dst_h; cand++) {
+    const long long ctas = (long long)n_frames * ((dst_h + cand - 1) / cand);
+    const double wave_eff = (double)ctas / (double)(((ctas + slots - 1) / slots) * slots);
+    const double halo_eff = cand * rows_per_out / (cand * rows_per_out + l.y.ksize);
+    if (wave_eff * halo_eff > best) { best = wave_eff * halo_eff; band = cand; }
+  }
+  if (dst_h < 4) band = dst_h;
   p.band = band;
   p.bands_per_frame = (dst_h + band - 1) / band;
   const size_t src_stride = ((size_t)src_w * channels + 31) & ~(size_t)15;
