@@ -1,4 +1,4 @@
 """GPU implementations of the reference's media elements (R/elements/media/), same class names."""
 from .common_io import DataSource, DataTarget, contains_all, file_glob_difference  # noqa: F401
 from .image_io import (ImageConvert, ImageOutput, ImageOverlay, ImageReadFile, ImageResize,  # noqa: F401
-                       ImageWriteFile)
+                       ImageToTensor, ImageWriteFile)

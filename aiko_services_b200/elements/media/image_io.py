@@ -16,7 +16,8 @@ from ...staging import FrameStager
 from ...stream import StreamEvent
 from .common_io import DataSource, DataTarget, contains_all
 
-__all__ = ["ImageConvert", "ImageOutput", "ImageOverlay", "ImageReadFile", "ImageResize", "ImageWriteFile"]
+__all__ = ["ImageConvert", "ImageOutput", "ImageOverlay", "ImageReadFile", "ImageResize", "ImageToTensor",
+           "ImageWriteFile"]
 
 _CONVERSIONS = ("RGB2BGR", "BGR2RGB", "RGB2GRAY", "BGR2GRAY", "GRAY2BGR")
 _FLIPS = {"vertical": 0, "horizontal": 1, "both": -1}
@@ -114,6 +115,43 @@ def logic_image_convert(element, stream, images):
             return StreamEvent.ERROR, {"diagnostic": f"ImageConvert: unknown flip {flip}"}
         images = _apply(stream, images, ("flip", _FLIPS[flip]))
     return StreamEvent.OKAY, {"images": images}
+
+
+def logic_image_to_tensor(element, stream, images):
+    """BASELINE config 4: frames -> the input a torch model element expects, without leaving the GPU:
+    cv2-exact bilinear resize to ``resolution`` and ((x / 255) - mean) / std as float32 [N, 3, H, W].
+    Parameters: ``resolution`` "WxH", ``mean`` and ``std`` "r,g,b" (default: the ImageNet constants).
+    Output ``tensor``: a CUDA tensor a downstream element can pass straight to its model (the reference's
+    detectors hand ndarrays to ultralytics / deepface instead, R/examples/yolo/yolo.py:62-64)."""
+    from ... import ops
+    resolution, _ = element.get_parameter("resolution")
+    width, height = (int(v) for v in resolution.split("x"))
+    mean, _ = element.get_parameter("mean", default="0.485,0.456,0.406")
+    std, _ = element.get_parameter("std", default="0.229,0.224,0.225")
+    mean = [float(v) for v in str(mean).split(",")]
+    std = [float(v) for v in str(std).split(",")]
+    if not images:
+        return StreamEvent.OKAY, {"tensor": None}
+    parts = [None] * len(images)
+    for batch, positions in stager_for(stream).upload(images):
+        frames = batch.tensor
+        if frames.dim() != 4 or frames.shape[3] != 3:
+            return StreamEvent.ERROR, {"diagnostic": "ImageToTensor: RGB frames expected"}
+        import torch
+        with torch.cuda.stream(batch.stream) if batch.stream is not None else _null():
+            out = ops.resize_norm_f32(frames, width, height, mean, std)
+        for k, pos in enumerate(positions):
+            parts[pos] = out[k]
+    import torch
+    return StreamEvent.OKAY, {"tensor": torch.stack(parts) if len(parts) > 1 else parts[0][None]}
+
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
 
 
 def logic_image_read_file(element, stream, paths):
@@ -254,6 +292,10 @@ class ImageConvert(PipelineElement):
     batch_across_streams = True
     process_frame = logic_image_convert
     process_frame_batch = _cross_stream(_prepare_convert)
+
+
+class ImageToTensor(PipelineElement):
+    process_frame = logic_image_to_tensor
 
 
 class ImageReadFile(DataSource):

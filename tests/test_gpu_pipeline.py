@@ -138,6 +138,37 @@ def test_gray_and_mixed_shapes(cuda, tmp_path):
         np.testing.assert_array_equal(np.asarray(im), r)
 
 
+def test_image_to_tensor_feeds_a_torch_model_element(cuda, tmp_path):
+    """BASELINE config 4 shape: frames -> fp32 NCHW CUDA tensor -> a torch module, no host round trip."""
+    model_src = tmp_path / "model.py"
+    model_src.write_text('''
+import torch
+from aiko_services_b200.pipeline import PipelineElement
+from aiko_services_b200.stream import StreamEvent
+
+class TinyModel(PipelineElement):
+    def process_frame(self, stream, tensor):
+        assert tensor.is_cuda and tensor.dtype == torch.float32
+        return StreamEvent.OKAY, {"scores": tensor.mean(dim=(2, 3))}
+''')
+    d = {"version": 0, "name": "p_cfg4", "runtime": "python", "graph": ["(ImageToTensor TinyModel)"],
+         "parameters": {"resolution": "56x56"},
+         "elements": [{"name": "ImageToTensor", "input": [{"name": "images", "type": "[image]"}],
+                       "output": [{"name": "tensor", "type": "tensor"}], "deploy": {"local": {"module": IMAGE_IO}}},
+                      {"name": "TinyModel", "input": [{"name": "tensor", "type": "tensor"}],
+                       "output": [{"name": "scores", "type": "tensor"}], "deploy": {"local": {"module": str(model_src)}}}]}
+    p = Pipeline(d)
+    assert p.create_stream("m")
+    frames = [cases.frame(950 + k, 270, 480, 3) for k in range(3)]
+    okay, swag = p.process_frame({"stream_id": "m"}, {"images": frames})
+    assert okay and tuple(swag["tensor"].shape) == (3, 3, 56, 56)
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    for k in range(3):
+        ref = O.resize_norm_f32(frames[k], 56, 56, mean, std)
+        np.testing.assert_array_equal(swag["tensor"][k].cpu().numpy(), ref)
+        np.testing.assert_allclose(swag["scores"][k].cpu().numpy(), ref.mean(axis=(1, 2)), rtol=1e-5)
+
+
 @pytest.mark.skipif(not ref_harness.available(), reason="reference package not present (baseline/install_ref.sh)")
 def test_drop_in_inside_the_unmodified_reference_runtime(cuda):
     """The reference's own PipelineImpl, its own JSON module names, GPU elements underneath."""
