@@ -95,15 +95,23 @@ __device__ __forceinline__ void bulk_wait_read() {
 // streaming 128-bit global accesses (frames are read once / written once)
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   uint4 r;
+#ifdef AIKO_PLAIN_LDST
+  r = *p;
+#else
   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                : "l"(p));
+#endif
   return r;
 }
 __device__ __forceinline__ void stg_stream(uint4* p, const uint4& v) {
+#ifdef AIKO_PLAIN_LDST
+  *p = v;
+#else
   asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
                "r"(v.w)
                : "memory");
+#endif
 }
 
 // Copy one finished row from shared memory to global memory.  Vector path when

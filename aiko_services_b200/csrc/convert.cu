@@ -181,7 +181,9 @@ __global__ void __launch_bounds__(kThreads) crop_rows_kernel(const uint8_t* __re
 
 static unsigned stream_grid(long long work_items) {
   long long blocks = (work_items + kThreads - 1) / kThreads;
-  const long long cap = (long long)sm_count() * 8;
+  // enough blocks that a launch of a few hundred MB runs without serialising many iterations per
+  // thread (measured: 8 per SM -> 0.67 of the HBM roofline for swap_rb, 64 per SM -> 0.88)
+  const long long cap = (long long)sm_count() * 64;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   return (unsigned)blocks;
@@ -234,7 +236,7 @@ extern "C" int aiko_b200_flip_u8(const uint8_t* src, uint8_t* dst, int n_frames,
   AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "flip: row of %d bytes exceeds shared memory", w * channels);
   AIKO_CUDA(cudaFuncSetAttribute(flip_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long rows = (long long)n_frames * h;
-  long long grid = (long long)sm_count() * 8;
+  long long grid = (long long)sm_count() * 32;
   if (grid > rows) grid = rows;
   flip_rows_kernel<<<(unsigned)grid, kThreads, smem, (cudaStream_t)stream>>>(src, dst, rows, h, w, channels,
                                                                             flip_code, rev_offset);
@@ -250,7 +252,7 @@ extern "C" int aiko_b200_crop_u8(const uint8_t* src, int n_frames, int h, int w,
   if (n_frames == 0 || crop_w == 0 || crop_h == 0) return AIKO_B200_OK;
   AIKO_CHECK_ARG(src && dst, "crop: null pointer");
   const long long rows = (long long)n_frames * crop_h;
-  long long grid = (long long)sm_count() * 8;
+  long long grid = (long long)sm_count() * 32;
   if (grid > rows) grid = rows;
   crop_rows_kernel<<<(unsigned)grid, kThreads, 0, (cudaStream_t)stream>>>(src, dst, rows, h, w, channels, x0, y0,
                                                                           crop_w, crop_h);

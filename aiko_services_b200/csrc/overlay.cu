@@ -320,7 +320,7 @@ extern "C" int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_fram
   AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "overlay: row of %zu bytes exceeds shared memory", smem);
   AIKO_CUDA(cudaFuncSetAttribute(overlay_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long rows = (long long)n_frames * h;
-  long long grid = (long long)sm_count() * 8;
+  long long grid = (long long)sm_count() * 32;
   if (grid > rows) grid = rows;
   overlay_rows_kernel<<<(unsigned)grid, kThreads, smem, (cudaStream_t)stream>>>(p);
   return cuda_status(cudaGetLastError(), "overlay launch");

@@ -81,7 +81,7 @@ extern "C" int aiko_b200_resize_norm_f32_nchw(const uint8_t* src, int n_frames, 
   }
   const long long total = (long long)n_frames * dst_h * dst_w;
   long long blocks = (total + kThreads - 1) / kThreads;
-  const long long cap = (long long)sm_count() * 16;
+  const long long cap = (long long)sm_count() * 64;
   if (blocks > cap) blocks = cap;
   resize_norm_kernel<<<(unsigned)blocks, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
   return cuda_status(cudaGetLastError(), "resize_norm launch");

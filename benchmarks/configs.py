@@ -74,6 +74,8 @@ def main():
     del odd_in
 
     sw = torch.empty_like(hd[0])
+    ms = timed(lambda i: sw.copy_(hd[i % rot]), args.steps)
+    report("calibration: torch device copy of one 199 MB batch (read + write)", 32, "frames", 2 * 6_220_800, ms)
     ms = timed(lambda i: ops.swap_rb(hd[i % rot], out=sw), args.steps)
     report("swap_rb 1080p", 32, "frames", 2 * 6_220_800, ms)
     gray = torch.empty((32, 1080, 1920), dtype=torch.uint8, device=dev)
