@@ -12,45 +12,9 @@
 //                          intermediate rows, and each output row is produced from that ring,
 //                          so a source byte is read from HBM once per band it belongs to and the
 //                          intermediate image never exists in global memory.
-#include "common.cuh"
+#include "bicubic.cuh"
 
 namespace aiko {
-
-constexpr int kPrecisionBits = 32 - 8 - 2;
-
-struct AxisTable {
-  int ksize;  // taps per output index (row stride of k)
-  int off_bounds;
-  int off_k;
-};
-struct BicubicLayout {
-  AxisTable x, y;
-  size_t ints;
-};
-
-__host__ __device__ inline int bicubic_ksize(int in_size, int out_size) {
-  double scale = (double)in_size / out_size;
-  if (scale < 1.0) scale = 1.0;
-  const double support = 2.0 * scale;
-  int c = (int)support;
-  if ((double)c < support) c++;
-  return c * 2 + 1;
-}
-
-static BicubicLayout bicubic_layout(int sh, int sw, int dh, int dw) {
-  BicubicLayout l;
-  l.x.ksize = (bicubic_ksize(sw, dw) + 3) & ~3;  // rows of k padded to 16 bytes
-  l.y.ksize = (bicubic_ksize(sh, dh) + 3) & ~3;
-  size_t o = 4;
-  l.x.off_bounds = (int)o; o += 2 * (size_t)dw;
-  o = (o + 3) & ~(size_t)3;
-  l.x.off_k = (int)o; o += (size_t)dw * l.x.ksize;
-  l.y.off_bounds = (int)o; o += 2 * (size_t)dh;
-  o = (o + 3) & ~(size_t)3;
-  l.y.off_k = (int)o; o += (size_t)dh * l.y.ksize;
-  l.ints = o;
-  return l;
-}
 
 __device__ __forceinline__ double bicubic_filter(double x) {
   // a = -0.5: ((a + 2) x - (a + 3)) x x + 1   |   (((x - 5) x + 8) x - 4) a
@@ -231,7 +195,7 @@ extern "C" size_t aiko_b200_resize_bicubic_workspace_bytes(int src_h, int src_w,
 extern "C" int aiko_b200_resize_bicubic_prepare(void* workspace, size_t workspace_bytes, int src_h, int src_w,
                                                 int dst_h, int dst_w, void* stream) {
   AIKO_CHECK_ARG(src_h > 0 && src_w > 0 && dst_h > 0 && dst_w > 0, "resize_bicubic_prepare: bad size");
-  const BicubicLayout l = bicubic_layout(src_h, src_w, dst_h, dst_w);
+  const BicubicLayout l = bicubic_layout_for(src_h, src_w, dst_h, dst_w, workspace_bytes);
   if (!workspace || workspace_bytes < l.ints * sizeof(int)) {
     set_last_error("resize_bicubic_prepare: workspace of %zu bytes, need %zu", workspace_bytes, l.ints * sizeof(int));
     return AIKO_B200_ERR_WORKSPACE;
@@ -239,9 +203,12 @@ extern "C" int aiko_b200_resize_bicubic_prepare(void* workspace, size_t workspac
   AIKO_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "resize_bicubic_prepare: workspace not 16-byte aligned");
   int* ws = static_cast<int*>(workspace);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  AIKO_CUDA(cudaMemsetAsync(ws, 0, 4 * sizeof(int), st));   // header; int 1 is the table builders' error flag
   bicubic_coeffs_kernel<<<(dst_w + 127) / 128, 128, 0, st>>>(ws, src_w, dst_w, l.x.ksize, l.x.off_bounds, l.x.off_k);
   bicubic_coeffs_kernel<<<(dst_h + 127) / 128, 128, 0, st>>>(ws, src_h, dst_h, l.y.ksize, l.y.off_bounds, l.y.off_k);
-  return cuda_status(cudaGetLastError(), "bicubic_coeffs launch");
+  const int rc = cuda_status(cudaGetLastError(), "bicubic_coeffs launch");
+  if (rc != AIKO_B200_OK) return rc;
+  return bicubic_mma_prepare(ws, l, src_h, src_w, dst_h, dst_w, st);
 }
 
 extern "C" int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, int src_h, int src_w, int channels,
@@ -253,11 +220,17 @@ extern "C" int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, 
   AIKO_CHECK_ARG(src_h > 0 && src_w > 0 && dst_h > 0 && dst_w > 0, "resize_bicubic: bad size");
   AIKO_CHECK_ARG(channels == 1 || channels == 3 || channels == 4, "resize_bicubic: channels %d not in {1,3,4}",
                  channels);
-  const BicubicLayout l = bicubic_layout(src_h, src_w, dst_h, dst_w);
+  const BicubicLayout l = bicubic_layout_for(src_h, src_w, dst_h, dst_w, workspace_bytes);
   if (!workspace || workspace_bytes < l.ints * sizeof(int)) {
     set_last_error("resize_bicubic: workspace of %zu bytes, need %zu (and it must have been prepared)", workspace_bytes,
                    l.ints * sizeof(int));
     return AIKO_B200_ERR_WORKSPACE;
+  }
+  {
+    bool done = false;
+    const int rc = bicubic_mma_launch(src, n_frames, src_h, src_w, channels, dst, dst_h, dst_w,
+                                      static_cast<const int*>(workspace), l, static_cast<cudaStream_t>(stream), &done);
+    if (rc != AIKO_B200_OK || done) return rc;
   }
   BicubicParams p{};
   p.src = src; p.dst = dst; p.ws = static_cast<const int*>(workspace);
@@ -341,7 +314,8 @@ extern "C" int aiko_b200_resize_bicubic_aa_u8_noalloc(const uint8_t* src, int n_
                                                       void* stream) {
   AIKO_CHECK_ARG(n_frames >= 0, "resize_bicubic_noalloc: n_frames < 0");
   AIKO_CHECK_ARG(src_h > 0 && src_w > 0 && dst_h > 0 && dst_w > 0, "resize_bicubic_noalloc: bad size");
-  const size_t need = aiko_b200_resize_bicubic_workspace_bytes(src_h, src_w, dst_h, dst_w);
+  // the coefficient tables must fit; the tensor-core tables are used when they fit as well
+  const size_t need = bicubic_layout(src_h, src_w, dst_h, dst_w, false).ints * sizeof(int);
   if (need > kStaticScratchBytes) {
     set_last_error(
         "resize_bicubic_noalloc: %dx%d -> %dx%d needs %zu bytes of weight tables but the built-in scratch holds %zu; "

@@ -1,0 +1,440 @@
+// Antialiased bicubic resize (Pillow arithmetic, see resize_bicubic.cu) on the tensor cores.
+//
+// Why tensor cores for byte work: Pillow's two passes are ~35 exact integer multiply-adds per
+// source pixel (1080p -> 640x480); on the integer pipe that is 10x more time than the frame takes
+// to cross HBM.  Both passes are banded matrix products, and an integer MMA computes them exactly:
+// a 22-bit weight is split into three byte planes, w = (w2 << 16) + (w1 << 8) + w0 with w2 signed,
+// and  sum(w * p) = ((sum(w2 p) << 8) + sum(w1 p) << 8) + sum(w0 p)  in wrapping 32-bit arithmetic,
+// which is the arithmetic Pillow's int accumulators use.  Each plane is one
+// mma.sync.m16n8k32 (u8/s8 x u8 -> s32); the rounding constant 1 << 21 enters as the initial
+// accumulator 32 of the top plane.  The result is bit-identical to the scalar kernel.
+//
+//   horizontal pass   D[16 dx][8 rows]  = A[16 dx][K px]   x B[K px][8 rows]
+//                     A = weights of one 16-pixel tile, kept in registers for the whole kernel;
+//                     B = source pixels of one channel, gathered from the interleaved rows the
+//                     TMA engine staged in shared memory (3 words -> 3 channel registers).
+//   vertical pass     D[16 bytes][8 dy] = A[16 bytes][K rows] x B[K rows][8 dy]
+//                     A = the uint8 intermediate image, held transposed ([byte column][row]) in a
+//                     shared-memory ring that the horizontal epilogue writes; B = weights.
+//
+// A CTA owns (frame, band of output rows, range of 16-pixel tiles).  Inside it every consumer
+// warp owns a fixed run of tiles and does horizontal pass, ring and vertical pass for those
+// columns alone, so warps synchronise only with the producer warp (full / empty mbarriers of the
+// two staging buffers), never with each other.
+#include "bicubic.cuh"
+
+namespace aiko {
+
+constexpr int kBatchRows = 8;        // source rows per staging buffer = N of the horizontal MMA
+constexpr int kMmaStages = 2;
+constexpr int kMmaMaxWarps = 11;     // consumer warps per CTA (+ 1 producer warp)
+
+// ---------------------------------------------------------------------------------------------
+// Table builders (run once per size pair by aiko_b200_resize_bicubic_prepare, after the
+// coefficient kernels on the same stream).
+__device__ __forceinline__ uint32_t weight_plane_byte(int w, int plane, int* bad) {
+  if (plane == 0) return (uint32_t)w & 255u;
+  if (plane == 1) return ((uint32_t)w >> 8) & 255u;
+  const int top = w >> 16;
+  if (top < -128 || top > 127) *bad = 1;
+  return (uint32_t)top & 255u;
+}
+
+// weight of source index `src` for output `out`, 0 outside the output's taps
+__device__ __forceinline__ int tap_weight(const int* bounds, const int* k, int ksize, int out, int n_out, int src) {
+  if (out >= n_out) return 0;
+  const int t = src - bounds[2 * out];
+  return (t >= 0 && t < bounds[2 * out + 1]) ? k[(size_t)out * ksize + t] : 0;
+}
+
+__global__ void bicubic_x_frags_kernel(int* ws, int dw, int ksize, int off_bounds, int off_k, int kx, int ntx,
+                                       int off_xa, int off_ax) {
+  const int id = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = id & 31, frag = id >> 5;   // frag = (tile * 3 + plane) * kx + ks
+  if (frag >= ntx * 3 * kx) return;
+  const int ks = frag % kx, plane = (frag / kx) % 3, tile = frag / (3 * kx);
+  const int* bounds = ws + off_bounds;
+  const int* k = ws + off_k;
+  const int dx0 = tile * 16;
+  const int xa = bounds[2 * dx0] & ~3;
+  const int g = lane >> 2, q = lane & 3;
+  int bad = 0;
+  uint32_t regs[4];
+  for (int r = 0; r < 4; r++) {      // a0: (g, 4q) a1: (g + 8, 4q) a2: (g, 16 + 4q) a3: (g + 8, 16 + 4q)
+    const int dx = dx0 + g + 8 * (r & 1);
+    const int px0 = xa + 32 * ks + 4 * q + 16 * (r >> 1);
+    uint32_t v = 0;
+    for (int i = 0; i < 4; i++)
+      v |= weight_plane_byte(tap_weight(bounds, k, ksize, dx, dw, px0 + i), plane, &bad) << (8 * i);
+    regs[r] = v;
+  }
+  reinterpret_cast<uint4*>(ws + off_ax)[(size_t)frag * 32 + lane] = make_uint4(regs[0], regs[1], regs[2], regs[3]);
+  if (plane == 0 && ks == 0 && lane == 0) {
+    ws[off_xa + tile] = xa;
+    const int last = min(dx0 + 15, dw - 1);
+    if (bounds[2 * last] + bounds[2 * last + 1] - xa > 32 * kx) bad = 1;   // window bound violated
+  }
+  if (bad) ws[1] = 1;
+}
+
+__global__ void bicubic_y_frags_kernel(int* ws, int dh, int ksize, int off_bounds, int off_k, int ky, int ngy,
+                                       int off_ya, int off_yend, int off_by) {
+  const int id = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = id & 31, frag = id >> 5;   // frag = (group * 3 + plane) * ky + ks
+  if (frag >= ngy * 3 * ky) return;
+  const int ks = frag % ky, plane = (frag / ky) % 3, group = frag / (3 * ky);
+  const int* bounds = ws + off_bounds;
+  const int* k = ws + off_k;
+  const int dy0 = group * 8;
+  const int ya = bounds[2 * dy0] & ~3;
+  const int g = lane >> 2, q = lane & 3;
+  int bad = 0;
+  uint32_t regs[2];
+  for (int r = 0; r < 2; r++) {      // b0: (k = 4q, n = g)  b1: (k = 16 + 4q, n = g)
+    const int row0 = ya + 32 * ks + 4 * q + 16 * r;
+    uint32_t v = 0;
+    for (int i = 0; i < 4; i++)
+      v |= weight_plane_byte(tap_weight(bounds, k, ksize, dy0 + g, dh, row0 + i), plane, &bad) << (8 * i);
+    regs[r] = v;
+  }
+  reinterpret_cast<uint2*>(ws + off_by)[(size_t)frag * 32 + lane] = make_uint2(regs[0], regs[1]);
+  if (plane == 0 && ks == 0 && lane == 0) {
+    const int last = min(dy0 + 7, dh - 1);
+    const int yend = bounds[2 * last] + bounds[2 * last + 1];
+    ws[off_ya + group] = ya;
+    ws[off_yend + group] = yend;
+    if (yend - ya > 32 * ky) bad = 1;
+  }
+  if (bad) ws[1] = 1;
+}
+
+int bicubic_mma_prepare(int* ws, const BicubicLayout& l, int sh, int sw, int dh, int dw, cudaStream_t stream) {
+  (void)sh; (void)sw;
+  const MmaPlan& m = l.mma;
+  if (!m.ok) return AIKO_B200_OK;
+  const int nx = m.ntx * 3 * m.kx * 32, ny = m.ngy * 3 * m.ky * 32;
+  bicubic_x_frags_kernel<<<(nx + 127) / 128, 128, 0, stream>>>(ws, dw, l.x.ksize, l.x.off_bounds, l.x.off_k, m.kx,
+                                                                m.ntx, m.off_xa, m.off_ax);
+  bicubic_y_frags_kernel<<<(ny + 127) / 128, 128, 0, stream>>>(ws, dh, l.y.ksize, l.y.off_bounds, l.y.off_k, m.ky,
+                                                                m.ngy, m.off_ya, m.off_yend, m.off_by);
+  return cuda_status(cudaGetLastError(), "bicubic table launch");
+}
+
+// ---------------------------------------------------------------------------------------------
+struct MmaParams {
+  const uint8_t* src;
+  uint8_t* dst;
+  const int* ws;
+  int n, sh, sw, dh, dw;
+  int ntx, ngy;
+  int off_xa, off_ax, off_ya, off_yend, off_by;
+  int band_groups, bands_per_frame;   // output-row groups (8 rows) per CTA
+  int chunks, tiles_per_chunk;        // 16-pixel tiles per CTA
+  int raw_pitch;                      // bytes between staged source rows (= 48 mod 128: see gather)
+};
+
+// D += A x B, m16n8k32, 8-bit operands, wrapping 32-bit accumulators.
+__device__ __forceinline__ void mma_u8u8(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                         uint32_t b0, uint32_t b1) {
+  asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void mma_s8u8(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                         uint32_t b0, uint32_t b1) {
+  asm("mma.sync.aligned.m16n8k32.row.col.s32.s8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void mma_u8s8(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                         uint32_t b0, uint32_t b1) {
+  asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ uint32_t clip8_acc(int acc) {
+  return (uint32_t)min(max(acc >> kPrecisionBits, 0), 255);
+}
+
+template <int KX>
+struct TilesPerWarp {
+  static constexpr int value = KX == 1 ? 8 : (KX == 2 ? 4 : 2);   // 12 * KX * T <= 96 weight registers
+};
+
+template <int KX, int KY>
+__global__ void __launch_bounds__((kMmaMaxWarps + 1) * 32, 1) bicubic_mma_kernel(const MmaParams p) {
+  constexpr int T = TilesPerWarp<KX>::value;
+  constexpr int CAP = 32 * KY + 16;   // ring rows: one K window + the rows a batch runs ahead, rounded;
+                                      // as a pitch (bytes) it is 16 mod 32, which keeps the loads below conflict-free
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty = full + kMmaStages;
+  uint8_t* raw = smem + 128;
+  uint8_t* ring = raw + (size_t)kMmaStages * kBatchRows * p.raw_pitch;   // [byte column][CAP rows]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, q = lane & 3;
+  const int nwarps = (int)blockDim.x / 32 - 1;   // consumer warps; the last warp feeds the TMA ring
+
+  int bid = blockIdx.x;
+  const int chunk = bid % p.chunks; bid /= p.chunks;
+  const int band = bid % p.bands_per_frame;
+  const int frame = bid / p.bands_per_frame;
+  const int tile0 = chunk * p.tiles_per_chunk, tile1 = min(p.ntx, tile0 + p.tiles_per_chunk);
+  const int j0 = band * p.band_groups, j1 = min(p.ngy, j0 + p.band_groups);
+  const int active = (tile1 - tile0 + T - 1) / T;     // consumer warps that own tiles
+
+  const int* xa = p.ws + p.off_xa;
+  const int* ya = p.ws + p.off_ya;
+  const int* yend = p.ws + p.off_yend;
+  if (__ldg(p.ws + 1) != 0) __trap();   // a weight or window outside what the tables can hold (cannot happen
+                                        // for the sizes MmaPlan.ok admits; better loud than wrong)
+  const int row_bytes = p.sw * 3;
+  const int row_start = __ldg(ya + j0), row_end = __ldg(yend + j1 - 1);
+  const int nbatches = (row_end - row_start + kBatchRows - 1) / kBatchRows;
+  const int byte_lo = (__ldg(xa + tile0) * 3) & ~15;
+  const int byte_hi = min(row_bytes, ((__ldg(xa + tile1 - 1) + 32 * KX) * 3 + 15) & ~15);
+  const int copy_bytes = byte_hi - byte_lo;
+  if (copy_bytes > p.raw_pitch) __trap();
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kMmaStages; s++) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], active);
+    }
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  const uint8_t* fsrc = p.src + (size_t)frame * p.sh * row_bytes;
+  if (warp == nwarps) {
+    // ---- producer -----------------------------------------------------------------------------
+    if (lane != 0) return;
+    for (int b = 0; b < nbatches; b++) {
+      const int s = b % kMmaStages, round = b / kMmaStages;
+      if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1), 1000, 100);
+      uint8_t* d = raw + (size_t)s * kBatchRows * p.raw_pitch;
+      for (int r = 0; r < kBatchRows; r++) {
+        const int row = min(row_start + b * kBatchRows + r, p.sh - 1);   // rows past the frame carry no weight
+        bulk_g2s(d + (size_t)r * p.raw_pitch, fsrc + (size_t)row * row_bytes + byte_lo, (uint32_t)copy_bytes, &full[s]);
+      }
+      mbar_expect_tx(&full[s], (uint32_t)(kBatchRows * copy_bytes));
+    }
+    return;
+  }
+  if (warp >= active) return;
+
+  // ---- consumers ------------------------------------------------------------------------------
+  const int wtile0 = tile0 + warp * T;
+  const int ntw = min(T, tile1 - wtile0);
+  const int wcol0 = warp * T * 48;                    // first ring column (byte column inside the chunk)
+  uint4 A[T][3][KX];
+  int xoff[T];
+  const uint4* ax = reinterpret_cast<const uint4*>(p.ws + p.off_ax);
+#pragma unroll
+  for (int t = 0; t < T; t++) {
+    const bool on = t < ntw;
+    xoff[t] = on ? __ldg(xa + wtile0 + t) * 3 - byte_lo : 0;
+#pragma unroll
+    for (int pl = 0; pl < 3; pl++)
+#pragma unroll
+      for (int ks = 0; ks < KX; ks++)
+        A[t][pl][ks] = on ? __ldg(ax + ((size_t)((wtile0 + t) * 3 + pl) * KX + ks) * 32 + lane) : make_uint4(0, 0, 0, 0);
+  }
+  const uint2* byf = reinterpret_cast<const uint2*>(p.ws + p.off_by);
+  uint8_t* fdst = p.dst + (size_t)frame * p.dh * p.dw * 3;
+  const int out_row_bytes = p.dw * 3;
+  const int gcol0 = tile0 * 48 + wcol0;               // first output byte column of this warp
+
+  int jn = j0;          // next group of output rows to emit
+  int slot = 0;         // ring row of the batch being filtered
+  for (int b = 0; b < nbatches; b++) {
+    const int s = b % kMmaStages, round = b / kMmaStages;
+    mbar_wait(&full[s], (uint32_t)(round & 1), 500, 0);
+    // -- horizontal pass: 8 staged rows x this warp's tiles -> ring rows slot .. slot + 7
+    const uint8_t* rrow = raw + (size_t)(s * kBatchRows + g) * p.raw_pitch;
+#pragma unroll
+    for (int t = 0; t < T; t++) {
+      if (t < ntw) {
+        uint32_t B[KX][2][3];
+#pragma unroll
+        for (int ks = 0; ks < KX; ks++)
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            // 4 pixels = 12 interleaved bytes = 3 words -> one register per channel.  Row pitch
+            // 12 words mod 32 and 3 words per lane: the 32 lanes of each load hit 32 banks.
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(rrow + xoff[t] + (32 * ks + 16 * h + 4 * q) * 3);
+            const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+            B[ks][h][0] = __byte_perm(__byte_perm(w0, w1, 0x0630), w2, 0x5210);
+            B[ks][h][1] = __byte_perm(__byte_perm(w0, w1, 0x0741), w2, 0x6210);
+            B[ks][h][2] = __byte_perm(__byte_perm(w0, w1, 0x0052), w2, 0x7410);
+          }
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+          int acc[4] = {32, 32, 32, 32};   // (1 << 21) >> 16: the rounding constant, shifted up with the top plane
+#pragma unroll
+          for (int ks = 0; ks < KX; ks++)
+            mma_s8u8(acc, A[t][2][ks].x, A[t][2][ks].y, A[t][2][ks].z, A[t][2][ks].w, B[ks][0][c], B[ks][1][c]);
+#pragma unroll
+          for (int i = 0; i < 4; i++) acc[i] <<= 8;
+#pragma unroll
+          for (int ks = 0; ks < KX; ks++)
+            mma_u8u8(acc, A[t][1][ks].x, A[t][1][ks].y, A[t][1][ks].z, A[t][1][ks].w, B[ks][0][c], B[ks][1][c]);
+#pragma unroll
+          for (int i = 0; i < 4; i++) acc[i] <<= 8;
+#pragma unroll
+          for (int ks = 0; ks < KX; ks++)
+            mma_u8u8(acc, A[t][0][ks].x, A[t][0][ks].y, A[t][0][ks].z, A[t][0][ks].w, B[ks][0][c], B[ks][1][c]);
+          // acc[0], acc[1]: pixel g, rows 2q, 2q + 1;  acc[2], acc[3]: pixel g + 8
+          uint8_t* o = ring + (size_t)(wcol0 + (t * 16 + g) * 3 + c) * CAP + slot + 2 * q;
+          *reinterpret_cast<uint16_t*>(o) = (uint16_t)(clip8_acc(acc[0]) | (clip8_acc(acc[1]) << 8));
+          *reinterpret_cast<uint16_t*>(o + 24 * CAP) = (uint16_t)(clip8_acc(acc[2]) | (clip8_acc(acc[3]) << 8));
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);     // the staged rows are free again
+    slot += kBatchRows;
+    if (slot >= CAP) slot -= CAP;
+    const int produced = (b + 1) * kBatchRows;
+
+    // -- vertical pass for every group of 8 output rows whose last intermediate row now exists
+    while (jn < j1 && __ldg(yend + jn) - row_start <= produced) {
+      const int base = (__ldg(ya + jn) - row_start) % CAP;
+      uint2 W[3][KY];
+#pragma unroll
+      for (int pl = 0; pl < 3; pl++)
+#pragma unroll
+        for (int ks = 0; ks < KY; ks++) W[pl][ks] = __ldg(byf + ((size_t)(jn * 3 + pl) * KY + ks) * 32 + lane);
+      int o0[KY], o1[KY];
+#pragma unroll
+      for (int ks = 0; ks < KY; ks++) {
+        o0[ks] = base + 32 * ks + 4 * q;
+        if (o0[ks] >= CAP) o0[ks] -= CAP;
+        o1[ks] = base + 32 * ks + 16 + 4 * q;
+        if (o1[ks] >= CAP) o1[ks] -= CAP;
+      }
+      const int dy = jn * 8 + 2 * q;
+      for (int mt = 0; mt < ntw * 3; mt++) {
+        const uint8_t* c0 = ring + (size_t)(wcol0 + mt * 16 + g) * CAP;
+        const uint8_t* c1 = c0 + 8 * CAP;
+        uint32_t a[KY][4];
+#pragma unroll
+        for (int ks = 0; ks < KY; ks++) {
+          a[ks][0] = *reinterpret_cast<const uint32_t*>(c0 + o0[ks]);
+          a[ks][1] = *reinterpret_cast<const uint32_t*>(c1 + o0[ks]);
+          a[ks][2] = *reinterpret_cast<const uint32_t*>(c0 + o1[ks]);
+          a[ks][3] = *reinterpret_cast<const uint32_t*>(c1 + o1[ks]);
+        }
+        int acc[4] = {32, 32, 32, 32};
+#pragma unroll
+        for (int ks = 0; ks < KY; ks++) mma_u8s8(acc, a[ks][0], a[ks][1], a[ks][2], a[ks][3], W[2][ks].x, W[2][ks].y);
+#pragma unroll
+        for (int i = 0; i < 4; i++) acc[i] <<= 8;
+#pragma unroll
+        for (int ks = 0; ks < KY; ks++) mma_u8u8(acc, a[ks][0], a[ks][1], a[ks][2], a[ks][3], W[1][ks].x, W[1][ks].y);
+#pragma unroll
+        for (int i = 0; i < 4; i++) acc[i] <<= 8;
+#pragma unroll
+        for (int ks = 0; ks < KY; ks++) mma_u8u8(acc, a[ks][0], a[ks][1], a[ks][2], a[ks][3], W[0][ks].x, W[0][ks].y);
+        // acc[0], acc[1]: byte column g, output rows dy, dy + 1;  acc[2], acc[3]: byte column g + 8
+        const int col = gcol0 + mt * 16 + g;
+        uint8_t* orow = fdst + (size_t)dy * out_row_bytes;
+        if (dy < p.dh) {
+          if (col < out_row_bytes) orow[col] = (uint8_t)clip8_acc(acc[0]);
+          if (col + 8 < out_row_bytes) orow[col + 8] = (uint8_t)clip8_acc(acc[2]);
+        }
+        if (dy + 1 < p.dh) {
+          if (col < out_row_bytes) orow[out_row_bytes + col] = (uint8_t)clip8_acc(acc[1]);
+          if (col + 8 < out_row_bytes) orow[out_row_bytes + col + 8] = (uint8_t)clip8_acc(acc[3]);
+        }
+      }
+      jn++;
+    }
+    __syncwarp();   // ring rows read above are rewritten by later batches
+  }
+}
+
+static int env_int(const char* name, int fallback) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : fallback;
+}
+
+template <int KX, int KY>
+static int launch_mma(MmaParams p, int n_frames, double scale_y, cudaStream_t stream, bool* done) {
+  constexpr int T = TilesPerWarp<KX>::value;
+  constexpr int CAP = 32 * KY + 16;
+  const int row_bytes = p.sw * 3;
+  const double scale_x = (double)p.sw / p.dw;
+  const size_t max_smem = (size_t)device_max_smem_optin();
+  int chunks = (p.ntx + kMmaMaxWarps * T - 1) / (kMmaMaxWarps * T);
+  chunks = max(chunks, env_int("AIKO_B200_BICUBIC_CHUNKS", 1));
+  size_t smem = 0;
+  int nwarps = 0;
+  for (;; chunks++) {
+    if (chunks > p.ntx) return AIKO_B200_OK;   // does not fit: the scalar kernel takes it
+    p.chunks = chunks;
+    p.tiles_per_chunk = (p.ntx + chunks - 1) / chunks;
+    p.chunks = (p.ntx + p.tiles_per_chunk - 1) / p.tiles_per_chunk;
+    nwarps = (p.tiles_per_chunk + T - 1) / T;
+    // source bytes a chunk touches per row (window starts are rounded down to 4 pixels, the copy to 16 bytes)
+    const long long bound_px = (long long)(p.tiles_per_chunk * 16 * scale_x) + 32 * KX + 8;
+    long long bound_bytes = (bound_px * 3 + 32 + 15) & ~15LL;
+    if (bound_bytes > row_bytes) bound_bytes = row_bytes;
+    long long pitch = (bound_bytes + 127) / 128 * 128 + 48;   // 48 mod 128: see the gather in the kernel
+    if (pitch - 128 >= bound_bytes) pitch -= 128;
+    p.raw_pitch = (int)pitch;
+    smem = 128 + (size_t)kMmaStages * kBatchRows * (size_t)pitch + (size_t)p.tiles_per_chunk * 48 * CAP + 128;
+    if (smem <= max_smem) break;
+  }
+  auto kernel = bicubic_mma_kernel<KX, KY>;
+  AIKO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int threads = (nwarps + 1) * 32;
+  int per_sm = 0;
+  AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
+  if (per_sm < 1) per_sm = 1;
+  // bands of output-row groups: long enough that the rows filtered twice (the vertical support at
+  // each band edge) stay few, and a CTA count that fills whole waves of the machine
+  const long long slots = (long long)sm_count() * per_sm;
+  const double rows_per_group = 8.0 * scale_y, halo = 4.0 * (scale_y < 1.0 ? 1.0 : scale_y) + kBatchRows;
+  int best_g = 1;
+  double best = -1.0;
+  for (int gsz = 1; gsz <= p.ngy; gsz++) {
+    const long long ctas = (long long)n_frames * p.chunks * ((p.ngy + gsz - 1) / gsz);
+    const double wave_eff = (double)ctas / (double)(((ctas + slots - 1) / slots) * slots);
+    const double halo_eff = gsz * rows_per_group / (gsz * rows_per_group + halo);
+    if (wave_eff * halo_eff > best) { best = wave_eff * halo_eff; best_g = gsz; }
+  }
+  p.band_groups = env_int("AIKO_B200_BICUBIC_BAND_GROUPS", best_g);
+  if (p.band_groups < 1) p.band_groups = 1;
+  p.bands_per_frame = (p.ngy + p.band_groups - 1) / p.band_groups;
+  const long long grid = (long long)n_frames * p.chunks * p.bands_per_frame;
+  AIKO_CHECK_ARG(grid < ((long long)1 << 31), "resize_bicubic: too many bands");
+  kernel<<<(unsigned)grid, threads, smem, stream>>>(p);
+  *done = true;
+  return cuda_status(cudaGetLastError(), "bicubic_mma launch");
+}
+
+int bicubic_mma_launch(const uint8_t* src, int n_frames, int sh, int sw, int channels, uint8_t* dst, int dh, int dw,
+                       const int* ws, const BicubicLayout& l, cudaStream_t stream, bool* done) {
+  *done = false;
+  const MmaPlan& m = l.mma;
+  // RGB frames whose rows the TMA engine can copy (16-byte aligned); everything else: scalar kernel
+  if (!m.ok || channels != 3 || env_int("AIKO_B200_BICUBIC_SCALAR", 0)) return AIKO_B200_OK;
+  if (((reinterpret_cast<uintptr_t>(src) | (uintptr_t)((size_t)sw * 3)) & 15) != 0) return AIKO_B200_OK;
+  MmaParams p{};
+  p.src = src; p.dst = dst; p.ws = ws;
+  p.n = n_frames; p.sh = sh; p.sw = sw; p.dh = dh; p.dw = dw;
+  p.ntx = m.ntx; p.ngy = m.ngy;
+  p.off_xa = m.off_xa; p.off_ax = m.off_ax; p.off_ya = m.off_ya; p.off_yend = m.off_yend; p.off_by = m.off_by;
+  const double scale_y = (double)sh / dh;
+#define AIKO_MMA_CASE(KX, KY) \
+  if (m.kx == KX && m.ky == KY) return launch_mma<KX, KY>(p, n_frames, scale_y, stream, done);
+  AIKO_MMA_CASE(1, 1) AIKO_MMA_CASE(2, 1) AIKO_MMA_CASE(3, 1) AIKO_MMA_CASE(4, 1)
+  AIKO_MMA_CASE(1, 2) AIKO_MMA_CASE(2, 2) AIKO_MMA_CASE(3, 2) AIKO_MMA_CASE(4, 2)
+#undef AIKO_MMA_CASE
+  return AIKO_B200_OK;
+}
+
+}  // namespace aiko

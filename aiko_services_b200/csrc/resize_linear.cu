@@ -338,12 +338,23 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
 }
 
 // ---------------------------------------------------------------------------------------
+// kGenericRows output rows per round: the byte gathers of all of them are in flight before the
+// first result is needed, so a round pays one memory latency instead of one per row.
+template <int C>
+struct GenericRows {
+  static constexpr int value = C == 1 ? 4 : 2;   // 16 (gray) / 24-32 (colour) byte loads in flight per thread
+};
+
 template <int C>
 __global__ void __launch_bounds__(kThreads) resize_rows_generic(const ResizeParams p) {
+  constexpr int kGenericRows = GenericRows<C>::value;
   extern __shared__ __align__(128) uint8_t smem[];
   int2* xtab = reinterpret_cast<int2*>(smem);
-  size_t off = ((size_t)p.dw * 8 + 15) & ~(size_t)15;
-  uint8_t* orow = smem + off;
+  const size_t off = ((size_t)p.dw * 8 + 15) & ~(size_t)15;
+  const int row_pitch = (p.dw * C + 15) & ~15;
+  uint8_t* orows = smem + off;
+  __shared__ int4 s_coef[kGenericRows];   // y0, y1, b0 << 16, b1 << 16
+  __shared__ int2 s_where[kGenericRows];  // frame, output row
 
   for (int dx = threadIdx.x; dx < p.dw; dx += kThreads) {
     int s;
@@ -351,41 +362,70 @@ __global__ void __launch_bounds__(kThreads) resize_rows_generic(const ResizePara
     horizontal_coef(dx, p.scale_x, p.sw, &s, &c);
     xtab[dx] = make_int2(s * C, (int)c);
   }
-  __syncthreads();
 
-  const int i0 = blockIdx.x * p.items_per_cta;
-  const int i1 = min(p.items, i0 + p.items_per_cta);
-  if (i0 >= i1) return;
-  int n = i0 / p.dh, dy = i0 - n * p.dh;
   const int last_off = (p.sw - 1) * C;
-  for (int item = i0; item < i1; ++item) {
-    const RowCoef rc = vertical_coef(dy, p.scale_y, p.sh);
-    const uint32_t b0s = (uint32_t)rc.b0 << 16, b1s = (uint32_t)rc.b1 << 16;
-    const uint8_t* f = p.src + (long long)n * p.src_frame_stride;
-    const uint8_t* r0 = f + (long long)rc.y0 * p.src_row_stride;
-    const uint8_t* r1 = f + (long long)rc.y1 * p.src_row_stride;
+  const int rounds = (p.items + kGenericRows - 1) / kGenericRows;
+  for (int round = blockIdx.x; round < rounds; round += gridDim.x) {
+    const int i0 = round * kGenericRows;
+    const int nrows = min(kGenericRows, p.items - i0);
+    if (threadIdx.x < nrows) {
+      const int item = i0 + threadIdx.x;
+      const int n = item / p.dh, dy = item - n * p.dh;
+      const RowCoef rc = vertical_coef(dy, p.scale_y, p.sh);
+      s_coef[threadIdx.x] = make_int4(rc.y0, rc.y1, rc.b0 << 16, rc.b1 << 16);
+      s_where[threadIdx.x] = make_int2(n, dy);
+    }
+    __syncthreads();   // also orders xtab (first round) and the previous round's stores
     for (int dx = threadIdx.x; dx < p.dw; dx += kThreads) {
       const int2 e = xtab[dx];
       const uint32_t a0 = (uint32_t)e.y & 0xffff, a1 = (uint32_t)e.y >> 16;
       const int o0 = e.x, o1 = min(e.x + C, last_off);
+      uint32_t t[kGenericRows][C][4];
 #pragma unroll
-      for (int c = 0; c < C; c++) {
-        const uint32_t t00 = __ldg(r0 + o0 + c), t01 = __ldg(r0 + o1 + c);
-        const uint32_t t10 = __ldg(r1 + o0 + c), t11 = __ldg(r1 + o1 + c);
-        const uint32_t v = vblend_hi(t00 * a0 + t01 * a1, t10 * a0 + t11 * a1, b0s, b1s);
-        const int cc = (p.swap_rb && C >= 3 && c < 3) ? 2 - c : c;
-        orow[dx * C + cc] = (uint8_t)v;
+      for (int j = 0; j < kGenericRows; j++) {
+        if (j < nrows) {
+          const int4 rc = s_coef[j];
+          const uint8_t* f = p.src + (long long)s_where[j].x * p.src_frame_stride;
+          const uint8_t* r0 = f + (long long)rc.x * p.src_row_stride;
+          const uint8_t* r1 = f + (long long)rc.y * p.src_row_stride;
+#pragma unroll
+          for (int c = 0; c < C; c++) {
+            t[j][c][0] = __ldg(r0 + o0 + c);
+            t[j][c][1] = __ldg(r0 + o1 + c);
+            t[j][c][2] = __ldg(r1 + o0 + c);
+            t[j][c][3] = __ldg(r1 + o1 + c);
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < kGenericRows; j++) {
+        if (j < nrows) {
+          const int4 rc = s_coef[j];
+          uint8_t* orow = orows + j * row_pitch;
+#pragma unroll
+          for (int c = 0; c < C; c++) {
+            const uint32_t v = vblend_hi(t[j][c][0] * a0 + t[j][c][1] * a1, t[j][c][2] * a0 + t[j][c][3] * a1,
+                                         (uint32_t)rc.z, (uint32_t)rc.w);
+            const int cc = (p.swap_rb && C >= 3 && c < 3) ? 2 - c : c;
+            orow[dx * C + cc] = (uint8_t)v;
+          }
+        }
       }
     }
     __syncthreads();
     if (C == 3 && p.has_overlay) {
-      const int ob = p.ov.op_offsets[n];
-      overlay_apply_row(p.ov.ops + ob, p.ov.op_offsets[n + 1] - ob, p.ov, dy, p.dw, orow, kThreads);
+      for (int j = 0; j < nrows; j++) {
+        const int n = s_where[j].x;
+        const int ob = p.ov.op_offsets[n];
+        overlay_apply_row(p.ov.ops + ob, p.ov.op_offsets[n + 1] - ob, p.ov, s_where[j].y, p.dw, orows + j * row_pitch,
+                          kThreads);
+      }
       __syncthreads();
     }
-    store_row(p.dst + (long long)n * p.dst_frame_stride + (long long)dy * p.dst_row_stride, orow, p.dw * C);
-    __syncthreads();  // orow is rewritten by the next item
-    if (++dy == p.dh) { dy = 0; ++n; }
+    for (int j = 0; j < nrows; j++)
+      store_row(p.dst + (long long)s_where[j].x * p.dst_frame_stride + (long long)s_where[j].y * p.dst_row_stride,
+                orows + j * row_pitch, p.dw * C);
+    __syncthreads();  // rows and their records are rewritten by the next round
   }
 }
 
@@ -443,7 +483,8 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
 
 template <int C>
 static int launch_generic(ResizeParams p, cudaStream_t stream) {
-  const size_t smem = (((size_t)p.dw * 8 + 15) & ~(size_t)15) + (((size_t)p.dw * C + 15) & ~(size_t)15);
+  constexpr int kGenericRows = GenericRows<C>::value;
+  const size_t smem = (((size_t)p.dw * 8 + 15) & ~(size_t)15) + kGenericRows * (((size_t)p.dw * C + 15) & ~(size_t)15);
   const int max_smem = device_max_smem_optin();
   if (smem > (size_t)max_smem) {
     set_last_error("resize_linear: destination width %d needs %zu bytes of shared memory (max %d)", p.dw, smem,
@@ -454,10 +495,9 @@ static int launch_generic(ResizeParams p, cudaStream_t stream) {
   int per_sm = 0;
   AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resize_rows_generic<C>, kThreads, smem));
   if (per_sm < 1) per_sm = 1;
-  long long grid = (long long)sm_count() * per_sm;
-  if (grid > p.items) grid = p.items;
-  p.items_per_cta = (int)((p.items + grid - 1) / grid);
-  grid = (p.items + p.items_per_cta - 1) / p.items_per_cta;
+  const long long rounds = ((long long)p.items + kGenericRows - 1) / kGenericRows;
+  long long grid = (long long)sm_count() * per_sm;   // resident CTAs stride over the rounds
+  if (grid > rounds) grid = rounds;
   resize_rows_generic<C><<<(unsigned)grid, kThreads, smem, stream>>>(p);
   return cuda_status(cudaGetLastError(), "resize_rows_generic launch");
 }

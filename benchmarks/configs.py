@@ -85,11 +85,11 @@ def main():
     report("flip horizontal 1080p", 32, "frames", 2 * 6_220_800, ms)
     del sw, gray
 
-    uhd = [torch.randint(0, 256, (8, 2160, 3840, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
-    nchw = torch.empty((8, 3, 224, 224), dtype=torch.float32, device=dev)
+    uhd = [torch.randint(0, 256, (32, 2160, 3840, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+    nchw = torch.empty((32, 3, 224, 224), dtype=torch.float32, device=dev)
     ms = timed(lambda i: ops.resize_norm_f32(uhd[i % rot], 224, 224, (0.485, 0.456, 0.406), (0.229, 0.224, 0.225),
                                              out=nchw), args.steps)
-    report("resize_norm_f32 4K->224x224 NCHW (config 4, batch 8)", 8, "frames", 4_272_128, ms)
+    report("resize_norm_f32 4K->224x224 NCHW (config 4, batch 32)", 32, "frames", 4_272_128, ms)
     del uhd
 
     t = np.arange(16000) / 16000.0

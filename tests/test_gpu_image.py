@@ -124,6 +124,50 @@ def test_resize_bicubic_cfg1_batch(cuda):
         assert (host(ops.resize_bicubic_aa(dev(img, cuda), 77, 51)) == v).all()
 
 
+TENSOR_CORE_SHAPES = [   # (h, w, H, W): RGB rows that are 16-byte aligned take the tensor-core kernel
+    (270, 480, 120, 160),    # the config-1 ratio (3 x 2.25): two K steps along x, one along y
+    (120, 160, 270, 480),    # upscale
+    (200, 320, 200, 100),    # height unchanged (identity vertical table)
+    (64, 64, 64, 64),        # both unchanged
+    (301, 208, 77, 51),      # odd targets: partial last tile and last row group
+    (480, 640, 100, 131),    # scale ~4.9 x 4.8: four K steps along x, two along y
+    (90, 1600, 45, 1000),    # wide: more tiles than one CTA owns -> several column chunks
+    (33, 48, 5, 7), (16, 16, 1, 1), (8, 16, 40, 300)]
+
+
+@pytest.mark.parametrize("shape", TENSOR_CORE_SHAPES, ids=lambda s: "%dx%d_to_%dx%d" % (s[1], s[0], s[3], s[2]))
+def test_resize_bicubic_tensor_core_path_vs_oracle(cuda, shape, monkeypatch):
+    h, w, H, W = shape
+    frames = np.stack([cases.frame(7000 + k, h, w, 3) for k in range(3)])
+    want = np.stack([O.resize_bicubic_aa(f, W, H) for f in frames])
+    d = dev(frames, cuda)
+    np.testing.assert_array_equal(host(ops.resize_bicubic_aa(d, W, H)), want)
+    # band and chunk edges: one row group per CTA, three column chunks
+    monkeypatch.setenv("AIKO_B200_BICUBIC_BAND_GROUPS", "1")
+    monkeypatch.setenv("AIKO_B200_BICUBIC_CHUNKS", "3")
+    np.testing.assert_array_equal(host(ops.resize_bicubic_aa(d, W, H)), want)
+    monkeypatch.setenv("AIKO_B200_BICUBIC_BAND_GROUPS", "3")
+    monkeypatch.setenv("AIKO_B200_BICUBIC_CHUNKS", "2")
+    np.testing.assert_array_equal(host(ops.resize_bicubic_aa(d, W, H)), want)
+
+
+def test_resize_bicubic_tensor_core_equals_scalar_kernel(cuda, monkeypatch):
+    """Full-size batch: the two kernels behind the entry point agree byte for byte."""
+    g = torch.Generator(device=cuda).manual_seed(3)
+    src = torch.randint(0, 256, (8, 1080, 1920, 3), dtype=torch.uint8, device=cuda, generator=g)
+    src[0, :, :960] = 255
+    src[1, :540] = 0
+    fast = ops.resize_bicubic_aa(src, 640, 480)
+    monkeypatch.setenv("AIKO_B200_BICUBIC_SCALAR", "1")
+    slow = ops.resize_bicubic_aa(src, 640, 480)
+    torch.cuda.synchronize()
+    assert torch.equal(fast, slow)
+    monkeypatch.delenv("AIKO_B200_BICUBIC_SCALAR")
+    up = ops.resize_bicubic_aa(src[:2, :480, :640].contiguous(), 1920, 1080)
+    monkeypatch.setenv("AIKO_B200_BICUBIC_SCALAR", "1")
+    assert torch.equal(up, ops.resize_bicubic_aa(src[:2, :480, :640].contiguous(), 1920, 1080))
+
+
 def test_resize_bicubic_workspace_errors(cuda):
     from aiko_services_b200 import _native
     lib = _native.lib()

@@ -32,7 +32,7 @@ def _noalloc(lib, src, dst_h, dst_w):
 
 def test_noalloc_matches_workspace_entry_point_twice_in_a_row(cuda):
     lib = _native.lib()
-    shapes = [((3, 1080, 1920, 3), (480, 640)),      # 73 KB of tables
+    shapes = [((3, 1080, 1920, 3), (480, 640)),      # 237 KB of tables (coefficients + tensor-core operand tables)
               ((2, 97, 131, 3), (41, 50)),           # much smaller tables: the rest of the array keeps call 1's
               ((2, 60, 64, 1), (20, 64))]            # width unchanged: identity horizontal table
     for i, (shape, (dh, dw)) in enumerate(shapes):
