@@ -27,7 +27,6 @@ namespace aiko {
 
 constexpr int kBatchRows = 8;        // source rows per staging buffer = N of the horizontal MMA
 constexpr int kMmaStages = 2;
-constexpr int kMmaMaxWarps = 11;     // consumer warps per CTA (+ 1 producer warp)
 
 // ---------------------------------------------------------------------------------------------
 // Table builders (run once per size pair by aiko_b200_resize_bicubic_prepare, after the
@@ -153,23 +152,76 @@ __device__ __forceinline__ void mma_u8s8(int (&d)[4], uint32_t a0, uint32_t a1, 
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-__device__ __forceinline__ uint32_t clip8_acc(int acc) {
-  return (uint32_t)min(max(acc >> kPrecisionBits, 0), 255);
+// Three plane sums -> the 32-bit sum Pillow forms (wrapping), with the rounding constant already
+// inside s0; two of them shifted down, saturated to bytes and packed (lo | hi << 8) by one
+// cvt.pack.sat.
+__device__ __forceinline__ int combine_planes(int s2, int s1, int s0) {
+  return (int)((((((uint32_t)s2) << 8) + (uint32_t)s1) << 8) + (uint32_t)s0);
+}
+__device__ __forceinline__ uint32_t pack2_sat_u8(int lo, int hi) {
+  uint32_t d;
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(hi >> kPrecisionBits), "r"(lo >> kPrecisionBits), "r"(0));
+  return d;
 }
 
-template <int KX>
-struct TilesPerWarp {
-  static constexpr int value = KX == 1 ? 8 : (KX == 2 ? 4 : 2);   // 12 * KX * T <= 96 weight registers
+// Horizontal pass of one warp: 8 staged rows x NT tiles -> 8 rows of the ring.  NT is a template
+// parameter so the tiles unroll without branches and their loads, MMAs and epilogues interleave.
+template <int KX, int T, int CAP, int NT, int FIRST = 0>
+__device__ __forceinline__ void horizontal_tiles(const uint4 (&A)[T][3][KX], const int (&xoff)[T],
+                                                 const uint8_t* __restrict__ rrow, uint8_t* __restrict__ ring_out,
+                                                 int q) {
+  constexpr int kRound = 1 << (kPrecisionBits - 1);
+#pragma unroll
+  for (int t = FIRST; t < FIRST + NT; t++) {
+    uint32_t B[KX][2][3];
+#pragma unroll
+    for (int ks = 0; ks < KX; ks++)
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        // 4 pixels = 12 interleaved bytes = 3 words -> one register per channel.  Row pitch
+        // 12 words mod 32 and 3 words per lane: the 32 lanes of each load hit 32 banks.
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(rrow + xoff[t] + (32 * ks + 16 * h + 4 * q) * 3);
+        const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+        B[ks][h][0] = __byte_perm(__byte_perm(w0, w1, 0x0630), w2, 0x5210);
+        B[ks][h][1] = __byte_perm(__byte_perm(w0, w1, 0x0741), w2, 0x6210);
+        B[ks][h][2] = __byte_perm(__byte_perm(w0, w1, 0x0052), w2, 0x7410);
+      }
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      // one accumulator set per weight plane: three independent MMA chains
+      int s2[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, s0[4] = {kRound, kRound, kRound, kRound};
+#pragma unroll
+      for (int ks = 0; ks < KX; ks++) {
+        mma_s8u8(s2, A[t][2][ks].x, A[t][2][ks].y, A[t][2][ks].z, A[t][2][ks].w, B[ks][0][c], B[ks][1][c]);
+        mma_u8u8(s1, A[t][1][ks].x, A[t][1][ks].y, A[t][1][ks].z, A[t][1][ks].w, B[ks][0][c], B[ks][1][c]);
+        mma_u8u8(s0, A[t][0][ks].x, A[t][0][ks].y, A[t][0][ks].z, A[t][0][ks].w, B[ks][0][c], B[ks][1][c]);
+      }
+      // element 0, 1: pixel g, rows 2q, 2q + 1;  element 2, 3: pixel g + 8 (ring_out is at pixel g, row 2q)
+      uint8_t* o = ring_out + (size_t)(t * 48 + c) * CAP;
+      *reinterpret_cast<uint16_t*>(o) = (uint16_t)pack2_sat_u8(combine_planes(s2[0], s1[0], s0[0]),
+                                                               combine_planes(s2[1], s1[1], s0[1]));
+      *reinterpret_cast<uint16_t*>(o + 24 * CAP) = (uint16_t)pack2_sat_u8(combine_planes(s2[2], s1[2], s0[2]),
+                                                                          combine_planes(s2[3], s1[3], s0[3]));
+    }
+  }
+}
+
+// A consumer warp keeps the weights of its T tiles in 12 * KX * T registers (96 for the settings
+// used: 10 consumer warps + the producer warp at <= 168 registers).  More, thinner warps (T halved,
+// 20 warps) and a producer-less variant with 12 evenly loaded warps were both measured slower
+// (99 / 101 us against 87 us for 32 x 1080p): spills, and more per-warp overhead per batch.
+template <int KX, int T>
+struct WarpBudget {
+  static constexpr int max_warps = 10;   // consumers
 };
 
-template <int KX, int KY>
-__global__ void __launch_bounds__((kMmaMaxWarps + 1) * 32, 1) bicubic_mma_kernel(const MmaParams p) {
-  constexpr int T = TilesPerWarp<KX>::value;
+template <int KX, int KY, int T>
+__global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bicubic_mma_kernel(const MmaParams p) {
   constexpr int CAP = 32 * KY + 16;   // ring rows: one K window + the rows a batch runs ahead, rounded;
                                       // as a pitch (bytes) it is 16 mod 32, which keeps the loads below conflict-free
   extern __shared__ __align__(128) uint8_t smem[];
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-  uint64_t* empty = full + kMmaStages;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);      // per staging buffer: its rows have landed
+  uint64_t* empty = full + kMmaStages;                     // per staging buffer: every consumer is done with it
   uint8_t* raw = smem + 128;
   uint8_t* ring = raw + (size_t)kMmaStages * kBatchRows * p.raw_pitch;   // [byte column][CAP rows]
 
@@ -188,16 +240,19 @@ __global__ void __launch_bounds__((kMmaMaxWarps + 1) * 32, 1) bicubic_mma_kernel
   const int* xa = p.ws + p.off_xa;
   const int* ya = p.ws + p.off_ya;
   const int* yend = p.ws + p.off_yend;
-  if (__ldg(p.ws + 1) != 0) __trap();   // a weight or window outside what the tables can hold (cannot happen
-                                        // for the sizes MmaPlan.ok admits; better loud than wrong)
+  const int flag = __ldg(p.ws + 1);
   const int row_bytes = p.sw * 3;
   const int row_start = __ldg(ya + j0), row_end = __ldg(yend + j1 - 1);
+  const int xa_lo = __ldg(xa + tile0), xa_hi = __ldg(xa + tile1 - 1);
+  if (flag != 0) __trap();   // a weight or window outside what the tables can hold (cannot happen for the
+                             // sizes MmaPlan.ok admits; better loud than wrong)
   const int nbatches = (row_end - row_start + kBatchRows - 1) / kBatchRows;
-  const int byte_lo = (__ldg(xa + tile0) * 3) & ~15;
-  const int byte_hi = min(row_bytes, ((__ldg(xa + tile1 - 1) + 32 * KX) * 3 + 15) & ~15);
+  const int byte_lo = (xa_lo * 3) & ~15;
+  const int byte_hi = min(row_bytes, ((xa_hi + 32 * KX) * 3 + 15) & ~15);
   const int copy_bytes = byte_hi - byte_lo;
   if (copy_bytes > p.raw_pitch) __trap();
 
+  const uint8_t* fsrc = p.src + (size_t)frame * p.sh * row_bytes + byte_lo;
   if (threadIdx.x == 0) {
     for (int s = 0; s < kMmaStages; s++) {
       mbar_init(&full[s], 1);
@@ -207,25 +262,24 @@ __global__ void __launch_bounds__((kMmaMaxWarps + 1) * 32, 1) bicubic_mma_kernel
   }
   __syncthreads();
 
-  const uint8_t* fsrc = p.src + (size_t)frame * p.sh * row_bytes;
   if (warp == nwarps) {
-    // ---- producer -----------------------------------------------------------------------------
-    if (lane != 0) return;
+    // ---- producer: lanes 0..7 each ask the TMA engine for one source row of the batch ------------
     for (int b = 0; b < nbatches; b++) {
       const int s = b % kMmaStages, round = b / kMmaStages;
       if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1), 1000, 100);
-      uint8_t* d = raw + (size_t)s * kBatchRows * p.raw_pitch;
-      for (int r = 0; r < kBatchRows; r++) {
-        const int row = min(row_start + b * kBatchRows + r, p.sh - 1);   // rows past the frame carry no weight
-        bulk_g2s(d + (size_t)r * p.raw_pitch, fsrc + (size_t)row * row_bytes + byte_lo, (uint32_t)copy_bytes, &full[s]);
+      if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)(kBatchRows * copy_bytes));
+      __syncwarp();
+      if (lane < kBatchRows) {
+        const int row = min(row_start + b * kBatchRows + lane, p.sh - 1);   // rows past the frame carry no weight
+        bulk_g2s(raw + (size_t)(s * kBatchRows + lane) * p.raw_pitch, fsrc + (size_t)row * row_bytes,
+                 (uint32_t)copy_bytes, &full[s]);
       }
-      mbar_expect_tx(&full[s], (uint32_t)(kBatchRows * copy_bytes));
     }
     return;
   }
   if (warp >= active) return;
 
-  // ---- consumers ------------------------------------------------------------------------------
+  // ---- consumers: horizontal pass, ring and vertical pass of the warp's own tiles ---------------
   const int wtile0 = tile0 + warp * T;
   const int ntw = min(T, tile1 - wtile0);
   const int wcol0 = warp * T * 48;                    // first ring column (byte column inside the chunk)
@@ -234,7 +288,7 @@ __global__ void __launch_bounds__((kMmaMaxWarps + 1) * 32, 1) bicubic_mma_kernel
   const uint4* ax = reinterpret_cast<const uint4*>(p.ws + p.off_ax);
 #pragma unroll
   for (int t = 0; t < T; t++) {
-    const bool on = t < ntw;
+    const bool on = t < ntw;       // a slot without a tile gets zero weights and is filtered like the others
     xoff[t] = on ? __ldg(xa + wtile0 + t) * 3 - byte_lo : 0;
 #pragma unroll
     for (int pl = 0; pl < 3; pl++)
@@ -246,53 +300,25 @@ __global__ void __launch_bounds__((kMmaMaxWarps + 1) * 32, 1) bicubic_mma_kernel
   uint8_t* fdst = p.dst + (size_t)frame * p.dh * p.dw * 3;
   const int out_row_bytes = p.dw * 3;
   const int gcol0 = tile0 * 48 + wcol0;               // first output byte column of this warp
+  const bool cols_inside = gcol0 + ntw * 48 <= out_row_bytes;
+  constexpr int kRound = 1 << (kPrecisionBits - 1);
 
   int jn = j0;          // next group of output rows to emit
   int slot = 0;         // ring row of the batch being filtered
+  // the next group's record and weights are fetched a group ahead, so no batch waits on L2 for them
+  int g_end = __ldg(yend + j0) - row_start, g_base = 0;
+  uint2 W[3][KY];
+#pragma unroll
+  for (int pl = 0; pl < 3; pl++)
+#pragma unroll
+    for (int ks = 0; ks < KY; ks++) W[pl][ks] = __ldg(byf + ((size_t)(j0 * 3 + pl) * KY + ks) * 32 + lane);
   for (int b = 0; b < nbatches; b++) {
     const int s = b % kMmaStages, round = b / kMmaStages;
     mbar_wait(&full[s], (uint32_t)(round & 1), 500, 0);
     // -- horizontal pass: 8 staged rows x this warp's tiles -> ring rows slot .. slot + 7
     const uint8_t* rrow = raw + (size_t)(s * kBatchRows + g) * p.raw_pitch;
-#pragma unroll
-    for (int t = 0; t < T; t++) {
-      if (t < ntw) {
-        uint32_t B[KX][2][3];
-#pragma unroll
-        for (int ks = 0; ks < KX; ks++)
-#pragma unroll
-          for (int h = 0; h < 2; h++) {
-            // 4 pixels = 12 interleaved bytes = 3 words -> one register per channel.  Row pitch
-            // 12 words mod 32 and 3 words per lane: the 32 lanes of each load hit 32 banks.
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(rrow + xoff[t] + (32 * ks + 16 * h + 4 * q) * 3);
-            const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
-            B[ks][h][0] = __byte_perm(__byte_perm(w0, w1, 0x0630), w2, 0x5210);
-            B[ks][h][1] = __byte_perm(__byte_perm(w0, w1, 0x0741), w2, 0x6210);
-            B[ks][h][2] = __byte_perm(__byte_perm(w0, w1, 0x0052), w2, 0x7410);
-          }
-#pragma unroll
-        for (int c = 0; c < 3; c++) {
-          int acc[4] = {32, 32, 32, 32};   // (1 << 21) >> 16: the rounding constant, shifted up with the top plane
-#pragma unroll
-          for (int ks = 0; ks < KX; ks++)
-            mma_s8u8(acc, A[t][2][ks].x, A[t][2][ks].y, A[t][2][ks].z, A[t][2][ks].w, B[ks][0][c], B[ks][1][c]);
-#pragma unroll
-          for (int i = 0; i < 4; i++) acc[i] <<= 8;
-#pragma unroll
-          for (int ks = 0; ks < KX; ks++)
-            mma_u8u8(acc, A[t][1][ks].x, A[t][1][ks].y, A[t][1][ks].z, A[t][1][ks].w, B[ks][0][c], B[ks][1][c]);
-#pragma unroll
-          for (int i = 0; i < 4; i++) acc[i] <<= 8;
-#pragma unroll
-          for (int ks = 0; ks < KX; ks++)
-            mma_u8u8(acc, A[t][0][ks].x, A[t][0][ks].y, A[t][0][ks].z, A[t][0][ks].w, B[ks][0][c], B[ks][1][c]);
-          // acc[0], acc[1]: pixel g, rows 2q, 2q + 1;  acc[2], acc[3]: pixel g + 8
-          uint8_t* o = ring + (size_t)(wcol0 + (t * 16 + g) * 3 + c) * CAP + slot + 2 * q;
-          *reinterpret_cast<uint16_t*>(o) = (uint16_t)(clip8_acc(acc[0]) | (clip8_acc(acc[1]) << 8));
-          *reinterpret_cast<uint16_t*>(o + 24 * CAP) = (uint16_t)(clip8_acc(acc[2]) | (clip8_acc(acc[3]) << 8));
-        }
-      }
-    }
+    uint8_t* ring_out = ring + (size_t)(wcol0 + g * 3) * CAP + slot + 2 * q;
+    horizontal_tiles<KX, T, CAP, T>(A, xoff, rrow, ring_out, q);   // slots without a tile: zero weights, spare columns
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[s]);     // the staged rows are free again
     slot += kBatchRows;
@@ -300,13 +326,8 @@ __global__ void __launch_bounds__((kMmaMaxWarps + 1) * 32, 1) bicubic_mma_kernel
     const int produced = (b + 1) * kBatchRows;
 
     // -- vertical pass for every group of 8 output rows whose last intermediate row now exists
-    while (jn < j1 && __ldg(yend + jn) - row_start <= produced) {
-      const int base = (__ldg(ya + jn) - row_start) % CAP;
-      uint2 W[3][KY];
-#pragma unroll
-      for (int pl = 0; pl < 3; pl++)
-#pragma unroll
-        for (int ks = 0; ks < KY; ks++) W[pl][ks] = __ldg(byf + ((size_t)(jn * 3 + pl) * KY + ks) * 32 + lane);
+    while (jn < j1 && g_end <= produced) {
+      const int base = g_base % CAP;
       int o0[KY], o1[KY];
 #pragma unroll
       for (int ks = 0; ks < KY; ks++) {
@@ -316,41 +337,53 @@ __global__ void __launch_bounds__((kMmaMaxWarps + 1) * 32, 1) bicubic_mma_kernel
         if (o1[ks] >= CAP) o1[ks] -= CAP;
       }
       const int dy = jn * 8 + 2 * q;
+      const bool inside = cols_inside && jn * 8 + 8 <= p.dh;   // no clipping of this group's stores
+      uint8_t* orow = fdst + (size_t)dy * out_row_bytes + gcol0 + g;
+#pragma unroll 3
       for (int mt = 0; mt < ntw * 3; mt++) {
         const uint8_t* c0 = ring + (size_t)(wcol0 + mt * 16 + g) * CAP;
         const uint8_t* c1 = c0 + 8 * CAP;
-        uint32_t a[KY][4];
+        int s2[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, s0[4] = {kRound, kRound, kRound, kRound};
 #pragma unroll
         for (int ks = 0; ks < KY; ks++) {
-          a[ks][0] = *reinterpret_cast<const uint32_t*>(c0 + o0[ks]);
-          a[ks][1] = *reinterpret_cast<const uint32_t*>(c1 + o0[ks]);
-          a[ks][2] = *reinterpret_cast<const uint32_t*>(c0 + o1[ks]);
-          a[ks][3] = *reinterpret_cast<const uint32_t*>(c1 + o1[ks]);
+          const uint32_t a0 = *reinterpret_cast<const uint32_t*>(c0 + o0[ks]);
+          const uint32_t a1 = *reinterpret_cast<const uint32_t*>(c1 + o0[ks]);
+          const uint32_t a2 = *reinterpret_cast<const uint32_t*>(c0 + o1[ks]);
+          const uint32_t a3 = *reinterpret_cast<const uint32_t*>(c1 + o1[ks]);
+          mma_u8s8(s2, a0, a1, a2, a3, W[2][ks].x, W[2][ks].y);
+          mma_u8u8(s1, a0, a1, a2, a3, W[1][ks].x, W[1][ks].y);
+          mma_u8u8(s0, a0, a1, a2, a3, W[0][ks].x, W[0][ks].y);
         }
-        int acc[4] = {32, 32, 32, 32};
-#pragma unroll
-        for (int ks = 0; ks < KY; ks++) mma_u8s8(acc, a[ks][0], a[ks][1], a[ks][2], a[ks][3], W[2][ks].x, W[2][ks].y);
-#pragma unroll
-        for (int i = 0; i < 4; i++) acc[i] <<= 8;
-#pragma unroll
-        for (int ks = 0; ks < KY; ks++) mma_u8u8(acc, a[ks][0], a[ks][1], a[ks][2], a[ks][3], W[1][ks].x, W[1][ks].y);
-#pragma unroll
-        for (int i = 0; i < 4; i++) acc[i] <<= 8;
-#pragma unroll
-        for (int ks = 0; ks < KY; ks++) mma_u8u8(acc, a[ks][0], a[ks][1], a[ks][2], a[ks][3], W[0][ks].x, W[0][ks].y);
-        // acc[0], acc[1]: byte column g, output rows dy, dy + 1;  acc[2], acc[3]: byte column g + 8
-        const int col = gcol0 + mt * 16 + g;
-        uint8_t* orow = fdst + (size_t)dy * out_row_bytes;
-        if (dy < p.dh) {
-          if (col < out_row_bytes) orow[col] = (uint8_t)clip8_acc(acc[0]);
-          if (col + 8 < out_row_bytes) orow[col + 8] = (uint8_t)clip8_acc(acc[2]);
-        }
-        if (dy + 1 < p.dh) {
-          if (col < out_row_bytes) orow[out_row_bytes + col] = (uint8_t)clip8_acc(acc[1]);
-          if (col + 8 < out_row_bytes) orow[out_row_bytes + col + 8] = (uint8_t)clip8_acc(acc[3]);
+        // element 0, 1: byte column g, output rows dy, dy + 1;  element 2, 3: byte column g + 8
+        const uint32_t lo = pack2_sat_u8(combine_planes(s2[0], s1[0], s0[0]), combine_planes(s2[1], s1[1], s0[1]));
+        const uint32_t hi = pack2_sat_u8(combine_planes(s2[2], s1[2], s0[2]), combine_planes(s2[3], s1[3], s0[3]));
+        uint8_t* o = orow + mt * 16;
+        if (inside) {
+          o[0] = (uint8_t)lo;
+          o[8] = (uint8_t)hi;
+          o[out_row_bytes] = (uint8_t)(lo >> 8);
+          o[out_row_bytes + 8] = (uint8_t)(hi >> 8);
+        } else {
+          const int col = gcol0 + mt * 16 + g;
+          if (dy < p.dh) {
+            if (col < out_row_bytes) o[0] = (uint8_t)lo;
+            if (col + 8 < out_row_bytes) o[8] = (uint8_t)hi;
+          }
+          if (dy + 1 < p.dh) {
+            if (col < out_row_bytes) o[out_row_bytes] = (uint8_t)(lo >> 8);
+            if (col + 8 < out_row_bytes) o[out_row_bytes + 8] = (uint8_t)(hi >> 8);
+          }
         }
       }
       jn++;
+      if (jn < j1) {
+        g_end = __ldg(yend + jn) - row_start;
+        g_base = __ldg(ya + jn) - row_start;
+#pragma unroll
+        for (int pl = 0; pl < 3; pl++)
+#pragma unroll
+          for (int ks = 0; ks < KY; ks++) W[pl][ks] = __ldg(byf + ((size_t)(jn * 3 + pl) * KY + ks) * 32 + lane);
+      }
     }
     __syncwarp();   // ring rows read above are rewritten by later batches
   }
@@ -361,9 +394,9 @@ static int env_int(const char* name, int fallback) {
   return v ? atoi(v) : fallback;
 }
 
-template <int KX, int KY>
+template <int KX, int KY, int T>
 static int launch_mma(MmaParams p, int n_frames, double scale_y, cudaStream_t stream, bool* done) {
-  constexpr int T = TilesPerWarp<KX>::value;
+  constexpr int kMmaMaxWarps = WarpBudget<KX, T>::max_warps;
   constexpr int CAP = 32 * KY + 16;
   const int row_bytes = p.sw * 3;
   const double scale_x = (double)p.sw / p.dw;
@@ -385,10 +418,10 @@ static int launch_mma(MmaParams p, int n_frames, double scale_y, cudaStream_t st
     long long pitch = (bound_bytes + 127) / 128 * 128 + 48;   // 48 mod 128: see the gather in the kernel
     if (pitch - 128 >= bound_bytes) pitch -= 128;
     p.raw_pitch = (int)pitch;
-    smem = 128 + (size_t)kMmaStages * kBatchRows * (size_t)pitch + (size_t)p.tiles_per_chunk * 48 * CAP + 128;
+    smem = 128 + (size_t)kMmaStages * kBatchRows * (size_t)pitch + (size_t)nwarps * T * 48 * CAP + 128;
     if (smem <= max_smem) break;
   }
-  auto kernel = bicubic_mma_kernel<KX, KY>;
+  auto kernel = bicubic_mma_kernel<KX, KY, T>;
   AIKO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int threads = (nwarps + 1) * 32;
   int per_sm = 0;
@@ -429,10 +462,10 @@ int bicubic_mma_launch(const uint8_t* src, int n_frames, int sh, int sw, int cha
   p.ntx = m.ntx; p.ngy = m.ngy;
   p.off_xa = m.off_xa; p.off_ax = m.off_ax; p.off_ya = m.off_ya; p.off_yend = m.off_yend; p.off_by = m.off_by;
   const double scale_y = (double)sh / dh;
-#define AIKO_MMA_CASE(KX, KY) \
-  if (m.kx == KX && m.ky == KY) return launch_mma<KX, KY>(p, n_frames, scale_y, stream, done);
-  AIKO_MMA_CASE(1, 1) AIKO_MMA_CASE(2, 1) AIKO_MMA_CASE(3, 1) AIKO_MMA_CASE(4, 1)
-  AIKO_MMA_CASE(1, 2) AIKO_MMA_CASE(2, 2) AIKO_MMA_CASE(3, 2) AIKO_MMA_CASE(4, 2)
+#define AIKO_MMA_CASE(KX, KY, T) \
+  if (m.kx == KX && m.ky == KY) return launch_mma<KX, KY, T>(p, n_frames, scale_y, stream, done);
+  AIKO_MMA_CASE(1, 1, 8) AIKO_MMA_CASE(2, 1, 4) AIKO_MMA_CASE(3, 1, 2) AIKO_MMA_CASE(4, 1, 2)
+  AIKO_MMA_CASE(1, 2, 8) AIKO_MMA_CASE(2, 2, 4) AIKO_MMA_CASE(3, 2, 2) AIKO_MMA_CASE(4, 2, 2)
 #undef AIKO_MMA_CASE
   return AIKO_B200_OK;
 }

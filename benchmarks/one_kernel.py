@@ -1,0 +1,73 @@
+"""Launch one op a few times on its BASELINE-sized input: the target of `ncu -k <kernel>` captures
+and of quick A/B timings (`--time`), e.g.
+
+    python benchmarks/one_kernel.py bicubic --time
+    ncu --set full --clock-control none --import-source on -k regex:bicubic_mma -c 2 -o gpurun_out/bicubic \
+        python benchmarks/one_kernel.py bicubic
+"""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from aiko_services_b200 import audio_ops, ops  # noqa: E402
+
+
+def make(name, dev):
+    g = torch.Generator(device=dev).manual_seed(1)
+    rot = 4
+    if name in ("bicubic", "linear", "flip", "swap_rb", "bgr2gray"):
+        hd = [torch.randint(0, 256, (32, 1080, 1920, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+        if name == "bicubic":
+            out = torch.empty((32, 480, 640, 3), dtype=torch.uint8, device=dev)
+            return lambda i: ops.resize_bicubic_aa(hd[i % rot], 640, 480, out=out), 32
+        if name == "linear":
+            out = torch.empty((32, 480, 640, 3), dtype=torch.uint8, device=dev)
+            return lambda i: ops.resize_linear(hd[i % rot], 640, 480, out=out), 32
+        if name == "bgr2gray":
+            gray = torch.empty((32, 1080, 1920), dtype=torch.uint8, device=dev)
+            return lambda i: ops.bgr2gray(hd[i % rot], out=gray), 32
+        out = torch.empty_like(hd[0])
+        if name == "flip":
+            return lambda i: ops.flip(hd[i % rot], 1, out=out), 32
+        return lambda i: ops.swap_rb(hd[i % rot], out=out), 32
+    if name in ("audio", "fft"):
+        t = np.arange(16000) / 16000.0
+        freqs = np.geomspace(50, 7000, 1024)
+        rng = np.random.default_rng(5000)
+        win = (3000 * np.sin(2 * np.pi * freqs[:, None] * t[None, :]) + rng.normal(0, 200, (1024, 16000))).astype(np.int16)
+        aud = [torch.from_numpy(np.roll(win, k, axis=0)).to(dev) for k in range(rot)]
+        if name == "audio":
+            return lambda i: audio_ops.audio_chain(aud[i % rot], 16000), 1024
+        return lambda i: audio_ops.audio_chain(aud[i % rot], 16000, bands=False, top=False), 1024
+    raise SystemExit(f"unknown op {name}")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("op")
+    ap.add_argument("--time", action="store_true")
+    ap.add_argument("--steps", type=int, default=50)
+    args = ap.parse_args()
+    dev = torch.device("cuda:0")
+    fn, units = make(args.op, dev)
+    for i in range(3):
+        fn(i)
+    torch.cuda.synchronize()
+    if args.time:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) / args.steps * 1e3
+        tag = " ".join(f"{k}={v}" for k, v in sorted(os.environ.items()) if k.startswith("AIKO_B200_"))
+        print(f"{args.op}: {us:.1f} us per launch, {units / us * 1e6:.0f} units/s {tag}")
+
+
+if __name__ == "__main__":
+    main()
