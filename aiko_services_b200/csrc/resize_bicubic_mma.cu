@@ -17,10 +17,14 @@
 //                     A = the uint8 intermediate image, held transposed ([byte column][row]) in a
 //                     shared-memory ring that the horizontal epilogue writes; B = weights.
 //
-// A CTA owns (frame, band of output rows, range of 16-pixel tiles).  Inside it every consumer
-// warp owns a fixed run of tiles and does horizontal pass, ring and vertical pass for those
-// columns alone, so warps synchronise only with the producer warp (full / empty mbarriers of the
-// two staging buffers), never with each other.
+// A work item is (frame, band of output rows, chunk of 16-pixel tiles); persistent CTAs stride over
+// the items.  Inside a CTA every consumer warp owns a fixed run of tiles and does horizontal pass,
+// ring and vertical pass for those columns alone, so warps synchronise only with the producer
+// warp (full / empty mbarriers of the two staging buffers), never with each other.
+//
+// tcgen05 is not used on purpose: the weight matrices are banded (12 taps wide at scale 3), and
+// the band fills 19 % of a 16-output x 64-pixel block but only 3-5 % of the 64/128-row blocks
+// tcgen05.mma works on, which costs more than its higher rate returns.
 #include "bicubic.cuh"
 
 namespace aiko {
@@ -130,6 +134,7 @@ struct MmaParams {
   int band_groups, bands_per_frame;   // output-row groups (8 rows) per CTA
   int chunks, tiles_per_chunk;        // 16-pixel tiles per CTA
   int raw_pitch;                      // bytes between staged source rows (= 48 mod 128: see gather)
+  int items;                          // n * bands_per_frame * chunks
 };
 
 // D += A x B, m16n8k32, 8-bit operands, wrapping 32-bit accumulators.
@@ -215,6 +220,36 @@ struct WarpBudget {
   static constexpr int max_warps = 10;   // consumers
 };
 
+// What one work item (frame, band of output-row groups, chunk of tiles) covers.
+struct MmaItem {
+  int frame, j0, j1, tile0, tile1;
+  int row_start, nbatches;     // first source row, batches of 8 rows
+  int byte_lo, copy_bytes;     // source bytes per row the chunk needs
+};
+template <int KX>
+__device__ __forceinline__ MmaItem mma_item(const MmaParams& p, int item) {
+  MmaItem it;
+  const int chunk = item % p.chunks;
+  item /= p.chunks;
+  const int band = item % p.bands_per_frame;
+  it.frame = item / p.bands_per_frame;
+  it.tile0 = chunk * p.tiles_per_chunk;
+  it.tile1 = min(p.ntx, it.tile0 + p.tiles_per_chunk);
+  it.j0 = band * p.band_groups;
+  it.j1 = min(p.ngy, it.j0 + p.band_groups);
+  it.row_start = __ldg(p.ws + p.off_ya + it.j0);
+  const int row_end = __ldg(p.ws + p.off_yend + it.j1 - 1);
+  const int xa_lo = __ldg(p.ws + p.off_xa + it.tile0), xa_hi = __ldg(p.ws + p.off_xa + it.tile1 - 1);
+  it.nbatches = (row_end - it.row_start + kBatchRows - 1) / kBatchRows;
+  it.byte_lo = (xa_lo * 3) & ~15;
+  it.copy_bytes = min(p.sw * 3, ((xa_hi + 32 * KX) * 3 + 15) & ~15) - it.byte_lo;
+  return it;
+}
+
+// Persistent CTAs: CTA c takes work items c, c + gridDim.x, ...; the producer warp runs ahead of
+// the consumers across item boundaries, so only the very first batch of a CTA waits for HBM with
+// nothing else to do, and a warp loads its tile weights once (the chunk of a CTA never changes:
+// the grid is a multiple of the chunk count).
 template <int KX, int KY, int T>
 __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bicubic_mma_kernel(const MmaParams p) {
   constexpr int CAP = 32 * KY + 16;   // ring rows: one K window + the rows a batch runs ahead, rounded;
@@ -228,35 +263,13 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, q = lane & 3;
   const int nwarps = (int)blockDim.x / 32 - 1;   // consumer warps; the last warp feeds the TMA ring
-
-  int bid = blockIdx.x;
-  const int chunk = bid % p.chunks; bid /= p.chunks;
-  const int band = bid % p.bands_per_frame;
-  const int frame = bid / p.bands_per_frame;
-  const int tile0 = chunk * p.tiles_per_chunk, tile1 = min(p.ntx, tile0 + p.tiles_per_chunk);
-  const int j0 = band * p.band_groups, j1 = min(p.ngy, j0 + p.band_groups);
-  const int active = (tile1 - tile0 + T - 1) / T;     // consumer warps that own tiles
-
-  const int* xa = p.ws + p.off_xa;
-  const int* ya = p.ws + p.off_ya;
-  const int* yend = p.ws + p.off_yend;
-  const int flag = __ldg(p.ws + 1);
+  if (__ldg(p.ws + 1) != 0) __trap();   // a weight or window outside what the tables can hold (cannot happen
+                                        // for the sizes MmaPlan.ok admits; better loud than wrong)
   const int row_bytes = p.sw * 3;
-  const int row_start = __ldg(ya + j0), row_end = __ldg(yend + j1 - 1);
-  const int xa_lo = __ldg(xa + tile0), xa_hi = __ldg(xa + tile1 - 1);
-  if (flag != 0) __trap();   // a weight or window outside what the tables can hold (cannot happen for the
-                             // sizes MmaPlan.ok admits; better loud than wrong)
-  const int nbatches = (row_end - row_start + kBatchRows - 1) / kBatchRows;
-  const int byte_lo = (xa_lo * 3) & ~15;
-  const int byte_hi = min(row_bytes, ((xa_hi + 32 * KX) * 3 + 15) & ~15);
-  const int copy_bytes = byte_hi - byte_lo;
-  if (copy_bytes > p.raw_pitch) __trap();
-
-  const uint8_t* fsrc = p.src + (size_t)frame * p.sh * row_bytes + byte_lo;
   if (threadIdx.x == 0) {
     for (int s = 0; s < kMmaStages; s++) {
       mbar_init(&full[s], 1);
-      mbar_init(&empty[s], active);
+      mbar_init(&empty[s], nwarps);     // every consumer warp arrives, with or without tiles in the chunk
     }
     fence_mbar_init();
   }
@@ -264,128 +277,146 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
 
   if (warp == nwarps) {
     // ---- producer: lanes 0..7 each ask the TMA engine for one source row of the batch ------------
-    for (int b = 0; b < nbatches; b++) {
-      const int s = b % kMmaStages, round = b / kMmaStages;
-      if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1), 1000, 100);
-      if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)(kBatchRows * copy_bytes));
-      __syncwarp();
-      if (lane < kBatchRows) {
-        const int row = min(row_start + b * kBatchRows + lane, p.sh - 1);   // rows past the frame carry no weight
-        bulk_g2s(raw + (size_t)(s * kBatchRows + lane) * p.raw_pitch, fsrc + (size_t)row * row_bytes,
-                 (uint32_t)copy_bytes, &full[s]);
+    int gb = 0;   // batches issued by this CTA so far: staging buffer and barrier phase follow from it
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+      const MmaItem it = mma_item<KX>(p, item);
+      if (it.copy_bytes > p.raw_pitch) __trap();
+      const uint8_t* fsrc = p.src + (size_t)it.frame * p.sh * row_bytes + it.byte_lo;
+      for (int b = 0; b < it.nbatches; b++, gb++) {
+        const int s = gb % kMmaStages, round = gb / kMmaStages;
+        if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1), 1000, 100);
+        if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)(kBatchRows * it.copy_bytes));
+        __syncwarp();
+        if (lane < kBatchRows) {
+          const int row = min(it.row_start + b * kBatchRows + lane, p.sh - 1);   // rows past the frame carry no weight
+          bulk_g2s(raw + (size_t)(s * kBatchRows + lane) * p.raw_pitch, fsrc + (size_t)row * row_bytes,
+                   (uint32_t)it.copy_bytes, &full[s]);
+        }
       }
     }
     return;
   }
-  if (warp >= active) return;
 
   // ---- consumers: horizontal pass, ring and vertical pass of the warp's own tiles ---------------
-  const int wtile0 = tile0 + warp * T;
-  const int ntw = min(T, tile1 - wtile0);
-  const int wcol0 = warp * T * 48;                    // first ring column (byte column inside the chunk)
   uint4 A[T][3][KX];
   int xoff[T];
-  const uint4* ax = reinterpret_cast<const uint4*>(p.ws + p.off_ax);
-#pragma unroll
-  for (int t = 0; t < T; t++) {
-    const bool on = t < ntw;       // a slot without a tile gets zero weights and is filtered like the others
-    xoff[t] = on ? __ldg(xa + wtile0 + t) * 3 - byte_lo : 0;
-#pragma unroll
-    for (int pl = 0; pl < 3; pl++)
-#pragma unroll
-      for (int ks = 0; ks < KX; ks++)
-        A[t][pl][ks] = on ? __ldg(ax + ((size_t)((wtile0 + t) * 3 + pl) * KX + ks) * 32 + lane) : make_uint4(0, 0, 0, 0);
-  }
+  const int wcol0 = warp * T * 48;                    // first ring column (byte column inside the chunk)
   const uint2* byf = reinterpret_cast<const uint2*>(p.ws + p.off_by);
-  uint8_t* fdst = p.dst + (size_t)frame * p.dh * p.dw * 3;
+  const int* ya = p.ws + p.off_ya;
+  const int* yend = p.ws + p.off_yend;
   const int out_row_bytes = p.dw * 3;
-  const int gcol0 = tile0 * 48 + wcol0;               // first output byte column of this warp
-  const bool cols_inside = gcol0 + ntw * 48 <= out_row_bytes;
   constexpr int kRound = 1 << (kPrecisionBits - 1);
-
-  int jn = j0;          // next group of output rows to emit
-  int slot = 0;         // ring row of the batch being filtered
-  // the next group's record and weights are fetched a group ahead, so no batch waits on L2 for them
-  int g_end = __ldg(yend + j0) - row_start, g_base = 0;
-  uint2 W[3][KY];
+  int cur_tile0 = -1, ntw = 0;
+  int gb = 0;
+  for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+    const MmaItem it = mma_item<KX>(p, item);
+    if (it.tile0 != cur_tile0) {     // first item of the CTA (and never again when the grid is a multiple of the chunks)
+      cur_tile0 = it.tile0;
+      const int wtile0 = it.tile0 + warp * T;
+      ntw = max(0, min(T, it.tile1 - wtile0));
+      const uint4* ax = reinterpret_cast<const uint4*>(p.ws + p.off_ax);
 #pragma unroll
-  for (int pl = 0; pl < 3; pl++)
-#pragma unroll
-    for (int ks = 0; ks < KY; ks++) W[pl][ks] = __ldg(byf + ((size_t)(j0 * 3 + pl) * KY + ks) * 32 + lane);
-  for (int b = 0; b < nbatches; b++) {
-    const int s = b % kMmaStages, round = b / kMmaStages;
-    mbar_wait(&full[s], (uint32_t)(round & 1), 500, 0);
-    // -- horizontal pass: 8 staged rows x this warp's tiles -> ring rows slot .. slot + 7
-    const uint8_t* rrow = raw + (size_t)(s * kBatchRows + g) * p.raw_pitch;
-    uint8_t* ring_out = ring + (size_t)(wcol0 + g * 3) * CAP + slot + 2 * q;
-    horizontal_tiles<KX, T, CAP, T>(A, xoff, rrow, ring_out, q);   // slots without a tile: zero weights, spare columns
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[s]);     // the staged rows are free again
-    slot += kBatchRows;
-    if (slot >= CAP) slot -= CAP;
-    const int produced = (b + 1) * kBatchRows;
-
-    // -- vertical pass for every group of 8 output rows whose last intermediate row now exists
-    while (jn < j1 && g_end <= produced) {
-      const int base = g_base % CAP;
-      int o0[KY], o1[KY];
-#pragma unroll
-      for (int ks = 0; ks < KY; ks++) {
-        o0[ks] = base + 32 * ks + 4 * q;
-        if (o0[ks] >= CAP) o0[ks] -= CAP;
-        o1[ks] = base + 32 * ks + 16 + 4 * q;
-        if (o1[ks] >= CAP) o1[ks] -= CAP;
-      }
-      const int dy = jn * 8 + 2 * q;
-      const bool inside = cols_inside && jn * 8 + 8 <= p.dh;   // no clipping of this group's stores
-      uint8_t* orow = fdst + (size_t)dy * out_row_bytes + gcol0 + g;
-#pragma unroll 3
-      for (int mt = 0; mt < ntw * 3; mt++) {
-        const uint8_t* c0 = ring + (size_t)(wcol0 + mt * 16 + g) * CAP;
-        const uint8_t* c1 = c0 + 8 * CAP;
-        int s2[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, s0[4] = {kRound, kRound, kRound, kRound};
-#pragma unroll
-        for (int ks = 0; ks < KY; ks++) {
-          const uint32_t a0 = *reinterpret_cast<const uint32_t*>(c0 + o0[ks]);
-          const uint32_t a1 = *reinterpret_cast<const uint32_t*>(c1 + o0[ks]);
-          const uint32_t a2 = *reinterpret_cast<const uint32_t*>(c0 + o1[ks]);
-          const uint32_t a3 = *reinterpret_cast<const uint32_t*>(c1 + o1[ks]);
-          mma_u8s8(s2, a0, a1, a2, a3, W[2][ks].x, W[2][ks].y);
-          mma_u8u8(s1, a0, a1, a2, a3, W[1][ks].x, W[1][ks].y);
-          mma_u8u8(s0, a0, a1, a2, a3, W[0][ks].x, W[0][ks].y);
-        }
-        // element 0, 1: byte column g, output rows dy, dy + 1;  element 2, 3: byte column g + 8
-        const uint32_t lo = pack2_sat_u8(combine_planes(s2[0], s1[0], s0[0]), combine_planes(s2[1], s1[1], s0[1]));
-        const uint32_t hi = pack2_sat_u8(combine_planes(s2[2], s1[2], s0[2]), combine_planes(s2[3], s1[3], s0[3]));
-        uint8_t* o = orow + mt * 16;
-        if (inside) {
-          o[0] = (uint8_t)lo;
-          o[8] = (uint8_t)hi;
-          o[out_row_bytes] = (uint8_t)(lo >> 8);
-          o[out_row_bytes + 8] = (uint8_t)(hi >> 8);
-        } else {
-          const int col = gcol0 + mt * 16 + g;
-          if (dy < p.dh) {
-            if (col < out_row_bytes) o[0] = (uint8_t)lo;
-            if (col + 8 < out_row_bytes) o[8] = (uint8_t)hi;
-          }
-          if (dy + 1 < p.dh) {
-            if (col < out_row_bytes) o[out_row_bytes] = (uint8_t)(lo >> 8);
-            if (col + 8 < out_row_bytes) o[out_row_bytes + 8] = (uint8_t)(hi >> 8);
-          }
-        }
-      }
-      jn++;
-      if (jn < j1) {
-        g_end = __ldg(yend + jn) - row_start;
-        g_base = __ldg(ya + jn) - row_start;
+      for (int t = 0; t < T; t++) {
+        const bool on = t < ntw;     // a slot without a tile gets zero weights and is filtered like the others
+        xoff[t] = on ? __ldg(p.ws + p.off_xa + wtile0 + t) * 3 - it.byte_lo : 0;
 #pragma unroll
         for (int pl = 0; pl < 3; pl++)
 #pragma unroll
-          for (int ks = 0; ks < KY; ks++) W[pl][ks] = __ldg(byf + ((size_t)(jn * 3 + pl) * KY + ks) * 32 + lane);
+          for (int ks = 0; ks < KX; ks++)
+            A[t][pl][ks] = on ? __ldg(ax + ((size_t)((wtile0 + t) * 3 + pl) * KX + ks) * 32 + lane) : make_uint4(0, 0, 0, 0);
       }
     }
-    __syncwarp();   // ring rows read above are rewritten by later batches
+    const int row_start = it.row_start, j1 = it.j1;
+    uint8_t* fdst = p.dst + (size_t)it.frame * p.dh * out_row_bytes;
+    const int gcol0 = it.tile0 * 48 + wcol0;          // first output byte column of this warp
+    const bool cols_inside = gcol0 + ntw * 48 <= out_row_bytes;
+
+    int jn = it.j0;       // next group of output rows to emit
+    int slot = 0;         // ring row of the batch being filtered
+    // the next group's record and weights are fetched a group ahead, so no batch waits on L2 for them
+    int g_end = __ldg(yend + jn) - row_start, g_base = 0;
+    uint2 W[3][KY];
+#pragma unroll
+    for (int pl = 0; pl < 3; pl++)
+#pragma unroll
+      for (int ks = 0; ks < KY; ks++) W[pl][ks] = __ldg(byf + ((size_t)(jn * 3 + pl) * KY + ks) * 32 + lane);
+    for (int b = 0; b < it.nbatches; b++, gb++) {
+      const int s = gb % kMmaStages, round = gb / kMmaStages;
+      mbar_wait(&full[s], (uint32_t)(round & 1), 500, 0);
+      if (ntw > 0) {
+        // -- horizontal pass: 8 staged rows x this warp's tiles -> ring rows slot .. slot + 7
+        const uint8_t* rrow = raw + (size_t)(s * kBatchRows + g) * p.raw_pitch;
+        uint8_t* ring_out = ring + (size_t)(wcol0 + g * 3) * CAP + slot + 2 * q;
+        horizontal_tiles<KX, T, CAP, T>(A, xoff, rrow, ring_out, q);   // slots without a tile: zero weights, spare columns
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);     // the staged rows are free again
+      slot += kBatchRows;
+      if (slot >= CAP) slot -= CAP;
+      const int produced = (b + 1) * kBatchRows;
+
+      // -- vertical pass for every group of 8 output rows whose last intermediate row now exists
+      while (jn < j1 && g_end <= produced) {
+        const int base = g_base % CAP;
+        int o0[KY], o1[KY];
+#pragma unroll
+        for (int ks = 0; ks < KY; ks++) {
+          o0[ks] = base + 32 * ks + 4 * q;
+          if (o0[ks] >= CAP) o0[ks] -= CAP;
+          o1[ks] = base + 32 * ks + 16 + 4 * q;
+          if (o1[ks] >= CAP) o1[ks] -= CAP;
+        }
+        const int dy = jn * 8 + 2 * q;
+        const bool inside = cols_inside && jn * 8 + 8 <= p.dh;   // no clipping of this group's stores
+        uint8_t* orow = fdst + (size_t)dy * out_row_bytes + gcol0 + g;
+#pragma unroll 3
+        for (int mt = 0; mt < ntw * 3; mt++) {
+          const uint8_t* c0 = ring + (size_t)(wcol0 + mt * 16 + g) * CAP;
+          const uint8_t* c1 = c0 + 8 * CAP;
+          int s2[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, s0[4] = {kRound, kRound, kRound, kRound};
+#pragma unroll
+          for (int ks = 0; ks < KY; ks++) {
+            const uint32_t a0 = *reinterpret_cast<const uint32_t*>(c0 + o0[ks]);
+            const uint32_t a1 = *reinterpret_cast<const uint32_t*>(c1 + o0[ks]);
+            const uint32_t a2 = *reinterpret_cast<const uint32_t*>(c0 + o1[ks]);
+            const uint32_t a3 = *reinterpret_cast<const uint32_t*>(c1 + o1[ks]);
+            mma_u8s8(s2, a0, a1, a2, a3, W[2][ks].x, W[2][ks].y);
+            mma_u8u8(s1, a0, a1, a2, a3, W[1][ks].x, W[1][ks].y);
+            mma_u8u8(s0, a0, a1, a2, a3, W[0][ks].x, W[0][ks].y);
+          }
+          // element 0, 1: byte column g, output rows dy, dy + 1;  element 2, 3: byte column g + 8
+          const uint32_t lo = pack2_sat_u8(combine_planes(s2[0], s1[0], s0[0]), combine_planes(s2[1], s1[1], s0[1]));
+          const uint32_t hi = pack2_sat_u8(combine_planes(s2[2], s1[2], s0[2]), combine_planes(s2[3], s1[3], s0[3]));
+          uint8_t* o = orow + mt * 16;
+          if (inside) {
+            o[0] = (uint8_t)lo;
+            o[8] = (uint8_t)hi;
+            o[out_row_bytes] = (uint8_t)(lo >> 8);
+            o[out_row_bytes + 8] = (uint8_t)(hi >> 8);
+          } else {
+            const int col = gcol0 + mt * 16 + g;
+            if (dy < p.dh) {
+              if (col < out_row_bytes) o[0] = (uint8_t)lo;
+              if (col + 8 < out_row_bytes) o[8] = (uint8_t)hi;
+            }
+            if (dy + 1 < p.dh) {
+              if (col < out_row_bytes) o[out_row_bytes] = (uint8_t)(lo >> 8);
+              if (col + 8 < out_row_bytes) o[out_row_bytes + 8] = (uint8_t)(hi >> 8);
+            }
+          }
+        }
+        jn++;
+        if (jn < j1) {
+          g_end = __ldg(yend + jn) - row_start;
+          g_base = __ldg(ya + jn) - row_start;
+#pragma unroll
+          for (int pl = 0; pl < 3; pl++)
+#pragma unroll
+            for (int ks = 0; ks < KY; ks++) W[pl][ks] = __ldg(byf + ((size_t)(jn * 3 + pl) * KY + ks) * 32 + lane);
+        }
+      }
+      __syncwarp();   // ring rows read above are rewritten by later batches
+    }
   }
 }
 
@@ -442,8 +473,11 @@ static int launch_mma(MmaParams p, int n_frames, double scale_y, cudaStream_t st
   p.band_groups = env_int("AIKO_B200_BICUBIC_BAND_GROUPS", best_g);
   if (p.band_groups < 1) p.band_groups = 1;
   p.bands_per_frame = (p.ngy + p.band_groups - 1) / p.band_groups;
-  const long long grid = (long long)n_frames * p.chunks * p.bands_per_frame;
-  AIKO_CHECK_ARG(grid < ((long long)1 << 31), "resize_bicubic: too many bands");
+  const long long items = (long long)n_frames * p.chunks * p.bands_per_frame;
+  AIKO_CHECK_ARG(items < ((long long)1 << 31), "resize_bicubic: too many bands");
+  p.items = (int)items;
+  long long grid = items < slots ? items : slots;       // persistent CTAs stride over the items
+  if (grid > p.chunks) grid -= grid % p.chunks;         // ... and keep their chunk (= their tile weights)
   kernel<<<(unsigned)grid, threads, smem, stream>>>(p);
   *done = true;
   return cuda_status(cudaGetLastError(), "bicubic_mma launch");
