@@ -103,6 +103,50 @@ __global__ void __launch_bounds__(kThreads) gray2bgr_kernel(const uint8_t* __res
   }
 }
 
+// Horizontal flip of RGB rows whose width is a multiple of 16 pixels, entirely in registers:
+// a thread loads 16 pixels (3 aligned vectors), reverses their order with byte permutes and
+// stores them at the mirrored position of the (possibly vertically mirrored) row.
+__device__ __forceinline__ void reverse16_rgb(const uint32_t (&w)[12], uint32_t (&o)[12]) {
+  uint32_t px[16];   // pixel i in the low three bytes
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    const int b = 3 * i, word = b >> 2, sh = b & 3;
+    const uint32_t hi = word + 1 < 12 ? w[word + 1] : 0u;
+    px[i] = __byte_perm(w[word], hi, 0x3210 + 0x1111 * sh);
+  }
+#pragma unroll
+  for (int j = 0; j < 4; j++) {   // output pixels 4j .. 4j + 3 = input pixels 15 - 4j .. 12 - 4j
+    const uint32_t a = px[15 - 4 * j], b = px[14 - 4 * j], c = px[13 - 4 * j], d = px[12 - 4 * j];
+    o[3 * j] = __byte_perm(a, b, 0x4210);
+    o[3 * j + 1] = __byte_perm(b, c, 0x5421);
+    o[3 * j + 2] = __byte_perm(c, d, 0x6542);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) flip_rgb16_kernel(const uint8_t* __restrict__ src,
+                                                              uint8_t* __restrict__ dst, long long n_groups,
+                                                              int h, int groups_per_row, int flip_vertical) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x; gi < n_groups; gi += stride) {
+    const long long row = gi / groups_per_row;
+    const int gs = (int)(gi - row * groups_per_row);
+    long long drow = row;
+    if (flip_vertical) {
+      const long long n = row / h;
+      drow = n * h + (h - 1 - (row - n * h));
+    }
+    const uint4* s = reinterpret_cast<const uint4*>(src) + gi * 3;
+    const uint4 v0 = ldg_stream(s), v1 = ldg_stream(s + 1), v2 = ldg_stream(s + 2);
+    const uint32_t w[12] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w};
+    uint32_t o[12];
+    reverse16_rgb(w, o);
+    uint4* d = reinterpret_cast<uint4*>(dst) + (drow * groups_per_row + (groups_per_row - 1 - gs)) * 3;
+    stg_stream(d, make_uint4(o[0], o[1], o[2], o[3]));
+    stg_stream(d + 1, make_uint4(o[4], o[5], o[6], o[7]));
+    stg_stream(d + 2, make_uint4(o[8], o[9], o[10], o[11]));
+  }
+}
+
 // Flip / crop: one CTA per output row; the source row (segment) goes through shared memory
 // so both the global read and the global write are coalesced vectors.
 __global__ void __launch_bounds__(kThreads) flip_rows_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
@@ -231,6 +275,12 @@ extern "C" int aiko_b200_flip_u8(const uint8_t* src, uint8_t* dst, int n_frames,
   if (n_frames == 0 || h == 0 || w == 0) return AIKO_B200_OK;
   AIKO_CHECK_ARG(src && dst && src != dst, "flip: null or aliased pointers");
   AIKO_CHECK_ARG(channels >= 1 && channels <= 4, "flip: channels %d not in 1..4", channels);
+  if (flip_code != 0 && channels == 3 && (w & 15) == 0 && ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0) {
+    const long long groups = (long long)n_frames * h * (w / 16);
+    flip_rgb16_kernel<<<stream_grid(groups), kThreads, 0, (cudaStream_t)stream>>>(src, dst, groups, h, w / 16,
+                                                                                  flip_code < 0 ? 1 : 0);
+    return cuda_status(cudaGetLastError(), "flip launch");
+  }
   const int rev_offset = (int)((((size_t)w * channels + 48) + 15) & ~(size_t)15);   // staged row, then reversed row
   const size_t smem = (size_t)rev_offset + (((size_t)w * channels + 15) & ~(size_t)15);
   AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "flip: row of %d bytes exceeds shared memory", w * channels);

@@ -225,7 +225,7 @@ def test_swap_is_involution_full_size(cuda):
     assert torch.equal(ops.swap_rb(ops.swap_rb(frames)), frames)
 
 
-@pytest.mark.parametrize("shape", [(2, 37, 53, 3), (1, 48, 64, 3), (3, 20, 33, 1), (1, 9, 16, 4), (1, 1080, 1920, 3)])
+@pytest.mark.parametrize("shape", [(2, 37, 53, 3), (1, 48, 64, 3), (3, 7, 32, 3), (3, 20, 33, 1), (1, 9, 16, 4), (1, 1080, 1920, 3)])
 @pytest.mark.parametrize("code", [0, 1, -1])
 def test_flip_vs_oracle(cuda, shape, code):
     n, h, w, c = shape
@@ -361,8 +361,10 @@ def test_sizes_beyond_on_chip_limits_are_refused_not_mangled(cuda):
         ops.resize_bicubic_aa(tiny, 60000, 2)
     assert e.value.code == _native.ERR_UNSUPPORTED
     with pytest.raises(_native.NativeError) as e:
-        ops.flip(torch.zeros((1, 1, 100000, 3), dtype=torch.uint8, device=cuda), 1)
+        ops.flip(torch.zeros((1, 1, 100001, 3), dtype=torch.uint8, device=cuda), 1)
     assert e.value.code == _native.ERR_INVALID_ARGUMENT
+    wide = torch.arange(100000 * 3, device=cuda).to(torch.uint8).view(1, 1, 100000, 3)   # multiple of 16 pixels:
+    assert torch.equal(ops.flip(wide, 1), wide.flip(2))                                   # register path, no row limit
     # the widest rows the staged kernel takes still resize exactly (8K frames)
     frames = np.stack([cases.frame(81, 24, 7680, 3)])
     out = host(ops.resize_linear(dev(frames, cuda), 3840, 12))
