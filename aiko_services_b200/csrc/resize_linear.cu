@@ -342,7 +342,9 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
 // first result is needed, so a round pays one memory latency instead of one per row.
 template <int C>
 struct GenericRows {
-  static constexpr int value = C == 1 ? 4 : 2;   // 16 (gray) / 24-32 (colour) byte loads in flight per thread
+  // gray: 4 rows (16 byte loads in flight per thread).  Colour: 1 -- with more, the source rows the
+  // resident CTAs of an SM gather from no longer fit its L1 (measured 81 / 90 / 85 us for 1 / 2 / 4 rows)
+  static constexpr int value = C == 1 ? 4 : 1;
 };
 
 template <int C>
