@@ -472,6 +472,13 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   int per_sm = 0;
   AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resize3_staged, threads, smem));
   if (per_sm < 1) per_sm = 1;
+  // Source rows in page-locked host memory (the TMA engine reads them over PCIe): the link, not the
+  // SMs, sets the pace, and one CTA per SM keeps far more bytes in flight than it needs.  Leaving
+  // the rest of each SM free lets the kernels of other streams (the previous batch's overlay) run
+  // beside this one instead of queueing behind its persistent CTAs for milliseconds.
+  cudaPointerAttributes attr{};
+  if (cudaPointerGetAttributes(&attr, p.src) == cudaSuccess && attr.type == cudaMemoryTypeHost) per_sm = 1;
+  else (void)cudaGetLastError();
   int chunk = env_int("AIKO_B200_RESIZE_CHUNK", 1);
   if (chunk < 1) chunk = 1;
   long long grid = (long long)sm_count() * per_sm;

@@ -25,10 +25,16 @@ _overlay_cache = OrderedDict()       # (overlay content, size, layout, frames, d
 
 
 class DeviceBatch:
-    def __init__(self, tensor, stream=None, recipe=None):
-        self._source = tensor            # uint8 [N, H, W, C] or [N, H, W] on a CUDA device
+    def __init__(self, tensor, stream=None, recipe=None, device=None, on_source_read=None):
+        # uint8 [N, H, W, C] or [N, H, W]: on a CUDA device, or (with ``device``) in page-locked host
+        # memory -- then the first kernel of the recipe reads it over PCIe if it touches every row
+        # once (bilinear downscale of RGB frames), and otherwise it is copied to ``device`` first
+        self._source = tensor
+        self._device = torch.device(device) if device is not None else tensor.device
+        self._mapped = not tensor.is_cuda
+        self._on_source_read = on_source_read   # called (stream-ordered) once the host source has been consumed
         self._recipe = list(recipe or [])
-        self._tensor = tensor if not self._recipe else None
+        self._tensor = tensor if not self._recipe and not self._mapped else None
         self._host = None
         self.stream = stream             # torch.cuda.Stream the batch's work is ordered on
         self.stager = None               # FrameStager that brought the frames in (pinned result buffers)
@@ -36,7 +42,7 @@ class DeviceBatch:
     # ---- geometry of the result, known without running anything
     @property
     def device(self):
-        return self._source.device
+        return self._device
 
     def __len__(self):
         return self._source.shape[0]
@@ -53,10 +59,18 @@ class DeviceBatch:
         return (h, w) if c == 1 else (h, w, c)
 
     def then(self, *step):
-        nxt = DeviceBatch(self._source if self._tensor is None else self._tensor, self.stream,
-                          (self._recipe if self._tensor is None else []) + [tuple(step)])
+        if self._tensor is None:
+            nxt = DeviceBatch(self._source, self.stream, self._recipe + [tuple(step)],
+                              self._device if self._mapped else None, self._on_source_read)
+        else:
+            nxt = DeviceBatch(self._tensor, self.stream, [tuple(step)])
         nxt.stager = self.stager
         return nxt
+
+    def launch(self):
+        """Enqueue the kernels of the recipe now (asynchronously); results are read later."""
+        self.tensor
+        return self
 
     # ---- materialisation
     @property
@@ -94,8 +108,20 @@ class DeviceBatch:
             _overlay_cache.popitem(last=False)
         return dev
 
+    def _source_read(self):
+        if self._on_source_read is not None:
+            self._on_source_read()
+            self._on_source_read = None
+
     def _run(self, t, recipe):
         i = 0
+        if self._mapped:
+            first = recipe[0] if recipe else None
+            direct = (first is not None and first[0] == "resize_linear" and t.dim() == 4 and
+                      ops.reads_source_rows_once(tuple(t.shape[1:]), first[1], first[2]))
+            if not direct:                  # everything else works on a copy in HBM
+                t = t.to(self._device, non_blocking=True)
+                self._source_read()
         while i < len(recipe):
             step = recipe[i]
             kind = step[0]
@@ -116,7 +142,11 @@ class DeviceBatch:
                                                                                  ("convert", "BGR2RGB")):
                     swap = True
                     used += 1
-                t = ops.resize_linear(t, w, h, swap_rb=swap, overlay=ov)
+                if t.is_cuda:
+                    t = ops.resize_linear(t, w, h, swap_rb=swap, overlay=ov)
+                else:                       # page-locked host frames, read by the kernel itself
+                    t = ops.resize_linear(t, w, h, swap_rb=swap, overlay=ov, device=self._device)
+                    self._source_read()
                 i += used
                 continue
             if kind == "resize_bicubic":

@@ -223,13 +223,33 @@ class DeviceOverlay:
         return ctypes.pointer(self.struct)
 
 
-def resize_linear(src, width, height, *, swap_rb=False, overlay=None, out=None, stream=None):
-    """cv2.resize(image, (width, height)) for every frame of ``src``; optional fused overlay / swap."""
-    _require_cuda(src, "resize_linear src")
+def reads_source_rows_once(frame_shape, width, height):
+    """True when ``resize_linear`` to (width, height) fetches every source row it needs exactly once
+    with bulk row copies (RGB, 16-byte aligned rows, horizontal scale <= 4, vertical scale >= 2):
+    the case in which the kernel may as well read the rows from page-locked host memory."""
+    if len(frame_shape) != 3 or frame_shape[2] != 3:
+        return False
+    h, w = frame_shape[:2]
+    return (w * 3) % 16 == 0 and w <= 4 * width and h >= 2 * height and width > 0 and height > 0
+
+
+def resize_linear(src, width, height, *, swap_rb=False, overlay=None, out=None, stream=None, device=None):
+    """cv2.resize(image, (width, height)) for every frame of ``src``; optional fused overlay / swap.
+
+    ``src`` is a CUDA tensor, or -- with ``device`` given -- a page-locked host tensor that the
+    kernel reads over PCIe itself (no staging copy in HBM; see ``reads_source_rows_once``).
+    """
+    if device is not None and isinstance(src, torch.Tensor) and not src.is_cuda:
+        if not src.is_pinned() or src.dtype != torch.uint8 or not src.is_contiguous():
+            raise RuntimeError("resize_linear src: a host tensor must be page-locked, uint8 and contiguous")
+        dev = torch.device(device)
+    else:
+        _require_cuda(src, "resize_linear src")
+        dev = src.device
     n, h, w, c, gray = _nhwc(src)
     shape = (n, height, width) if gray else (n, height, width, c)
-    out = _out(out, shape, src.device, "resize_linear out")
-    with torch.cuda.device(src.device):
+    out = _out(out, shape, dev, "resize_linear out")
+    with torch.cuda.device(dev):
         check(_native.lib().aiko_b200_resize_linear_u8(
             src.data_ptr(), n, h, w, c, w * c, h * w * c, out.data_ptr(), height, width, width * c,
             height * width * c, int(bool(swap_rb)), overlay.pointer() if overlay is not None else None,

@@ -450,6 +450,19 @@ class Pipeline:
             dt = time.monotonic() - t_node
             for job in live:
                 job["frame"].metrics.setdefault("pipeline_elements", {})[f"time_{node}"] = dt
+        # The graph has been walked: whatever the elements left as lazy device work is enqueued now
+        # (asynchronously), so it overlaps the next frame's host work and the previous frame's read-back.
+        launched = set()
+        for job in jobs:
+            if job and job["alive"]:
+                for image in job["frame"].swag.get("images") or ():
+                    batch = getattr(image, "batch", None)
+                    if batch is not None and id(batch) not in launched:
+                        launched.add(id(batch))
+                        try:
+                            batch.launch()
+                        except Exception as error:   # reported when the pixels are asked for, as before
+                            self.logger.debug(f"deferred launch: {error}")
         results = []
         for job in jobs:
             if job is None:

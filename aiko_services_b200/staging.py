@@ -5,6 +5,8 @@ elements for per-stream state, R/main/stream.py:81).  ``upload`` packs a list of
 frames into a pinned buffer and enqueues one asynchronous copy; buffers rotate so the host can
 fill the next batch while the previous copy is in flight.
 """
+import os
+
 import numpy as np
 import torch
 
@@ -19,6 +21,11 @@ class FrameStager:
         self._pinned = [None] * slots
         self._events = [None] * slots
         self._next = 0
+        # AIKO_B200_ZERO_COPY=1: frames written into allocate() memory stay there until their first kernel
+        # and a bilinear downscale reads them over PCIe itself.  Off by default: measured on B200 the TMA
+        # engine pulls 50 GB/s from host memory against 54 GB/s for the copy engine, and the 11 % of rows a
+        # 1080p -> 480p resize never touches do not make up for it end to end (6.9-7.2 k vs 7.5-7.9 k frames/s).
+        self.zero_copy = os.environ.get("AIKO_B200_ZERO_COPY", "0") == "1"
         self._owned = {}          # pinned blocks handed out by allocate(): base address -> tensor
         self._out = {}            # pinned result buffers by (shape): reused for device-to-host copies
 
@@ -35,8 +42,9 @@ class FrameStager:
         """-> list of ``n`` uint8 ndarray views, each of ``frame_shape``, over one pinned buffer.
 
         A source element (decoder, camera reader, test generator) writes its frames here; ``upload``
-        recognises such frames and issues the cudaMemcpyAsync straight from this memory, with no
-        intermediate host copy.  The buffer belongs to the caller until it is uploaded.
+        recognises such frames and lets the GPU work read them from this memory (``mapped``), with no
+        intermediate host copy.  The buffer must stay untouched from the moment its frames enter the
+        pipeline until their results have been read.
         """
         count = int(np.prod(frame_shape))
         pinned = torch.empty(max(n * count, 1), dtype=torch.uint8).pin_memory()
@@ -63,6 +71,17 @@ class FrameStager:
         view = pinned[:frames.nbytes].view(frames.shape)
         view.numpy()[...] = frames
         return self.upload_pinned(view, i)
+
+    def mapped(self, pinned_tensor):
+        """A caller-owned tensor in pinned host memory -> lazy DeviceBatch, not copied anywhere yet.
+
+        If the first thing done to the frames is a bilinear downscale that reads each source row
+        once, the kernel fetches the rows over PCIe itself (only the rows that carry weight, and no
+        staging copy in HBM); otherwise the batch copies itself to the device when it is first used.
+        Either way the work is enqueued when the frame leaves the pipeline, and the host buffer
+        belongs to the caller again once the frame's results have been read.
+        """
+        return DeviceBatch(pinned_tensor, self.stream, device=self.device)
 
     def upload_pinned(self, pinned_tensor, slot=None):
         """A tensor already in pinned host memory -> DeviceBatch (one cudaMemcpyAsync)."""
@@ -104,7 +123,7 @@ class FrameStager:
                 arrs = [images[p] if isinstance(images[p], np.ndarray) else np.asarray(images[p]) for p in positions]
                 block = self._owned_block(arrs)
                 if block is not None:                 # frames were produced in our pinned memory: no host copy
-                    batch = self.upload_pinned(block)
+                    batch = self.mapped(block) if self.zero_copy else self.upload_pinned(block)
                     batch.stager = self
                     out.append((batch, positions))
                     continue

@@ -265,15 +265,22 @@ def run_gpu_arm(args):
         result = images[0].batch.host_view()          # kernel launch + D2H into pinned memory + sync
         return int(result[0, 0, 0, 0])
 
-    pending = e2e_submit(0)
-    checksum += e2e_collect(pending)                      # warm-up: plan caches, atlas upload, first launches
+    for i in range(4):                                    # warm-up, both streams: plan caches, atlas upload,
+        checksum += e2e_collect(e2e_submit(i))            # first launches, pinned result buffers
     barrier()
     t0 = time.perf_counter()
     pending = e2e_submit(0)
+    trace = [] if os.environ.get("AIKO_BENCH_E2E_TRACE") else None
     for i in range(1, e2e_steps):
+        ta = time.perf_counter()
         nxt = e2e_submit(i)
+        tb = time.perf_counter()
         checksum += e2e_collect(pending)
+        if trace is not None:
+            trace.append((round((tb - ta) * 1e3, 3), round((time.perf_counter() - tb) * 1e3, 3)))
         pending = nxt
+    if trace:
+        print("e2e per step (submit ms, collect ms):", trace, file=sys.stderr)
     checksum += e2e_collect(pending)
     barrier()
     e2e_s = time.perf_counter() - t0

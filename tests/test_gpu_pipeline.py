@@ -62,11 +62,52 @@ def test_chain_device_resident_and_fused(cuda, tmp_path):
     images = swag["images"]
     assert all(isinstance(im, DeviceImage) for im in images)
     batch = images[0].batch
-    assert batch._tensor is None and [s[0] for s in batch._recipe] == ["resize_linear", "overlay", "convert"]
+    # one lazy recipe for the three elements (run as one C-ABI call), enqueued when the frame left the pipeline
+    assert [s[0] for s in batch._recipe] == ["resize_linear", "overlay", "convert"] and batch._tensor is not None
     ref = reference_port.chain_resize_overlay_bgr(frames, "160x120", cases.OVERLAY_SMALL)
     for im, r in zip(images, ref):
         np.testing.assert_array_equal(np.asarray(im), r)          # D2H on demand, like an ndarray
     assert images[0].shape == (120, 160, 3)
+
+
+def test_frames_in_pinned_memory_are_read_by_the_kernel_itself(cuda, tmp_path, monkeypatch):
+    """Frames written into FrameStager.allocate() memory: a downscale reads them over PCIe with no
+    staging copy, anything else copies them first; both equal the reference arithmetic."""
+    from aiko_services_b200.elements.media.image_io import stager_for
+    names = ["Feed", "ImageResize", "ImageOverlay", "ImageConvert", "ImageOutput"]
+    src = [cases.frame(900 + k, 270, 480, 3) for k in range(3)]
+    for zero_copy, resolution in (("1", "160x120"), ("0", "160x120"), ("1", "400x250"), ("1", "640x360")):
+        monkeypatch.setenv("AIKO_B200_ZERO_COPY", zero_copy)
+        p = Pipeline(definition(tmp_path, names, resolution, {"ImageConvert": {"conversion": "RGB2BGR"}}))
+        assert p.create_stream("s1")
+        views = stager_for(p.streams["s1"]).allocate(3, (270, 480, 3))
+        for v, f in zip(views, src):
+            v[...] = f
+        okay, swag = p.process_frame({"stream_id": "s1", "frame_id": 0}, {"images": views, "overlay": cases.OVERLAY_SMALL})
+        assert okay
+        batch = swag["images"][0].batch
+        w, h = (int(v) for v in resolution.split("x"))
+        direct = zero_copy == "1" and 270 >= 2 * h             # each needed source row is fetched once
+        assert batch._mapped == (zero_copy == "1") and batch._source.is_cuda == (zero_copy == "0")
+        assert direct == (zero_copy == "1" and ops_reads_once((270, 480, 3), w, h))
+        ref = reference_port.chain_resize_overlay_bgr(src, resolution, cases.OVERLAY_SMALL)
+        for im, r in zip(swag["images"], ref):
+            np.testing.assert_array_equal(np.asarray(im), r)
+    # an overlay-only pipeline (no resize first) copies the pinned frames, then draws
+    p = Pipeline(definition(tmp_path, ["Feed", "ImageOverlay", "ImageOutput"], "480x270"))
+    assert p.create_stream("s2")
+    views = stager_for(p.streams["s2"]).allocate(3, (270, 480, 3))
+    for v, f in zip(views, src):
+        v[...] = f
+    okay, swag = p.process_frame({"stream_id": "s2", "frame_id": 0}, {"images": views, "overlay": cases.OVERLAY_SMALL})
+    assert okay
+    for im, r in zip(swag["images"], reference_port.image_overlay(src, cases.OVERLAY_SMALL)):
+        np.testing.assert_array_equal(np.asarray(im), r)
+
+
+def ops_reads_once(shape, w, h):
+    from aiko_services_b200 import ops
+    return ops.reads_source_rows_once(shape, w, h)
 
 
 def test_cross_stream_batching_one_launch(cuda, tmp_path):
