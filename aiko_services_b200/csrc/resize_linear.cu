@@ -31,6 +31,8 @@ struct ResizeParams {
   int items, items_per_cta;
   int index_words_per_frame;   // uint32 words of the overlay's spatial index staged per ring slot (0: none)
   int ops_cap;                 // draw-list entries staged per ring slot next to the index (0: read from global)
+  int wait_ns[4];              // producer wait: suspend hint, back-off; consumer wait: suspend hint, back-off
+  int fast_rows;               // no draw list in the row loop, whole 4-pixel groups, 4-byte aligned output rows
 };
 
 // cv2's coefficient derivation (float32 phase from a double position, 11-bit weights).
@@ -81,7 +83,7 @@ __device__ __forceinline__ uint32_t vblend_hi(uint32_t r0, uint32_t r1, uint32_t
 // Row scheduling shared by the producer warp and the consumer warps of resize3_staged: CTA c
 // takes chunks c, c + G, c + 2G, ... of `chunk` consecutive output rows, so rows being read at
 // the same time are neighbours in memory and label rows (slow) are spread over many CTAs.
-constexpr int kRecHeader = 8;   // ints: n, dy, b0 << 16, b1 << 16, first op, op count, -, -
+constexpr int kRecHeader = 8;   // ints: n, dy, b0, b1, first op, op count, output row pointer (2)
 
 // Row scheduling of resize3_staged: CTA c takes chunks c, c + G, c + 2G, ... of `chunk`
 // consecutive output rows, so rows being read at the same time are neighbours in memory and
@@ -123,7 +125,37 @@ __device__ __forceinline__ uint32_t vblend_decim(uint32_t t0, uint32_t t1, uint3
   return (__umulhi(b0d, t0) + __umulhi(b1d, t1) + 2u) >> 2;
 }
 
+// Four consecutive output pixels (12 bytes, 3 words) from the two staged source rows.
 // DECIM: horizontal pass degenerates to picking one source pixel (all weights 2048, 0).
+template <bool DECIM>
+__device__ __forceinline__ void group_pixels(const uint8_t* r0, const uint8_t* r1, const int (&wo)[4], const int (&sh)[4],
+                                             const uint32_t (&cs)[4], uint32_t b0s, uint32_t b1s, uint32_t sel_rgb,
+                                             uint32_t (&o)[3]) {
+  uint32_t px[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const uint32_t* w0 = reinterpret_cast<const uint32_t*>(r0 + wo[k]);
+    const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1 + wo[k]);
+    uint32_t c0, c1, c2;
+    if (DECIM) {
+      const uint32_t u = __funnelshift_r(w0[0], w0[1], sh[k]), v = __funnelshift_r(w1[0], w1[1], sh[k]);
+      c0 = vblend_decim(__byte_perm(u, 0, 0x4404), __byte_perm(v, 0, 0x4404), b0s, b1s);   // tap << 8
+      c1 = vblend_decim(__byte_perm(u, 0, 0x4414), __byte_perm(v, 0, 0x4414), b0s, b1s);
+      c2 = vblend_decim(__byte_perm(u, 0, 0x4424), __byte_perm(v, 0, 0x4424), b0s, b1s);
+    } else {
+      const uint32_t u0 = w0[0], u1 = w0[1], u2 = w0[2];
+      const uint32_t v0 = w1[0], v1 = w1[1], v2 = w1[2];
+      pixel_general(__funnelshift_r(u0, u1, sh[k]), __funnelshift_r(u1, u2, sh[k]), __funnelshift_r(v0, v1, sh[k]),
+                    __funnelshift_r(v1, v2, sh[k]), cs[k], b0s, b1s, &c0, &c1, &c2);
+    }
+    // c0 c1 c2 -> 24-bit pixel in stored channel order (sel_rgb swaps R and B when asked)
+    px[k] = __byte_perm(__byte_perm(c0, c1, 0x0040), c2, sel_rgb);
+  }
+  o[0] = __byte_perm(px[0], px[1], 0x4210);
+  o[1] = __byte_perm(px[1], px[2], 0x5421);
+  o[2] = __byte_perm(px[2], px[3], 0x6542);
+}
+
 template <bool DECIM>
 __device__ __forceinline__ void consume_row(const uint8_t* r0, const uint8_t* r1, const int* xw, const int* xs,
                                             const uint32_t* xcoef, uint8_t* orow, int g_first, int g_step, int groups,
@@ -139,30 +171,52 @@ __device__ __forceinline__ void consume_row(const uint8_t* r0, const uint8_t* r1
       const uint4 c4 = reinterpret_cast<const uint4*>(xcoef)[g];
       cs[0] = c4.x; cs[1] = c4.y; cs[2] = c4.z; cs[3] = c4.w;
     }
-    uint32_t px[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const uint32_t* w0 = reinterpret_cast<const uint32_t*>(r0 + wo[k]);
-      const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1 + wo[k]);
-      uint32_t c0, c1, c2;
-      if (DECIM) {
-        const uint32_t u = __funnelshift_r(w0[0], w0[1], sh[k]), v = __funnelshift_r(w1[0], w1[1], sh[k]);
-        c0 = vblend_decim(__byte_perm(u, 0, 0x4404), __byte_perm(v, 0, 0x4404), b0s, b1s);   // tap << 8
-        c1 = vblend_decim(__byte_perm(u, 0, 0x4414), __byte_perm(v, 0, 0x4414), b0s, b1s);
-        c2 = vblend_decim(__byte_perm(u, 0, 0x4424), __byte_perm(v, 0, 0x4424), b0s, b1s);
-      } else {
-        const uint32_t u0 = w0[0], u1 = w0[1], u2 = w0[2];
-        const uint32_t v0 = w1[0], v1 = w1[1], v2 = w1[2];
-        pixel_general(__funnelshift_r(u0, u1, sh[k]), __funnelshift_r(u1, u2, sh[k]), __funnelshift_r(v0, v1, sh[k]),
-                      __funnelshift_r(v1, v2, sh[k]), cs[k], b0s, b1s, &c0, &c1, &c2);
-      }
-      // c0 c1 c2 -> 24-bit pixel in stored channel order (sel_rgb swaps R and B when asked)
-      px[k] = __byte_perm(__byte_perm(c0, c1, 0x0040), c2, sel_rgb);
+    uint32_t o[3];
+    group_pixels<DECIM>(r0, r1, wo, sh, cs, b0s, b1s, sel_rgb, o);
+    uint32_t* d = reinterpret_cast<uint32_t*>(orow) + 3 * g;
+    d[0] = o[0]; d[1] = o[1]; d[2] = o[2];
+  }
+}
+
+// The common case without a draw list in the row loop: every thread owns one group of 4 output
+// pixels for the whole kernel, so its tap offsets and weights stay in registers and its 12 result
+// bytes go from registers straight to global memory (the destination pointer of the row comes
+// from the producer's record).  No per-row table loads, no output row in shared memory.
+template <bool DECIM>
+__device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_t* full, uint64_t* empty, const int* recs,
+                                                  const uint8_t* stage, int my_items, const int* xw, const int* xs,
+                                                  const uint32_t* xcoef, int g, bool on, uint32_t sel_rgb, int lane) {
+  int wo[4] = {0, 0, 0, 0}, sh[4] = {0, 0, 0, 0};
+  uint32_t cs[4] = {0, 0, 0, 0};
+  if (on) {
+    const int4 w4 = reinterpret_cast<const int4*>(xw)[g];
+    const int4 s4 = reinterpret_cast<const int4*>(xs)[g];
+    wo[0] = w4.x; wo[1] = w4.y; wo[2] = w4.z; wo[3] = w4.w;
+    sh[0] = s4.x; sh[1] = s4.y; sh[2] = s4.z; sh[3] = s4.w;
+    if (!DECIM) {
+      const uint4 c4 = reinterpret_cast<const uint4*>(xcoef)[g];
+      cs[0] = c4.x; cs[1] = c4.y; cs[2] = c4.z; cs[3] = c4.w;
     }
-    uint32_t* o = reinterpret_cast<uint32_t*>(orow) + 3 * g;
-    o[0] = __byte_perm(px[0], px[1], 0x4210);
-    o[1] = __byte_perm(px[1], px[2], 0x5421);
-    o[2] = __byte_perm(px[2], px[3], 0x6542);
+  }
+  int slot = 0, round = 0;
+  for (int it = 0; it < my_items; ++it) {
+    mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
+    const int* rec = recs + slot * kRecHeader;
+    const int2 bb = *reinterpret_cast<const int2*>(rec + 2);                       // b0, b1
+    uint32_t* drow = *reinterpret_cast<uint32_t* const*>(rec + 6);                 // first byte of the output row
+    const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
+    if (on) {
+      uint32_t o[3];
+      group_pixels<DECIM>(r0, r0 + p.seg_stride, wo, sh, cs, DECIM ? ((uint32_t)bb.x << 15) : ((uint32_t)bb.x << 16),
+                          DECIM ? ((uint32_t)bb.y << 15) : ((uint32_t)bb.y << 16), sel_rgb, o);
+      uint32_t* d = drow + 3 * g;
+      asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d), "r"(o[0]) : "memory");
+      asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d + 1), "r"(o[1]) : "memory");
+      asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d + 2), "r"(o[2]) : "memory");
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[slot]);      // the staged rows of this slot are free again
+    if (++slot == p.stages) { slot = 0; ++round; }
   }
 }
 
@@ -231,7 +285,7 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
     if (p.has_overlay) { ob = __ldg(p.ov.op_offsets + ri.n); oe = __ldg(p.ov.op_offsets + ri.n + 1); }
     int slot = 0, round = 0;
     for (int it = 0; it < my_items; ++it) {
-      if (round > 0) mbar_wait(&empty[slot], (uint32_t)((round - 1) & 1), 1000, 100);
+      if (round > 0) mbar_wait(&empty[slot], (uint32_t)((round - 1) & 1), (uint32_t)p.wait_ns[0], (uint32_t)p.wait_ns[1]);
       const RowCoef rc = vertical_coef(ri.dy, p.scale_y, p.sh);
       uint8_t* s0 = stage + (size_t)slot * 2 * p.seg_stride;
       const uint8_t* f = p.src + (long long)ri.n * p.src_frame_stride;
@@ -258,6 +312,7 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
       *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
       rec[4] = ob;
       rec[5] = nops;
+      *reinterpret_cast<uint8_t**>(rec + 6) = p.dst + (long long)ri.n * p.dst_frame_stride + (long long)ri.dy * p.dst_row_stride;
       mbar_expect_tx(&full[slot], 2u * (uint32_t)p.row_bytes + idx_bytes);   // release: record visible
       ri.next(p.items, chunk, stride_items, p.dh);
       ob = ob_next; oe = oe_next;
@@ -270,9 +325,15 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
   const int row_bytes_out = p.dw * 3;
   const uint32_t sel_rgb = p.swap_rb ? 0x7014u : 0x7410u;   // (c0 c1 . .),(c2) -> c0 c1 c2 0 | c2 c1 c0 0
   const int nseg = p.ov.index_segments, nw = p.ov.index_words;
+  if (p.fast_rows && groups <= ncons * 32) {
+    const int g = warp * 32 + lane;
+    if (decim) consume_rows_fast<true>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, g < groups, sel_rgb, lane);
+    else consume_rows_fast<false>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, g < groups, sel_rgb, lane);
+    return;
+  }
   int slot = 0, round = 0;
   for (int it = 0; it < my_items; ++it) {
-    mbar_wait(&full[slot], (uint32_t)(round & 1), 500, 0);
+    mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
     const int* rec = recs + slot * kRecHeader;
     const int4 hdr = *reinterpret_cast<const int4*>(rec);   // n, dy, b0, b1
     const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
@@ -485,6 +546,11 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   const long long chunks = ((long long)p.items + chunk - 1) / chunk;
   if (grid > chunks) grid = chunks;
   p.items_per_cta = chunk;
+  p.fast_rows = (!p.has_overlay && (p.dw & 3) == 0 && !env_int("AIKO_B200_RESIZE_SLOW_ROWS", 0) &&
+                 ((reinterpret_cast<uintptr_t>(p.dst) | (uintptr_t)p.dst_row_stride | (uintptr_t)p.dst_frame_stride) & 3) == 0)
+                    ? 1 : 0;
+  p.wait_ns[0] = env_int("AIKO_B200_RESIZE_PW", 1000); p.wait_ns[1] = env_int("AIKO_B200_RESIZE_PB", 100);
+  p.wait_ns[2] = env_int("AIKO_B200_RESIZE_CW", 500); p.wait_ns[3] = env_int("AIKO_B200_RESIZE_CB", 0);
   resize3_staged<<<(unsigned)grid, threads, smem, stream>>>(p);
   *done = true;
   return cuda_status(cudaGetLastError(), "resize3_staged launch");
