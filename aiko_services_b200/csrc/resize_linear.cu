@@ -522,7 +522,11 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
     return fixed + (size_t)st * (kRecHeader * 4 + (size_t)p.index_words_per_frame * 4 +
                                  (size_t)p.ops_cap * sizeof(aiko_b200_overlay_op) + 2 * (size_t)p.seg_stride);
   };
-  int stages = env_int("AIKO_B200_RESIZE_STAGES", 2);
+  // Measured on 32 x 1080p (us per launch; CTAs per SM x ring stages): 6x2 37.8, 5x2 35.5, 4x3 37.5, 5x3 39.5,
+  // 4x4 39.3, 3x2 38.6, 3x3 35.1, 2x4 35.1, 2x6 35.1, 2x8 35.9, 1x8 55.4.  The consumers wait for the ring
+  // half of the time, so few CTAs with deeper rings lose nothing, and large shared-memory footprints per SM
+  // (> ~200 KB) were consistently slower: three stages, at most three CTAs per SM.
+  int stages = env_int("AIKO_B200_RESIZE_STAGES", 3);
   if (stages > 8) stages = 8;
   const size_t max_smem = (size_t)device_max_smem_optin();
   while (stages > 2 && need(stages) > max_smem) stages--;
@@ -540,6 +544,7 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   cudaPointerAttributes attr{};
   if (cudaPointerGetAttributes(&attr, p.src) == cudaSuccess && attr.type == cudaMemoryTypeHost) per_sm = 1;
   else (void)cudaGetLastError();
+  { const int cap = env_int("AIKO_B200_RESIZE_CTAS_PER_SM", 3); if (cap > 0 && cap < per_sm) per_sm = cap; }
   int chunk = env_int("AIKO_B200_RESIZE_CHUNK", 1);
   if (chunk < 1) chunk = 1;
   long long grid = (long long)sm_count() * per_sm;
