@@ -526,7 +526,8 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   // 4x4 39.3, 3x2 38.6, 3x3 35.1, 2x4 35.1, 2x6 35.1, 2x8 35.9, 1x8 55.4.  The consumers wait for the ring
   // half of the time, so few CTAs with deeper rings lose nothing, and large shared-memory footprints per SM
   // (> ~200 KB) were consistently slower: three stages, at most three CTAs per SM.
-  int stages = env_int("AIKO_B200_RESIZE_STAGES", 3);
+  // (The single-kernel overlay variant keeps the settings it was tuned with: every occupancy slot, two stages.)
+  int stages = env_int("AIKO_B200_RESIZE_STAGES", p.has_overlay ? 2 : 3);
   if (stages > 8) stages = 8;
   const size_t max_smem = (size_t)device_max_smem_optin();
   while (stages > 2 && need(stages) > max_smem) stages--;
@@ -544,7 +545,7 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   cudaPointerAttributes attr{};
   if (cudaPointerGetAttributes(&attr, p.src) == cudaSuccess && attr.type == cudaMemoryTypeHost) per_sm = 1;
   else (void)cudaGetLastError();
-  { const int cap = env_int("AIKO_B200_RESIZE_CTAS_PER_SM", 3); if (cap > 0 && cap < per_sm) per_sm = cap; }
+  { const int cap = env_int("AIKO_B200_RESIZE_CTAS_PER_SM", p.has_overlay ? 0 : 3); if (cap > 0 && cap < per_sm) per_sm = cap; }
   int chunk = env_int("AIKO_B200_RESIZE_CHUNK", 1);
   if (chunk < 1) chunk = 1;
   long long grid = (long long)sm_count() * per_sm;
