@@ -9,6 +9,8 @@
 // the copy that is still in shared memory.  Twiddles come from a table generated in double
 // precision (aiko_b200_audio_prepare); all arithmetic is fp32 (tolerance 1e-4).
 // Per window HBM sees 2N bytes in (int16) and 4N bytes out: the path is HBM-bound.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace aiko {
@@ -110,17 +112,17 @@ __device__ __forceinline__ void butterfly_store(float2* __restrict__ y, float2* 
 #pragma unroll
   for (int j = 1; j < R; j++) y[pidx(q + s * (R * p + j))] = cmul(a[j], tw[p * j * tw_step]);
 }
-template <int R>
+template <int R, int NT>
 __device__ __forceinline__ void stockham_pass(const float2* __restrict__ x, float2* __restrict__ y, int n, int s,
                                               const float2* __restrict__ tw, int half) {
   const int m = n / R, total = m * s, tw_step = half / n;
   const float inv_s = 1.0f / (float)s;
   int b = threadIdx.x;
-  for (; b + kAudioThreads < total; b += 2 * kAudioThreads) {
+  for (; b + NT < total; b += 2 * NT) {
     float2 a0[R], a1[R];
     int p0, q0, p1, q1;
     butterfly_load<R>(x, b, m, s, inv_s, a0, &p0, &q0);
-    butterfly_load<R>(x, b + kAudioThreads, m, s, inv_s, a1, &p1, &q1);
+    butterfly_load<R>(x, b + NT, m, s, inv_s, a1, &p1, &q1);
     butterfly_store<R>(y, a0, p0, q0, s, tw, tw_step);
     butterfly_store<R>(y, a1, p1, q1, s, tw, tw_step);
   }
@@ -132,14 +134,75 @@ __device__ __forceinline__ void stockham_pass(const float2* __restrict__ x, floa
   }
 }
 
-__global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const AudioParams p) {
+// ---- half = 8000 = 20^3 (the reference's 16 kHz x 1 s window): three radix-20 passes ----------
+// A radix-20 butterfly runs in registers as 5 DFTs of 4 points, 12 twiddles, 4 DFTs of 5 points
+// (n = 5 n1 + n2, k = k1 + 4 k2), so the window crosses shared memory three times instead of six.
+// Points are padded by one element after every 20: the stride-20 stores of the first pass then
+// step through shared memory with an odd stride and are conflict-free.
+__device__ __forceinline__ int pad20(int i) { return i + i / 20; }
+
+__device__ __forceinline__ void dft20(float2* a) {   // in: a[n]; out: X[k1 + 4 k2] in a[5 k1 + k2]
+  // exp(-2 pi i e / 20), e = 1 .. 9, 12
+  const float2 w1 = make_float2(0.95105651629515357f, -0.30901699437494742f);
+  const float2 w2 = make_float2(0.80901699437494742f, -0.58778525229247313f);
+  const float2 w3 = make_float2(0.58778525229247313f, -0.80901699437494742f);
+  const float2 w4 = make_float2(0.30901699437494742f, -0.95105651629515357f);
+  const float2 w6 = make_float2(-0.30901699437494742f, -0.95105651629515357f);
+  const float2 w8 = make_float2(-0.80901699437494742f, -0.58778525229247313f);
+  const float2 w9 = make_float2(-0.95105651629515357f, -0.30901699437494742f);
+  const float2 w12 = make_float2(-0.80901699437494742f, 0.58778525229247313f);
+  float2 y[4][5];                       // y[k1][n2]
+#pragma unroll
+  for (int n2 = 0; n2 < 5; n2++) {
+    float2 t[4] = {a[n2], a[5 + n2], a[10 + n2], a[15 + n2]};
+    dft_small<4>(t);
+#pragma unroll
+    for (int k1 = 0; k1 < 4; k1++) y[k1][n2] = t[k1];
+  }
+  y[1][1] = cmul(y[1][1], w1); y[1][2] = cmul(y[1][2], w2); y[1][3] = cmul(y[1][3], w3); y[1][4] = cmul(y[1][4], w4);
+  y[2][1] = cmul(y[2][1], w2); y[2][2] = cmul(y[2][2], w4); y[2][3] = cmul(y[2][3], w6); y[2][4] = cmul(y[2][4], w8);
+  y[3][1] = cmul(y[3][1], w3); y[3][2] = cmul(y[3][2], w6); y[3][3] = cmul(y[3][3], w9); y[3][4] = cmul(y[3][4], w12);
+#pragma unroll
+  for (int k1 = 0; k1 < 4; k1++) {
+    dft_small<5>(y[k1]);
+#pragma unroll
+    for (int k2 = 0; k2 < 5; k2++) a[5 * k1 + k2] = y[k1][k2];
+  }
+}
+
+// One radix-20 Stockham pass over 8000 points by threads 0 .. 399: sub-transform stride S
+// (1, 20, 400), reads x, writes y; twiddles exp(-2 pi i p j S / 8000) from the table.
+template <int S>
+__device__ __forceinline__ void radix20_pass(const float2* __restrict__ x, float2* __restrict__ y,
+                                             const float2* __restrict__ tw) {
+  constexpr int M = 400 / S;            // butterflies per sub-transform = stride between the 20 inputs / S
+  const int b = threadIdx.x;
+  if (b >= 400) return;
+  const int p = b / S, q = b - p * S;
+  float2 a[20];
+#pragma unroll
+  for (int k = 0; k < 20; k++) a[k] = x[pad20(q + S * (p + M * k))];
+  dft20(a);
+#pragma unroll
+  for (int j = 0; j < 20; j++) {
+    float2 v = a[5 * (j & 3) + (j >> 2)];
+    if (S < 400 && j > 0) v = cmul(v, tw[p * j * S]);
+    y[pad20(q + S * (20 * p + j))] = v;
+  }
+}
+
+template <bool FAST>
+__device__ __forceinline__ int point_index(int i) { return FAST ? pad20(i) : pidx(i); }
+
+template <int NT, bool FAST>
+__global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
   float2* buf0 = reinterpret_cast<float2*>(smem);
   float2* buf1 = buf0 + padded_points(p.half);
   const float2* tw = p.tw_half;
   if (p.tw_in_smem) {           // the pass twiddles next to the data: one copy per CTA, reused for every window
     float2* tws = buf1 + padded_points(p.half);
-    for (int i = threadIdx.x; i < p.half; i += kAudioThreads) tws[i] = __ldg(p.tw_half + i);
+    for (int i = threadIdx.x; i < p.half; i += NT) tws[i] = __ldg(p.tw_half + i);
     tw = tws;
     __syncthreads();
   }
@@ -147,43 +210,72 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
   __shared__ int hist[kHistBins];
   const int half = p.half, n = p.n;
 
+  // int16 windows are fetched one window ahead into registers (while the previous window is
+  // unpacked and gated), so the FFT never waits for HBM
+  constexpr int PRE = kMaxHalf / NT;
+  uint32_t pre[PRE];
+  auto prefetch = [&](int w) {
+    const uint32_t* in = reinterpret_cast<const uint32_t*>(static_cast<const int16_t*>(p.audio) + (size_t)w * n);
+#pragma unroll
+    for (int j = 0; j < PRE; j++) {
+      const int i = threadIdx.x + j * NT;
+      pre[j] = i < half ? __ldg(in + i) : 0u;
+    }
+  };
+  if (p.dtype == 0 && (int)blockIdx.x < p.n_windows) prefetch(blockIdx.x);
+  const float2 w_odd = __ldg(p.tw_full + 1);          // exp(-2 pi i / n): tw_full[k] = tw_half[k / 2] * w_odd^(k & 1)
+
   for (int w = blockIdx.x; w < p.n_windows; w += gridDim.x) {
     // ---- pack the real window into half complex points
     if (p.dtype == 0) {
-      const short2* in = reinterpret_cast<const short2*>(static_cast<const int16_t*>(p.audio) + (size_t)w * n);
-      for (int i = threadIdx.x; i < half; i += kAudioThreads) {
-        const short2 v = __ldg(in + i);
-        buf0[pidx(i)] = make_float2((float)v.x, (float)v.y);
+#pragma unroll
+      for (int j = 0; j < PRE; j++) {
+        const int i = threadIdx.x + j * NT;
+        if (i < half)
+          buf0[point_index<FAST>(i)] = make_float2((float)(short)(pre[j] & 0xffffu), (float)(short)(pre[j] >> 16));
       }
     } else {
       const float2* in = reinterpret_cast<const float2*>(static_cast<const float*>(p.audio) + (size_t)w * n);
-      for (int i = threadIdx.x; i < half; i += kAudioThreads) buf0[pidx(i)] = __ldg(in + i);
+      for (int i = threadIdx.x; i < half; i += NT) buf0[point_index<FAST>(i)] = __ldg(in + i);
     }
     __syncthreads();
     // ---- half-length complex FFT
     float2 *x = buf0, *y = buf1;
-    int len = half, stride = 1;
-    for (int st = 0; st < p.n_stages; st++) {
-      const int r = p.radix[st];
-      if (r == 4) stockham_pass<4>(x, y, len, stride, tw, half);
-      else if (r == 5) stockham_pass<5>(x, y, len, stride, tw, half);
-      else if (r == 3) stockham_pass<3>(x, y, len, stride, tw, half);
-      else stockham_pass<2>(x, y, len, stride, tw, half);
-      len /= r;
-      stride *= r;
-      float2* t = x; x = y; y = t;
+    if (FAST) {
+      radix20_pass<1>(buf0, buf1, tw);
       __syncthreads();
+      radix20_pass<20>(buf1, buf0, tw);
+      __syncthreads();
+      radix20_pass<400>(buf0, buf1, tw);
+      __syncthreads();
+      x = buf1; y = buf0;               // spectrum in buf1, buf0 is idle
+    } else {
+      int len = half, stride = 1;
+      for (int st = 0; st < p.n_stages; st++) {
+        const int r = p.radix[st];
+        if (r == 4) stockham_pass<4, NT>(x, y, len, stride, tw, half);
+        else if (r == 5) stockham_pass<5, NT>(x, y, len, stride, tw, half);
+        else if (r == 3) stockham_pass<3, NT>(x, y, len, stride, tw, half);
+        else stockham_pass<2, NT>(x, y, len, stride, tw, half);
+        len /= r;
+        stride *= r;
+        float2* t = x; x = y; y = t;
+        __syncthreads();
+      }
     }
     // ---- unpack to the spectrum of the real window, magnitudes / 1e6 (audio_io.py:299,309)
     float* amp = reinterpret_cast<float*>(y);          // half + 1 magnitudes, in the idle buffer
     float* out = p.amplitudes + (size_t)w * n;
-    for (int k = threadIdx.x; k <= half; k += kAudioThreads) {
-      const float2 zk = x[pidx(k == half ? 0 : k)];
-      const float2 zr = x[pidx(k == 0 ? 0 : half - k)];
+    if (p.dtype == 0 && w + (int)gridDim.x < p.n_windows) prefetch(w + gridDim.x);
+    for (int k = threadIdx.x; k <= half; k += NT) {
+      const float2 zk = x[point_index<FAST>(k == half ? 0 : k)];
+      const float2 zr = x[point_index<FAST>(k == 0 ? 0 : half - k)];
       const float2 zc = make_float2(zr.x, -zr.y);
       const float2 e = cscale(cadd(zk, zc), 0.5f);
       const float2 o = cscale(mul_mi(csub(zk, zc)), 0.5f);
-      const float2 xk = cadd(e, cmul(__ldg(p.tw_full + k), o));
+      float2 tk = tw[k >> 1];                             // (k == half: tw_half[half / 2] = -1)
+      if (k & 1) tk = cmul(tk, w_odd);
+      const float2 xk = cadd(e, cmul(tk, o));
       const float a = sqrtf(__fmaf_rn(xk.x, xk.x, xk.y * xk.y)) * 1e-6f;
       amp[k] = a;
       out[k] = a;
@@ -211,7 +303,7 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
       // Appends every bin that passes the gates and whose key bin is >= min_bin (each bin k stands
       // for spectrum indices k and n - k).  One atomic per warp; order in the list is irrelevant.
       auto collect = [&](unsigned min_bin) {
-        for (int base = klo; base <= khi; base += kAudioThreads) {
+        for (int base = klo; base <= khi; base += NT) {
           const int k = base + (int)threadIdx.x;
           float a = 0.f;
           int copies = 0;
@@ -244,10 +336,10 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
       if (s_count > kDirectSort) {
         // Many bins pass the gates (noise-like input): keep only key bins that can reach the top 100.
         __syncthreads();
-        for (int i = threadIdx.x; i < kHistBins; i += kAudioThreads) hist[i] = 0;
+        for (int i = threadIdx.x; i < kHistBins; i += NT) hist[i] = 0;
         if (threadIdx.x == 0) { s_count = 0; s_threshold_bin = 0; }
         __syncthreads();
-        for (int k = klo + threadIdx.x; k <= khi; k += kAudioThreads) {
+        for (int k = klo + threadIdx.x; k <= khi; k += NT) {
           const float a = amp[k];
           if (a >= p.amp_min && a <= p.amp_max)
             atomicAdd(&hist[__float_as_uint(a) >> 20], (k != 0 && k != half) ? 2 : 1);
@@ -276,12 +368,12 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
       const int count = min(s_count, list_cap);
       int padded = 1;
       while (padded < count) padded <<= 1;
-      for (int i = count + threadIdx.x; i < padded; i += kAudioThreads) list[i] = 0ull;   // sorts last
+      for (int i = count + threadIdx.x; i < padded; i += NT) list[i] = 0ull;   // sorts last
       __syncthreads();
       // Bitonic sort, descending.  Only the warps that hold elements take part; exchanges with
       // a stride below 32 stay inside a warp (__syncwarp), wider ones use a named barrier over
       // the participating threads.
-      const int sorters = min(max(padded, 32), kAudioThreads);
+      const int sorters = min(max(padded, 32), NT);
       if ((int)threadIdx.x < sorters) {
         for (int size = 2; size <= padded; size <<= 1) {
           for (int strd = size >> 1; strd > 0; strd >>= 1) {
@@ -303,7 +395,7 @@ __global__ void __launch_bounds__(kAudioThreads, 1) audio_chain_kernel(const Aud
       }
       __syncthreads();
       const int take = min(count, kTopK);
-      for (int i = threadIdx.x; i < kTopK; i += kAudioThreads) {
+      for (int i = threadIdx.x; i < kTopK; i += NT) {
         float a = 0.f, f = 0.f;
         if (i < take) {
           const unsigned long long e = list[i];
@@ -414,12 +506,16 @@ extern "C" int aiko_b200_audio_chain(const void* audio, int dtype, int n_windows
   // static shared memory: 16 KB histogram + a few words; keep the twiddles on chip when there is room
   p.tw_in_smem = (smem + (size_t)p.half * sizeof(float2) + 17 * 1024 <= (size_t)device_max_smem_optin()) ? 1 : 0;
   if (p.tw_in_smem) smem += (size_t)p.half * sizeof(float2);
-  AIKO_CUDA(cudaFuncSetAttribute(audio_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // 16000-sample windows (half = 20^3) take the radix-20 kernel: 512 threads, 128 registers each
+  const bool fast = p.half == 8000 && !getenv("AIKO_B200_AUDIO_GENERIC");
+  auto kernel = fast ? audio_chain_kernel<512, true> : audio_chain_kernel<kAudioThreads, false>;
+  const int threads = fast ? 512 : kAudioThreads;
+  AIKO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, audio_chain_kernel, kAudioThreads, smem));
+  AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
   if (per_sm < 1) per_sm = 1;
   long long grid = (long long)sm_count() * per_sm;
   if (grid > n_windows) grid = n_windows;
-  audio_chain_kernel<<<(unsigned)grid, kAudioThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  kernel<<<(unsigned)grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(p);
   return cuda_status(cudaGetLastError(), "audio_chain launch");
 }
