@@ -22,6 +22,7 @@ constexpr int kTopK = 100;           // AF_SAMPLES_MAXIMUM, audio_io.py:206
 constexpr int kBands = 8;            // AR_BAND_COUNT, audio_io.py:237
 constexpr int kHistBins = 4096;
 constexpr int kDirectSort = 1024;    // up to this many gated bins are sorted directly
+constexpr int kRankSort = 512;       // ... and up to this many by counting ranks instead of exchanging
 
 struct AudioParams {
   const void* audio;
@@ -207,6 +208,8 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
     __syncthreads();
   }
   __shared__ int s_count, s_threshold_bin;
+  __shared__ float s_band[kBands][4];
+  __shared__ unsigned long long s_top[kTopK];
   __shared__ int hist[kHistBins];
   const int half = p.half, n = p.n;
 
@@ -284,13 +287,26 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
     __syncthreads();
     // ---- PE_AudioResampler: 8 band sums over the first half of the spectrum (audio_io.py:250-277)
     if (p.band_sums != nullptr) {
+      // every warp sums one slice of one band; the slices of a band are then added in a fixed order
+      constexpr int kParts = NT / 32 / kBands;
       const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-      if (warp < kBands) {
-        float sum = 0.f;
-        for (int k = p.band_lo[warp] + lane; k < p.band_hi[warp]; k += 32) sum += amp[k];
+      const int band = warp % kBands, part = warp / kBands;
+      const int lo = p.band_lo[band], len = p.band_hi[band] - lo;
+      const int k0 = lo + (int)((long long)len * part / kParts), k1 = lo + (int)((long long)len * (part + 1) / kParts);
+      float s0 = 0.f, s1 = 0.f;
+      int k = k0 + lane;
+      for (; k + 32 < k1; k += 64) { s0 += amp[k]; s1 += amp[k + 32]; }
+      if (k < k1) s0 += amp[k];
+      float sum = s0 + s1;
 #pragma unroll
-        for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
-        if (lane == 0) p.band_sums[(size_t)w * kBands + warp] = sum;
+      for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+      if (lane == 0) s_band[band][part] = sum;
+      __syncthreads();
+      if (threadIdx.x < kBands) {
+        float total = 0.f;
+#pragma unroll
+        for (int q = 0; q < kParts; q++) total += s_band[threadIdx.x][q];
+        p.band_sums[(size_t)w * kBands + threadIdx.x] = total;
       }
     }
     // ---- PE_AudioFilter: gate on amplitude and |frequency|, then the 100 largest by amplitude,
@@ -366,6 +382,20 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
         __syncthreads();
       }
       const int count = min(s_count, list_cap);
+      const unsigned long long* sorted = list;
+      if (count <= kRankSort) {
+        // Few candidates: every thread finds the rank of its own key by counting the larger ones
+        // (keys are distinct: the bin index is part of them).  No exchanges, one barrier.
+        for (int i = threadIdx.x; i < count; i += NT) {
+          const unsigned long long key = list[i];
+          int rank = 0;
+#pragma unroll 4
+          for (int j = 0; j < count; j++) rank += (list[j] > key) ? 1 : 0;
+          if (rank < kTopK) s_top[rank] = key;
+        }
+        sorted = s_top;
+        __syncthreads();
+      } else {
       int padded = 1;
       while (padded < count) padded <<= 1;
       for (int i = count + threadIdx.x; i < padded; i += NT) list[i] = 0ull;   // sorts last
@@ -394,11 +424,12 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
         }
       }
       __syncthreads();
+      }
       const int take = min(count, kTopK);
       for (int i = threadIdx.x; i < kTopK; i += NT) {
         float a = 0.f, f = 0.f;
         if (i < take) {
-          const unsigned long long e = list[i];
+          const unsigned long long e = sorted[i];
           const unsigned idx = 0xffffffffu - (unsigned)(e & 0xffffffffu);
           a = __uint_as_float((unsigned)(e >> 32));
           f = (float)min(idx, (unsigned)n - idx) * p.hz_per_bin;
@@ -503,8 +534,8 @@ extern "C" int aiko_b200_audio_chain(const void* audio, int dtype, int n_windows
   p.amp_max = 12.0f;
   p.hz_per_bin = (float)(sample_rate / (double)n_samples);
   size_t smem = (size_t)2 * padded_points(p.half) * sizeof(float2);
-  // static shared memory: 16 KB histogram + a few words; keep the twiddles on chip when there is room
-  p.tw_in_smem = (smem + (size_t)p.half * sizeof(float2) + 17 * 1024 <= (size_t)device_max_smem_optin()) ? 1 : 0;
+  // static shared memory: 16 KB histogram + ~1 KB of small tables; keep the twiddles on chip when there is room
+  p.tw_in_smem = (smem + (size_t)p.half * sizeof(float2) + 18 * 1024 <= (size_t)device_max_smem_optin()) ? 1 : 0;
   if (p.tw_in_smem) smem += (size_t)p.half * sizeof(float2);
   // 16000-sample windows (half = 20^3) take the radix-20 kernel: 512 threads, 128 registers each
   const bool fast = p.half == 8000 && !getenv("AIKO_B200_AUDIO_GENERIC");
