@@ -279,7 +279,9 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
       float2 tk = tw[k >> 1];                             // (k == half: tw_half[half / 2] = -1)
       if (k & 1) tk = cmul(tk, w_odd);
       const float2 xk = cadd(e, cmul(tk, o));
-      const float a = sqrtf(__fmaf_rn(xk.x, xk.x, xk.y * xk.y)) * 1e-6f;
+      float a;                                            // |X[k]| / 1e6; the approximate root is within 1e-6 relative
+      asm("sqrt.approx.f32 %0, %1;" : "=f"(a) : "f"(__fmaf_rn(xk.x, xk.x, xk.y * xk.y)));
+      a *= 1e-6f;
       amp[k] = a;
       out[k] = a;
       if (k != 0 && k != half) out[n - k] = a;         // |X[n-k]| = |X[k]| for real input
@@ -329,15 +331,12 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
               copies = (k != 0 && k != half) ? 2 : 1;
           }
           if (__ballot_sync(0xffffffffu, copies != 0) == 0) continue;
-          int incl = copies;
-#pragma unroll
-          for (int d = 1; d < 32; d <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += t;
-          }
+          // exclusive prefix of `copies` (0, 1 or 2) over the warp from two ballots
+          const unsigned m1 = __ballot_sync(0xffffffffu, copies >= 1), m2 = __ballot_sync(0xffffffffu, copies == 2);
+          const unsigned below = (1u << lane) - 1u;
           int start = 0;
-          if (lane == 31) start = atomicAdd(&s_count, incl);
-          start = __shfl_sync(0xffffffffu, start, 31) + incl - copies;
+          if (lane == 0) start = atomicAdd(&s_count, __popc(m1) + __popc(m2));
+          start = __shfl_sync(0xffffffffu, start, 0) + __popc(m1 & below) + __popc(m2 & below);
           if (copies) {
             const unsigned long long hi = (unsigned long long)__float_as_uint(a) << 32;
             if (start < list_cap) list[start] = hi | (0xffffffffu - (unsigned)k);
