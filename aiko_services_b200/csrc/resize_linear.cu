@@ -33,6 +33,7 @@ struct ResizeParams {
   int ops_cap;                 // draw-list entries staged per ring slot next to the index (0: read from global)
   int wait_ns[4];              // producer wait: suspend hint, back-off; consumer wait: suspend hint, back-off
   int fast_rows;               // no draw list in the row loop, whole 4-pixel groups, 4-byte aligned output rows
+  int evict_first;             // source rows are read once: keep them from displacing other data in L2
 };
 
 // cv2's coefficient derivation (float32 phase from a double position, 11-bit weights).
@@ -284,13 +285,19 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
     int ob = 0, oe = 0, ob_next = 0, oe_next = 0;
     if (p.has_overlay) { ob = __ldg(p.ov.op_offsets + ri.n); oe = __ldg(p.ov.op_offsets + ri.n + 1); }
     int slot = 0, round = 0;
+    const uint64_t policy = l2_policy_evict_first();
     for (int it = 0; it < my_items; ++it) {
       if (round > 0) mbar_wait(&empty[slot], (uint32_t)((round - 1) & 1), (uint32_t)p.wait_ns[0], (uint32_t)p.wait_ns[1]);
       const RowCoef rc = vertical_coef(ri.dy, p.scale_y, p.sh);
       uint8_t* s0 = stage + (size_t)slot * 2 * p.seg_stride;
       const uint8_t* f = p.src + (long long)ri.n * p.src_frame_stride;
-      bulk_g2s(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
-      bulk_g2s(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
+      if (p.evict_first) {      // each source row is read once (vertical scale >= 2)
+        bulk_g2s_hint(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot], policy);
+        bulk_g2s_hint(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot], policy);
+      } else {
+        bulk_g2s(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
+        bulk_g2s(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
+      }
       const int nops = oe - ob;
       uint32_t idx_bytes = 0;
       if (p.index_words_per_frame > 0 && nops > 0) {
@@ -555,6 +562,7 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   p.fast_rows = (!p.has_overlay && (p.dw & 3) == 0 && !env_int("AIKO_B200_RESIZE_SLOW_ROWS", 0) &&
                  ((reinterpret_cast<uintptr_t>(p.dst) | (uintptr_t)p.dst_row_stride | (uintptr_t)p.dst_frame_stride) & 3) == 0)
                     ? 1 : 0;
+  p.evict_first = (p.sh >= 2 * p.dh && env_int("AIKO_B200_RESIZE_EVICT_FIRST", 1)) ? 1 : 0;
   p.wait_ns[0] = env_int("AIKO_B200_RESIZE_PW", 1000); p.wait_ns[1] = env_int("AIKO_B200_RESIZE_PB", 100);
   p.wait_ns[2] = env_int("AIKO_B200_RESIZE_CW", 500); p.wait_ns[3] = env_int("AIKO_B200_RESIZE_CB", 0);
   resize3_staged<<<(unsigned)grid, threads, smem, stream>>>(p);
