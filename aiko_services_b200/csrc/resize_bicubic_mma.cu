@@ -278,6 +278,7 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
   if (warp == nwarps) {
     // ---- producer: lanes 0..7 each ask the TMA engine for one source row of the batch ------------
     int gb = 0;   // batches issued by this CTA so far: staging buffer and barrier phase follow from it
+    const uint64_t policy = l2_policy_evict_first();   // source rows are read once (plus the band halo)
     for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
       const MmaItem it = mma_item<KX>(p, item);
       if (it.copy_bytes > p.raw_pitch) __trap();
@@ -289,8 +290,8 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
         __syncwarp();
         if (lane < kBatchRows) {
           const int row = min(it.row_start + b * kBatchRows + lane, p.sh - 1);   // rows past the frame carry no weight
-          bulk_g2s(raw + (size_t)(s * kBatchRows + lane) * p.raw_pitch, fsrc + (size_t)row * row_bytes,
-                   (uint32_t)it.copy_bytes, &full[s]);
+          bulk_g2s_hint(raw + (size_t)(s * kBatchRows + lane) * p.raw_pitch, fsrc + (size_t)row * row_bytes,
+                        (uint32_t)it.copy_bytes, &full[s], policy);
         }
       }
     }

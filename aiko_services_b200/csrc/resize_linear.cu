@@ -34,6 +34,7 @@ struct ResizeParams {
   int wait_ns[4];              // producer wait: suspend hint, back-off; consumer wait: suspend hint, back-off
   int fast_rows;               // no draw list in the row loop, whole 4-pixel groups, 4-byte aligned output rows
   int evict_first;             // source rows are read once: keep them from displacing other data in L2
+  int keep_output;             // a second pass over the output follows: store it with an L2 evict-last hint
 };
 
 // cv2's coefficient derivation (float32 phase from a double position, 11-bit weights).
@@ -200,6 +201,8 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
     }
   }
   int slot = 0, round = 0;
+  uint64_t keep;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
   for (int it = 0; it < my_items; ++it) {
     mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
     const int* rec = recs + slot * kRecHeader;
@@ -211,9 +214,15 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
       group_pixels<DECIM>(r0, r0 + p.seg_stride, wo, sh, cs, DECIM ? ((uint32_t)bb.x << 15) : ((uint32_t)bb.x << 16),
                           DECIM ? ((uint32_t)bb.y << 15) : ((uint32_t)bb.y << 16), sel_rgb, o);
       uint32_t* d = drow + 3 * g;
-      asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d), "r"(o[0]) : "memory");
-      asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d + 1), "r"(o[1]) : "memory");
-      asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d + 2), "r"(o[2]) : "memory");
+      if (p.keep_output) {      // the overlay pass reads these pixels next: ask L2 to hold on to them
+        asm volatile("st.global.L1::no_allocate.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(d), "r"(o[0]), "l"(keep) : "memory");
+        asm volatile("st.global.L1::no_allocate.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(d + 1), "r"(o[1]), "l"(keep) : "memory");
+        asm volatile("st.global.L1::no_allocate.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(d + 2), "r"(o[2]), "l"(keep) : "memory");
+      } else {
+        asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d), "r"(o[0]) : "memory");
+        asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d + 1), "r"(o[1]) : "memory");
+        asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d + 2), "r"(o[2]) : "memory");
+      }
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[slot]);      // the staged rows of this slot are free again
@@ -563,6 +572,7 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
                  ((reinterpret_cast<uintptr_t>(p.dst) | (uintptr_t)p.dst_row_stride | (uintptr_t)p.dst_frame_stride) & 3) == 0)
                     ? 1 : 0;
   p.evict_first = (p.sh >= 2 * p.dh && env_int("AIKO_B200_RESIZE_EVICT_FIRST", 1)) ? 1 : 0;
+  p.keep_output = env_int("AIKO_B200_RESIZE_KEEP_OUTPUT", p.keep_output);
   p.wait_ns[0] = env_int("AIKO_B200_RESIZE_PW", 1000); p.wait_ns[1] = env_int("AIKO_B200_RESIZE_PB", 100);
   p.wait_ns[2] = env_int("AIKO_B200_RESIZE_CW", 500); p.wait_ns[3] = env_int("AIKO_B200_RESIZE_CB", 0);
   resize3_staged<<<(unsigned)grid, threads, smem, stream>>>(p);
@@ -639,7 +649,7 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
     // inside the row loop (AIKO_B200_OVERLAY_FUSED=1 selects that single-kernel variant).
     const bool two_pass = p.has_overlay && !env_int("AIKO_B200_OVERLAY_FUSED", 0);
     ResizeParams q = p;
-    if (two_pass) q.has_overlay = 0;
+    if (two_pass) { q.has_overlay = 0; q.keep_output = 1; }   // the overlay pass re-reads the pixels it touches
     bool done = false;
     const int rc = launch_staged3(q, st, &done);
     if (rc != AIKO_B200_OK) return rc;
