@@ -8,6 +8,8 @@
 // magnitudes / 1e6 go to HBM once, and the band sums and the gate + top-100 selection run on
 // the copy that is still in shared memory.  Twiddles come from a table generated in double
 // precision (aiko_b200_audio_prepare); all arithmetic is fp32 (tolerance 1e-4).
+// 16000-sample windows (8000 = 20^3 points) take three radix-20 passes whose butterflies stay in
+// registers, and the next window's samples are fetched while the current one is unpacked and gated.
 // Per window HBM sees 2N bytes in (int16) and 4N bytes out: the path is HBM-bound.
 #include <stdlib.h>
 

@@ -39,3 +39,14 @@ def test_version_and_error_string_without_gpu():
 def test_overlay_op_struct_layout():
     assert ctypes.sizeof(_native.OverlayOp) == 32
     assert ctypes.sizeof(_native.Overlay) == 104   # 7 pointers + 11 int32 (+ padding)
+
+
+def test_zero_copy_eligibility_rule():
+    """Frames may be read from pinned host memory by the kernel only when every needed source row is
+    fetched once with bulk row copies: RGB, 16-byte aligned rows, scale x <= 4, scale y >= 2."""
+    from aiko_services_b200 import ops
+    assert ops.reads_source_rows_once((1080, 1920, 3), 640, 480)
+    assert not ops.reads_source_rows_once((1080, 1920, 3), 1280, 720)      # rows would be fetched twice
+    assert not ops.reads_source_rows_once((1080, 1918, 3), 640, 480)       # unaligned rows: gathers
+    assert not ops.reads_source_rows_once((1080, 1920), 640, 480)          # gray: generic kernel
+    assert not ops.reads_source_rows_once((2160, 3840, 3), 224, 224)       # scale x > 4: gathers
