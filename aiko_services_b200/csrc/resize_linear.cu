@@ -35,6 +35,7 @@ struct ResizeParams {
   int fast_rows;               // no draw list in the row loop, whole 4-pixel groups, 4-byte aligned output rows
   int evict_first;             // source rows are read once: keep them from displacing other data in L2
   int keep_output;             // a second pass over the output follows: store it with an L2 evict-last hint
+  int unaligned;               // source rows do not start on 16-byte boundaries (register-resident row path only)
 };
 
 // cv2's coefficient derivation (float32 phase from a double position, 11-bit weights).
@@ -131,24 +132,24 @@ __device__ __forceinline__ uint32_t vblend_decim(uint32_t t0, uint32_t t1, uint3
 // DECIM: horizontal pass degenerates to picking one source pixel (all weights 2048, 0).
 template <bool DECIM>
 __device__ __forceinline__ void group_pixels(const uint8_t* r0, const uint8_t* r1, const int (&wo)[4], const int (&sh)[4],
-                                             const uint32_t (&cs)[4], uint32_t b0s, uint32_t b1s, uint32_t sel_rgb,
-                                             uint32_t (&o)[3]) {
+                                             const int (&wo1)[4], const int (&sh1)[4], const uint32_t (&cs)[4],
+                                             uint32_t b0s, uint32_t b1s, uint32_t sel_rgb, uint32_t (&o)[3]) {
   uint32_t px[4];
 #pragma unroll
   for (int k = 0; k < 4; k++) {
     const uint32_t* w0 = reinterpret_cast<const uint32_t*>(r0 + wo[k]);
-    const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1 + wo[k]);
+    const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1 + wo1[k]);
     uint32_t c0, c1, c2;
     if (DECIM) {
-      const uint32_t u = __funnelshift_r(w0[0], w0[1], sh[k]), v = __funnelshift_r(w1[0], w1[1], sh[k]);
+      const uint32_t u = __funnelshift_r(w0[0], w0[1], sh[k]), v = __funnelshift_r(w1[0], w1[1], sh1[k]);
       c0 = vblend_decim(__byte_perm(u, 0, 0x4404), __byte_perm(v, 0, 0x4404), b0s, b1s);   // tap << 8
       c1 = vblend_decim(__byte_perm(u, 0, 0x4414), __byte_perm(v, 0, 0x4414), b0s, b1s);
       c2 = vblend_decim(__byte_perm(u, 0, 0x4424), __byte_perm(v, 0, 0x4424), b0s, b1s);
     } else {
       const uint32_t u0 = w0[0], u1 = w0[1], u2 = w0[2];
       const uint32_t v0 = w1[0], v1 = w1[1], v2 = w1[2];
-      pixel_general(__funnelshift_r(u0, u1, sh[k]), __funnelshift_r(u1, u2, sh[k]), __funnelshift_r(v0, v1, sh[k]),
-                    __funnelshift_r(v1, v2, sh[k]), cs[k], b0s, b1s, &c0, &c1, &c2);
+      pixel_general(__funnelshift_r(u0, u1, sh[k]), __funnelshift_r(u1, u2, sh[k]), __funnelshift_r(v0, v1, sh1[k]),
+                    __funnelshift_r(v1, v2, sh1[k]), cs[k], b0s, b1s, &c0, &c1, &c2);
     }
     // c0 c1 c2 -> 24-bit pixel in stored channel order (sel_rgb swaps R and B when asked)
     px[k] = __byte_perm(__byte_perm(c0, c1, 0x0040), c2, sel_rgb);
@@ -174,7 +175,7 @@ __device__ __forceinline__ void consume_row(const uint8_t* r0, const uint8_t* r1
       cs[0] = c4.x; cs[1] = c4.y; cs[2] = c4.z; cs[3] = c4.w;
     }
     uint32_t o[3];
-    group_pixels<DECIM>(r0, r1, wo, sh, cs, b0s, b1s, sel_rgb, o);
+    group_pixels<DECIM>(r0, r1, wo, sh, wo, sh, cs, b0s, b1s, sel_rgb, o);
     uint32_t* d = reinterpret_cast<uint32_t*>(orow) + 3 * g;
     d[0] = o[0]; d[1] = o[1]; d[2] = o[2];
   }
@@ -184,7 +185,10 @@ __device__ __forceinline__ void consume_row(const uint8_t* r0, const uint8_t* r1
 // pixels for the whole kernel, so its tap offsets and weights stay in registers and its 12 result
 // bytes go from registers straight to global memory (the destination pointer of the row comes
 // from the producer's record).  No per-row table loads, no output row in shared memory.
-template <bool DECIM>
+// UNALIGNED: source rows that do not start on a 16-byte boundary were copied from the boundary
+// below, so each staged row starts `delta` (0..15, from the record) bytes into its buffer and the
+// word / shift split of a tap offset is redone per row.
+template <bool DECIM, bool UNALIGNED>
 __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_t* full, uint64_t* empty, const int* recs,
                                                   const uint8_t* stage, int my_items, const int* xw, const int* xs,
                                                   const uint32_t* xcoef, int g, bool on, uint32_t sel_rgb, int lane) {
@@ -211,8 +215,21 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
     const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
     if (on) {
       uint32_t o[3];
-      group_pixels<DECIM>(r0, r0 + p.seg_stride, wo, sh, cs, DECIM ? ((uint32_t)bb.x << 15) : ((uint32_t)bb.x << 16),
-                          DECIM ? ((uint32_t)bb.y << 15) : ((uint32_t)bb.y << 16), sel_rgb, o);
+      const uint32_t b0s = DECIM ? ((uint32_t)bb.x << 15) : ((uint32_t)bb.x << 16);
+      const uint32_t b1s = DECIM ? ((uint32_t)bb.y << 15) : ((uint32_t)bb.y << 16);
+      if (UNALIGNED) {
+        const int2 delta = *reinterpret_cast<const int2*>(rec + 4);
+        int wa[4], sa[4], wb[4], sb[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          const int exact = wo[k] + (sh[k] >> 3);      // byte offset of the tap in the source row
+          wa[k] = (exact + delta.x) & ~3; sa[k] = ((exact + delta.x) & 3) * 8;
+          wb[k] = (exact + delta.y) & ~3; sb[k] = ((exact + delta.y) & 3) * 8;
+        }
+        group_pixels<DECIM>(r0, r0 + p.seg_stride, wa, sa, wb, sb, cs, b0s, b1s, sel_rgb, o);
+      } else {
+        group_pixels<DECIM>(r0, r0 + p.seg_stride, wo, sh, wo, sh, cs, b0s, b1s, sel_rgb, o);
+      }
       uint32_t* d = drow + 3 * g;
       if (p.keep_output) {      // the overlay pass reads these pixels next: ask L2 to hold on to them
         asm volatile("st.global.L1::no_allocate.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(d), "r"(o[0]), "l"(keep) : "memory");
@@ -300,12 +317,17 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
       const RowCoef rc = vertical_coef(ri.dy, p.scale_y, p.sh);
       uint8_t* s0 = stage + (size_t)slot * 2 * p.seg_stride;
       const uint8_t* f = p.src + (long long)ri.n * p.src_frame_stride;
+      // a row is copied from the 16-byte boundary below its first byte to the one above its last
+      const uint8_t* a0 = f + (long long)rc.y0 * p.src_row_stride;
+      const uint8_t* a1 = f + (long long)rc.y1 * p.src_row_stride;
+      const uint32_t d0 = (uint32_t)(reinterpret_cast<uintptr_t>(a0) & 15), d1 = (uint32_t)(reinterpret_cast<uintptr_t>(a1) & 15);
+      const uint32_t n0 = (d0 + (uint32_t)p.row_bytes + 15u) & ~15u, n1 = (d1 + (uint32_t)p.row_bytes + 15u) & ~15u;
       if (p.evict_first) {      // each source row is read once (vertical scale >= 2)
-        bulk_g2s_hint(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot], policy);
-        bulk_g2s_hint(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot], policy);
+        bulk_g2s_hint(s0, a0 - d0, n0, &full[slot], policy);
+        bulk_g2s_hint(s0 + p.seg_stride, a1 - d1, n1, &full[slot], policy);
       } else {
-        bulk_g2s(s0, f + (long long)rc.y0 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
-        bulk_g2s(s0 + p.seg_stride, f + (long long)rc.y1 * p.src_row_stride, (uint32_t)p.row_bytes, &full[slot]);
+        bulk_g2s(s0, a0 - d0, n0, &full[slot]);
+        bulk_g2s(s0 + p.seg_stride, a1 - d1, n1, &full[slot]);
       }
       const int nops = oe - ob;
       uint32_t idx_bytes = 0;
@@ -326,10 +348,10 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
       }
       int* rec = recs + slot * kRecHeader;
       *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
-      rec[4] = ob;
-      rec[5] = nops;
+      rec[4] = p.unaligned ? (int)d0 : ob;          // (unaligned rows never carry a draw list in the row loop)
+      rec[5] = p.unaligned ? (int)d1 : nops;
       *reinterpret_cast<uint8_t**>(rec + 6) = p.dst + (long long)ri.n * p.dst_frame_stride + (long long)ri.dy * p.dst_row_stride;
-      mbar_expect_tx(&full[slot], 2u * (uint32_t)p.row_bytes + idx_bytes);   // release: record visible
+      mbar_expect_tx(&full[slot], n0 + n1 + idx_bytes);   // release: record visible
       ri.next(p.items, chunk, stride_items, p.dh);
       ob = ob_next; oe = oe_next;
       if (++slot == p.stages) { slot = 0; ++round; }
@@ -341,10 +363,16 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
   const int row_bytes_out = p.dw * 3;
   const uint32_t sel_rgb = p.swap_rb ? 0x7014u : 0x7410u;   // (c0 c1 . .),(c2) -> c0 c1 c2 0 | c2 c1 c0 0
   const int nseg = p.ov.index_segments, nw = p.ov.index_words;
-  if (p.fast_rows && groups <= ncons * 32) {
+  if (p.fast_rows) {
     const int g = warp * 32 + lane;
-    if (decim) consume_rows_fast<true>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, g < groups, sel_rgb, lane);
-    else consume_rows_fast<false>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, g < groups, sel_rgb, lane);
+    const bool on = g < groups;
+    if (p.unaligned) {
+      if (decim) consume_rows_fast<true, true>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
+      else consume_rows_fast<false, true>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
+    } else {
+      if (decim) consume_rows_fast<true, false>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
+      else consume_rows_fast<false, false>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
+    }
     return;
   }
   int slot = 0, round = 0;
@@ -523,7 +551,11 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   if (ncons > 8) ncons = 8;
   const int threads = (ncons + 1) * 32;            // + the TMA producer warp
   p.row_bytes = p.sw * 3;
-  p.seg_stride = p.row_bytes + 16;                 // tap reads may run a few bytes past the row end
+  p.fast_rows = (!p.has_overlay && (p.dw & 3) == 0 && groups <= ncons * 32 && !env_int("AIKO_B200_RESIZE_SLOW_ROWS", 0) &&
+                 ((reinterpret_cast<uintptr_t>(p.dst) | (uintptr_t)p.dst_row_stride | (uintptr_t)p.dst_frame_stride) & 3) == 0)
+                    ? 1 : 0;
+  if (p.unaligned && !p.fast_rows) return AIKO_B200_OK;   // not staged: the generic kernel takes it
+  p.seg_stride = ((p.row_bytes + 15) & ~15) + 32;  // room for the 16-byte rounding at both ends; tap reads may run a few bytes past the row end
   // the host-built index is usable when it was made for this output width
   const bool indexed = p.has_overlay && p.ov.index != nullptr && p.ov.index_width == p.dw &&
                        p.ov.index_segments == (groups + 31) / 32 && p.ov.index_words > 0 &&
@@ -568,9 +600,6 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   const long long chunks = ((long long)p.items + chunk - 1) / chunk;
   if (grid > chunks) grid = chunks;
   p.items_per_cta = chunk;
-  p.fast_rows = (!p.has_overlay && (p.dw & 3) == 0 && !env_int("AIKO_B200_RESIZE_SLOW_ROWS", 0) &&
-                 ((reinterpret_cast<uintptr_t>(p.dst) | (uintptr_t)p.dst_row_stride | (uintptr_t)p.dst_frame_stride) & 3) == 0)
-                    ? 1 : 0;
   p.evict_first = (p.sh >= 2 * p.dh && env_int("AIKO_B200_RESIZE_EVICT_FIRST", 1)) ? 1 : 0;
   p.keep_output = env_int("AIKO_B200_RESIZE_KEEP_OUTPUT", p.keep_output);
   p.wait_ns[0] = env_int("AIKO_B200_RESIZE_PW", 1000); p.wait_ns[1] = env_int("AIKO_B200_RESIZE_PB", 100);
@@ -643,13 +672,14 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)src_row_stride | (uintptr_t)src_frame_stride |
                          (uintptr_t)((int64_t)src_w * channels)) & 15) == 0;
-  if (channels == 3 && aligned && p.scale_x <= 4.0) {
+  if (channels == 3 && p.scale_x <= 4.0) {     // (rows off 16-byte boundaries: handled by the register-resident path)
     // Default: resize (+ swap) with the row pipeline, then the draw list in a second, tile-parallel
     // kernel while the output frames are still in L2 -- measured faster than replaying the list
     // inside the row loop (AIKO_B200_OVERLAY_FUSED=1 selects that single-kernel variant).
     const bool two_pass = p.has_overlay && !env_int("AIKO_B200_OVERLAY_FUSED", 0);
     ResizeParams q = p;
     if (two_pass) { q.has_overlay = 0; q.keep_output = 1; }   // the overlay pass re-reads the pixels it touches
+    q.unaligned = aligned ? 0 : 1;
     bool done = false;
     const int rc = launch_staged3(q, st, &done);
     if (rc != AIKO_B200_OK) return rc;

@@ -62,7 +62,7 @@ def main():
     ms = timed(lambda i: ops.resize_bicubic_aa(hd[i % rot], 640, 480, out=out), max(args.steps // 5, 5))
     report("resize_bicubic_aa 1080p->640x480 (config 1, codecs excluded)", 32, "frames", 7_142_400, ms)
 
-    # the generic row kernel: gray, RGBA and rows that are not 16-byte aligned
+    # the generic row kernel (gray, RGBA), and RGB rows that are not 16-byte aligned (row pipeline, per-row offsets)
     gray_in = [torch.randint(0, 256, (32, 1080, 1920), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
     gray_out = torch.empty((32, 480, 640), dtype=torch.uint8, device=dev)
     ms = timed(lambda i: ops.resize_linear(gray_in[i % rot], 640, 480, out=gray_out), args.steps)
@@ -70,7 +70,7 @@ def main():
     del gray_in, gray_out
     odd_in = [torch.randint(0, 256, (32, 1080, 1918, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
     ms = timed(lambda i: ops.resize_linear(odd_in[i % rot], 640, 480, out=out), args.steps)
-    report("resize_linear 1918x1080->640x480 (unaligned rows, generic kernel)", 32, "frames", 960 * 1918 * 3 + 921_600, ms)
+    report("resize_linear 1918x1080->640x480 (rows off 16-byte boundaries)", 32, "frames", 960 * 1918 * 3 + 921_600, ms)
     del odd_in
 
     sw = torch.empty_like(hd[0])

@@ -61,6 +61,21 @@ def test_resize_linear_unaligned_base_pointer(cuda):
     np.testing.assert_array_equal(out[0], O.resize_linear(frames[0], 20, 30))
 
 
+@pytest.mark.parametrize("shape", [(3, 270, 479, 160, 120), (2, 1080, 1918, 640, 480), (2, 97, 333, 84, 33),
+                                   (1, 64, 1366, 1024, 31), (2, 50, 131, 400, 20)])
+def test_resize_linear_rows_off_16_byte_boundaries_take_the_row_pipeline(cuda, shape):
+    """RGB rows that are not 16-byte aligned (odd widths, odd base pointers) are staged from the
+    boundary below each row; the result is the oracle's, with and without the channel swap."""
+    n, h, w, W, H = shape
+    frames = np.stack([cases.frame(8100 + k, h, w, 3) for k in range(n)])
+    want = np.stack([O.resize_linear(f, W, H) for f in frames])
+    np.testing.assert_array_equal(host(ops.resize_linear(dev(frames, cuda), W, H)), want)
+    buf = torch.empty(frames.size + 5, dtype=torch.uint8, device=cuda)
+    view = buf[5:].view(frames.shape)
+    view.copy_(dev(frames, cuda))
+    np.testing.assert_array_equal(host(ops.resize_linear(view, W, H, swap_rb=True)), want[..., ::-1])
+
+
 def test_resize_linear_edge_values(cuda):
     for v in (0, 255):
         img = np.full((2, 90, 160, 3), v, np.uint8)
