@@ -171,10 +171,16 @@ __device__ __forceinline__ uint32_t pack2_sat_u8(int lo, int hi) {
 
 // Horizontal pass of one warp: 8 staged rows x NT tiles -> 8 rows of the ring.  NT is a template
 // parameter so the tiles unroll without branches and their loads, MMAs and epilogues interleave.
-template <int KX, int T, int CAP, int NT, int FIRST = 0>
+// UA: the staged row starts `delta` (0..15) bytes into its buffer (rows that are not 16-byte
+// aligned in global memory are copied from the boundary below them): four aligned words and a
+// funnel shift replace the three aligned words of a gather.
+template <int KX, int T, int CAP, int NT, bool UA>
 __device__ __forceinline__ void horizontal_tiles(const uint4 (&A)[T][3][KX], const int (&xoff)[T],
                                                  const uint8_t* __restrict__ rrow, uint8_t* __restrict__ ring_out,
-                                                 int q) {
+                                                 int q, int delta) {
+  constexpr int FIRST = 0;
+  const uint8_t* rbase = rrow + (UA ? (delta & ~3) : 0);
+  const int shift = UA ? (delta & 3) * 8 : 0;
   constexpr int kRound = 1 << (kPrecisionBits - 1);
 #pragma unroll
   for (int t = FIRST; t < FIRST + NT; t++) {
@@ -185,8 +191,14 @@ __device__ __forceinline__ void horizontal_tiles(const uint4 (&A)[T][3][KX], con
       for (int h = 0; h < 2; h++) {
         // 4 pixels = 12 interleaved bytes = 3 words -> one register per channel.  Row pitch
         // 12 words mod 32 and 3 words per lane: the 32 lanes of each load hit 32 banks.
-        const uint32_t* wp = reinterpret_cast<const uint32_t*>(rrow + xoff[t] + (32 * ks + 16 * h + 4 * q) * 3);
-        const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(rbase + xoff[t] + (32 * ks + 16 * h + 4 * q) * 3);
+        uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+        if (UA) {
+          const uint32_t w3 = wp[3];
+          w0 = __funnelshift_r(w0, w1, shift);
+          w1 = __funnelshift_r(w1, w2, shift);
+          w2 = __funnelshift_r(w2, w3, shift);
+        }
         B[ks][h][0] = __byte_perm(__byte_perm(w0, w1, 0x0630), w2, 0x5210);
         B[ks][h][1] = __byte_perm(__byte_perm(w0, w1, 0x0741), w2, 0x6210);
         B[ks][h][2] = __byte_perm(__byte_perm(w0, w1, 0x0052), w2, 0x7410);
@@ -250,13 +262,14 @@ __device__ __forceinline__ MmaItem mma_item(const MmaParams& p, int item) {
 // the consumers across item boundaries, so only the very first batch of a CTA waits for HBM with
 // nothing else to do, and a warp loads its tile weights once (the chunk of a CTA never changes:
 // the grid is a multiple of the chunk count).
-template <int KX, int KY, int T>
+template <int KX, int KY, int T, bool UA>
 __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bicubic_mma_kernel(const MmaParams p) {
   constexpr int CAP = 32 * KY + 16;   // ring rows: one K window + the rows a batch runs ahead, rounded;
                                       // as a pitch (bytes) it is 16 mod 32, which keeps the loads below conflict-free
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);      // per staging buffer: its rows have landed
   uint64_t* empty = full + kMmaStages;                     // per staging buffer: every consumer is done with it
+  int* deltas = reinterpret_cast<int*>(smem + 64);         // per staging buffer and row: bytes before the row's first byte
   uint8_t* raw = smem + 128;
   uint8_t* ring = raw + (size_t)kMmaStages * kBatchRows * p.raw_pitch;   // [byte column][CAP rows]
 
@@ -281,18 +294,22 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
     const uint64_t policy = l2_policy_evict_first();   // source rows are read once (plus the band halo)
     for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
       const MmaItem it = mma_item<KX>(p, item);
-      if (it.copy_bytes > p.raw_pitch) __trap();
+      if (it.copy_bytes + (UA ? 32 : 0) > p.raw_pitch) __trap();
       const uint8_t* fsrc = p.src + (size_t)it.frame * p.sh * row_bytes + it.byte_lo;
       for (int b = 0; b < it.nbatches; b++, gb++) {
         const int s = gb % kMmaStages, round = gb / kMmaStages;
         if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1), 1000, 100);
-        if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)(kBatchRows * it.copy_bytes));
+        const int row = min(it.row_start + b * kBatchRows + (lane & 7), p.sh - 1);   // rows past the frame carry no weight
+        const uint8_t* a = fsrc + (size_t)row * row_bytes;
+        const uint32_t d = UA ? (uint32_t)(reinterpret_cast<uintptr_t>(a) & 15) : 0u;
+        const uint32_t nbytes = UA ? ((d + (uint32_t)it.copy_bytes + 15u) & ~15u) : (uint32_t)it.copy_bytes;
+        if (UA && lane < kBatchRows) deltas[s * kBatchRows + lane] = (int)d;
+        const uint32_t total = __reduce_add_sync(0xffffffffu, lane < kBatchRows ? nbytes : 0u);
         __syncwarp();
-        if (lane < kBatchRows) {
-          const int row = min(it.row_start + b * kBatchRows + lane, p.sh - 1);   // rows past the frame carry no weight
-          bulk_g2s_hint(raw + (size_t)(s * kBatchRows + lane) * p.raw_pitch, fsrc + (size_t)row * row_bytes,
-                        (uint32_t)it.copy_bytes, &full[s], policy);
-        }
+        if (lane == 0) mbar_expect_tx(&full[s], total);   // release: the row offsets above are visible with it
+        __syncwarp();
+        if (lane < kBatchRows)
+          bulk_g2s_hint(raw + (size_t)(s * kBatchRows + lane) * p.raw_pitch, a - d, nbytes, &full[s], policy);
       }
     }
     return;
@@ -348,7 +365,8 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
         // -- horizontal pass: 8 staged rows x this warp's tiles -> ring rows slot .. slot + 7
         const uint8_t* rrow = raw + (size_t)(s * kBatchRows + g) * p.raw_pitch;
         uint8_t* ring_out = ring + (size_t)(wcol0 + g * 3) * CAP + slot + 2 * q;
-        horizontal_tiles<KX, T, CAP, T>(A, xoff, rrow, ring_out, q);   // slots without a tile: zero weights, spare columns
+        // slots without a tile: zero weights, spare columns
+        horizontal_tiles<KX, T, CAP, T, UA>(A, xoff, rrow, ring_out, q, UA ? deltas[s * kBatchRows + g] : 0);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[s]);     // the staged rows are free again
@@ -426,7 +444,7 @@ static int env_int(const char* name, int fallback) {
   return v ? atoi(v) : fallback;
 }
 
-template <int KX, int KY, int T>
+template <int KX, int KY, int T, bool UA>
 static int launch_mma(MmaParams p, int n_frames, double scale_y, cudaStream_t stream, bool* done) {
   constexpr int kMmaMaxWarps = WarpBudget<KX, T>::max_warps;
   constexpr int CAP = 32 * KY + 16;
@@ -446,14 +464,15 @@ static int launch_mma(MmaParams p, int n_frames, double scale_y, cudaStream_t st
     // source bytes a chunk touches per row (window starts are rounded down to 4 pixels, the copy to 16 bytes)
     const long long bound_px = (long long)(p.tiles_per_chunk * 16 * scale_x) + 32 * KX + 8;
     long long bound_bytes = (bound_px * 3 + 32 + 15) & ~15LL;
-    if (bound_bytes > row_bytes) bound_bytes = row_bytes;
+    if (bound_bytes > row_bytes) bound_bytes = (row_bytes + 15) & ~15;
+    if (UA) bound_bytes += 32;                                // the 16-byte rounding at both ends of a row
     long long pitch = (bound_bytes + 127) / 128 * 128 + 48;   // 48 mod 128: see the gather in the kernel
     if (pitch - 128 >= bound_bytes) pitch -= 128;
     p.raw_pitch = (int)pitch;
     smem = 128 + (size_t)kMmaStages * kBatchRows * (size_t)pitch + (size_t)nwarps * T * 48 * CAP + 128;
     if (smem <= max_smem) break;
   }
-  auto kernel = bicubic_mma_kernel<KX, KY, T>;
+  auto kernel = bicubic_mma_kernel<KX, KY, T, UA>;
   AIKO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int threads = (nwarps + 1) * 32;
   int per_sm = 0;
@@ -488,17 +507,19 @@ int bicubic_mma_launch(const uint8_t* src, int n_frames, int sh, int sw, int cha
                        const int* ws, const BicubicLayout& l, cudaStream_t stream, bool* done) {
   *done = false;
   const MmaPlan& m = l.mma;
-  // RGB frames whose rows the TMA engine can copy (16-byte aligned); everything else: scalar kernel
+  // RGB frames (rows off 16-byte boundaries are copied from the boundary below them); everything else: scalar kernel
   if (!m.ok || channels != 3 || env_int("AIKO_B200_BICUBIC_SCALAR", 0)) return AIKO_B200_OK;
-  if (((reinterpret_cast<uintptr_t>(src) | (uintptr_t)((size_t)sw * 3)) & 15) != 0) return AIKO_B200_OK;
+  const bool unaligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)((size_t)sw * 3)) & 15) != 0;
   MmaParams p{};
   p.src = src; p.dst = dst; p.ws = ws;
   p.n = n_frames; p.sh = sh; p.sw = sw; p.dh = dh; p.dw = dw;
   p.ntx = m.ntx; p.ngy = m.ngy;
   p.off_xa = m.off_xa; p.off_ax = m.off_ax; p.off_ya = m.off_ya; p.off_yend = m.off_yend; p.off_by = m.off_by;
   const double scale_y = (double)sh / dh;
-#define AIKO_MMA_CASE(KX, KY, T) \
-  if (m.kx == KX && m.ky == KY) return launch_mma<KX, KY, T>(p, n_frames, scale_y, stream, done);
+#define AIKO_MMA_CASE(KX, KY, T)                                                                   \
+  if (m.kx == KX && m.ky == KY)                                                                    \
+    return unaligned ? launch_mma<KX, KY, T, true>(p, n_frames, scale_y, stream, done)              \
+                     : launch_mma<KX, KY, T, false>(p, n_frames, scale_y, stream, done);
   AIKO_MMA_CASE(1, 1, 8) AIKO_MMA_CASE(2, 1, 4) AIKO_MMA_CASE(3, 1, 2) AIKO_MMA_CASE(4, 1, 2)
   AIKO_MMA_CASE(1, 2, 8) AIKO_MMA_CASE(2, 2, 4) AIKO_MMA_CASE(3, 2, 2) AIKO_MMA_CASE(4, 2, 2)
 #undef AIKO_MMA_CASE

@@ -139,7 +139,7 @@ def test_resize_bicubic_cfg1_batch(cuda):
         assert (host(ops.resize_bicubic_aa(dev(img, cuda), 77, 51)) == v).all()
 
 
-TENSOR_CORE_SHAPES = [   # (h, w, H, W): RGB rows that are 16-byte aligned take the tensor-core kernel
+TENSOR_CORE_SHAPES = [   # (h, w, H, W): RGB frames take the tensor-core kernel (scale up to ~5)
     (270, 480, 120, 160),    # the config-1 ratio (3 x 2.25): two K steps along x, one along y
     (120, 160, 270, 480),    # upscale
     (200, 320, 200, 100),    # height unchanged (identity vertical table)
@@ -147,7 +147,8 @@ TENSOR_CORE_SHAPES = [   # (h, w, H, W): RGB rows that are 16-byte aligned take 
     (301, 208, 77, 51),      # odd targets: partial last tile and last row group
     (480, 640, 100, 131),    # scale ~4.9 x 4.8: four K steps along x, two along y
     (90, 1600, 45, 1000),    # wide: more tiles than one CTA owns -> several column chunks
-    (33, 48, 5, 7), (16, 16, 1, 1), (8, 16, 40, 300)]
+    (33, 48, 5, 7), (16, 16, 1, 1), (8, 16, 40, 300),
+    (270, 479, 120, 160), (97, 333, 41, 50), (60, 1366, 45, 700)]   # rows off 16-byte boundaries
 
 
 @pytest.mark.parametrize("shape", TENSOR_CORE_SHAPES, ids=lambda s: "%dx%d_to_%dx%d" % (s[1], s[0], s[3], s[2]))
@@ -164,6 +165,10 @@ def test_resize_bicubic_tensor_core_path_vs_oracle(cuda, shape, monkeypatch):
     monkeypatch.setenv("AIKO_B200_BICUBIC_BAND_GROUPS", "3")
     monkeypatch.setenv("AIKO_B200_BICUBIC_CHUNKS", "2")
     np.testing.assert_array_equal(host(ops.resize_bicubic_aa(d, W, H)), want)
+    buf = torch.empty(frames.size + 3, dtype=torch.uint8, device=cuda)     # odd base pointer
+    view = buf[3:].view(frames.shape)
+    view.copy_(d)
+    np.testing.assert_array_equal(host(ops.resize_bicubic_aa(view, W, H)), want)
 
 
 def test_resize_bicubic_tensor_core_equals_scalar_kernel(cuda, monkeypatch):
