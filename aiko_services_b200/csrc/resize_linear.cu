@@ -36,6 +36,7 @@ struct ResizeParams {
   int evict_first;             // source rows are read once: keep them from displacing other data in L2
   int keep_output;             // a second pass over the output follows: store it with an L2 evict-last hint
   int unaligned;               // source rows do not start on 16-byte boundaries (register-resident row path only)
+  int ch;                      // channels of the staged kernel: 3, or 1 (gray: register-resident row path only)
 };
 
 // cv2's coefficient derivation (float32 phase from a double position, 11-bit weights).
@@ -247,6 +248,48 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
   }
 }
 
+// Gray frames on the same ring: a thread owns 4 consecutive output pixels = one output word; a tap
+// pair is two adjacent bytes (one dp2a), taken from two aligned words with a funnel shift.
+__device__ __forceinline__ void consume_rows_gray(const ResizeParams& p, uint64_t* full, uint64_t* empty, const int* recs,
+                                                  const uint8_t* stage, int my_items, const int* xw, const int* xs,
+                                                  const uint32_t* xcoef, int g, bool on, int lane) {
+  int exact[4] = {0, 0, 0, 0};
+  uint32_t cs[4] = {0, 0, 0, 0};
+  if (on) {
+    const int4 w4 = reinterpret_cast<const int4*>(xw)[g];
+    const int4 s4 = reinterpret_cast<const int4*>(xs)[g];
+    const uint4 c4 = reinterpret_cast<const uint4*>(xcoef)[g];
+    exact[0] = w4.x + (s4.x >> 3); exact[1] = w4.y + (s4.y >> 3); exact[2] = w4.z + (s4.z >> 3); exact[3] = w4.w + (s4.w >> 3);
+    cs[0] = c4.x; cs[1] = c4.y; cs[2] = c4.z; cs[3] = c4.w;
+  }
+  int slot = 0, round = 0;
+  for (int it = 0; it < my_items; ++it) {
+    mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
+    const int* rec = recs + slot * kRecHeader;
+    const int2 bb = *reinterpret_cast<const int2*>(rec + 2);                       // b0, b1
+    const int2 delta = p.unaligned ? *reinterpret_cast<const int2*>(rec + 4) : make_int2(0, 0);
+    uint32_t* drow = *reinterpret_cast<uint32_t* const*>(rec + 6);                 // first byte of the output row
+    const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
+    const uint8_t* r1 = r0 + p.seg_stride;
+    if (on) {
+      const uint32_t b0s = (uint32_t)bb.x << 16, b1s = (uint32_t)bb.y << 16;
+      uint32_t out = 0;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int e0 = exact[k] + delta.x, e1 = exact[k] + delta.y;
+        const uint32_t* w0 = reinterpret_cast<const uint32_t*>(r0 + (e0 & ~3));
+        const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1 + (e1 & ~3));
+        const uint32_t u = __funnelshift_r(w0[0], w0[1], (e0 & 3) * 8), v = __funnelshift_r(w1[0], w1[1], (e1 & 3) * 8);
+        out |= vblend_hi(__dp2a_lo(cs[k], u, 0u), __dp2a_lo(cs[k], v, 0u), b0s, b1s) << (8 * k);
+      }
+      asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(drow + g), "r"(out) : "memory");
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[slot]);
+    if (++slot == p.stages) { slot = 0; ++round; }
+  }
+}
+
 // Warp roles: warps [0, ncons) consume rows; warp ncons is the TMA producer.  Per ring slot the
 // producer brings in the two source rows and, with an overlay, the frame's spatial index of its
 // draw list; `full` completes when the bytes have landed, `empty` when every consumer warp is
@@ -279,8 +322,8 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
     int s;
     uint32_t c;
     horizontal_coef(min(dx, p.dw - 1), p.scale_x, p.sw, &s, &c);
-    xw[dx] = (s * 3) & ~3;
-    xs[dx] = ((s * 3) & 3) * 8;
+    xw[dx] = (s * p.ch) & ~3;
+    xs[dx] = ((s * p.ch) & 3) * 8;
     xcoef[dx] = c;
     not_decim |= (c != 2048u);
   }
@@ -366,7 +409,9 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
   if (p.fast_rows) {
     const int g = warp * 32 + lane;
     const bool on = g < groups;
-    if (p.unaligned) {
+    if (p.ch == 1) {
+      consume_rows_gray(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, lane);
+    } else if (p.unaligned) {
       if (decim) consume_rows_fast<true, true>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
       else consume_rows_fast<false, true>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
     } else {
@@ -550,11 +595,11 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   if (ncons < 1) ncons = 1;
   if (ncons > 8) ncons = 8;
   const int threads = (ncons + 1) * 32;            // + the TMA producer warp
-  p.row_bytes = p.sw * 3;
+  p.row_bytes = p.sw * p.ch;
   p.fast_rows = (!p.has_overlay && (p.dw & 3) == 0 && groups <= ncons * 32 && !env_int("AIKO_B200_RESIZE_SLOW_ROWS", 0) &&
                  ((reinterpret_cast<uintptr_t>(p.dst) | (uintptr_t)p.dst_row_stride | (uintptr_t)p.dst_frame_stride) & 3) == 0)
                     ? 1 : 0;
-  if (p.unaligned && !p.fast_rows) return AIKO_B200_OK;   // not staged: the generic kernel takes it
+  if ((p.unaligned || p.ch == 1) && !p.fast_rows) return AIKO_B200_OK;   // not staged: the generic kernel takes it
   p.seg_stride = ((p.row_bytes + 15) & ~15) + 32;  // room for the 16-byte rounding at both ends; tap reads may run a few bytes past the row end
   // the host-built index is usable when it was made for this output width
   const bool indexed = p.has_overlay && p.ov.index != nullptr && p.ov.index_width == p.dw &&
@@ -672,7 +717,7 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)src_row_stride | (uintptr_t)src_frame_stride |
                          (uintptr_t)((int64_t)src_w * channels)) & 15) == 0;
-  if (channels == 3 && p.scale_x <= 4.0) {     // (rows off 16-byte boundaries: handled by the register-resident path)
+  if ((channels == 3 || channels == 1) && p.scale_x <= 4.0) {   // (gray, and rows off 16-byte boundaries: register-resident path only)
     // Default: resize (+ swap) with the row pipeline, then the draw list in a second, tile-parallel
     // kernel while the output frames are still in L2 -- measured faster than replaying the list
     // inside the row loop (AIKO_B200_OVERLAY_FUSED=1 selects that single-kernel variant).
@@ -680,6 +725,7 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
     ResizeParams q = p;
     if (two_pass) { q.has_overlay = 0; q.keep_output = 1; }   // the overlay pass re-reads the pixels it touches
     q.unaligned = aligned ? 0 : 1;
+    q.ch = channels;
     bool done = false;
     const int rc = launch_staged3(q, st, &done);
     if (rc != AIKO_B200_OK) return rc;

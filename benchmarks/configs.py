@@ -66,7 +66,7 @@ def main():
     gray_in = [torch.randint(0, 256, (32, 1080, 1920), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
     gray_out = torch.empty((32, 480, 640), dtype=torch.uint8, device=dev)
     ms = timed(lambda i: ops.resize_linear(gray_in[i % rot], 640, 480, out=gray_out), args.steps)
-    report("resize_linear gray 1080p->640x480 (generic kernel)", 32, "frames", 960 * 1920 + 640 * 480, ms)
+    report("resize_linear gray 1080p->640x480", 32, "frames", 960 * 1920 + 640 * 480, ms)
     del gray_in, gray_out
     odd_in = [torch.randint(0, 256, (32, 1080, 1918, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
     ms = timed(lambda i: ops.resize_linear(odd_in[i % rot], 640, 480, out=out), args.steps)

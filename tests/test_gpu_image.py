@@ -76,6 +76,21 @@ def test_resize_linear_rows_off_16_byte_boundaries_take_the_row_pipeline(cuda, s
     np.testing.assert_array_equal(host(ops.resize_linear(view, W, H, swap_rb=True)), want[..., ::-1])
 
 
+@pytest.mark.parametrize("shape", [(3, 270, 480, 160, 120), (2, 1080, 1920, 640, 480), (2, 97, 333, 84, 33),
+                                   (1, 40, 50, 200, 90), (2, 64, 1366, 1024, 31)])
+def test_resize_linear_gray_frames_take_the_row_pipeline(cuda, shape):
+    """Gray frames (aligned or not) whose output width is a multiple of 4 run on the TMA ring."""
+    n, h, w, W, H = shape
+    frames = np.stack([cases.frame(8300 + k, h, w, 1).reshape(h, w) for k in range(n)])
+    want = np.stack([O.resize_linear(f, W, H) for f in frames])
+    np.testing.assert_array_equal(host(ops.resize_linear(dev(frames, cuda), W, H)), want)
+    buf = torch.empty(frames.size + 7, dtype=torch.uint8, device=cuda)
+    view = buf[7:].view(frames.shape)
+    view.copy_(dev(frames, cuda))
+    out = torch.empty((n, H, W), dtype=torch.uint8, device=cuda)
+    np.testing.assert_array_equal(host(ops.resize_linear(view, W, H, out=out)), want)
+
+
 def test_resize_linear_edge_values(cuda):
     for v in (0, 255):
         img = np.full((2, 90, 160, 3), v, np.uint8)
@@ -378,8 +393,11 @@ def test_sizes_beyond_on_chip_limits_are_refused_not_mangled(cuda):
         ops.resize_linear(tiny, 40000, 2)                 # 40000-pixel output rows: tables exceed shared memory
     assert e.value.code == _native.ERR_UNSUPPORTED and "shared memory" in str(e.value)
     with pytest.raises(_native.NativeError) as e:
-        ops.resize_bicubic_aa(tiny, 60000, 2)
+        ops.resize_bicubic_aa(tiny[..., 0].contiguous(), 60000, 2)       # gray: the scalar kernel, one row per CTA
     assert e.value.code == _native.ERR_UNSUPPORTED
+    wide = np.stack([cases.frame(82, 2, 4, 3)])                        # RGB: column chunks of the tensor-core kernel
+    np.testing.assert_array_equal(host(ops.resize_bicubic_aa(dev(wide, cuda), 60000, 2))[0],
+                                  O.resize_bicubic_aa(wide[0], 60000, 2))
     with pytest.raises(_native.NativeError) as e:
         ops.flip(torch.zeros((1, 1, 100001, 3), dtype=torch.uint8, device=cuda), 1)
     assert e.value.code == _native.ERR_INVALID_ARGUMENT
