@@ -5,16 +5,18 @@
 //
 // Work item = one output row of one frame; each CTA owns a contiguous run of items.
 //
-// resize3_staged (RGB frames with 16-byte aligned rows, horizontal scale <= 4): the two
-// source rows an output row needs are pulled into shared memory by the TMA engine (1-D
-// cp.async.bulk, mbarrier completion) through a ring of stages, so every 32-byte sector of
-// a needed source row crosses HBM exactly once and the SM's load/store units only see shared
-// memory.  A thread produces 4 consecutive output pixels: taps are fetched as aligned words,
-// the horizontal pass is one dp2a per channel (two 11-bit weights x two 8-bit taps), the
-// vertical pass one mad.hi per source row.
+// resize3_staged (RGB and gray frames, horizontal scale <= 4): the two source rows an output
+// row needs are pulled into shared memory by the TMA engine (1-D cp.async.bulk, mbarrier
+// completion) through a ring of stages, so every 32-byte sector of a needed source row crosses
+// HBM exactly once and the SM's load/store units only see shared memory.  A thread produces 4
+// consecutive output pixels: taps are fetched as aligned words, the horizontal pass is one dp2a
+// per channel (two 11-bit weights x two 8-bit taps), the vertical pass one mad.hi per source row.
+// Rows that do not start on 16-byte boundaries are copied from the boundary below them and the
+// tap offsets are shifted per row (register-resident row path only, as is gray).
 //
-// resize_rows_generic (1/4 channels, unaligned rows, or scale > 4 where most sectors of a
-// source row carry no weight): same row structure, taps read straight from global memory.
+// resize_rows_generic (RGBA, scale > 4 where most sectors of a source row carry no weight, and
+// the shapes the register-resident path does not take): same row structure, taps read straight
+// from global memory.
 #include "overlay.cuh"
 
 namespace aiko {
