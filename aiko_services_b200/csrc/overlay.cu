@@ -122,19 +122,21 @@ __device__ __forceinline__ bool apply_op_regs(const int4 lo4, const int4 hi4, co
       any |= id[k][c] != 0;
     }
   if (!any) return false;
-  uint32_t v[3] = {px.w0, px.w1, px.w2};
+  // All twelve transfer-table look-ups read the ORIGINAL bytes, so they are issued together and only
+  // then merged: one L2 round trip for the glyph instead of a chain of up to twelve.
+  const uint32_t v[3] = {px.w0, px.w1, px.w2};
+  uint32_t nv[12];
 #pragma unroll
   for (int k = 0; k < 4; k++)
 #pragma unroll
     for (int c = 0; c < 3; c++) {
       const int byte = 3 * k + c;                       // compile-time after unrolling
-      if (id[k][c]) {
-        const uint32_t old = (v[byte >> 2] >> (8 * (byte & 3))) & 0xffu;
-        const uint32_t nv = __ldg(ov.luts + (size_t)id[k][c] * 256 + old);
-        v[byte >> 2] = (v[byte >> 2] & ~(0xffu << (8 * (byte & 3)))) | (nv << (8 * (byte & 3)));
-      }
+      const uint32_t old = (v[byte >> 2] >> (8 * (byte & 3))) & 0xffu;
+      nv[byte] = id[k][c] ? (uint32_t)__ldg(ov.luts + (size_t)id[k][c] * 256 + old) : old;
     }
-  px.w0 = v[0]; px.w1 = v[1]; px.w2 = v[2];
+  px.w0 = nv[0] | (nv[1] << 8) | (nv[2] << 16) | (nv[3] << 24);
+  px.w1 = nv[4] | (nv[5] << 8) | (nv[6] << 16) | (nv[7] << 24);
+  px.w2 = nv[8] | (nv[9] << 8) | (nv[10] << 16) | (nv[11] << 24);
   return true;
 }
 
