@@ -6,7 +6,7 @@
 //
 // Large downscales (4K -> 224x224) touch 2x2 taps out of every ~17x10 source pixels, so taps
 // are gathered straight from global memory (only the sectors that carry weight are read); one
-// thread per output pixel, the three planes written with fully coalesced 4-byte stores.
+// CTA per output row at a time, the three planes written with fully coalesced 4-byte stores.
 #include "common.cuh"
 
 namespace aiko {
@@ -35,26 +35,44 @@ struct NormParams {
   float mean[3], stdv[3];
 };
 
+// A CTA strides over output rows (frame, dy).  The horizontal taps of every output column are
+// worked out once per CTA into shared memory (they are the same for every row), the vertical tap
+// once per row; per pixel what is left is 12 byte loads, the fixed-point blend and the three
+// IEEE divisions of the transform.
 __global__ void __launch_bounds__(kThreads) resize_norm_kernel(const NormParams p) {
-  const long long total = (long long)p.n * p.dh * p.dw;
-  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < total; i += (long long)gridDim.x * kThreads) {
-    const int dx = (int)(i % p.dw);
-    const long long r = i / p.dw;
-    const int dy = (int)(r % p.dh), n = (int)(r / p.dh);
-    int x0, x1, a0, a1, y0, y1, b0, b1;
+  extern __shared__ int4 xtap[];             // x0 * 3, x1 * 3, a0, a1 per output column
+  for (int dx = threadIdx.x; dx < p.dw; dx += kThreads) {
+    int x0, x1, a0, a1;
     linear_tap(dx, p.scale_x, p.sw, true, &x0, &x1, &a0, &a1);
+    xtap[dx] = make_int4(x0 * 3, x1 * 3, a0, a1);
+  }
+  __syncthreads();
+  const size_t plane = (size_t)p.dh * p.dw;
+  const int rows = p.n * p.dh;
+  for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+    const int n = r / p.dh, dy = r - n * p.dh;
+    int y0, y1, b0, b1;
     linear_tap(dy, p.scale_y, p.sh, false, &y0, &y1, &b0, &b1);
     const uint8_t* f = p.src + (size_t)n * p.sh * p.sw * 3;
     const uint8_t* r0 = f + (size_t)y0 * p.sw * 3;
     const uint8_t* r1 = f + (size_t)y1 * p.sw * 3;
-    const size_t plane = (size_t)p.dh * p.dw;
-    float* o = p.dst + (size_t)n * 3 * plane + (size_t)dy * p.dw + dx;
+    const uint32_t b0s = (uint32_t)b0 << 16, b1s = (uint32_t)b1 << 16;
+    float* orow = p.dst + (size_t)n * 3 * plane + (size_t)dy * p.dw;
+    for (int dx = threadIdx.x; dx < p.dw; dx += kThreads) {
+      const int4 t = xtap[dx];
+      uint32_t u[3][4];
 #pragma unroll
-    for (int c = 0; c < 3; c++) {
-      const uint32_t h0 = __ldg(r0 + x0 * 3 + c) * a0 + __ldg(r0 + x1 * 3 + c) * a1;
-      const uint32_t h1 = __ldg(r1 + x0 * 3 + c) * a0 + __ldg(r1 + x1 * 3 + c) * a1;
-      const uint32_t v = (__umulhi((uint32_t)b0 << 16, h0 >> 4) + __umulhi((uint32_t)b1 << 16, h1 >> 4) + 2u) >> 2;
-      o[c * plane] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.f), p.mean[c]), p.stdv[c]);
+      for (int c = 0; c < 3; c++) {          // all twelve gathers first
+        u[c][0] = __ldg(r0 + t.x + c); u[c][1] = __ldg(r0 + t.y + c);
+        u[c][2] = __ldg(r1 + t.x + c); u[c][3] = __ldg(r1 + t.y + c);
+      }
+#pragma unroll
+      for (int c = 0; c < 3; c++) {
+        const uint32_t h0 = u[c][0] * t.z + u[c][1] * t.w;
+        const uint32_t h1 = u[c][2] * t.z + u[c][3] * t.w;
+        const uint32_t v = (__umulhi(b0s, h0 >> 4) + __umulhi(b1s, h1 >> 4) + 2u) >> 2;
+        orow[c * plane + dx] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.f), p.mean[c]), p.stdv[c]);
+      }
     }
   }
 }
@@ -79,10 +97,16 @@ extern "C" int aiko_b200_resize_norm_f32_nchw(const uint8_t* src, int n_frames, 
     p.mean[c] = mean_host[c];
     p.stdv[c] = std_host[c];
   }
-  const long long total = (long long)n_frames * dst_h * dst_w;
-  long long blocks = (total + kThreads - 1) / kThreads;
-  const long long cap = (long long)sm_count() * 64;
+  AIKO_CHECK_ARG((long long)n_frames * dst_h < ((long long)1 << 31), "resize_norm: more than 2^31 output rows");
+  const size_t smem = (size_t)dst_w * sizeof(int4);
+  if (smem > (size_t)device_max_smem_optin()) {
+    set_last_error("resize_norm: destination width %d needs %zu bytes of shared memory", dst_w, smem);
+    return AIKO_B200_ERR_UNSUPPORTED;
+  }
+  AIKO_CUDA(cudaFuncSetAttribute(resize_norm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  long long blocks = (long long)n_frames * dst_h;
+  const long long cap = (long long)sm_count() * 16;
   if (blocks > cap) blocks = cap;
-  resize_norm_kernel<<<(unsigned)blocks, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  resize_norm_kernel<<<(unsigned)blocks, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
   return cuda_status(cudaGetLastError(), "resize_norm launch");
 }
