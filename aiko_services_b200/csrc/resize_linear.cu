@@ -39,6 +39,7 @@ struct ResizeParams {
   int keep_output;             // a second pass over the output follows: store it with an L2 evict-last hint
   int unaligned;               // source rows do not start on 16-byte boundaries (register-resident row path only)
   int ch;                      // channels of the staged kernel: 3, or 1 (gray: register-resident row path only)
+  int rows_per_slot;           // output rows (pairs of source rows) per ring slot: > 1 for short rows, register-resident path only
 };
 
 // cv2's coefficient derivation (float32 phase from a double position, 11-bit weights).
@@ -210,12 +211,14 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
   int slot = 0, round = 0;
   uint64_t keep;
   asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
+  const int R = p.rows_per_slot;
   for (int it = 0; it < my_items; ++it) {
-    mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
-    const int* rec = recs + slot * kRecHeader;
+    const int sub = it % R;
+    if (sub == 0) mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
+    const int* rec = recs + (slot * R + sub) * kRecHeader;
     const int2 bb = *reinterpret_cast<const int2*>(rec + 2);                       // b0, b1
     uint32_t* drow = *reinterpret_cast<uint32_t* const*>(rec + 6);                 // first byte of the output row
-    const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
+    const uint8_t* r0 = stage + (size_t)(slot * R + sub) * 2 * p.seg_stride;
     if (on) {
       uint32_t o[3];
       const uint32_t b0s = DECIM ? ((uint32_t)bb.x << 15) : ((uint32_t)bb.x << 16);
@@ -244,9 +247,11 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
         asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d + 2), "r"(o[2]) : "memory");
       }
     }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[slot]);      // the staged rows of this slot are free again
-    if (++slot == p.stages) { slot = 0; ++round; }
+    if (sub + 1 == R || it + 1 == my_items) {
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);    // the staged rows of this slot are free again
+      if (++slot == p.stages) { slot = 0; ++round; }
+    }
   }
 }
 
@@ -265,13 +270,15 @@ __device__ __forceinline__ void consume_rows_gray(const ResizeParams& p, uint64_
     cs[0] = c4.x; cs[1] = c4.y; cs[2] = c4.z; cs[3] = c4.w;
   }
   int slot = 0, round = 0;
+  const int R = p.rows_per_slot;
   for (int it = 0; it < my_items; ++it) {
-    mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
-    const int* rec = recs + slot * kRecHeader;
+    const int sub = it % R;
+    if (sub == 0) mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
+    const int* rec = recs + (slot * R + sub) * kRecHeader;
     const int2 bb = *reinterpret_cast<const int2*>(rec + 2);                       // b0, b1
     const int2 delta = p.unaligned ? *reinterpret_cast<const int2*>(rec + 4) : make_int2(0, 0);
     uint32_t* drow = *reinterpret_cast<uint32_t* const*>(rec + 6);                 // first byte of the output row
-    const uint8_t* r0 = stage + (size_t)slot * 2 * p.seg_stride;
+    const uint8_t* r0 = stage + (size_t)(slot * R + sub) * 2 * p.seg_stride;
     const uint8_t* r1 = r0 + p.seg_stride;
     if (on) {
       const uint32_t b0s = (uint32_t)bb.x << 16, b1s = (uint32_t)bb.y << 16;
@@ -286,9 +293,11 @@ __device__ __forceinline__ void consume_rows_gray(const ResizeParams& p, uint64_
       }
       asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(drow + g), "r"(out) : "memory");
     }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[slot]);
-    if (++slot == p.stages) { slot = 0; ++round; }
+    if (sub + 1 == R || it + 1 == my_items) {
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+      if (++slot == p.stages) { slot = 0; ++round; }
+    }
   }
 }
 
@@ -310,7 +319,7 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
   uint64_t* empty = full + 8;
   off += 128;
   int* recs = reinterpret_cast<int*>(smem + off);  // per slot: n, dy, b0, b1, first op, op count, -, -
-  off += (size_t)p.stages * kRecHeader * 4;
+  off += (size_t)p.stages * p.rows_per_slot * kRecHeader * 4;
   uint32_t* idxring = reinterpret_cast<uint32_t*>(smem + off);          // per slot: the frame's index block
   off += (size_t)p.stages * p.index_words_per_frame * 4;
   aiko_b200_overlay_op* opsring = reinterpret_cast<aiko_b200_overlay_op*>(smem + off);   // ... and its draw list
@@ -355,12 +364,15 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
     rn = ri;
     int ob = 0, oe = 0, ob_next = 0, oe_next = 0;
     if (p.has_overlay) { ob = __ldg(p.ov.op_offsets + ri.n); oe = __ldg(p.ov.op_offsets + ri.n + 1); }
-    int slot = 0, round = 0;
+    int slot = 0, round = 0, sub = 0;               // a slot takes rows_per_slot consecutive rows (1 unless rows are short)
+    uint32_t slot_bytes = 0;
+    const int R = p.rows_per_slot;
     const uint64_t policy = l2_policy_evict_first();
     for (int it = 0; it < my_items; ++it) {
-      if (round > 0) mbar_wait(&empty[slot], (uint32_t)((round - 1) & 1), (uint32_t)p.wait_ns[0], (uint32_t)p.wait_ns[1]);
+      if (sub == 0 && round > 0)
+        mbar_wait(&empty[slot], (uint32_t)((round - 1) & 1), (uint32_t)p.wait_ns[0], (uint32_t)p.wait_ns[1]);
       const RowCoef rc = vertical_coef(ri.dy, p.scale_y, p.sh);
-      uint8_t* s0 = stage + (size_t)slot * 2 * p.seg_stride;
+      uint8_t* s0 = stage + (size_t)(slot * R + sub) * 2 * p.seg_stride;
       const uint8_t* f = p.src + (long long)ri.n * p.src_frame_stride;
       // a row is copied from the 16-byte boundary below its first byte to the one above its last
       const uint8_t* a0 = f + (long long)rc.y0 * p.src_row_stride;
@@ -391,15 +403,20 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
         ob_next = __ldg(p.ov.op_offsets + rn.n);
         oe_next = __ldg(p.ov.op_offsets + rn.n + 1);
       }
-      int* rec = recs + slot * kRecHeader;
+      int* rec = recs + (slot * R + sub) * kRecHeader;
       *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
       rec[4] = p.unaligned ? (int)d0 : ob;          // (unaligned rows never carry a draw list in the row loop)
       rec[5] = p.unaligned ? (int)d1 : nops;
       *reinterpret_cast<uint8_t**>(rec + 6) = p.dst + (long long)ri.n * p.dst_frame_stride + (long long)ri.dy * p.dst_row_stride;
-      mbar_expect_tx(&full[slot], n0 + n1 + idx_bytes);   // release: record visible
+      slot_bytes += n0 + n1 + idx_bytes;
       ri.next(p.items, chunk, stride_items, p.dh);
       ob = ob_next; oe = oe_next;
-      if (++slot == p.stages) { slot = 0; ++round; }
+      if (++sub == R || it + 1 == my_items) {       // the slot is complete: one arrival for all its bytes
+        mbar_expect_tx(&full[slot], slot_bytes);    // release: records visible
+        slot_bytes = 0;
+        sub = 0;
+        if (++slot == p.stages) { slot = 0; ++round; }
+      }
     }
     return;
   }
@@ -613,9 +630,18 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   p.ops_cap = (env_int("AIKO_B200_RESIZE_STAGE_OPS", 0) && indexed && p.ov.max_ops > 0 &&
                p.ov.max_ops <= 32 * p.ov.index_words) ? p.ov.max_ops : 0;
   const size_t fixed = (size_t)groups * 48 + (((size_t)groups * 12 + 15) & ~(size_t)15) + 128;
+  // Short rows (gray, small frames): several output rows share a ring slot, so the hand-off between
+  // producer and consumers (one barrier round trip, ~1 us) is paid once per ~12 KB and not per row.
+  p.rows_per_slot = 1;
+  if (p.fast_rows) {
+    int r = 12288 / (2 * p.seg_stride);
+    r = env_int("AIKO_B200_RESIZE_ROWS_PER_SLOT", r);
+    p.rows_per_slot = r < 1 ? 1 : (r > 8 ? 8 : r);
+  }
   auto need = [&](int st) {
-    return fixed + (size_t)st * (kRecHeader * 4 + (size_t)p.index_words_per_frame * 4 +
-                                 (size_t)p.ops_cap * sizeof(aiko_b200_overlay_op) + 2 * (size_t)p.seg_stride);
+    return fixed + (size_t)st * ((size_t)p.rows_per_slot * kRecHeader * 4 + (size_t)p.index_words_per_frame * 4 +
+                                 (size_t)p.ops_cap * sizeof(aiko_b200_overlay_op) +
+                                 (size_t)p.rows_per_slot * 2 * (size_t)p.seg_stride);
   };
   // Measured on 32 x 1080p (us per launch; CTAs per SM x ring stages): 6x2 37.8, 5x2 35.5, 4x3 37.5, 5x3 39.5,
   // 4x4 39.3, 3x2 38.6, 3x3 35.1, 2x4 35.1, 2x6 35.1, 2x8 35.9, 1x8 55.4.  The consumers wait for the ring
@@ -640,9 +666,12 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   cudaPointerAttributes attr{};
   if (cudaPointerGetAttributes(&attr, p.src) == cudaSuccess && attr.type == cudaMemoryTypeHost) per_sm = 1;
   else (void)cudaGetLastError();
-  { const int cap = env_int("AIKO_B200_RESIZE_CTAS_PER_SM", p.has_overlay ? 0 : 3); if (cap > 0 && cap < per_sm) per_sm = cap; }
+  // (short rows, < 4 KB: measured better with up to 6 CTAs -- 640x480 RGB 92 -> 82 us, gray 1080p 28.9 -> 26.9 us)
+  { const int cap = env_int("AIKO_B200_RESIZE_CTAS_PER_SM", p.has_overlay ? 0 : (p.row_bytes < 4096 ? 6 : 3));
+    if (cap > 0 && cap < per_sm) per_sm = cap; }
   int chunk = env_int("AIKO_B200_RESIZE_CHUNK", 1);
   if (chunk < 1) chunk = 1;
+  if (p.rows_per_slot > 1) chunk = p.rows_per_slot;   // a slot is one chunk of consecutive rows
   long long grid = (long long)sm_count() * per_sm;
   const long long chunks = ((long long)p.items + chunk - 1) / chunk;
   if (grid > chunks) grid = chunks;

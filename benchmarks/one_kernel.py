@@ -34,6 +34,12 @@ def make(name, dev):
         if name == "flip":
             return lambda i: ops.flip(hd[i % rot], 1, out=out), 32
         return lambda i: ops.swap_rb(hd[i % rot], out=out), 32
+    if name in ("vga", "gray"):
+        shape = (256, 480, 640, 3) if name == "vga" else (32, 1080, 1920)
+        size = (320, 240) if name == "vga" else (640, 480)
+        src = [torch.randint(0, 256, shape, dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+        out = torch.empty((shape[0], size[1], size[0]) + shape[3:], dtype=torch.uint8, device=dev)
+        return lambda i: ops.resize_linear(src[i % rot], size[0], size[1], out=out), shape[0]
     if name in ("audio", "fft"):
         t = np.arange(16000) / 16000.0
         freqs = np.geomspace(50, 7000, 1024)
