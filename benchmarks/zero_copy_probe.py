@@ -2,7 +2,7 @@
 cudaMemcpyAsync H2D followed by the kernel on the device copy."""
 import ctypes, sys, os, time
 import torch
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # repo root
 from aiko_services_b200 import _native, ops
 
 lib = _native.lib()
