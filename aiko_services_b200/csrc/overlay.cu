@@ -236,7 +236,9 @@ __global__ void __launch_bounds__(kThreads) overlay_groups_kernel(const TilePara
   if ((int)threadIdx.x < count) {
     const uint32_t* rec = p.ov.group_records + (size_t)(first + threadIdx.x) * rec_words;
     yx = __ldg(rec);
-    for (int w = 0; w < p.ov.group_words && w < 4; w++) m[w] = __ldg(rec + 1 + w);
+#pragma unroll
+    for (int w = 0; w < 4; w++)            // (unrolled: the masks stay in registers)
+      if (w < p.ov.group_words) m[w] = __ldg(rec + 1 + w);
   }
   const int4* src = reinterpret_cast<const int4*>(p.ov.ops + ob);
   for (int i = threadIdx.x; i < nops * 2; i += kThreads) sops[i] = __ldg(src + i);
@@ -250,9 +252,9 @@ __global__ void __launch_bounds__(kThreads) overlay_groups_kernel(const TilePara
   if (!active) return;
   const int psize = p.ov.patch_w * p.ov.patch_h;
   bool dirty = false;
-#pragma unroll 1
-  for (int w = 0; w < p.ov.group_words && w < 4; w++) {
-    uint32_t bits = m[w];
+#pragma unroll
+  for (int w = 0; w < 4; w++) {
+    uint32_t bits = m[w];               // zero beyond group_words
     while (bits) {
       const int b = __ffs(bits) - 1;
       bits &= bits - 1;
