@@ -174,7 +174,7 @@ __device__ __forceinline__ uint32_t pack2_sat_u8(int lo, int hi) {
 // UA: the staged row starts `delta` (0..15) bytes into its buffer (rows that are not 16-byte
 // aligned in global memory are copied from the boundary below them): four aligned words and a
 // funnel shift replace the three aligned words of a gather.
-template <int KX, int T, int CAP, int NT, bool UA>
+template <int KX, int T, int CAP, int NT, bool UA, int C>
 __device__ __forceinline__ void horizontal_tiles(const uint4 (&A)[T][3][KX], const int (&xoff)[T],
                                                  const uint8_t* __restrict__ rrow, uint8_t* __restrict__ ring_out,
                                                  int q, int delta) {
@@ -184,27 +184,36 @@ __device__ __forceinline__ void horizontal_tiles(const uint4 (&A)[T][3][KX], con
   constexpr int kRound = 1 << (kPrecisionBits - 1);
 #pragma unroll
   for (int t = FIRST; t < FIRST + NT; t++) {
-    uint32_t B[KX][2][3];
+    uint32_t B[KX][2][C];
 #pragma unroll
     for (int ks = 0; ks < KX; ks++)
 #pragma unroll
       for (int h = 0; h < 2; h++) {
-        // 4 pixels = 12 interleaved bytes = 3 words -> one register per channel.  Row pitch
-        // 12 words mod 32 and 3 words per lane: the 32 lanes of each load hit 32 banks.
-        const uint32_t* wp = reinterpret_cast<const uint32_t*>(rbase + xoff[t] + (32 * ks + 16 * h + 4 * q) * 3);
-        uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+        // 4 pixels = 4 * C interleaved bytes = C words -> one register per channel.  (RGB: row pitch
+        // 12 words mod 32 and 3 words per lane: the 32 lanes of each load hit 32 banks.)
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(rbase + xoff[t] + (32 * ks + 16 * h + 4 * q) * C);
+        uint32_t w[C + 1];
+#pragma unroll
+        for (int i = 0; i < C; i++) w[i] = wp[i];
         if (UA) {
-          const uint32_t w3 = wp[3];
-          w0 = __funnelshift_r(w0, w1, shift);
-          w1 = __funnelshift_r(w1, w2, shift);
-          w2 = __funnelshift_r(w2, w3, shift);
+          w[C] = wp[C];
+#pragma unroll
+          for (int i = 0; i < C; i++) w[i] = __funnelshift_r(w[i], w[i + 1], shift);
         }
-        B[ks][h][0] = __byte_perm(__byte_perm(w0, w1, 0x0630), w2, 0x5210);
-        B[ks][h][1] = __byte_perm(__byte_perm(w0, w1, 0x0741), w2, 0x6210);
-        B[ks][h][2] = __byte_perm(__byte_perm(w0, w1, 0x0052), w2, 0x7410);
+        if (C == 3) {
+          B[ks][h][0] = __byte_perm(__byte_perm(w[0], w[1], 0x0630), w[2], 0x5210);
+          B[ks][h][1] = __byte_perm(__byte_perm(w[0], w[1], 0x0741), w[2], 0x6210);
+          B[ks][h][2 % C] = __byte_perm(__byte_perm(w[0], w[1], 0x0052), w[2 % C], 0x7410);
+        } else if (C == 4) {
+#pragma unroll
+          for (int c = 0; c < C; c++)   // byte c of each of the four words
+            B[ks][h][c] = __byte_perm(__byte_perm(w[0], w[1 % C], 0x0040 + 0x11 * c), __byte_perm(w[2 % C], w[3 % C], 0x0040 + 0x11 * c), 0x5410);
+        } else {
+          B[ks][h][0] = w[0];
+        }
       }
 #pragma unroll
-    for (int c = 0; c < 3; c++) {
+    for (int c = 0; c < C; c++) {
       // one accumulator set per weight plane: three independent MMA chains
       int s2[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, s0[4] = {kRound, kRound, kRound, kRound};
 #pragma unroll
@@ -214,10 +223,10 @@ __device__ __forceinline__ void horizontal_tiles(const uint4 (&A)[T][3][KX], con
         mma_u8u8(s0, A[t][0][ks].x, A[t][0][ks].y, A[t][0][ks].z, A[t][0][ks].w, B[ks][0][c], B[ks][1][c]);
       }
       // element 0, 1: pixel g, rows 2q, 2q + 1;  element 2, 3: pixel g + 8 (ring_out is at pixel g, row 2q)
-      uint8_t* o = ring_out + (size_t)(t * 48 + c) * CAP;
+      uint8_t* o = ring_out + (size_t)(t * 16 * C + c) * CAP;
       *reinterpret_cast<uint16_t*>(o) = (uint16_t)pack2_sat_u8(combine_planes(s2[0], s1[0], s0[0]),
                                                                combine_planes(s2[1], s1[1], s0[1]));
-      *reinterpret_cast<uint16_t*>(o + 24 * CAP) = (uint16_t)pack2_sat_u8(combine_planes(s2[2], s1[2], s0[2]),
+      *reinterpret_cast<uint16_t*>(o + 8 * C * CAP) = (uint16_t)pack2_sat_u8(combine_planes(s2[2], s1[2], s0[2]),
                                                                           combine_planes(s2[3], s1[3], s0[3]));
     }
   }
@@ -238,7 +247,7 @@ struct MmaItem {
   int row_start, nbatches;     // first source row, batches of 8 rows
   int byte_lo, copy_bytes;     // source bytes per row the chunk needs
 };
-template <int KX>
+template <int KX, int C>
 __device__ __forceinline__ MmaItem mma_item(const MmaParams& p, int item) {
   MmaItem it;
   const int chunk = item % p.chunks;
@@ -253,8 +262,8 @@ __device__ __forceinline__ MmaItem mma_item(const MmaParams& p, int item) {
   const int row_end = __ldg(p.ws + p.off_yend + it.j1 - 1);
   const int xa_lo = __ldg(p.ws + p.off_xa + it.tile0), xa_hi = __ldg(p.ws + p.off_xa + it.tile1 - 1);
   it.nbatches = (row_end - it.row_start + kBatchRows - 1) / kBatchRows;
-  it.byte_lo = (xa_lo * 3) & ~15;
-  it.copy_bytes = min(p.sw * 3, ((xa_hi + 32 * KX) * 3 + 15) & ~15) - it.byte_lo;
+  it.byte_lo = (xa_lo * C) & ~15;
+  it.copy_bytes = min(p.sw * C, ((xa_hi + 32 * KX) * C + 15) & ~15) - it.byte_lo;
   return it;
 }
 
@@ -262,7 +271,7 @@ __device__ __forceinline__ MmaItem mma_item(const MmaParams& p, int item) {
 // the consumers across item boundaries, so only the very first batch of a CTA waits for HBM with
 // nothing else to do, and a warp loads its tile weights once (the chunk of a CTA never changes:
 // the grid is a multiple of the chunk count).
-template <int KX, int KY, int T, bool UA>
+template <int KX, int KY, int T, bool UA, int C>
 __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bicubic_mma_kernel(const MmaParams p) {
   constexpr int CAP = 32 * KY + 16;   // ring rows: one K window + the rows a batch runs ahead, rounded;
                                       // as a pitch (bytes) it is 16 mod 32, which keeps the loads below conflict-free
@@ -278,7 +287,7 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
   const int nwarps = (int)blockDim.x / 32 - 1;   // consumer warps; the last warp feeds the TMA ring
   if (__ldg(p.ws + 1) != 0) __trap();   // a weight or window outside what the tables can hold (cannot happen
                                         // for the sizes MmaPlan.ok admits; better loud than wrong)
-  const int row_bytes = p.sw * 3;
+  const int row_bytes = p.sw * C;
   if (threadIdx.x == 0) {
     for (int s = 0; s < kMmaStages; s++) {
       mbar_init(&full[s], 1);
@@ -293,7 +302,7 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
     int gb = 0;   // batches issued by this CTA so far: staging buffer and barrier phase follow from it
     const uint64_t policy = l2_policy_evict_first();   // source rows are read once (plus the band halo)
     for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
-      const MmaItem it = mma_item<KX>(p, item);
+      const MmaItem it = mma_item<KX, C>(p, item);
       if (it.copy_bytes + (UA ? 32 : 0) > p.raw_pitch) __trap();
       const uint8_t* fsrc = p.src + (size_t)it.frame * p.sh * row_bytes + it.byte_lo;
       for (int b = 0; b < it.nbatches; b++, gb++) {
@@ -318,16 +327,16 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
   // ---- consumers: horizontal pass, ring and vertical pass of the warp's own tiles ---------------
   uint4 A[T][3][KX];
   int xoff[T];
-  const int wcol0 = warp * T * 48;                    // first ring column (byte column inside the chunk)
+  const int wcol0 = warp * T * 16 * C;                // first ring column (byte column inside the chunk)
   const uint2* byf = reinterpret_cast<const uint2*>(p.ws + p.off_by);
   const int* ya = p.ws + p.off_ya;
   const int* yend = p.ws + p.off_yend;
-  const int out_row_bytes = p.dw * 3;
+  const int out_row_bytes = p.dw * C;
   constexpr int kRound = 1 << (kPrecisionBits - 1);
   int cur_tile0 = -1, ntw = 0;
   int gb = 0;
   for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
-    const MmaItem it = mma_item<KX>(p, item);
+    const MmaItem it = mma_item<KX, C>(p, item);
     if (it.tile0 != cur_tile0) {     // first item of the CTA (and never again when the grid is a multiple of the chunks)
       cur_tile0 = it.tile0;
       const int wtile0 = it.tile0 + warp * T;
@@ -336,7 +345,7 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
 #pragma unroll
       for (int t = 0; t < T; t++) {
         const bool on = t < ntw;     // a slot without a tile gets zero weights and is filtered like the others
-        xoff[t] = on ? __ldg(p.ws + p.off_xa + wtile0 + t) * 3 - it.byte_lo : 0;
+        xoff[t] = on ? __ldg(p.ws + p.off_xa + wtile0 + t) * C - it.byte_lo : 0;
 #pragma unroll
         for (int pl = 0; pl < 3; pl++)
 #pragma unroll
@@ -346,8 +355,8 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
     }
     const int row_start = it.row_start, j1 = it.j1;
     uint8_t* fdst = p.dst + (size_t)it.frame * p.dh * out_row_bytes;
-    const int gcol0 = it.tile0 * 48 + wcol0;          // first output byte column of this warp
-    const bool cols_inside = gcol0 + ntw * 48 <= out_row_bytes;
+    const int gcol0 = it.tile0 * 16 * C + wcol0;      // first output byte column of this warp
+    const bool cols_inside = gcol0 + ntw * 16 * C <= out_row_bytes;
 
     int jn = it.j0;       // next group of output rows to emit
     int slot = 0;         // ring row of the batch being filtered
@@ -364,9 +373,9 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
       if (ntw > 0) {
         // -- horizontal pass: 8 staged rows x this warp's tiles -> ring rows slot .. slot + 7
         const uint8_t* rrow = raw + (size_t)(s * kBatchRows + g) * p.raw_pitch;
-        uint8_t* ring_out = ring + (size_t)(wcol0 + g * 3) * CAP + slot + 2 * q;
+        uint8_t* ring_out = ring + (size_t)(wcol0 + g * C) * CAP + slot + 2 * q;
         // slots without a tile: zero weights, spare columns
-        horizontal_tiles<KX, T, CAP, T, UA>(A, xoff, rrow, ring_out, q, UA ? deltas[s * kBatchRows + g] : 0);
+        horizontal_tiles<KX, T, CAP, T, UA, C>(A, xoff, rrow, ring_out, q, UA ? deltas[s * kBatchRows + g] : 0);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[s]);     // the staged rows are free again
@@ -389,7 +398,7 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
         const bool inside = cols_inside && jn * 8 + 8 <= p.dh;   // no clipping of this group's stores
         uint8_t* orow = fdst + (size_t)dy * out_row_bytes + gcol0 + g;
 #pragma unroll 3
-        for (int mt = 0; mt < ntw * 3; mt++) {
+        for (int mt = 0; mt < ntw * C; mt++) {
           const uint8_t* c0 = ring + (size_t)(wcol0 + mt * 16 + g) * CAP;
           const uint8_t* c1 = c0 + 8 * CAP;
           int s2[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, s0[4] = {kRound, kRound, kRound, kRound};
@@ -444,11 +453,11 @@ static int env_int(const char* name, int fallback) {
   return v ? atoi(v) : fallback;
 }
 
-template <int KX, int KY, int T, bool UA>
+template <int KX, int KY, int T, bool UA, int C>
 static int launch_mma(MmaParams p, int n_frames, double scale_y, cudaStream_t stream, bool* done) {
   constexpr int kMmaMaxWarps = WarpBudget<KX, T>::max_warps;
   constexpr int CAP = 32 * KY + 16;
-  const int row_bytes = p.sw * 3;
+  const int row_bytes = p.sw * C;
   const double scale_x = (double)p.sw / p.dw;
   const size_t max_smem = (size_t)device_max_smem_optin();
   int chunks = (p.ntx + kMmaMaxWarps * T - 1) / (kMmaMaxWarps * T);
@@ -463,16 +472,16 @@ static int launch_mma(MmaParams p, int n_frames, double scale_y, cudaStream_t st
     nwarps = (p.tiles_per_chunk + T - 1) / T;
     // source bytes a chunk touches per row (window starts are rounded down to 4 pixels, the copy to 16 bytes)
     const long long bound_px = (long long)(p.tiles_per_chunk * 16 * scale_x) + 32 * KX + 8;
-    long long bound_bytes = (bound_px * 3 + 32 + 15) & ~15LL;
+    long long bound_bytes = (bound_px * C + 32 + 15) & ~15LL;
     if (bound_bytes > row_bytes) bound_bytes = (row_bytes + 15) & ~15;
     if (UA) bound_bytes += 32;                                // the 16-byte rounding at both ends of a row
     long long pitch = (bound_bytes + 127) / 128 * 128 + 48;   // 48 mod 128: see the gather in the kernel
     if (pitch - 128 >= bound_bytes) pitch -= 128;
     p.raw_pitch = (int)pitch;
-    smem = 128 + (size_t)kMmaStages * kBatchRows * (size_t)pitch + (size_t)nwarps * T * 48 * CAP + 128;
+    smem = 128 + (size_t)kMmaStages * kBatchRows * (size_t)pitch + (size_t)nwarps * T * 16 * C * CAP + 128;
     if (smem <= max_smem) break;
   }
-  auto kernel = bicubic_mma_kernel<KX, KY, T, UA>;
+  auto kernel = bicubic_mma_kernel<KX, KY, T, UA, C>;
   AIKO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int threads = (nwarps + 1) * 32;
   int per_sm = 0;
@@ -507,22 +516,29 @@ int bicubic_mma_launch(const uint8_t* src, int n_frames, int sh, int sw, int cha
                        const int* ws, const BicubicLayout& l, cudaStream_t stream, bool* done) {
   *done = false;
   const MmaPlan& m = l.mma;
-  // RGB frames (rows off 16-byte boundaries are copied from the boundary below them); everything else: scalar kernel
-  if (!m.ok || channels != 3 || env_int("AIKO_B200_BICUBIC_SCALAR", 0)) return AIKO_B200_OK;
-  const bool unaligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)((size_t)sw * 3)) & 15) != 0;
+  // 1-, 3- and 4-channel frames (rows off 16-byte boundaries are copied from the boundary below them);
+  // reductions beyond the tables (scale > ~5): scalar kernel
+  if (!m.ok || env_int("AIKO_B200_BICUBIC_SCALAR", 0)) return AIKO_B200_OK;
+  const bool unaligned = ((reinterpret_cast<uintptr_t>(src) | (uintptr_t)((size_t)sw * channels)) & 15) != 0;
   MmaParams p{};
   p.src = src; p.dst = dst; p.ws = ws;
   p.n = n_frames; p.sh = sh; p.sw = sw; p.dh = dh; p.dw = dw;
   p.ntx = m.ntx; p.ngy = m.ngy;
   p.off_xa = m.off_xa; p.off_ax = m.off_ax; p.off_ya = m.off_ya; p.off_yend = m.off_yend; p.off_by = m.off_by;
   const double scale_y = (double)sh / dh;
+#define AIKO_MMA_CH(KX, KY, T, C)                                                                 \
+  return unaligned ? launch_mma<KX, KY, T, true, C>(p, n_frames, scale_y, stream, done)              \
+                   : launch_mma<KX, KY, T, false, C>(p, n_frames, scale_y, stream, done);
 #define AIKO_MMA_CASE(KX, KY, T)                                                                   \
-  if (m.kx == KX && m.ky == KY)                                                                    \
-    return unaligned ? launch_mma<KX, KY, T, true>(p, n_frames, scale_y, stream, done)              \
-                     : launch_mma<KX, KY, T, false>(p, n_frames, scale_y, stream, done);
+  if (m.kx == KX && m.ky == KY) {                                                                  \
+    if (channels == 3) { AIKO_MMA_CH(KX, KY, T, 3) }                                               \
+    if (channels == 1) { AIKO_MMA_CH(KX, KY, T, 1) }                                               \
+    AIKO_MMA_CH(KX, KY, T, 4)                                                                      \
+  }
   AIKO_MMA_CASE(1, 1, 8) AIKO_MMA_CASE(2, 1, 4) AIKO_MMA_CASE(3, 1, 2) AIKO_MMA_CASE(4, 1, 2)
   AIKO_MMA_CASE(1, 2, 8) AIKO_MMA_CASE(2, 2, 4) AIKO_MMA_CASE(3, 2, 2) AIKO_MMA_CASE(4, 2, 2)
 #undef AIKO_MMA_CASE
+#undef AIKO_MMA_CH
   return AIKO_B200_OK;
 }
 

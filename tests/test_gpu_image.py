@@ -186,6 +186,16 @@ def test_resize_bicubic_tensor_core_path_vs_oracle(cuda, shape, monkeypatch):
     np.testing.assert_array_equal(host(ops.resize_bicubic_aa(view, W, H)), want)
 
 
+@pytest.mark.parametrize("channels", [1, 4])
+@pytest.mark.parametrize("shape", [(270, 480, 120, 160), (120, 161, 270, 480), (301, 207, 77, 51), (480, 640, 100, 131)])
+def test_resize_bicubic_tensor_core_gray_and_rgba(cuda, shape, channels):
+    """PIL 'L' and 'RGBA' frames take the same tensor-core kernel (one / four channel planes)."""
+    h, w, H, W = shape
+    frames = np.stack([cases.frame(7400 + k, h, w, channels) for k in range(2)])
+    want = np.stack([O.resize_bicubic_aa(f, W, H) for f in frames])
+    np.testing.assert_array_equal(host(ops.resize_bicubic_aa(dev(frames, cuda), W, H)), want)
+
+
 def test_resize_bicubic_tensor_core_equals_scalar_kernel(cuda, monkeypatch):
     """Full-size batch: the two kernels behind the entry point agree byte for byte."""
     g = torch.Generator(device=cuda).manual_seed(3)
@@ -393,7 +403,8 @@ def test_sizes_beyond_on_chip_limits_are_refused_not_mangled(cuda):
         ops.resize_linear(tiny, 40000, 2)                 # 40000-pixel output rows: tables exceed shared memory
     assert e.value.code == _native.ERR_UNSUPPORTED and "shared memory" in str(e.value)
     with pytest.raises(_native.NativeError) as e:
-        ops.resize_bicubic_aa(tiny[..., 0].contiguous(), 60000, 2)       # gray: the scalar kernel, one row per CTA
+        # a 10x reduction is outside the tensor-core kernel's tables: the scalar kernel, one row per CTA
+        ops.resize_bicubic_aa(torch.zeros((1, 2, 600000, 3), dtype=torch.uint8, device=cuda), 60000, 2)
     assert e.value.code == _native.ERR_UNSUPPORTED
     wide = np.stack([cases.frame(82, 2, 4, 3)])                        # RGB: column chunks of the tensor-core kernel
     np.testing.assert_array_equal(host(ops.resize_bicubic_aa(dev(wide, cuda), 60000, 2))[0],
