@@ -122,7 +122,9 @@ int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int src_h, int 
 /*   bytes   = aiko_b200_resize_bicubic_workspace_bytes(...)  (0 for bad sizes)    */
 /*   prepare = fills it for one (src, dst) size pair; reusable for any number of   */
 /*             resize calls with that size pair, on any stream ordered after it.   */
-/* Frames are tight: [n, h, w, channels], channels in {1, 3, 4}.                    */
+/* Frames are tight: [n, h, w, channels], channels in {1, 3, 4}.  The workspace      */
+/* holds the 22-bit coefficients and, for reductions up to ~5x, the same weights as  */
+/* integer-MMA operand tables (237 KB in all for 1080p -> 640x480).                  */
 size_t aiko_b200_resize_bicubic_workspace_bytes(int src_h, int src_w, int dst_h, int dst_w);
 int aiko_b200_resize_bicubic_prepare(void* workspace, size_t workspace_bytes, int src_h, int src_w, int dst_h,
                                      int dst_w, void* stream);
@@ -136,7 +138,9 @@ int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, int src_h, 
 /* a minimal binding that only has the frame buffers).  No counterpart in the        */
 /* reference.  The weight tables go into a 256 KiB array built into the library      */
 /* (resident on every GPU that loads it); size pairs needing more are refused with   */
-/* AIKO_B200_ERR_UNSUPPORTED (1080p -> 640x480 needs 73 KB).  The first call on a    */
+/* AIKO_B200_ERR_UNSUPPORTED (the limit applies to the coefficient tables: 73 KB for */
+/* 1080p -> 640x480; the tensor-core operand tables, 164 KB more, are used when they */
+/* fit as well, else the slower scalar kernel runs).  The first call on a            */
 /* device looks up that array's device address (cudaGetSymbolAddress): make it       */
 /* before any stream capture.  All calls share the one array and each rewrites it:   */
 /* calls that can overlap on the GPU (different streams, no ordering) race -- give   */
