@@ -272,21 +272,32 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
     float* amp = reinterpret_cast<float*>(y);          // half + 1 magnitudes, in the idle buffer
     float* out = p.amplitudes + (size_t)w * n;
     if (p.dtype == 0 && w + (int)gridDim.x < p.n_windows) prefetch(w + gridDim.x);
-    for (int k = threadIdx.x; k <= half; k += NT) {
-      const float2 zk = x[point_index<FAST>(k == half ? 0 : k)];
-      const float2 zr = x[point_index<FAST>(k == 0 ? 0 : half - k)];
+    // Bins k and half - k come from the same pair (z[k], z[half - k]): X[k] = E + W^k O and
+    // X[half - k] = conj(E - W^k O), so one thread makes both magnitudes from one set of loads.
+    for (int k = threadIdx.x; k <= half / 2; k += NT) {
+      const int kr = half - k;                            // (k == 0 pairs bin 0 with bin half)
+      const float2 zk = x[point_index<FAST>(k)];
+      const float2 zr = x[point_index<FAST>(k == 0 ? 0 : kr)];
       const float2 zc = make_float2(zr.x, -zr.y);
       const float2 e = cscale(cadd(zk, zc), 0.5f);
       const float2 o = cscale(mul_mi(csub(zk, zc)), 0.5f);
-      float2 tk = tw[k >> 1];                             // (k == half: tw_half[half / 2] = -1)
+      float2 tk = tw[k >> 1];
       if (k & 1) tk = cmul(tk, w_odd);
-      const float2 xk = cadd(e, cmul(tk, o));
-      float a;                                            // |X[k]| / 1e6; the approximate root is within 1e-6 relative
-      asm("sqrt.approx.f32 %0, %1;" : "=f"(a) : "f"(__fmaf_rn(xk.x, xk.x, xk.y * xk.y)));
+      const float2 t = cmul(tk, o);
+      const float2 xa = cadd(e, t), xb = csub(e, t);
+      float a, b;                                         // |X| / 1e6; the approximate root is within 1e-6 relative
+      asm("sqrt.approx.f32 %0, %1;" : "=f"(a) : "f"(__fmaf_rn(xa.x, xa.x, xa.y * xa.y)));
+      asm("sqrt.approx.f32 %0, %1;" : "=f"(b) : "f"(__fmaf_rn(xb.x, xb.x, xb.y * xb.y)));
       a *= 1e-6f;
+      b *= 1e-6f;
       amp[k] = a;
       out[k] = a;
-      if (k != 0 && k != half) out[n - k] = a;         // |X[n-k]| = |X[k]| for real input
+      if (k != 0) out[n - k] = a;                         // |X[n-k]| = |X[k]| for real input
+      if (kr != k) {
+        amp[kr] = b;
+        out[kr] = b;
+        if (k != 0) out[n - kr] = b;                      // (bin half has no mirror)
+      }
     }
     __syncthreads();
     // ---- PE_AudioResampler: 8 band sums over the first half of the spectrum (audio_io.py:250-277)
