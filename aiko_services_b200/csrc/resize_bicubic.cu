@@ -78,6 +78,8 @@ struct BicubicParams {
   int ksx, ksy, off_bx, off_kx, off_by, off_ky;
   int band, bands_per_frame, ring_rows;
   int kx_in_smem;
+  int chunks, chunk_w;            // output columns are split when a whole row does not fit in shared memory
+  int src_stride, mid_stride;     // shared-memory pitch of a staged source row segment / an intermediate row
 };
 
 constexpr int kBicubicThreads = 512;
@@ -85,28 +87,35 @@ constexpr int kRowsPerRound = 4;   // source rows staged and filtered between tw
 
 __global__ void __launch_bounds__(kBicubicThreads) resize_bicubic_rows(const BicubicParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
-  const int src_row_bytes = p.sw * p.ch, mid_row_bytes = p.dw * p.ch;
-  const int src_stride = (src_row_bytes + 31) & ~15, mid_stride = (mid_row_bytes + 15) & ~15;
-  uint8_t* srow = smem;                               // kRowsPerRound staged source rows
+  const int src_row_bytes = p.sw * p.ch, out_row_bytes = p.dw * p.ch;
+  const int src_stride = p.src_stride, mid_stride = p.mid_stride;
+  uint8_t* srow = smem;                               // kRowsPerRound staged source row segments
   uint8_t* ring = srow + (size_t)kRowsPerRound * src_stride;   // ring_rows intermediate rows
-  int* bx_s = reinterpret_cast<int*>(ring + (size_t)p.ring_rows * mid_stride);   // xmin, count per dx
-  int* kx_s = bx_s + ((2 * p.dw + 3) & ~3);           // weights, when they fit (16-byte aligned rows)
+  int* bx_s = reinterpret_cast<int*>(ring + (size_t)p.ring_rows * mid_stride);   // xmin, count per column
+  int* kx_s = bx_s + ((2 * p.chunk_w + 3) & ~3);      // weights, when they fit (16-byte aligned rows)
 
   const int* bx = p.ws + p.off_bx;
   const int* kx = p.ws + p.off_kx;
   const int* by = p.ws + p.off_by;
   const int* ky = p.ws + p.off_ky;
-  for (int i = threadIdx.x; i < 2 * p.dw; i += kBicubicThreads) bx_s[i] = bx[i];
+  // this CTA: (frame, band of output rows, chunk of output columns cx0 .. cx1)
+  const int chunk = blockIdx.x % p.chunks, fb = blockIdx.x / p.chunks;
+  const int cx0 = chunk * p.chunk_w, cx1 = min(p.dw, cx0 + p.chunk_w), cw = cx1 - cx0;
+  for (int i = threadIdx.x; i < 2 * cw; i += kBicubicThreads) bx_s[i] = bx[2 * cx0 + i];
   if (p.kx_in_smem)
-    for (int i = threadIdx.x; i < p.dw * p.ksx; i += kBicubicThreads) kx_s[i] = kx[i];
-  const int* kxt = p.kx_in_smem ? kx_s : kx;
+    for (int i = threadIdx.x; i < cw * p.ksx; i += kBicubicThreads) kx_s[i] = kx[(size_t)cx0 * p.ksx + i];
+  const int* kxt = p.kx_in_smem ? kx_s : kx + (size_t)cx0 * p.ksx;
+  // source bytes of a row that the chunk's columns read, from a 16-byte boundary
+  const int s_lo = (bx[2 * cx0] * p.ch) & ~15;
+  const int s_hi = min(src_row_bytes, (bx[2 * (cx1 - 1)] + bx[2 * (cx1 - 1) + 1]) * p.ch);
+  const int seg_bytes = s_hi - s_lo, mid_row_bytes = cw * p.ch;
   __syncthreads();
 
-  const int frame = blockIdx.x / p.bands_per_frame;
-  const int dy0 = (blockIdx.x - frame * p.bands_per_frame) * p.band;
+  const int frame = fb / p.bands_per_frame;
+  const int dy0 = (fb - frame * p.bands_per_frame) * p.band;
   const int dy1 = min(dy0 + p.band, p.dh);
   const uint8_t* fsrc = p.src + (size_t)frame * p.sh * src_row_bytes;
-  uint8_t* fdst = p.dst + (size_t)frame * p.dh * mid_row_bytes;
+  uint8_t* fdst = p.dst + (size_t)frame * p.dh * out_row_bytes + (size_t)cx0 * p.ch;
   const int band_last = by[2 * (dy1 - 1)] + by[2 * (dy1 - 1) + 1] - 1;   // last source row this band needs
 
   int next_src = by[2 * dy0];
@@ -118,23 +127,23 @@ __global__ void __launch_bounds__(kBicubicThreads) resize_bicubic_rows(const Bic
       const int nrows = min(kRowsPerRound, band_last - next_src + 1);
       const bool vec = ((reinterpret_cast<uintptr_t>(fsrc) | (uintptr_t)src_row_bytes) & 15) == 0;
       for (int r = 0; r < nrows; r++) {
-        const uint8_t* g = fsrc + (size_t)(next_src + r) * src_row_bytes;
+        const uint8_t* g = fsrc + (size_t)(next_src + r) * src_row_bytes + s_lo;
         uint8_t* s = srow + (size_t)r * src_stride;
-        if (vec) {
-          for (int i = threadIdx.x; i < (src_row_bytes >> 4); i += kBicubicThreads)
+        if (vec) {                                  // (rows are a multiple of 16 bytes: rounding up stays inside the row)
+          for (int i = threadIdx.x; i < ((seg_bytes + 15) >> 4); i += kBicubicThreads)
             reinterpret_cast<uint4*>(s)[i] = ldg_stream(reinterpret_cast<const uint4*>(g) + i);
         } else {
-          for (int i = threadIdx.x; i < src_row_bytes; i += kBicubicThreads) s[i] = g[i];
+          for (int i = threadIdx.x; i < seg_bytes; i += kBicubicThreads) s[i] = g[i];
         }
       }
       __syncthreads();
       for (int r = 0; r < nrows; r++) {
         const uint8_t* srcrow = srow + (size_t)r * src_stride;
         uint8_t* mid = ring + (size_t)((next_src + r) % p.ring_rows) * mid_stride;
-        for (int dx = threadIdx.x; dx < p.dw; dx += kBicubicThreads) {
+        for (int dx = threadIdx.x; dx < cw; dx += kBicubicThreads) {     // dx: column inside the chunk
           const int xmin = bx_s[2 * dx], cnt = bx_s[2 * dx + 1];
           const int4* k4 = reinterpret_cast<const int4*>(kxt + (size_t)dx * p.ksx);   // rows of 4-padded weights
-          const uint8_t* s = srcrow + xmin * p.ch;
+          const uint8_t* s = srcrow + xmin * p.ch - s_lo;
           if (p.ch == 3) {
             int a0 = 1 << (kPrecisionBits - 1), a1 = a0, a2 = a0;
             for (int t = 0; t < cnt; t += 4) {       // padding weights are zero; staged rows have slack bytes
@@ -160,7 +169,7 @@ __global__ void __launch_bounds__(kBicubicThreads) resize_bicubic_rows(const Bic
     }
     // vertical pass: one output row from ycnt intermediate rows
     const int* k = ky + (size_t)dy * p.ksy;
-    uint8_t* o = fdst + (size_t)dy * mid_row_bytes;
+    uint8_t* o = fdst + (size_t)dy * out_row_bytes;
     for (int i4 = threadIdx.x * 4; i4 < mid_row_bytes; i4 += kBicubicThreads * 4) {
       int a[4];
 #pragma unroll
@@ -254,21 +263,36 @@ extern "C" int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, 
   if (dst_h < 4) band = dst_h;
   p.band = band;
   p.bands_per_frame = (dst_h + band - 1) / band;
-  const size_t src_stride = ((size_t)src_w * channels + 31) & ~(size_t)15;
-  const size_t mid_stride = ((size_t)dst_w * channels + 15) & ~(size_t)15;
-  size_t smem = (size_t)kRowsPerRound * src_stride + 16 + (size_t)p.ring_rows * mid_stride +
-                (size_t)((2 * dst_w + 3) & ~3) * sizeof(int);
-  const size_t kx_bytes = (size_t)dst_w * l.x.ksize * sizeof(int);
+  // Shared memory per CTA: staged source segments, the ring of intermediate rows, the column tables.
+  // When a whole output row does not fit (wide rows under a large vertical reduction), the columns
+  // are split into chunks, each with its own CTAs.
   const size_t max_smem = (size_t)device_max_smem_optin();
-  p.kx_in_smem = (smem + kx_bytes <= 100 * 1024) ? 1 : 0;
-  if (p.kx_in_smem) smem += kx_bytes;
-  if (smem > max_smem) {
-    set_last_error("resize_bicubic: %dx%d -> %dx%d needs %zu bytes of shared memory (max %zu)", src_w, src_h, dst_w,
-                   dst_h, smem, max_smem);
-    return AIKO_B200_ERR_UNSUPPORTED;
+  const double scale_x = (double)src_w / dst_w, support_x = 2.0 * (scale_x < 1.0 ? 1.0 : scale_x);
+  size_t smem = 0;
+  for (int chunks = 1;; chunks *= 2) {
+    const int chunk_w = (dst_w + chunks - 1) / chunks;
+    p.chunk_w = chunk_w;
+    p.chunks = (dst_w + chunk_w - 1) / chunk_w;
+    long long seg = (long long)((chunk_w - 1) * scale_x + 2.0 * support_x + 3.0) * channels + 16;   // bytes a chunk reads per row
+    if (seg > (long long)src_w * channels) seg = (long long)src_w * channels;
+    const size_t src_stride = ((size_t)seg + 31) & ~(size_t)15;
+    const size_t mid_stride = ((size_t)chunk_w * channels + 15) & ~(size_t)15;
+    p.src_stride = (int)src_stride;
+    p.mid_stride = (int)mid_stride;
+    smem = (size_t)kRowsPerRound * src_stride + 16 + (size_t)p.ring_rows * mid_stride +
+           (size_t)((2 * chunk_w + 3) & ~3) * sizeof(int);
+    const size_t kx_bytes = (size_t)chunk_w * l.x.ksize * sizeof(int);
+    p.kx_in_smem = (smem + kx_bytes <= 100 * 1024) ? 1 : 0;
+    if (p.kx_in_smem) smem += kx_bytes;
+    if (smem <= max_smem) break;
+    if (chunk_w <= 16) {
+      set_last_error("resize_bicubic: %dx%d -> %dx%d needs %zu bytes of shared memory for 16 columns (max %zu)", src_w,
+                     src_h, dst_w, dst_h, smem, max_smem);
+      return AIKO_B200_ERR_UNSUPPORTED;
+    }
   }
   AIKO_CUDA(cudaFuncSetAttribute(resize_bicubic_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const long long grid = (long long)n_frames * p.bands_per_frame;
+  const long long grid = (long long)n_frames * p.bands_per_frame * p.chunks;
   AIKO_CHECK_ARG(grid < ((long long)1 << 31), "resize_bicubic: too many bands");
   resize_bicubic_rows<<<(unsigned)grid, kBicubicThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
   return cuda_status(cudaGetLastError(), "resize_bicubic launch");

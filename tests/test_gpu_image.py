@@ -402,10 +402,11 @@ def test_sizes_beyond_on_chip_limits_are_refused_not_mangled(cuda):
     with pytest.raises(_native.NativeError) as e:
         ops.resize_linear(tiny, 40000, 2)                 # 40000-pixel output rows: tables exceed shared memory
     assert e.value.code == _native.ERR_UNSUPPORTED and "shared memory" in str(e.value)
-    with pytest.raises(_native.NativeError) as e:
-        # a 10x reduction is outside the tensor-core kernel's tables: the scalar kernel, one row per CTA
-        ops.resize_bicubic_aa(torch.zeros((1, 2, 600000, 3), dtype=torch.uint8, device=cuda), 60000, 2)
-    assert e.value.code == _native.ERR_UNSUPPORTED
+    # a 10x reduction is outside the tensor-core kernel's tables: the scalar kernel, which splits rows that do not
+    # fit in shared memory into column chunks; so does a wide row under a large vertical reduction
+    for (h, w, H, W) in ((2, 60000, 2, 6000), (229, 696, 6, 430), (300, 2000, 7, 1999)):
+        big = np.stack([cases.frame(83, h, w, 3)])
+        np.testing.assert_array_equal(host(ops.resize_bicubic_aa(dev(big, cuda), W, H))[0], O.resize_bicubic_aa(big[0], W, H))
     wide = np.stack([cases.frame(82, 2, 4, 3)])                        # RGB: column chunks of the tensor-core kernel
     np.testing.assert_array_equal(host(ops.resize_bicubic_aa(dev(wide, cuda), 60000, 2))[0],
                                   O.resize_bicubic_aa(wide[0], 60000, 2))
