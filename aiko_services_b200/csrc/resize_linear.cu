@@ -212,8 +212,8 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
   uint64_t keep;
   asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
   const int R = p.rows_per_slot;
+  int sub = 0;                                     // row inside the slot
   for (int it = 0; it < my_items; ++it) {
-    const int sub = it % R;
     if (sub == 0) mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
     const int* rec = recs + (slot * R + sub) * kRecHeader;
     const int2 bb = *reinterpret_cast<const int2*>(rec + 2);                       // b0, b1
@@ -247,7 +247,8 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
         asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(d + 2), "r"(o[2]) : "memory");
       }
     }
-    if (sub + 1 == R || it + 1 == my_items) {
+    if (++sub == R || it + 1 == my_items) {
+      sub = 0;
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);    // the staged rows of this slot are free again
       if (++slot == p.stages) { slot = 0; ++round; }
@@ -271,8 +272,8 @@ __device__ __forceinline__ void consume_rows_gray(const ResizeParams& p, uint64_
   }
   int slot = 0, round = 0;
   const int R = p.rows_per_slot;
+  int sub = 0;                                     // row inside the slot
   for (int it = 0; it < my_items; ++it) {
-    const int sub = it % R;
     if (sub == 0) mbar_wait(&full[slot], (uint32_t)(round & 1), (uint32_t)p.wait_ns[2], (uint32_t)p.wait_ns[3]);
     const int* rec = recs + (slot * R + sub) * kRecHeader;
     const int2 bb = *reinterpret_cast<const int2*>(rec + 2);                       // b0, b1
@@ -293,7 +294,8 @@ __device__ __forceinline__ void consume_rows_gray(const ResizeParams& p, uint64_
       }
       asm volatile("st.global.L1::no_allocate.b32 [%0], %1;" ::"l"(drow + g), "r"(out) : "memory");
     }
-    if (sub + 1 == R || it + 1 == my_items) {
+    if (++sub == R || it + 1 == my_items) {
+      sub = 0;
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
       if (++slot == p.stages) { slot = 0; ++round; }
