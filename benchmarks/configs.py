@@ -73,6 +73,12 @@ def main():
     report("resize_linear 1918x1080->640x480 (rows off 16-byte boundaries)", 32, "frames", 960 * 1918 * 3 + 921_600, ms)
     del odd_in
 
+    vga = [torch.randint(0, 256, (256, 480, 640, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+    vga_out = torch.empty((256, 240, 320, 3), dtype=torch.uint8, device=dev)
+    ms = timed(lambda i: ops.resize_linear(vga[i % rot], 320, 240, out=vga_out), args.steps)
+    report("resize_linear 640x480->320x240 (short rows: several per ring slot)", 256, "frames", 640 * 480 * 3 + 320 * 240 * 3, ms)
+    del vga, vga_out
+
     sw = torch.empty_like(hd[0])
     ms = timed(lambda i: sw.copy_(hd[i % rot]), args.steps)
     report("calibration: torch device copy of one 199 MB batch (read + write)", 32, "frames", 2 * 6_220_800, ms)
