@@ -192,21 +192,26 @@ __device__ __forceinline__ void consume_row(const uint8_t* r0, const uint8_t* r1
 // UNALIGNED: source rows that do not start on a 16-byte boundary were copied from the boundary
 // below, so each staged row starts `delta` (0..15, from the record) bytes into its buffer and the
 // word / shift split of a tap offset is redone per row.
-template <bool DECIM, bool UNALIGNED>
+template <bool DECIM, bool UNALIGNED, int G>
 __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_t* full, uint64_t* empty, const int* recs,
                                                   const uint8_t* stage, int my_items, const int* xw, const int* xs,
-                                                  const uint32_t* xcoef, int g, bool on, uint32_t sel_rgb, int lane) {
-  int wo[4] = {0, 0, 0, 0}, sh[4] = {0, 0, 0, 0};
-  uint32_t cs[4] = {0, 0, 0, 0};
-  if (on) {
-    const int4 w4 = reinterpret_cast<const int4*>(xw)[g];
-    const int4 s4 = reinterpret_cast<const int4*>(xs)[g];
-    wo[0] = w4.x; wo[1] = w4.y; wo[2] = w4.z; wo[3] = w4.w;
-    sh[0] = s4.x; sh[1] = s4.y; sh[2] = s4.z; sh[3] = s4.w;
-    if (!DECIM) {
-      const uint4 c4 = reinterpret_cast<const uint4*>(xcoef)[g];
-      cs[0] = c4.x; cs[1] = c4.y; cs[2] = c4.z; cs[3] = c4.w;
-    }
+                                                  const uint32_t* xcoef, int g0, int gstep, int groups, uint32_t sel_rgb,
+                                                  int lane) {
+  // G groups per thread (rows wider than 1024 output pixels): group g0 + i * gstep, so the lanes of a
+  // warp still write consecutive 12-byte pieces
+  int wo[G][4], sh[G][4];
+  uint32_t cs[G][4];
+  bool on[G];
+#pragma unroll
+  for (int i = 0; i < G; i++) {
+    const int g = g0 + i * gstep;
+    on[i] = g < groups;
+    const int4 w4 = on[i] ? reinterpret_cast<const int4*>(xw)[g] : make_int4(0, 0, 0, 0);
+    const int4 s4 = on[i] ? reinterpret_cast<const int4*>(xs)[g] : make_int4(0, 0, 0, 0);
+    wo[i][0] = w4.x; wo[i][1] = w4.y; wo[i][2] = w4.z; wo[i][3] = w4.w;
+    sh[i][0] = s4.x; sh[i][1] = s4.y; sh[i][2] = s4.z; sh[i][3] = s4.w;
+    const uint4 c4 = (!DECIM && on[i]) ? reinterpret_cast<const uint4*>(xcoef)[g] : make_uint4(0, 0, 0, 0);
+    cs[i][0] = c4.x; cs[i][1] = c4.y; cs[i][2] = c4.z; cs[i][3] = c4.w;
   }
   int slot = 0, round = 0;
   uint64_t keep;
@@ -219,24 +224,26 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
     const int2 bb = *reinterpret_cast<const int2*>(rec + 2);                       // b0, b1
     uint32_t* drow = *reinterpret_cast<uint32_t* const*>(rec + 6);                 // first byte of the output row
     const uint8_t* r0 = stage + (size_t)(slot * R + sub) * 2 * p.seg_stride;
-    if (on) {
+    const uint32_t b0s = DECIM ? ((uint32_t)bb.x << 15) : ((uint32_t)bb.x << 16);
+    const uint32_t b1s = DECIM ? ((uint32_t)bb.y << 15) : ((uint32_t)bb.y << 16);
+    const int2 delta = UNALIGNED ? *reinterpret_cast<const int2*>(rec + 4) : make_int2(0, 0);
+#pragma unroll
+    for (int i = 0; i < G; i++) {
+      if (!on[i]) continue;
       uint32_t o[3];
-      const uint32_t b0s = DECIM ? ((uint32_t)bb.x << 15) : ((uint32_t)bb.x << 16);
-      const uint32_t b1s = DECIM ? ((uint32_t)bb.y << 15) : ((uint32_t)bb.y << 16);
       if (UNALIGNED) {
-        const int2 delta = *reinterpret_cast<const int2*>(rec + 4);
         int wa[4], sa[4], wb[4], sb[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-          const int exact = wo[k] + (sh[k] >> 3);      // byte offset of the tap in the source row
+          const int exact = wo[i][k] + (sh[i][k] >> 3);      // byte offset of the tap in the source row
           wa[k] = (exact + delta.x) & ~3; sa[k] = ((exact + delta.x) & 3) * 8;
           wb[k] = (exact + delta.y) & ~3; sb[k] = ((exact + delta.y) & 3) * 8;
         }
-        group_pixels<DECIM>(r0, r0 + p.seg_stride, wa, sa, wb, sb, cs, b0s, b1s, sel_rgb, o);
+        group_pixels<DECIM>(r0, r0 + p.seg_stride, wa, sa, wb, sb, cs[i], b0s, b1s, sel_rgb, o);
       } else {
-        group_pixels<DECIM>(r0, r0 + p.seg_stride, wo, sh, wo, sh, cs, b0s, b1s, sel_rgb, o);
+        group_pixels<DECIM>(r0, r0 + p.seg_stride, wo[i], sh[i], wo[i], sh[i], cs[i], b0s, b1s, sel_rgb, o);
       }
-      uint32_t* d = drow + 3 * g;
+      uint32_t* d = drow + 3 * (g0 + i * gstep);
       if (p.keep_output) {      // the overlay pass reads these pixels next: ask L2 to hold on to them
         asm volatile("st.global.L1::no_allocate.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(d), "r"(o[0]), "l"(keep) : "memory");
         asm volatile("st.global.L1::no_allocate.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(d + 1), "r"(o[1]), "l"(keep) : "memory");
@@ -253,6 +260,20 @@ __device__ __forceinline__ void consume_rows_fast(const ResizeParams& p, uint64_
       if (lane == 0) mbar_arrive(&empty[slot]);    // the staged rows of this slot are free again
       if (++slot == p.stages) { slot = 0; ++round; }
     }
+  }
+}
+
+template <int G>
+__device__ __forceinline__ void consume_rows_fast_g(const ResizeParams& p, bool decim, uint64_t* full, uint64_t* empty,
+                                                    const int* recs, const uint8_t* stage, int my_items, const int* xw,
+                                                    const int* xs, const uint32_t* xcoef, int g0, int gstep, int groups,
+                                                    uint32_t sel_rgb, int lane) {
+  if (p.unaligned) {
+    if (decim) consume_rows_fast<true, true, G>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g0, gstep, groups, sel_rgb, lane);
+    else consume_rows_fast<false, true, G>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g0, gstep, groups, sel_rgb, lane);
+  } else {
+    if (decim) consume_rows_fast<true, false, G>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g0, gstep, groups, sel_rgb, lane);
+    else consume_rows_fast<false, false, G>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g0, gstep, groups, sel_rgb, lane);
   }
 }
 
@@ -432,12 +453,11 @@ __global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
     const bool on = g < groups;
     if (p.ch == 1) {
       consume_rows_gray(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, lane);
-    } else if (p.unaligned) {
-      if (decim) consume_rows_fast<true, true>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
-      else consume_rows_fast<false, true>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
     } else {
-      if (decim) consume_rows_fast<true, false>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
-      else consume_rows_fast<false, false>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, sel_rgb, lane);
+      const int gstep = ncons * 32, per_thread = (groups + gstep - 1) / gstep;
+      if (per_thread <= 1) consume_rows_fast_g<1>(p, decim, full, empty, recs, stage, my_items, xw, xs, xcoef, g, gstep, groups, sel_rgb, lane);
+      else if (per_thread == 2) consume_rows_fast_g<2>(p, decim, full, empty, recs, stage, my_items, xw, xs, xcoef, g, gstep, groups, sel_rgb, lane);
+      else consume_rows_fast_g<4>(p, decim, full, empty, recs, stage, my_items, xw, xs, xcoef, g, gstep, groups, sel_rgb, lane);
     }
     return;
   }
@@ -617,7 +637,7 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   if (ncons > 8) ncons = 8;
   const int threads = (ncons + 1) * 32;            // + the TMA producer warp
   p.row_bytes = p.sw * p.ch;
-  p.fast_rows = (!p.has_overlay && (p.dw & 3) == 0 && groups <= ncons * 32 && !env_int("AIKO_B200_RESIZE_SLOW_ROWS", 0) &&
+  p.fast_rows = (!p.has_overlay && (p.dw & 3) == 0 && groups <= ncons * 32 * (p.ch == 1 ? 1 : 4) && !env_int("AIKO_B200_RESIZE_SLOW_ROWS", 0) &&
                  ((reinterpret_cast<uintptr_t>(p.dst) | (uintptr_t)p.dst_row_stride | (uintptr_t)p.dst_frame_stride) & 3) == 0)
                     ? 1 : 0;
   if ((p.unaligned || p.ch == 1) && !p.fast_rows) return AIKO_B200_OK;   // not staged: the generic kernel takes it

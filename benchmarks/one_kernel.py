@@ -34,6 +34,10 @@ def make(name, dev):
         if name == "flip":
             return lambda i: ops.flip(hd[i % rot], 1, out=out), 32
         return lambda i: ops.swap_rb(hd[i % rot], out=out), 32
+    if name == "uhd":                      # 4K -> 1080p, 8 frames (199 MB in, 50 MB out)
+        src = [torch.randint(0, 256, (8, 2160, 3840, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+        out = torch.empty((8, 1080, 1920, 3), dtype=torch.uint8, device=dev)
+        return lambda i: ops.resize_linear(src[i % rot], 1920, 1080, out=out), 8
     if name in ("vga", "gray"):
         shape = (256, 480, 640, 3) if name == "vga" else (32, 1080, 1920)
         size = (320, 240) if name == "vga" else (640, 480)

@@ -62,7 +62,8 @@ def test_resize_linear_unaligned_base_pointer(cuda):
 
 
 @pytest.mark.parametrize("shape", [(3, 270, 479, 160, 120), (2, 1080, 1918, 640, 480), (2, 97, 333, 84, 33),
-                                   (1, 64, 1366, 1024, 31), (2, 50, 131, 400, 20)])
+                                   (1, 64, 1366, 1024, 31), (2, 50, 131, 400, 20),
+                                   (1, 40, 3000, 1500, 20), (2, 32, 3840, 1920, 16), (1, 24, 5000, 2800, 12)])   # 2 / 4 groups per thread
 def test_resize_linear_rows_off_16_byte_boundaries_take_the_row_pipeline(cuda, shape):
     """RGB rows that are not 16-byte aligned (odd widths, odd base pointers) are staged from the
     boundary below each row; the result is the oracle's, with and without the channel swap."""
