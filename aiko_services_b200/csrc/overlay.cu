@@ -2,6 +2,8 @@
 // One CTA per image row: the row is staged in shared memory as 3-channel pixels, the
 // frame's draw list is replayed on it in order, and the row is written back.  Grayscale
 // frames take the reference's GRAY->BGR, draw, BGR->GRAY round trip (image_io.py:115,158).
+#include <stdlib.h>
+
 #include "overlay.cuh"
 
 namespace aiko {
@@ -320,6 +322,23 @@ extern "C" int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_fram
                       overlay->index_width, overlay->index_segments, overlay->index_words,
                       overlay->index_frame_words, overlay->index_height, overlay->group_records,
                       overlay->group_ctas, overlay->n_group_ctas, overlay->group_words};
+  if (channels == 3 && !getenv("AIKO_B200_OVERLAY_ROWS")) {
+    // RGB: a plain device copy (when the frames are not drawn in place), then the draw list on the
+    // touched 4-pixel groups only -- the frames cross HBM once at copy speed instead of going
+    // through a row kernel that culls the list for every row.
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (src != dst) {
+      const size_t row_bytes = (size_t)w * 3;
+      if (row_stride == (int64_t)row_bytes && frame_stride == (int64_t)row_bytes * h) {
+        AIKO_CUDA(cudaMemcpyAsync(dst, src, row_bytes * h * n_frames, cudaMemcpyDeviceToDevice, st));
+      } else {
+        for (int f = 0; f < n_frames; f++)
+          AIKO_CUDA(cudaMemcpy2DAsync(dst + (size_t)f * frame_stride, (size_t)row_stride, src + (size_t)f * frame_stride,
+                                      (size_t)row_stride, row_bytes, (size_t)h, cudaMemcpyDeviceToDevice, st));
+      }
+    }
+    return launch_overlay_tiles(dst, n_frames, h, w, row_stride, frame_stride, p.ov, st);
+  }
   const size_t smem = ((size_t)w * 3 + 15) & ~(size_t)15;
   AIKO_CHECK_ARG(smem <= (size_t)device_max_smem_optin(), "overlay: row of %zu bytes exceeds shared memory", smem);
   AIKO_CUDA(cudaFuncSetAttribute(overlay_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

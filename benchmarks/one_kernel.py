@@ -34,6 +34,17 @@ def make(name, dev):
         if name == "flip":
             return lambda i: ops.flip(hd[i % rot], 1, out=out), 32
         return lambda i: ops.swap_rb(hd[i % rot], out=out), 32
+    if name == "overlay":                  # ImageOverlay alone on 32 x 1080p frames (copy + draw)
+        from aiko_services_b200.overlay_plan import build_ops
+        from aiko_services_b200.text_atlas import TextAtlas
+        atlas = TextAtlas.shared()
+        overlay = {"rectangles": [{"x": 100 + 400 * i, "y": 150 + 180 * i, "w": 300, "h": 250} for i in range(4)],
+                   "objects": [{"name": n, "confidence": 0.9 - 0.1 * i} for i, n in enumerate(("person", "car", "dog", "bicycle"))]}
+        per_frame = [build_ops(overlay, 1920, 1080, "rgb", atlas)] * 32
+        ov = ops.DeviceOverlay.from_host(per_frame, dev, atlas.device(dev), width=1920, height=1080)
+        hd = [torch.randint(0, 256, (32, 1080, 1920, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+        out = torch.empty_like(hd[0])
+        return lambda i: ops.overlay_draw(hd[i % rot], ov, out=out), 32
     if name == "uhd":                      # 4K -> 1080p, 8 frames (199 MB in, 50 MB out)
         src = [torch.randint(0, 256, (8, 2160, 3840, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
         out = torch.empty((8, 1080, 1920, 3), dtype=torch.uint8, device=dev)
