@@ -123,8 +123,9 @@ def test_cross_stream_batching_one_launch(cuda, tmp_path):
         work.append(({"stream_id": sid, "frame_id": 0}, {"images": [frame], "overlay": overlay}))
         expect.append(reference_port.image_overlay(reference_port.image_resize([frame], "96x64"), overlay)[0])
     results = p.process_frames(work)
-    batches = {id(swag["images"][0].batch) for okay, swag in results}
-    assert len(batches) == 1                      # 12 streams -> one DeviceBatch -> one fused launch
+    batches = {id(swag["images"][0].batch): str(swag["images"][0].batch.device) for okay, swag in results}
+    # 12 streams -> one DeviceBatch -> one fused launch per GPU the streams are pinned to (one on a 1-GPU box)
+    assert len(batches) == len(set(batches.values())) <= torch.cuda.device_count()
     for (okay, swag), ref in zip(results, expect):
         assert okay
         np.testing.assert_array_equal(np.asarray(swag["images"][0]), ref)
