@@ -328,7 +328,7 @@ __device__ __forceinline__ void consume_rows_gray(const ResizeParams& p, uint64_
 // producer brings in the two source rows and, with an overlay, the frame's spatial index of its
 // draw list; `full` completes when the bytes have landed, `empty` when every consumer warp is
 // done with the slot.
-__global__ void __launch_bounds__(288) resize3_staged(const ResizeParams p) {
+__global__ void __launch_bounds__(352) resize3_staged(const ResizeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int groups = (p.dw + 3) >> 2;  // 4 output pixels per group
   const int dwp = groups * 4;
@@ -630,11 +630,13 @@ static int env_int(const char* name, int fallback) {
 static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   *done = false;
   const int groups = (p.dw + 3) / 4;
-  int ncons = (groups + 31) / 32;
-  if (ncons > 8) ncons = 8;
+  // consumer warps: one 4-pixel group per thread up to 10 warps (1280 output pixels), beyond that the
+  // fewest groups per thread, spread evenly (1920 pixels: 2 groups x 8 warps)
+  const int per_thread = (groups + 32 * 10 - 1) / (32 * 10);
+  int ncons = (groups + 32 * per_thread - 1) / (32 * per_thread);
   ncons = env_int("AIKO_B200_RESIZE_WARPS", ncons);
   if (ncons < 1) ncons = 1;
-  if (ncons > 8) ncons = 8;
+  if (ncons > 10) ncons = 10;
   const int threads = (ncons + 1) * 32;            // + the TMA producer warp
   p.row_bytes = p.sw * p.ch;
   p.fast_rows = (!p.has_overlay && (p.dw & 3) == 0 && groups <= ncons * 32 * (p.ch == 1 ? 1 : 4) && !env_int("AIKO_B200_RESIZE_SLOW_ROWS", 0) &&
