@@ -115,6 +115,7 @@ class DeviceBatch:
 
     def _run(self, t, recipe):
         i = 0
+        owned = False               # t was made by a step of this recipe: nobody else can see it, draw in place
         if self._mapped:
             first = recipe[0] if recipe else None
             direct = (first is not None and first[0] == "resize_linear" and t.dim() == 4 and
@@ -122,6 +123,7 @@ class DeviceBatch:
             if not direct:                  # everything else works on a copy in HBM
                 t = t.to(self._device, non_blocking=True)
                 self._source_read()
+                owned = True
         while i < len(recipe):
             step = recipe[i]
             kind = step[0]
@@ -147,6 +149,7 @@ class DeviceBatch:
                 else:                       # page-locked host frames, read by the kernel itself
                     t = ops.resize_linear(t, w, h, swap_rb=swap, overlay=ov, device=self._device)
                     self._source_read()
+                owned = True
                 i += used
                 continue
             if kind == "resize_bicubic":
@@ -154,7 +157,7 @@ class DeviceBatch:
             elif kind == "overlay":
                 gray = t.dim() == 3
                 h, w = t.shape[1:3]
-                t = ops.overlay_draw(t, self._overlay(step[1], w, h, gray, False, n))
+                t = ops.overlay_draw(t, self._overlay(step[1], w, h, gray, False, n), out=t if owned else None)
             elif kind == "convert":
                 code = step[1]
                 if code in ("RGB2BGR", "BGR2RGB"):
@@ -171,6 +174,7 @@ class DeviceBatch:
                 t = ops.crop(t, *step[1:])
             else:
                 raise ValueError(f"unknown step {kind}")
+            owned = True
             i += 1
         return t
 

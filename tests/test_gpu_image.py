@@ -291,6 +291,19 @@ def test_crop_vs_numpy(cuda):
 
 
 # ---------------------------------------------------------------- overlay (a-3)
+def test_overlay_in_place(cuda, atlas):
+    """src == dst: the frames are drawn where they are (no copy), RGB and gray."""
+    rng = np.random.default_rng(77)
+    for c in (3, 1):
+        frames = np.stack([cases.frame(300 + k, 120, 200, c) for k in range(3)])
+        overlay = random_overlay(rng, 200, 120)
+        ov = device_overlay([overlay] * 3, 200, 120, "rgb" if c == 3 else "bgr", atlas, cuda)
+        d = dev(frames, cuda)
+        assert ops.overlay_draw(d, ov, out=d).data_ptr() == d.data_ptr()
+        for k in range(3):
+            np.testing.assert_array_equal(host(d)[k], overlay_cpu(frames[k], overlay, atlas))
+
+
 def device_overlay(overlays, w, h, layout, atlas, cuda):
     per_frame = [build_ops(o, w, h, layout, atlas) for o in overlays]
     return ops.DeviceOverlay.from_host(per_frame, cuda, atlas.device(cuda), width=w, height=h)
