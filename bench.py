@@ -32,6 +32,7 @@ BATCH = 32
 # 960 of 1080 source rows carry weight (5,529,600 B) + 921,600 B written once
 ALGO_BYTES_PER_FRAME = 960 * SRC_W * 3 + DST_H * DST_W * 3
 FALLBACK_HBM_GBS = 6650.0
+OVERLAY_KERNEL = "overlay_groups_kernel"
 N_ROTATING_BATCHES = 4     # 4 x 199 MB of distinct inputs: each step reads a batch the 126 MB L2 cannot hold
 
 OVERLAY = {
@@ -111,59 +112,140 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- CPU reference
-def _ref_worker(args):
-    """One worker: the reference chain on `count` frames generated in-process (inputs resident)."""
-    seed, count, reps = args
+CPU_ROTATE = 4        # distinct input sets per worker, rotated like the GPU arm's batches
+CPU_ROUNDS = 3        # timed rounds of K steps each; the median round is reported
+
+
+def _ref_worker(idx, count, warmup, steps, rounds, barrier, results):
+    """One host core of the reference arm.  Its share of every 32-frame batch (``count`` frames,
+    CPU_ROTATE distinct sets) is generated BEFORE the barrier; the timed region is the reference
+    chain only, on this worker's own clock."""
     import cv2
     from oracle import reference_port
     cv2.setNumThreads(1)
-    frames = list(synthetic_batch(seed, count))
-    t0 = time.perf_counter()
-    for _ in range(reps):
-        reference_port.chain_resize_overlay_bgr(frames, f"{DST_W}x{DST_H}", OVERLAY)
-    return time.perf_counter() - t0
+    sets = [list(synthetic_batch(100_000 + 1000 * idx + r, count)) for r in range(CPU_ROTATE)]
+    resolution = f"{DST_W}x{DST_H}"
+    for i in range(max(warmup, 1)):
+        reference_port.chain_resize_overlay_bgr(sets[i % CPU_ROTATE], resolution, OVERLAY)
+    times = []
+    for _ in range(rounds):
+        barrier.wait()
+        t0 = time.perf_counter()
+        for i in range(steps):
+            reference_port.chain_resize_overlay_bgr(sets[i % CPU_ROTATE], resolution, OVERLAY)
+        times.append(time.perf_counter() - t0)
+    results.put((idx, times))
 
 
 def cpu_reference_rate(steps, warmup, frames_per_step=BATCH):
-    """frames/s of the reference's CPU path, all host cores: one process per core, each running
-    the reference elements' cv2 calls (oracle/reference_port.py) on its shard of the batch."""
+    """frames/s of the reference's CPU path on all host cores: one process per core (cv2 threads
+    = 1), each running the reference elements' cv2 calls (oracle/reference_port.py) on its shard
+    of every batch.  Inputs are resident before the clock starts; a round's time is the SLOWEST
+    worker's own perf_counter span over its K steps (process start-up, imports and frame
+    generation are outside it).  -> (frames/s of the median round, workers, s per step, rounds)"""
     import multiprocessing as mp
     cores = os.cpu_count() or 1
     workers = max(1, min(cores, frames_per_step))
     per = [frames_per_step // workers + (1 if i < frames_per_step % workers else 0) for i in range(workers)]
     ctx = mp.get_context("spawn")
-    with ctx.Pool(workers) as pool:
-        pool.map(_ref_worker, [(i, per[i], max(warmup, 1)) for i in range(workers)])      # warm-up
-        t0 = time.perf_counter()
-        pool.map(_ref_worker, [(i, per[i], steps) for i in range(workers)])
-        dt = time.perf_counter() - t0
-    return frames_per_step * steps / dt, workers, dt / steps
+    barrier, results = ctx.Barrier(workers), ctx.Queue()
+    procs = [ctx.Process(target=_ref_worker, args=(i, per[i], warmup, steps, CPU_ROUNDS, barrier, results))
+             for i in range(workers)]
+    for p in procs:
+        p.start()
+    times = {}
+    deadline = time.time() + 1800
+    while len(times) < workers:                      # never wait on a worker that died
+        try:
+            idx, t = results.get(timeout=2.0)
+            times[idx] = t
+        except Exception:
+            if any(p.exitcode not in (None, 0) for p in procs) or time.time() > deadline:
+                for p in procs:
+                    p.kill()
+                raise RuntimeError("bench.py: a CPU reference worker exited without a result")
+    for p in procs:
+        p.join()
+    round_s = sorted(max(times[i][r] for i in range(workers)) for r in range(CPU_ROUNDS))
+    dt = round_s[len(round_s) // 2]
+    return frames_per_step * steps / dt, workers, dt / steps, [frames_per_step * steps / t for t in round_s]
+
+
+def as_shipped_rate(batches=6):
+    """The reference AS SHIPPED: its own ImageResize -> ImageOverlay inside its own PipelineImpl
+    (R/main/pipeline.py:618-654,1018-1113), one Python process, cv2's default threading, driven by
+    oracle/ref_harness.py from the unmodified copy in baseline/_ref (or /root/reference).  Runs in a
+    child process; -> dict or None when the reference is not on this machine."""
+    code = ("import json,sys,time;sys.path.insert(0,%r);import numpy as np;from oracle import ref_harness as H\n"
+            "import bench,cv2\n"
+            "if not H.available():\n    print(json.dumps(None));sys.exit(0)\n"
+            "IO='aiko_services.elements.media.image_io'\n"
+            "frames=[list(bench.synthetic_batch(9000+i)) for i in range(2)]\n"
+            "b=[{'images':frames[i%%2],'overlay':bench.OVERLAY} for i in range(%d)]\n"
+            "stamps=[]\n"
+            "H.run_reference_pipeline([('ImageResize',IO,['images'],['images'],{'resolution':'%dx%d'}),"
+            "('ImageOverlay',IO,['images','overlay'],['images'],None),('ImageOutput',IO,['images'],['images'],None)],"
+            "b,timestamps=stamps)\n"
+            "n=len(stamps)-1\n"
+            "print(json.dumps({'value':bench.BATCH*n/(stamps[-1]-stamps[0]),'batches':n,"
+            "'cv2_threads':cv2.getNumThreads()}))\n") % (ROOT, batches + 1, DST_W, DST_H)
+    try:
+        out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=ROOT)
+        last = [l for l in out.stdout.splitlines() if l.startswith("{") or l == "null"]
+        return json.loads(last[-1]) if last else None
+    except Exception:
+        return None
+
+
+def cpu_baseline_objects(steps, warmup):
+    import cv2
+    rate, workers, step_s, rounds = cpu_reference_rate(steps, warmup)
+    port = {"value": rate, "unit": "frames/s", "cores": workers, "kind": "port",
+            "rounds_frames_per_s": [round(r, 1) for r in rounds],
+            "sample": f"{CPU_ROUNDS} rounds x {steps} steps x {BATCH} frames (median round; a round is timed by its "
+                      f"slowest worker's own clock, inputs resident): the reference elements' cv2 {cv2.__version__} "
+                      f"calls (oracle/reference_port.py), one process per core, cv2 threads=1"}
+    shipped = as_shipped_rate()
+    if shipped:
+        shipped = {"value": shipped["value"], "unit": "frames/s", "cores": shipped["cv2_threads"], "kind": "_ref",
+                   "sample": f"{shipped['batches']} batches x {BATCH} frames through the unmodified reference's own "
+                             f"PipelineImpl and elements (baseline/_ref), one process, cv2 default threads"}
+    return port, shipped, step_s
+
+
+def config_dict(world):
+    return {"workload": WORKLOAD, "frames_per_step_per_gpu": BATCH,
+            "l2": f"{N_ROTATING_BATCHES} rotating input batches of 199 MB each (> 126 MB L2), no flush",
+            "sharding": "independent streams per rank, no collective" if world > 1 else "single GPU"}
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import cv2
-    steps = min(args.steps, 20)
-    rate, workers, step_s = cpu_reference_rate(steps, min(args.warmup, 2))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    port, shipped, step_s = cpu_baseline_objects(args.steps, args.warmup)
     line = {
-        "impl": "reference", "metric": "1080p frames/sec through resize+convert+overlay", "value": rate,
-        "unit": "frames/s", "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 2),
+        "impl": "reference", "metric": "1080p frames/sec through resize+convert+overlay", "value": port["value"],
+        "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step": BATCH},
-        "cpu_baseline": {"value": rate, "unit": "frames/s", "cores": workers, "kind": "port",
-                         "sample": f"{steps} steps x {BATCH} frames; the reference elements' cv2 {cv2.__version__} "
-                                   f"calls (oracle/reference_port.py), one process per core, cv2 threads=1"},
-        "e2e": {"value": rate, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "dtype": "u8", "data": "synthetic", "config": config_dict(world),
+        "cpu_baseline": port,
+        "e2e": {"value": port["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if shipped:
+        line["cpu_baseline_as_shipped"] = shipped
     print(json.dumps(line), flush=True)
 
 
 # --------------------------------------------------------------------------- GPU arm
 def run_gpu_arm(args):
+    if int(os.environ.get("WORLD_SIZE", "1")) == 1 and "LOCAL_RANK" not in os.environ:
+        # --gpus 1 on a multi-GPU box: every aiko stream of the e2e leg must land on the one GPU
+        # under test (elements pin streams by crc32(stream_id) % visible devices)
+        first = os.environ.get("CUDA_VISIBLE_DEVICES", "0").split(",")[0] or "0"
+        os.environ["CUDA_VISIBLE_DEVICES"] = first
     import torch
     import torch.distributed as dist
     from aiko_services_b200 import ops
@@ -223,18 +305,47 @@ def run_gpu_arm(args):
     ms = ev0.elapsed_time(ev1)
     clocks = sampler.stop(wall0, wall1)
     # A step launches two kernels: resize3_staged (resize + swap: reads every weighted source
-    # sector and writes every output byte -- the algorithmic bytes) and overlay_groups (the draw
-    # list, in place on the L2-resident output).  The dominant kernel's own duration is measured
-    # live with the same inputs and launch configuration, overlay off.
+    # sector and writes every output byte -- the algorithmic bytes) and the overlay kernel (the draw
+    # list, in place on the L2-resident output).  The dominant kernel is timed INSIDE the real step
+    # sequence: the same two launches issued as two C-ABI calls (resize + swap, then the draw list
+    # in place -- what the fused call does internally) with an event pair around the first one.
     barrier()
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    k0.record(stream)
+    pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     for i in range(args.steps):
+        pairs[i][0].record(stream)
         ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, out=out)
-    k1.record(stream)
+        pairs[i][1].record(stream)
+        if exp_ov is not None:
+            ops.overlay_draw(out, exp_ov, out=out)
     barrier()
-    kernel_ms = k0.elapsed_time(k1) / args.steps
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in pairs]))
     step_ms = ms / args.steps
+
+    # ---- the same step with a NEW overlay every step (labels carry the confidence, so detections
+    # change the text every frame, R/elements/media/image_io.py:139): draw-list planning on the host
+    # and its upload are inside the timed region.
+    def changing_overlay(i):
+        o = {"rectangles": [dict(r, x=r["x"] + (i * 7) % 23, y=r["y"] + (i * 5) % 17) for r in OVERLAY["rectangles"]],
+             "objects": [dict(ob, confidence=0.01 + ((i * 13 + 29 * k) % 99) / 100.0)
+                         for k, ob in enumerate(OVERLAY["objects"])]}
+        return o
+
+    def changing_step(i):
+        fops = build_ops(changing_overlay(i), DST_W, DST_H, "bgr", atlas)
+        dov = ops.DeviceOverlay.from_host([fops] * BATCH, device, atlas.device(device), width=DST_W, height=DST_H)
+        ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=dov, out=out)
+        return dov
+
+    changing_steps = max(3, min(args.steps, 50))
+    keep = [changing_step(i) for i in range(3)]
+    barrier()
+    tc0 = time.perf_counter()
+    for i in range(changing_steps):
+        keep.append(changing_step(1000 + i))       # kept alive until the stream has drained
+    torch.cuda.synchronize()
+    changing_s = time.perf_counter() - tc0
+    del keep
+    barrier()
 
     # ---- end to end through the public API: the reference-facing elements on this package's
     # pipeline runtime.  Frames sit in pinned host memory (FrameStager.allocate, where a decoder
@@ -289,8 +400,8 @@ def run_gpu_arm(args):
 
     # max over ranks of the device / wall timings, sum over ranks of the frames processed
     from aiko_services_b200 import sharding
-    (ms, e2e_s), (frames_timed, frames_e2e) = sharding.combine([ms, e2e_s], [BATCH * args.steps, BATCH * e2e_steps],
-                                                               device=device)
+    (ms, e2e_s, changing_s), (frames_timed, frames_e2e, frames_changing) = sharding.combine(
+        [ms, e2e_s, changing_s], [BATCH * args.steps, BATCH * e2e_steps, BATCH * changing_steps], device=device)
 
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -299,21 +410,34 @@ def run_gpu_arm(args):
         else:
             peak, peak_src = FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
         achieved = ALGO_BYTES_PER_FRAME * BATCH / (kernel_ms * 1e-3) / 1e9
+        # DRAM traffic of the dominant kernel: from the committed ncu --set full summary of the CURRENT
+        # kernel (profiles/roofline_traffic.json names the capture it was read from), never typed in here
+        traffic, traffic_src = None, "no ncu capture on record (profiles/roofline_traffic.json missing)"
+        tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        if os.path.exists(tpath):
+            t = json.load(open(tpath))
+            traffic = int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
+            traffic_src = t["source"]
         line = {
             "metric": "1080p frames/sec through resize+convert+overlay", "value": frames_timed / (ms * 1e-3),
             "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": BATCH,
-                       "l2": f"{N_ROTATING_BATCHES} rotating input batches of 199 MB each (> 126 MB L2), no flush",
-                       "sharding": "independent streams per rank, no collective" if world > 1 else "single GPU"},
+            "dtype": "u8", "data": "synthetic", "config": config_dict(world),
+            "overlay": "static: one draw list built before the timed loop and reused by every step (the best case; "
+                       "value_changing_overlay plans and uploads a new list every step)",
+            "value_changing_overlay": {"value": frames_changing / changing_s, "unit": "frames/s",
+                                       "steps": changing_steps,
+                                       "note": "same step, a different overlay dict every step (boxes move, label "
+                                               "text changes); host planning + upload inside the timed region, wall "
+                                               "clock with a final synchronize"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": 197_457_408, "traffic_source": "ncu --set full, profiles/ncu_final_r01_summary.csv "
-                                                                   "(dram read 176.99 MB + write 20.47 MB per launch)",
+                         "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": peak_src, "kernel": "resize3_staged",
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_FRAME * BATCH, "kernel_ms": kernel_ms,
+                         "kernel_ms_how": "mean over the steps of a CUDA-event pair around the resize launch, the "
+                                          "overlay launch running between consecutive pairs (real step sequence)",
                          "step_ms": step_ms, "step_frac": ALGO_BYTES_PER_FRAME * BATCH / (step_ms * 1e-3) / 1e9 / peak,
-                         "kernels_per_step": ["resize3_staged", "overlay_groups_kernel"]},
+                         "kernels_per_step": ["resize3_staged", OVERLAY_KERNEL]},
             "e2e": {"value": frames_e2e / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                     "note": "Pipeline.process_frame over ImageResize -> ImageOverlay -> ImageConvert(RGB2BGR) -> "
@@ -323,11 +447,10 @@ def run_gpu_arm(args):
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:
-            rate, workers, _ = cpu_reference_rate(5, 1)
-            import cv2
-            line["cpu_baseline"] = {"value": rate, "unit": "frames/s", "cores": workers, "kind": "port",
-                                    "sample": f"5 steps x {BATCH} frames of the same chain via the reference "
-                                              f"elements' cv2 {cv2.__version__} calls, one process per core"}
+            port, shipped, _ = cpu_baseline_objects(args.steps, args.warmup)
+            line["cpu_baseline"] = port
+            if shipped:
+                line["cpu_baseline_as_shipped"] = shipped
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -2,7 +2,8 @@
 
 TEST INFRASTRUCTURE.  Used only by tests/golden/make_golden.py (to generate the committed
 golden vectors) and by tests that are skipped when /root/reference is absent (the GPU box).
-Nothing here is imported by the product path, bench.py or smoke().
+Nothing here is imported by the product path or smoke(); bench.py runs it only in a child
+process of its CPU legs (the "as shipped" baseline: the reference's own pipeline and elements).
 
 The reference needs six third-party modules that are not installed (paho-mqtt, avro,
 avro_validator, transitions, asciimatics, pyperclip).  They are stubbed only as deep as the
@@ -13,6 +14,7 @@ import os
 import queue
 import sys
 import threading
+import time
 import types
 
 _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -149,12 +151,13 @@ class SyntheticSource(aiko.PipelineElement):
 
 
 def run_reference_pipeline(graph_elements, batches, parameters=None, workdir="/tmp/aiko_ref_harness",
-                           timeout=120.0):
+                           timeout=120.0, timestamps=None):
     """Drive the reference's own PipelineImpl over ``batches`` (list of frame_data dicts).
 
     graph_elements: list of (element_name, module, inputs, outputs, element_parameters), in
     graph order, placed after the synthetic source.  Returns the list of frame_data_out dicts
-    the pipeline put on its queue_response, in frame order.
+    the pipeline put on its queue_response, in frame order.  ``timestamps`` (a list) receives the
+    perf_counter time at which each response arrived (the as-shipped CPU baseline of bench.py).
     """
     import json
     aiko = load_reference()
@@ -198,6 +201,8 @@ def run_reference_pipeline(graph_elements, batches, parameters=None, workdir="/t
             except queue.Empty:
                 break
             results.append(item)
+            if timestamps is not None:
+                timestamps.append(time.perf_counter())
         done.set()
         aiko.process.terminate()
 
