@@ -31,14 +31,25 @@ class OverlayOp(ctypes.Structure):
 
 
 class Overlay(ctypes.Structure):
-    _fields_ = [("ops", ctypes.c_void_p), ("op_offsets", ctypes.c_void_p),
+    _fields_ = [("ops", ctypes.c_void_p), ("op_offsets", ctypes.c_void_p), ("list_of_frame", ctypes.c_void_p),
                 ("patch_ids", ctypes.c_void_p), ("luts", ctypes.c_void_p),
-                ("patch_w", ctypes.c_int32), ("patch_h", ctypes.c_int32),
-                ("n_patches", ctypes.c_int32), ("max_ops_per_frame", ctypes.c_int32),
-                ("index", ctypes.c_void_p), ("index_width", ctypes.c_int32), ("index_segments", ctypes.c_int32),
-                ("index_words", ctypes.c_int32), ("index_frame_words", ctypes.c_int32),
-                ("index_height", ctypes.c_int32), ("group_records", ctypes.c_void_p),
-                ("group_ctas", ctypes.c_void_p), ("n_group_ctas", ctypes.c_int32), ("group_words", ctypes.c_int32)]
+                ("patch_w", ctypes.c_int32), ("patch_h", ctypes.c_int32), ("n_patches", ctypes.c_int32),
+                ("n_lists", ctypes.c_int32), ("n_frames", ctypes.c_int32), ("max_ops_per_list", ctypes.c_int32),
+                ("max_marks_per_list", ctypes.c_int32), ("max_cells_per_list", ctypes.c_int32),
+                ("frame_width", ctypes.c_int32), ("frame_height", ctypes.c_int32)]
+
+
+class OverlayPlanInfo(ctypes.Structure):
+    _fields_ = [("n_ops", ctypes.c_int32), ("max_ops_per_list", ctypes.c_int32),
+                ("max_marks_per_list", ctypes.c_int32), ("max_cells_per_list", ctypes.c_int32),
+                ("atlas_version", ctypes.c_uint64), ("atlas_epoch", ctypes.c_uint64)]
+
+
+class AtlasView(ctypes.Structure):
+    _fields_ = [("patch_ids_host", ctypes.c_void_p), ("luts_host", ctypes.c_void_p),
+                ("patch_w", ctypes.c_int32), ("patch_h", ctypes.c_int32), ("n_patches", ctypes.c_int32),
+                ("n_luts", ctypes.c_int32), ("max_patches", ctypes.c_int32), ("max_luts", ctypes.c_int32),
+                ("version", ctypes.c_uint64), ("epoch", ctypes.c_uint64)]
 
 
 _vp, _i, _i64, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t
@@ -50,6 +61,13 @@ SIGNATURES = {
     "aiko_b200_abi_version": [],
     "aiko_b200_last_error": [],
     "aiko_b200_device_info": [ctypes.c_char_p, _sz, ctypes.POINTER(_i), ctypes.POINTER(_i)],
+    "aiko_b200_overlay_plan_host": [_i, _vp, _vp, ctypes.c_char_p, _i, _i, _i, _vp, _i, _vp,
+                                    ctypes.POINTER(OverlayPlanInfo)],
+    "aiko_b200_overlay_upload": [_vp, _vp, _sz, _vp],
+    "aiko_b200_overlay_text_size_host": [ctypes.c_char_p, ctypes.POINTER(_i), ctypes.POINTER(_i)],
+    "aiko_b200_overlay_cells_host": [_vp, _i, _i, _i, ctypes.POINTER(_i), ctypes.POINTER(ctypes.c_longlong)],
+    "aiko_b200_overlay_marks_host": [_vp, _i, _i, _vp],
+    "aiko_b200_overlay_atlas_host": [ctypes.POINTER(AtlasView)],
     "aiko_b200_resize_linear_u8": [_vp, _i, _i, _i, _i, _i64, _i64, _vp, _i, _i, _i64, _i64, _i, _ovp, _vp],
     "aiko_b200_resize_bicubic_workspace_bytes": [_i, _i, _i, _i],
     "aiko_b200_resize_bicubic_prepare": [_vp, _sz, _i, _i, _i, _i, _vp],

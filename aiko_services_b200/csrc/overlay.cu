@@ -5,8 +5,11 @@
 #include <stdlib.h>
 
 #include "overlay.cuh"
+#include "overlay_marks.h"
 
 namespace aiko {
+
+static_assert(sizeof(aiko_b200_overlay) == 80 && sizeof(aiko_b200_overlay_op) == 32, "ABI layout (tests/test_abi.py)");
 
 struct OverlayParams {
   const uint8_t* src;
@@ -36,8 +39,9 @@ __global__ void __launch_bounds__(kThreads) overlay_rows_kernel(const OverlayPar
       for (int x = threadIdx.x; x < p.w; x += kThreads) row[3 * x] = row[3 * x + 1] = row[3 * x + 2] = s[x];
     }
     __syncthreads();
-    const int ob = p.ov.op_offsets[n];
-    overlay_apply_row(p.ov.ops + ob, p.ov.op_offsets[n + 1] - ob, p.ov, y, p.w, row, kThreads);
+    const int li = overlay_list(p.ov, n);
+    const int ob = p.ov.op_offsets[li];
+    overlay_apply_row(p.ov.ops + ob, p.ov.op_offsets[li + 1] - ob, p.ov, y, p.w, row, kThreads);
     __syncthreads();
     if (p.channels == 3) {
       store_row(p.dst + o, row, p.w * 3);
@@ -65,6 +69,7 @@ struct TileParams {
   int n, h, w;
   long long row_stride, frame_stride;
   int tiles_x, tiles_y;
+  int cells_per_cta;       // overlay_cells_kernel: consecutive cells of one frame handled by a CTA
   OverlayDev ov;
 };
 
@@ -149,8 +154,9 @@ __global__ void __launch_bounds__(kThreads, 6) overlay_tiles_kernel(const TilePa
   const int frame = blockIdx.x / tiles_per_frame;
   const int t = blockIdx.x - frame * tiles_per_frame;
   const int ty = t / p.tiles_x, tx = t - ty * p.tiles_x;
-  const int ob = __ldg(p.ov.op_offsets + frame);
-  const int nops = __ldg(p.ov.op_offsets + frame + 1) - ob;
+  const int li = overlay_list(p.ov, frame);
+  const int ob = __ldg(p.ov.op_offsets + li);
+  const int nops = __ldg(p.ov.op_offsets + li + 1) - ob;
   const int tile_x0 = tx * kTileW, tile_y0 = ty * kTileH;
   const int tile_x1 = min(tile_x0 + kTileW, p.w) - 1, tile_y1 = min(tile_y0 + kTileH, p.h) - 1;
   const aiko_b200_overlay_op* ops = p.ov.ops + ob;
@@ -220,59 +226,161 @@ __global__ void __launch_bounds__(kThreads, 6) overlay_tiles_kernel(const TilePa
 }
 
 // ---------------------------------------------------------------------------------------------
-// Overlay by touched groups: the host lists, per draw list, the 4-pixel groups the list can touch
-// with the ops per group (aiko_b200_overlay.group_records / group_ctas).  One thread per
-// (frame, touched group): it loads its 12 bytes, applies its ops in list order from the copy of the
-// list staged in shared memory, and stores them.  No thread idles, nothing is culled on the
-// device, and the dependent chain is record -> {pixels, glyph ids} -> transfer table -> store.
-constexpr int kGroupOps = 128;             // the host only builds group lists for lists up to this long
+// Overlay by cells: one thread per 4-pixel group that a draw list can touch, found ON THE DEVICE
+// from the 32-byte op records alone (the host ships nothing but the ops).
+//   * Each op has up to four marks (overlay_marks.h): blocks of groups it can touch.  A CTA builds
+//     the marks of its frame's list in shared memory together with two bit tables -- for every row
+//     and for every group column, the set of marks that cover it -- so "which marks cover cell
+//     (row, group)" is one AND of two bit words.
+//   * Threads enumerate the cells of all marks (prefix sums over the marks, binary search per
+//     thread).  A cell covered by several marks would be enumerated once per mark: only the thread
+//     that comes from the FIRST covering mark owns it, the others leave.  The owner applies the
+//     ops of all covering marks in list order to its 12 bytes, held in registers, and stores them
+//     once; ownership makes synchronisation between ops unnecessary.
+// A CTA handles kCellsPerCta consecutive cells of one frame (blockIdx.y); the grid's x extent
+// comes from the host's upper bound on cells per list.
+constexpr int kCellsPerCta = 256;           // default: one cell per thread (measured: see DESIGN.md)
+constexpr int kCellOps = 256;              // the cell kernel takes lists of up to this many ops and marks
 
-__global__ void __launch_bounds__(kThreads) overlay_groups_kernel(const TileParams p) {
-  __shared__ int4 sops[kGroupOps * 2];
-  const uint4 cta = __ldg(reinterpret_cast<const uint4*>(p.ov.group_ctas) + blockIdx.x);
-  const int first = (int)cta.x, count = (int)cta.y, frame = (int)cta.z;
-  const int ob = (int)(cta.w & 0xffffffu), nops = (int)(cta.w >> 24);
-  const int rec_words = 1 + p.ov.group_words;
-  // this thread's group record (issued before the list is staged, so both fetches overlap)
-  uint32_t yx = 0, m[4] = {0, 0, 0, 0};
-  if ((int)threadIdx.x < count) {
-    const uint32_t* rec = p.ov.group_records + (size_t)(first + threadIdx.x) * rec_words;
-    yx = __ldg(rec);
+__device__ __forceinline__ int block_scan_exclusive(int v, int* warp_sums, int* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = v;
 #pragma unroll
-    for (int w = 0; w < 4; w++)            // (unrolled: the masks stay in registers)
-      if (w < p.ov.group_words) m[w] = __ldg(rec + 1 + w);
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
   }
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  int before = 0, all = 0;
+#pragma unroll
+  for (int w = 0; w < kThreads / 32; w++) {
+    const int s = warp_sums[w];
+    if (w < warp) before += s;
+    all += s;
+  }
+  __syncthreads();                          // warp_sums may be reused right away
+  *total = all;
+  return before + incl - v;
+}
+
+template <int MW>                           // mask words: lists of up to 32 * MW marks
+__global__ void __launch_bounds__(kThreads) overlay_cells_kernel(const TileParams p, int ops_cap) {
+  extern __shared__ __align__(16) uint8_t cell_smem[];
+  __shared__ int warp_sums[kThreads / 32];
+  constexpr int kMarks = 32 * MW;
+  const int G = (p.w + 3) >> 2;
+  int4* sops = reinterpret_cast<int4*>(cell_smem);                               // [2 * ops_cap]
+  OverlayMark* marks = reinterpret_cast<OverlayMark*>(sops + 2 * ops_cap);       // [kMarks]
+  int* prefix = reinterpret_cast<int*>(marks + kMarks);                          // [kMarks + 1]
+  uint32_t* rowmask = reinterpret_cast<uint32_t*>(prefix + kMarks + 1);          // [h][MW]
+  uint32_t* gmask = rowmask + (size_t)p.h * MW;                                  // [G][MW]
+  unsigned short* mark_op = reinterpret_cast<unsigned short*>(gmask + (size_t)G * MW);   // [kMarks]
+
+  const int frame = blockIdx.y;
+  const int li = overlay_list(p.ov, frame);
+  const int ob = __ldg(p.ov.op_offsets + li);
+  const int nops = __ldg(p.ov.op_offsets + li + 1) - ob;
+  if (nops <= 0 || nops > ops_cap || nops > kThreads) return;     // (longer lists: the host picks the tile kernel)
   const int4* src = reinterpret_cast<const int4*>(p.ov.ops + ob);
   for (int i = threadIdx.x; i < nops * 2; i += kThreads) sops[i] = __ldg(src + i);
-  const int y = (int)(yx >> 16), mlo = (int)(yx & 0xffff) * 4, mhi = min(mlo + 3, p.w - 1);
-  uint8_t* pix = p.frames + (long long)frame * p.frame_stride + (long long)y * p.row_stride + (long long)mlo * 3;
-  const bool active = (int)threadIdx.x < count;
-  const bool words = active && mlo + 3 < p.w && ((reinterpret_cast<uintptr_t>(pix) & 3) == 0);
-  Pixels4 px{0, 0, 0};
-  if (active) px = load_pixels(pix, words, mhi - mlo + 1);
-  __syncthreads();
-  if (!active) return;
-  const int psize = p.ov.patch_w * p.ov.patch_h;
-  bool dirty = false;
+  for (int i = threadIdx.x; i < (p.h + G) * MW; i += kThreads) rowmask[i] = 0;
+  // marks of op threadIdx.x (same registers as the staged copy: no barrier needed yet)
+  OverlayMarks4 mine;
+  mine.valid = 0;
+  if ((int)threadIdx.x < nops) {
+    const int4 lo4 = __ldg(src + 2 * threadIdx.x);
+    const int y1 = __ldg(&p.ov.ops[ob + threadIdx.x].y1);
+    mine = overlay_op_marks4(lo4.x, lo4.y, lo4.z, lo4.w, y1, p.w, p.h);
+  }
+  const int nmine = __popc(mine.valid);
+  int nmarks;
+  const int mfirst = block_scan_exclusive(nmine, warp_sums, &nmarks);
+  if (nmarks > kMarks) return;                                     // uniform: the host's mark bound was wrong
+  {
+    int at = mfirst;
 #pragma unroll
-  for (int w = 0; w < 4; w++) {
-    uint32_t bits = m[w];               // zero beyond group_words
-    while (bits) {
-      const int b = __ffs(bits) - 1;
-      bits &= bits - 1;
-      dirty |= apply_op_regs(sops[2 * (w * 32 + b)], sops[2 * (w * 32 + b) + 1], p.ov, psize, y, mlo, mhi, px);
+    for (int k = 0; k < kMaxMarksPerOp; k++)
+      if (mine.valid >> k & 1) {
+        marks[at] = mine.m[k];
+        mark_op[at] = (unsigned short)threadIdx.x;
+        at++;
+      }
+  }
+  __syncthreads();
+  // bit tables: warps take marks round-robin, lanes stride over the mark's rows, then its groups
+  for (int m = threadIdx.x >> 5; m < nmarks; m += kThreads / 32) {
+    const OverlayMark mk = marks[m];
+    const uint32_t bit = 1u << (m & 31);
+    const int wd = m >> 5;
+    for (int r = mk.y0 + (threadIdx.x & 31); r <= mk.y1; r += 32) atomicOr(&rowmask[r * MW + wd], bit);
+    for (int g = mk.g0 + (threadIdx.x & 31); g <= mk.g1; g += 32) atomicOr(&gmask[g * MW + wd], bit);
+  }
+  int total;
+  {
+    const int cells = ((int)threadIdx.x < nmarks) ? overlay_mark_cells(marks[threadIdx.x]) : 0;
+    const int before = block_scan_exclusive(cells, warp_sums, &total);      // (its barriers also publish the bit tables)
+    if ((int)threadIdx.x < nmarks) prefix[threadIdx.x] = before;
+    if (threadIdx.x == 0) prefix[nmarks] = total;
+  }
+  __syncthreads();
+  const int cell_end = min(total, (int)(blockIdx.x + 1) * p.cells_per_cta);
+  const int psize = p.ov.patch_w * p.ov.patch_h;
+  for (int c = blockIdx.x * p.cells_per_cta + threadIdx.x; c < cell_end; c += kThreads) {
+    int lo = 0, hi = nmarks - 1;                        // last mark whose first cell is <= c
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (prefix[mid] <= c) lo = mid; else hi = mid - 1;
+    }
+    const OverlayMark mk = marks[lo];
+    const int local = c - prefix[lo], ng = mk.g1 - mk.g0 + 1;
+    const int r = local / ng;
+    const int g = mk.g0 + (local - r * ng), y = mk.y0 + r;
+    uint32_t cover[MW];
+    int firstmark = -1;
+#pragma unroll
+    for (int w = MW - 1; w >= 0; w--) {
+      cover[w] = rowmask[y * MW + w] & gmask[g * MW + w];
+      if (cover[w]) firstmark = w * 32 + __ffs(cover[w]) - 1;
+    }
+    if (firstmark != lo) continue;                       // another thread owns this cell
+    const int mlo = g * 4, mhi = min(mlo + 3, p.w - 1);
+    uint8_t* pix = p.frames + (long long)frame * p.frame_stride + (long long)y * p.row_stride + (long long)mlo * 3;
+    const bool words = mlo + 3 < p.w && ((reinterpret_cast<uintptr_t>(pix) & 3) == 0);
+    Pixels4 px = load_pixels(pix, words, mhi - mlo + 1);
+    bool dirty = false;
+    int last_op = -1;
+#pragma unroll
+    for (int w = 0; w < MW; w++) {
+      uint32_t bits = cover[w];
+      while (bits) {
+        const int b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int op = mark_op[w * 32 + b];
+        if (op == last_op) continue;                     // two marks of one op
+        last_op = op;
+        dirty |= apply_op_regs(sops[2 * op], sops[2 * op + 1], p.ov, psize, y, mlo, mhi, px);
+      }
+    }
+    if (dirty) {
+      if (words) {
+        reinterpret_cast<uint32_t*>(pix)[0] = px.w0;
+        reinterpret_cast<uint32_t*>(pix)[1] = px.w1;
+        reinterpret_cast<uint32_t*>(pix)[2] = px.w2;
+      } else {
+        const uint32_t v[3] = {px.w0, px.w1, px.w2};
+        for (int q = 0; q < (mhi - mlo + 1) * 3; q++) pix[q] = (uint8_t)(v[q >> 2] >> (8 * (q & 3)));
+      }
     }
   }
-  if (dirty) {
-    if (words) {
-      reinterpret_cast<uint32_t*>(pix)[0] = px.w0;
-      reinterpret_cast<uint32_t*>(pix)[1] = px.w1;
-      reinterpret_cast<uint32_t*>(pix)[2] = px.w2;
-    } else {
-      const uint32_t v[3] = {px.w0, px.w1, px.w2};
-      for (int q = 0; q < (mhi - mlo + 1) * 3; q++) pix[q] = (uint8_t)(v[q >> 2] >> (8 * (q & 3)));
-    }
-  }
+}
+
+template <int MW>
+static int launch_cells(const TileParams& p, int ops_cap, size_t smem, dim3 grid, cudaStream_t stream) {
+  if (smem > 48 * 1024)
+    AIKO_CUDA(cudaFuncSetAttribute(overlay_cells_kernel<MW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  overlay_cells_kernel<MW><<<grid, kThreads, smem, stream>>>(p, ops_cap);
+  return cuda_status(cudaGetLastError(), "overlay_cells launch");
 }
 
 // frames: uint8 [n, h, w, 3] with the given strides, modified in place
@@ -283,12 +391,26 @@ int launch_overlay_tiles(uint8_t* frames, int n, int h, int w, long long row_str
   p.tiles_x = (w + kTileW - 1) / kTileW;
   p.tiles_y = (h + kTileH - 1) / kTileH;
   p.ov = ov;
-  const bool grouped = ov.group_records != nullptr && ov.group_ctas != nullptr && ov.index_width == w &&
-                       ov.index_height == h && ov.group_words >= 1 && ov.group_words <= 4;
-  if (grouped) {
-    if (ov.n_group_ctas == 0) return AIKO_B200_OK;       // nothing is drawn
-    overlay_groups_kernel<<<(unsigned)ov.n_group_ctas, kThreads, 0, stream>>>(p);
-    return cuda_status(cudaGetLastError(), "overlay_groups launch");
+  const int G = (w + 3) >> 2;
+  if (ov.max_cells > 0 && ov.max_marks > 0 && ov.max_marks <= kCellOps && ov.max_ops > 0 && ov.max_ops <= kCellOps &&
+      ov.frame_w == w && ov.frame_h == h && h <= kMarkLimit && G <= kMarkLimit && n <= 65535 &&
+      !getenv("AIKO_B200_OVERLAY_TILES")) {
+    const int mw = ov.max_marks <= 32 ? 1 : ov.max_marks <= 64 ? 2 : ov.max_marks <= 128 ? 4 : 8;
+    const int ops_cap = (ov.max_ops + 3) & ~3;
+    const size_t smem = (size_t)ops_cap * 32 + (size_t)mw * 32 * sizeof(OverlayMark) + ((size_t)mw * 32 + 1) * 4 +
+                        (size_t)(h + G) * mw * 4 + (size_t)mw * 32 * 2 + 16;
+    if (smem <= (size_t)device_max_smem_optin()) {
+      int per_cta = kCellsPerCta;
+      if (const char* e = getenv("AIKO_B200_OVERLAY_CELLS_PER_CTA")) per_cta = atoi(e) >= kThreads ? atoi(e) / kThreads * kThreads : kCellsPerCta;
+      p.cells_per_cta = per_cta;
+      const dim3 grid((unsigned)((ov.max_cells + per_cta - 1) / per_cta), (unsigned)n);
+      switch (mw) {
+        case 1: return launch_cells<1>(p, ops_cap, smem, grid, stream);
+        case 2: return launch_cells<2>(p, ops_cap, smem, grid, stream);
+        case 4: return launch_cells<4>(p, ops_cap, smem, grid, stream);
+        default: return launch_cells<8>(p, ops_cap, smem, grid, stream);
+      }
+    }
   }
   const long long grid = (long long)n * p.tiles_x * p.tiles_y;
   if (grid >= ((long long)1 << 31)) {
@@ -301,9 +423,27 @@ int launch_overlay_tiles(uint8_t* frames, int n, int h, int w, long long row_str
   return cuda_status(cudaGetLastError(), "overlay_tiles launch");
 }
 
+int overlay_from_abi(const aiko_b200_overlay* o, int n_frames, OverlayDev* out) {
+  AIKO_CHECK_ARG(o && o->ops && o->op_offsets, "overlay: missing draw list (ops / op_offsets)");
+  AIKO_CHECK_ARG(o->n_frames >= n_frames, "overlay: draw list made for %d frames, call has %d", o->n_frames, n_frames);
+  AIKO_CHECK_ARG(o->list_of_frame || o->n_lists >= n_frames, "overlay: %d lists for %d frames and no list_of_frame",
+                 o->n_lists, n_frames);
+  AIKO_CHECK_ARG(o->patch_w >= 0 && o->patch_h >= 0, "overlay: bad patch size");
+  *out = OverlayDev{o->ops, o->op_offsets, o->list_of_frame, o->patch_ids, o->luts, o->patch_w, o->patch_h,
+                    o->max_ops_per_list, o->max_marks_per_list, o->max_cells_per_list, o->frame_width, o->frame_height};
+  return AIKO_B200_OK;
+}
+
 }  // namespace aiko
 
 using namespace aiko;
+
+extern "C" int aiko_b200_overlay_upload(void* plan_dev, const void* plan_host, size_t bytes, void* stream) {
+  if (bytes == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(plan_dev && plan_host, "overlay_upload: null pointer");
+  AIKO_CUDA(cudaMemcpyAsync(plan_dev, plan_host, bytes, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+  return AIKO_B200_OK;
+}
 
 extern "C" int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_frames, int h, int w, int channels,
                                     int64_t row_stride, int64_t frame_stride, const aiko_b200_overlay* overlay,
@@ -312,16 +452,14 @@ extern "C" int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_fram
   if (n_frames == 0 || h == 0 || w == 0) return AIKO_B200_OK;
   AIKO_CHECK_ARG(src && dst, "overlay: null frame pointer");
   AIKO_CHECK_ARG(channels == 1 || channels == 3, "overlay: channels %d not in {1,3}", channels);
-  AIKO_CHECK_ARG(overlay && overlay->ops && overlay->op_offsets, "overlay: missing draw list");
   AIKO_CHECK_ARG(row_stride >= (int64_t)w * channels, "overlay: row stride smaller than a row");
   OverlayParams p{};
   p.src = src; p.dst = dst; p.n = n_frames; p.h = h; p.w = w; p.channels = channels;
   p.row_stride = row_stride; p.frame_stride = frame_stride;
-  p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
-                    overlay->patch_h, overlay->max_ops_per_frame, overlay->index,
-                      overlay->index_width, overlay->index_segments, overlay->index_words,
-                      overlay->index_frame_words, overlay->index_height, overlay->group_records,
-                      overlay->group_ctas, overlay->n_group_ctas, overlay->group_words};
+  {
+    const int rc = overlay_from_abi(overlay, n_frames, &p.ov);
+    if (rc != AIKO_B200_OK) return rc;
+  }
   if (channels == 3 && !getenv("AIKO_B200_OVERLAY_ROWS")) {
     // RGB: a plain device copy (when the frames are not drawn in place), then the draw list on the
     // touched 4-pixel groups only -- the frames cross HBM once at copy speed instead of going

@@ -10,17 +10,21 @@ namespace aiko {
 struct OverlayDev {
   const aiko_b200_overlay_op* ops;
   const int32_t* op_offsets;
+  const int32_t* list_of_frame;   // or null: frame f uses list f
   const uint16_t* patch_ids;
   const uint8_t* luts;
   int patch_w, patch_h;
-  int max_ops;   // host hint: largest per-frame op count (0 = unknown)
-  const uint32_t* index;   // optional spatial index (include/aiko_b200.h), or null
-  int index_width, index_segments, index_words, index_frame_words;
-  int index_height;
-  const uint32_t* group_records;   // optional list of touched 4-pixel groups (include/aiko_b200.h), or null
-  const uint32_t* group_ctas;
-  int n_group_ctas, group_words;
+  int max_ops;     // host hints (include/aiko_b200.h): largest per-list op / mark / cell counts, 0 = unknown
+  int max_marks, max_cells;
+  int frame_w, frame_h;           // frame size max_marks / max_cells were computed for
 };
+
+// Checks an overlay given through the C ABI against the call's frame count and copies it.
+int overlay_from_abi(const aiko_b200_overlay* overlay, int n_frames, OverlayDev* out);
+
+__device__ __forceinline__ int overlay_list(const OverlayDev& ov, int frame) {
+  return ov.list_of_frame ? __ldg(ov.list_of_frame + frame) : frame;
+}
 
 // cv2.rectangle(.., thickness=2) coverage, closed form.
 __device__ __forceinline__ bool rect_covers(int x, int y, int xa, int ya, int xb, int yb) {

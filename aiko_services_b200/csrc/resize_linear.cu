@@ -31,8 +31,6 @@ struct ResizeParams {
   OverlayDev ov;
   int stages, seg_stride, row_bytes;
   int items, items_per_cta;
-  int index_words_per_frame;   // uint32 words of the overlay's spatial index staged per ring slot (0: none)
-  int ops_cap;                 // draw-list entries staged per ring slot next to the index (0: read from global)
   int wait_ns[4];              // producer wait: suspend hint, back-off; consumer wait: suspend hint, back-off
   int fast_rows;               // no draw list in the row loop, whole 4-pixel groups, 4-byte aligned output rows
   int evict_first;             // source rows are read once: keep them from displacing other data in L2
@@ -325,9 +323,8 @@ __device__ __forceinline__ void consume_rows_gray(const ResizeParams& p, uint64_
 }
 
 // Warp roles: warps [0, ncons) consume rows; warp ncons is the TMA producer.  Per ring slot the
-// producer brings in the two source rows and, with an overlay, the frame's spatial index of its
-// draw list; `full` completes when the bytes have landed, `empty` when every consumer warp is
-// done with the slot.
+// producer brings in the two source rows; `full` completes when the bytes have landed, `empty`
+// when every consumer warp is done with the slot.
 __global__ void __launch_bounds__(352) resize3_staged(const ResizeParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int groups = (p.dw + 3) >> 2;  // 4 output pixels per group
@@ -343,10 +340,6 @@ __global__ void __launch_bounds__(352) resize3_staged(const ResizeParams p) {
   off += 128;
   int* recs = reinterpret_cast<int*>(smem + off);  // per slot: n, dy, b0, b1, first op, op count, -, -
   off += (size_t)p.stages * p.rows_per_slot * kRecHeader * 4;
-  uint32_t* idxring = reinterpret_cast<uint32_t*>(smem + off);          // per slot: the frame's index block
-  off += (size_t)p.stages * p.index_words_per_frame * 4;
-  aiko_b200_overlay_op* opsring = reinterpret_cast<aiko_b200_overlay_op*>(smem + off);   // ... and its draw list
-  off += (size_t)p.stages * p.ops_cap * sizeof(aiko_b200_overlay_op);
   uint8_t* stage = smem + off;
 
   const int ncons = (int)blockDim.x / 32 - 1;
@@ -386,7 +379,7 @@ __global__ void __launch_bounds__(352) resize3_staged(const ResizeParams p) {
     ri.start(blockIdx.x * chunk, p.items, chunk, p.dh);
     rn = ri;
     int ob = 0, oe = 0, ob_next = 0, oe_next = 0;
-    if (p.has_overlay) { ob = __ldg(p.ov.op_offsets + ri.n); oe = __ldg(p.ov.op_offsets + ri.n + 1); }
+    if (p.has_overlay) { const int li = overlay_list(p.ov, ri.n); ob = __ldg(p.ov.op_offsets + li); oe = __ldg(p.ov.op_offsets + li + 1); }
     int slot = 0, round = 0, sub = 0;               // a slot takes rows_per_slot consecutive rows (1 unless rows are short)
     uint32_t slot_bytes = 0;
     const int R = p.rows_per_slot;
@@ -410,28 +403,18 @@ __global__ void __launch_bounds__(352) resize3_staged(const ResizeParams p) {
         bulk_g2s(s0 + p.seg_stride, a1 - d1, n1, &full[slot]);
       }
       const int nops = oe - ob;
-      uint32_t idx_bytes = 0;
-      if (p.index_words_per_frame > 0 && nops > 0) {
-        idx_bytes = (uint32_t)p.index_words_per_frame * 4u;
-        bulk_g2s(idxring + (size_t)slot * p.index_words_per_frame,
-                 p.ov.index + (size_t)ri.n * p.ov.index_frame_words, idx_bytes, &full[slot]);
-        if (nops <= p.ops_cap) {
-          const uint32_t ops_bytes = (uint32_t)nops * (uint32_t)sizeof(aiko_b200_overlay_op);
-          bulk_g2s(opsring + (size_t)slot * p.ops_cap, p.ov.ops + ob, ops_bytes, &full[slot]);
-          idx_bytes += ops_bytes;
-        }
-      }
       if (p.has_overlay && it + 1 < my_items) {    // next row's offsets: in flight while this row is consumed
         rn.next(p.items, chunk, stride_items, p.dh);
-        ob_next = __ldg(p.ov.op_offsets + rn.n);
-        oe_next = __ldg(p.ov.op_offsets + rn.n + 1);
+        const int li = overlay_list(p.ov, rn.n);
+        ob_next = __ldg(p.ov.op_offsets + li);
+        oe_next = __ldg(p.ov.op_offsets + li + 1);
       }
       int* rec = recs + (slot * R + sub) * kRecHeader;
       *reinterpret_cast<int4*>(rec) = make_int4(ri.n, ri.dy, rc.b0, rc.b1);
       rec[4] = p.unaligned ? (int)d0 : ob;          // (unaligned rows never carry a draw list in the row loop)
       rec[5] = p.unaligned ? (int)d1 : nops;
       *reinterpret_cast<uint8_t**>(rec + 6) = p.dst + (long long)ri.n * p.dst_frame_stride + (long long)ri.dy * p.dst_row_stride;
-      slot_bytes += n0 + n1 + idx_bytes;
+      slot_bytes += n0 + n1;
       ri.next(p.items, chunk, stride_items, p.dh);
       ob = ob_next; oe = oe_next;
       if (++sub == R || it + 1 == my_items) {       // the slot is complete: one arrival for all its bytes
@@ -447,7 +430,6 @@ __global__ void __launch_bounds__(352) resize3_staged(const ResizeParams p) {
   // ---- consumers: each warp produces, overlays and stores its own 128-pixel segments --------
   const int row_bytes_out = p.dw * 3;
   const uint32_t sel_rgb = p.swap_rb ? 0x7014u : 0x7410u;   // (c0 c1 . .),(c2) -> c0 c1 c2 0 | c2 c1 c0 0
-  const int nseg = p.ov.index_segments, nw = p.ov.index_words;
   if (p.fast_rows) {
     const int g = warp * 32 + lane;
     const bool on = g < groups;
@@ -477,37 +459,7 @@ __global__ void __launch_bounds__(352) resize3_staged(const ResizeParams p) {
     __syncwarp();
     if (p.has_overlay) {
       const int ob = rec[4], nops = rec[5];
-      if (nops > 0 && p.index_words_per_frame == 0) {        // no index from the host: cull here
-        overlay_apply_row(p.ov.ops + ob, nops, p.ov, hdr.y, p.dw, orow, ncons * 32);
-      } else if (nops > 0) {
-        const uint32_t* idx = idxring + (size_t)slot * p.index_words_per_frame;
-        const uint32_t* yinfo = idx + 2 * nseg * nw * 32;
-        const aiko_b200_overlay_op* fops = (nops <= p.ops_cap) ? opsring + (size_t)slot * p.ops_cap : p.ov.ops + ob;
-        const int y = hdr.y;
-        for (int wi = 0; wi < nw; wi++) {
-          // which of these 32 ops touch this row, and which rectangles are in their band rows
-          const uint2 yi = reinterpret_cast<const uint2*>(yinfo)[wi * 32 + lane];
-          const int first = (int)(short)(yi.x & 0xffff), last = (int)(short)(yi.x >> 16);
-          const int band0 = (int)(short)(yi.y & 0xffff), band1 = (int)(short)(yi.y >> 16);
-          const uint32_t rowmask = __ballot_sync(0xffffffffu, y >= first && y <= last);
-          if (rowmask == 0) continue;
-          const uint32_t bandmask = __ballot_sync(0xffffffffu, y <= band0 || y >= band1);
-          for (int gbase = warp * 32; gbase < groups; gbase += ncons * 32) {
-            const int seg = gbase >> 5;
-            const int mlo = (gbase + lane) * 4, mhi = min(mlo + 3, p.dw - 1);
-            const uint32_t side = idx[(seg * nw + wi) * 32 + lane];
-            const uint32_t band = idx[((nseg + seg) * nw + wi) * 32 + lane];
-            uint32_t rem = rowmask & ((side & ~bandmask) | (band & bandmask));
-            while (__any_sync(0xffffffffu, rem != 0)) {   // lanes apply their own (different) entries together
-              if (rem) {
-                const int b = __ffs(rem) - 1;
-                rem &= rem - 1;
-                apply_op_to_pixels(fops + wi * 32 + b, p.ov, y, mlo, mhi, orow);
-              }
-            }
-          }
-        }
-      }
+      if (nops > 0) overlay_apply_row(p.ov.ops + ob, nops, p.ov, hdr.y, p.dw, orow, ncons * 32);
       __syncwarp();
     }
     uint8_t* drow = p.dst + (long long)hdr.x * p.dst_frame_stride + (long long)hdr.y * p.dst_row_stride;
@@ -523,7 +475,7 @@ __global__ void __launch_bounds__(352) resize3_staged(const ResizeParams p) {
       }
     }
     __syncwarp();                                  // the segment is rewritten by the next row
-    if (lane == 0) mbar_arrive(&empty[slot]);      // rows, record and index of this slot are free again
+    if (lane == 0) mbar_arrive(&empty[slot]);      // rows and records of this slot are free again
     if (++slot == p.stages) { slot = 0; ++round; }
   }
 }
@@ -609,8 +561,9 @@ __global__ void __launch_bounds__(kThreads) resize_rows_generic(const ResizePara
     if (C == 3 && p.has_overlay) {
       for (int j = 0; j < nrows; j++) {
         const int n = s_where[j].x;
-        const int ob = p.ov.op_offsets[n];
-        overlay_apply_row(p.ov.ops + ob, p.ov.op_offsets[n + 1] - ob, p.ov, s_where[j].y, p.dw, orows + j * row_pitch,
+        const int li = overlay_list(p.ov, n);
+        const int ob = p.ov.op_offsets[li];
+        overlay_apply_row(p.ov.ops + ob, p.ov.op_offsets[li + 1] - ob, p.ov, s_where[j].y, p.dw, orows + j * row_pitch,
                           kThreads);
       }
       __syncthreads();
@@ -644,15 +597,6 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
                     ? 1 : 0;
   if ((p.unaligned || p.ch == 1) && !p.fast_rows) return AIKO_B200_OK;   // not staged: the generic kernel takes it
   p.seg_stride = ((p.row_bytes + 15) & ~15) + 32;  // room for the 16-byte rounding at both ends; tap reads may run a few bytes past the row end
-  // the host-built index is usable when it was made for this output width
-  const bool indexed = p.has_overlay && p.ov.index != nullptr && p.ov.index_width == p.dw &&
-                       p.ov.index_segments == (groups + 31) / 32 && p.ov.index_words > 0 &&
-                       p.ov.index_frame_words == 2 * p.ov.index_segments * p.ov.index_words * 32 + p.ov.index_words * 64;
-  p.index_words_per_frame = indexed ? p.ov.index_frame_words : 0;
-  // Staging the op records next to the index was measured slower (more shared memory per CTA, fewer
-  // CTAs per SM) than letting hit lanes fetch their record through L2: off unless asked for.
-  p.ops_cap = (env_int("AIKO_B200_RESIZE_STAGE_OPS", 0) && indexed && p.ov.max_ops > 0 &&
-               p.ov.max_ops <= 32 * p.ov.index_words) ? p.ov.max_ops : 0;
   const size_t fixed = (size_t)groups * 48 + (((size_t)groups * 12 + 15) & ~(size_t)15) + 128;
   // Short rows (gray, small frames): several output rows share a ring slot, so the hand-off between
   // producer and consumers (one barrier round trip, ~1 us) is paid once per ~12 KB and not per row.
@@ -663,8 +607,7 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
     p.rows_per_slot = r < 1 ? 1 : (r > 8 ? 8 : r);
   }
   auto need = [&](int st) {
-    return fixed + (size_t)st * ((size_t)p.rows_per_slot * kRecHeader * 4 + (size_t)p.index_words_per_frame * 4 +
-                                 (size_t)p.ops_cap * sizeof(aiko_b200_overlay_op) +
+    return fixed + (size_t)st * ((size_t)p.rows_per_slot * kRecHeader * 4 +
                                  (size_t)p.rows_per_slot * 2 * (size_t)p.seg_stride);
   };
   // Measured on 32 x 1080p (us per launch; CTAs per SM x ring stages): 6x2 37.8, 5x2 35.5, 4x3 37.5, 5x3 39.5,
@@ -761,12 +704,8 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
   p.swap_rb = swap_rb ? 1 : 0;
   p.has_overlay = overlay ? 1 : 0;
   if (overlay) {
-    AIKO_CHECK_ARG(overlay->ops && overlay->op_offsets, "resize_linear: overlay without ops/op_offsets");
-    p.ov = OverlayDev{overlay->ops, overlay->op_offsets, overlay->patch_ids, overlay->luts, overlay->patch_w,
-                      overlay->patch_h, overlay->max_ops_per_frame, overlay->index,
-                      overlay->index_width, overlay->index_segments, overlay->index_words,
-                      overlay->index_frame_words, overlay->index_height, overlay->group_records,
-                      overlay->group_ctas, overlay->n_group_ctas, overlay->group_words};
+    const int rc = overlay_from_abi(overlay, n_frames, &p.ov);
+    if (rc != AIKO_B200_OK) return rc;
   }
   p.items = n_frames * dst_h;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

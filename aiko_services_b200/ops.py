@@ -5,8 +5,8 @@ torch is used here for device memory and streams only (``tensor.data_ptr()``,
 mirrors the library call the reference element makes (cited in include/aiko_b200.h) but
 takes a whole batch ``uint8[N, H, W, C]`` (or ``[N, H, W]`` for grayscale) resident on the GPU.
 """
+import contextlib
 import ctypes
-import os
 
 import numpy as np
 import torch
@@ -48,179 +48,131 @@ def _out(out, shape, device, name, dtype=torch.uint8):
     return out
 
 
-INDEX_MAX_OPS = 128      # frames with longer draw lists are culled on the device instead
-
-
-def build_overlay_index(ops_per_frame, width):
-    """Spatial index of a draw list for frames ``width`` pixels wide (layout: include/aiko_b200.h).
-    -> (uint32 ndarray [frames, frame_words], segments, words) or None when a list is too long."""
-    most = max((len(o) for o in ops_per_frame), default=0)
-    if most == 0 or most > INDEX_MAX_OPS:
-        return None
-    words = (most + 31) // 32
-    segments = ((width + 3) // 4 + 31) // 32
-    lane_lo = (np.arange(segments)[:, None] * 128 + np.arange(32)[None, :] * 4)          # [seg, lane]
-    lane_hi = lane_lo + 3
-    frame_words = 2 * segments * words * 32 + words * 32 * 2
-    out = np.zeros((len(ops_per_frame), frame_words), np.uint32)
-    cache = {}
-    for f, frame_ops in enumerate(ops_per_frame):
-        key = id(frame_ops)
-        if key in cache:                     # the same list object for many frames (one overlay per batch)
-            out[f] = out[cache[key]]
-            continue
-        cache[key] = f
-        n = len(frame_ops)
-        if n == 0:
-            continue
-        kind = np.array([o.kind for o in frame_ops])
-        x0 = np.array([o.x0 for o in frame_ops]); x1 = np.array([o.x1 for o in frame_ops])
-        y0 = np.array([o.y0 for o in frame_ops]); y1 = np.array([o.y1 for o in frame_ops])
-        rect = kind == 0
-        grow = rect.astype(np.int64)
-        # side variant: two intervals A, B (equal for glyphs); band variant: the whole span
-        a0 = x0 - grow; a1 = np.where(rect, x0 + 1, x1); b0 = np.where(rect, x1 - 1, x0); b1 = x1 + grow
-        full0, full1 = x0 - grow, x1 + grow
-
-        def touches(lo, hi):                 # [op, seg, lane]
-            return (lo[:, None, None] <= lane_hi[None]) & (hi[:, None, None] >= lane_lo[None])
-
-        side = touches(a0, a1) | touches(b0, b1)
-        band = touches(full0, full1)
-        xm = np.zeros((2, segments, words, 32), np.uint32)
-        for b in range(n):
-            w, bit = divmod(b, 32)
-            xm[0, :, w, :] |= (side[b].astype(np.uint32) << np.uint32(bit))
-            xm[1, :, w, :] |= (band[b].astype(np.uint32) << np.uint32(bit))
-        clip = lambda v: np.clip(v, -32768, 32767).astype(np.int64) & 0xffff
-        yinfo = np.zeros((words * 32, 2), np.uint32)
-        yinfo[:, 0] = 1                      # unused slots: first_row 1 > last_row 0 -> never hit
-        yinfo[:n, 0] = (clip(y0 - grow) | (clip(y1 + grow) << 16)).astype(np.uint32)
-        yb0 = np.where(rect, y0 + 1, 32767); yb1 = np.where(rect, y1 - 1, -32768)
-        yinfo[:n, 1] = (clip(yb0) | (clip(yb1) << 16)).astype(np.uint32)
-        out[f] = np.concatenate([xm.reshape(-1), yinfo.reshape(-1)])
-    return out, segments, words
-
-
-GROUPS_PER_CTA = 256
-
-
-def build_group_list(ops_per_frame, width, height):
-    """The 4-pixel groups (pixels 4g .. 4g+3 of a row) that each frame's draw list can touch, with
-    a bit mask of the ops per group, arranged for one thread per (frame, touched group)
-    (layout: include/aiko_b200.h).  Frames that share one list object share their records.
-    -> (records uint32 [n_records, 1 + words], ctas uint32 [n_ctas, 4], words) or None."""
-    most = max((len(o) for o in ops_per_frame), default=0)
-    if most == 0 or most > INDEX_MAX_OPS or sum(len(o) for o in ops_per_frame) >= (1 << 24):
-        return None
-    words = (most + 31) // 32
-    groups = (width + 3) // 4
-    first_ops = np.concatenate([[0], np.cumsum([len(o) for o in ops_per_frame])])
-    cache, records, ctas, n_records = {}, [], [], 0
-    for f, frame_ops in enumerate(ops_per_frame):
-        key = id(frame_ops)
-        if key not in cache:
-            mask = np.zeros((height, groups, words), np.uint32)
-
-            def mark(ya, yb, xa, xb, w, bit):
-                ya, yb, xa, xb = max(ya, 0), min(yb, height - 1), max(xa, 0), min(xb, width - 1)
-                if ya <= yb and xa <= xb:
-                    mask[ya:yb + 1, xa // 4:xb // 4 + 1, w] |= np.uint32(1 << bit)
-
-            for b_, o in enumerate(frame_ops):
-                w, bit = divmod(b_, 32)
-                if o.kind == 0:        # rectangle outline: top / bottom bands, then the two side bands
-                    mark(o.y0 - 1, o.y0 + 1, o.x0 - 1, o.x1 + 1, w, bit)
-                    mark(o.y1 - 1, o.y1 + 1, o.x0 - 1, o.x1 + 1, w, bit)
-                    mark(o.y0 + 2, o.y1 - 2, o.x0 - 1, o.x0 + 1, w, bit)
-                    mark(o.y0 + 2, o.y1 - 2, o.x1 - 1, o.x1 + 1, w, bit)
-                else:
-                    mark(o.y0, o.y1, o.x0, o.x1, w, bit)
-            ys, gs = np.nonzero(mask.any(axis=2))
-            rec = np.empty((len(ys), 1 + words), np.uint32)
-            rec[:, 0] = gs.astype(np.uint32) | (ys.astype(np.uint32) << 16)
-            rec[:, 1:] = mask[ys, gs]
-            cache[key] = (n_records, len(ys))
-            records.append(rec)
-            n_records += len(ys)
-        offset, count = cache[key]
-        for start in range(0, count, GROUPS_PER_CTA):
-            ctas.append((offset + start, min(GROUPS_PER_CTA, count - start), f, first_ops[f] | (len(frame_ops) << 24)))
-    if not ctas:
-        return None
-    return np.concatenate(records), np.array(ctas, np.uint32), words
-
-
 class DeviceOverlay:
-    """A draw list resident on the GPU (see aiko_b200_overlay in include/aiko_b200.h)."""
+    """Draw lists resident on the GPU (see aiko_b200_overlay in include/aiko_b200.h).  One device
+    buffer holds ops | op_offsets | list_of_frame, uploaded with a single copy."""
 
-    def __init__(self, ops, op_offsets, atlas=None, max_ops_per_frame=0, index=None, index_width=0, groups=None,
-                 index_height=0):
-        self.ops, self.op_offsets, self.atlas = ops, op_offsets, atlas
-        self.struct = Overlay()
-        self.struct.max_ops_per_frame = int(max_ops_per_frame)
-        self.index = None
-        if index is not None:
-            table, segments, words = index
-            self.index = table
-            self.struct.index = table.data_ptr()
-            self.struct.index_width, self.struct.index_segments = int(index_width), int(segments)
-            self.struct.index_words, self.struct.index_frame_words = int(words), int(table.shape[1])
-        self.groups = None
-        if groups is not None and index_width:
-            records, ctas, words = groups
-            self.groups = (records, ctas)
-            self.struct.index_width, self.struct.index_height = int(index_width), int(index_height)
-            self.struct.group_records, self.struct.group_ctas = records.data_ptr(), ctas.data_ptr()
-            self.struct.n_group_ctas, self.struct.group_words = int(ctas.shape[0]), int(words)
-            if ctas.shape[0] == 0:             # "nothing is drawn": the pointers only need to be non-null
-                self.struct.group_ctas = records.data_ptr()
-        self.struct.ops = ops.data_ptr()
-        self.struct.op_offsets = op_offsets.data_ptr()
+    def __init__(self, buffer, n_ops, n_lists, n_frames, ops_bytes, atlas, width, height, max_ops, max_marks,
+                 max_cells):
+        self.buffer, self.atlas, self.n_ops = buffer, atlas, n_ops
+        st = self.struct = Overlay()
+        base = buffer.data_ptr()
+        st.ops, st.op_offsets = base, base + ops_bytes
+        st.list_of_frame = base + ops_bytes + 4 * (n_lists + 1)
+        st.n_lists, st.n_frames = int(n_lists), int(n_frames)
+        st.max_ops_per_list, st.max_marks_per_list = int(max_ops), int(max_marks)
+        st.max_cells_per_list = int(max_cells)
+        st.frame_width, st.frame_height = int(width or 0), int(height or 0)
         if atlas is not None:
-            self.struct.patch_ids = atlas.patch_ids.data_ptr()
-            self.struct.luts = atlas.luts.data_ptr()
-            self.struct.patch_w, self.struct.patch_h = atlas.patch_w, atlas.patch_h
-            self.struct.n_patches = atlas.patch_ids.shape[0]
+            st.patch_ids, st.luts = atlas.patch_ids.data_ptr(), atlas.luts.data_ptr()
+            st.patch_w, st.patch_h = atlas.patch_w, atlas.patch_h
+            st.n_patches = atlas.patch_ids.shape[0]
 
     @staticmethod
-    def pack_host(ops_per_frame):
-        """-> (uint8 ndarray of packed ops, int32 ndarray of offsets)"""
-        flat = [op for ops in ops_per_frame for op in ops]
-        offsets = np.zeros(len(ops_per_frame) + 1, np.int32)
-        if ops_per_frame:
-            np.cumsum([len(o) for o in ops_per_frame], out=offsets[1:])
-        count = max(len(flat), 1)
-        arr = (OverlayOp * count)(*flat)
-        raw = np.frombuffer(arr, dtype=np.uint8, count=ctypes.sizeof(OverlayOp) * count).copy()
-        return raw, offsets
+    def from_plan(plan, device, atlas=None, pinned=None, stream=None):
+        """``plan``: overlay_plan.Plan.  ``pinned``: optional pinned uint8 tensor the plan was written
+        into (then the copy is asynchronous; the caller keeps it untouched until the copy is done)."""
+        device = torch.device(device)
+        if atlas is None:
+            from .text_atlas import TextAtlas
+            atlas = TextAtlas.shared().device(device)
+        s = stream if stream is not None else torch.cuda.current_stream(device)
+        if atlas.ready is not None:
+            s.wait_event(atlas.ready)            # the tables may have been appended to on another stream
+        n = plan.buffer.nbytes
+        with torch.cuda.stream(s):
+            buf = torch.empty(n, dtype=torch.uint8, device=device)
+            if pinned is not None and plan.buffer.ctypes.data == pinned.data_ptr():
+                buf.copy_(pinned[:n], non_blocking=True)
+            else:
+                buf.copy_(torch.from_numpy(plan.buffer))
+        i = plan.info
+        return DeviceOverlay(buf, plan.n_ops, plan.n_lists, plan.n_frames, plan.ops_bytes, atlas, plan.width,
+                             plan.height, i.max_ops_per_list, i.max_marks_per_list, i.max_cells_per_list)
 
     @staticmethod
     def from_host(ops_per_frame, device, atlas=None, width=None, height=None):
-        """ops_per_frame: list (one entry per frame) of lists of OverlayOp; ``width`` / ``height``:
-        frame size the ops were built for (enables the spatial indices the kernels use)."""
-        raw, offsets = DeviceOverlay.pack_host(ops_per_frame)
-        most = max((len(o) for o in ops_per_frame), default=0)
-        index = None
-        if width and os.environ.get("AIKO_B200_OVERLAY_FUSED"):      # only the single-kernel variant uses it
-            built = build_overlay_index(ops_per_frame, width)
-            if built is not None:
-                index = (torch.from_numpy(built[0]).to(device), built[1], built[2])
-        groups = None
+        """ops_per_frame: list (one entry per frame) of lists of OverlayOp made by other means than
+        ``overlay_plan.plan``; frames that pass the same list object share it.  ``width`` / ``height``:
+        the frame size (lets the library run one thread per touched 4-pixel group)."""
+        lists, list_of_frame, seen = [], [], {}
+        for o in ops_per_frame:
+            li = seen.get(id(o))
+            if li is None:
+                li = seen[id(o)] = len(lists)
+                lists.append(o)
+            list_of_frame.append(li)
+        flat = [op for o in lists for op in o]
+        offsets = np.zeros(len(lists) + 1, np.int32)
+        if lists:
+            np.cumsum([len(o) for o in lists], out=offsets[1:])
+        count = max(len(flat), 1)
+        arr = (OverlayOp * count)(*flat)
+        max_ops = max((len(o) for o in lists), default=0)
+        max_marks = max_cells = 0
         if width and height:
-            if most == 0:                       # nothing to draw at all: no kernel is launched
-                empty = torch.zeros((1, 4), dtype=torch.int32, device=device)
-                groups = (empty, empty[:0], 1)
-            else:
-                built = build_group_list(ops_per_frame, width, height)
-                if built is not None:
-                    groups = (torch.from_numpy(built[0].view(np.int32)).to(device),
-                              torch.from_numpy(built[1].view(np.int32)).to(device), built[2])
-        return DeviceOverlay(torch.from_numpy(raw).to(device), torch.from_numpy(offsets).to(device), atlas, most,
-                             index, width or 0, groups, height or 0)
+            marks, cells = ctypes.c_int(), ctypes.c_longlong()
+            for i in range(len(lists)):
+                first = int(offsets[i])
+                check(_native.lib().aiko_b200_overlay_cells_host(
+                    ctypes.byref(arr, first * ctypes.sizeof(OverlayOp)), len(lists[i]), int(width), int(height),
+                    ctypes.byref(marks), ctypes.byref(cells)))
+                max_marks, max_cells = max(max_marks, marks.value), max(max_cells, min(cells.value, 2 ** 31 - 1))
+        ops_bytes = count * 32
+        raw = np.concatenate([np.frombuffer(arr, dtype=np.uint8, count=ops_bytes), offsets.view(np.uint8),
+                              np.asarray(list_of_frame, np.int32).view(np.uint8)])
+        device = torch.device(device)
+        if atlas is not None and atlas.ready is not None:
+            torch.cuda.current_stream(device).wait_event(atlas.ready)
+        return DeviceOverlay(torch.from_numpy(raw).to(device), len(flat), len(lists), len(list_of_frame), ops_bytes,
+                             atlas, width, height, max_ops, max_marks, max_cells)
 
     def pointer(self):
         return ctypes.pointer(self.struct)
+
+
+class OverlayRing:
+    """Draw lists that change with every call (detections move, label text carries the confidence):
+    a ring of page-locked + device buffer pairs allocated once, so that a new list costs one host
+    planning call and one asynchronous copy -- no allocation, no synchronisation unless the ring
+    wraps onto a copy still in flight.  A DeviceOverlay returned by ``plan`` stays valid until
+    ``slots`` further calls."""
+
+    def __init__(self, device, capacity=1 << 16, slots=8, stream=None):
+        from .text_atlas import TextAtlas
+        self.device = torch.device(device)
+        self.atlas = TextAtlas.shared()
+        self.capacity = capacity
+        self.slots = []
+        for _ in range(slots):
+            pinned = torch.empty(capacity, dtype=torch.uint8).pin_memory()
+            dev = torch.empty(capacity, dtype=torch.uint8, device=self.device)
+            self.slots.append([pinned, pinned.numpy(), dev, None])
+        self.next = 0
+
+    def plan(self, overlays, width, height, layout="rgb", n_frames=None, stream=None):
+        from .overlay_plan import plan
+        slot = self.slots[self.next]
+        self.next = (self.next + 1) % len(self.slots)
+        if slot[3] is not None:
+            slot[3].synchronize()                 # the copy out of this pinned buffer has run
+        planned = plan(overlays, width, height, layout, out=slot[1], n_frames=n_frames)
+        atlas = self.atlas.device(self.device)
+        s = stream if stream is not None else torch.cuda.current_stream(self.device)
+        if atlas.ready is not None:
+            s.wait_event(atlas.ready)
+        if planned.buffer.ctypes.data != slot[0].data_ptr():     # did not fit the slot: one-off buffers
+            return DeviceOverlay.from_plan(planned, self.device, atlas, stream=s)
+        with torch.cuda.device(self.device):
+            check(_native.lib().aiko_b200_overlay_upload(slot[2].data_ptr(), slot[0].data_ptr(), planned.buffer.nbytes,
+                                                         ctypes.c_void_p(s.cuda_stream)))
+        if slot[3] is None:
+            slot[3] = torch.cuda.Event()
+        slot[3].record(s)
+        i = planned.info
+        return DeviceOverlay(slot[2], planned.n_ops, planned.n_lists, planned.n_frames, planned.ops_bytes, atlas,
+                             planned.width, planned.height, i.max_ops_per_list, i.max_marks_per_list,
+                             i.max_cells_per_list)
 
 
 def reads_source_rows_once(frame_shape, width, height):
@@ -249,6 +201,8 @@ def resize_linear(src, width, height, *, swap_rb=False, overlay=None, out=None, 
     n, h, w, c, gray = _nhwc(src)
     shape = (n, height, width) if gray else (n, height, width, c)
     out = _out(out, shape, dev, "resize_linear out")
+    if overlay is not None and overlay.n_ops == 0:      # nothing to draw
+        overlay = None
     with torch.cuda.device(dev):
         check(_native.lib().aiko_b200_resize_linear_u8(
             src.data_ptr(), n, h, w, c, w * c, h * w * c, out.data_ptr(), height, width, width * c,
@@ -313,6 +267,11 @@ def overlay_draw(src, overlay, *, out=None, stream=None):
     _require_cuda(src, "overlay src")
     n, h, w, c, _ = _nhwc(src)
     out = _out(out, src.shape, src.device, "overlay out")
+    if overlay.n_ops == 0:                               # nothing to draw (the gray round trip is the identity)
+        if out.data_ptr() != src.data_ptr():
+            with torch.cuda.stream(stream) if stream is not None else contextlib.nullcontext():
+                out.copy_(src)
+        return out
     with torch.cuda.device(src.device):
         check(_native.lib().aiko_b200_overlay_u8(src.data_ptr(), out.data_ptr(), n, h, w, c, w * c, h * w * c,
                                                  overlay.pointer(), _stream_ptr(stream)))

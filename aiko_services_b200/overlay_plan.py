@@ -1,29 +1,114 @@
-"""Host-side translation of ImageOverlay's per-object logic into a GPU draw list.
+"""ImageOverlay's per-object logic -> GPU draw lists.
 
-Follows R/elements/media/image_io.py:119-155 step by step: objects and rectangles are
-zipped, objects at or below the confidence threshold are skipped, the label text is
-``f"{name}: {confidence:0.2f}"``, its position follows the reference's placement rule, and
-for each object the label is drawn before its rectangle.  The result is a list of
-``OverlayOp`` records (include/aiko_b200.h) that the kernels replay in order.
+The reference (R/elements/media/image_io.py:119-155) zips objects with rectangles, skips objects
+at or below the confidence threshold, formats the label ``f"{name}: {confidence:0.2f}"``, places
+it, and draws the label before its rectangle.  The dictionary handling and the text formatting
+stay here (they are Python semantics); size, placement, glyphs and rectangles are planned by
+``aiko_b200_overlay_plan_host`` in libaiko_b200.so (csrc/overlay_plan.cpp), which fills a caller
+buffer with 32-byte ``OverlayOp`` records (include/aiko_b200.h) that the kernels replay in order.
 """
-from ._native import OverlayOp
-from .text_atlas import COMPONENTS, TextAtlas
+import ctypes
+from array import array
+
+import numpy as np
+
+from . import _native
+from ._native import OverlayOp, OverlayPlanInfo, check
+from .text_atlas import TextAtlas, _encode
 
 OP_RECT, OP_GLYPH = 0, 1
-
-COLOR_BGR = (0, 255, 255)   # image_io.py:101, drawn on the BGR copy of the frame
 THRESHOLD = 0.0             # image_io.py:105
+LAYOUTS = {"rgb": 0, "bgr": 1}     # channel order of the stored frame the ops will be applied to
 
-# memory-channel colour of the stored frame for each layout the kernels produce
-CHANNEL_COLOURS = {
-    "rgb": (COLOR_BGR[2], COLOR_BGR[1], COLOR_BGR[0]),   # frame stays RGB (image_io.py:117,160)
-    "bgr": COLOR_BGR,                                    # frame stored swapped, or the gray round trip
-}
+
+def _objects(overlay, rects, labels):
+    """image_io.py:127-139 for one overlay dict: appends x, y, w, h and the label bytes per drawn
+    object; -> number of objects appended."""
+    if "rectangles" not in overlay:
+        return 0
+    rectangles = overlay["rectangles"]
+    objects = overlay["objects"] if "objects" in overlay else [{}] * len(rectangles)
+    count = 0
+    for obj, rectangle in zip(objects, rectangles):
+        name = obj.get("name", None)
+        confidence = obj.get("confidence", 1.0)
+        if not confidence > THRESHOLD:
+            continue
+        rects += (int(rectangle["x"]), int(rectangle["y"]), int(rectangle["w"]), int(rectangle["h"]))
+        labels.append(f"{name}: {confidence:0.2f}" if name else "")
+        count += 1
+    return count
+
+
+class Plan:
+    """Draw lists of one call, packed for a single host-to-device copy:
+    ``buffer`` = ops (32 bytes each) | op_offsets int32[n_lists + 1] | list_of_frame int32[n_frames]."""
+
+    __slots__ = ("buffer", "n_ops", "n_lists", "n_frames", "info", "width", "height", "ops_bytes")
+
+    def ops(self):
+        """The ops as a list of OverlayOp per list (tests, CPU replay)."""
+        arr = (OverlayOp * max(self.n_ops, 1)).from_buffer_copy(self.buffer[:max(self.n_ops, 1) * 32].tobytes())
+        offsets = self.buffer[self.ops_bytes:self.ops_bytes + 4 * (self.n_lists + 1)].view(np.int32)
+        return [[arr[k] for k in range(offsets[i], offsets[i + 1])] for i in range(self.n_lists)]
+
+
+def plan(overlays, image_width, image_height, layout="rgb", out=None, n_frames=None):
+    """``overlays``: one overlay dict (shared by every frame of the call, as in the reference), or a
+    list with one dict per frame (frames of several streams batched together).  Identical dicts
+    share one draw list.  ``out``: optional uint8 ndarray to plan into (e.g. over pinned memory).
+    ``n_frames``: frames of the call when one dict is shared (default 1).  -> Plan"""
+    shared = isinstance(overlays, dict)
+    dicts = [overlays] if shared else list(overlays)
+    lists, list_of_frame, seen = [], [], {}
+    for o in dicts:
+        key = id(o)
+        li = seen.get(key)
+        if li is None:
+            li = seen[key] = len(lists)
+            lists.append(o)
+        list_of_frame.append(li)
+    if shared and n_frames:
+        list_of_frame = [0] * int(n_frames)
+    rects, labels, offsets = [], [], [0]
+    for o in lists:
+        offsets.append(offsets[-1] + _objects(o, rects, labels))
+    n_obj = offsets[-1]
+    n_lists, n_frames = len(lists), len(list_of_frame)
+    # every character is at most one op, every object one more
+    text = "\0".join(labels)
+    try:
+        raw = text.encode("ascii")
+    except UnicodeEncodeError:           # cv2 sees the UTF-8 bytes, one glyph each ('?' outside 32..126)
+        raw = b"\0".join(_encode(t) for t in labels)
+    cap = len(raw) + 1
+    ops_bytes = max(cap, 1) * 32
+    need = ops_bytes + 4 * (n_lists + 1) + 4 * n_frames
+    if out is None or out.nbytes < need:
+        out = np.empty(need, np.uint8)
+    base = out.ctypes.data
+    c_offsets = array("i", offsets)
+    c_rects = array("i", rects or (0,))
+    info = OverlayPlanInfo()
+    check(_native.lib().aiko_b200_overlay_plan_host(
+        n_lists, c_offsets.buffer_info()[0], c_rects.buffer_info()[0], raw + b"\0", int(image_width), int(image_height),
+        LAYOUTS[layout], base, cap, base + ops_bytes, ctypes.byref(info)))
+    out[ops_bytes + 4 * (n_lists + 1):need].view(np.int32)[:] = list_of_frame
+    p = Plan()
+    p.buffer, p.n_ops, p.n_lists, p.n_frames, p.info = out[:need], info.n_ops, n_lists, n_frames, info
+    p.width, p.height, p.ops_bytes = int(image_width), int(image_height), ops_bytes
+    return p
+
+
+def build_ops(overlay, image_width, image_height, layout="rgb", atlas=None):
+    """-> list[OverlayOp] for one frame of size image_width x image_height."""
+    return plan(overlay, image_width, image_height, layout).ops()[0]
 
 
 def label_origin(atlas, text, x, y, w, h, image_width):
-    """image_io.py:140-150 -> (tx, ty), the bottom-left text origin given to cv2.putText."""
-    tw, th = atlas.text_size(text)
+    """image_io.py:140-150 -> (tx, ty), the bottom-left text origin given to cv2.putText (the rule
+    the library applies; kept here as its executable statement for the tests)."""
+    tw, th = (atlas or TextAtlas.shared()).text_size(text)
     tx = x
     if y > th * 1.5:
         ty = int(y - th / 2 - 2)
@@ -33,61 +118,3 @@ def label_origin(atlas, text, x, y, w, h, image_width):
         tx = x - tw
         ty = y + th
     return tx, ty
-
-
-def build_ops(overlay, image_width, image_height, layout="rgb", atlas=None):
-    """-> list[OverlayOp] for one frame of size image_width x image_height.
-
-    ``layout`` names the channel order of the frame the ops will be applied to.
-    """
-    atlas = atlas or TextAtlas.shared()
-    colour = CHANNEL_COLOURS[layout]
-    for comp in colour:
-        if comp not in COMPONENTS:
-            raise ValueError(f"glyph atlas has no tables for colour component {comp}")
-    ops = []
-    if "rectangles" not in overlay:
-        return ops
-    rectangles = overlay["rectangles"]
-    objects = overlay["objects"] if "objects" in overlay else [{}] * len(rectangles)
-    for obj, rectangle in zip(objects, rectangles):
-        name = obj.get("name", None)
-        confidence = obj.get("confidence", 1.0)
-        if not confidence > THRESHOLD:
-            continue
-        x, y, w, h = int(rectangle["x"]), int(rectangle["y"]), int(rectangle["w"]), int(rectangle["h"])
-        if name:
-            text = f"{name}: {confidence:0.2f}"
-            tx, ty = label_origin(atlas, text, x, y, w, h, image_width)
-            for ch, phase, px, py in atlas.glyphs(text, tx, ty):
-                pidx = [atlas.patch_index(ch, phase, comp) for comp in colour]
-                keys = [atlas.border_key(p, px, py, image_width, image_height) for p in set(pidx)]
-                key = next((k for k in keys if k is not None), None)
-                if key is not None:
-                    pidx = atlas.border_variant(ch, phase, colour, key)
-                boxes = [atlas.bbox[p] for p in pidx]
-                boxes = [b for b in boxes if b[2] >= b[0]]
-                if not boxes:
-                    continue
-                bx0 = min(b[0] for b in boxes); by0 = min(b[1] for b in boxes)
-                bx1 = max(b[2] for b in boxes); by1 = max(b[3] for b in boxes)
-                ax0, ay0, ax1, ay1 = px + bx0, py + by0, px + bx1, py + by1
-                # clip to the image; skip glyphs that fall entirely outside
-                cx0, cy0 = max(ax0, 0), max(ay0, 0)
-                cx1, cy1 = min(ax1, image_width - 1), min(ay1, image_height - 1)
-                if cx1 < cx0 or cy1 < cy0:
-                    continue
-                ops.append(OverlayOp(OP_GLYPH, int(cx0), int(cy0), int(cx1), int(cy1),
-                                     int(pidx[0]) | (int(pidx[1]) << 16), int(pidx[2]),
-                                     int(cx0 - px) | (int(cy0 - py) << 16)))
-        x0, y0, x1, y1 = x, y, x + w, y + h
-        xa, xb = min(x0, x1), max(x0, x1)
-        ya, yb = min(y0, y1), max(y0, y1)
-        if xb + 1 < 0 or yb + 1 < 0 or xa - 1 >= image_width or ya - 1 >= image_height:
-            continue
-        # keep coordinates in a range where +-2 arithmetic cannot overflow int32 on the device
-        lim = 1 << 24
-        xa, ya, xb, yb = (max(-lim, min(lim, v)) for v in (xa, ya, xb, yb))
-        ops.append(OverlayOp(OP_RECT, xa, ya, xb, yb,
-                             colour[0] | (colour[1] << 8) | (colour[2] << 16), 0, 0))
-    return ops

@@ -32,7 +32,7 @@ BATCH = 32
 # 960 of 1080 source rows carry weight (5,529,600 B) + 921,600 B written once
 ALGO_BYTES_PER_FRAME = 960 * SRC_W * 3 + DST_H * DST_W * 3
 FALLBACK_HBM_GBS = 6650.0
-OVERLAY_KERNEL = "overlay_groups_kernel"
+OVERLAY_KERNEL = "overlay_cells_kernel"
 N_ROTATING_BATCHES = 4     # 4 x 199 MB of distinct inputs: each step reads a batch the 126 MB L2 cannot hold
 
 OVERLAY = {
@@ -330,13 +330,14 @@ def run_gpu_arm(args):
                          for k, ob in enumerate(OVERLAY["objects"])]}
         return o
 
-    def changing_step(i):
-        fops = build_ops(changing_overlay(i), DST_W, DST_H, "bgr", atlas)
-        dov = ops.DeviceOverlay.from_host([fops] * BATCH, device, atlas.device(device), width=DST_W, height=DST_H)
-        ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=dov, out=out)
-        return dov
+    ring = ops.OverlayRing(device)
 
-    changing_steps = max(3, min(args.steps, 50))
+    def changing_step(i):
+        dov = ring.plan(changing_overlay(i), DST_W, DST_H, "bgr", n_frames=BATCH)
+        ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=dov, out=out)
+        return None
+
+    changing_steps = max(3, min(args.steps, 200))
     keep = [changing_step(i) for i in range(3)]
     barrier()
     tc0 = time.perf_counter()

@@ -34,6 +34,17 @@ def make(name, dev):
         if name == "flip":
             return lambda i: ops.flip(hd[i % rot], 1, out=out), 32
         return lambda i: ops.swap_rb(hd[i % rot], out=out), 32
+    if name in ("step", "step_draw"):      # the bench.py step: 1080p -> 640x480 + swap, then the draw list in place
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        import bench
+        from aiko_services_b200.overlay_plan import plan
+        hd = [torch.randint(0, 256, (32, 1080, 1920, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+        out = torch.empty((32, 480, 640, 3), dtype=torch.uint8, device=dev)
+        ov = ops.DeviceOverlay.from_plan(plan(bench.OVERLAY, 640, 480, "bgr", n_frames=32), dev)
+        if name == "step":
+            return lambda i: ops.resize_linear(hd[i % rot], 640, 480, swap_rb=True, overlay=ov, out=out), 32
+        ops.resize_linear(hd[0], 640, 480, swap_rb=True, out=out)
+        return lambda i: ops.overlay_draw(out, ov, out=out), 32
     if name == "overlay":                  # ImageOverlay alone on 32 x 1080p frames (copy + draw)
         from aiko_services_b200.overlay_plan import build_ops
         from aiko_services_b200.text_atlas import TextAtlas

@@ -38,7 +38,7 @@ extern "C" {
 #define AIKO_B200_ERR_CUDA (-3)
 #define AIKO_B200_ERR_WORKSPACE (-4)
 
-#define AIKO_B200_ABI_VERSION 1
+#define AIKO_B200_ABI_VERSION 2
 
 int aiko_b200_abi_version(void);
 const char* aiko_b200_last_error(void);
@@ -69,37 +69,87 @@ typedef struct aiko_b200_overlay_op {
  * luts[id][old_value], which replays cv2.putText(..., LINE_AA) exactly. */
 typedef struct aiko_b200_overlay {
   const aiko_b200_overlay_op* ops; /* device */
-  const int32_t* op_offsets;       /* device, [n_frames + 1]: frame i uses ops[op_offsets[i] .. op_offsets[i+1]) */
+  const int32_t* op_offsets;       /* device, [n_lists + 1]: list i is ops[op_offsets[i] .. op_offsets[i+1]) */
+  const int32_t* list_of_frame;    /* device, [n_frames]: the list frame f is drawn with, or NULL = list f.
+                                      The reference applies ONE overlay to all images of a call
+                                      (image_io.py:111-127), so a batch usually shares one list. */
   const uint16_t* patch_ids;       /* device, may be NULL when no GLYPH ops */
   const uint8_t* luts;             /* device */
   int32_t patch_w, patch_h;
   int32_t n_patches;
-  int32_t max_ops_per_frame;       /* largest op count of any frame, or 0 if unknown */
-  /* Optional spatial index of the draw list for frames `index_width` pixels wide (NULL = kernels
-   * cull the list themselves).  Per frame, index_frame_words uint32:
-   *   xmask[2][index_segments][index_words][32]  bit b of word [v][s][w][l] = op 32*w + b can touch
-   *       pixels 128*s + 4*l .. +3; v = 0: rows where a rectangle only has its two side bands,
-   *       v = 1: rows inside a rectangle's top / bottom band (glyph ops: same in both);
-   *   yinfo[index_words][32][2]  per op: (first_row | last_row << 16), (band_row_0 | band_row_1 << 16)
-   *       as int16: the op touches rows first..last; a rectangle is in its band variant on rows
-   *       <= band_row_0 or >= band_row_1.
-   * Built by aiko_services_b200.ops.build_overlay_index (numpy). */
-  const uint32_t* index;
-  int32_t index_width, index_segments, index_words, index_frame_words;
-  int32_t index_height;
-  /* Optional list of the 4-pixel groups (pixels 4g .. 4g+3 of row y) that the draw lists can touch,
-   * for frames index_width x index_height, arranged for one thread per (frame, touched group):
-   *   group_records[r] = (1 + group_words) uint32: g | y << 16, then bit b of word w = op 32*w + b
-   *       of the frame's list can touch the group;
-   *   group_ctas[c]    = 4 uint32: first record, record count (<= 256), frame,
-   *       op_offsets[frame] | op count << 24  -- one CTA's share.
-   * Frames with identical lists may share records.  n_group_ctas == 0 with non-NULL pointers means
-   * nothing is drawn.  NULL = not provided (the kernel then culls the list per 64 x 16 tile).
-   * Built by aiko_services_b200.ops.build_group_list (numpy). */
-  const uint32_t* group_records;
-  const uint32_t* group_ctas;
-  int32_t n_group_ctas, group_words;
+  int32_t n_lists;                 /* lists described by op_offsets */
+  int32_t n_frames;                /* frames the overlay was made for; a call with more frames is refused */
+  int32_t max_ops_per_list;        /* largest op count of any list, or 0 if unknown */
+  /* From aiko_b200_overlay_plan_host / aiko_b200_overlay_cells_host, for frames of
+   * frame_width x frame_height: the largest number of marks (blocks of 4-pixel groups an op can
+   * touch) and of cells (groups in those blocks) of any list.  With them the draw list runs as
+   * one thread per cell (overlay_cells_kernel); 0 = unknown, the kernels then cull the list
+   * per 64 x 16 tile. */
+  int32_t max_marks_per_list;
+  int32_t max_cells_per_list;
+  int32_t frame_width, frame_height;
 } aiko_b200_overlay;
+
+/* ---------------------------------------------------------------------- */
+/* Host-side planning of ImageOverlay's drawing (image_io.py:119-155): no   */
+/* device work, no OpenCV.  The caller has already paired objects with      */
+/* rectangles, dropped objects at or below the confidence threshold          */
+/* (image_io.py:131) and formatted the label text (image_io.py:139).         */
+
+typedef struct aiko_b200_overlay_plan_info {
+  int32_t n_ops;               /* ops produced (may exceed the capacity given: ERR_WORKSPACE) */
+  int32_t max_ops_per_list;
+  int32_t max_marks_per_list;
+  int32_t max_cells_per_list;
+  uint64_t atlas_version;      /* glyph atlas state the ops refer to (see aiko_b200_overlay_atlas_host) */
+  uint64_t atlas_epoch;
+} aiko_b200_overlay_plan_info;
+
+/* n_lists draw lists; list i covers objects object_offsets_host[i] .. [i+1).  rects_host: x, y, w, h per
+ * object (the ints of image_io.py:132-135).  labels_host: one NUL-terminated string per object, in
+ * order; an empty string = no label (NULL = no labels at all).  layout: 0 = the frames stay RGB
+ * (image_io.py:117,160), 1 = stored BGR (fused RGB->BGR, or the gray round trip image_io.py:115).
+ * Per object: label size as cv2.getTextSize(FONT_HERSHEY_SIMPLEX, 0.75, 2), placement rule
+ * image_io.py:143-150, one GLYPH op per character (cv2.putText LINE_AA, image_io.py:151-153), then
+ * the RECT op (cv2.rectangle thickness 2, image_io.py:154-155).  May grow the glyph atlas (labels
+ * clipped by the image border). */
+int aiko_b200_overlay_plan_host(int n_lists, const int32_t* object_offsets_host, const int32_t* rects_host,
+                                const char* labels_host, int image_width, int image_height, int layout,
+                                aiko_b200_overlay_op* ops_out_host, int ops_capacity,
+                                int32_t* op_offsets_out_host, aiko_b200_overlay_plan_info* info_host);
+
+/* Ships a planned buffer (ops | op_offsets | list_of_frame, as laid out by the caller around
+ * aiko_b200_overlay_plan_host) to the device: one cudaMemcpyAsync on `stream`.  plan_host should be
+ * page-locked and stay untouched until the copy has run. */
+int aiko_b200_overlay_upload(void* plan_dev, const void* plan_host, size_t bytes, void* stream);
+
+/* cv2.getTextSize(text, FONT_HERSHEY_SIMPLEX, 0.75, 2)[0] (image_io.py:141-142). */
+int aiko_b200_overlay_text_size_host(const char* text_host, int* width_host, int* height_host);
+
+/* Marks and cells of a draw list built by other means (see aiko_b200_overlay). */
+int aiko_b200_overlay_cells_host(const aiko_b200_overlay_op* ops_host, int n_ops, int image_width,
+                                 int image_height, int* n_marks_host, long long* n_cells_host);
+
+/* The marks of one op for frames image_width x image_height (what overlay_cells_kernel enumerates):
+ * up to 4 blocks of 4-pixel groups, written as int16 {first row, last row, first group, last group}
+ * (group g = pixels 4g .. 4g+3).  Every pixel the op can change lies in one of them.  Returns the
+ * number of marks (0..4) or a negative error code. */
+int aiko_b200_overlay_marks_host(const aiko_b200_overlay_op* op_host, int image_width, int image_height,
+                                 int16_t* marks_out_host);
+
+/* The host copy of the glyph atlas, to be mirrored on each GPU by the caller (the library never
+ * allocates device memory).  Rows only ever get appended while `epoch` stays the same -- copy rows
+ * [old n .. new n) when `version` moved; a new epoch means the border-clipped glyph variants were
+ * dropped to make room and indices beyond the first 761 patches were re-used: upload afresh, into
+ * new device buffers if kernels using the old ones may still be queued.  Pointers stay valid for
+ * the life of the process (capacity max_patches / max_luts is reserved up front). */
+typedef struct aiko_b200_atlas_view {
+  const uint16_t* patch_ids_host; /* [n_patches][patch_h][patch_w] */
+  const uint8_t* luts_host;       /* [n_luts][256] */
+  int32_t patch_w, patch_h, n_patches, n_luts, max_patches, max_luts;
+  uint64_t version, epoch;
+} aiko_b200_atlas_view;
+int aiko_b200_overlay_atlas_host(aiko_b200_atlas_view* view_host);
 
 /* ---------------------------------------------------------------------- */
 /* ImageResize, ndarray branch: cv2.resize(image, (W, H)), INTER_LINEAR,   */

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_version_and_error_string_without_gpu():
     lib = _native.lib()
-    assert lib.aiko_b200_abi_version() == 1
+    assert lib.aiko_b200_abi_version() == 2
     # argument validation happens before any CUDA call, so it is testable on CPU
     rc = lib.aiko_b200_swap_rb_u8(None, None, -1, None)
     assert rc == _native.ERR_INVALID_ARGUMENT
@@ -38,7 +38,7 @@ def test_version_and_error_string_without_gpu():
 
 def test_overlay_op_struct_layout():
     assert ctypes.sizeof(_native.OverlayOp) == 32
-    assert ctypes.sizeof(_native.Overlay) == 104   # 7 pointers + 11 int32 (+ padding)
+    assert ctypes.sizeof(_native.Overlay) == 80    # 5 pointers + 10 int32
 
 
 def test_zero_copy_eligibility_rule():

@@ -338,7 +338,7 @@ def test_overlay_many_ops_per_frame(cuda, atlas):
     overlay = random_overlay(rng, w, h, n=70)     # > 256 ops: several cull passes per row
     img = cases.frame(204, h, w, 3)
     ov = device_overlay([overlay], w, h, "rgb", atlas, cuda)
-    assert int(ov.op_offsets[-1]) > 256
+    assert ov.n_ops > 256
     np.testing.assert_array_equal(host(ops.overlay_draw(dev(img[None], cuda), ov))[0], overlay_cpu(img, overlay, atlas))
 
 
@@ -372,20 +372,21 @@ def test_fused_equals_unfused_random(cuda, atlas):
 
 
 def test_fused_resize_with_long_draw_list_uses_device_side_culling(cuda, atlas):
-    """More ops than the host-built group list carries (128): the tile kernel culls by itself."""
+    """More ops than the cell kernel takes per list (256): the tile kernel culls by itself."""
     rng = np.random.default_rng(206)
     H, W = 120, 160
     frames = np.stack([cases.frame(500 + k, 270, 480, 3) for k in range(2)])
     overlays = [random_overlay(rng, W, H, n=60) for _ in range(2)]
     ov = device_overlay(overlays, W, H, "rgb", atlas, cuda)
-    assert ov.groups is None and int(ov.op_offsets[-1]) > 256
+    assert ov.struct.max_ops_per_list > 256
     out = host(ops.resize_linear(dev(frames, cuda), W, H, overlay=ov))
     for k in range(2):
         np.testing.assert_array_equal(out[k], overlay_cpu(O.resize_linear(frames[k], W, H), overlays[k], atlas))
 
 
 def test_overlay_variants_agree(cuda, atlas, monkeypatch):
-    """Two-launch (default) and single-kernel (AIKO_B200_OVERLAY_FUSED=1) overlays are bit-identical."""
+    """Cell kernel (default), tile kernel (AIKO_B200_OVERLAY_TILES=1) and the single-kernel variant
+    (AIKO_B200_OVERLAY_FUSED=1) are bit-identical."""
     frames = dev(np.stack([cases.frame(2000 + i, 1080, 1920, 3) for i in range(3)]), cuda)
     two_pass = ops.resize_linear(frames, 640, 480, swap_rb=True,
                                  overlay=device_overlay([cases.OVERLAY_4] * 3, 640, 480, "bgr", atlas, cuda))
@@ -393,6 +394,39 @@ def test_overlay_variants_agree(cuda, atlas, monkeypatch):
     fused = ops.resize_linear(frames, 640, 480, swap_rb=True,
                               overlay=device_overlay([cases.OVERLAY_4] * 3, 640, 480, "bgr", atlas, cuda))
     assert torch.equal(two_pass, fused)
+    monkeypatch.delenv("AIKO_B200_OVERLAY_FUSED")
+    monkeypatch.setenv("AIKO_B200_OVERLAY_TILES", "1")
+    tiles = ops.resize_linear(frames, 640, 480, swap_rb=True,
+                              overlay=device_overlay([cases.OVERLAY_4] * 3, 640, 480, "bgr", atlas, cuda))
+    assert torch.equal(two_pass, tiles)
+
+
+def test_planned_overlay_per_frame_lists_and_shared_list(cuda, atlas):
+    """overlay_plan.plan -> DeviceOverlay.from_plan: one dict shared by all frames, and distinct dicts
+    per frame (cross-stream batch), both against the CPU replay; many marks (8 mask words)."""
+    from aiko_services_b200.overlay_plan import plan
+    rng = np.random.default_rng(77)
+    W, H = 320, 200
+    frames = np.stack([cases.frame(900 + k, H, W, 3) for k in range(5)])
+    for n_obj in (1, 4, 12, 40):
+        overlays = [random_overlay(rng, W, H, n=n_obj) for _ in range(5)]
+        overlays[3] = overlays[1]                              # two frames share a dict
+        ov = ops.DeviceOverlay.from_plan(plan(overlays, W, H, "rgb"), cuda)
+        out = host(ops.overlay_draw(dev(frames, cuda), ov))
+        for k in range(5):
+            np.testing.assert_array_equal(out[k], overlay_cpu(frames[k], overlays[k], atlas), err_msg=f"{n_obj} {k}")
+        ov = ops.DeviceOverlay.from_plan(plan(overlays[0], W, H, "rgb", n_frames=5), cuda)
+        out = host(ops.overlay_draw(dev(frames, cuda), ov))
+        for k in range(5):
+            np.testing.assert_array_equal(out[k], overlay_cpu(frames[k], overlays[0], atlas))
+
+
+def test_overlay_refuses_a_list_made_for_fewer_frames(cuda, atlas):
+    from aiko_services_b200._native import NativeError
+    ov = device_overlay([cases.OVERLAY_4] * 2, 640, 480, "rgb", atlas, cuda)
+    assert ov.n_ops > 0
+    with pytest.raises(NativeError):
+        ops.overlay_draw(dev(np.zeros((3, 480, 640, 3), np.uint8), cuda), ov)
 
 
 def test_resize_rgba_swap_and_widths_not_multiple_of_four(cuda, atlas):
@@ -433,3 +467,19 @@ def test_sizes_beyond_on_chip_limits_are_refused_not_mangled(cuda):
     frames = np.stack([cases.frame(81, 24, 7680, 3)])
     out = host(ops.resize_linear(dev(frames, cuda), 3840, 12))
     np.testing.assert_array_equal(out[0], O.resize_linear(frames[0], 3840, 12))
+
+
+def test_overlay_ring_changing_lists(cuda, atlas):
+    """A new draw list per call through OverlayRing (planned into pinned memory, one async copy):
+    results match the CPU replay while the ring wraps several times."""
+    rng = np.random.default_rng(88)
+    W, H = 160, 120
+    frames = np.stack([cases.frame(700 + k, 270, 480, 3) for k in range(2)])
+    d = dev(frames, cuda)
+    ring = ops.OverlayRing(cuda, capacity=1 << 14, slots=3)
+    for i in range(10):
+        overlay = random_overlay(rng, W, H, n=3)
+        ov = ring.plan(overlay, W, H, "rgb", n_frames=2)
+        out = host(ops.resize_linear(d, W, H, overlay=ov))
+        for k in range(2):
+            np.testing.assert_array_equal(out[k], overlay_cpu(O.resize_linear(frames[k], W, H), overlay, atlas))

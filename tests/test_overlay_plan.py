@@ -74,33 +74,47 @@ def test_skips_and_empty(atlas):
     assert ops == []      # confidence must exceed the threshold (image_io.py:131)
 
 
-def test_group_list_covers_every_pixel_an_op_changes(atlas):
-    """The GPU applies an op only to the 4-pixel groups the host flagged for it: for random
-    overlays (clipped boxes, labels at the border), every pixel that op changes when replayed
-    alone must lie in a flagged group, and frames sharing a list must share its records."""
-    from aiko_services_b200.ops import build_group_list
+def test_marks_cover_every_pixel_an_op_changes(atlas):
+    """The GPU applies an op only inside its marks (blocks of 4-pixel groups, csrc/overlay_marks.h):
+    for random overlays (clipped boxes, labels at the border), every pixel an op changes when
+    replayed alone must lie in one of its marks, and the planner's mark / cell bounds must hold."""
+    import ctypes
+    from aiko_services_b200 import _native
+    from aiko_services_b200.overlay_plan import plan
     from util import replay_ops_cpu
+    lib = _native.lib()
     rng = np.random.default_rng(6)
     for trial in range(12):
         h, w = int(rng.integers(40, 140)), int(rng.integers(60, 260))
         overlay = random_overlay(rng, w, h, n=int(rng.integers(1, 7)))
-        ops = build_ops(overlay, w, h, "rgb", atlas)
-        if not ops:
-            continue
-        records, ctas, words = build_group_list([ops, ops, list(ops)], w, h)
-        n_rec = len(records) // 2                      # frames 0 and 1 share one list object, frame 2 has a copy
-        assert [int(c[2]) for c in ctas] == sorted(int(c[2]) for c in ctas)
-        first_of_frame = {f: min(int(c[0]) for c in ctas if int(c[2]) == f) for f in (0, 1, 2)}
-        assert first_of_frame[0] == first_of_frame[1] != first_of_frame[2]
-        flagged = {}                                    # (y, g) -> mask words
-        for r in records[:n_rec]:
-            flagged[(int(r[0] >> 16), int(r[0] & 0xffff))] = [int(v) for v in r[1:]]
-        for b, op in enumerate(ops):
+        planned = plan(overlay, w, h, "rgb")
+        ops = planned.ops()[0]
+        n_marks = n_cells = 0
+        for op in ops:
+            marks = (ctypes.c_int16 * 16)()
+            n = lib.aiko_b200_overlay_marks_host(ctypes.byref(op), w, h, marks)
+            assert 0 <= n <= 4
+            blocks = [tuple(marks[4 * i:4 * i + 4]) for i in range(n)]
+            n_marks += n
+            n_cells += sum((y1 - y0 + 1) * (g1 - g0 + 1) for y0, y1, g0, g1 in blocks)
+            for y0, y1, g0, g1 in blocks:
+                assert 0 <= y0 <= y1 < h and 0 <= g0 <= g1 <= (w - 1) // 4
             probes = [np.zeros((h, w, 3), np.uint8), np.full((h, w, 3), 255, np.uint8),
                       rng.integers(0, 256, (h, w, 3), dtype=np.uint8)]
             changed = np.zeros((h, w), bool)
             for base in probes:
                 changed |= (replay_ops_cpu(base.copy(), [op], atlas) != base).any(axis=2)
             for y, x in zip(*np.nonzero(changed)):
-                mask = flagged.get((int(y), int(x) // 4))
-                assert mask is not None and (mask[b // 32] >> (b % 32)) & 1, (trial, b, int(x), int(y))
+                assert any(y0 <= y <= y1 and g0 <= x // 4 <= g1 for y0, y1, g0, g1 in blocks), (trial, int(x), int(y))
+        assert planned.info.max_marks_per_list == n_marks and planned.info.max_cells_per_list == n_cells
+        assert planned.info.n_ops == planned.info.max_ops_per_list == len(ops)
+
+
+def test_shared_and_per_frame_lists(atlas):
+    from aiko_services_b200.overlay_plan import plan
+    a, b = cases.OVERLAY_4, {"rectangles": [{"x": 3, "y": 4, "w": 10, "h": 12}]}
+    p = plan([a, b, a], 640, 480, "bgr")
+    assert p.n_lists == 2 and p.n_frames == 3
+    tail = p.buffer[p.ops_bytes:].view(np.int32)
+    assert list(tail[p.n_lists + 1:]) == [0, 1, 0]
+    assert tail[0] == 0 and tail[2] == p.n_ops and len(p.ops()[1]) == 1
