@@ -36,7 +36,8 @@ class Overlay(ctypes.Structure):
                 ("patch_w", ctypes.c_int32), ("patch_h", ctypes.c_int32), ("n_patches", ctypes.c_int32),
                 ("n_lists", ctypes.c_int32), ("n_frames", ctypes.c_int32), ("max_ops_per_list", ctypes.c_int32),
                 ("max_marks_per_list", ctypes.c_int32), ("max_cells_per_list", ctypes.c_int32),
-                ("frame_width", ctypes.c_int32), ("frame_height", ctypes.c_int32)]
+                ("frame_width", ctypes.c_int32), ("frame_height", ctypes.c_int32),
+                ("upload_from_host", ctypes.c_void_p), ("upload_bytes", ctypes.c_uint64)]
 
 
 class OverlayPlanInfo(ctypes.Structure):

@@ -3,13 +3,14 @@
 // frame's draw list is replayed on it in order, and the row is written back.  Grayscale
 // frames take the reference's GRAY->BGR, draw, BGR->GRAY round trip (image_io.py:115,158).
 #include <stdlib.h>
+#include <string.h>
 
 #include "overlay.cuh"
 #include "overlay_marks.h"
 
 namespace aiko {
 
-static_assert(sizeof(aiko_b200_overlay) == 80 && sizeof(aiko_b200_overlay_op) == 32, "ABI layout (tests/test_abi.py)");
+static_assert(sizeof(aiko_b200_overlay) == 96 && sizeof(aiko_b200_overlay_op) == 32, "ABI layout (tests/test_abi.py)");
 
 struct OverlayParams {
   const uint8_t* src;
@@ -423,12 +424,43 @@ int launch_overlay_tiles(uint8_t* frames, int n, int h, int w, long long row_str
   return cuda_status(cudaGetLastError(), "overlay_tiles launch");
 }
 
-int overlay_from_abi(const aiko_b200_overlay* o, int n_frames, OverlayDev* out) {
+// A planned buffer of a few KB travels as a kernel ARGUMENT (copied by the launch itself, so the host
+// buffer is free again when the call returns) and is stored by one small CTA: cheaper on the stream
+// than a copy-engine transfer between two kernels.
+template <int WORDS>
+struct PlanBlob {
+  uint4 w[WORDS];
+};
+template <int WORDS>
+__global__ void __launch_bounds__(kThreads) overlay_plan_store_kernel(const __grid_constant__ PlanBlob<WORDS> blob,
+                                                                      uint4* dst, int words) {
+  for (int i = threadIdx.x; i < words; i += kThreads) dst[i] = blob.w[i];
+}
+template <int WORDS>
+static int store_plan(const void* host, size_t bytes, void* dst, cudaStream_t stream) {
+  PlanBlob<WORDS> blob;
+  memcpy(&blob, host, bytes);
+  overlay_plan_store_kernel<WORDS><<<1, kThreads, 0, stream>>>(blob, static_cast<uint4*>(dst), (int)((bytes + 15) / 16));
+  return cuda_status(cudaGetLastError(), "overlay_plan_store launch");
+}
+
+int overlay_from_abi(const aiko_b200_overlay* o, int n_frames, cudaStream_t stream, OverlayDev* out) {
   AIKO_CHECK_ARG(o && o->ops && o->op_offsets, "overlay: missing draw list (ops / op_offsets)");
   AIKO_CHECK_ARG(o->n_frames >= n_frames, "overlay: draw list made for %d frames, call has %d", o->n_frames, n_frames);
   AIKO_CHECK_ARG(o->list_of_frame || o->n_lists >= n_frames, "overlay: %d lists for %d frames and no list_of_frame",
                  o->n_lists, n_frames);
   AIKO_CHECK_ARG(o->patch_w >= 0 && o->patch_h >= 0, "overlay: bad patch size");
+  if (o->upload_from_host && o->upload_bytes) {
+    void* dst = const_cast<aiko_b200_overlay_op*>(o->ops);
+    const size_t bytes = (size_t)o->upload_bytes;
+    int rc = AIKO_B200_OK;
+    if ((reinterpret_cast<uintptr_t>(dst) & 15) != 0 || bytes > 16384 || getenv("AIKO_B200_OVERLAY_UPLOAD_COPY"))
+      rc = cuda_status(cudaMemcpyAsync(dst, o->upload_from_host, bytes, cudaMemcpyHostToDevice, stream), "overlay upload");
+    else if (bytes <= 2048) rc = store_plan<128>(o->upload_from_host, bytes, dst, stream);
+    else if (bytes <= 6144) rc = store_plan<384>(o->upload_from_host, bytes, dst, stream);
+    else rc = store_plan<1024>(o->upload_from_host, bytes, dst, stream);
+    if (rc != AIKO_B200_OK) return rc;
+  }
   *out = OverlayDev{o->ops, o->op_offsets, o->list_of_frame, o->patch_ids, o->luts, o->patch_w, o->patch_h,
                     o->max_ops_per_list, o->max_marks_per_list, o->max_cells_per_list, o->frame_width, o->frame_height};
   return AIKO_B200_OK;
@@ -457,7 +489,7 @@ extern "C" int aiko_b200_overlay_u8(const uint8_t* src, uint8_t* dst, int n_fram
   p.src = src; p.dst = dst; p.n = n_frames; p.h = h; p.w = w; p.channels = channels;
   p.row_stride = row_stride; p.frame_stride = frame_stride;
   {
-    const int rc = overlay_from_abi(overlay, n_frames, &p.ov);
+    const int rc = overlay_from_abi(overlay, n_frames, static_cast<cudaStream_t>(stream), &p.ov);
     if (rc != AIKO_B200_OK) return rc;
   }
   if (channels == 3 && !getenv("AIKO_B200_OVERLAY_ROWS")) {

@@ -20,7 +20,8 @@ struct OverlayDev {
 };
 
 // Checks an overlay given through the C ABI against the call's frame count and copies it.
-int overlay_from_abi(const aiko_b200_overlay* overlay, int n_frames, OverlayDev* out);
+// (and ships the planned buffer first when it is still in host memory).
+int overlay_from_abi(const aiko_b200_overlay* overlay, int n_frames, cudaStream_t stream, OverlayDev* out);
 
 __device__ __forceinline__ int overlay_list(const OverlayDev& ov, int frame) {
   return ov.list_of_frame ? __ldg(ov.list_of_frame + frame) : frame;

@@ -17,6 +17,8 @@
 // resize_rows_generic (RGBA, scale > 4 where most sectors of a source row carry no weight, and
 // the shapes the register-resident path does not take): same row structure, taps read straight
 // from global memory.
+#include <atomic>
+
 #include "overlay.cuh"
 
 namespace aiko {
@@ -622,9 +624,22 @@ static int launch_staged3(ResizeParams p, cudaStream_t stream, bool* done) {
   if (stages < 2 || need(stages) > max_smem) return AIKO_B200_OK;  // not staged
   p.stages = stages;
   const size_t smem = need(stages);
-  AIKO_CUDA(cudaFuncSetAttribute(resize3_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 0;
-  AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resize3_staged, threads, smem));
+  // (attribute + occupancy of the last launch shape are remembered: a stream repeats one shape)
+  static thread_local struct { int dev = -1, threads = 0, per_sm = 0; size_t smem = 0; } seen;
+  int device = 0, per_sm = 0;
+  AIKO_CUDA(cudaGetDevice(&device));
+  static std::atomic<int> smem_limit[64];          // per device: the limit only ever grows (it is process-wide)
+  if (device >= 0 && device < 64 && smem_limit[device].load() < (int)smem) {
+    AIKO_CUDA(cudaFuncSetAttribute(resize3_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int cur = smem_limit[device].load();
+    while (cur < (int)smem && !smem_limit[device].compare_exchange_weak(cur, (int)smem)) {}
+  }
+  if (seen.dev == device && seen.threads == threads && seen.smem == smem) {
+    per_sm = seen.per_sm;
+  } else {
+    AIKO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resize3_staged, threads, smem));
+    seen.dev = device; seen.threads = threads; seen.smem = smem; seen.per_sm = per_sm;
+  }
   if (per_sm < 1) per_sm = 1;
   // Source rows in page-locked host memory (the TMA engine reads them over PCIe): the link, not the
   // SMs, sets the pace, and one CTA per SM keeps far more bytes in flight than it needs.  Leaving
@@ -704,7 +719,7 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
   p.swap_rb = swap_rb ? 1 : 0;
   p.has_overlay = overlay ? 1 : 0;
   if (overlay) {
-    const int rc = overlay_from_abi(overlay, n_frames, &p.ov);
+    const int rc = overlay_from_abi(overlay, n_frames, static_cast<cudaStream_t>(stream), &p.ov);
     if (rc != AIKO_B200_OK) return rc;
   }
   p.items = n_frames * dst_h;

@@ -133,46 +133,68 @@ class DeviceOverlay:
 
 class OverlayRing:
     """Draw lists that change with every call (detections move, label text carries the confidence):
-    a ring of page-locked + device buffer pairs allocated once, so that a new list costs one host
-    planning call and one asynchronous copy -- no allocation, no synchronisation unless the ring
-    wraps onto a copy still in flight.  A DeviceOverlay returned by ``plan`` stays valid until
-    ``slots`` further calls."""
+    a ring of page-locked + device buffer pairs allocated once.  A new list costs one host planning
+    call; its bytes travel inside the call that draws it (``upload_from_host`` of aiko_b200_overlay),
+    so there is no allocation, no extra copy call and no synchronisation unless the ring wraps onto
+    copies still in flight.  The DeviceOverlay returned by ``plan`` must be used (once, on
+    ``stream``) before the next ``plan`` and stays valid for ``slots`` / 2 further calls."""
 
-    def __init__(self, device, capacity=1 << 16, slots=8, stream=None):
+    def __init__(self, device, capacity=1 << 16, slots=16):
         from .text_atlas import TextAtlas
         self.device = torch.device(device)
         self.atlas = TextAtlas.shared()
         self.capacity = capacity
-        self.slots = []
-        for _ in range(slots):
-            pinned = torch.empty(capacity, dtype=torch.uint8).pin_memory()
-            dev = torch.empty(capacity, dtype=torch.uint8, device=self.device)
-            self.slots.append([pinned, pinned.numpy(), dev, None])
+        self.pinned = torch.empty((slots, capacity), dtype=torch.uint8).pin_memory()
+        self.dev = torch.empty((slots, capacity), dtype=torch.uint8, device=self.device)
+        self.views = [self.pinned[i].numpy() for i in range(slots)]
+        self.overlays = [None] * slots
+        self.half = max(slots // 2, 1)
+        self.events = [None, None]        # one per half of the ring: recorded after the half's last use
         self.next = 0
+        self._atlas_dev = None
 
     def plan(self, overlays, width, height, layout="rgb", n_frames=None, stream=None):
         from .overlay_plan import plan
-        slot = self.slots[self.next]
-        self.next = (self.next + 1) % len(self.slots)
-        if slot[3] is not None:
-            slot[3].synchronize()                 # the copy out of this pinned buffer has run
-        planned = plan(overlays, width, height, layout, out=slot[1], n_frames=n_frames)
-        atlas = self.atlas.device(self.device)
+        i = self.next
+        n = len(self.views)
         s = stream if stream is not None else torch.cuda.current_stream(self.device)
-        if atlas.ready is not None:
-            s.wait_event(atlas.ready)
-        if planned.buffer.ctypes.data != slot[0].data_ptr():     # did not fit the slot: one-off buffers
+        if i == 0 or i == self.half:
+            # entering a half: everything queued from it a lap ago must have run (the event recorded when
+            # the other half was entered); and everything queued so far covers the other half's last lap
+            h = 0 if i == 0 else 1
+            if n == 1:
+                s.synchronize()
+            else:
+                if self.events[h] is not None:
+                    self.events[h].synchronize()
+                if self.events[1 - h] is None:
+                    self.events[1 - h] = torch.cuda.Event()
+                self.events[1 - h].record(s)
+        self.next = (i + 1) % n
+        planned = plan(overlays, width, height, layout, out=self.views[i], n_frames=n_frames)
+        atlas = self._atlas_dev
+        info = planned.info
+        if atlas is None or atlas.version != info.atlas_version or atlas.epoch != info.atlas_epoch:
+            atlas = self._atlas_dev = self.atlas.device(self.device)       # uploads what the planner appended
+            if atlas.ready is not None:
+                s.wait_event(atlas.ready)
+        if planned.buffer.ctypes.data != self.views[i].ctypes.data:        # did not fit the slot: one-off buffers
             return DeviceOverlay.from_plan(planned, self.device, atlas, stream=s)
-        with torch.cuda.device(self.device):
-            check(_native.lib().aiko_b200_overlay_upload(slot[2].data_ptr(), slot[0].data_ptr(), planned.buffer.nbytes,
-                                                         ctypes.c_void_p(s.cuda_stream)))
-        if slot[3] is None:
-            slot[3] = torch.cuda.Event()
-        slot[3].record(s)
-        i = planned.info
-        return DeviceOverlay(slot[2], planned.n_ops, planned.n_lists, planned.n_frames, planned.ops_bytes, atlas,
-                             planned.width, planned.height, i.max_ops_per_list, i.max_marks_per_list,
-                             i.max_cells_per_list)
+        ov = self.overlays[i]
+        if ov is None or ov.atlas is not atlas:
+            ov = self.overlays[i] = DeviceOverlay(self.dev[i], 0, 0, 0, 0, atlas, 0, 0, 0, 0, 0)
+            ov.struct.upload_from_host = self.pinned[i].data_ptr()
+            ov.base = self.dev[i].data_ptr()
+        st = ov.struct
+        ov.n_ops = planned.n_ops
+        st.op_offsets = ov.base + planned.ops_bytes
+        st.list_of_frame = st.op_offsets + 4 * (planned.n_lists + 1)
+        st.n_lists, st.n_frames = planned.n_lists, planned.n_frames
+        st.max_ops_per_list, st.max_marks_per_list = info.max_ops_per_list, info.max_marks_per_list
+        st.max_cells_per_list = info.max_cells_per_list
+        st.frame_width, st.frame_height = planned.width, planned.height
+        st.upload_bytes = planned.buffer.nbytes
+        return ov
 
 
 def reads_source_rows_once(frame_shape, width, height):

@@ -88,6 +88,14 @@ typedef struct aiko_b200_overlay {
   int32_t max_marks_per_list;
   int32_t max_cells_per_list;
   int32_t frame_width, frame_height;
+  /* Optional: the planned buffer (ops | op_offsets | list_of_frame, contiguous from `ops`) still sits
+   * in page-locked HOST memory; the call that draws the overlay first copies upload_bytes from here to
+   * `ops` on its stream, so a list that changes every call costs no extra call.  Up to 16 KB travel as
+   * a kernel argument (the host bytes are read before the call returns; the device buffer must hold
+   * upload_bytes rounded up to 16), more as one cudaMemcpyAsync (the host buffer then has to be
+   * page-locked and stay untouched until the copy has run).  NULL = the device buffers are filled. */
+  const void* upload_from_host;
+  uint64_t upload_bytes;
 } aiko_b200_overlay;
 
 /* ---------------------------------------------------------------------- */

@@ -38,7 +38,7 @@ def test_version_and_error_string_without_gpu():
 
 def test_overlay_op_struct_layout():
     assert ctypes.sizeof(_native.OverlayOp) == 32
-    assert ctypes.sizeof(_native.Overlay) == 80    # 5 pointers + 10 int32
+    assert ctypes.sizeof(_native.Overlay) == 96    # 6 pointers + 10 int32 + uint64
 
 
 def test_zero_copy_eligibility_rule():
