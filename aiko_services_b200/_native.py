@@ -80,6 +80,8 @@ SIGNATURES = {
     "aiko_b200_audio_prepare": [_vp, _sz, _i, _vp],
     "aiko_b200_audio_chain": [_vp, _i, _i, _i, ctypes.c_double, _vp, _vp, ctypes.POINTER(_i), _vp, _vp, _vp, _i, _i,
                               _vp, _sz, _vp],
+    "aiko_b200_audio_filter_f64": [_vp, _vp, _i, _i, _i64, _vp, _vp, _vp, _vp],
+    "aiko_b200_audio_bands_f64": [_vp, _vp, _i, _i, _i64, _vp, _vp, _vp],
     "aiko_b200_overlay_u8": [_vp, _vp, _i, _i, _i, _i, _i64, _i64, _ovp, _vp],
     "aiko_b200_swap_rb_u8": [_vp, _vp, _i64, _vp],
     "aiko_b200_bgr2gray_u8": [_vp, _vp, _i64, _i, _vp],

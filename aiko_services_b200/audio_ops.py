@@ -82,3 +82,53 @@ def audio_chain(audio, sample_rate, *, bands=True, top=True, stream=None):
     if top:
         out["top_frequencies"], out["top_amplitudes"], out["top_count"] = tf, ta, tc
     return out
+
+
+def _f64_windows(x, device, name):
+    """ndarray / sequence / tensor -> contiguous float64 CUDA tensor [windows, n]; -> (tensor, single)"""
+    if not isinstance(x, torch.Tensor):
+        x = torch.from_numpy(np.ascontiguousarray(np.asarray(x, dtype=np.float64)))
+    single = x.dim() == 1
+    if single:
+        x = x[None]
+    if x.dim() != 2:
+        raise ValueError(f"{name}: expected [n] or [windows, n]")
+    return x.to(device=device, dtype=torch.float64).contiguous(), single
+
+
+def audio_filter(amplitudes, frequencies, device=None, stream=None):
+    """PE_AudioFilter (audio_io.py:216-227) on arrays from anywhere: float64 in and out, on the GPU.
+    -> (frequencies [windows, 100], amplitudes [windows, 100], count [windows]) CUDA tensors
+    (leading dimension dropped for a single window)."""
+    device = torch.device(device if device is not None else
+                          (amplitudes.device if isinstance(amplitudes, torch.Tensor) and amplitudes.is_cuda else "cuda"))
+    a, single = _f64_windows(amplitudes, device, "audio_filter amplitudes")
+    f, f_single = _f64_windows(frequencies, device, "audio_filter frequencies")
+    b, n = a.shape
+    if f.shape[1] != n or f.shape[0] not in (1, b):
+        raise ValueError("audio_filter: amplitudes and frequencies differ in shape")
+    tf = torch.empty((b, 100), dtype=torch.float64, device=device)
+    ta = torch.empty((b, 100), dtype=torch.float64, device=device)
+    tc = torch.empty((b,), dtype=torch.int32, device=device)
+    with torch.cuda.device(device):
+        check(_native.lib().aiko_b200_audio_filter_f64(a.data_ptr(), f.data_ptr(), b, n, 0 if f.shape[0] == 1 else n,
+                                                       tf.data_ptr(), ta.data_ptr(), tc.data_ptr(), _stream_ptr(stream)))
+    return (tf[0], ta[0], tc[0]) if single else (tf, ta, tc)
+
+
+def audio_bands(amplitudes, frequencies, device=None, stream=None):
+    """PE_AudioResampler (audio_io.py:253-277) on arrays from anywhere.
+    -> (band frequencies [windows, 8], band amplitudes [windows, 8]) float64 CUDA tensors."""
+    device = torch.device(device if device is not None else
+                          (amplitudes.device if isinstance(amplitudes, torch.Tensor) and amplitudes.is_cuda else "cuda"))
+    a, single = _f64_windows(amplitudes, device, "audio_bands amplitudes")
+    f, _ = _f64_windows(frequencies, device, "audio_bands frequencies")
+    b, n = a.shape
+    if f.shape[1] != n or f.shape[0] not in (1, b):
+        raise ValueError("audio_bands: amplitudes and frequencies differ in shape")
+    bf = torch.empty((b, 8), dtype=torch.float64, device=device)
+    ba = torch.empty((b, 8), dtype=torch.float64, device=device)
+    with torch.cuda.device(device):
+        check(_native.lib().aiko_b200_audio_bands_f64(a.data_ptr(), f.data_ptr(), b, n, 0 if f.shape[0] == 1 else n,
+                                                      bf.data_ptr(), ba.data_ptr(), _stream_ptr(stream)))
+    return (bf[0], ba[0]) if single else (bf, ba)

@@ -262,6 +262,21 @@ int aiko_b200_audio_chain(const void* audio, int dtype, int n_windows, int n_sam
                           float* top_amp, int* top_count, int gate_lo, int gate_hi, const void* workspace,
                           size_t workspace_bytes, void* stream);
 
+/* The same two elements for (amplitudes, frequencies) arrays that did not come from         */
+/* aiko_b200_audio_chain -- the reference's elements accept any float64 array pair                */
+/* (audio_io.py:213-216, 250-251).  float64 in, float64 out, one CTA per window:                  */
+/*   audio_filter_f64 : audio_io.py:216-227; outputs [n_windows][100] (|f|, a) sorted by a          */
+/*                      descending (ties in original order) and the number of valid entries.        */
+/*   audio_bands_f64  : audio_io.py:253-277; outputs [n_windows][8] band centres and band sums.     */
+/* frequency_stride: elements between the frequency rows of consecutive windows; 0 = one row        */
+/* shared by all windows (np.fft.fftfreq is the same for every window, audio_io.py:312-313).       */
+int aiko_b200_audio_filter_f64(const double* amplitudes, const double* frequencies, int n_windows, int n,
+                               int64_t frequency_stride, double* top_frequencies, double* top_amplitudes,
+                               int* top_count, void* stream);
+int aiko_b200_audio_bands_f64(const double* amplitudes, const double* frequencies, int n_windows, int n,
+                              int64_t frequency_stride, double* band_frequencies, double* band_amplitudes,
+                              void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,8 +1,12 @@
 """numpy float64 restatement of the reference's audio chain -- TEST INFRASTRUCTURE.
 
-The reference code sits inside a module-level string literal and cannot be imported or run
-(R/elements/media/audio_io.py:162-642), so there is no reference output to pin this against:
-PARITY UNPINNED.  Each function follows the cited lines; only what cannot execute is changed
+The reference code sits inside a module-level string literal and cannot be imported
+(R/elements/media/audio_io.py:162-642).  PINNED all the same: tests/golden/make_golden_audio.py cuts
+the statement lines of the three process_frame bodies out of the reference file at run time,
+exec()s them on the seeded config-5 windows and stores the results (tests/golden/golden_audio.npz);
+tests/test_oracle_golden.py checks this restatement against those vectors, and the generator
+asserts exact equality when it runs.  Each function follows the cited lines; only what cannot
+execute is changed
 (``StreamEvent.AIKO`` does not exist; ``fftfreq`` uses the window's own length and rate instead
 of the microphone constants of :312-313).  The MQTT / LED side effect of :279-290 is left out.
 """

@@ -131,3 +131,115 @@ def test_audio_elements_in_pipeline(cuda, tmp_path):
         tf, ta = A.pe_audio_filter(amp, freq)
         assert len(swag["amplitudes"]) == len(ta)
         np.testing.assert_allclose(np.sort(swag["amplitudes"])[::-1], ta, rtol=1e-4)
+
+
+# ---- against the vectors computed by the reference's own statements (tests/golden/golden_audio.npz) ----
+def _golden_audio():
+    import os
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_audio.npz"))
+
+
+def test_audio_chain_vs_reference_statement_golden(cuda):
+    """The CUDA chain against what R/elements/media/audio_io.py:216-227,253-277,307-313 compute
+    (exec'd from the reference file by tests/golden/make_golden_audio.py), fp32 tolerance 1e-4."""
+    g = _golden_audio()
+    fs = int(g["sample_rate"])
+    w = windows_cfg5(24)
+    res = audio_ops.audio_chain(torch.from_numpy(w).to(cuda), fs)
+    np.testing.assert_array_equal(res["frequencies"], g["frequencies"])
+    np.testing.assert_allclose(res["band_frequencies"], g["band_frequencies"], rtol=1e-12)
+    amps = res["amplitudes"].cpu().numpy().astype(np.float64)
+    for k in range(24):
+        if f"w{k}/amplitudes" in g:
+            ref = g[f"w{k}/amplitudes"]
+            assert np.abs(amps[k] - ref).max() <= 1e-4 * np.abs(ref).max()
+            np.testing.assert_allclose(amps[k], ref, rtol=1e-4, atol=1e-4 * np.median(np.abs(ref)))
+        probe = g[f"w{k}/amplitude_probe"]
+        assert np.abs(amps[k][::97] - probe).max() <= 1e-4 * np.abs(probe).max() + 1e-4 * np.abs(amps[k]).max()
+        ba = g[f"w{k}/band_amplitudes"]
+        np.testing.assert_allclose(res["band_amplitudes"][k].cpu().numpy(), ba, rtol=1e-4, atol=1e-4 * np.abs(ba).max())
+        ta, tf = g[f"w{k}/top_amplitudes"], g[f"w{k}/top_frequencies"]
+        count = int(res["top_count"][k])
+        ga = res["top_amplitudes"][k].cpu().numpy()[:count]
+        gf = res["top_frequencies"][k].cpu().numpy()[:count]
+        # a bin within 1e-4 of a gate edge may fall on either side in fp32: compare the clear ones
+        edge = np.sum((np.abs(amps[k] - 0.1) < 2e-5) | (np.abs(amps[k] - 12) < 2e-3))
+        if edge == 0 and len(ta) < 100:
+            assert count == len(ta)
+            np.testing.assert_allclose(ga, ta, rtol=1e-4)
+            np.testing.assert_allclose(np.sort(gf), np.sort(tf), rtol=1e-6, atol=1e-3)
+
+
+def test_audio_filter_and_bands_on_plain_arrays(cuda):
+    """float64 arrays from anywhere (not PE_FFT's fused results): same selection, order and ties as
+    the reference's Python (stable sort), sums to 1e-12."""
+    g = _golden_audio()
+    fs = int(g["sample_rate"])
+    w = windows_cfg5(24)
+    amps, freqs = zip(*[A.pe_fft(w[k], fs) for k in range(24)])
+    amps = np.stack(amps)
+    tf, ta, tc = audio_ops.audio_filter(amps, freqs[0], cuda)
+    bf, ba = audio_ops.audio_bands(amps, np.stack(freqs), cuda)
+    tf, ta, tc, bf, ba = (t.cpu().numpy() for t in (tf, ta, tc, bf, ba))
+    for k in range(24):
+        n = len(g[f"w{k}/top_amplitudes"])
+        assert tc[k] == n
+        np.testing.assert_allclose(ta[k][:n], g[f"w{k}/top_amplitudes"], rtol=1e-12)
+        np.testing.assert_array_equal(tf[k][:n], g[f"w{k}/top_frequencies"])
+        np.testing.assert_allclose(ba[k], g[f"w{k}/band_amplitudes"], rtol=1e-12)
+        np.testing.assert_allclose(bf[k], g["band_frequencies"], rtol=1e-15)
+    # more than 100 pass the gate, with many exact ties (quantised amplitudes): stable order decides
+    rng = np.random.default_rng(3)
+    a = np.round(rng.random((5, 4000)) * 13, 1)
+    f = rng.random((5, 4000)) * 20000 - 10000
+    f[3] = np.fft.fftfreq(4000, 1 / 16000)
+    tf, ta, tc = (t.cpu().numpy() for t in audio_ops.audio_filter(a, f, cuda))
+    for k in range(5):
+        rf, ra = A.pe_audio_filter(a[k], f[k])
+        assert tc[k] == len(ra) == 100
+        np.testing.assert_array_equal(ta[k], ra)
+        np.testing.assert_array_equal(tf[k], rf)
+    # nothing passes / a single window as a 1-D array
+    tf, ta, tc = audio_ops.audio_filter(np.zeros(64), np.arange(64.0), cuda)
+    assert int(tc) == 0
+    rf, ra = A.pe_audio_resampler(a[3], f[3])
+    bf, ba = audio_ops.audio_bands(a[3], f[3], cuda)
+    np.testing.assert_allclose(ba.cpu().numpy(), ra, rtol=1e-12)
+    np.testing.assert_allclose(bf.cpu().numpy(), rf, rtol=1e-15)
+
+
+def test_reference_audio_graph_definition_unchanged(cuda):
+    """R/examples/pipeline/pipeline_mic_fft_graph.json: the PE_FFT / PE_AudioResampler / PE_AudioFilter
+    element definitions verbatim (inputs: amplitudes, frequencies only), without the microphone and
+    graph-window elements; module name as existing definitions would spell it for the media package."""
+    from aiko_services_b200.pipeline import Pipeline
+    mod = "aiko_services.elements.media.audio_io"
+    two = [{"name": "amplitudes", "type": "bytes"}, {"name": "frequencies", "type": "bytes"}]
+    d = {"version": 0, "name": "p_mic_fft_graph", "runtime": "python",
+         "graph": ["(PE_FFT PE_AudioResampler PE_AudioFilter)"], "parameters": {},
+         "elements": [
+             {"name": "PE_FFT", "input": [{"name": "audio", "type": "bytes"}], "output": two,
+              "deploy": {"local": {"module": mod}}},
+             {"name": "PE_AudioResampler", "input": two, "output": [], "deploy": {"local": {"module": mod}}},
+             {"name": "PE_AudioFilter", "input": two, "output": two, "deploy": {"local": {"module": mod}}}]}
+    p = Pipeline(d)
+    g = _golden_audio()
+    w = windows_cfg5(24)
+    assert p.create_stream("mic")
+    for k in (0, 5, 17):
+        okay, swag = p.process_frame({"stream_id": "mic", "frame_id": k}, {"audio": w[k]})
+        assert okay
+        ta = g[f"w{k}/top_amplitudes"]
+        assert len(swag["amplitudes"]) == len(ta) == len(swag["frequencies"])
+        np.testing.assert_allclose(swag["amplitudes"], ta, rtol=1e-4)
+        np.testing.assert_allclose(np.sort(swag["frequencies"]), np.sort(g[f"w{k}/top_frequencies"]), rtol=1e-6, atol=1e-3)
+        bf, ba = p.streams["mic"].variables["audio_bands"]
+        np.testing.assert_allclose(ba, g[f"w{k}/band_amplitudes"], rtol=1e-4, atol=1e-4 * np.abs(ba).max())
+    # arrays from another element (plain float64 ndarrays) go through the float64 GPU path
+    flt = p.elements["PE_AudioFilter"]
+    amp, freq = A.pe_fft(w[3], 16000)
+    p._enable_thread_local(p.streams["mic"], 99)
+    event, out = flt.process_frame(p.streams["mic"], amp, freq)
+    p._disable_thread_local()
+    np.testing.assert_allclose(out["amplitudes"], g["w3/top_amplitudes"], rtol=1e-12)
+    np.testing.assert_array_equal(out["frequencies"], g["w3/top_frequencies"])

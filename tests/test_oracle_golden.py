@@ -85,3 +85,39 @@ def test_resize_norm_f32_matches_numpy():
     ref = ((u8.astype(np.float32) / np.float32(255) - np.asarray(mean, np.float32)) /
            np.asarray(std, np.float32)).transpose(2, 0, 1)
     np.testing.assert_array_equal(O.resize_norm_f32(img, 56, 56, mean, std), ref)
+
+
+# ---- audio chain: the restatement against vectors produced by the reference's own statements --------
+def _audio_golden():
+    import os
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_audio.npz"))
+
+
+def test_audio_oracle_matches_the_reference_statements():
+    """tests/golden/golden_audio.npz holds what R/elements/media/audio_io.py:216-227,253-277,307-313
+    compute (exec'd from the reference file) on the config-5 windows; numpy's FFT may differ in the
+    last bits between builds, hence 1e-12 instead of equality on the magnitudes."""
+    from golden.make_golden_audio import windows_cfg5
+    from oracle import audio as A
+    g = _audio_golden()
+    fs = int(g["sample_rate"])
+    w = windows_cfg5(24)
+    for k in range(24):
+        amp, freq = A.pe_fft(w[k], fs)
+        np.testing.assert_array_equal(freq, g["frequencies"])
+        np.testing.assert_allclose(amp[::97], g[f"w{k}/amplitude_probe"], rtol=1e-12, atol=1e-15)
+        if f"w{k}/amplitudes" in g:
+            np.testing.assert_allclose(amp, g[f"w{k}/amplitudes"], rtol=1e-12, atol=1e-15)
+        bf, ba = A.pe_audio_resampler(amp, freq)
+        np.testing.assert_array_equal(bf, g["band_frequencies"])
+        np.testing.assert_allclose(ba, g[f"w{k}/band_amplitudes"], rtol=1e-12)
+        tf, ta = A.pe_audio_filter(amp, freq)
+        np.testing.assert_array_equal(tf, g[f"w{k}/top_frequencies"])
+        np.testing.assert_allclose(ta, g[f"w{k}/top_amplitudes"], rtol=1e-12)
+    rng = np.random.default_rng(77)
+    x = (rng.standard_normal(9600) * 4000).astype(np.float32)
+    x += 30000 * np.sin(2 * np.pi * 440 * np.arange(9600) / 48000).astype(np.float32)
+    amp, freq = A.pe_fft(x, 48000)
+    np.testing.assert_allclose(amp, g["f32_9600/amplitudes"], rtol=1e-12, atol=1e-15)
+    tf, ta = A.pe_audio_filter(amp, freq)
+    np.testing.assert_array_equal(tf, g["f32_9600/top_frequencies"])
