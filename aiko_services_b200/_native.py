@@ -74,6 +74,8 @@ SIGNATURES = {
     "aiko_b200_resize_bicubic_prepare": [_vp, _sz, _i, _i, _i, _i, _vp],
     "aiko_b200_resize_bicubic_aa_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp, _sz, _vp],
     "aiko_b200_resize_bicubic_aa_u8_noalloc": [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp],
+    "aiko_b200_premultiply_u8": [_vp, _vp, _i64, _i, _i, _vp],
+    "aiko_b200_gather_nearest_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp],
     "aiko_b200_resize_norm_f32_nchw": [_vp, _i, _i, _i, _vp, _i, _i, ctypes.POINTER(ctypes.c_float),
                                        ctypes.POINTER(ctypes.c_float), _vp],
     "aiko_b200_audio_workspace_bytes": [_i],

@@ -285,8 +285,10 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, q = lane & 3;
   const int nwarps = (int)blockDim.x / 32 - 1;   // consumer warps; the last warp feeds the TMA ring
-  if (__ldg(p.ws + 1) != 0) __trap();   // a weight or window outside what the tables can hold (cannot happen
-                                        // for the sizes MmaPlan.ok admits; better loud than wrong)
+  // A weight or window outside what the tables can hold (cannot happen for the sizes MmaPlan.ok
+  // admits): prepare left a non-zero word 1 in the workspace, which the host reports; the kernel
+  // leaves the output alone instead of trapping (a trap would poison the whole CUDA context).
+  if (__ldg(p.ws + 1) != 0) return;
   const int row_bytes = p.sw * C;
   if (threadIdx.x == 0) {
     for (int s = 0; s < kMmaStages; s++) {
@@ -303,7 +305,7 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
     const uint64_t policy = l2_policy_evict_first();   // source rows are read once (plus the band halo)
     for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
       const MmaItem it = mma_item<KX, C>(p, item);
-      if (it.copy_bytes + (UA ? 32 : 0) > p.raw_pitch) __trap();
+      if (it.copy_bytes + (UA ? 32 : 0) > p.raw_pitch) continue;   // (consumers skip the same items)
       const uint8_t* fsrc = p.src + (size_t)it.frame * p.sh * row_bytes + it.byte_lo;
       for (int b = 0; b < it.nbatches; b++, gb++) {
         const int s = gb % kMmaStages, round = gb / kMmaStages;
@@ -337,6 +339,7 @@ __global__ void __launch_bounds__((WarpBudget<KX, T>::max_warps + 1) * 32, 1) bi
   int gb = 0;
   for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
     const MmaItem it = mma_item<KX, C>(p, item);
+    if (it.copy_bytes + (UA ? 32 : 0) > p.raw_pitch) continue;     // never true for admitted sizes; see the producer
     if (it.tile0 != cur_tile0) {     // first item of the CTA (and never again when the grid is a multiple of the chunks)
       cur_tile0 = it.tile0;
       const int wtile0 = it.tile0 + warp * T;

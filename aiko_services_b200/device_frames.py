@@ -52,7 +52,7 @@ class DeviceBatch:
         h, w = self._source.shape[1:3]
         c = self._source.shape[3] if self._source.dim() == 4 else 1
         for step in self._recipe:
-            if step[0] in ("resize_linear", "resize_bicubic"):
+            if step[0] in ("resize_linear", "resize_bicubic", "resize_pil"):
                 w, h = step[1], step[2]
             elif step[0] == "convert":
                 c = {"RGB2BGR": 3, "BGR2RGB": 3, "RGB2GRAY": 1, "BGR2GRAY": 1, "GRAY2BGR": 3}[step[1]]
@@ -149,6 +149,8 @@ class DeviceBatch:
                 continue
             if kind == "resize_bicubic":
                 t = ops.resize_bicubic_aa(t, step[1], step[2])
+            elif kind == "resize_pil":
+                t = ops.resize_pil(t, step[3], step[1], step[2])
             elif kind == "overlay":
                 gray = t.dim() == 3
                 h, w = t.shape[1:3]
@@ -231,10 +233,19 @@ class DeviceImage:
     def astype(self, dtype):
         return np.asarray(self).astype(dtype)
 
+    pil_mode = None        # set for frames that came in as PIL images: the mode they go out with
+    pil_palette = None
+
     def to_pil(self):
         from PIL import Image
         a = np.asarray(self)
-        return Image.fromarray(a, "L" if a.ndim == 2 else "RGB")
+        mode = self.pil_mode or ("L" if a.ndim == 2 else {2: "LA", 3: "RGB", 4: "RGBA"}[a.shape[2]])
+        if mode == "1":
+            return Image.fromarray(a > 0)
+        image = Image.fromarray(a, mode)
+        if mode == "P" and self.pil_palette is not None:
+            image.putpalette(self.pil_palette[1], self.pil_palette[0])
+        return image
 
 
 def group_device_images(images):

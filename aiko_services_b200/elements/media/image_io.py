@@ -62,29 +62,53 @@ def _apply(stream, images, step):
 # ---- behaviour shared by both bindings ------------------------------------------------------
 def logic_image_resize(element, stream, images):
     """ImageResize.process_frame (image_io.py:208-220): ndarray frames take cv2's bilinear
-    arithmetic, PIL frames take Pillow's antialiased bicubic arithmetic."""
+    arithmetic, PIL frames take what PIL.Image.resize does for their mode (antialiased bicubic;
+    RGBA / LA premultiplied around it; P / 1 nearest)."""
+    from ... import ops
     resolution, _ = element.get_parameter("resolution")
     width, height = resolution.split("x")
     width, height = int(width), int(height)
-    arrays = [i for i, im in enumerate(images) if isinstance(im, (np.ndarray, DeviceImage))]
-    pil = [i for i in range(len(images)) if i not in set(arrays)]
     out = [None] * len(images)
-    for idx, kind in ((arrays, "resize_linear"), (pil, "resize_bicubic")):
-        if idx:
-            for i, r in zip(idx, _apply(stream, [images[i] for i in idx], (kind, width, height))):
-                out[i] = r
-    if pil:   # the reference returns PIL images for PIL inputs
-        for i in pil:
-            out[i] = _LazyPil(out[i])
+    arrays = [i for i, im in enumerate(images) if isinstance(im, (np.ndarray, DeviceImage)) and not isinstance(im, _LazyPil)]
+    if arrays:
+        for i, r in zip(arrays, _apply(stream, [images[i] for i in arrays], ("resize_linear", width, height))):
+            out[i] = r
+    by_mode = {}
+    for i, im in enumerate(images):
+        if out[i] is None and i not in arrays:
+            mode = getattr(im, "pil_mode", None) or getattr(im, "mode", None)
+            if mode not in ops.PIL_PLAIN_MODES + ops.PIL_ALPHA_MODES + ops.PIL_NEAREST_MODES:
+                return StreamEvent.ERROR, {"diagnostic": f"ImageResize: PIL mode {mode!r} is not supported on the GPU "
+                                                         "(8-bit modes L, LA, RGB, RGBA, CMYK, YCbCr, HSV, LAB, P, 1)"}
+            by_mode.setdefault(mode, []).append(i)
+    for mode, idx in by_mode.items():
+        frames = []
+        for i in idx:
+            im = images[i]
+            if isinstance(im, _LazyPil):
+                frames.append(im)
+            else:
+                a = np.asarray(im)
+                frames.append(a.astype(np.uint8) * 255 if mode == "1" else a)
+        for i, r in zip(idx, _apply(stream, frames, ("resize_pil", width, height, mode))):
+            palette = getattr(images[i], "pil_palette", None)
+            if palette is None and mode == "P":
+                palette = (images[i].palette.mode, images[i].getpalette(None))
+            out[i] = _LazyPil(r, mode, palette)      # the reference returns PIL images for PIL inputs
     return StreamEvent.OKAY, {"images": out}
 
 
 class _LazyPil(DeviceImage):
-    """A DeviceImage that came from a PIL input: ``save`` / ``size`` like the PIL image the
+    """A DeviceImage that came from a PIL input: ``save`` / ``size`` / ``mode`` like the PIL image the
     reference would have produced, pixels still on the GPU until asked for."""
 
-    def __init__(self, image):
+    def __init__(self, image, mode="RGB", palette=None):
         super().__init__(image.batch, image.index)
+        self.pil_mode, self.pil_palette = mode, palette
+
+    @property
+    def mode(self):
+        return self.pil_mode
 
     @property
     def size(self):
@@ -244,7 +268,7 @@ def _cross_stream(prepare):
 
 
 def _prepare_resize(element, stream, images):
-    if any(not isinstance(im, (np.ndarray, DeviceImage)) for im in images):
+    if any(not isinstance(im, (np.ndarray, DeviceImage)) or isinstance(im, _LazyPil) for im in images):
         return logic_image_resize(element, stream, images)       # PIL frames: per-stream path
     resolution, _ = element.get_parameter("resolution")
     width, height = (int(v) for v in resolution.split("x"))

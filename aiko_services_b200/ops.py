@@ -250,6 +250,9 @@ def bicubic_workspace(device, sh, sw, dh, dw, stream=None):
                                                                  _stream_ptr(stream)))
         # later calls may come from other streams: make the tables visible to all of them
         (stream or torch.cuda.current_stream()).synchronize()
+        if nbytes >= 8 and int(ws[:8].view(torch.int32)[1]) != 0:      # set by prepare when a table overflowed
+            raise _native.NativeError(_native.ERR_UNSUPPORTED,
+                                      f"resize_bicubic_aa: weight tables cannot hold {sw}x{sh} -> {dw}x{dh}")
         _bicubic_plans[key] = ws
     return ws
 
@@ -267,6 +270,66 @@ def resize_bicubic_aa(src, width, height, *, out=None, stream=None):
         check(_native.lib().aiko_b200_resize_bicubic_aa_u8(src.data_ptr(), n, h, w, c, out.data_ptr(), height, width,
                                                            ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
     return out
+
+
+PIL_PLAIN_MODES = ("L", "RGB", "CMYK", "YCbCr", "HSV", "LAB")     # 8-bit bands, filtered band by band
+PIL_ALPHA_MODES = ("LA", "RGBA")                                  # premultiplied around the filter
+PIL_NEAREST_MODES = ("P", "1")                                    # Image.resize forces NEAREST
+_nearest_tables = {}
+
+
+def premultiply(src, *, inverse=False, channels=None, out=None, stream=None):
+    """Pillow's RGBA -> RGBa / LA -> La conversion (and back with ``inverse``).  Forward: ``src``
+    [..., 2 or 4] -> [..., 4]; inverse: ``src`` [..., 4] -> [..., channels]."""
+    _require_cuda(src, "premultiply src")
+    c = int(channels if inverse else src.shape[-1])
+    shape = tuple(src.shape[:-1]) + ((c,) if inverse else (4,))
+    out = _out(out, shape, src.device, "premultiply out")
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_premultiply_u8(src.data_ptr(), out.data_ptr(), src.numel() // src.shape[-1], c,
+                                                     int(bool(inverse)), _stream_ptr(stream)))
+    return out
+
+
+def _nearest_table(src, dst):
+    """Source index per destination index as Pillow's ImagingScaleAffine tabulates it: the position
+    starts at 0.5 * (src / dst) and grows by src / dst per step, summed sequentially in double."""
+    a = src / dst
+    pos = np.add.accumulate(np.concatenate([[a * 0.5], np.full(dst - 1, a)]))
+    idx = np.where(pos < 0.0, -1, pos.astype(np.int64))
+    return np.where((idx >= 0) & (idx < src), idx, -1).astype(np.int32)
+
+
+def resize_nearest_pil(src, width, height, *, out=None, stream=None):
+    """PIL.Image.resize((width, height), NEAREST) -- what Pillow does for modes P and 1."""
+    _require_cuda(src, "resize_nearest_pil src")
+    n, h, w, c, gray = _nhwc(src)
+    shape = (n, height, width) if gray else (n, height, width, c)
+    out = _out(out, shape, src.device, "resize_nearest_pil out")
+    key = (str(src.device), h, w, height, width)
+    tabs = _nearest_tables.get(key)
+    if tabs is None:
+        tabs = _nearest_tables[key] = (torch.from_numpy(_nearest_table(w, width)).to(src.device),
+                                       torch.from_numpy(_nearest_table(h, height)).to(src.device))
+        torch.cuda.current_stream(src.device).synchronize()
+    with torch.cuda.device(src.device):
+        check(_native.lib().aiko_b200_gather_nearest_u8(src.data_ptr(), n, h, w, c, out.data_ptr(), height, width,
+                                                        tabs[0].data_ptr(), tabs[1].data_ptr(), _stream_ptr(stream)))
+    return out
+
+
+def resize_pil(src, mode, width, height, *, stream=None):
+    """PIL.Image.resize((width, height)) for frames of PIL mode ``mode`` (uint8 [N, H, W(, bands)]):
+    antialiased bicubic per band; RGBA / LA premultiplied around it; P / 1 nearest."""
+    if mode in PIL_PLAIN_MODES:
+        return resize_bicubic_aa(src, width, height, stream=stream)
+    if mode in PIL_ALPHA_MODES:
+        pre = premultiply(src, stream=stream)
+        return premultiply(resize_bicubic_aa(pre, width, height, stream=stream), inverse=True,
+                           channels=src.shape[-1], stream=stream)
+    if mode in PIL_NEAREST_MODES:
+        return resize_nearest_pil(src, width, height, stream=stream)
+    raise ValueError(f"PIL mode {mode!r} is not supported (8-bit modes only)")
 
 
 def resize_norm_f32(src, width, height, mean, std, *, out=None, stream=None):

@@ -435,21 +435,27 @@ class Pipeline:
             # STOP still processes queued frames, ERROR ignores them (R/main/stream.py:48-53)
             jobs.append({"stream": stream, "frame_id": frame_id, "frame": frame,
                          "alive": stream.state in (StreamState.RUN, StreamState.STOP), "t0": time.monotonic()})
-        path = self.graph_path()
-        for node in path:
-            element = self.elements[node]
-            live = [j for j in jobs if j and j["alive"]]
-            if not live:
-                break
-            t_node = time.monotonic()
-            if element.batch_across_streams and len(live) > 1:
-                self._call_batched(element, live)
-            else:
+        # every stream walks the path that starts at ITS head (stream.graph_path, R/main/pipeline.py:1156);
+        # frames are batched across the streams that share a path
+        by_path = OrderedDict()
+        for job in jobs:
+            if job:
+                by_path.setdefault(tuple(self.graph_path(job["stream"].graph_path)), []).append(job)
+        for path, members in by_path.items():
+            for node in path:
+                element = self.elements[node]
+                live = [j for j in members if j["alive"]]
+                if not live:
+                    break
+                t_node = time.monotonic()
+                if element.batch_across_streams and len(live) > 1:
+                    self._call_batched(element, live)
+                else:
+                    for job in live:
+                        self._call_one(element, job)
+                dt = time.monotonic() - t_node
                 for job in live:
-                    self._call_one(element, job)
-            dt = time.monotonic() - t_node
-            for job in live:
-                job["frame"].metrics.setdefault("pipeline_elements", {})[f"time_{node}"] = dt
+                    job["frame"].metrics.setdefault("pipeline_elements", {})[f"time_{node}"] = dt
         # The graph has been walked: whatever the elements left as lazy device work is enqueued now
         # (asynchronously), so it overlaps the next frame's host work and the previous frame's read-back.
         launched = set()

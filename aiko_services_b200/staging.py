@@ -6,6 +6,7 @@ frames into a pinned buffer and enqueues one asynchronous copy; buffers rotate s
 fill the next batch while the previous copy is in flight.
 """
 import os
+from contextlib import nullcontext as _nullcontext
 
 import numpy as np
 import torch
@@ -117,8 +118,15 @@ class FrameStager:
                 if idx == list(range(len(b))):
                     out.append((b, positions))
                 else:
-                    sel = torch.as_tensor(idx, device=b.device)
-                    out.append((DeviceBatch(b.tensor.index_select(0, sel).contiguous(), b.stream), positions))
+                    # a subset / reordering of a batch: gather ON THE BATCH'S STREAM (its frames are
+                    # produced there; the gathered tensor is then owned by that stream's allocator pool)
+                    source = b.tensor
+                    with torch.cuda.stream(b.stream) if b.stream is not None else _nullcontext():
+                        sel = torch.as_tensor(idx, device=b.device)
+                        gathered = source.index_select(0, sel).contiguous()
+                    sub = DeviceBatch(gathered, b.stream)
+                    sub.stager = b.stager
+                    out.append((sub, positions))
             else:
                 arrs = [images[p] if isinstance(images[p], np.ndarray) else np.asarray(images[p]) for p in positions]
                 block = self._owned_block(arrs)

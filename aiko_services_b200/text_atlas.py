@@ -99,6 +99,31 @@ class _DeviceAtlas:
         self.n_patches = self.n_luts = 0
         self.version = None
         self.ready = None            # event: the last append has been enqueued before it
+        self._stage = None
+
+    STAGE_BYTES = 1 << 18
+
+    def _push(self, dst, address, nbytes, dtype, shape, stream):
+        """Host rows at ``address`` -> ``dst`` (device view).  Small appends (border variants made while
+        frames are in flight) go through page-locked staging and never stall the stream; the bulk
+        upload at start-up is an ordinary copy."""
+        import torch
+        src = np.frombuffer((ctypes.c_uint8 * nbytes).from_address(address), np.uint8)
+        if nbytes > self.STAGE_BYTES:
+            dst.copy_(torch.from_numpy(src.view(dtype).reshape(shape).copy()))
+            return
+        if self._stage is None:
+            self._stage = [[torch.empty(self.STAGE_BYTES, dtype=torch.uint8).pin_memory(), None] for _ in range(4)]
+            self._stage_next = 0
+        slot = self._stage[self._stage_next]
+        self._stage_next = (self._stage_next + 1) % len(self._stage)
+        if slot[1] is not None:
+            slot[1].synchronize()
+        slot[0][:nbytes].numpy()[...] = src
+        dst.copy_(slot[0][:nbytes].view(dst.dtype).view(dst.shape), non_blocking=True)
+        if slot[1] is None:
+            slot[1] = torch.cuda.Event()
+        slot[1].record(stream)
 
     def sync(self, view):
         """Copy the rows the host has appended since the last call; work that uses the tables on
@@ -110,15 +135,15 @@ class _DeviceAtlas:
         if self.ready is not None:
             stream.wait_event(self.ready)
         if view.n_patches > self.n_patches:
-            count = (view.n_patches - self.n_patches) * view.patch_h * view.patch_w
-            src = (ctypes.c_int16 * count).from_address(view.patch_ids_host + 2 * self.n_patches * view.patch_h * view.patch_w)
-            host = torch.from_numpy(np.frombuffer(src, np.int16).reshape(-1, view.patch_h, view.patch_w).copy())
-            self.patch_ids[self.n_patches:view.n_patches].copy_(host)
+            per = view.patch_h * view.patch_w
+            rows = view.n_patches - self.n_patches
+            self._push(self.patch_ids[self.n_patches:view.n_patches], view.patch_ids_host + 2 * self.n_patches * per,
+                       2 * rows * per, np.int16, (rows, view.patch_h, view.patch_w), stream)
             self.n_patches = view.n_patches
         if view.n_luts > self.n_luts:
-            src = (ctypes.c_uint8 * ((view.n_luts - self.n_luts) * 256)).from_address(view.luts_host + 256 * self.n_luts)
-            host = torch.from_numpy(np.frombuffer(src, np.uint8).reshape(-1, 256).copy())
-            self.luts[self.n_luts:view.n_luts].copy_(host)
+            rows = view.n_luts - self.n_luts
+            self._push(self.luts[self.n_luts:view.n_luts], view.luts_host + 256 * self.n_luts, 256 * rows, np.uint8,
+                       (rows, 256), stream)
             self.n_luts = view.n_luts
         self.version = view.version
         self.ready = torch.cuda.Event()

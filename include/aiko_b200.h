@@ -182,13 +182,33 @@ int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int src_h, int 
 /*             resize calls with that size pair, on any stream ordered after it.   */
 /* Frames are tight: [n, h, w, channels], channels in {1, 3, 4}.  The workspace      */
 /* holds the 22-bit coefficients and, for reductions up to ~5x, the same weights as  */
-/* integer-MMA operand tables (237 KB in all for 1080p -> 640x480).                  */
+/* integer-MMA operand tables (237 KB in all for 1080p -> 640x480).  After prepare,   */
+/* int32 word 1 of the workspace is non-zero if a table overflowed (not for any size  */
+/* the library admits); a resize with such a workspace leaves dst untouched.  Source  */
+/* rows that do not start on 16-byte boundaries are fetched from the boundary below   */
+/* to the boundary above: src must be readable for 15 bytes before its first and      */
+/* after its last byte (any cudaMalloc / torch allocation is).                        */
 size_t aiko_b200_resize_bicubic_workspace_bytes(int src_h, int src_w, int dst_h, int dst_w);
 int aiko_b200_resize_bicubic_prepare(void* workspace, size_t workspace_bytes, int src_h, int src_w, int dst_h,
                                      int dst_w, void* stream);
 int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, int src_h, int src_w, int channels,
                                    uint8_t* dst, int dst_h, int dst_w, const void* workspace,
                                    size_t workspace_bytes, void* stream);
+
+/* What PIL.Image.resize does around the filter for other modes (image_io.py:218 resizes   */
+/* whatever mode the file had):                                                             */
+/*   premultiply_u8 : RGBA (channels 4) / LA (channels 2) -> 4-byte premultiplied pixels     */
+/*                    (R, G, B, A) / (L, L, L, A) before the filter (inverse = 0), and back  */
+/*                    after it (inverse = 1); Pillow's MULDIV255 and CLIP8(255 * v / a).     */
+/*                    Run aiko_b200_resize_bicubic_aa_u8 with channels = 4 in between.       */
+/*   gather_nearest_u8 : modes P and 1 are resized with NEAREST: dst[y][x] = src[ytab[y]][xtab[x]]; */
+/*                    xtab / ytab (device int32, dst_w / dst_h entries; -1 = outside) are      */
+/*                    the source positions Pillow pretabulates: (int)(0.5 * s + k * s summed   */
+/*                    in double), s = src / dst.                                               */
+int aiko_b200_premultiply_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, int channels, int inverse,
+                             void* stream);
+int aiko_b200_gather_nearest_u8(const uint8_t* src, int n_frames, int src_h, int src_w, int channels, uint8_t* dst,
+                                int dst_h, int dst_w, const int32_t* xtab, const int32_t* ytab, void* stream);
 
 /* Same resize for callers that cannot allocate device memory where they call it    */
 /* (an element running on the pipeline's one event-loop thread, where cudaMalloc     */

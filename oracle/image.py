@@ -124,3 +124,58 @@ def resize_norm_f32(img, width, height, mean, std):
     rc = lib().orc_resize_norm_f32(_p(img), h, w, _p(out), height, width, _p(m), _p(s))
     assert rc == 0
     return out
+
+
+# ---- PIL.Image.resize for modes other than RGB / L (numpy restatement of Pillow's Convert.c / Geometry.c)
+def _muldiv255(a, b):
+    t = a.astype(np.uint32) * b.astype(np.uint32) + 128
+    return (((t >> 8) + t) >> 8).astype(np.uint8)
+
+
+def pil_premultiply(img):
+    """RGBA -> RGBa / LA -> La (Pillow rgbA2rgba, lA2la); LA comes back as 4 bands (L, L, L, A)."""
+    img = np.asarray(img, np.uint8)
+    if img.shape[2] == 2:
+        img = np.stack([img[:, :, 0]] * 3 + [img[:, :, 1]], axis=2)
+    out = img.copy()
+    for c in range(3):
+        out[:, :, c] = _muldiv255(img[:, :, c], img[:, :, 3])
+    return out
+
+
+def pil_unpremultiply(img, bands):
+    """RGBa -> RGBA / La -> LA (Pillow rgba2rgbA, la2lA): CLIP8(255 * v / alpha) unless alpha is 0 or 255."""
+    img = np.asarray(img, np.uint8)
+    a = img[:, :, 3].astype(np.uint32)
+    out = img.copy()
+    keep = (a == 0) | (a == 255)
+    for c in range(3):
+        q = np.minimum((255 * img[:, :, c].astype(np.uint32)) // np.maximum(a, 1), 255)
+        out[:, :, c] = np.where(keep, img[:, :, c], q).astype(np.uint8)
+    return out if bands == 4 else np.stack([out[:, :, 0], out[:, :, 3]], axis=2)
+
+
+def pil_nearest_table(src, dst):
+    """ImagingScaleAffine: position 0.5 * a, then += a per output index (a = src / dst, double)."""
+    a = src / dst
+    pos, tab = a * 0.5, []
+    for _ in range(dst):
+        i = -1 if pos < 0.0 else int(pos)
+        tab.append(i if 0 <= i < src else -1)
+        pos += a
+    return np.array(tab)
+
+
+def pil_resize(img, mode, width, height):
+    """PIL.Image.resize((width, height)) on the array of an image of PIL mode ``mode``
+    (R/elements/media/image_io.py:218 for whatever mode the file had)."""
+    img = np.asarray(img, np.uint8)
+    if mode in ("LA", "RGBA"):
+        return pil_unpremultiply(resize_bicubic_aa(pil_premultiply(img), width, height), img.shape[2])
+    if mode in ("P", "1"):
+        xt, yt = pil_nearest_table(img.shape[1], width), pil_nearest_table(img.shape[0], height)
+        out = img[np.clip(yt, 0, None)][:, np.clip(xt, 0, None)].copy()
+        out[yt < 0] = 0
+        out[:, xt < 0] = 0
+        return out
+    return resize_bicubic_aa(img, width, height)

@@ -49,3 +49,37 @@ def frame(seed, h, w, c):
     rng = np.random.default_rng(seed)
     img = rng.integers(0, 256, (h, w, c), dtype=np.uint8)
     return img[:, :, 0].copy() if c == 1 else img
+
+# PIL modes other than RGB through ImageResize's PIL branch: (name, seed, mode, src_h, src_w, dst_w, dst_h)
+RESIZE_PIL_MODES = [
+    ("rgba_down", 31, "RGBA", 108, 192, 64, 48),
+    ("rgba_up", 32, "RGBA", 30, 41, 100, 70),
+    ("la_down", 33, "LA", 90, 131, 50, 41),
+    ("la_up", 34, "LA", 20, 30, 64, 48),
+    ("l_down", 35, "L", 97, 131, 50, 41),
+    ("cmyk_down", 36, "CMYK", 64, 96, 40, 30),
+    ("p_down", 37, "P", 108, 192, 64, 48),
+    ("p_up_odd", 38, "P", 31, 47, 101, 67),
+    ("bilevel_down", 39, "1", 99, 150, 60, 40),
+    ("bilevel_up", 40, "1", 20, 33, 77, 50),
+]
+
+
+def pil_image(seed, mode, h, w):
+    """A seeded PIL image of ``mode``; alpha channels mix 0, 255 and everything between."""
+    from PIL import Image
+    rng = np.random.default_rng(seed)
+    bands = {"L": 1, "P": 1, "1": 1, "LA": 2, "RGB": 3, "RGBA": 4, "CMYK": 4}[mode]
+    a = rng.integers(0, 256, (h, w, bands), dtype=np.uint8)
+    if mode in ("LA", "RGBA"):
+        alpha = a[:, :, -1]
+        alpha[rng.random((h, w)) < 0.2] = 0
+        alpha[rng.random((h, w)) < 0.2] = 255
+    if mode == "1":
+        return Image.fromarray(a[:, :, 0] > 127)
+    if bands == 1:
+        im = Image.fromarray(a[:, :, 0], "L" if mode == "L" else "P")
+        if mode == "P":
+            im.putpalette(rng.integers(0, 256, 768, dtype=np.uint8).tobytes())
+        return im
+    return Image.fromarray(a, mode)

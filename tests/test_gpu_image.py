@@ -483,3 +483,32 @@ def test_overlay_ring_changing_lists(cuda, atlas):
         out = host(ops.resize_linear(d, W, H, overlay=ov))
         for k in range(2):
             np.testing.assert_array_equal(out[k], overlay_cpu(O.resize_linear(frames[k], W, H), overlay, atlas))
+
+
+def _pil_array(im, mode):
+    a = np.asarray(im)
+    return a.astype(np.uint8) * 255 if mode == "1" else a
+
+
+@pytest.mark.parametrize("case", cases.RESIZE_PIL_MODES, ids=lambda c: c[0])
+def test_pil_mode_resize_golden(cuda, case):
+    """ops.resize_pil against the reference's ImageResize on RGBA / LA / L / CMYK / P / 1 images
+    (tests/golden/golden_pil_modes.npz): premultiplied alpha around the filter, nearest for P and 1."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_pil_modes.npz"))
+    name, seed, mode, sh, sw, dw, dh = case
+    src = _pil_array(cases.pil_image(seed, mode, sh, sw), mode)
+    got = host(ops.resize_pil(dev(src[None], cuda), mode, dw, dh))[0]
+    np.testing.assert_array_equal(got, g[name])
+
+
+def test_pil_mode_resize_random_vs_oracle(cuda):
+    rng = np.random.default_rng(19)
+    for trial in range(24):
+        mode = ("RGBA", "LA", "P", "1")[trial % 4]
+        sh, sw = int(rng.integers(2, 200)), int(rng.integers(2, 300))
+        dh, dw = int(rng.integers(1, 160)), int(rng.integers(1, 200))
+        frames = np.stack([_pil_array(cases.pil_image(int(rng.integers(1 << 30)), mode, sh, sw), mode) for _ in range(3)])
+        got = host(ops.resize_pil(dev(frames, cuda), mode, dw, dh))
+        for k in range(3):
+            np.testing.assert_array_equal(got[k], O.pil_resize(frames[k], mode, dw, dh), err_msg=f"{mode} {sw}x{sh}->{dw}x{dh}")

@@ -231,3 +231,53 @@ def test_drop_in_inside_the_unmodified_reference_runtime(cuda):
             np.testing.assert_array_equal(np.asarray(im), r)
     finally:
         reference_adapter.uninstall()
+
+
+@pytest.mark.gpu
+def test_subset_of_a_lazy_batch_is_gathered_on_its_own_stream(cuda):
+    """An element that forwards only some images of a lazy batch: the gather must run after (and on
+    the stream of) the kernels that produce the frames, for many rounds without a synchronize."""
+    import numpy as np
+    from aiko_services_b200.staging import FrameStager
+    from golden import cases
+    from oracle import image as O
+    stager = FrameStager(cuda)
+    frames = [cases.frame(3100 + k, 540, 960, 3) for k in range(6)]
+    want = [O.resize_linear(f, 320, 180)[:, :, ::-1] for f in frames]
+    for _ in range(20):
+        (batch, _), = stager.upload(frames)
+        resized = batch.then("resize_linear", 320, 180).images()
+        picked = [resized[4], resized[1], resized[5]]
+        (sub, positions), = stager.upload(picked)
+        out = sub.then("convert", "RGB2BGR").host()
+        for k, src in zip(positions, (4, 1, 5)):
+            np.testing.assert_array_equal(out[k], want[src])
+
+
+@pytest.mark.gpu
+def test_pil_rgba_and_palette_images_through_the_elements(cuda, tmp_path):
+    """ImageReadFile -> ImageResize -> ImageWriteFile on RGBA and palette PNGs: the files written equal
+    what Pillow's own resize gives (mode kept, alpha premultiplied around the filter, P nearest)."""
+    from PIL import Image
+    for mode in ("RGBA", "P", "LA"):
+        src = cases.pil_image(4242, mode, 120, 200)
+        src.save(tmp_path / f"in_{mode}.png")
+        d = {"version": 0, "name": "p_png", "runtime": "python", "graph": ["(ImageReadFile ImageResize ImageWriteFile)"],
+             "parameters": {"resolution": "64x48"},
+             "elements": [
+                 {"name": "ImageReadFile", "input": [{"name": "paths", "type": "[path]"}],
+                  "output": [{"name": "images", "type": "[image]"}],
+                  "parameters": {"data_sources": f"(file://{tmp_path}/in_{mode}.png)", "data_batch_size": 1},
+                  "deploy": {"local": {"module": IMAGE_IO}}},
+                 {"name": "ImageResize", "input": [{"name": "images", "type": "[image]"}],
+                  "output": [{"name": "images", "type": "[image]"}], "deploy": {"local": {"module": IMAGE_IO}}},
+                 {"name": "ImageWriteFile", "input": [{"name": "images", "type": "[image]"}], "output": [],
+                  "parameters": {"data_targets": f"file://{tmp_path}/out_{mode}.png"},
+                  "deploy": {"local": {"module": IMAGE_IO}}}]}
+        p = Pipeline(d)
+        assert p.create_stream("1")
+        p.run()
+        got = Image.open(tmp_path / f"out_{mode}.png")
+        want = Image.open(tmp_path / f"in_{mode}.png").resize((64, 48))
+        assert got.mode == want.mode == mode
+        np.testing.assert_array_equal(np.asarray(got.convert("RGBA")), np.asarray(want.convert("RGBA")))

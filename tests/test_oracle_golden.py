@@ -121,3 +121,31 @@ def test_audio_oracle_matches_the_reference_statements():
     np.testing.assert_allclose(amp, g["f32_9600/amplitudes"], rtol=1e-12, atol=1e-15)
     tf, ta = A.pe_audio_filter(amp, freq)
     np.testing.assert_array_equal(tf, g["f32_9600/top_frequencies"])
+
+
+def _pil_array(im, mode):
+    a = np.asarray(im)
+    return a.astype(np.uint8) * 255 if mode == "1" else a
+
+
+@pytest.mark.parametrize("case", cases.RESIZE_PIL_MODES, ids=lambda c: c[0])
+def test_pil_mode_resize_oracle_vs_reference_golden(case):
+    """oracle.pil_resize (premultiplied RGBA / LA, nearest P / 1, plain CMYK / L) against the reference's
+    ImageResize run on PIL images of those modes (tests/golden/make_golden_pil_modes.py)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_pil_modes.npz"))
+    name, seed, mode, sh, sw, dw, dh = case
+    src = _pil_array(cases.pil_image(seed, mode, sh, sw), mode)
+    np.testing.assert_array_equal(O.pil_resize(src, mode, dw, dh), g[name])
+
+
+def test_pil_mode_resize_oracle_vs_pillow_random():
+    Image = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(9)
+    for trial in range(40):
+        mode = ("RGBA", "LA", "P", "1")[trial % 4]
+        sh, sw = int(rng.integers(1, 90)), int(rng.integers(1, 120))
+        dh, dw = int(rng.integers(1, 120)), int(rng.integers(1, 150))
+        im = cases.pil_image(int(rng.integers(1 << 30)), mode, sh, sw)
+        want = _pil_array(im.resize((dw, dh)), mode)
+        np.testing.assert_array_equal(O.pil_resize(_pil_array(im, mode), mode, dw, dh), want, err_msg=f"{mode} {sw}x{sh}->{dw}x{dh}")

@@ -194,3 +194,33 @@ def test_reference_modules_resolve_to_gpu_elements():
     assert module.__name__ == "aiko_services_b200.elements.media.image_io"
     for name in ("ImageOutput", "ImageOverlay", "ImageReadFile", "ImageResize", "ImageWriteFile"):
         assert issubclass(getattr(module, name), PipelineElement)
+
+
+def test_streams_walk_the_path_of_their_own_head(tmp_path):
+    """Two heads: a stream created with graph_path=B gets start_stream on B's elements AND its frames
+    run through B's elements (R/main/pipeline.py:1156 walks get_path(stream.graph_path) per frame)."""
+    import textwrap
+    from aiko_services_b200.pipeline import Pipeline
+    mod = tmp_path / "two_heads.py"
+    mod.write_text(textwrap.dedent("""
+        from aiko_services_b200.pipeline import PipelineElement
+        from aiko_services_b200.stream import StreamEvent
+
+        class Tag(PipelineElement):
+            def start_stream(self, stream, stream_id):
+                stream.variables.setdefault("started", []).append(self.name)
+                return StreamEvent.OKAY, None
+            def process_frame(self, stream, trail):
+                return StreamEvent.OKAY, {"trail": trail + [self.name]}
+    """))
+    io = [{"name": "trail", "type": "list"}]
+    element = lambda name: {"name": name, "input": io, "output": io,
+                            "deploy": {"local": {"module": str(mod), "class_name": "Tag"}}}
+    p = Pipeline({"version": 0, "name": "p_heads", "runtime": "python", "graph": ["(A A2)", "(B B2)"],
+                  "elements": [element(n) for n in ("A", "A2", "B", "B2")]})
+    assert p.create_stream("sa") and p.create_stream("sb", graph_path="B")
+    assert p.streams["sa"].variables["started"] == ["A", "A2"]
+    assert p.streams["sb"].variables["started"] == ["B", "B2"]
+    results = p.process_frames([({"stream_id": "sa", "frame_id": 0}, {"trail": []}),
+                                ({"stream_id": "sb", "frame_id": 0}, {"trail": []})])
+    assert [r[1]["trail"] for r in results] == [["A", "A2"], ["B", "B2"]]
