@@ -179,15 +179,53 @@ class _null:
 
 
 def logic_image_read_file(element, stream, paths):
-    """ImageReadFile.process_frame (image_io.py:180-191): lazy PIL open, decode deferred."""
+    """ImageReadFile.process_frame (image_io.py:180-191): lazy PIL open, decode deferred into the
+    consumer, exactly as the reference -- unless the parameter ``decode`` is "gpu": then baseline
+    colour JPEG files are decoded on the GPU (NVJPG engines / nvJPEG, aiko_services_b200.jpeg) and
+    handed on as device-resident frames that downstream elements treat as the RGB PIL images the
+    reference would have produced (ImageResize takes its PIL branch).  Other files stay lazy PIL."""
     from PIL import Image
-    images = []
-    for path in paths:
+    decode, _ = element.get_parameter("decode", default="host")
+    images = [None] * len(paths)
+    if str(decode).lower() == "gpu":
         try:
-            images.append(Image.open(path))
+            _read_jpegs_on_gpu(stream, paths, images)
         except Exception as exception:
-            return StreamEvent.ERROR, {"diagnostic": f"Error loading image: {exception}"}
+            return StreamEvent.ERROR, {"diagnostic": f"Error decoding image: {exception}"}
+    for k, path in enumerate(paths):
+        if images[k] is None:
+            try:
+                images[k] = Image.open(path)
+            except Exception as exception:
+                return StreamEvent.ERROR, {"diagnostic": f"Error loading image: {exception}"}
     return StreamEvent.OKAY, {"images": images}
+
+
+def _read_jpegs_on_gpu(stream, paths, images):
+    """Fills ``images[k]`` with a device-resident frame for every path that is a colour JPEG;
+    equal-sized files are decoded as one batch."""
+    from ... import jpeg
+    from ...device_frames import DeviceBatch
+    stager = stager_for(stream)
+    decoder = jpeg.decoder_for(stager.device)
+    groups = {}
+    for k, path in enumerate(paths):
+        with open(path, "rb") as f:
+            data = f.read()
+        if not jpeg.is_jpeg(data):
+            continue
+        width, height, components, _ = decoder.info(data)
+        if components != 3:
+            continue                      # gray / CMYK JPEGs keep the reference's host path
+        groups.setdefault((width, height), []).append((k, data))
+    import torch
+    for members in groups.values():
+        with torch.cuda.stream(stager.stream):
+            frames = decoder.decode([data for _, data in members], stream=stager.stream)
+        batch = DeviceBatch(frames, stager.stream)
+        batch.stager = stager
+        for image, (k, _) in zip(batch.images(), members):
+            images[k] = _LazyPil(image, "RGB")
 
 
 def logic_image_write_file(element, stream, images):

@@ -1,0 +1,119 @@
+"""JPEG frames decoded on the GPU (libaiko_b200_jpeg.so, include/aiko_b200_jpeg.h): the decode half of
+``PIL.Image.open(path)`` ... ``image.resize(...)`` (R/elements/media/image_io.py:184,218) so that
+frames are born device-resident instead of crossing PCIe as raw pixels.  The decoder is nvJPEG (the
+NVJPG hardware engines when available).  torch only provides the destination tensor and the stream."""
+import ctypes
+import os
+
+import torch
+
+from . import _native
+from ._native import NativeError
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libaiko_b200_jpeg.so")
+_vp, _i, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+SIGNATURES = {
+    "aiko_b200_jpeg_decoder_create": [ctypes.POINTER(_vp), _i, _i],
+    "aiko_b200_jpeg_decoder_destroy": [_vp],
+    "aiko_b200_jpeg_decoder_is_hardware": [_vp],
+    "aiko_b200_jpeg_last_error": [],
+    "aiko_b200_jpeg_info": [_vp, ctypes.c_char_p, _sz, ctypes.POINTER(_i), ctypes.POINTER(_i), ctypes.POINTER(_i),
+                            ctypes.POINTER(_i)],
+    "aiko_b200_jpeg_decode_rgb_u8": [_vp, _vp, _vp, _i, _vp, _i, _i, ctypes.c_int64, _vp],
+}
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: build it with `make -C aiko_services_b200/csrc` "
+                              "(there is no CPU decoder behind this module)")
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, argtypes in SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.argtypes = argtypes
+            fn.restype = ctypes.c_char_p if name.endswith("last_error") else ctypes.c_int
+        _lib = handle
+    return _lib
+
+
+def _check(code):
+    if code != 0:
+        msg = lib().aiko_b200_jpeg_last_error()
+        raise NativeError(code, msg.decode() if msg else "")
+
+
+def is_jpeg(data):
+    return len(data) > 3 and data[0] == 0xFF and data[1] == 0xD8 and data[2] == 0xFF
+
+
+class JpegDecoder:
+    """Batched JPEG -> uint8 [n, h, w, 3] RGB CUDA tensor.  One decoder per (GPU, thread)."""
+
+    def __init__(self, device, max_batch=64, backend=0):
+        self.device = torch.device(device)
+        self.max_batch = max_batch
+        self._handle = _vp()
+        with torch.cuda.device(self.device):
+            _check(lib().aiko_b200_jpeg_decoder_create(ctypes.byref(self._handle), backend, max_batch))
+        self.hardware = bool(lib().aiko_b200_jpeg_decoder_is_hardware(self._handle))
+
+    def info(self, data):
+        """-> (width, height, components, subsampling) from the JPEG header"""
+        w, h, c, s = _i(), _i(), _i(), _i()
+        _check(lib().aiko_b200_jpeg_info(self._handle, data, len(data), ctypes.byref(w), ctypes.byref(h),
+                                         ctypes.byref(c), ctypes.byref(s)))
+        return w.value, h.value, c.value, s.value
+
+    def decode(self, buffers, out=None, stream=None):
+        """``buffers``: list of bytes-like JPEG images of one size (bytes, or uint8 tensors in pinned
+        memory).  -> uint8 tensor [n, h, w, 3] on the device; work is enqueued on ``stream``."""
+        n = len(buffers)
+        if n == 0:
+            return torch.empty((0, 0, 0, 3), dtype=torch.uint8, device=self.device)
+        ptrs, lens, keep = (_vp * n)(), (_sz * n)(), []
+        for k, b in enumerate(buffers):
+            if isinstance(b, torch.Tensor):
+                ptrs[k], lens[k] = b.data_ptr(), b.numel()
+            else:
+                raw = bytes(b) if not isinstance(b, bytes) else b
+                keep.append(raw)
+                ptrs[k] = ctypes.cast(ctypes.c_char_p(raw), _vp).value
+                lens[k] = len(raw)
+        first = buffers[0]
+        head = bytes(first[:min(len(first), 1 << 16)].numpy().tobytes()) if isinstance(first, torch.Tensor) else keep[0]
+        w, h, _, _ = self.info(head)
+        if out is None:
+            out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=self.device)
+        s = stream if stream is not None else torch.cuda.current_stream(self.device)
+        with torch.cuda.device(self.device):
+            for start in range(0, n, self.max_batch):
+                count = min(self.max_batch, n - start)
+                _check(lib().aiko_b200_jpeg_decode_rgb_u8(
+                    self._handle, ctypes.byref(ptrs, start * ctypes.sizeof(_vp)), ctypes.byref(lens, start * ctypes.sizeof(_sz)),
+                    count, out[start].data_ptr(), h, w, h * w * 3, _vp(s.cuda_stream)))
+        return out
+
+    def close(self):
+        if self._handle:
+            lib().aiko_b200_jpeg_decoder_destroy(self._handle)
+            self._handle = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_decoders = {}
+
+
+def decoder_for(device, max_batch=64):
+    key = (str(torch.device(device)), max_batch)
+    if key not in _decoders:
+        _decoders[key] = JpegDecoder(device, max_batch)
+    return _decoders[key]

@@ -20,6 +20,24 @@ def _stream_ptr(stream=None):
     return ctypes.c_void_p(s.cuda_stream)
 
 
+class _on_device:
+    """``torch.cuda.device(dev)`` that costs nothing when ``dev`` already is the current device."""
+    __slots__ = ("ctx",)
+
+    def __init__(self, dev):
+        index = dev.index if dev.index is not None else torch.cuda.current_device()
+        self.ctx = None if index == torch.cuda.current_device() else torch.cuda.device(index)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *a):
+        if self.ctx is not None:
+            return self.ctx.__exit__(*a)
+        return False
+
+
 def _require_cuda(t, name, dtype=torch.uint8):
     if not isinstance(t, torch.Tensor) or not t.is_cuda:
         raise RuntimeError(f"{name}: expected a CUDA tensor (aiko_services_b200 has no CPU path)")
@@ -225,7 +243,7 @@ def resize_linear(src, width, height, *, swap_rb=False, overlay=None, out=None, 
     out = _out(out, shape, dev, "resize_linear out")
     if overlay is not None and overlay.n_ops == 0:      # nothing to draw
         overlay = None
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         check(_native.lib().aiko_b200_resize_linear_u8(
             src.data_ptr(), n, h, w, c, w * c, h * w * c, out.data_ptr(), height, width, width * c,
             height * width * c, int(bool(swap_rb)), overlay.pointer() if overlay is not None else None,

@@ -208,6 +208,8 @@ class PipelineElement:
         self.pipeline.create_frame(stream, frame_data, frame_id)
 
     def create_frames(self, stream, frame_generator, frame_id=FIRST_FRAME_ID, rate=None):
+        with self.pipeline._lock:
+            self.pipeline._generators += 1
         threading.Thread(target=self.pipeline._frames_generator, daemon=True,
                          args=(self, stream, frame_generator, int(frame_id), rate)).start()
 
@@ -264,6 +266,7 @@ class Pipeline:
         self.thread_local = threading.local()
         self.streams: Dict[str, Stream] = OrderedDict()
         self._pending = queue.Queue()           # (stream_id, frame_id, frame_data) from create_frame(s)
+        self._generators = 0                    # frame-generator threads still running
         self._lock = threading.RLock()
         heads, successors, _ = parse_graph(self.definition.graph)
         self._heads, self._successors = heads, successors
@@ -381,6 +384,8 @@ class Pipeline:
                     self.thread_local.frame_id = frame_id
         finally:
             self._disable_thread_local()
+            with self._lock:
+                self._generators -= 1
             self._pending.put((stream.stream_id, None, None))     # generator finished
 
     # -- the per-frame graph walk
@@ -545,7 +550,10 @@ class Pipeline:
             except queue.Empty:
                 pass
             if not batch:
-                if all(s.state != StreamState.RUN for s in self.streams.values()):
+                # done when nothing is queued and nobody can queue any more: every stream has stopped,
+                # or no frame generator is left running (a source that posted single frames with
+                # create_frame keeps its stream in RUN; the reference ends such streams by lease expiry)
+                if all(s.state != StreamState.RUN for s in self.streams.values()) or self._generators == 0:
                     for stream_id in list(self.streams):      # stopped streams with nothing queued
                         self.destroy_stream(stream_id, graceful=True)
                     return

@@ -99,7 +99,9 @@ class _DeviceAtlas:
         self.n_patches = self.n_luts = 0
         self.version = None
         self.ready = None            # event: the last append has been enqueued before it
-        self._stage = None
+        # page-locked staging for appends, allocated up front (cudaHostAlloc takes milliseconds)
+        self._stage = [[torch.empty(self.STAGE_BYTES, dtype=torch.uint8).pin_memory(), None] for _ in range(4)]
+        self._stage_next = 0
 
     STAGE_BYTES = 1 << 18
 
@@ -112,9 +114,6 @@ class _DeviceAtlas:
         if nbytes > self.STAGE_BYTES:
             dst.copy_(torch.from_numpy(src.view(dtype).reshape(shape).copy()))
             return
-        if self._stage is None:
-            self._stage = [[torch.empty(self.STAGE_BYTES, dtype=torch.uint8).pin_memory(), None] for _ in range(4)]
-            self._stage_next = 0
         slot = self._stage[self._stage_next]
         self._stage_next = (self._stage_next + 1) % len(self._stage)
         if slot[1] is not None:

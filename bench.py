@@ -69,6 +69,28 @@ def synthetic_batch(seed, n=BATCH):
     return rng.integers(0, 256, (n, SRC_H, SRC_W, 3), dtype=np.uint8)
 
 
+def natural_frame(seed, h=SRC_H, w=SRC_W):
+    """Smooth random field + mild noise: a synthetic frame that compresses like camera content
+    (uniform noise, the resize inputs above, would make every JPEG as large as the raw frame)."""
+    from PIL import Image
+    rng = np.random.default_rng(seed)
+    low = (rng.random((h // 40 + 2, w // 40 + 2, 3)) * 255).astype(np.uint8)
+    up = np.asarray(Image.fromarray(low, "RGB").resize((w, h), Image.BICUBIC)).astype(np.float32)
+    return np.clip(up + rng.normal(0, 4, (h, w, 3)), 0, 255).astype(np.uint8)
+
+
+def jpeg_blob(seed):
+    import io
+    from PIL import Image
+    buf = io.BytesIO()
+    Image.fromarray(natural_frame(seed), "RGB").save(buf, "JPEG", quality=90, subsampling=2)
+    return buf.getvalue()
+
+
+JPEG_WORKLOAD = ("config1: JPEG bytes in host memory (1080p, quality 90, 4:2:0) -> decode -> ImageResize PIL branch "
+                 "(antialiased bicubic 1920x1080->640x480) -> RGB frames in host memory, 32-frame batches")
+
+
 # --------------------------------------------------------------------------- clocks
 class ClockSampler:
     QUERY = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -114,6 +136,7 @@ class ClockSampler:
 # --------------------------------------------------------------------------- CPU reference
 CPU_ROTATE = 4        # distinct input sets per worker, rotated like the GPU arm's batches
 CPU_ROUNDS = 3        # timed rounds of K steps each; the median round is reported
+JPEG_SEED = 640_000
 
 
 def _ref_worker(idx, count, warmup, steps, rounds, barrier, results):
@@ -169,6 +192,73 @@ def cpu_reference_rate(steps, warmup, frames_per_step=BATCH):
     round_s = sorted(max(times[i][r] for i in range(workers)) for r in range(CPU_ROUNDS))
     dt = round_s[len(round_s) // 2]
     return frames_per_step * steps / dt, workers, dt / steps, [frames_per_step * steps / t for t in round_s]
+
+
+def _ref_worker_jpeg(idx, seeds, warmup, steps, rounds, barrier, results):
+    """One host core of the JPEG leg: Image.open + resize (R/elements/media/image_io.py:184,218; the
+    decode runs lazily inside resize, as in the reference) on its share of every 32-blob batch."""
+    import io
+    from PIL import Image
+    blobs = [jpeg_blob(s) for s in seeds]
+    def step():
+        out = None
+        for b in blobs:
+            out = np.asarray(Image.open(io.BytesIO(b)).resize((DST_W, DST_H)))
+        return out
+    for _ in range(max(warmup, 1)):
+        step()
+    times = []
+    for _ in range(rounds):
+        barrier.wait()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            step()
+        times.append(time.perf_counter() - t0)
+    results.put((idx, times))
+
+
+def cpu_reference_rate_jpeg(steps, warmup, frames_per_step=BATCH):
+    """frames/s of the reference's CPU path from JPEG bytes (Pillow decode + bicubic resize), one process
+    per host core, timed like cpu_reference_rate.  -> (frames/s, workers, rounds' frames/s)"""
+    import multiprocessing as mp
+    cores = os.cpu_count() or 1
+    workers = max(1, min(cores, frames_per_step))
+    shards = [[JPEG_SEED + k for k in range(frames_per_step) if k % workers == i] for i in range(workers)]
+    ctx = mp.get_context("spawn")
+    barrier, results = ctx.Barrier(workers), ctx.Queue()
+    procs = [ctx.Process(target=_ref_worker_jpeg, args=(i, shards[i], warmup, steps, CPU_ROUNDS, barrier, results))
+             for i in range(workers)]
+    for p in procs:
+        p.start()
+    times = {}
+    deadline = time.time() + 1800
+    while len(times) < workers:
+        try:
+            idx, t = results.get(timeout=2.0)
+            times[idx] = t
+        except Exception:
+            if any(p.exitcode not in (None, 0) for p in procs) or time.time() > deadline:
+                for p in procs:
+                    p.kill()
+                raise RuntimeError("bench.py: a CPU JPEG worker exited without a result")
+    for p in procs:
+        p.join()
+    round_s = sorted(max(times[i][r] for i in range(workers)) for r in range(CPU_ROUNDS))
+    dt = round_s[len(round_s) // 2]
+    return frames_per_step * steps / dt, workers, [frames_per_step * steps / t for t in round_s]
+
+
+def jpeg_steps(args):
+    return max(2, min(args.steps, 10))
+
+
+def cpu_jpeg_object(args):
+    import PIL
+    rate, workers, rounds = cpu_reference_rate_jpeg(jpeg_steps(args), min(args.warmup, 2))
+    return {"value": rate, "unit": "frames/s", "cores": workers, "kind": "reference library calls",
+            "workload": JPEG_WORKLOAD, "rounds_frames_per_s": [round(r, 1) for r in rounds],
+            "sample": f"{CPU_ROUNDS} rounds x {jpeg_steps(args)} steps x {BATCH} frames: PIL.Image.open(bytes).resize "
+                      f"(Pillow {PIL.__version__}), one process per core"}
 
 
 def as_shipped_rate(batches=6):
@@ -236,6 +326,7 @@ def run_reference_arm(args):
     }
     if shipped:
         line["cpu_baseline_as_shipped"] = shipped
+    line["e2e_jpeg"] = cpu_jpeg_object(args)
     print(json.dumps(line), flush=True)
 
 
@@ -404,10 +495,64 @@ def run_gpu_arm(args):
     h2d = BATCH * SRC_H * SRC_W * 3
     d2h = BATCH * DST_H * DST_W * 3
 
+    # ---- end to end from JPEG bytes (BASELINE config 1): the frames are born on the device.  32 JPEG
+    # blobs per step in page-locked host memory -> nvJPEG batched decode -> antialiased bicubic resize
+    # (the reference's PIL branch) -> D2H of the 640x480 frames.  Two CUDA streams alternate.
+    jpeg_result = None
+    try:
+        from aiko_services_b200 import jpeg
+        blobs = [jpeg_blob(JPEG_SEED + 100 * rank + k) for k in range(BATCH)]
+        pinned_blobs = []
+        for b in blobs:
+            t = torch.empty(len(b), dtype=torch.uint8).pin_memory()
+            t.numpy()[...] = np.frombuffer(b, np.uint8)
+            pinned_blobs.append(t)
+        lanes = []
+        for k in range(2):
+            st = torch.cuda.Stream(device)
+            lanes.append({"stream": st, "decoder": jpeg.JpegDecoder(device, BATCH),
+                          "frames": torch.empty((BATCH, SRC_H, SRC_W, 3), dtype=torch.uint8, device=device),
+                          "small": torch.empty((BATCH, DST_H, DST_W, 3), dtype=torch.uint8, device=device),
+                          "host": torch.empty((BATCH, DST_H, DST_W, 3), dtype=torch.uint8).pin_memory(), "busy": False})
+
+        def jpeg_submit(i):
+            lane = lanes[i % 2]
+            if lane["busy"]:
+                lane["stream"].synchronize()
+            with torch.cuda.stream(lane["stream"]):
+                lane["decoder"].decode(pinned_blobs, out=lane["frames"], stream=lane["stream"])
+                ops.resize_bicubic_aa(lane["frames"], DST_W, DST_H, out=lane["small"], stream=lane["stream"])
+                lane["host"].copy_(lane["small"], non_blocking=True)
+            lane["busy"] = True
+
+        n_jpeg = max(4, min(args.steps, 40))
+        for i in range(4):
+            jpeg_submit(i)
+        for lane in lanes:
+            lane["stream"].synchronize()
+        barrier()
+        tj0 = time.perf_counter()
+        for i in range(n_jpeg):
+            jpeg_submit(i)
+        for lane in lanes:
+            lane["stream"].synchronize()
+        jpeg_s = time.perf_counter() - tj0
+        barrier()
+        jpeg_result = {"seconds": jpeg_s, "frames": BATCH * n_jpeg, "steps": n_jpeg,
+                       "h2d": sum(len(b) for b in blobs), "hardware": lanes[0]["decoder"].hardware,
+                       "checksum": int(lanes[0]["host"][0, 0, 0, 0])}
+    except Exception as error:      # the JPEG leg needs libaiko_b200_jpeg.so + nvJPEG; the headline does not
+        jpeg_result = {"error": repr(error)}
+
     # max over ranks of the device / wall timings, sum over ranks of the frames processed
     from aiko_services_b200 import sharding
     (ms, e2e_s, changing_s), (frames_timed, frames_e2e, frames_changing) = sharding.combine(
         [ms, e2e_s, changing_s], [BATCH * args.steps, BATCH * e2e_steps, BATCH * changing_steps], device=device)
+    ok_everywhere = sharding.combine([0.0 if (jpeg_result and "error" not in jpeg_result) else 1.0], [], device=device)[0][0] == 0.0
+    if ok_everywhere:
+        jpeg_totals = sharding.combine([jpeg_result["seconds"]], [jpeg_result["frames"]], device=device)
+    elif jpeg_result is not None and "error" not in jpeg_result:
+        jpeg_result = {"error": "JPEG leg failed on another rank"}
 
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -454,11 +599,24 @@ def run_gpu_arm(args):
             "gpu_launches": 2 * args.steps * world,
             "clocks": clocks,
         }
+        if jpeg_result is not None and "error" not in jpeg_result:
+            (jpeg_s,), (jpeg_frames,) = jpeg_totals
+            line["e2e_jpeg"] = {"value": jpeg_frames / jpeg_s, "unit": "frames/s", "workload": JPEG_WORKLOAD,
+                                "steps": jpeg_result["steps"], "h2d_bytes_per_step": jpeg_result["h2d"],
+                                "d2h_bytes_per_step": d2h,
+                                "decoder": "nvJPEG, NVJPG hardware engines" if jpeg_result["hardware"]
+                                else "nvJPEG, CUDA decoder (hardware backend not offered by this driver)",
+                                "note": "decode is library code (nvJPEG); resize = bicubic_mma_kernel; pixels differ from "
+                                        "Pillow's decoder within the tolerance of tests/test_gpu_jpeg.py"}
+        elif jpeg_result is not None:
+            line["e2e_jpeg"] = {"unavailable": jpeg_result["error"]}
         if world == 1 and not args.no_cpu_baseline:
             port, shipped, _ = cpu_baseline_objects(args.steps, args.warmup)
             line["cpu_baseline"] = port
             if shipped:
                 line["cpu_baseline_as_shipped"] = shipped
+            if "e2e_jpeg" in line and "value" in line["e2e_jpeg"]:
+                line["e2e_jpeg"]["cpu_baseline"] = cpu_jpeg_object(args)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

