@@ -7,7 +7,7 @@ import torch
 
 from . import _native
 from ._native import check
-from .ops import _require_cuda, _stream_ptr
+from .ops import _T, _require_cuda, _stream_int
 
 AF_FREQUENCY_MINIMUM, AF_FREQUENCY_MAXIMUM = 10, 9000     # audio_io.py:204-205
 AR_BAND_COUNT = 8                                         # audio_io.py:237
@@ -27,7 +27,7 @@ class AudioPlan:
             raise ValueError(f"audio window length {n} must be even and >= 4")
         self.workspace = torch.empty(nbytes, dtype=torch.uint8, device=device)
         with torch.cuda.device(device):
-            check(lib.aiko_b200_audio_prepare(self.workspace.data_ptr(), nbytes, n, _stream_ptr()))
+            _T().audio_prepare(self.workspace, n, _stream_int())
         torch.cuda.current_stream(device).synchronize()
         self.frequencies = np.fft.fftfreq(n, 1 / self.sample_rate)             # PE_FFT, :312-313
         half = self.frequencies[0:n // 2]                                      # PE_AudioResampler, :253-257
@@ -37,7 +37,7 @@ class AudioPlan:
             start, end = band * band_width, band * band_width + band_width
             idx = np.nonzero((half >= start) & (half < end))[0]
             ranges += [int(idx[0]), int(idx[-1]) + 1] if len(idx) else [0, 0]
-        self.band_ranges = (ctypes.c_int * 16)(*ranges)
+        self.band_ranges = [int(v) for v in ranges]
         self.band_frequencies = np.array([(b * band_width + b * band_width + band_width) / 2
                                           for b in range(AR_BAND_COUNT)])
         folded = np.abs(self.frequencies[:n // 2 + 1])                         # |f| of bins k = 0 .. n/2
@@ -71,12 +71,12 @@ def audio_chain(audio, sample_rate, *, bands=True, top=True, stream=None):
     tf = torch.empty((b, 100), dtype=torch.float32, device=dev) if top else None
     ta = torch.empty((b, 100), dtype=torch.float32, device=dev) if top else None
     tc = torch.empty((b,), dtype=torch.int32, device=dev) if top else None
-    with torch.cuda.device(dev):
-        check(_native.lib().aiko_b200_audio_chain(
-            audio.data_ptr(), 0 if audio.dtype == torch.int16 else 1, b, n, pl.sample_rate,
-            out["amplitudes"].data_ptr(), band.data_ptr() if bands else None, pl.band_ranges,
-            tf.data_ptr() if top else None, ta.data_ptr() if top else None, tc.data_ptr() if top else None,
-            pl.gate[0], pl.gate[1], pl.workspace.data_ptr(), pl.workspace.numel(), _stream_ptr(stream)))
+    if b == 0:
+        pass
+    else:
+        with torch.cuda.device(dev):
+            _T().audio_chain(audio, pl.sample_rate, out["amplitudes"], band, pl.band_ranges, tf, ta, tc, pl.gate[0],
+                             pl.gate[1], pl.workspace, _stream_int(stream))
     if bands:
         out["band_frequencies"], out["band_amplitudes"] = pl.band_frequencies, band
     if top:
@@ -111,8 +111,7 @@ def audio_filter(amplitudes, frequencies, device=None, stream=None):
     ta = torch.empty((b, 100), dtype=torch.float64, device=device)
     tc = torch.empty((b,), dtype=torch.int32, device=device)
     with torch.cuda.device(device):
-        check(_native.lib().aiko_b200_audio_filter_f64(a.data_ptr(), f.data_ptr(), b, n, 0 if f.shape[0] == 1 else n,
-                                                       tf.data_ptr(), ta.data_ptr(), tc.data_ptr(), _stream_ptr(stream)))
+        _T().audio_filter_f64(a, f, tf, ta, tc, _stream_int(stream))
     return (tf[0], ta[0], tc[0]) if single else (tf, ta, tc)
 
 
@@ -129,6 +128,5 @@ def audio_bands(amplitudes, frequencies, device=None, stream=None):
     bf = torch.empty((b, 8), dtype=torch.float64, device=device)
     ba = torch.empty((b, 8), dtype=torch.float64, device=device)
     with torch.cuda.device(device):
-        check(_native.lib().aiko_b200_audio_bands_f64(a.data_ptr(), f.data_ptr(), b, n, 0 if f.shape[0] == 1 else n,
-                                                      bf.data_ptr(), ba.data_ptr(), _stream_ptr(stream)))
+        _T().audio_bands_f64(a, f, bf, ba, _stream_int(stream))
     return (bf[0], ba[0]) if single else (bf, ba)

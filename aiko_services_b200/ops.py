@@ -20,6 +20,22 @@ def _stream_ptr(stream=None):
     return ctypes.c_void_p(s.cuda_stream)
 
 
+def _stream_int(stream=None):
+    return (stream if stream is not None else torch.cuda.current_stream()).cuda_stream
+
+
+def _T():
+    """torch.ops.aiko_b200: the C ABI as PyTorch custom ops (torch_ops.py)."""
+    global _T_cache
+    if _T_cache is None:
+        from . import torch_ops
+        _T_cache = torch_ops.OPS
+    return _T_cache
+
+
+_T_cache = None
+
+
 class _on_device:
     """``torch.cuda.device(dev)`` that costs nothing when ``dev`` already is the current device."""
     __slots__ = ("ctx",)
@@ -243,11 +259,8 @@ def resize_linear(src, width, height, *, swap_rb=False, overlay=None, out=None, 
     out = _out(out, shape, dev, "resize_linear out")
     if overlay is not None and overlay.n_ops == 0:      # nothing to draw
         overlay = None
-    with _on_device(dev):
-        check(_native.lib().aiko_b200_resize_linear_u8(
-            src.data_ptr(), n, h, w, c, w * c, h * w * c, out.data_ptr(), height, width, width * c,
-            height * width * c, int(bool(swap_rb)), overlay.pointer() if overlay is not None else None,
-            _stream_ptr(stream)))
+    _T().resize_linear_u8(src, out, bool(swap_rb), ctypes.addressof(overlay.struct) if overlay is not None else 0,
+                          _stream_int(stream))
     return out
 
 
@@ -264,8 +277,7 @@ def bicubic_workspace(device, sh, sw, dh, dw, stream=None):
             raise ValueError(f"resize_bicubic_aa: bad size {sw}x{sh} -> {dw}x{dh}")
         ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
         with torch.cuda.device(device):
-            check(_native.lib().aiko_b200_resize_bicubic_prepare(ws.data_ptr(), nbytes, sh, sw, dh, dw,
-                                                                 _stream_ptr(stream)))
+            _T().resize_bicubic_prepare(ws, sh, sw, dh, dw, _stream_int(stream))
         # later calls may come from other streams: make the tables visible to all of them
         (stream or torch.cuda.current_stream()).synchronize()
         if nbytes >= 8 and int(ws[:8].view(torch.int32)[1]) != 0:      # set by prepare when a table overflowed
@@ -284,9 +296,8 @@ def resize_bicubic_aa(src, width, height, *, out=None, stream=None):
     if n == 0:
         return out
     ws = bicubic_workspace(src.device, h, w, height, width, stream)
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_resize_bicubic_aa_u8(src.data_ptr(), n, h, w, c, out.data_ptr(), height, width,
-                                                           ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().resize_bicubic_aa_u8(src, out, ws, _stream_int(stream))
     return out
 
 
@@ -303,9 +314,8 @@ def premultiply(src, *, inverse=False, channels=None, out=None, stream=None):
     c = int(channels if inverse else src.shape[-1])
     shape = tuple(src.shape[:-1]) + ((c,) if inverse else (4,))
     out = _out(out, shape, src.device, "premultiply out")
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_premultiply_u8(src.data_ptr(), out.data_ptr(), src.numel() // src.shape[-1], c,
-                                                     int(bool(inverse)), _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().premultiply_u8(src, out, c, bool(inverse), _stream_int(stream))
     return out
 
 
@@ -330,9 +340,8 @@ def resize_nearest_pil(src, width, height, *, out=None, stream=None):
         tabs = _nearest_tables[key] = (torch.from_numpy(_nearest_table(w, width)).to(src.device),
                                        torch.from_numpy(_nearest_table(h, height)).to(src.device))
         torch.cuda.current_stream(src.device).synchronize()
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_gather_nearest_u8(src.data_ptr(), n, h, w, c, out.data_ptr(), height, width,
-                                                        tabs[0].data_ptr(), tabs[1].data_ptr(), _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().gather_nearest_u8(src, out, tabs[0], tabs[1], _stream_int(stream))
     return out
 
 
@@ -357,11 +366,8 @@ def resize_norm_f32(src, width, height, mean, std, *, out=None, stream=None):
     if c != 3:
         raise ValueError("resize_norm_f32: RGB frames expected")
     out = _out(out, (n, 3, height, width), src.device, "resize_norm_f32 out", torch.float32)
-    m = (ctypes.c_float * 3)(*[float(v) for v in mean])
-    s = (ctypes.c_float * 3)(*[float(v) for v in std])
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_resize_norm_f32_nchw(src.data_ptr(), n, h, w, out.data_ptr(), height, width,
-                                                           m, s, _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().resize_norm_f32_nchw(src, out, [float(v) for v in mean], [float(v) for v in std], _stream_int(stream))
     return out
 
 
@@ -375,9 +381,8 @@ def overlay_draw(src, overlay, *, out=None, stream=None):
             with torch.cuda.stream(stream) if stream is not None else contextlib.nullcontext():
                 out.copy_(src)
         return out
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_overlay_u8(src.data_ptr(), out.data_ptr(), n, h, w, c, w * c, h * w * c,
-                                                 overlay.pointer(), _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().overlay_u8(src, out, ctypes.addressof(overlay.struct), _stream_int(stream))
     return out
 
 
@@ -386,9 +391,8 @@ def swap_rb(src, *, out=None, stream=None):
     if src.shape[-1] != 3:
         raise ValueError("swap_rb: last dimension must be 3")
     out = _out(out, src.shape, src.device, "swap_rb out")
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_swap_rb_u8(src.data_ptr(), out.data_ptr(), src.numel() // 3,
-                                                 _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().swap_rb_u8(src, out, _stream_int(stream))
     return out
 
 
@@ -397,18 +401,16 @@ def bgr2gray(src, *, rgb_order=False, out=None, stream=None):
     if src.shape[-1] != 3:
         raise ValueError("bgr2gray: last dimension must be 3")
     out = _out(out, src.shape[:-1], src.device, "bgr2gray out")
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_bgr2gray_u8(src.data_ptr(), out.data_ptr(), src.numel() // 3,
-                                                  int(bool(rgb_order)), _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().bgr2gray_u8(src, out, bool(rgb_order), _stream_int(stream))
     return out
 
 
 def gray2bgr(src, *, out=None, stream=None):
     _require_cuda(src, "gray2bgr src")
     out = _out(out, tuple(src.shape) + (3,), src.device, "gray2bgr out")
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_gray2bgr_u8(src.data_ptr(), out.data_ptr(), src.numel(),
-                                                  _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().gray2bgr_u8(src, out, _stream_int(stream))
     return out
 
 
@@ -417,9 +419,8 @@ def flip(src, flip_code, *, out=None, stream=None):
     _require_cuda(src, "flip src")
     n, h, w, c, _ = _nhwc(src)
     out = _out(out, src.shape, src.device, "flip out")
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_flip_u8(src.data_ptr(), out.data_ptr(), n, h, w, c, int(flip_code),
-                                              _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().flip_u8(src, out, int(flip_code), _stream_int(stream))
     return out
 
 
@@ -428,7 +429,6 @@ def crop(src, x0, y0, width, height, *, out=None, stream=None):
     n, h, w, c, gray = _nhwc(src)
     shape = (n, height, width) if gray else (n, height, width, c)
     out = _out(out, shape, src.device, "crop out")
-    with torch.cuda.device(src.device):
-        check(_native.lib().aiko_b200_crop_u8(src.data_ptr(), n, h, w, c, out.data_ptr(), int(x0), int(y0),
-                                              int(width), int(height), _stream_ptr(stream)))
+    with _on_device(src.device):
+        _T().crop_u8(src, out, int(x0), int(y0), _stream_int(stream))
     return out

@@ -605,7 +605,8 @@ def run_gpu_arm(args):
                                 "steps": jpeg_result["steps"], "h2d_bytes_per_step": jpeg_result["h2d"],
                                 "d2h_bytes_per_step": d2h,
                                 "decoder": "nvJPEG, NVJPG hardware engines" if jpeg_result["hardware"]
-                                else "nvJPEG, CUDA decoder (hardware backend not offered by this driver)",
+                                else "nvJPEG hybrid (hardware backend not offered by this driver): entropy decode on the host cores, "
+                                     "IDCT / upsampling / colour conversion on the GPU",
                                 "note": "decode is library code (nvJPEG); resize = bicubic_mma_kernel; pixels differ from "
                                         "Pillow's decoder within the tolerance of tests/test_gpu_jpeg.py"}
         elif jpeg_result is not None:

@@ -27,12 +27,13 @@ extern "C" {
 
 typedef struct aiko_b200_jpeg_decoder aiko_b200_jpeg_decoder;
 
-/* backend: 0 = best available (hardware engines, else CUDA decoder), 1 = CUDA decoder (nvJPEG
- * GPU_HYBRID), 2 = hardware engines only.  max_batch: largest batch a decode call will pass.
+/* backend: 0 = best available (hardware engines, else the hybrid decoder), 1 = hybrid decoder
+ * (entropy decode on host threads, one image each; IDCT, upsampling and colour conversion on the
+ * GPU), 2 = hardware engines only.  max_batch: largest batch a decode call will pass.
  * Returns 0 or a negative AIKO_B200_ERR_* code (aiko_b200_jpeg_last_error() has the text). */
 int aiko_b200_jpeg_decoder_create(aiko_b200_jpeg_decoder** decoder_host, int backend, int max_batch);
 int aiko_b200_jpeg_decoder_destroy(aiko_b200_jpeg_decoder* decoder);
-/* 1 if the decoder runs on the NVJPG hardware engines, 0 if on nvJPEG's CUDA decoder. */
+/* 1 if the decoder runs on the NVJPG hardware engines, 0 if it is the hybrid (host threads + GPU) decoder. */
 int aiko_b200_jpeg_decoder_is_hardware(const aiko_b200_jpeg_decoder* decoder);
 const char* aiko_b200_jpeg_last_error(void);
 

@@ -224,3 +224,29 @@ def test_streams_walk_the_path_of_their_own_head(tmp_path):
     results = p.process_frames([({"stream_id": "sa", "frame_id": 0}, {"trail": []}),
                                 ({"stream_id": "sb", "frame_id": 0}, {"trail": []})])
     assert [r[1]["trail"] for r in results] == [["A", "A2"], ["B", "B2"]]
+
+
+def test_locators_items_and_batches(tmp_path):
+    """common_io: URL parsing, "{}" patterns, ordering, batches, diagnostics."""
+    from aiko_services_b200.elements.media.common_io import (Batcher, Locator, LocatorError, contains_all,
+                                                              file_glob_difference)
+    for k in (2, 0, 1):
+        (tmp_path / f"in_{k:02d}.jpeg").write_bytes(b"x")
+    (tmp_path / "other.txt").write_bytes(b"y")
+    loc = Locator.parse(f"file://{tmp_path}/in_{{}}.jpeg")
+    assert loc.location == str(tmp_path) and loc.pattern == "in_*.jpeg"
+    items = loc.expand()
+    assert [i.path.name for i in items] == ["in_00.jpeg", "in_01.jpeg", "in_02.jpeg"]
+    assert [i.file_id for i in items] == ["00", "01", "02"]
+    assert [i.path.name for i in Locator.parse(str(tmp_path / "other.txt")).expand()] == ["other.txt"]
+    assert len(Locator.parse(str(tmp_path)).expand()) == 4 and Locator.parse(str(tmp_path)).expand()[0].file_id is None
+    both = Locator.parse_list(f"(file://{tmp_path}/in_{{}}.jpeg {tmp_path}/other.txt)")
+    assert len(both) == 2
+    with pytest.raises(LocatorError, match="scheme"):
+        Locator.parse("http://example/x")
+    with pytest.raises(LocatorError, match="does not exist"):
+        Locator.parse(str(tmp_path / "missing")).expand()
+    b = Batcher(items)
+    assert [len(b.take(2)), len(b.take(2)), len(b.take(2))] == [2, 1, 0]
+    assert contains_all("a{}b", "{}") and not contains_all("ab", "{}")
+    assert file_glob_difference("in_*.jpeg", "in_07.jpeg") == "07" and file_glob_difference("in_*.jpeg", "x.png") is None
