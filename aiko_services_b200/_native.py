@@ -64,6 +64,8 @@ SIGNATURES = {
     "aiko_b200_device_info": [ctypes.c_char_p, _sz, ctypes.POINTER(_i), ctypes.POINTER(_i)],
     "aiko_b200_overlay_plan_host": [_i, _vp, _vp, ctypes.c_char_p, _i, _i, _i, _vp, _i, _vp,
                                     ctypes.POINTER(OverlayPlanInfo)],
+    "aiko_b200_overlay_plan_struct_host": [_i, _vp, _vp, ctypes.c_char_p, _i, _i, _i, _i, _vp, _vp, _sz, _vp, _ovp,
+                                           ctypes.POINTER(OverlayPlanInfo)],
     "aiko_b200_overlay_upload": [_vp, _vp, _sz, _vp],
     "aiko_b200_overlay_text_size_host": [ctypes.c_char_p, ctypes.POINTER(_i), ctypes.POINTER(_i)],
     "aiko_b200_overlay_cells_host": [_vp, _i, _i, _i, ctypes.POINTER(_i), ctypes.POINTER(ctypes.c_longlong)],

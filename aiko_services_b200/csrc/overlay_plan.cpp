@@ -445,3 +445,58 @@ extern "C" int aiko_b200_overlay_plan_host(int n_lists, const int32_t* object_of
   }
   return AIKO_B200_OK;
 }
+
+// Plans straight into a caller-owned page-locked buffer and fills the aiko_b200_overlay that the
+// drawing call takes: ops | op_offsets | list_of_frame laid out in buffer_host, device pointers set
+// to the same offsets inside buffer_dev, upload_from_host / upload_bytes set so that the drawing call
+// ships the bytes itself.  One call per new overlay on the per-frame path.
+extern "C" int aiko_b200_overlay_plan_struct_host(int n_lists, const int32_t* object_offsets_host,
+                                                  const int32_t* rects_host, const char* labels_host, int image_width,
+                                                  int image_height, int layout, int n_frames,
+                                                  const int32_t* list_of_frame_host, void* buffer_host,
+                                                  size_t buffer_bytes, void* buffer_dev, aiko_b200_overlay* overlay_host,
+                                                  aiko_b200_overlay_plan_info* info_host) {
+  if (!buffer_host || !buffer_dev || !overlay_host || !info_host || n_frames < 0 || n_lists < 0 ||
+      (reinterpret_cast<uintptr_t>(buffer_host) & 15) || (reinterpret_cast<uintptr_t>(buffer_dev) & 15)) {
+    aiko::set_last_error("overlay_plan_struct: bad argument (buffers must be 16-byte aligned)");
+    return AIKO_B200_ERR_INVALID_ARGUMENT;
+  }
+  const size_t tail = sizeof(int32_t) * ((size_t)n_lists + 1 + (size_t)n_frames);
+  if (buffer_bytes < tail + sizeof(aiko_b200_overlay_op)) {
+    aiko::set_last_error("overlay_plan_struct: buffer of %zu bytes is too small", buffer_bytes);
+    return AIKO_B200_ERR_WORKSPACE;
+  }
+  // the op area takes what the offsets and the frame map leave, rounded down to whole ops
+  const int capacity = (int)std::min<size_t>((buffer_bytes - tail) / sizeof(aiko_b200_overlay_op), 1u << 24);
+  std::vector<int32_t> offsets((size_t)n_lists + 1);
+  aiko_b200_overlay_op* ops = static_cast<aiko_b200_overlay_op*>(buffer_host);
+  const int rc = aiko_b200_overlay_plan_host(n_lists, object_offsets_host, rects_host, labels_host, image_width,
+                                             image_height, layout, ops, capacity, offsets.data(), info_host);
+  if (rc != AIKO_B200_OK) return rc;
+  const size_t ops_bytes = sizeof(aiko_b200_overlay_op) * (size_t)std::max(info_host->n_ops, 1);
+  int32_t* tailp = reinterpret_cast<int32_t*>(static_cast<char*>(buffer_host) + ops_bytes);
+  std::memcpy(tailp, offsets.data(), sizeof(int32_t) * offsets.size());
+  int32_t* frames = tailp + offsets.size();
+  for (int f = 0; f < n_frames; f++) {
+    const int li = list_of_frame_host ? list_of_frame_host[f] : 0;
+    if (li < 0 || li >= n_lists) {
+      aiko::set_last_error("overlay_plan_struct: frame %d names list %d of %d", f, li, n_lists);
+      return AIKO_B200_ERR_INVALID_ARGUMENT;
+    }
+    frames[f] = li;
+  }
+  char* dev = static_cast<char*>(buffer_dev);
+  overlay_host->ops = reinterpret_cast<const aiko_b200_overlay_op*>(dev);
+  overlay_host->op_offsets = reinterpret_cast<const int32_t*>(dev + ops_bytes);
+  overlay_host->list_of_frame = overlay_host->op_offsets + offsets.size();
+  overlay_host->n_lists = n_lists;
+  overlay_host->n_frames = n_frames;
+  overlay_host->max_ops_per_list = info_host->max_ops_per_list;
+  overlay_host->max_marks_per_list = info_host->max_marks_per_list;
+  overlay_host->max_cells_per_list = info_host->max_cells_per_list;
+  overlay_host->frame_width = image_width;
+  overlay_host->frame_height = image_height;
+  overlay_host->upload_from_host = buffer_host;
+  overlay_host->upload_bytes = ops_bytes + tail;
+  return AIKO_B200_OK;
+}

@@ -7,6 +7,7 @@ takes a whole batch ``uint8[N, H, W, C]`` (or ``[N, H, W]`` for grayscale) resid
 """
 import contextlib
 import ctypes
+from array import array
 
 import numpy as np
 import torch
@@ -186,9 +187,10 @@ class OverlayRing:
         self.events = [None, None]        # one per half of the ring: recorded after the half's last use
         self.next = 0
         self._atlas_dev = None
+        self._info = _native.OverlayPlanInfo()
 
     def plan(self, overlays, width, height, layout="rgb", n_frames=None, stream=None):
-        from .overlay_plan import plan
+        from .overlay_plan import LAYOUTS, gather_objects, plan
         i = self.next
         n = len(self.views)
         s = stream if stream is not None else torch.cuda.current_stream(self.device)
@@ -205,29 +207,33 @@ class OverlayRing:
                     self.events[1 - h] = torch.cuda.Event()
                 self.events[1 - h].record(s)
         self.next = (i + 1) % n
-        planned = plan(overlays, width, height, layout, out=self.views[i], n_frames=n_frames)
+        n_lists, offsets, rects, labels, list_of_frame = gather_objects(overlays)
+        if list_of_frame is None:
+            frames, frame_map = int(n_frames or 1), None
+        else:
+            frames, frame_map = len(list_of_frame), array("i", list_of_frame).buffer_info()[0]
+        ov = self.overlays[i]
+        if ov is None:
+            atlas = self._atlas_dev or self.atlas.device(self.device)
+            ov = self.overlays[i] = DeviceOverlay(self.dev[i], 0, 0, 0, 0, atlas, 0, 0, 0, 0, 0)
+            ov.host_ptr, ov.dev_ptr = self.pinned[i].data_ptr(), self.dev[i].data_ptr()
+        info = self._info
+        rc = _native.lib().aiko_b200_overlay_plan_struct_host(
+            n_lists, offsets.buffer_info()[0], rects.buffer_info()[0], labels, int(width), int(height),
+            LAYOUTS[layout], frames, frame_map, ov.host_ptr, self.capacity, ov.dev_ptr, ov.struct, info)
+        if rc == _native.ERR_WORKSPACE:                  # does not fit a slot: one-off buffers
+            planned = plan(overlays, width, height, layout, n_frames=n_frames)
+            return DeviceOverlay.from_plan(planned, self.device, self.atlas.device(self.device), stream=s)
+        check(rc)
         atlas = self._atlas_dev
-        info = planned.info
         if atlas is None or atlas.version != info.atlas_version or atlas.epoch != info.atlas_epoch:
             atlas = self._atlas_dev = self.atlas.device(self.device)       # uploads what the planner appended
             if atlas.ready is not None:
                 s.wait_event(atlas.ready)
-        if planned.buffer.ctypes.data != self.views[i].ctypes.data:        # did not fit the slot: one-off buffers
-            return DeviceOverlay.from_plan(planned, self.device, atlas, stream=s)
-        ov = self.overlays[i]
-        if ov is None or ov.atlas is not atlas:
-            ov = self.overlays[i] = DeviceOverlay(self.dev[i], 0, 0, 0, 0, atlas, 0, 0, 0, 0, 0)
-            ov.struct.upload_from_host = self.pinned[i].data_ptr()
-            ov.base = self.dev[i].data_ptr()
-        st = ov.struct
-        ov.n_ops = planned.n_ops
-        st.op_offsets = ov.base + planned.ops_bytes
-        st.list_of_frame = st.op_offsets + 4 * (planned.n_lists + 1)
-        st.n_lists, st.n_frames = planned.n_lists, planned.n_frames
-        st.max_ops_per_list, st.max_marks_per_list = info.max_ops_per_list, info.max_marks_per_list
-        st.max_cells_per_list = info.max_cells_per_list
-        st.frame_width, st.frame_height = planned.width, planned.height
-        st.upload_bytes = planned.buffer.nbytes
+        if ov.atlas is not atlas:                        # a new atlas epoch: the tables moved
+            ov.atlas = atlas
+            ov.struct.patch_ids, ov.struct.luts = atlas.patch_ids.data_ptr(), atlas.luts.data_ptr()
+        ov.n_ops = info.n_ops
         return ov
 
 

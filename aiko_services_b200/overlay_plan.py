@@ -118,3 +118,27 @@ def label_origin(atlas, text, x, y, w, h, image_width):
         tx = x - tw
         ty = y + th
     return tx, ty
+
+
+def gather_objects(overlays):
+    """-> (n_lists, offsets array('i'), rects array('i'), labels bytes, list_of_frame or None) for one
+    overlay dict (shared by all frames: list_of_frame None) or a list of dicts (one per frame)."""
+    if isinstance(overlays, dict):
+        lists, list_of_frame = [overlays], None
+    else:
+        lists, list_of_frame, seen = [], [], {}
+        for o in overlays:
+            li = seen.get(id(o))
+            if li is None:
+                li = seen[id(o)] = len(lists)
+                lists.append(o)
+            list_of_frame.append(li)
+    rects, labels, offsets = [], [], [0]
+    for o in lists:
+        offsets.append(offsets[-1] + _objects(o, rects, labels))
+    text = "\0".join(labels)
+    try:
+        raw = text.encode("ascii")
+    except UnicodeEncodeError:
+        raw = b"\0".join(_encode(t) for t in labels)
+    return len(lists), array("i", offsets), array("i", rects or (0,)), raw + b"\0", list_of_frame

@@ -425,8 +425,12 @@ def run_gpu_arm(args):
     changing_steps = max(3, min(args.steps, 200))
     dicts = [changing_overlay(i) for i in range(changing_steps + 3)]      # the inputs: one new dict per step
 
+    plan_s = [0.0]
+
     def changing_step(i):
+        t_plan = time.perf_counter()
         dov = ring.plan(dicts[i], DST_W, DST_H, "bgr", n_frames=BATCH)
+        plan_s[0] += time.perf_counter() - t_plan
         ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=dov, out=out)
 
     for i in range(3):
@@ -434,6 +438,7 @@ def run_gpu_arm(args):
     barrier()
     c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     c0.record(stream)
+    plan_s[0] = 0.0
     tc0 = time.perf_counter()
     for i in range(changing_steps):
         changing_step(3 + i)
@@ -579,6 +584,7 @@ def run_gpu_arm(args):
             "value_changing_overlay": {"value": frames_changing / changing_s, "unit": "frames/s",
                                        "steps": changing_steps,
                                        "host_us_per_step": changing_host_s / changing_steps * 1e6,
+                                       "host_plan_us_per_step": plan_s[0] / changing_steps * 1e6,
                                        "device_us_per_step": changing_device_ms / changing_steps * 1e3,
                                        "note": "same step, a different overlay dict every step (boxes move, label "
                                                "text changes); host planning + upload inside the timed region, wall "

@@ -126,6 +126,19 @@ int aiko_b200_overlay_plan_host(int n_lists, const int32_t* object_offsets_host,
                                 aiko_b200_overlay_op* ops_out_host, int ops_capacity,
                                 int32_t* op_offsets_out_host, aiko_b200_overlay_plan_info* info_host);
 
+/* The same planning, written straight into a caller-owned buffer pair and into the aiko_b200_overlay
+ * the drawing call takes: buffer_host (page-locked, 16-byte aligned, buffer_bytes long) receives
+ * ops | op_offsets | list_of_frame; overlay_host gets its device pointers set to the same offsets
+ * inside buffer_dev, its counts, bounds and frame size, and upload_from_host / upload_bytes so that
+ * the drawing call ships the bytes itself.  list_of_frame_host: n_frames list numbers, or NULL = every
+ * frame uses list 0.  The atlas fields of overlay_host (patch_ids, luts, patch_w, patch_h, n_patches)
+ * are the caller's and are left alone.  One call per new overlay on the per-frame path. */
+int aiko_b200_overlay_plan_struct_host(int n_lists, const int32_t* object_offsets_host, const int32_t* rects_host,
+                                       const char* labels_host, int image_width, int image_height, int layout,
+                                       int n_frames, const int32_t* list_of_frame_host, void* buffer_host,
+                                       size_t buffer_bytes, void* buffer_dev, aiko_b200_overlay* overlay_host,
+                                       aiko_b200_overlay_plan_info* info_host);
+
 /* Ships a planned buffer (ops | op_offsets | list_of_frame, as laid out by the caller around
  * aiko_b200_overlay_plan_host) to the device: one cudaMemcpyAsync on `stream`.  plan_host should be
  * page-locked and stay untouched until the copy has run. */
