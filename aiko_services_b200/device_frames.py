@@ -17,6 +17,7 @@ import numpy as np
 import torch
 
 from . import ops
+from .metrics import current_tag
 from .overlay_plan import plan
 from .text_atlas import TextAtlas
 
@@ -25,7 +26,7 @@ _overlay_cache = OrderedDict()       # (overlay content, size, layout, frames, d
 
 
 class DeviceBatch:
-    def __init__(self, tensor, stream=None, recipe=None, device=None, on_source_read=None):
+    def __init__(self, tensor, stream=None, recipe=None, device=None, on_source_read=None, tags=None, timings=None):
         # uint8 [N, H, W, C] or [N, H, W]: on a CUDA device, or (with ``device``) in page-locked host
         # memory -- then the first kernel of the recipe reads it over PCIe if it touches every row
         # once (bilinear downscale of RGB frames), and otherwise it is copied to ``device`` first
@@ -34,6 +35,8 @@ class DeviceBatch:
         self._mapped = not tensor.is_cuda
         self._on_source_read = on_source_read   # called (stream-ordered) once the host source has been consumed
         self._recipe = list(recipe or [])
+        self._tags = list(tags or [None] * len(self._recipe))      # element that appended each step
+        self.timings = timings if timings is not None else {}      # element -> [(start, end) events] | ("fused", element)
         self._tensor = tensor if not self._recipe and not self._mapped else None
         self._host = None
         self.stream = stream             # torch.cuda.Stream the batch's work is ordered on
@@ -59,13 +62,28 @@ class DeviceBatch:
         return (h, w) if c == 1 else (h, w, c)
 
     def then(self, *step):
+        tag = current_tag()
         if self._tensor is None:
             nxt = DeviceBatch(self._source, self.stream, self._recipe + [tuple(step)],
-                              self._device if self._mapped else None, self._on_source_read)
+                              self._device if self._mapped else None, self._on_source_read,
+                              self._tags + [tag], self.timings)
         else:
-            nxt = DeviceBatch(self._tensor, self.stream, [tuple(step)])
+            nxt = DeviceBatch(self._tensor, self.stream, [tuple(step)], tags=[tag], timings=self.timings)
         nxt.stager = self.stager
         return nxt
+
+    def _timed(self, first, used):
+        """Start a CUDA-event pair for recipe steps [first, first + used); -> the end event to record."""
+        tags = [t for t in self._tags[first:first + used] if t is not None]
+        if not tags:
+            return None
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        start.record()
+        self.timings.setdefault(tags[0], []).append((start, end))
+        for t in tags[1:]:
+            if t != tags[0]:
+                self.timings.setdefault(t, ("fused", tags[0]))
+        return end
 
     def launch(self):
         """Enqueue the kernels of the recipe now (asynchronously); results are read later."""
@@ -139,14 +157,18 @@ class DeviceBatch:
                                                                                  ("convert", "BGR2RGB")):
                     swap = True
                     used += 1
+                end = self._timed(i, used)
                 if t.is_cuda:
                     t = ops.resize_linear(t, w, h, swap_rb=swap, overlay=ov)
                 else:                       # page-locked host frames, read by the kernel itself
                     t = ops.resize_linear(t, w, h, swap_rb=swap, overlay=ov, device=self._device)
                     self._source_read()
+                if end is not None:
+                    end.record()
                 owned = True
                 i += used
                 continue
+            end = self._timed(i, 1)
             if kind == "resize_bicubic":
                 t = ops.resize_bicubic_aa(t, step[1], step[2])
             elif kind == "resize_pil":
@@ -171,6 +193,8 @@ class DeviceBatch:
                 t = ops.crop(t, *step[1:])
             else:
                 raise ValueError(f"unknown step {kind}")
+            if end is not None:
+                end.record()
             owned = True
             i += 1
         return t

@@ -220,9 +220,10 @@ def _read_jpegs_on_gpu(stream, paths, images):
         groups.setdefault((width, height), []).append((k, data))
     import torch
     for members in groups.values():
-        with torch.cuda.stream(stager.stream):
-            frames = decoder.decode([data for _, data in members], stream=stager.stream)
-        batch = DeviceBatch(frames, stager.stream)
+        lane = stager.next_lane()
+        with torch.cuda.stream(lane):
+            frames = decoder.decode([data for _, data in members], stream=lane)
+        batch = DeviceBatch(frames, lane)
         batch.stager = stager
         for image, (k, _) in zip(batch.images(), members):
             images[k] = _LazyPil(image, "RGB")

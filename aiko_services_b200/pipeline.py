@@ -35,6 +35,7 @@ from collections import OrderedDict
 from dataclasses import dataclass, field
 from typing import Any, Dict, List, Tuple
 
+from .metrics import GpuSeconds as _GpuSeconds, set_element_tag as _set_element_tag
 from .stream import DEFAULT_STREAM_ID, FIRST_FRAME_ID, Frame, Stream, StreamEvent, StreamEventName, StreamState
 
 __all__ = ["Pipeline", "PipelineDefinition", "PipelineElement", "PipelineElementDefinition", "parse_graph"]
@@ -474,6 +475,24 @@ class Pipeline:
                             batch.launch()
                         except Exception as error:   # reported when the pixels are asked for, as before
                             self.logger.debug(f"deferred launch: {error}")
+        # Element times (R/main/pipeline.py:1170-1182): the host time of the call plus -- for elements whose
+        # work ran lazily on the GPU -- the CUDA-event time of the kernels it caused (GpuSeconds)
+        for job in jobs:
+            if job and job["alive"]:
+                timings = {}
+                for image in job["frame"].swag.get("images") or ():
+                    batch = getattr(image, "batch", None)
+                    if batch is not None and getattr(batch, "timings", None):
+                        timings.update(batch.timings)
+                if timings:
+                    elements = job["frame"].metrics.get("pipeline_elements", {})
+                    for name, recorded in timings.items():
+                        key = f"time_{name}"
+                        if key in elements and not isinstance(elements[key], _GpuSeconds):
+                            if isinstance(recorded, tuple):
+                                elements[key] = _GpuSeconds(elements[key], (), fused_into=recorded[1])
+                            else:
+                                elements[key] = _GpuSeconds(elements[key], recorded)
         results = []
         for job in jobs:
             if job is None:
@@ -508,6 +527,7 @@ class Pipeline:
     def _call_one(self, element, job):
         stream = job["stream"]
         self._enable_thread_local(stream, job["frame_id"])
+        _set_element_tag(element.name)
         try:
             inputs = self._map_in(element, job["frame"].swag)
             event, out = element.process_frame(stream, **inputs)
@@ -515,6 +535,7 @@ class Pipeline:
             event, out = StreamEvent.ERROR, {"diagnostic": traceback.format_exc()}
         finally:
             self._disable_thread_local()
+            _set_element_tag(None)
         self._finish_call(element, job, event, out)
 
     def _call_batched(self, element, live):
@@ -526,11 +547,14 @@ class Pipeline:
                 self._finish_call(element, job, StreamEvent.ERROR, {"diagnostic": traceback.format_exc()})
         if not calls:
             return
+        _set_element_tag(element.name)
         try:
             results = element.process_frame_batch([(job["stream"], inputs) for job, inputs in calls], self)
         except Exception:
             diagnostic = {"diagnostic": traceback.format_exc()}
             results = [(StreamEvent.ERROR, diagnostic)] * len(calls)
+        finally:
+            _set_element_tag(None)
         for (job, _), (event, out) in zip(calls, results):
             self._finish_call(element, job, event, out)
 

@@ -33,6 +33,7 @@ BATCH = 32
 ALGO_BYTES_PER_FRAME = 960 * SRC_W * 3 + DST_H * DST_W * 3
 FALLBACK_HBM_GBS = 6650.0
 OVERLAY_KERNEL = "overlay_cells_kernel"
+LANES = max(1, int(os.environ.get("AIKO_BENCH_LANES", "3")))   # CUDA streams the device-resident loop alternates between
 N_ROTATING_BATCHES = 4     # 4 x 199 MB of distinct inputs: each step reads a batch the 126 MB L2 cannot hold
 
 OVERLAY = {
@@ -305,6 +306,7 @@ def cpu_baseline_objects(steps, warmup):
 
 def config_dict(world):
     return {"workload": WORKLOAD, "frames_per_step_per_gpu": BATCH,
+            "cuda_streams": f"consecutive batches alternate between {LANES} CUDA streams with their own output buffers",
             "l2": f"{N_ROTATING_BATCHES} rotating input batches of 199 MB each (> 126 MB L2), no flush",
             "sharding": "independent streams per rank, no collective" if world > 1 else "single GPU"}
 
@@ -368,11 +370,36 @@ def run_gpu_arm(args):
     batches = [torch.from_numpy(synthetic_batch(1000 * rank + i)).to(device) for i in range(N_ROTATING_BATCHES)]
     out = torch.empty((BATCH, DST_H, DST_W, 3), dtype=torch.uint8, device=device)
     stream = torch.cuda.current_stream()
+    # Consecutive batches alternate between LANES CUDA streams, each with its own output buffer: the
+    # latency-bound overlay pass of batch i then runs beside the HBM-bound resize of batch i + 1, and
+    # the launch ramp / tail of one resize hides behind the next (frames are independent, results stay
+    # in order per lane).  LANES = 1 is the plain back-to-back sequence (value_single_stream).
+    lane_streams = [torch.cuda.Stream(device) for _ in range(LANES)]
+    lane_outs = [torch.empty((BATCH, DST_H, DST_W, 3), dtype=torch.uint8, device=device) for _ in range(LANES)]
 
     exp_ov = None if os.environ.get("AIKO_BENCH_EXPERIMENT_NO_OVERLAY") else ov   # experiments only
 
-    def step(i):
-        ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=exp_ov, out=out)
+    def step(i, lanes=LANES):
+        if lanes == 1:
+            ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=exp_ov, out=out)
+        else:
+            ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=exp_ov,
+                              out=lane_outs[i % lanes], stream=lane_streams[i % lanes])
+
+    def timed_steps(lanes):
+        """-> ms for args.steps steps: CUDA events on the main stream, which the lanes fork from and join."""
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for s in lane_streams[:lanes] if lanes > 1 else ():
+            s.wait_event(ev0)
+        for i in range(args.steps):
+            step(i, lanes)
+        for s in lane_streams[:lanes] if lanes > 1 else ():
+            done = torch.cuda.Event()
+            done.record(s)
+            stream.wait_event(done)
+        ev1.record(stream)
+        return ev0, ev1
 
     def barrier():
         if world > 1:
@@ -385,16 +412,18 @@ def run_gpu_arm(args):
     sampler.start()
     time.sleep(0.3)
     barrier()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.time()
-    ev0.record(stream)
-    for i in range(args.steps):
-        step(i)
-    ev1.record(stream)
+    ev0, ev1 = timed_steps(LANES)
     barrier()
     wall1 = time.time()
     ms = ev0.elapsed_time(ev1)
     clocks = sampler.stop(wall0, wall1)
+    for i in range(3):
+        step(i, 1)
+    barrier()
+    s0, s1 = timed_steps(1)
+    barrier()
+    single_ms = s0.elapsed_time(s1)
     # A step launches two kernels: resize3_staged (resize + swap: reads every weighted source
     # sector and writes every output byte -- the algorithmic bytes) and the overlay kernel (the draw
     # list, in place on the L2-resident output).  The dominant kernel is timed INSIDE the real step
@@ -411,6 +440,7 @@ def run_gpu_arm(args):
     barrier()
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in pairs]))
     step_ms = ms / args.steps
+    single_step_ms = single_ms / args.steps
 
     # ---- the same step with a NEW overlay every step (labels carry the confidence, so detections
     # change the text every frame, R/elements/media/image_io.py:139): draw-list planning on the host
@@ -581,6 +611,10 @@ def run_gpu_arm(args):
             "dtype": "u8", "data": "synthetic", "config": config_dict(world),
             "overlay": "static: one draw list built before the timed loop and reused by every step (the best case; "
                        "value_changing_overlay plans and uploads a new list every step)",
+            "value_single_stream": {"value": BATCH * args.steps / (single_ms * 1e-3) if world == 1 else None,
+                                    "unit": "frames/s", "ms_per_step": single_step_ms,
+                                    "note": "the same steps back to back on ONE CUDA stream (rank 0): resize and "
+                                            "overlay kernels strictly serialised"},
             "value_changing_overlay": {"value": frames_changing / changing_s, "unit": "frames/s",
                                        "steps": changing_steps,
                                        "host_us_per_step": changing_host_s / changing_steps * 1e6,
@@ -596,6 +630,8 @@ def run_gpu_arm(args):
                          "kernel_ms_how": "mean over the steps of a CUDA-event pair around the resize launch, the "
                                           "overlay launch running between consecutive pairs (real step sequence)",
                          "step_ms": step_ms, "step_frac": ALGO_BYTES_PER_FRAME * BATCH / (step_ms * 1e-3) / 1e9 / peak,
+                         "single_stream_step_ms": single_step_ms,
+                         "single_stream_step_frac": ALGO_BYTES_PER_FRAME * BATCH / (single_step_ms * 1e-3) / 1e9 / peak,
                          "kernels_per_step": ["resize3_staged", OVERLAY_KERNEL]},
             "e2e": {"value": frames_e2e / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps,

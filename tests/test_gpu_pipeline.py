@@ -281,3 +281,33 @@ def test_pil_rgba_and_palette_images_through_the_elements(cuda, tmp_path):
         want = Image.open(tmp_path / f"in_{mode}_0.png").resize((64, 48))
         assert got.mode == want.mode == mode
         np.testing.assert_array_equal(np.asarray(got.convert("RGBA")), np.asarray(want.convert("RGBA")))
+
+
+@pytest.mark.gpu
+def test_element_metrics_carry_gpu_time(cuda, tmp_path, monkeypatch):
+    """frame.metrics["pipeline_elements"] (R/main/pipeline.py:1170-1182; consumer PE_Metrics,
+    R/examples/pipeline/elements.py:133-149): GPU elements report host time + CUDA-event time of the
+    kernels they caused; an element fused into another's kernel says so."""
+    import aiko_services_b200.pipeline as P
+    from aiko_services_b200.metrics import GpuSeconds
+    captured = {}
+
+    class KeepFrame(P.Frame):          # the runtime releases a Frame when it completes: keep a handle
+        def __init__(self, *a, **k):
+            super().__init__(*a, **k)
+            captured["frame"] = self
+    monkeypatch.setattr(P, "Frame", KeepFrame)
+    p = Pipeline(definition(tmp_path, ["Feed", "ImageResize", "ImageOverlay", "ImageOutput"], "320x180"))
+    assert p.create_stream("m")
+    frames = [cases.frame(5200 + k, 540, 960, 3) for k in range(4)]
+    for frame_id in range(2):
+        okay, swag = p.process_frame({"stream_id": "m", "frame_id": frame_id},
+                                     {"images": frames, "overlay": cases.OVERLAY_SMALL})
+        assert okay
+    elements = captured["frame"].metrics["pipeline_elements"]
+    resize, overlay = elements["time_ImageResize"], elements["time_ImageOverlay"]
+    assert isinstance(resize, GpuSeconds) and isinstance(overlay, GpuSeconds)
+    assert overlay.fused_into == "ImageResize" and not overlay.events
+    assert 2e-6 < resize.gpu < 0.05                                    # microseconds .. milliseconds of kernels
+    assert float(resize) >= resize.gpu and f"{resize * 1000:.3f}"      # what PE_Metrics does with the value
+    assert not isinstance(elements["time_Feed"], GpuSeconds)
