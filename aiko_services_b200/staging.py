@@ -150,6 +150,21 @@ class FrameStager:
                     batch.stager = self
                     out.append((batch, positions))
                     continue
+                if len(arrs) > 1 and all(a.flags.c_contiguous and a.dtype == np.uint8 for a in arrs):
+                    sources = [torch.from_numpy(a) for a in arrs]
+                    if all(t.is_pinned() for t in sources):
+                        # frames of several streams, each already in page-locked memory (decoders'
+                        # or cameras' own buffers): one asynchronous copy per frame straight into
+                        # the batch on the device -- no staging copy on the host
+                        lane = self.next_lane()
+                        with torch.cuda.stream(lane):
+                            dev = torch.empty((len(arrs),) + arrs[0].shape, dtype=torch.uint8, device=self.device)
+                            for k, t in enumerate(sources):
+                                dev[k].copy_(t, non_blocking=True)
+                        batch = DeviceBatch(dev, lane)
+                        batch.stager = self
+                        out.append((batch, positions))
+                        continue
                 nbytes = sum(a.nbytes for a in arrs)
                 i, pinned = self._slot(nbytes)
                 view = pinned[:nbytes].view((len(arrs),) + arrs[0].shape)

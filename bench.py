@@ -304,6 +304,13 @@ def cpu_baseline_objects(steps, warmup):
     return port, shipped, step_s
 
 
+def sharding_ids(world, total=64):
+    """Config 3's streams: ids whose owners (crc32(stream_id) % world, sharding.owner_rank) split the
+    64 streams evenly over the ranks; -> {rank: [stream ids]}"""
+    from aiko_services_b200 import sharding
+    return sharding.balanced_stream_ids(total // world, world)
+
+
 def config_dict(world):
     return {"workload": WORKLOAD, "frames_per_step_per_gpu": BATCH,
             "cuda_streams": f"consecutive batches alternate between {LANES} CUDA streams with their own output buffers",
@@ -530,6 +537,48 @@ def run_gpu_arm(args):
     h2d = BATCH * SRC_H * SRC_W * 3
     d2h = BATCH * DST_H * DST_W * 3
 
+    # ---- BASELINE config 3: 64 concurrent 1080p streams sharded by stream_id across the ranks
+    # (sharding.owner_rank, no collective), one frame per stream per step, all of a rank's streams
+    # batched into one launch by Pipeline.process_frames; frames sit in page-locked host memory.
+    config3 = None
+    try:
+        c3_ids = sharding_ids(world)[rank]
+        c3_pipeline = Pipeline(E2E_DEFINITION)
+        c3_frames = {}
+        for k, sid in enumerate(c3_ids):
+            assert c3_pipeline.create_stream(sid)
+            t = torch.empty((SRC_H, SRC_W, 3), dtype=torch.uint8).pin_memory()
+            t.numpy()[...] = synthetic_batch(30_000 + 64 * rank + k, 1)[0]
+            c3_frames[sid] = t.numpy()
+
+        def c3_step(i):
+            work = [({"stream_id": sid, "frame_id": i}, {"images": [c3_frames[sid]], "overlay": OVERLAY})
+                    for sid in c3_ids]
+            results = c3_pipeline.process_frames(work)
+            assert all(okay for okay, _ in results)
+            batches = {id(swag["images"][0].batch): swag["images"][0].batch for _, swag in results}
+            return batches.values()
+
+        def c3_collect(batches):
+            return sum(int(b.host_view()[0, 0, 0, 0]) for b in batches)
+
+        c3_steps = max(3, min(args.steps, 20))
+        for i in range(3):
+            c3_collect(c3_step(i))
+        barrier()
+        t3 = time.perf_counter()
+        pending = c3_step(0)
+        for i in range(1, c3_steps):
+            nxt = c3_step(i)
+            c3_collect(pending)
+            pending = nxt
+        c3_collect(pending)
+        barrier()
+        config3 = {"seconds": time.perf_counter() - t3, "frames": len(c3_ids) * c3_steps, "steps": c3_steps,
+                   "streams": len(c3_ids)}
+    except Exception as error:
+        config3 = {"error": repr(error)}
+
     # ---- end to end from JPEG bytes (BASELINE config 1): the frames are born on the device.  32 JPEG
     # blobs per step in page-locked host memory -> nvJPEG batched decode -> antialiased bicubic resize
     # (the reference's PIL branch) -> D2H of the 640x480 frames.  Two CUDA streams alternate.
@@ -583,6 +632,8 @@ def run_gpu_arm(args):
     from aiko_services_b200 import sharding
     (ms, e2e_s, changing_s), (frames_timed, frames_e2e, frames_changing) = sharding.combine(
         [ms, e2e_s, changing_s], [BATCH * args.steps, BATCH * e2e_steps, BATCH * changing_steps], device=device)
+    c3_ok = sharding.combine([0.0 if (config3 and "error" not in config3) else 1.0], [], device=device)[0][0] == 0.0
+    c3_totals = sharding.combine([config3["seconds"]], [config3["frames"], config3["streams"]], device=device) if c3_ok else None
     ok_everywhere = sharding.combine([0.0 if (jpeg_result and "error" not in jpeg_result) else 1.0], [], device=device)[0][0] == 0.0
     if ok_everywhere:
         jpeg_totals = sharding.combine([jpeg_result["seconds"]], [jpeg_result["frames"]], device=device)
@@ -641,6 +692,16 @@ def run_gpu_arm(args):
             "gpu_launches": 2 * args.steps * world,
             "clocks": clocks,
         }
+        if c3_totals is not None:
+            (c3_s,), (c3_frames_total, c3_streams) = c3_totals
+            line["config3"] = {"value": c3_frames_total / c3_s, "unit": "frames/s", "streams": int(c3_streams),
+                               "steps": config3["steps"],
+                               "workload": "config3: 64 concurrent 1080p streams sharded by stream_id over the ranks "
+                                           "(no collective), one frame per stream per step, Pipeline.process_frames "
+                                           "batches a rank's streams into one launch; end to end from page-locked host "
+                                           "frames (one cudaMemcpyAsync per frame) to results in host memory"}
+        elif config3 is not None:
+            line["config3"] = {"unavailable": config3.get("error", "failed on another rank")}
         if jpeg_result is not None and "error" not in jpeg_result:
             (jpeg_s,), (jpeg_frames,) = jpeg_totals
             line["e2e_jpeg"] = {"value": jpeg_frames / jpeg_s, "unit": "frames/s", "workload": JPEG_WORKLOAD,
