@@ -24,7 +24,8 @@ constexpr int kTopK = 100;           // AF_SAMPLES_MAXIMUM, audio_io.py:206
 constexpr int kBands = 8;            // AR_BAND_COUNT, audio_io.py:237
 constexpr int kHistBins = 4096;
 constexpr int kDirectSort = 1024;    // up to this many gated bins are sorted directly
-constexpr int kRankSort = 512;       // ... and up to this many by counting ranks instead of exchanging
+constexpr int kRankSort = 512;
+constexpr int kDirectList = kHistBins * 4 / 8;   // u64 entries that fit the histogram's storage (2048)       // ... and up to this many by counting ranks instead of exchanging
 
 struct AudioParams {
   const void* audio;
@@ -231,6 +232,7 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
   const float2 w_odd = __ldg(p.tw_full + 1);          // exp(-2 pi i / n): tw_full[k] = tw_half[k / 2] * w_odd^(k & 1)
 
   for (int w = blockIdx.x; w < p.n_windows; w += gridDim.x) {
+    if (threadIdx.x == 0) s_count = 0;   // gated bins of this window (ordered before their appends by the barriers below)
     // ---- pack the real window into half complex points
     if (p.dtype == 0) {
 #pragma unroll
@@ -271,6 +273,20 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
     // ---- unpack to the spectrum of the real window, magnitudes / 1e6 (audio_io.py:299,309)
     float* amp = reinterpret_cast<float*>(y);          // half + 1 magnitudes, in the idle buffer
     float* out = p.amplitudes + (size_t)w * n;
+    // PE_AudioFilter's gates are applied right here, while the magnitudes are in registers: the few
+    // bins that pass (a tone and its neighbours) go to a small list in shared memory (it shares its
+    // storage with the histogram of the rare many-candidates path, which re-collects everything).
+    const bool gate = p.top_amp != nullptr;
+    const int gate_klo = max(p.gate_lo, 0), gate_khi = min(p.gate_hi, half);
+    unsigned long long* direct = reinterpret_cast<unsigned long long*>(hist);
+    auto gate_bin = [&](int k, float a) {
+      if (k < gate_klo || k > gate_khi || !(a >= p.amp_min && a <= p.amp_max)) return;
+      const int copies = (k != 0 && k != half) ? 2 : 1;
+      const int start = atomicAdd(&s_count, copies);
+      const unsigned long long hi = (unsigned long long)__float_as_uint(a) << 32;
+      if (start < kDirectList) direct[start] = hi | (0xffffffffu - (unsigned)k);
+      if (copies == 2 && start + 1 < kDirectList) direct[start + 1] = hi | (0xffffffffu - (unsigned)(n - k));
+    };
     if (p.dtype == 0 && w + (int)gridDim.x < p.n_windows) prefetch(w + gridDim.x);
     // Bins k and half - k come from the same pair (z[k], z[half - k]): X[k] = E + W^k O and
     // X[half - k] = conj(E - W^k O), so one thread makes both magnitudes from one set of loads.
@@ -293,10 +309,12 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
       amp[k] = a;
       out[k] = a;
       if (k != 0) out[n - k] = a;                         // |X[n-k]| = |X[k]| for real input
+      if (gate) gate_bin(k, a);
       if (kr != k) {
         amp[kr] = b;
         out[kr] = b;
         if (k != 0) out[n - kr] = b;                      // (bin half has no mirror)
+        if (gate) gate_bin(kr, b);
       }
     }
     __syncthreads();
@@ -357,11 +375,15 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
           }
         }
       };
-      if (threadIdx.x == 0) s_count = 0;
-      __syncthreads();
-      collect(0u);
-      __syncthreads();
-      if (s_count > kDirectSort) {
+      const bool direct_ok = s_count <= kDirectList;      // every gated bin is in the small list already
+      if (!direct_ok) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_count = 0;
+        __syncthreads();
+        collect(0u);
+        __syncthreads();
+      }
+      if (!direct_ok && s_count > kDirectSort) {
         // Many bins pass the gates (noise-like input): keep only key bins that can reach the top 100.
         __syncthreads();
         for (int i = threadIdx.x; i < kHistBins; i += NT) hist[i] = 0;
@@ -394,6 +416,7 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
         __syncthreads();
       }
       const int count = min(s_count, list_cap);
+      if (direct_ok) list = direct;
       const unsigned long long* sorted = list;
       if (count <= kRankSort) {
         // Few candidates: every thread finds the rank of its own key by counting the larger ones

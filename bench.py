@@ -15,6 +15,7 @@ stream_id across ranks, no data-path collective; weak scaling (32 frames per ran
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -33,6 +34,7 @@ BATCH = 32
 ALGO_BYTES_PER_FRAME = 960 * SRC_W * 3 + DST_H * DST_W * 3
 FALLBACK_HBM_GBS = 6650.0
 OVERLAY_KERNEL = "overlay_cells_kernel"
+USE_GRAPHS = os.environ.get("AIKO_BENCH_GRAPHS", "1") != "0"   # replay the timed steps as CUDA graphs
 LANES = max(1, int(os.environ.get("AIKO_BENCH_LANES", "3")))   # CUDA streams the device-resident loop alternates between
 N_ROTATING_BATCHES = 4     # 4 x 199 MB of distinct inputs: each step reads a batch the 126 MB L2 cannot hold
 
@@ -314,6 +316,8 @@ def sharding_ids(world, total=64):
 def config_dict(world):
     return {"workload": WORKLOAD, "frames_per_step_per_gpu": BATCH,
             "cuda_streams": f"consecutive batches alternate between {LANES} CUDA streams with their own output buffers",
+            "launch": "CUDA graphs of lcm(streams, rotating batches) steps captured from the C-ABI calls, replayed; "
+                      "the remainder eagerly" if USE_GRAPHS else "eager C-ABI calls",
             "l2": f"{N_ROTATING_BATCHES} rotating input batches of 199 MB each (> 126 MB L2), no flush",
             "sharding": "independent streams per rank, no collective" if world > 1 else "single GPU"}
 
@@ -393,19 +397,56 @@ def run_gpu_arm(args):
             ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=exp_ov,
                               out=lane_outs[i % lanes], stream=lane_streams[i % lanes])
 
-    def timed_steps(lanes):
-        """-> ms for args.steps steps: CUDA events on the main stream, which the lanes fork from and join."""
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record(stream)
-        for s in lane_streams[:lanes] if lanes > 1 else ():
-            s.wait_event(ev0)
-        for i in range(args.steps):
+    # The timed loop is issued as CUDA graphs of GRAPH_STEPS consecutive steps (captured once from the very
+    # same C-ABI calls, fork / join over the lane streams included) so that the 35 us step is not paced by
+    # the ~30 us of host time one call costs through Python; the remainder K % GRAPH_STEPS runs eagerly.
+    graph_steps = math.lcm(LANES, N_ROTATING_BATCHES)
+    graphs = {}
+
+    def issue(first, count, lanes):
+        """Fork from the current stream to the lanes, enqueue steps [first, first + count), join back."""
+        cur = torch.cuda.current_stream()
+        if lanes > 1:
+            fork = torch.cuda.Event()
+            fork.record(cur)
+            for s in lane_streams[:lanes]:
+                s.wait_event(fork)
+        for i in range(first, first + count):
             step(i, lanes)
-        for s in lane_streams[:lanes] if lanes > 1 else ():
-            done = torch.cuda.Event()
-            done.record(s)
-            stream.wait_event(done)
-        ev1.record(stream)
+        if lanes > 1:
+            for s in lane_streams[:lanes]:
+                done = torch.cuda.Event()
+                done.record(s)
+                cur.wait_event(done)
+
+    def graph_for(lanes):
+        if lanes not in graphs:
+            graphs[lanes] = None
+            if USE_GRAPHS:
+                try:
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=torch.cuda.Stream(device), capture_error_mode="relaxed"):
+                        issue(0, graph_steps, lanes)
+                    graphs[lanes] = g
+                except Exception as error:          # stay measurable: eager launches
+                    print(f"bench.py: CUDA graph capture failed ({error!r}); launching eagerly", file=sys.stderr)
+                    torch.cuda.synchronize()
+        return graphs[lanes]
+
+    def timed_steps(lanes):
+        """-> CUDA events on the main stream around exactly args.steps steps."""
+        g = graph_for(lanes)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            ev0.record(stream)
+            done = 0
+            if g is not None:
+                for _ in range(args.steps // graph_steps):
+                    g.replay()
+                done = args.steps // graph_steps * graph_steps
+            if done < args.steps:
+                issue(done, args.steps - done, lanes)
+            ev1.record(stream)
         return ev0, ev1
 
     def barrier():
@@ -418,6 +459,10 @@ def run_gpu_arm(args):
     sampler = ClockSampler(local_rank)
     sampler.start()
     time.sleep(0.3)
+    for lanes in (LANES, 1):                  # capture (and upload) the graphs outside the timed region
+        g = graph_for(lanes)
+        if g is not None:
+            g.replay()
     barrier()
     wall0 = time.time()
     ev0, ev1 = timed_steps(LANES)
