@@ -72,6 +72,8 @@ SIGNATURES = {
     "aiko_b200_overlay_marks_host": [_vp, _i, _i, _vp],
     "aiko_b200_overlay_atlas_host": [ctypes.POINTER(AtlasView)],
     "aiko_b200_resize_linear_u8": [_vp, _i, _i, _i, _i, _i64, _i64, _vp, _i, _i, _i64, _i64, _i, _ovp, _vp],
+    "aiko_b200_resize_linear_rows_host": [_i, _i, _vp],
+    "aiko_b200_copy_rows_h2d": [_vp, _vp, _i, _i64, _i64, _vp, _i, _vp],
     "aiko_b200_resize_bicubic_workspace_bytes": [_i, _i, _i, _i],
     "aiko_b200_resize_bicubic_prepare": [_vp, _sz, _i, _i, _i, _i, _vp],
     "aiko_b200_resize_bicubic_aa_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp, _sz, _vp],
@@ -89,6 +91,7 @@ SIGNATURES = {
     "aiko_b200_overlay_u8": [_vp, _vp, _i, _i, _i, _i, _i64, _i64, _ovp, _vp],
     "aiko_b200_swap_rb_u8": [_vp, _vp, _i64, _vp],
     "aiko_b200_bgr2gray_u8": [_vp, _vp, _i64, _i, _vp],
+    "aiko_b200_yuv_u8": [_vp, _vp, _i64, _i, _i, _vp],
     "aiko_b200_gray2bgr_u8": [_vp, _vp, _i64, _vp],
     "aiko_b200_flip_u8": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "aiko_b200_crop_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _vp],

@@ -103,6 +103,70 @@ __global__ void __launch_bounds__(kThreads) gray2bgr_kernel(const uint8_t* __res
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// RGB / BGR <-> YUV (extension: north_star names it, the reference has no call site; the oracle is
+// cv2.cvtColor(COLOR_RGB2YUV / BGR2YUV / YUV2RGB / YUV2BGR) on 8-bit images, whose 14-bit fixed-point
+// arithmetic this restates -- checked against cv2 over all 2^24 colours in tests/test_oracle_golden.py):
+//   Y = (4899 R + 9617 G + 1868 B + 8192) >> 14
+//   U = ((B - Y) 8061 + (128 << 14) + 8192) >> 14      V = ((R - Y) 14369 + (128 << 14) + 8192) >> 14
+//   R = Y + ((V - 128) 18678 + 8192 >> 14)   G = Y + ((V - 128)(-9519) + (U - 128)(-6472) + 8192 >> 14)
+//   B = Y + ((U - 128) 33292 + 8192 >> 14)    each result saturated to 0..255.
+// 16 pixels (three uint8x16 vectors) per thread in and out.
+__device__ __forceinline__ int sat8(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
+__device__ __forceinline__ int descale14(int v) { return (v + (1 << 13)) >> 14; }
+
+// p = c0 | c1 << 8 | c2 << 16 (memory order) -> converted pixel in the same packing
+__device__ __forceinline__ uint32_t yuv_pixel(uint32_t p, int bgr_order, int inverse) {
+  const int c0 = p & 0xff, c1 = (p >> 8) & 0xff, c2 = (p >> 16) & 0xff;
+  if (!inverse) {
+    const int r = bgr_order ? c2 : c0, g = c1, b = bgr_order ? c0 : c2;
+    const int y = descale14(r * 4899 + g * 9617 + b * 1868);
+    const int u = descale14((b - y) * 8061 + (128 << 14)), v = descale14((r - y) * 14369 + (128 << 14));
+    return (uint32_t)sat8(y) | ((uint32_t)sat8(u) << 8) | ((uint32_t)sat8(v) << 16);
+  }
+  const int y = c0, u = c1 - 128, v = c2 - 128;
+  const int r = sat8(y + descale14(v * 18678)), g = sat8(y + descale14(v * -9519 + u * -6472));
+  const int b = sat8(y + descale14(u * 33292));
+  return bgr_order ? ((uint32_t)b | ((uint32_t)g << 8) | ((uint32_t)r << 16))
+                   : ((uint32_t)r | ((uint32_t)g << 8) | ((uint32_t)b << 16));
+}
+
+__global__ void __launch_bounds__(kThreads) yuv_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                                       long long n_groups, long long n_pixels, int bgr_order,
+                                                       int inverse, int vec_ok) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < n_groups; g += stride) {
+    if (vec_ok && (g + 1) * 16 <= n_pixels) {
+      const uint4* s = reinterpret_cast<const uint4*>(src) + g * 3;
+      const uint4 v0 = ldg_stream(s), v1 = ldg_stream(s + 1), v2 = ldg_stream(s + 2);
+      const uint32_t w[12] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w};
+      uint32_t o[12];
+#pragma unroll
+      for (int q = 0; q < 4; q++) {        // 4 pixels = 3 words in, 3 words out
+        const uint32_t a = w[3 * q], b = w[3 * q + 1], c = w[3 * q + 2];
+        const uint32_t p0 = yuv_pixel(a & 0xffffffu, bgr_order, inverse);
+        const uint32_t p1 = yuv_pixel(((a >> 24) | (b << 8)) & 0xffffffu, bgr_order, inverse);
+        const uint32_t p2 = yuv_pixel(((b >> 16) | (c << 16)) & 0xffffffu, bgr_order, inverse);
+        const uint32_t p3 = yuv_pixel(c >> 8, bgr_order, inverse);
+        o[3 * q] = p0 | (p1 << 24);
+        o[3 * q + 1] = (p1 >> 8) | (p2 << 16);
+        o[3 * q + 2] = (p2 >> 16) | (p3 << 8);
+      }
+      uint4* d = reinterpret_cast<uint4*>(dst) + g * 3;
+      stg_stream(d, make_uint4(o[0], o[1], o[2], o[3]));
+      stg_stream(d + 1, make_uint4(o[4], o[5], o[6], o[7]));
+      stg_stream(d + 2, make_uint4(o[8], o[9], o[10], o[11]));
+    } else {
+      const long long pe = min((g + 1) * 16, n_pixels);
+      for (long long px = g * 16; px < pe; px++) {
+        const uint32_t p = src[3 * px] | ((uint32_t)src[3 * px + 1] << 8) | ((uint32_t)src[3 * px + 2] << 16);
+        const uint32_t r = yuv_pixel(p, bgr_order, inverse);
+        dst[3 * px] = (uint8_t)r; dst[3 * px + 1] = (uint8_t)(r >> 8); dst[3 * px + 2] = (uint8_t)(r >> 16);
+      }
+    }
+  }
+}
+
 // Horizontal flip of RGB rows whose width is a multiple of 16 pixels, entirely in registers:
 // a thread loads 16 pixels (3 aligned vectors), reverses their order with byte permutes and
 // stores them at the mirrored position of the (possibly vertically mirrored) row.
@@ -245,6 +309,18 @@ extern "C" int aiko_b200_swap_rb_u8(const uint8_t* src, uint8_t* dst, int64_t n_
   const int vec_ok = ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0;
   swap_rb_kernel<<<stream_grid(groups), kThreads, 0, (cudaStream_t)stream>>>(src, dst, groups, n_pixels, vec_ok);
   return cuda_status(cudaGetLastError(), "swap_rb launch");
+}
+
+extern "C" int aiko_b200_yuv_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, int bgr_order, int inverse,
+                                void* stream) {
+  AIKO_CHECK_ARG(n_pixels >= 0, "yuv: n_pixels < 0");
+  if (n_pixels == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(src && dst, "yuv: null pointer");
+  const long long groups = (n_pixels + 15) / 16;
+  const int vec_ok = ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0;
+  yuv_kernel<<<stream_grid(groups), kThreads, 0, (cudaStream_t)stream>>>(src, dst, groups, n_pixels, bgr_order ? 1 : 0,
+                                                                          inverse ? 1 : 0, vec_ok);
+  return cuda_status(cudaGetLastError(), "yuv launch");
 }
 
 extern "C" int aiko_b200_bgr2gray_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, int rgb_order,

@@ -18,6 +18,7 @@
 // the shapes the register-resident path does not take): same row structure, taps read straight
 // from global memory.
 #include <atomic>
+#include <math.h>
 
 #include "overlay.cuh"
 
@@ -746,4 +747,41 @@ extern "C" int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int 
     case 3: return launch_generic<3>(p, st);
     default: return launch_generic<4>(p, st);
   }
+}
+
+// Which source rows does aiko_b200_resize_linear_u8 read for src_h -> dst_h?  (Same arithmetic as
+// vertical_coef above, on the host.)  needed_host[y] = 1 for every row that carries weight.
+extern "C" int aiko_b200_resize_linear_rows_host(int src_h, int dst_h, uint8_t* needed_host) {
+  AIKO_CHECK_ARG(src_h > 0 && dst_h > 0 && needed_host, "resize_linear_rows: bad argument");
+  const double scale = 1.0 / ((double)dst_h / (double)src_h);
+  for (int y = 0; y < src_h; y++) needed_host[y] = 0;
+  for (int dy = 0; dy < dst_h; dy++) {
+    volatile double pos = ((double)dy + 0.5) * scale;      // (volatile: every step rounded to double, as on the device)
+    pos = pos + -0.5;
+    const float f = (float)pos;
+    const int s = (int)floorf(f);
+    const int y0 = s < 0 ? 0 : (s > src_h - 1 ? src_h - 1 : s);
+    const int y1 = s + 1 < 0 ? 0 : (s + 1 > src_h - 1 ? src_h - 1 : s + 1);
+    needed_host[y0] = 1;
+    needed_host[y1] = 1;
+  }
+  return AIKO_B200_OK;
+}
+
+// Host -> device copy of the listed row runs of every frame of a batch (runs_host: first row, row count
+// pairs): one strided copy per run across all frames.  The rows in between are left as they are.
+extern "C" int aiko_b200_copy_rows_h2d(uint8_t* dst, const uint8_t* src_host, int n_frames, int64_t frame_bytes,
+                                       int64_t row_bytes, const int32_t* runs_host, int n_runs, void* stream) {
+  AIKO_CHECK_ARG(n_frames >= 0 && n_runs >= 0 && frame_bytes > 0 && row_bytes > 0, "copy_rows: bad size");
+  if (n_frames == 0 || n_runs == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(dst && src_host && runs_host, "copy_rows: null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  for (int r = 0; r < n_runs; r++) {
+    const int64_t first = runs_host[2 * r], count = runs_host[2 * r + 1];
+    AIKO_CHECK_ARG(first >= 0 && count > 0 && (first + count) * row_bytes <= frame_bytes, "copy_rows: run %d outside the frame", r);
+    AIKO_CUDA(cudaMemcpy2DAsync(dst + first * row_bytes, (size_t)frame_bytes, src_host + first * row_bytes,
+                                (size_t)frame_bytes, (size_t)(count * row_bytes), (size_t)n_frames,
+                                cudaMemcpyHostToDevice, st));
+  }
+  return AIKO_B200_OK;
 }

@@ -58,7 +58,7 @@ class DeviceBatch:
             if step[0] in ("resize_linear", "resize_bicubic", "resize_pil"):
                 w, h = step[1], step[2]
             elif step[0] == "convert":
-                c = {"RGB2BGR": 3, "BGR2RGB": 3, "RGB2GRAY": 1, "BGR2GRAY": 1, "GRAY2BGR": 3}[step[1]]
+                c = {"RGB2GRAY": 1, "BGR2GRAY": 1}.get(step[1], 3)
         return (h, w) if c == 1 else (h, w, c)
 
     def then(self, *step):
@@ -185,6 +185,8 @@ class DeviceBatch:
                     t = ops.bgr2gray(t, rgb_order=(code == "RGB2GRAY"))
                 elif code == "GRAY2BGR":
                     t = ops.gray2bgr(t)
+                elif code in ("RGB2YUV", "BGR2YUV", "YUV2RGB", "YUV2BGR"):
+                    t = ops.yuv(t, bgr_order="BGR" in code, inverse=code.startswith("YUV"))
                 else:
                     raise ValueError(f"unknown conversion {code}")
             elif kind == "flip":

@@ -19,7 +19,7 @@ from .common_io import DataSource, DataTarget, contains_all
 __all__ = ["ImageConvert", "ImageOutput", "ImageOverlay", "ImageReadFile", "ImageResize", "ImageToTensor",
            "ImageWriteFile"]
 
-_CONVERSIONS = ("RGB2BGR", "BGR2RGB", "RGB2GRAY", "BGR2GRAY", "GRAY2BGR")
+_CONVERSIONS = ("RGB2BGR", "BGR2RGB", "RGB2GRAY", "BGR2GRAY", "GRAY2BGR", "RGB2YUV", "BGR2YUV", "YUV2RGB", "YUV2BGR")
 _FLIPS = {"vertical": 0, "horizontal": 1, "both": -1}
 
 
@@ -52,7 +52,8 @@ def _apply(stream, images, step):
     if not images:
         return []
     out = [None] * len(images)
-    for batch, positions in stager_for(stream).upload(images):
+    hint = (step[1], step[2]) if step[0] == "resize_linear" else None     # only the rows a resize reads are staged
+    for batch, positions in stager_for(stream).upload(images, resize_to=hint):
         result = batch.then(*step).images()
         for k, pos in enumerate(positions):
             out[pos] = result[k]
@@ -293,7 +294,9 @@ def _cross_stream(prepare):
                     owner.append((ci, k, step))
             outputs = {ci: [None] * len(images) for ci, images, _ in members}
             if flat:
-                for batch, positions in _pipeline_stager(pipeline, device_index).upload(flat):
+                first_step = owner[0][2]
+                hint = (first_step[1], first_step[2]) if first_step[0] == "resize_linear" else None
+                for batch, positions in _pipeline_stager(pipeline, device_index).upload(flat, resize_to=hint):
                     step = owner[positions[0]][2]
                     if step[0] == "overlay":   # one overlay dict per frame, in batch order
                         step = ("overlay", [owner[p][2][1] for p in positions])

@@ -412,6 +412,17 @@ def bgr2gray(src, *, rgb_order=False, out=None, stream=None):
     return out
 
 
+def yuv(src, *, bgr_order=False, inverse=False, out=None, stream=None):
+    """cv2.cvtColor(RGB2YUV / BGR2YUV) of uint8 frames, or YUV2RGB / YUV2BGR with ``inverse``."""
+    _require_cuda(src, "yuv src")
+    if src.shape[-1] != 3:
+        raise ValueError("yuv: last dimension must be 3")
+    out = _out(out, src.shape, src.device, "yuv out")
+    with _on_device(src.device):
+        _T().yuv_u8(src, out, bool(bgr_order), bool(inverse), _stream_int(stream))
+    return out
+
+
 def gray2bgr(src, *, out=None, stream=None):
     _require_cuda(src, "gray2bgr src")
     out = _out(out, tuple(src.shape) + (3,), src.device, "gray2bgr out")

@@ -111,6 +111,13 @@ def bgr2gray_u8(src, out, rgb_order, stream):
                                                   _vp(stream)))
 
 
+@_op("yuv_u8(Tensor src, Tensor(a!) out, bool bgr_order, bool inverse, int stream) -> ()")
+def yuv_u8(src, out, bgr_order, inverse, stream):
+    with _current(src):
+        check(_native.lib().aiko_b200_yuv_u8(src.data_ptr(), out.data_ptr(), src.numel() // 3, int(bgr_order),
+                                             int(inverse), _vp(stream)))
+
+
 @_op("gray2bgr_u8(Tensor src, Tensor(a!) out, int stream) -> ()")
 def gray2bgr_u8(src, out, stream):
     with _current(src):

@@ -208,6 +208,14 @@ int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, int src_h, 
                                    uint8_t* dst, int dst_h, int dst_w, const void* workspace,
                                    size_t workspace_bytes, void* stream);
 
+/* The source rows aiko_b200_resize_linear_u8 reads for src_h -> dst_h (needed_host[y] = 1): a 2.25x   */
+/* vertical reduction touches 8 rows of every 9.  With aiko_b200_copy_rows_h2d (one strided            */
+/* cudaMemcpy2DAsync per run of rows, across all frames of a batch laid out frame_bytes apart) a       */
+/* caller that stages frames for a resize ships only the rows that carry weight over PCIe.             */
+int aiko_b200_resize_linear_rows_host(int src_h, int dst_h, uint8_t* needed_host);
+int aiko_b200_copy_rows_h2d(uint8_t* dst, const uint8_t* src_host, int n_frames, int64_t frame_bytes, int64_t row_bytes,
+                            const int32_t* runs_host, int n_runs, void* stream);
+
 /* What PIL.Image.resize does around the filter for other modes (image_io.py:218 resizes   */
 /* whatever mode the file had):                                                             */
 /*   premultiply_u8 : RGBA (channels 4) / LA (channels 2) -> 4-byte premultiplied pixels     */
@@ -264,6 +272,12 @@ int aiko_b200_swap_rb_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, voi
 /* cv2.cvtColor(.., COLOR_BGR2GRAY) (rgb_order=0) / COLOR_RGB2GRAY (1):      */
 /* webcam_io.py:124, image_io.py:158.                                        */
 int aiko_b200_bgr2gray_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, int rgb_order, void* stream);
+/* RGB / BGR <-> YUV, 8 bits per channel (extension: BASELINE.json's north_star names YUV     */
+/* conversion, the reference has no call site for it).  Arithmetic: cv2.cvtColor(..,          */
+/* COLOR_RGB2YUV / COLOR_BGR2YUV) for inverse = 0 and COLOR_YUV2RGB / COLOR_YUV2BGR for       */
+/* inverse = 1 (bgr_order picks the BGR variants), 14-bit fixed point, bit-exact with OpenCV   */
+/* over all 2^24 colours.  n_pixels 3-byte pixels.                                            */
+int aiko_b200_yuv_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, int bgr_order, int inverse, void* stream);
 /* cv2.cvtColor(.., COLOR_GRAY2BGR): image_io.py:115.                        */
 int aiko_b200_gray2bgr_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, void* stream);
 /* cv2.flip(image, flip_code): webcam_io.py:127 (1, horizontal), :129 (0,    */

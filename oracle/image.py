@@ -179,3 +179,26 @@ def pil_resize(img, mode, width, height):
         out[:, xt < 0] = 0
         return out
     return resize_bicubic_aa(img, width, height)
+
+
+# ---- RGB / BGR <-> YUV (extension: no reference call site; numpy restatement of cv2.cvtColor's 8-bit
+# arithmetic, pinned against cv2 over all 2^24 colours in tests/test_oracle_golden.py)
+def _descale14(x):
+    return (x + (1 << 13)) >> 14
+
+
+def yuv(img, bgr_order=False, inverse=False):
+    a = np.asarray(img, np.uint8).astype(np.int64)
+    if not inverse:
+        r, g, b = (a[..., 2], a[..., 1], a[..., 0]) if bgr_order else (a[..., 0], a[..., 1], a[..., 2])
+        y = _descale14(r * 4899 + g * 9617 + b * 1868)
+        u = _descale14((b - y) * 8061 + (128 << 14))
+        v = _descale14((r - y) * 14369 + (128 << 14))
+        out = np.stack([y, u, v], -1)
+    else:
+        y, u, v = a[..., 0], a[..., 1] - 128, a[..., 2] - 128
+        r = y + _descale14(v * 18678)
+        g = y + _descale14(v * -9519 + u * -6472)
+        b = y + _descale14(u * 33292)
+        out = np.stack([b, g, r] if bgr_order else [r, g, b], -1)
+    return np.clip(out, 0, 255).astype(np.uint8)

@@ -512,3 +512,22 @@ def test_pil_mode_resize_random_vs_oracle(cuda):
         got = host(ops.resize_pil(dev(frames, cuda), mode, dw, dh))
         for k in range(3):
             np.testing.assert_array_equal(got[k], O.pil_resize(frames[k], mode, dw, dh), err_msg=f"{mode} {sw}x{sh}->{dw}x{dh}")
+
+
+def test_yuv_conversions_vs_oracle(cuda):
+    """RGB / BGR <-> YUV (cv2.cvtColor arithmetic, oracle pinned on all 2^24 colours): vector path,
+    tails that are not a multiple of 16 pixels, unaligned buffers, and the ImageConvert recipe step."""
+    rng = np.random.default_rng(31)
+    for shape in ((3, 64, 96, 3), (1, 7, 13, 3), (2, 33, 50, 3)):
+        frames = rng.integers(0, 256, shape, dtype=np.uint8)
+        d = dev(frames, cuda)
+        for bgr in (False, True):
+            for inverse in (False, True):
+                got = host(ops.yuv(d, bgr_order=bgr, inverse=inverse))
+                np.testing.assert_array_equal(got, O.yuv(frames, bgr, inverse))
+    flat = torch.from_numpy(rng.integers(0, 256, 3 * 1000 + 1, dtype=np.uint8)).to(cuda)
+    src = flat[1:].view(1, 10, 100, 3)                      # deliberately off the 16-byte grid
+    np.testing.assert_array_equal(host(ops.yuv(src.contiguous())), O.yuv(host(src)))
+    out = torch.empty(3 * 1000 + 1, dtype=torch.uint8, device=cuda)[1:].view(1, 10, 100, 3)
+    torch.ops.aiko_b200.yuv_u8(src, out, False, False, torch.cuda.current_stream().cuda_stream)
+    np.testing.assert_array_equal(host(out), O.yuv(host(src)))

@@ -149,3 +149,16 @@ def test_pil_mode_resize_oracle_vs_pillow_random():
         im = cases.pil_image(int(rng.integers(1 << 30)), mode, sh, sw)
         want = _pil_array(im.resize((dw, dh)), mode)
         np.testing.assert_array_equal(O.pil_resize(_pil_array(im, mode), mode, dw, dh), want, err_msg=f"{mode} {sw}x{sh}->{dw}x{dh}")
+
+
+def test_yuv_oracle_equals_cv2_on_every_colour():
+    """Extension (north_star names YUV; the reference never converts to it): the oracle of record is
+    cv2.cvtColor on 8-bit images -- all 2^24 colours, both channel orders, both directions."""
+    cv2 = pytest.importorskip("cv2")
+    codes = {(False, False): cv2.COLOR_RGB2YUV, (True, False): cv2.COLOR_BGR2YUV,
+             (False, True): cv2.COLOR_YUV2RGB, (True, True): cv2.COLOR_YUV2BGR}
+    for c0 in range(0, 256, 64):
+        cube = np.stack(np.meshgrid(np.arange(c0, c0 + 64), np.arange(256), np.arange(256), indexing="ij"), -1)
+        cube = cube.astype(np.uint8).reshape(-1, 1, 3)
+        for (bgr, inverse), code in codes.items():
+            np.testing.assert_array_equal(O.yuv(cube, bgr, inverse), cv2.cvtColor(cube, code))
