@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
     tw = tws;
     __syncthreads();
   }
-  __shared__ int s_count, s_threshold_bin;
+  __shared__ int s_count, s_threshold_bin, s_kept;
   __shared__ float s_band[kBands][4];
   __shared__ unsigned long long s_top[kTopK];
   __shared__ int hist[kHistBins];
@@ -420,12 +420,53 @@ __global__ void __launch_bounds__(NT, 1) audio_chain_kernel(const AudioParams p)
       const unsigned long long* sorted = list;
       if (count <= kRankSort) {
         // Few candidates: every thread finds the rank of its own key by counting the larger ones
-        // (keys are distinct: the bin index is part of them).  No exchanges, one barrier.
-        for (int i = threadIdx.x; i < count; i += NT) {
-          const unsigned long long key = list[i];
+        // (keys are distinct: the bin index is part of them).  No exchanges.  With more than 100
+        // candidates (a loud tone leaks into ~300 bins) only those that can reach the top 100 are
+        // ranked: a 512-bin histogram over the amplitude bits (the gate spans 442 such bins) gives the
+        // bin holding the 100th value, and the candidates at or above it are compacted first --
+        // the quadratic part shrinks from count^2 to little more than 100^2 comparisons.
+        const unsigned long long* cand = list;
+        int ncand = count;
+        if (count > kTopK && direct_ok) {
+          int* fine = hist + 2048;                                      // (the list itself sits in hist[0 .. 1024))
+          unsigned long long* keep = reinterpret_cast<unsigned long long*>(hist + 2560);
+          const unsigned base = __float_as_uint(p.amp_min) >> 17;
+          auto fine_bin = [&](unsigned long long key) { return min((int)((unsigned)(key >> 49) - base), 511); };
+          if (threadIdx.x < 512) fine[threadIdx.x] = 0;
+          if (threadIdx.x == 0) { s_threshold_bin = 0; s_kept = 0; }
+          __syncthreads();
+          for (int i = threadIdx.x; i < count; i += NT) atomicAdd(&fine[fine_bin(list[i])], 1);
+          __syncthreads();
+          if (threadIdx.x < 32) {                                       // highest bin T with count(bins >= T) >= 100
+            int running = 0, found = -1;
+            for (int top = 511; top >= 0 && found < 0; top -= 32) {
+              const int c = fine[top - (int)threadIdx.x];               // lane 0 = highest bin of the chunk
+              int incl = c;
+#pragma unroll
+              for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                if ((int)threadIdx.x >= d) incl += t;
+              }
+              const unsigned hit = __ballot_sync(0xffffffffu, running + incl >= kTopK);
+              if (hit) found = top - (__ffs(hit) - 1);
+              running += __shfl_sync(0xffffffffu, incl, 31);
+            }
+            if (threadIdx.x == 0) s_threshold_bin = max(found, 0);
+          }
+          __syncthreads();
+          for (int i = threadIdx.x; i < count; i += NT) {
+            const unsigned long long key = list[i];
+            if (fine_bin(key) >= s_threshold_bin) keep[atomicAdd(&s_kept, 1)] = key;
+          }
+          __syncthreads();
+          cand = keep;
+          ncand = s_kept;
+        }
+        for (int i = threadIdx.x; i < ncand; i += NT) {
+          const unsigned long long key = cand[i];
           int rank = 0;
 #pragma unroll 4
-          for (int j = 0; j < count; j++) rank += (list[j] > key) ? 1 : 0;
+          for (int j = 0; j < ncand; j++) rank += (cand[j] > key) ? 1 : 0;
           if (rank < kTopK) s_top[rank] = key;
         }
         sorted = s_top;

@@ -311,3 +311,19 @@ def test_element_metrics_carry_gpu_time(cuda, tmp_path, monkeypatch):
     assert 2e-6 < resize.gpu < 0.05                                    # microseconds .. milliseconds of kernels
     assert float(resize) >= resize.gpu and f"{resize * 1000:.3f}"      # what PE_Metrics does with the value
     assert not isinstance(elements["time_Feed"], GpuSeconds)
+
+
+@pytest.mark.gpu
+def test_staging_only_the_rows_a_resize_reads(cuda, monkeypatch):
+    """AIKO_B200_COPY_NEEDED_ROWS=1: frames staged for a bilinear resize cross PCIe without the source rows
+    that carry no weight (aiko_b200_resize_linear_rows_host / aiko_b200_copy_rows_h2d); same pixels."""
+    from aiko_services_b200.staging import FrameStager, needed_row_runs
+    runs = needed_row_runs(1080, 480)
+    assert runs is not None and sum(list(runs[0])[1::2]) == 960 and needed_row_runs(480, 480) is None
+    monkeypatch.setenv("AIKO_B200_COPY_NEEDED_ROWS", "1")
+    stager = FrameStager(cuda)
+    frames = [cases.frame(6100 + k, 270, 480, 3) for k in range(3)]
+    (batch, _), = stager.upload(frames, resize_to=(160, 120))
+    out = batch.then("resize_linear", 160, 120).host()
+    for k in range(3):
+        np.testing.assert_array_equal(out[k], O.resize_linear(frames[k], 160, 120))
