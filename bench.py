@@ -419,31 +419,38 @@ def run_gpu_arm(args):
                 done.record(s)
                 cur.wait_event(done)
 
-    def graph_for(lanes):
-        if lanes not in graphs:
-            graphs[lanes] = None
-            if USE_GRAPHS:
+    def graph_for(lanes, count=None):
+        """A CUDA graph of ``count`` steps (default: the full rotation) starting at step index 0."""
+        count = graph_steps if count is None else count
+        key = (lanes, count)
+        if key not in graphs:
+            graphs[key] = None
+            if USE_GRAPHS and count > 0:
                 try:
                     g = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(g, stream=torch.cuda.Stream(device), capture_error_mode="relaxed"):
-                        issue(0, graph_steps, lanes)
-                    graphs[lanes] = g
+                        issue(0, count, lanes)
+                    graphs[key] = g
                 except Exception as error:          # stay measurable: eager launches
                     print(f"bench.py: CUDA graph capture failed ({error!r}); launching eagerly", file=sys.stderr)
                     torch.cuda.synchronize()
-        return graphs[lanes]
+        return graphs[key]
 
     def timed_steps(lanes):
-        """-> CUDA events on the main stream around exactly args.steps steps."""
-        g = graph_for(lanes)
+        """-> CUDA events on the main stream around exactly args.steps steps: whole rotations as replays
+        of one graph, the remaining K % rotation steps as one replay of a second, shorter graph."""
+        full, rest = graph_for(lanes), graph_for(lanes, args.steps % graph_steps)
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with torch.cuda.stream(stream):
             ev0.record(stream)
             done = 0
-            if g is not None:
+            if full is not None:
                 for _ in range(args.steps // graph_steps):
-                    g.replay()
+                    full.replay()
                 done = args.steps // graph_steps * graph_steps
+                if rest is not None:
+                    rest.replay()
+                    done = args.steps
             if done < args.steps:
                 issue(done, args.steps - done, lanes)
             ev1.record(stream)
@@ -460,9 +467,9 @@ def run_gpu_arm(args):
     sampler.start()
     time.sleep(0.3)
     for lanes in (LANES, 1):                  # capture (and upload) the graphs outside the timed region
-        g = graph_for(lanes)
-        if g is not None:
-            g.replay()
+        for g in (graph_for(lanes), graph_for(lanes, args.steps % graph_steps)):
+            if g is not None:
+                g.replay()
     barrier()
     wall0 = time.time()
     ev0, ev1 = timed_steps(LANES)

@@ -1,6 +1,8 @@
 """One-off sweep of ImageOverlay's drawing over random frame sizes and random detection lists:
-overlay alone (copy + touched groups) and fused behind a resize, against the CPU replay of the same
-draw list (tests/util.py).  python benchmarks/stress_overlay.py [seed] [cases]"""
+overlay alone (copy + cell kernel) and fused behind a resize, with one list shared by the frames or
+one list per frame, against the CPU replay of the same draw list (tests/util.py) AND, where OpenCV is
+installed, against the reference element's own cv2 calls (oracle/reference_port.py).
+python benchmarks/stress_overlay.py [seed] [cases]"""
 import os
 import sys
 import time
@@ -15,6 +17,8 @@ from aiko_services_b200 import ops  # noqa: E402
 from aiko_services_b200.overlay_plan import build_ops  # noqa: E402
 from aiko_services_b200.text_atlas import TextAtlas  # noqa: E402
 from oracle import image as O  # noqa: E402
+from oracle import reference_port  # noqa: E402
+from aiko_services_b200.overlay_plan import plan  # noqa: E402
 from util import overlay_cpu, random_overlay  # noqa: E402
 
 
@@ -42,6 +46,20 @@ def main():
             ov = ops.DeviceOverlay.from_host([build_ops(overlay, W, H, "rgb", atlas)] * n, dev, atlas.device(dev), width=W, height=H)
             got = ops.resize_linear(d, W, H, overlay=ov).cpu().numpy()
             want = [overlay_cpu(O.resize_linear(f, W, H), overlay, atlas) for f in frames]
+        if i % 3 == 0:      # the same through the planner's packed buffer, one list per frame, vs cv2 itself
+            try:
+                import cv2  # noqa: F401
+                shape = (w, h) if i % 2 == 0 else (W, H)
+                per_frame = [random_overlay(rng, shape[0], shape[1], int(rng.integers(1, 6))) for _ in range(n)]
+                ovp = ops.DeviceOverlay.from_plan(plan(per_frame, shape[0], shape[1], "rgb"), dev)
+                if i % 2 == 0:
+                    got = ops.overlay_draw(d, ovp).cpu().numpy()
+                    want = [reference_port.image_overlay([f], o)[0] for f, o in zip(frames, per_frame)]
+                else:
+                    got = ops.resize_linear(d, W, H, overlay=ovp).cpu().numpy()
+                    want = [reference_port.image_overlay([cv2.resize(f, (W, H))], o)[0] for f, o in zip(frames, per_frame)]
+            except ModuleNotFoundError:
+                pass
         for k in range(n):
             if not np.array_equal(got[k], want[k]):
                 bad += 1
