@@ -14,8 +14,8 @@ _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
 
 def build(force=False):
-    src = os.path.join(_HERE, "image_oracle.c")
-    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+    sources = [os.path.join(_HERE, name) for name in ("image_oracle.c", "jpeg_oracle.c")]
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < max(os.path.getmtime(s) for s in sources):
         subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
     return _LIB_PATH
 
@@ -202,3 +202,18 @@ def yuv(img, bgr_order=False, inverse=False):
         b = y + _descale14(u * 33292)
         out = np.stack([b, g, r] if bgr_order else [r, g, b], -1)
     return np.clip(out, 0, 255).astype(np.uint8)
+
+
+def jpeg_decode(data):
+    """Baseline JPEG -> uint8 [H, W, 3] RGB, as libjpeg-turbo's default decoder (what Pillow runs) does;
+    gray files give R = G = B.  Raises ValueError for files outside the oracle's subset."""
+    data = bytes(data)
+    w, h = ctypes.c_int(), ctypes.c_int()
+    rc = lib().orc_jpeg_decode_rgb(data, len(data), None, ctypes.byref(w), ctypes.byref(h))
+    if rc != 0:
+        raise ValueError(f"jpeg oracle: cannot read this file (code {rc})")
+    out = np.empty((h.value, w.value, 3), np.uint8)
+    rc = lib().orc_jpeg_decode_rgb(data, len(data), _p(out), ctypes.byref(w), ctypes.byref(h))
+    if rc != 0:
+        raise ValueError(f"jpeg oracle: cannot decode this file (code {rc})")
+    return out

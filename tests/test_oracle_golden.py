@@ -162,3 +162,41 @@ def test_yuv_oracle_equals_cv2_on_every_colour():
         cube = cube.astype(np.uint8).reshape(-1, 1, 3)
         for (bgr, inverse), code in codes.items():
             np.testing.assert_array_equal(O.yuv(cube, bgr, inverse), cv2.cvtColor(cube, code))
+
+
+def _natural(rng, h, w):
+    from PIL import Image
+    low = (rng.random((h // 20 + 2, w // 20 + 2, 3)) * 255).astype(np.uint8)
+    up = np.asarray(Image.fromarray(low, "RGB").resize((w, h), Image.BICUBIC)).astype(np.float32)
+    return np.clip(up + rng.normal(0, 6, (h, w, 3)), 0, 255).astype(np.uint8)
+
+
+def test_jpeg_oracle_is_bit_exact_with_pillow():
+    """oracle/jpeg_oracle.c (Huffman, islow IDCT, fancy upsampling, YCbCr tables as libjpeg-turbo's default
+    decoder) against Pillow's decoder -- the decode that runs inside the reference's image.resize
+    (R/elements/media/image_io.py:184,218) -- on random images: every sampling layout, gray, odd and tiny
+    sizes, any quality, with and without restart markers."""
+    import io
+    Image = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(5)
+    for t in range(80):
+        h, w = int(rng.integers(1, 200)), int(rng.integers(1, 300))
+        img = _natural(rng, h, w) if t % 3 else rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        kw = {}
+        if t % 4 == 0:
+            kw["restart_marker_rows"] = 1
+        if t % 4 == 1:
+            kw["restart_marker_blocks"] = int(rng.integers(1, 9))
+        im = Image.fromarray(img, "RGB")
+        if t % 7 == 0:
+            im = im.convert("L")
+        buf = io.BytesIO()
+        im.save(buf, "JPEG", quality=int(rng.integers(30, 100)), subsampling=t % 3 if im.mode == "RGB" else -1, **kw)
+        ref = np.asarray(Image.open(io.BytesIO(buf.getvalue())).convert("RGB"))
+        np.testing.assert_array_equal(O.jpeg_decode(buf.getvalue()), ref, err_msg=f"case {t}: {w}x{h}")
+    with pytest.raises(ValueError):
+        O.jpeg_decode(b"\xff\xd8\xff\xe0 nonsense")
+    buf = io.BytesIO()
+    Image.fromarray(_natural(rng, 40, 40), "RGB").save(buf, "JPEG", progressive=True)
+    with pytest.raises(ValueError):
+        O.jpeg_decode(buf.getvalue())                 # progressive: outside the subset, refused
