@@ -1,0 +1,762 @@
+// Baseline JPEG decoding on the GPU, hand-written: frames are BORN device-resident
+// and are bit-identical to what the reference's decoder produces.  The reference decodes inside
+// PIL.Image.open(path) ... image.resize(...) (R/elements/media/image_io.py:184,218), i.e. with
+// libjpeg-turbo's defaults: Huffman entropy decoding, the accurate integer inverse DCT ("islow"), "fancy"
+// triangle-filter chroma upsampling, 16-bit fixed-point YCbCr -> RGB.  This file restates that pipeline
+// (oracle: oracle/jpeg_oracle.c, itself pinned against Pillow):
+//
+//   host    : parse the markers of every image (quantisation and Huffman tables, frame geometry, restart
+//             interval, where the entropy-coded scan starts); build 9-bit look-up tables for the Huffman
+//             codes; ship tables + compressed bytes (a few hundred KB per 1080p frame instead of 6.2 MB
+//             of pixels) with one copy.
+//   kernel 1: jpeg_segments_kernel -- find the restart markers of every scan (one CTA per image).
+//   kernel 2: jpeg_huffman_kernel  -- entropy decoding, ONE THREAD PER RESTART SEGMENT: a restart marker
+//             resets the DC predictors and byte-aligns the stream, so the segments of an image (one per
+//             MCU row for typical encoders) decode independently; quantised coefficients go to HBM.
+//   kernel 3: jpeg_idct_kernel     -- dequantise + islow IDCT, one thread per 8x8 block, into planes.
+//   kernel 4: jpeg_colour_kernel   -- fancy upsampling of the chroma planes + YCbCr -> RGB, interleaved
+//             uint8 RGB frames: the layout np.asarray(PIL image) has.
+//
+// Subset: SOF0, 8 bit, one interleaved scan, gray or YCbCr with luma sampling 1x1 / 2x1 / 2x2 and chroma
+// 1x1, a restart interval (the parallel entropy decoder needs one), all images of a call of one geometry.
+// Everything else returns AIKO_B200_ERR_UNSUPPORTED and the caller keeps its other decoder.
+#include <string.h>
+
+#include <vector>
+
+#include "common.cuh"
+
+namespace aiko {
+
+constexpr int kLutBits = 9;
+constexpr int kMaxSegments = 65535;
+
+struct HuffDev {                 // one Huffman table, ready for the device
+  uint16_t lut[1 << kLutBits];   // next 9 bits -> (length << 8) | symbol, 0 = longer than 9 bits
+  int maxcode[18];               // per length; -1 = none
+  int mincode[17];
+  int valptr[17];
+  uint8_t vals[256];
+};
+
+struct JpegTables {              // per distinct set of tables (most images of a stream share one)
+  uint16_t q[4][64];             // natural order
+  HuffDev dc[4], ac[4];
+};
+
+struct JpegImage {               // per image
+  uint32_t scan_offset;          // of the entropy-coded data, inside the compressed area
+  uint32_t scan_bytes;
+  int32_t restart_interval;      // MCUs per segment
+  int32_t n_segments;
+  int32_t table_set;
+  uint8_t td[3], ta[3], tq[3];
+  uint8_t pad[3];
+};
+
+struct JpegGeometry {            // the same for every image of a call
+  int W, H, ncomp, hmax, vmax;
+  int mcux, mcuy;
+  int h[3], v[3];                // sampling factors (1 for chroma, 1 or 2 for luma)
+  int bw[3], bh[3];              // blocks per row / column, padded to whole MCUs
+  int dw[3], dh[3];              // true downsampled size
+  long long coef_offset[3];      // int16 elements from the start of an image's coefficient area
+  long long coef_per_image;
+  long long plane_offset[3];     // bytes from the start of an image's plane area
+  long long plane_per_image;
+};
+
+struct ParsedImage {
+  int W = 0, H = 0, ncomp = 0, restart = 0;
+  int id[3], h[3], v[3], tq[3], td[3], ta[3];
+  const uint8_t* scan = nullptr;
+  size_t scan_bytes = 0;
+  JpegTables tables;
+};
+
+static const uint8_t kZigzagHost[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,
+                                        12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6,  7,  14, 21, 28,
+                                        35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51,
+                                        58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+__constant__ uint8_t kZigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,
+                                    12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6,  7,  14, 21, 28,
+                                    35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51,
+                                    58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
+static int be16(const uint8_t* p) { return (p[0] << 8) | p[1]; }
+
+static bool build_huff(HuffDev* h, const uint8_t* counts /* [1..16] at counts[0..15] */, const uint8_t* vals, int total) {
+  memset(h, 0, sizeof(*h));
+  memcpy(h->vals, vals, (size_t)total);
+  int code = 0, k = 0;
+  for (int len = 1; len <= 16; len++) {
+    const int n = counts[len - 1];
+    h->valptr[len] = k;
+    h->mincode[len] = code;
+    for (int i = 0; i < n; i++, code++, k++) {
+      if (len <= kLutBits) {
+        const int first = code << (kLutBits - len), span = 1 << (kLutBits - len);
+        if (first + span > (1 << kLutBits)) return false;
+        for (int j = 0; j < span; j++) h->lut[first + j] = (uint16_t)((len << 8) | vals[k]);
+      }
+    }
+    h->maxcode[len] = n ? code - 1 : -1;
+    if (code > (1 << len)) return false;
+    code <<= 1;
+  }
+  h->maxcode[17] = 0x7fffffff;
+  return true;
+}
+
+// -> 0, AIKO_B200_ERR_INVALID_ARGUMENT (malformed) or AIKO_B200_ERR_UNSUPPORTED (outside the subset)
+static int parse_jpeg(const uint8_t* data, size_t len, ParsedImage* out, bool header_only) {
+  if (len < 4 || data[0] != 0xff || data[1] != 0xd8) {
+    set_last_error("jpeg: not a JPEG stream");
+    return AIKO_B200_ERR_INVALID_ARGUMENT;
+  }
+  memset(&out->tables, 0, sizeof(out->tables));
+  bool have_sof = false;
+  size_t pos = 2;
+  while (pos + 4 <= len) {
+    if (data[pos] != 0xff) { set_last_error("jpeg: marker expected at byte %zu", pos); return AIKO_B200_ERR_INVALID_ARGUMENT; }
+    const int m = data[pos + 1];
+    if (m == 0xff) { pos++; continue; }
+    const int seg = be16(data + pos + 2);
+    const uint8_t* s = data + pos + 4;
+    if (seg < 2 || pos + 2 + (size_t)seg > len) { set_last_error("jpeg: truncated segment"); return AIKO_B200_ERR_INVALID_ARGUMENT; }
+    const uint8_t* e = data + pos + 2 + seg;
+    if (m == 0xdb) {
+      while (s < e) {
+        const int pq = s[0] >> 4, tq = s[0] & 15;
+        if (tq > 3 || s + 1 + (pq ? 128 : 64) > e) { set_last_error("jpeg: bad DQT"); return AIKO_B200_ERR_INVALID_ARGUMENT; }
+        s++;
+        for (int i = 0; i < 64; i++) {
+          out->tables.q[tq][kZigzagHost[i]] = (uint16_t)(pq ? be16(s) : s[0]);
+          s += pq ? 2 : 1;
+        }
+      }
+    } else if (m == 0xc4) {
+      while (s < e) {
+        const int tc = s[0] >> 4, th = s[0] & 15;
+        int total = 0;
+        for (int k = 1; k <= 16; k++) total += s[k];
+        if (th > 3 || tc > 1 || total > 256 || s + 17 + total > e) { set_last_error("jpeg: bad DHT"); return AIKO_B200_ERR_INVALID_ARGUMENT; }
+        if (!build_huff(tc ? &out->tables.ac[th] : &out->tables.dc[th], s + 1, s + 17, total)) {
+          set_last_error("jpeg: inconsistent Huffman table");
+          return AIKO_B200_ERR_INVALID_ARGUMENT;
+        }
+        s += 17 + total;
+      }
+    } else if (m == 0xc0) {
+      if (s[0] != 8) { set_last_error("jpeg: %d-bit samples", s[0]); return AIKO_B200_ERR_UNSUPPORTED; }
+      out->H = be16(s + 1); out->W = be16(s + 3); out->ncomp = s[5];
+      if ((out->ncomp != 1 && out->ncomp != 3) || out->W <= 0 || out->H <= 0) {
+        set_last_error("jpeg: %d components", out->ncomp);
+        return AIKO_B200_ERR_UNSUPPORTED;
+      }
+      for (int i = 0; i < out->ncomp; i++) {
+        out->id[i] = s[6 + 3 * i]; out->h[i] = s[7 + 3 * i] >> 4; out->v[i] = s[7 + 3 * i] & 15;
+        out->tq[i] = s[8 + 3 * i] & 3;
+      }
+      have_sof = true;
+      if (header_only) return AIKO_B200_OK;
+    } else if (m >= 0xc1 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc) {
+      set_last_error("jpeg: not baseline (SOF%d)", m - 0xc0);
+      return AIKO_B200_ERR_UNSUPPORTED;
+    } else if (m == 0xdd) {
+      out->restart = be16(s);
+    } else if (m == 0xda) {
+      if (!have_sof || s[0] != out->ncomp) { set_last_error("jpeg: scan does not cover all components"); return AIKO_B200_ERR_UNSUPPORTED; }
+      for (int i = 0; i < out->ncomp; i++) {
+        if (s[1 + 2 * i] != out->id[i]) { set_last_error("jpeg: component order"); return AIKO_B200_ERR_UNSUPPORTED; }
+        out->td[i] = (s[2 + 2 * i] >> 4) & 3; out->ta[i] = s[2 + 2 * i] & 3;
+      }
+      out->scan = e;
+      out->scan_bytes = len - (size_t)(e - data);
+      return AIKO_B200_OK;
+    }
+    pos += 2 + (size_t)seg;
+  }
+  set_last_error("jpeg: no scan found");
+  return AIKO_B200_ERR_INVALID_ARGUMENT;
+}
+
+static int make_geometry(const ParsedImage& im, JpegGeometry* g) {
+  memset(g, 0, sizeof(*g));
+  g->W = im.W; g->H = im.H; g->ncomp = im.ncomp;
+  for (int i = 0; i < 3; i++) { g->h[i] = g->v[i] = 1; }
+  if (im.ncomp == 3) {
+    if (im.h[1] != 1 || im.v[1] != 1 || im.h[2] != 1 || im.v[2] != 1) { set_last_error("jpeg: subsampled chroma layout"); return AIKO_B200_ERR_UNSUPPORTED; }
+    g->h[0] = im.h[0]; g->v[0] = im.v[0];
+  }
+  g->hmax = g->h[0]; g->vmax = g->v[0];
+  if (!((g->hmax == 1 && g->vmax == 1) || (g->hmax == 2 && g->vmax == 1) || (g->hmax == 2 && g->vmax == 2))) {
+    set_last_error("jpeg: luma sampling %dx%d", g->hmax, g->vmax);
+    return AIKO_B200_ERR_UNSUPPORTED;
+  }
+  g->mcux = (g->W + 8 * g->hmax - 1) / (8 * g->hmax);
+  g->mcuy = (g->H + 8 * g->vmax - 1) / (8 * g->vmax);
+  long long coef = 0, plane = 0;
+  for (int i = 0; i < g->ncomp; i++) {
+    g->bw[i] = g->mcux * g->h[i]; g->bh[i] = g->mcuy * g->v[i];
+    g->dw[i] = (g->W * g->h[i] + g->hmax - 1) / g->hmax;
+    g->dh[i] = (g->H * g->v[i] + g->vmax - 1) / g->vmax;
+    g->coef_offset[i] = coef;
+    coef += (long long)g->bw[i] * g->bh[i] * 64;
+    g->plane_offset[i] = plane;
+    plane += (long long)g->bw[i] * g->bh[i] * 64;
+  }
+  g->coef_per_image = coef;
+  g->plane_per_image = (plane + 15) & ~15ll;
+  return AIKO_B200_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// kernel 1: where the restart segments of each scan begin.  One CTA per image; every thread scans a
+// contiguous slice for FF D0..D7 (inside entropy-coded data FF is always followed by 00, so these two
+// bytes can only be a restart marker), a block scan orders the hits, segment k starts after marker k.
+__device__ __forceinline__ int block_scan_excl(int v, int* warp_sums, int* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  int before = 0, all = 0;
+  for (int w = 0; w < (int)blockDim.x / 32; w++) {
+    const int s = warp_sums[w];
+    if (w < warp) before += s;
+    all += s;
+  }
+  __syncthreads();
+  *total = all;
+  return before + incl - v;
+}
+
+__global__ void __launch_bounds__(256) jpeg_segments_kernel(const uint8_t* __restrict__ compressed,
+                                                            const JpegImage* __restrict__ images,
+                                                            uint32_t* __restrict__ seg_offsets, int seg_pitch,
+                                                            int* __restrict__ status) {
+  __shared__ int warp_sums[8];
+  const JpegImage im = images[blockIdx.x];
+  const uint8_t* data = compressed + im.scan_offset;
+  const int bytes = (int)im.scan_bytes;
+  const int chunk = (bytes + 255) / 256;
+  const int lo = min((int)threadIdx.x * chunk, bytes), hi = min(lo + chunk, bytes);
+  int count = 0;
+  for (int i = lo; i < hi; i++)
+    if (data[i] == 0xff && i + 1 < bytes && (data[i + 1] & 0xf8) == 0xd0) count++;
+  int total;
+  int at = block_scan_excl(count, warp_sums, &total);
+  uint32_t* out = seg_offsets + (size_t)blockIdx.x * seg_pitch;
+  if (threadIdx.x == 0) {
+    out[0] = 0;
+    if (total != im.n_segments - 1) atomicExch(status, 1 + (int)blockIdx.x);   // markers do not match the restart interval
+  }
+  for (int i = lo; i < hi; i++)
+    if (data[i] == 0xff && i + 1 < bytes && (data[i + 1] & 0xf8) == 0xd0) {
+      at++;
+      if (at < im.n_segments) out[at] = (uint32_t)(i + 2);
+    }
+  if (threadIdx.x == 0)                                   // segments that have no marker (corrupt stream) decode nothing
+    for (int k = total + 1; k < im.n_segments; k++) out[k] = (uint32_t)bytes;
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 2: Huffman decoding (jdhuff.c), one thread per restart segment.
+struct BitReader {
+  const uint8_t* p;
+  const uint8_t* end;
+  unsigned long long acc;
+  int n;
+};
+
+__device__ __forceinline__ void refill(BitReader& b) {
+  while (b.n <= 56) {
+    unsigned byte = 0;
+    if (b.p < b.end) {
+      byte = *b.p;
+      if (byte == 0xffu) {
+        const unsigned next = (b.p + 1 < b.end) ? b.p[1] : 0xd9u;
+        if (next == 0u) b.p += 2;          // a stuffed zero follows a data FF
+        else { byte = 0; b.end = b.p; }     // a marker: the segment ends here, feed zeros
+      } else {
+        b.p++;
+      }
+    }
+    b.acc |= (unsigned long long)byte << (56 - b.n);
+    b.n += 8;
+  }
+}
+
+__device__ __forceinline__ int take_bits(BitReader& b, int s) {      // 1 <= s <= 16
+  const int v = (int)(b.acc >> (64 - s));
+  b.acc <<= s;
+  b.n -= s;
+  return v;
+}
+
+__device__ __forceinline__ int decode_symbol(BitReader& b, const HuffDev& h) {
+  const unsigned e = h.lut[(unsigned)(b.acc >> (64 - kLutBits))];
+  if (e) {
+    const int len = (int)(e >> 8);
+    b.acc <<= len;
+    b.n -= len;
+    return (int)(e & 0xffu);
+  }
+  for (int len = kLutBits + 1; len <= 16; len++) {
+    const int code = (int)(b.acc >> (64 - len));
+    if (code <= h.maxcode[len]) {
+      b.acc <<= len;
+      b.n -= len;
+      return h.vals[(h.valptr[len] + code - h.mincode[len]) & 255];
+    }
+  }
+  return -1;
+}
+
+__device__ __forceinline__ int extend_sign(int v, int s) { return v < (1 << (s - 1)) ? v - (1 << s) + 1 : v; }
+
+constexpr int kHuffThreads = 64;
+
+__global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_t* __restrict__ compressed,
+                                                                    const JpegImage* __restrict__ images,
+                                                                    const JpegTables* __restrict__ tables,
+                                                                    const uint32_t* __restrict__ seg_offsets,
+                                                                    int seg_pitch, const JpegGeometry g,
+                                                                    int16_t* __restrict__ coef, int* __restrict__ status) {
+  __shared__ HuffDev s_dc[2], s_ac[2];                    // the tables the image's components use (luma, chroma)
+  __shared__ int s_slot_dc[4], s_slot_ac[4];
+  const JpegImage im = images[blockIdx.y];
+  const JpegTables& t = tables[im.table_set];
+  // components use at most two DC and two AC tables in this subset (luma's and chroma's)
+  if (threadIdx.x < 4) { s_slot_dc[threadIdx.x] = -1; s_slot_ac[threadIdx.x] = -1; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int nd = 0, na = 0;
+    for (int c = 0; c < g.ncomp; c++) {
+      if (s_slot_dc[im.td[c]] < 0 && nd < 2) s_slot_dc[im.td[c]] = nd++;
+      if (s_slot_ac[im.ta[c]] < 0 && na < 2) s_slot_ac[im.ta[c]] = na++;
+    }
+  }
+  __syncthreads();
+  for (int id = 0; id < 4; id++) {
+    if (s_slot_dc[id] >= 0) {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(&t.dc[id]);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(&s_dc[s_slot_dc[id]]);
+      for (int i = threadIdx.x; i < (int)(sizeof(HuffDev) / 4); i += kHuffThreads) dst[i] = __ldg(src + i);
+    }
+    if (s_slot_ac[id] >= 0) {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(&t.ac[id]);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(&s_ac[s_slot_ac[id]]);
+      for (int i = threadIdx.x; i < (int)(sizeof(HuffDev) / 4); i += kHuffThreads) dst[i] = __ldg(src + i);
+    }
+  }
+  __syncthreads();
+  const int seg = blockIdx.x * kHuffThreads + threadIdx.x;
+  if (seg >= im.n_segments) return;
+  bool table_ok = true;
+  for (int c = 0; c < g.ncomp; c++) table_ok &= s_slot_dc[im.td[c]] >= 0 && s_slot_ac[im.ta[c]] >= 0;
+  if (!table_ok) {                                        // three different tables: not produced by any common encoder
+    atomicExch(status, 1000 + (int)blockIdx.y);
+    return;
+  }
+  const uint32_t* offs = seg_offsets + (size_t)blockIdx.y * seg_pitch;
+  const uint8_t* base = compressed + im.scan_offset;
+  BitReader b;
+  b.p = base + offs[seg];
+  b.end = base + ((seg + 1 < im.n_segments) ? offs[seg + 1] : im.scan_bytes);
+  b.acc = 0;
+  b.n = 0;
+  int16_t* image_coef = coef + (size_t)blockIdx.y * g.coef_per_image;
+  const int total_mcus = g.mcux * g.mcuy;
+  const int first = seg * im.restart_interval, last = min(first + im.restart_interval, total_mcus);
+  int pred[3] = {0, 0, 0};
+  bool bad = false;
+  for (int m = first; m < last && !bad; m++) {
+    const int my = m / g.mcux, mx = m - my * g.mcux;
+#pragma unroll 1
+    for (int c = 0; c < g.ncomp; c++) {
+      const HuffDev& hd = s_dc[s_slot_dc[im.td[c]]];
+      const HuffDev& ha = s_ac[s_slot_ac[im.ta[c]]];
+      const int nblocks = g.h[c] * g.v[c];
+#pragma unroll 1
+      for (int q = 0; q < nblocks; q++) {
+        const int by = q / g.h[c], bx = q - by * g.h[c];
+        int16_t* blk = image_coef + g.coef_offset[c] + ((size_t)(my * g.v[c] + by) * g.bw[c] + (mx * g.h[c] + bx)) * 64;
+        if (b.n < 32) refill(b);
+        int s = decode_symbol(b, hd);
+        if (s < 0 || s > 15) { bad = true; break; }
+        if (s) pred[c] += extend_sign(take_bits(b, s), s);
+        if (pred[c]) blk[0] = (int16_t)pred[c];
+        for (int k = 1; k < 64; k++) {
+          if (b.n < 32) refill(b);
+          const int rs = decode_symbol(b, ha);
+          if (rs < 0) { bad = true; break; }
+          const int r = rs >> 4, sz = rs & 15;
+          if (sz) {
+            k += r;
+            if (k > 63) { bad = true; break; }
+            blk[kZigzag[k]] = (int16_t)extend_sign(take_bits(b, sz), sz);
+          } else if (r == 15) {
+            k += 15;
+          } else {
+            break;
+          }
+        }
+        if (bad) break;
+      }
+      if (bad) break;
+    }
+  }
+  if (bad) atomicExch(status, 2000 + (int)blockIdx.y);
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 3: dequantisation + the accurate integer inverse DCT (jidctint.c, CONST_BITS 13, PASS1_BITS 2),
+// one thread per 8x8 block.
+#define AIKO_IDCT_1D(i0, i1, i2, i3, i4, i5, i6, i7, o0, o1, o2, o3, o4, o5, o6, o7, SHIFT)          \
+  {                                                                                                    \
+    int z1, z2, z3, z4, z5, t0, t1, t2, t3, t10, t11, t12, t13;                                        \
+    z2 = (i2); z3 = (i6);                                                                              \
+    z1 = (z2 + z3) * 4433;                                                                             \
+    t2 = z1 + z3 * (-15137);                                                                           \
+    t3 = z1 + z2 * 6270;                                                                               \
+    z2 = (i0); z3 = (i4);                                                                              \
+    t0 = (z2 + z3) * 8192;                                                                             \
+    t1 = (z2 - z3) * 8192;                                                                             \
+    t10 = t0 + t3; t13 = t0 - t3; t11 = t1 + t2; t12 = t1 - t2;                                        \
+    t0 = (i7); t1 = (i5); t2 = (i3); t3 = (i1);                                                        \
+    z1 = t0 + t3; z2 = t1 + t2; z3 = t0 + t2; z4 = t1 + t3;                                            \
+    z5 = (z3 + z4) * 9633;                                                                             \
+    t0 *= 2446; t1 *= 16819; t2 *= 25172; t3 *= 12299;                                                 \
+    z1 *= -7373; z2 *= -20995; z3 *= -16069; z4 *= -3196;                                              \
+    z3 += z5; z4 += z5;                                                                                \
+    t0 += z1 + z3; t1 += z2 + z4; t2 += z2 + z3; t3 += z1 + z4;                                        \
+    (o0) = (t10 + t3 + (1 << ((SHIFT)-1))) >> (SHIFT);                                                 \
+    (o7) = (t10 - t3 + (1 << ((SHIFT)-1))) >> (SHIFT);                                                 \
+    (o1) = (t11 + t2 + (1 << ((SHIFT)-1))) >> (SHIFT);                                                 \
+    (o6) = (t11 - t2 + (1 << ((SHIFT)-1))) >> (SHIFT);                                                 \
+    (o2) = (t12 + t1 + (1 << ((SHIFT)-1))) >> (SHIFT);                                                 \
+    (o5) = (t12 - t1 + (1 << ((SHIFT)-1))) >> (SHIFT);                                                 \
+    (o3) = (t13 + t0 + (1 << ((SHIFT)-1))) >> (SHIFT);                                                 \
+    (o4) = (t13 - t0 + (1 << ((SHIFT)-1))) >> (SHIFT);                                                 \
+  }
+
+__device__ __forceinline__ unsigned clamp_sample(int v) {
+  v += 128;
+  return (unsigned)(v < 0 ? 0 : (v > 255 ? 255 : v));
+}
+
+constexpr int kIdctThreads = 128;
+
+__global__ void __launch_bounds__(kIdctThreads) jpeg_idct_kernel(const int16_t* __restrict__ coef,
+                                                                 const JpegImage* __restrict__ images,
+                                                                 const JpegTables* __restrict__ tables,
+                                                                 const JpegGeometry g, uint8_t* __restrict__ planes) {
+  __shared__ uint16_t s_q[3][64];
+  const JpegImage im = images[blockIdx.y];
+  for (int i = threadIdx.x; i < g.ncomp * 64; i += kIdctThreads) s_q[i >> 6][i & 63] = tables[im.table_set].q[im.tq[i >> 6]][i & 63];
+  __syncthreads();
+  const long long blocks_per_image = g.coef_per_image / 64;
+  const long long blk = (long long)blockIdx.x * kIdctThreads + threadIdx.x;
+  if (blk >= blocks_per_image) return;
+  int c = 0;
+  if (g.ncomp == 3) c = blk * 64 >= g.coef_offset[2] ? 2 : (blk * 64 >= g.coef_offset[1] ? 1 : 0);
+  const long long local = blk - g.coef_offset[c] / 64;
+  const int by = (int)(local / g.bw[c]), bx = (int)(local - (long long)by * g.bw[c]);
+  const uint4* src = reinterpret_cast<const uint4*>(coef + (size_t)blockIdx.y * g.coef_per_image + blk * 64);
+  int x[64];
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    const uint4 v = __ldg(src + r);                       // eight coefficients of row r
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      x[8 * r + 2 * k] = (int)(short)(w[k] & 0xffffu) * (int)s_q[c][8 * r + 2 * k];
+      x[8 * r + 2 * k + 1] = (int)(short)(w[k] >> 16) * (int)s_q[c][8 * r + 2 * k + 1];
+    }
+  }
+#pragma unroll
+  for (int col = 0; col < 8; col++)                       // pass 1: columns
+    AIKO_IDCT_1D(x[col], x[8 + col], x[16 + col], x[24 + col], x[32 + col], x[40 + col], x[48 + col], x[56 + col],
+                 x[col], x[8 + col], x[16 + col], x[24 + col], x[32 + col], x[40 + col], x[48 + col], x[56 + col], 11)
+  const int pitch = g.bw[c] * 8;
+  uint8_t* out = planes + (size_t)blockIdx.y * g.plane_per_image + g.plane_offset[c] + (size_t)by * 8 * pitch + bx * 8;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {                           // pass 2: rows
+    int o0, o1, o2, o3, o4, o5, o6, o7;
+    AIKO_IDCT_1D(x[8 * r], x[8 * r + 1], x[8 * r + 2], x[8 * r + 3], x[8 * r + 4], x[8 * r + 5], x[8 * r + 6], x[8 * r + 7],
+                 o0, o1, o2, o3, o4, o5, o6, o7, 18)
+    uint2 px;
+    px.x = clamp_sample(o0) | (clamp_sample(o1) << 8) | (clamp_sample(o2) << 16) | (clamp_sample(o3) << 24);
+    px.y = clamp_sample(o4) | (clamp_sample(o5) << 8) | (clamp_sample(o6) << 16) | (clamp_sample(o7) << 24);
+    *reinterpret_cast<uint2*>(out + (size_t)r * pitch) = px;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 4: fancy upsampling (jdsample.c h2v1 / h2v2 triangle filters; rows above / below the image
+// repeat the edge row) + YCbCr -> RGB (jdcolor.c, 16-bit fixed point).  One thread per 4 output pixels.
+__device__ __forceinline__ int chroma_at(const uint8_t* plane, int pitch, int dw, int dh, int hs, int vs, int x, int y) {
+  if (hs == 1) return plane[(size_t)y * pitch + x];
+  const int sx = x >> 1;
+  if (vs == 1) {                                          // h2v1
+    const uint8_t* row = plane + (size_t)y * pitch;
+    const int v = row[sx];
+    if (dw == 1 || x == 0 || ((x & 1) && sx == dw - 1)) return v;
+    return (x & 1) ? (v * 3 + row[sx + 1] + 2) >> 2 : (v * 3 + row[sx - 1] + 1) >> 2;
+  }
+  const int sy = y >> 1;
+  const int fy = min(max((y & 1) ? sy + 1 : sy - 1, 0), dh - 1);
+  const uint8_t* near = plane + (size_t)sy * pitch;
+  const uint8_t* far = plane + (size_t)fy * pitch;
+  const int cur = near[sx] * 3 + far[sx];
+  if (dw == 1) return (cur * 4 + ((x & 1) ? 7 : 8)) >> 4;
+  if (x == 0) return (cur * 4 + 8) >> 4;
+  if ((x & 1) && sx == dw - 1) return (cur * 4 + 7) >> 4;
+  if (x & 1) return (cur * 3 + near[sx + 1] * 3 + far[sx + 1] + 7) >> 4;
+  return (cur * 3 + near[sx - 1] * 3 + far[sx - 1] + 8) >> 4;
+}
+
+__device__ __forceinline__ unsigned clamp8(int v) { return (unsigned)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+
+__global__ void __launch_bounds__(256) jpeg_colour_kernel(const uint8_t* __restrict__ planes, const JpegGeometry g,
+                                                          uint8_t* __restrict__ dst, long long frame_stride) {
+  const int groups = (g.W + 3) >> 2;
+  const long long item = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (item >= (long long)groups * g.H) return;
+  const int y = (int)(item / groups), x0 = (int)(item - (long long)y * groups) * 4;
+  const uint8_t* base = planes + (size_t)blockIdx.y * g.plane_per_image;
+  const uint8_t* py = base + g.plane_offset[0];
+  const int pitch_y = g.bw[0] * 8;
+  uint8_t* out = dst + (size_t)blockIdx.y * frame_stride + ((size_t)y * g.W + x0) * 3;
+  unsigned bytes[12];
+  const int npx = min(4, g.W - x0);
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const int x = min(x0 + k, g.W - 1);
+    const int yy = py[(size_t)y * pitch_y + x];
+    unsigned r, gg, b;
+    if (g.ncomp == 1) {
+      r = gg = b = (unsigned)yy;
+    } else {
+      const int hs = g.hmax, vs = g.vmax, pitch_c = g.bw[1] * 8;
+      const int cb = chroma_at(base + g.plane_offset[1], pitch_c, g.dw[1], g.dh[1], hs, vs, x, y) - 128;
+      const int cr = chroma_at(base + g.plane_offset[2], pitch_c, g.dw[2], g.dh[2], hs, vs, x, y) - 128;
+      r = clamp8(yy + ((91881 * cr + 32768) >> 16));
+      gg = clamp8(yy + ((-22554 * cb + 32768 - 46802 * cr) >> 16));
+      b = clamp8(yy + ((116130 * cb + 32768) >> 16));
+    }
+    bytes[3 * k] = r; bytes[3 * k + 1] = gg; bytes[3 * k + 2] = b;
+  }
+  if (npx == 4 && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
+    uint32_t* o = reinterpret_cast<uint32_t*>(out);
+    o[0] = bytes[0] | (bytes[1] << 8) | (bytes[2] << 16) | (bytes[3] << 24);
+    o[1] = bytes[4] | (bytes[5] << 8) | (bytes[6] << 16) | (bytes[7] << 24);
+    o[2] = bytes[8] | (bytes[9] << 8) | (bytes[10] << 16) | (bytes[11] << 24);
+  } else {
+    for (int q = 0; q < npx * 3; q++) out[q] = (uint8_t)bytes[q];
+  }
+}
+
+}  // namespace aiko
+
+// ---------------------------------------------------------------------------------------------
+// Host side of the C ABI.
+using namespace aiko;
+
+namespace {
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct WorkspaceLayout {
+  size_t images, tables, head_bytes;       // uploaded from the staging buffer in one copy
+  size_t seg_offsets, status, compressed, coef, planes, total;
+  int seg_pitch;
+};
+
+WorkspaceLayout layout_for(int n, const JpegGeometry& g, size_t compressed_capacity, int max_segments) {
+  WorkspaceLayout L{};
+  size_t at = 0;
+  L.images = at; at = align_up(at + (size_t)n * sizeof(JpegImage), 256);
+  L.tables = at; at = align_up(at + (size_t)n * sizeof(JpegTables), 256);
+  L.head_bytes = at;
+  L.seg_pitch = max_segments + 1;
+  L.seg_offsets = at; at = align_up(at + (size_t)n * L.seg_pitch * sizeof(uint32_t), 256);
+  L.status = at; at += 256;
+  L.compressed = at; at = align_up(at + compressed_capacity + 16 * (size_t)n + 64, 256);
+  L.coef = at; at = align_up(at + (size_t)n * g.coef_per_image * sizeof(int16_t), 256);
+  L.planes = at; at = align_up(at + (size_t)n * g.plane_per_image, 256);
+  L.total = at;
+  return L;
+}
+
+int geometry_from_args(int width, int height, int ncomp, int hmax, int vmax, JpegGeometry* g) {
+  ParsedImage im;
+  im.W = width; im.H = height; im.ncomp = ncomp;
+  for (int i = 0; i < 3; i++) { im.h[i] = im.v[i] = 1; }
+  im.h[0] = hmax; im.v[0] = vmax;
+  if (ncomp != 1 && ncomp != 3) { set_last_error("jpeg: %d components", ncomp); return AIKO_B200_ERR_UNSUPPORTED; }
+  return make_geometry(im, g);
+}
+
+}  // namespace
+
+extern "C" int aiko_b200_jpeg_gpu_info_host(const uint8_t* jpeg_host, size_t length, int* width_host, int* height_host,
+                                        int* components_host, int* hmax_host, int* vmax_host,
+                                        int* restart_interval_host) {
+  AIKO_CHECK_ARG(jpeg_host && width_host && height_host, "jpeg_info: null argument");
+  ParsedImage im;
+  const int rc = parse_jpeg(jpeg_host, length, &im, false);
+  if (rc != AIKO_B200_OK) return rc;
+  *width_host = im.W; *height_host = im.H;
+  if (components_host) *components_host = im.ncomp;
+  if (hmax_host) *hmax_host = im.ncomp == 3 ? im.h[0] : 1;
+  if (vmax_host) *vmax_host = im.ncomp == 3 ? im.v[0] : 1;
+  if (restart_interval_host) *restart_interval_host = im.restart;
+  return AIKO_B200_OK;
+}
+
+extern "C" size_t aiko_b200_jpeg_gpu_staging_bytes(int n_images) {
+  if (n_images <= 0) return 0;
+  return align_up((size_t)n_images * sizeof(JpegImage), 256) + align_up((size_t)n_images * sizeof(JpegTables), 256);
+}
+
+extern "C" size_t aiko_b200_jpeg_gpu_workspace_bytes(int n_images, int width, int height, int components, int hmax, int vmax,
+                                                 size_t compressed_capacity, int max_segments) {
+  JpegGeometry g;
+  if (n_images <= 0 || max_segments <= 0 || max_segments > kMaxSegments ||
+      geometry_from_args(width, height, components, hmax, vmax, &g) != AIKO_B200_OK)
+    return 0;
+  return layout_for(n_images, g, compressed_capacity, max_segments).total;
+}
+
+extern "C" int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host, const size_t* lengths_host, int n_images,
+                                            uint8_t* dst, int height, int width, int64_t frame_stride,
+                                            void* staging_host, size_t staging_bytes, void* workspace,
+                                            size_t workspace_bytes, size_t compressed_capacity, int max_segments,
+                                            void* stream) {
+  AIKO_CHECK_ARG(n_images >= 0, "jpeg_decode: n_images < 0");
+  if (n_images == 0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(jpegs_host && lengths_host && dst && staging_host && workspace, "jpeg_decode: null pointer");
+  AIKO_CHECK_ARG(frame_stride >= (int64_t)height * width * 3, "jpeg_decode: frame stride smaller than a frame");
+  AIKO_CHECK_ARG(staging_bytes >= aiko_b200_jpeg_gpu_staging_bytes(n_images), "jpeg_decode: staging buffer too small");
+  AIKO_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "jpeg_decode: workspace must be 256-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+  // ---- parse every image; all must share one geometry
+  std::vector<ParsedImage> parsed((size_t)n_images);
+  JpegGeometry g{};
+  size_t scan_total = 0;
+  int needed_segments = 1;
+  for (int i = 0; i < n_images; i++) {
+    const int rc = parse_jpeg(jpegs_host[i], lengths_host[i], &parsed[i], false);
+    if (rc != AIKO_B200_OK) return rc;
+    JpegGeometry gi;
+    const int rg = make_geometry(parsed[i], &gi);
+    if (rg != AIKO_B200_OK) return rg;
+    if (i == 0) g = gi;
+    if (gi.W != g.W || gi.H != g.H || gi.ncomp != g.ncomp || gi.hmax != g.hmax || gi.vmax != g.vmax) {
+      set_last_error("jpeg_decode: image %d is %dx%d (%d components, %dx%d sampling), the batch is %dx%d (%d, %dx%d)", i,
+                     gi.W, gi.H, gi.ncomp, gi.hmax, gi.vmax, g.W, g.H, g.ncomp, g.hmax, g.vmax);
+      return AIKO_B200_ERR_INVALID_ARGUMENT;
+    }
+    if (parsed[i].restart <= 0) {
+      set_last_error("jpeg_decode: image %d has no restart interval (the parallel entropy decoder needs one)", i);
+      return AIKO_B200_ERR_UNSUPPORTED;
+    }
+    const int segs = (g.mcux * g.mcuy + parsed[i].restart - 1) / parsed[i].restart;
+    needed_segments = segs > needed_segments ? segs : needed_segments;
+    scan_total += align_up(parsed[i].scan_bytes, 16);
+  }
+  AIKO_CHECK_ARG(g.W == width && g.H == height, "jpeg_decode: images are %dx%d, the destination is %dx%d", g.W, g.H, width, height);
+  if (needed_segments > max_segments || scan_total > compressed_capacity + 16 * (size_t)n_images) {
+    set_last_error("jpeg_decode: workspace sized for %d segments / %zu compressed bytes, the batch needs %d / %zu",
+                   max_segments, compressed_capacity, needed_segments, scan_total);
+    return AIKO_B200_ERR_WORKSPACE;
+  }
+  const WorkspaceLayout L = layout_for(n_images, g, compressed_capacity, max_segments);
+  if (workspace_bytes < L.total) {
+    set_last_error("jpeg_decode: workspace of %zu bytes, need %zu", workspace_bytes, L.total);
+    return AIKO_B200_ERR_WORKSPACE;
+  }
+
+  // ---- descriptors and (de-duplicated) tables into the staging buffer
+  uint8_t* stage = static_cast<uint8_t*>(staging_host);
+  JpegImage* images = reinterpret_cast<JpegImage*>(stage + L.images);
+  JpegTables* tables = reinterpret_cast<JpegTables*>(stage + L.tables);
+  int n_sets = 0;
+  size_t scan_at = 0;
+  for (int i = 0; i < n_images; i++) {
+    const ParsedImage& im = parsed[i];
+    int set = -1;
+    for (int k = n_sets - 1; k >= 0 && set < 0; k--)
+      if (memcmp(&tables[k], &im.tables, sizeof(JpegTables)) == 0) set = k;
+    if (set < 0) {
+      set = n_sets++;
+      memcpy(&tables[set], &im.tables, sizeof(JpegTables));
+    }
+    JpegImage& d = images[i];
+    memset(&d, 0, sizeof(d));
+    d.scan_offset = (uint32_t)scan_at;
+    d.scan_bytes = (uint32_t)im.scan_bytes;
+    d.restart_interval = im.restart;
+    d.n_segments = (g.mcux * g.mcuy + im.restart - 1) / im.restart;
+    d.table_set = set;
+    for (int c = 0; c < g.ncomp; c++) { d.td[c] = (uint8_t)im.td[c]; d.ta[c] = (uint8_t)im.ta[c]; d.tq[c] = (uint8_t)im.tq[c]; }
+    scan_at += align_up(im.scan_bytes, 16);
+  }
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  const size_t head = L.tables + (size_t)n_sets * sizeof(JpegTables);
+  AIKO_CUDA(cudaMemcpyAsync(ws, stage, head, cudaMemcpyHostToDevice, st));
+  for (int i = 0; i < n_images; i++)              // the compressed scans travel as they are (asynchronously when page-locked)
+    AIKO_CUDA(cudaMemcpyAsync(ws + L.compressed + images[i].scan_offset, parsed[i].scan, parsed[i].scan_bytes,
+                              cudaMemcpyHostToDevice, st));
+  AIKO_CUDA(cudaMemsetAsync(ws + L.status, 0, 256, st));
+  AIKO_CUDA(cudaMemsetAsync(ws + L.coef, 0, (size_t)n_images * g.coef_per_image * sizeof(int16_t), st));
+
+  const JpegImage* d_images = reinterpret_cast<const JpegImage*>(ws + L.images);
+  const JpegTables* d_tables = reinterpret_cast<const JpegTables*>(ws + L.tables);
+  uint32_t* d_seg = reinterpret_cast<uint32_t*>(ws + L.seg_offsets);
+  int* d_status = reinterpret_cast<int*>(ws + L.status);
+  int16_t* d_coef = reinterpret_cast<int16_t*>(ws + L.coef);
+  uint8_t* d_planes = ws + L.planes;
+
+  jpeg_segments_kernel<<<(unsigned)n_images, 256, 0, st>>>(ws + L.compressed, d_images, d_seg, L.seg_pitch, d_status);
+  AIKO_CUDA(cudaGetLastError());
+  jpeg_huffman_kernel<<<dim3((unsigned)((needed_segments + kHuffThreads - 1) / kHuffThreads), (unsigned)n_images),
+                        kHuffThreads, 0, st>>>(ws + L.compressed, d_images, d_tables, d_seg, L.seg_pitch, g, d_coef, d_status);
+  AIKO_CUDA(cudaGetLastError());
+  const long long blocks = g.coef_per_image / 64;
+  jpeg_idct_kernel<<<dim3((unsigned)((blocks + kIdctThreads - 1) / kIdctThreads), (unsigned)n_images), kIdctThreads, 0, st>>>(
+      d_coef, d_images, d_tables, g, d_planes);
+  AIKO_CUDA(cudaGetLastError());
+  const long long items = (long long)((g.W + 3) / 4) * g.H;
+  jpeg_colour_kernel<<<dim3((unsigned)((items + 255) / 256), (unsigned)n_images), 256, 0, st>>>(d_planes, g, dst, frame_stride);
+  return cuda_status(cudaGetLastError(), "jpeg_colour launch");
+}
+
+// 0 when the last decode that used `workspace` on `stream` met no corrupt entropy data; synchronises the stream.
+extern "C" int aiko_b200_jpeg_gpu_status(const void* workspace, int n_images, int width, int height, int components, int hmax,
+                                     int vmax, size_t compressed_capacity, int max_segments, void* stream) {
+  JpegGeometry g;
+  AIKO_CHECK_ARG(workspace && n_images > 0, "jpeg_status: bad argument");
+  const int rg = geometry_from_args(width, height, components, hmax, vmax, &g);
+  if (rg != AIKO_B200_OK) return rg;
+  const WorkspaceLayout L = layout_for(n_images, g, compressed_capacity, max_segments);
+  int status = 0;
+  AIKO_CUDA(cudaMemcpyAsync(&status, static_cast<const uint8_t*>(workspace) + L.status, sizeof(int), cudaMemcpyDeviceToHost,
+                            static_cast<cudaStream_t>(stream)));
+  AIKO_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  if (status != 0) {
+    set_last_error("jpeg: corrupt entropy-coded data (code %d: 1+i restart markers of image i do not match its restart "
+                   "interval, 1000+i more than two Huffman tables, 2000+i invalid code in image i)", status);
+    return AIKO_B200_ERR_INVALID_ARGUMENT;
+  }
+  return AIKO_B200_OK;
+}

@@ -208,22 +208,25 @@ def _read_jpegs_on_gpu(stream, paths, images):
     from ... import jpeg
     from ...device_frames import DeviceBatch
     stager = stager_for(stream)
-    decoder = jpeg.decoder_for(stager.device)
     groups = {}
     for k, path in enumerate(paths):
         with open(path, "rb") as f:
             data = f.read()
         if not jpeg.is_jpeg(data):
             continue
-        width, height, components, _ = decoder.info(data)
+        try:
+            width, height, components, hmax, vmax, restart = jpeg.GpuJpegDecoder.info(data)
+        except Exception:
+            continue                      # progressive, CMYK, 12-bit, ...: the reference's host path
         if components != 3:
-            continue                      # gray / CMYK JPEGs keep the reference's host path
-        groups.setdefault((width, height), []).append((k, data))
+            continue                      # gray JPEGs open as mode L in Pillow: keep the host path
+        groups.setdefault((width, height, hmax, vmax, restart > 0), []).append((k, data))
     import torch
     for members in groups.values():
         lane = stager.next_lane()
         with torch.cuda.stream(lane):
-            frames = decoder.decode([data for _, data in members], stream=lane)
+            # this library's decoder (bit-identical to Pillow) for files with restart markers, nvJPEG otherwise
+            frames, _ = jpeg.decode_on_gpu([data for _, data in members], stager.device, stream=lane)
         batch = DeviceBatch(frames, lane)
         batch.stager = stager
         for image, (k, _) in zip(batch.images(), members):

@@ -117,3 +117,113 @@ def decoder_for(device, max_batch=64):
     if key not in _decoders:
         _decoders[key] = JpegDecoder(device, max_batch)
     return _decoders[key]
+
+
+class GpuJpegDecoder:
+    """This library's own JPEG decoder (csrc/jpeg_decode.cu; include/aiko_b200.h, aiko_b200_jpeg_gpu_*):
+    Huffman decoding, IDCT, upsampling and colour conversion all on the GPU, pixels bit-identical to
+    Pillow's decoder.  Needs baseline files with restart markers (entropy decoding runs one thread per
+    restart segment); for anything else ``decode`` raises NativeError(ERR_UNSUPPORTED) and the caller
+    keeps its other decoder (``JpegDecoder`` above, or Pillow).  One decoder per (GPU, CUDA stream)."""
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self._buffers = {}        # geometry key -> (workspace, staging, capacity, segments)
+        self._event = None        # the staging buffer's last upload has run
+        self._last = None
+
+    @staticmethod
+    def info(data):
+        """-> (width, height, components, hmax, vmax, restart_interval) from the JPEG headers"""
+        vals = [_i() for _ in range(6)]
+        raw = data if isinstance(data, bytes) else bytes(data)
+        _native.check(_native.lib().aiko_b200_jpeg_gpu_info_host(raw, len(raw), *[ctypes.byref(v) for v in vals]))
+        return tuple(v.value for v in vals)
+
+    def _pointers(self, buffers):
+        n = len(buffers)
+        ptrs, lens, keep = (_vp * n)(), (_sz * n)(), []
+        for k, b in enumerate(buffers):
+            if isinstance(b, torch.Tensor):
+                ptrs[k], lens[k] = b.data_ptr(), b.numel()
+            else:
+                raw = b if isinstance(b, bytes) else bytes(b)
+                keep.append(raw)
+                ptrs[k] = ctypes.cast(ctypes.c_char_p(raw), _vp).value
+                lens[k] = len(raw)
+        return ptrs, lens, keep
+
+    def decode(self, buffers, out=None, stream=None, check=False):
+        """``buffers``: JPEG images of one geometry (bytes, or uint8 tensors in page-locked memory).
+        -> uint8 tensor [n, h, w, 3] RGB on the device, enqueued on ``stream``.  ``check`` waits for the
+        result and raises if the entropy-coded data was corrupt."""
+        n = len(buffers)
+        if n == 0:
+            return torch.empty((0, 0, 0, 3), dtype=torch.uint8, device=self.device)
+        first = buffers[0]
+        head = bytes(first[:min(first.numel(), 1 << 16)].numpy().tobytes()) if isinstance(first, torch.Tensor) else bytes(first)
+        w, h, comps, hmax, vmax, restart = self.info(head)
+        if restart <= 0:
+            raise NativeError(_native.ERR_UNSUPPORTED, "jpeg: no restart interval (the parallel entropy decoder needs one)")
+        mcus = -(-w // (8 * hmax)) * -(-h // (8 * vmax))
+        segments = -(-mcus // restart)
+        ptrs, lens, keep = self._pointers(buffers)
+        total = sum(int(v) for v in lens)
+        key = (n, w, h, comps, hmax, vmax)
+        lib = _native.lib()
+        entry = self._buffers.get(key)
+        if entry is None or entry[2] < total or entry[3] < segments:
+            capacity = max(-(-total * 5 // 4 // (1 << 20)) * (1 << 20), 1 << 20)
+            nbytes = lib.aiko_b200_jpeg_gpu_workspace_bytes(n, w, h, comps, hmax, vmax, capacity, segments)
+            if nbytes == 0:
+                raise NativeError(_native.ERR_UNSUPPORTED, f"jpeg: unsupported layout ({comps} components, {hmax}x{vmax})")
+            with torch.cuda.device(self.device):
+                workspace = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            staging = torch.empty(lib.aiko_b200_jpeg_gpu_staging_bytes(n), dtype=torch.uint8).pin_memory()
+            entry = self._buffers[key] = (workspace, staging, capacity, segments)
+        workspace, staging, capacity, max_segments = entry
+        if out is None:
+            out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=self.device)
+        s = stream if stream is not None else torch.cuda.current_stream(self.device)
+        if self._event is not None:
+            self._event.synchronize()            # the previous call's descriptors have left the staging buffer
+        with torch.cuda.device(self.device):
+            _native.check(lib.aiko_b200_jpeg_gpu_decode_rgb_u8(
+                ptrs, lens, n, out.data_ptr(), h, w, h * w * 3, staging.data_ptr(), staging.numel(), workspace.data_ptr(),
+                workspace.numel(), capacity, max_segments, _vp(s.cuda_stream)))
+        if self._event is None:
+            self._event = torch.cuda.Event()
+        self._event.record(s)
+        self._last = (workspace, n, w, h, comps, hmax, vmax, capacity, max_segments, s, keep)
+        if check:
+            self.check()
+        return out
+
+    def check(self):
+        """Wait for the last decode and raise NativeError if its entropy-coded data was corrupt."""
+        if self._last is not None:
+            workspace, n, w, h, comps, hmax, vmax, capacity, segs, s, _ = self._last
+            with torch.cuda.device(self.device):
+                _native.check(_native.lib().aiko_b200_jpeg_gpu_status(workspace.data_ptr(), n, w, h, comps, hmax, vmax,
+                                                                      capacity, segs, _vp(s.cuda_stream)))
+
+
+_gpu_decoders = {}
+
+
+def gpu_decoder_for(device):
+    key = str(torch.device(device))
+    if key not in _gpu_decoders:
+        _gpu_decoders[key] = GpuJpegDecoder(device)
+    return _gpu_decoders[key]
+
+
+def decode_on_gpu(buffers, device, stream=None):
+    """JPEG images of one size -> uint8 [n, h, w, 3] RGB on ``device``: this library's own decoder when the
+    files allow it (bit-identical to Pillow), nvJPEG otherwise.  -> (tensor, "aiko" | "nvjpeg")"""
+    try:
+        return gpu_decoder_for(device).decode(buffers, stream=stream), "aiko"
+    except NativeError as error:
+        if error.code != _native.ERR_UNSUPPORTED:
+            raise
+    return decoder_for(device).decode(buffers, stream=stream), "nvjpeg"

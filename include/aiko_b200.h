@@ -264,6 +264,39 @@ int aiko_b200_resize_norm_f32_nchw(const uint8_t* src, int n_frames, int src_h, 
                                    int dst_w, const float* mean_host, const float* std_host, void* stream);
 
 /* ---------------------------------------------------------------------- */
+/* Baseline JPEG decoding on the GPU: the decode half of PIL.Image.open(path) ... image.resize(...)  */
+/* (R/elements/media/image_io.py:184,218 -- Pillow decodes lazily, inside the resize call), so that   */
+/* frames are born device-resident and only the compressed bytes cross PCIe.  The kernels restate      */
+/* libjpeg-turbo's default decoder (Huffman decoding, accurate integer IDCT, "fancy" chroma             */
+/* upsampling, fixed-point YCbCr -> RGB): the decoded pixels are BIT-IDENTICAL to Pillow's.             */
+/* Subset: SOF0, 8 bit, one interleaved scan, gray or YCbCr (4:4:4, 4:2:2, 4:2:0), and a restart        */
+/* interval -- entropy decoding runs one thread per restart segment; files without restart markers      */
+/* return AIKO_B200_ERR_UNSUPPORTED (use another decoder for those, e.g. libaiko_b200_jpeg.so).         */
+/* All images of a call have one geometry.  dst: uint8 [n][height][width][3] RGB at frame_stride.        */
+/*   info_host       : width, height, components (1 / 3), luma sampling, restart interval of one file    */
+/*   staging_bytes   : page-locked host buffer the call fills with descriptors and tables                */
+/*   workspace_bytes : device workspace for n images of that geometry holding up to compressed_capacity  */
+/*                     bytes of entropy-coded data in all and max_segments restart segments per image    */
+/*                     (quantised coefficients and component planes live there: ~9.4 MB per 1080p        */
+/*                     4:2:0 frame); 0 for an unsupported geometry                                      */
+/*   decode_rgb_u8   : everything is enqueued on `stream`; the compressed scans are copied straight      */
+/*                     from jpegs_host (asynchronously when that memory is page-locked; they and the     */
+/*                     staging buffer must stay untouched until the copies have run)                     */
+/*   status          : synchronises `stream` and reports corrupt entropy-coded data met by the last      */
+/*                     decode that used the workspace (the kernels never read or write out of bounds)    */
+int aiko_b200_jpeg_gpu_info_host(const uint8_t* jpeg_host, size_t length, int* width_host, int* height_host,
+                                 int* components_host, int* hmax_host, int* vmax_host, int* restart_interval_host);
+size_t aiko_b200_jpeg_gpu_staging_bytes(int n_images);
+size_t aiko_b200_jpeg_gpu_workspace_bytes(int n_images, int width, int height, int components, int hmax, int vmax,
+                                          size_t compressed_capacity, int max_segments);
+int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host, const size_t* lengths_host, int n_images,
+                                     uint8_t* dst, int height, int width, int64_t frame_stride, void* staging_host,
+                                     size_t staging_bytes, void* workspace, size_t workspace_bytes,
+                                     size_t compressed_capacity, int max_segments, void* stream);
+int aiko_b200_jpeg_gpu_status(const void* workspace, int n_images, int width, int height, int components, int hmax,
+                              int vmax, size_t compressed_capacity, int max_segments, void* stream);
+
+/* ---------------------------------------------------------------------- */
 /* Colour conversion / flip / crop call sites.                              */
 
 /* cv2.cvtColor(.., COLOR_RGB2BGR / COLOR_BGR2RGB): image_io.py:117,160;   */

@@ -104,3 +104,75 @@ def test_image_read_file_decodes_on_the_gpu(cuda, tmp_path):
         want = np.asarray(Image.open(tmp_path / f"in_{k:02d}.jpeg").resize((160, 90))).astype(np.int32)
         assert got.shape == (90, 160, 3)
         assert np.abs(got - want).mean() <= 1.0 and np.abs(got - want).max() <= 12, (k, np.abs(got - want).max())
+
+
+# ---- this library's own decoder (csrc/jpeg_decode.cu): bit-exact with Pillow ------------------------------
+def encode_rst(frame, quality=90, subsampling=2, mode="RGB", **kw):
+    from PIL import Image
+    buf = io.BytesIO()
+    im = Image.fromarray(frame, "RGB")
+    if mode == "L":
+        im = im.convert("L")
+    im.save(buf, "JPEG", quality=quality, subsampling=subsampling if mode == "RGB" else -1, **(kw or {"restart_marker_rows": 1}))
+    return buf.getvalue()
+
+
+def pillow_rgb(blob):
+    from PIL import Image
+    return np.asarray(Image.open(io.BytesIO(blob)).convert("RGB"))
+
+
+@pytest.mark.parametrize("subsampling", [0, 1, 2], ids=["444", "422", "420"])
+def test_own_decoder_is_bit_exact_with_pillow(cuda, subsampling):
+    from aiko_services_b200 import jpeg
+    dec = jpeg.GpuJpegDecoder(cuda)
+    rng = np.random.default_rng(40 + subsampling)
+    for h, w in ((270, 480), (64, 96), (67, 101), (8, 8), (1, 1), (17, 250)):
+        frames = [natural_frame(int(rng.integers(1 << 30)), max(h, 2), max(w, 2))[:h, :w] for _ in range(3)]
+        frames[1] = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)               # noise: long codes, big coefficients
+        blobs = [encode_rst(f, int(rng.integers(40, 100)), subsampling) for f in frames]
+        got = dec.decode(blobs, check=True).cpu().numpy()
+        for k in range(3):
+            np.testing.assert_array_equal(got[k], pillow_rgb(blobs[k]), err_msg=f"{w}x{h} image {k}")
+            np.testing.assert_array_equal(got[k], O.jpeg_decode(blobs[k]))
+
+
+def test_own_decoder_gray_restart_blocks_and_1080p(cuda):
+    from aiko_services_b200 import jpeg
+    dec = jpeg.GpuJpegDecoder(cuda)
+    frame = natural_frame(7, 120, 200)
+    for kw in ({"restart_marker_blocks": 1}, {"restart_marker_blocks": 7}, {"restart_marker_rows": 3}):
+        blob = encode_rst(frame, 85, 2, **kw)
+        np.testing.assert_array_equal(dec.decode([blob], check=True).cpu().numpy()[0], pillow_rgb(blob))
+    gray = encode_rst(frame, 80, 0, mode="L")
+    np.testing.assert_array_equal(dec.decode([gray, gray], check=True).cpu().numpy()[1], pillow_rgb(gray))
+    big = [encode_rst(natural_frame(90 + k, 1080, 1920), 90, 2) for k in range(2)]       # BASELINE config 1 size
+    got = dec.decode(big, check=True).cpu().numpy()
+    for k in range(2):
+        np.testing.assert_array_equal(got[k], pillow_rgb(big[k]))
+
+
+def test_own_decoder_refuses_what_it_cannot_do(cuda):
+    from PIL import Image
+    from aiko_services_b200 import jpeg
+    from aiko_services_b200._native import ERR_UNSUPPORTED, NativeError
+    dec = jpeg.GpuJpegDecoder(cuda)
+    frame = natural_frame(3, 64, 96)
+    with pytest.raises(NativeError) as e:
+        dec.decode([encode(frame)])                          # no restart markers
+    assert e.value.code == ERR_UNSUPPORTED
+    buf = io.BytesIO()
+    Image.fromarray(frame, "RGB").save(buf, "JPEG", progressive=True)
+    with pytest.raises(NativeError):
+        dec.decode([buf.getvalue()])
+    good = encode_rst(frame)
+    with pytest.raises(NativeError):
+        dec.decode([good, encode_rst(natural_frame(4, 48, 96))])      # sizes differ within a batch
+    cut = good[:len(good) // 2]                                        # truncated scan: reported, no crash
+    with pytest.raises(NativeError):
+        dec.decode([cut], check=True)
+    frames, which = jpeg.decode_on_gpu([encode(frame)], cuda)          # falls back to nvJPEG for plain files
+    assert which == "nvjpeg" and frames.shape == (1, 64, 96, 3)
+    frames, which = jpeg.decode_on_gpu([good], cuda)
+    assert which == "aiko"
+    np.testing.assert_array_equal(frames.cpu().numpy()[0], pillow_rgb(good))
