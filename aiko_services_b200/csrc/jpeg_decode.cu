@@ -331,6 +331,8 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
                                                                     int16_t* __restrict__ coef, int* __restrict__ status) {
   __shared__ HuffDev s_dc[2], s_ac[2];                    // the tables the image's components use (luma, chroma)
   __shared__ int s_slot_dc[4], s_slot_ac[4];
+  __shared__ uint8_t s_zigzag[64];                        // (divergent indices: shared memory, not the constant cache)
+  if (threadIdx.x < 64) s_zigzag[threadIdx.x] = kZigzag[threadIdx.x];
   const JpegImage im = images[blockIdx.y];
   const JpegTables& t = tables[im.table_set];
   // components use at most two DC and two AC tables in this subset (luma's and chroma's)
@@ -401,7 +403,7 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
           if (sz) {
             k += r;
             if (k > 63) { bad = true; break; }
-            blk[kZigzag[k]] = (int16_t)extend_sign(take_bits(b, sz), sz);
+            blk[s_zigzag[k]] = (int16_t)extend_sign(take_bits(b, sz), sz);
           } else if (r == 15) {
             k += 15;
           } else {
