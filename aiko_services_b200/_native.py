@@ -16,6 +16,7 @@ ERR_INVALID_ARGUMENT = -1
 ERR_UNSUPPORTED = -2
 ERR_CUDA = -3
 ERR_WORKSPACE = -4
+ATLAS_GREW = 1          # aiko_b200_resize_linear_objects_u8: planned, not drawn
 
 
 class NativeError(RuntimeError):
@@ -66,6 +67,9 @@ SIGNATURES = {
                                     ctypes.POINTER(OverlayPlanInfo)],
     "aiko_b200_overlay_plan_struct_host": [_i, _vp, _vp, ctypes.c_char_p, _i, _i, _i, _i, _vp, _vp, _sz, _vp, _ovp,
                                            ctypes.POINTER(OverlayPlanInfo)],
+    "aiko_b200_resize_linear_objects_u8": [_vp, _i, _i, _i, _i, _i64, _i64, _vp, _i, _i, _i64, _i64, _i, _i, _vp, _vp,
+                                           ctypes.c_char_p, _i, _vp, _vp, _sz, _vp, _ovp,
+                                           ctypes.POINTER(OverlayPlanInfo), ctypes.c_uint64, ctypes.c_uint64, _vp],
     "aiko_b200_overlay_upload": [_vp, _vp, _sz, _vp],
     "aiko_b200_overlay_text_size_host": [ctypes.c_char_p, ctypes.POINTER(_i), ctypes.POINTER(_i)],
     "aiko_b200_overlay_cells_host": [_vp, _i, _i, _i, ctypes.POINTER(_i), ctypes.POINTER(ctypes.c_longlong)],

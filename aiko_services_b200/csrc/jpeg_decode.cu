@@ -20,6 +20,7 @@
 // Subset: SOF0, 8 bit, one interleaved scan, gray or YCbCr with luma sampling 1x1 / 2x1 / 2x2 and chroma
 // 1x1, a restart interval (the parallel entropy decoder needs one), all images of a call of one geometry.
 // Everything else returns AIKO_B200_ERR_UNSUPPORTED and the caller keeps its other decoder.
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -211,59 +212,85 @@ static int make_geometry(const ParsedImage& im, JpegGeometry* g) {
   return AIKO_B200_OK;
 }
 
-
 // ---------------------------------------------------------------------------------------------
-// kernel 1: where the restart segments of each scan begin.  One CTA per image; every thread scans a
-// contiguous slice for FF D0..D7 (inside entropy-coded data FF is always followed by 00, so these two
-// bytes can only be a restart marker), a block scan orders the hits, segment k starts after marker k.
-__device__ __forceinline__ int block_scan_excl(int v, int* warp_sums, int* total) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int incl = v;
+// kernel 1: where the restart segments of each scan begin (inside entropy-coded data FF is always followed by
+// 00, so FF D0..D7 can only be a restart marker).
+constexpr int kSegThreads = 1024;
+
+// bit p set: a restart marker (FF D0..D7) starts at byte 16 * v + p of the scan
+__device__ __forceinline__ unsigned restart_marks(const uint8_t* __restrict__ data, int v, int bytes) {
+  const uint4 q = __ldg(reinterpret_cast<const uint4*>(data) + v);
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+  unsigned any_ff = 0;
 #pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const int t = __shfl_up_sync(0xffffffffu, incl, d);
-    if (lane >= d) incl += t;
+  for (int k = 0; k < 4; k++) any_ff |= (~w[k] - 0x01010101u) & w[k] & 0x80808080u;   // exact for "no FF byte at all"
+  if (any_ff == 0) return 0;
+  const int at = 16 * v;
+  const unsigned after = at + 16 < bytes ? (unsigned)__ldg(data + at + 16) : 0u;
+  unsigned m = 0;
+#pragma unroll
+  for (int p = 0; p < 16; p++) {
+    const unsigned b = (w[p >> 2] >> (8 * (p & 3))) & 0xffu;
+    const unsigned n = p < 15 ? (w[(p + 1) >> 2] >> (8 * ((p + 1) & 3))) & 0xffu : after;
+    if (b == 0xffu && (n & 0xf8u) == 0xd0u && at + p + 1 < bytes) m |= 1u << p;
   }
-  if (lane == 31) warp_sums[warp] = incl;
-  __syncthreads();
-  int before = 0, all = 0;
-  for (int w = 0; w < (int)blockDim.x / 32; w++) {
-    const int s = warp_sums[w];
-    if (w < warp) before += s;
-    all += s;
-  }
-  __syncthreads();
-  *total = all;
-  return before + incl - v;
+  return m;
 }
 
-__global__ void __launch_bounds__(256) jpeg_segments_kernel(const uint8_t* __restrict__ compressed,
-                                                            const JpegImage* __restrict__ images,
-                                                            uint32_t* __restrict__ seg_offsets, int seg_pitch,
-                                                            int* __restrict__ status) {
-  __shared__ int warp_sums[8];
+// kernel 1: one CTA per image finds the restart markers of the scan.  A warp owns a contiguous run of 16-byte
+// vectors (lanes interleaved, so loads coalesce); pass 1 counts, pass 2 writes the byte offset after each marker.
+__global__ void __launch_bounds__(kSegThreads) jpeg_segments_kernel(const uint8_t* __restrict__ compressed,
+                                                                    const JpegImage* __restrict__ images,
+                                                                    uint32_t* __restrict__ seg_offsets, int seg_pitch,
+                                                                    int* __restrict__ status) {
+  __shared__ int warp_count[kSegThreads / 32];
   const JpegImage im = images[blockIdx.x];
-  const uint8_t* data = compressed + im.scan_offset;
+  const uint8_t* data = compressed + im.scan_offset;      // 16-byte aligned, padded to a multiple of 16
   const int bytes = (int)im.scan_bytes;
-  const int chunk = (bytes + 255) / 256;
-  const int lo = min((int)threadIdx.x * chunk, bytes), hi = min(lo + chunk, bytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int vecs = (bytes + 15) >> 4;
+  const int per_warp = (vecs + kSegThreads / 32 - 1) / (kSegThreads / 32);
+  const int v_lo = min(warp * per_warp, vecs), v_hi = min(v_lo + per_warp, vecs);
   int count = 0;
-  for (int i = lo; i < hi; i++)
-    if (data[i] == 0xff && i + 1 < bytes && (data[i + 1] & 0xf8) == 0xd0) count++;
-  int total;
-  int at = block_scan_excl(count, warp_sums, &total);
+  for (int v = v_lo + lane; v < v_hi; v += 32) count += __popc(restart_marks(data, v, bytes));
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) count += __shfl_xor_sync(0xffffffffu, count, d);
+  if (lane == 0) warp_count[warp] = count;
+  __syncthreads();
+  int before = 0, total = 0;
+  for (int w = 0; w < kSegThreads / 32; w++) {
+    const int c = warp_count[w];
+    before += w < warp ? c : 0;
+    total += c;
+  }
   uint32_t* out = seg_offsets + (size_t)blockIdx.x * seg_pitch;
   if (threadIdx.x == 0) {
     out[0] = 0;
     if (total != im.n_segments - 1) atomicExch(status, 1 + (int)blockIdx.x);   // markers do not match the restart interval
+    for (int k = total + 1; k < im.n_segments; k++) out[k] = (uint32_t)bytes;   // (corrupt stream) such segments decode nothing
   }
-  for (int i = lo; i < hi; i++)
-    if (data[i] == 0xff && i + 1 < bytes && (data[i + 1] & 0xf8) == 0xd0) {
-      at++;
-      if (at < im.n_segments) out[at] = (uint32_t)(i + 2);
+  if (count == 0) return;                                  // (warp-uniform)
+  int running = before;
+  for (int v0 = v_lo; v0 < v_hi; v0 += 32) {
+    const int v = v0 + lane;
+    unsigned m = v < v_hi ? restart_marks(data, v, bytes) : 0u;
+    if (__ballot_sync(0xffffffffu, m != 0) == 0) continue;
+    const int c = __popc(m);
+    int incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
     }
-  if (threadIdx.x == 0)                                   // segments that have no marker (corrupt stream) decode nothing
-    for (int k = total + 1; k < im.n_segments; k++) out[k] = (uint32_t)bytes;
+    int at = running + incl - c;
+    while (m) {
+      const int p = __ffs(m) - 1;
+      m &= m - 1;
+      at++;
+      if (at < im.n_segments) out[at] = (uint32_t)(16 * v + p + 2);
+    }
+    running += __shfl_sync(0xffffffffu, incl, 31);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -503,66 +530,106 @@ __global__ void __launch_bounds__(kIdctThreads) jpeg_idct_kernel(const int16_t* 
 
 // ---------------------------------------------------------------------------------------------
 // kernel 4: fancy upsampling (jdsample.c h2v1 / h2v2 triangle filters; rows above / below the image
-// repeat the edge row) + YCbCr -> RGB (jdcolor.c, 16-bit fixed point).  One thread per 4 output pixels.
-__device__ __forceinline__ int chroma_at(const uint8_t* plane, int pitch, int dw, int dh, int hs, int vs, int x, int y) {
-  if (hs == 1) return plane[(size_t)y * pitch + x];
-  const int sx = x >> 1;
-  if (vs == 1) {                                          // h2v1
-    const uint8_t* row = plane + (size_t)y * pitch;
-    const int v = row[sx];
-    if (dw == 1 || x == 0 || ((x & 1) && sx == dw - 1)) return v;
-    return (x & 1) ? (v * 3 + row[sx + 1] + 2) >> 2 : (v * 3 + row[sx - 1] + 1) >> 2;
+// repeat the edge row) + YCbCr -> RGB (jdcolor.c, 16-bit fixed point).  One thread per 8 output pixels
+// of one row; MODE: 0 gray, 1 = 4:4:4, 2 = 4:2:2 (h2v1), 3 = 4:2:0 (h2v2).
+__device__ __forceinline__ unsigned clamp8(int v) { return (unsigned)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+
+// Six neighbouring chroma samples c[0..5] = columns sx0 - 1 .. sx0 + 4 of one row (sx0 % 4 == 0; columns outside
+// the padded plane read as 0 and are never used by the edge rules below).
+__device__ __forceinline__ void chroma_six(const uint8_t* __restrict__ row, int sx0, int pitch, int c[6]) {
+  const uint32_t w = *reinterpret_cast<const uint32_t*>(row + sx0);
+  c[0] = sx0 > 0 ? (int)row[sx0 - 1] : 0;
+  c[1] = (int)(w & 0xffu); c[2] = (int)((w >> 8) & 0xffu); c[3] = (int)((w >> 16) & 0xffu); c[4] = (int)(w >> 24);
+  c[5] = sx0 + 4 < pitch ? (int)row[sx0 + 4] : 0;
+}
+
+template <int MODE>
+__device__ __forceinline__ void chroma_eight(const uint8_t* __restrict__ plane, int pitch, int dw, int dh, int x0, int y,
+                                             int out[8]) {
+  if (MODE == 1) {
+    const uint2 v = *reinterpret_cast<const uint2*>(plane + (size_t)y * pitch + x0);
+#pragma unroll
+    for (int k = 0; k < 4; k++) { out[k] = (int)((v.x >> (8 * k)) & 0xffu); out[4 + k] = (int)((v.y >> (8 * k)) & 0xffu); }
+    return;
+  }
+  const int sx0 = x0 >> 1;
+  int c[6];
+  if (MODE == 2) {
+    chroma_six(plane + (size_t)y * pitch, sx0, pitch, c);
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const int j = 1 + (k >> 1), v = c[j];
+      if (k & 1) out[k] = (sx0 + (k >> 1) == dw - 1) ? v : (v * 3 + c[j + 1] + 2) >> 2;
+      else out[k] = (x0 + k == 0) ? v : (v * 3 + c[j - 1] + 1) >> 2;
+    }
+    return;
   }
   const int sy = y >> 1;
   const int fy = min(max((y & 1) ? sy + 1 : sy - 1, 0), dh - 1);
-  const uint8_t* near = plane + (size_t)sy * pitch;
-  const uint8_t* far = plane + (size_t)fy * pitch;
-  const int cur = near[sx] * 3 + far[sx];
-  if (dw == 1) return (cur * 4 + ((x & 1) ? 7 : 8)) >> 4;
-  if (x == 0) return (cur * 4 + 8) >> 4;
-  if ((x & 1) && sx == dw - 1) return (cur * 4 + 7) >> 4;
-  if (x & 1) return (cur * 3 + near[sx + 1] * 3 + far[sx + 1] + 7) >> 4;
-  return (cur * 3 + near[sx - 1] * 3 + far[sx - 1] + 8) >> 4;
+  int f[6];
+  chroma_six(plane + (size_t)sy * pitch, sx0, pitch, c);
+  chroma_six(plane + (size_t)fy * pitch, sx0, pitch, f);
+#pragma unroll
+  for (int j = 0; j < 6; j++) c[j] = c[j] * 3 + f[j];     // jdsample.c: thiscolsum
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    const int j = 1 + (k >> 1), v = c[j];
+    if (k & 1) out[k] = (sx0 + (k >> 1) == dw - 1) ? (v * 4 + 7) >> 4 : (v * 3 + c[j + 1] + 7) >> 4;
+    else out[k] = (x0 + k == 0) ? (v * 4 + 8) >> 4 : (v * 3 + c[j - 1] + 8) >> 4;
+  }
 }
 
-__device__ __forceinline__ unsigned clamp8(int v) { return (unsigned)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
-
+template <int MODE>
 __global__ void __launch_bounds__(256) jpeg_colour_kernel(const uint8_t* __restrict__ planes, const JpegGeometry g,
                                                           uint8_t* __restrict__ dst, long long frame_stride) {
-  const int groups = (g.W + 3) >> 2;
-  const long long item = (long long)blockIdx.x * 256 + threadIdx.x;
-  if (item >= (long long)groups * g.H) return;
-  const int y = (int)(item / groups), x0 = (int)(item - (long long)y * groups) * 4;
+  const int groups = (g.W + 7) >> 3;
+  const int item = (int)blockIdx.x * 256 + (int)threadIdx.x;
+  if (item >= groups * g.H) return;
+  const int y = item / groups, x0 = (item - y * groups) * 8;
   const uint8_t* base = planes + (size_t)blockIdx.y * g.plane_per_image;
-  const uint8_t* py = base + g.plane_offset[0];
-  const int pitch_y = g.bw[0] * 8;
-  uint8_t* out = dst + (size_t)blockIdx.y * frame_stride + ((size_t)y * g.W + x0) * 3;
-  unsigned bytes[12];
-  const int npx = min(4, g.W - x0);
+  const uint2 yw = *reinterpret_cast<const uint2*>(base + g.plane_offset[0] + (size_t)y * (g.bw[0] * 8) + x0);
+  uint32_t o[6];
+  if (MODE == 0) {
 #pragma unroll
-  for (int k = 0; k < 4; k++) {
-    const int x = min(x0 + k, g.W - 1);
-    const int yy = py[(size_t)y * pitch_y + x];
-    unsigned r, gg, b;
-    if (g.ncomp == 1) {
-      r = gg = b = (unsigned)yy;
-    } else {
-      const int hs = g.hmax, vs = g.vmax, pitch_c = g.bw[1] * 8;
-      const int cb = chroma_at(base + g.plane_offset[1], pitch_c, g.dw[1], g.dh[1], hs, vs, x, y) - 128;
-      const int cr = chroma_at(base + g.plane_offset[2], pitch_c, g.dw[2], g.dh[2], hs, vs, x, y) - 128;
-      r = clamp8(yy + ((91881 * cr + 32768) >> 16));
-      gg = clamp8(yy + ((-22554 * cb + 32768 - 46802 * cr) >> 16));
-      b = clamp8(yy + ((116130 * cb + 32768) >> 16));
+    for (int k = 0; k < 8; k++) {
+      const unsigned yy = ((k < 4 ? yw.x : yw.y) >> (8 * (k & 3))) & 0xffu;
+#pragma unroll
+      for (int q = 0; q < 3; q++) {
+        const int at = 3 * k + q;
+        if ((at & 3) == 0) o[at >> 2] = yy; else o[at >> 2] |= yy << (8 * (at & 3));
+      }
     }
-    bytes[3 * k] = r; bytes[3 * k + 1] = gg; bytes[3 * k + 2] = b;
-  }
-  if (npx == 4 && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
-    uint32_t* o = reinterpret_cast<uint32_t*>(out);
-    o[0] = bytes[0] | (bytes[1] << 8) | (bytes[2] << 16) | (bytes[3] << 24);
-    o[1] = bytes[4] | (bytes[5] << 8) | (bytes[6] << 16) | (bytes[7] << 24);
-    o[2] = bytes[8] | (bytes[9] << 8) | (bytes[10] << 16) | (bytes[11] << 24);
   } else {
-    for (int q = 0; q < npx * 3; q++) out[q] = (uint8_t)bytes[q];
+    int cb[8], cr[8];
+    const int pitch_c = g.bw[1] * 8;
+    chroma_eight<MODE>(base + g.plane_offset[1], pitch_c, g.dw[1], g.dh[1], x0, y, cb);
+    chroma_eight<MODE>(base + g.plane_offset[2], pitch_c, g.dw[2], g.dh[2], x0, y, cr);
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const int yy = (int)(((k < 4 ? yw.x : yw.y) >> (8 * (k & 3))) & 0xffu);
+      const int u = cb[k] - 128, v = cr[k] - 128;
+      const unsigned px[3] = {clamp8(yy + ((91881 * v + 32768) >> 16)),
+                              clamp8(yy + ((-22554 * u + 32768 - 46802 * v) >> 16)),
+                              clamp8(yy + ((116130 * u + 32768) >> 16))};
+#pragma unroll
+      for (int q = 0; q < 3; q++) {
+        const int at = 3 * k + q;
+        if ((at & 3) == 0) o[at >> 2] = px[q]; else o[at >> 2] |= px[q] << (8 * (at & 3));
+      }
+    }
+  }
+  uint8_t* out = dst + (size_t)blockIdx.y * frame_stride + ((size_t)y * g.W + x0) * 3;
+  const int npx = min(8, g.W - x0);
+  const uintptr_t addr = reinterpret_cast<uintptr_t>(out);
+  if (npx == 8 && (addr & 7) == 0) {
+    uint2* p = reinterpret_cast<uint2*>(out);
+    p[0] = make_uint2(o[0], o[1]); p[1] = make_uint2(o[2], o[3]); p[2] = make_uint2(o[4], o[5]);
+  } else if (npx == 8 && (addr & 3) == 0) {
+    uint32_t* p = reinterpret_cast<uint32_t*>(out);
+#pragma unroll
+    for (int q = 0; q < 6; q++) p[q] = o[q];
+  } else {
+    for (int q = 0; q < npx * 3; q++) out[q] = (uint8_t)(o[q >> 2] >> (8 * (q & 3)));
   }
 }
 
@@ -719,8 +786,11 @@ extern "C" int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host
   for (int i = 0; i < n_images; i++)              // the compressed scans travel as they are (asynchronously when page-locked)
     AIKO_CUDA(cudaMemcpyAsync(ws + L.compressed + images[i].scan_offset, parsed[i].scan, parsed[i].scan_bytes,
                               cudaMemcpyHostToDevice, st));
+  // diagnostic: AIKO_B200_JPEG_STAGES = bit mask of the stages to run (1 segments, 2 entropy decode, 4 IDCT, 8 colour)
+  const char* stage_env = getenv("AIKO_B200_JPEG_STAGES");
+  const int stages = stage_env ? atoi(stage_env) : 15;
   AIKO_CUDA(cudaMemsetAsync(ws + L.status, 0, 256, st));
-  AIKO_CUDA(cudaMemsetAsync(ws + L.coef, 0, (size_t)n_images * g.coef_per_image * sizeof(int16_t), st));
+  if (stages & 2) AIKO_CUDA(cudaMemsetAsync(ws + L.coef, 0, (size_t)n_images * g.coef_per_image * sizeof(int16_t), st));
 
   const JpegImage* d_images = reinterpret_cast<const JpegImage*>(ws + L.images);
   const JpegTables* d_tables = reinterpret_cast<const JpegTables*>(ws + L.tables);
@@ -729,17 +799,22 @@ extern "C" int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host
   int16_t* d_coef = reinterpret_cast<int16_t*>(ws + L.coef);
   uint8_t* d_planes = ws + L.planes;
 
-  jpeg_segments_kernel<<<(unsigned)n_images, 256, 0, st>>>(ws + L.compressed, d_images, d_seg, L.seg_pitch, d_status);
+  if (stages & 1) jpeg_segments_kernel<<<(unsigned)n_images, kSegThreads, 0, st>>>(ws + L.compressed, d_images, d_seg, L.seg_pitch, d_status);
   AIKO_CUDA(cudaGetLastError());
-  jpeg_huffman_kernel<<<dim3((unsigned)((needed_segments + kHuffThreads - 1) / kHuffThreads), (unsigned)n_images),
+  if (stages & 2) jpeg_huffman_kernel<<<dim3((unsigned)((needed_segments + kHuffThreads - 1) / kHuffThreads), (unsigned)n_images),
                         kHuffThreads, 0, st>>>(ws + L.compressed, d_images, d_tables, d_seg, L.seg_pitch, g, d_coef, d_status);
   AIKO_CUDA(cudaGetLastError());
   const long long blocks = g.coef_per_image / 64;
-  jpeg_idct_kernel<<<dim3((unsigned)((blocks + kIdctThreads - 1) / kIdctThreads), (unsigned)n_images), kIdctThreads, 0, st>>>(
+  if (stages & 4) jpeg_idct_kernel<<<dim3((unsigned)((blocks + kIdctThreads - 1) / kIdctThreads), (unsigned)n_images), kIdctThreads, 0, st>>>(
       d_coef, d_images, d_tables, g, d_planes);
   AIKO_CUDA(cudaGetLastError());
-  const long long items = (long long)((g.W + 3) / 4) * g.H;
-  jpeg_colour_kernel<<<dim3((unsigned)((items + 255) / 256), (unsigned)n_images), 256, 0, st>>>(d_planes, g, dst, frame_stride);
+  const long long items = (long long)((g.W + 7) / 8) * g.H;
+  const dim3 colour_grid((unsigned)((items + 255) / 256), (unsigned)n_images);
+  if (!(stages & 8)) return AIKO_B200_OK;
+  if (g.ncomp == 1) jpeg_colour_kernel<0><<<colour_grid, 256, 0, st>>>(d_planes, g, dst, frame_stride);
+  else if (g.hmax == 1) jpeg_colour_kernel<1><<<colour_grid, 256, 0, st>>>(d_planes, g, dst, frame_stride);
+  else if (g.vmax == 1) jpeg_colour_kernel<2><<<colour_grid, 256, 0, st>>>(d_planes, g, dst, frame_stride);
+  else jpeg_colour_kernel<3><<<colour_grid, 256, 0, st>>>(d_planes, g, dst, frame_stride);
   return cuda_status(cudaGetLastError(), "jpeg_colour launch");
 }
 

@@ -500,3 +500,23 @@ extern "C" int aiko_b200_overlay_plan_struct_host(int n_lists, const int32_t* ob
   overlay_host->upload_bytes = ops_bytes + tail;
   return AIKO_B200_OK;
 }
+
+// Plan + draw in one crossing of the ABI (the per-frame call when the overlay is new every time).
+extern "C" int aiko_b200_resize_linear_objects_u8(const uint8_t* src, int n_frames, int src_h, int src_w, int channels,
+                                                  int64_t src_row_stride, int64_t src_frame_stride, uint8_t* dst, int dst_h,
+                                                  int dst_w, int64_t dst_row_stride, int64_t dst_frame_stride, int swap_rb,
+                                                  int n_lists, const int32_t* object_offsets_host,
+                                                  const int32_t* rects_host, const char* labels_host, int layout,
+                                                  const int32_t* list_of_frame_host, void* buffer_host, size_t buffer_bytes,
+                                                  void* buffer_dev, aiko_b200_overlay* overlay_host,
+                                                  aiko_b200_overlay_plan_info* info_host, uint64_t atlas_version,
+                                                  uint64_t atlas_epoch, void* stream) {
+  const int rc = aiko_b200_overlay_plan_struct_host(n_lists, object_offsets_host, rects_host, labels_host, dst_w, dst_h,
+                                                    layout, n_frames, list_of_frame_host, buffer_host, buffer_bytes,
+                                                    buffer_dev, overlay_host, info_host);
+  if (rc != AIKO_B200_OK) return rc;
+  if (info_host->atlas_version != atlas_version || info_host->atlas_epoch != atlas_epoch) return AIKO_B200_ATLAS_GREW;
+  return aiko_b200_resize_linear_u8(src, n_frames, src_h, src_w, channels, src_row_stride, src_frame_stride, dst, dst_h,
+                                    dst_w, dst_row_stride, dst_frame_stride, swap_rb,
+                                    info_host->n_ops > 0 ? overlay_host : nullptr, stream);
+}

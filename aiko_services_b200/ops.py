@@ -189,11 +189,10 @@ class OverlayRing:
         self._atlas_dev = None
         self._info = _native.OverlayPlanInfo()
 
-    def plan(self, overlays, width, height, layout="rgb", n_frames=None, stream=None):
-        from .overlay_plan import LAYOUTS, gather_objects, plan
+    def _slot(self, s):
+        """Next ring slot (waits only when the ring wraps onto work still in flight) -> its DeviceOverlay."""
         i = self.next
         n = len(self.views)
-        s = stream if stream is not None else torch.cuda.current_stream(self.device)
         if i == 0 or i == self.half:
             # entering a half: everything queued from it a lap ago must have run (the event recorded when
             # the other half was entered); and everything queued so far covers the other half's last lap
@@ -207,24 +206,15 @@ class OverlayRing:
                     self.events[1 - h] = torch.cuda.Event()
                 self.events[1 - h].record(s)
         self.next = (i + 1) % n
-        n_lists, offsets, rects, labels, list_of_frame = gather_objects(overlays)
-        if list_of_frame is None:
-            frames, frame_map = int(n_frames or 1), None
-        else:
-            frames, frame_map = len(list_of_frame), array("i", list_of_frame).buffer_info()[0]
         ov = self.overlays[i]
         if ov is None:
             atlas = self._atlas_dev or self.atlas.device(self.device)
             ov = self.overlays[i] = DeviceOverlay(self.dev[i], 0, 0, 0, 0, atlas, 0, 0, 0, 0, 0)
             ov.host_ptr, ov.dev_ptr = self.pinned[i].data_ptr(), self.dev[i].data_ptr()
-        info = self._info
-        rc = _native.lib().aiko_b200_overlay_plan_struct_host(
-            n_lists, offsets.buffer_info()[0], rects.buffer_info()[0], labels, int(width), int(height),
-            LAYOUTS[layout], frames, frame_map, ov.host_ptr, self.capacity, ov.dev_ptr, ov.struct, info)
-        if rc == _native.ERR_WORKSPACE:                  # does not fit a slot: one-off buffers
-            planned = plan(overlays, width, height, layout, n_frames=n_frames)
-            return DeviceOverlay.from_plan(planned, self.device, self.atlas.device(self.device), stream=s)
-        check(rc)
+        return ov
+
+    def _sync_atlas(self, ov, info, s):
+        """Bring the device copy of the glyph atlas to the state the planner left it in."""
         atlas = self._atlas_dev
         if atlas is None or atlas.version != info.atlas_version or atlas.epoch != info.atlas_epoch:
             atlas = self._atlas_dev = self.atlas.device(self.device)       # uploads what the planner appended
@@ -234,7 +224,72 @@ class OverlayRing:
             ov.atlas = atlas
             ov.struct.patch_ids, ov.struct.luts = atlas.patch_ids.data_ptr(), atlas.luts.data_ptr()
         ov.n_ops = info.n_ops
+
+    def plan(self, overlays, width, height, layout="rgb", n_frames=None, stream=None):
+        from .overlay_plan import LAYOUTS, gather_objects, plan
+        s = stream if stream is not None else torch.cuda.current_stream(self.device)
+        ov = self._slot(s)
+        n_lists, offsets, rects, labels, list_of_frame = gather_objects(overlays)
+        if list_of_frame is None:
+            frames, frame_map, keep = int(n_frames or 1), None, None
+        else:
+            keep = array("i", list_of_frame)               # (stays alive until the call has returned)
+            frames, frame_map = len(list_of_frame), keep.buffer_info()[0]
+        info = self._info
+        rc = _native.lib().aiko_b200_overlay_plan_struct_host(
+            n_lists, offsets.buffer_info()[0], rects.buffer_info()[0], labels, int(width), int(height),
+            LAYOUTS[layout], frames, frame_map, ov.host_ptr, self.capacity, ov.dev_ptr, ov.struct, info)
+        if rc == _native.ERR_WORKSPACE:                  # does not fit a slot: one-off buffers
+            planned = plan(overlays, width, height, layout, n_frames=n_frames)
+            return DeviceOverlay.from_plan(planned, self.device, self.atlas.device(self.device), stream=s)
+        check(rc)
+        self._sync_atlas(ov, info, s)
         return ov
+
+    def resize_draw(self, src, overlays, width, height, *, swap_rb=False, out=None, stream=None):
+        """``resize_linear(src, width, height, swap_rb=..., overlay=self.plan(overlays, ...))`` as one call of
+        the library (aiko_b200_resize_linear_objects_u8): ImageResize -> ImageOverlay (-> RGB2BGR) for
+        detections that are new on every call.  ``overlays``: one dict for all frames or one per frame;
+        colours follow the stored channel order (BGR when ``swap_rb``)."""
+        from .overlay_plan import gather_objects
+        _require_cuda(src, "resize_draw src")
+        n, h, w, c, gray = _nhwc(src)
+        out = _out(out, (n, height, width) if gray else (n, height, width, c), src.device, "resize_draw out")
+        s = stream if stream is not None else torch.cuda.current_stream(self.device)
+        ov = self._slot(s)
+        n_lists, offsets, rects, labels, list_of_frame = gather_objects(overlays)
+        if list_of_frame is not None and len(list_of_frame) != n:
+            raise ValueError(f"resize_draw: {len(list_of_frame)} overlays for {n} frames")
+        keep = array("i", list_of_frame) if list_of_frame is not None else None     # alive across the call
+        frame_map = keep.buffer_info()[0] if keep is not None else None
+        info, atlas = self._info, self._atlas_dev
+        if atlas is None:
+            atlas = self._atlas_dev = self.atlas.device(self.device)
+            if atlas.ready is not None:
+                s.wait_event(atlas.ready)
+        if ov.atlas is not atlas:
+            ov.atlas = atlas
+            ov.struct.patch_ids, ov.struct.luts = atlas.patch_ids.data_ptr(), atlas.luts.data_ptr()
+        lib = _native.lib()
+        with _on_device(self.device):
+            rc = lib.aiko_b200_resize_linear_objects_u8(
+                src.data_ptr(), n, h, w, c, w * c, h * w * c, out.data_ptr(), height, width, width * c,
+                height * width * c, int(swap_rb), n_lists, offsets.buffer_info()[0], rects.buffer_info()[0], labels,
+                1 if swap_rb else 0, frame_map, ov.host_ptr, self.capacity, ov.dev_ptr, ov.struct, info,
+                atlas.version, atlas.epoch, s.cuda_stream)
+            if rc == _native.ERR_WORKSPACE or rc == _native.ATLAS_GREW:
+                # the lists do not fit a ring slot, or the planner appended glyph variants: the two-call path
+                if rc == _native.ATLAS_GREW:
+                    self._sync_atlas(ov, info, s)
+                else:
+                    from .overlay_plan import plan
+                    planned = plan(overlays, width, height, "bgr" if swap_rb else "rgb", n_frames=n)
+                    ov = DeviceOverlay.from_plan(planned, self.device, self.atlas.device(self.device), stream=s)
+                rc = lib.aiko_b200_resize_linear_u8(
+                    src.data_ptr(), n, h, w, c, w * c, h * w * c, out.data_ptr(), height, width, width * c,
+                    height * width * c, int(swap_rb), ov.struct if ov.n_ops else None, s.cuda_stream)
+        check(rc)
+        return out
 
 
 def reads_source_rows_once(frame_shape, width, height):

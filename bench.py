@@ -515,28 +515,45 @@ def run_gpu_arm(args):
                          for k, ob in enumerate(OVERLAY["objects"])]}
         return o
 
-    ring = ops.OverlayRing(device)
+    rings = [ops.OverlayRing(device) for _ in range(LANES)]      # one ring of draw-list buffers per CUDA stream
     changing_steps = max(3, min(args.steps, 200))
-    dicts = [changing_overlay(i) for i in range(changing_steps + 3)]      # the inputs: one new dict per step
+    dicts = [changing_overlay(i) for i in range(changing_steps)]          # the inputs: one new dict per step
 
-    plan_s = [0.0]
+    def changing_step(i, overlay):
+        # plan the new draw list + resize + swap + draw: ONE call of the library (aiko_b200_resize_linear_objects_u8)
+        lane = i % LANES
+        rings[lane].resize_draw(batches[i % N_ROTATING_BATCHES], overlay, DST_W, DST_H, swap_rb=True,
+                                out=lane_outs[lane] if LANES > 1 else out,
+                                stream=lane_streams[lane] if LANES > 1 else stream)
 
-    def changing_step(i):
-        t_plan = time.perf_counter()
-        dov = ring.plan(dicts[i], DST_W, DST_H, "bgr", n_frames=BATCH)
-        plan_s[0] += time.perf_counter() - t_plan
-        ops.resize_linear(batches[i % N_ROTATING_BATCHES], DST_W, DST_H, swap_rb=True, overlay=dov, out=out)
-
-    for i in range(3):
-        changing_step(i)
+    # Warm-up: a label cut by the image border needs glyph variants rasterised against that border geometry
+    # (~50 us per glyph, once, then cached by the library); a long-running pipeline is in that steady state, so
+    # the cache is warmed with OTHER overlays (different boxes and confidences) before the timed steps.
+    for i in range(max(args.warmup, 400)):
+        changing_step(i, changing_overlay(100_000 + i))
     barrier()
     c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     c0.record(stream)
-    plan_s[0] = 0.0
+    if LANES > 1:
+        for s in lane_streams[:LANES]:
+            s.wait_event(c0)
+    stamps = [] if os.environ.get("AIKO_BENCH_DEBUG") else None
     tc0 = time.perf_counter()
     for i in range(changing_steps):
-        changing_step(3 + i)
+        changing_step(i, dicts[i])
+        if stamps is not None:
+            stamps.append(time.perf_counter())
     changing_host_s = time.perf_counter() - tc0          # host time to plan and enqueue
+    if stamps:
+        d = np.diff(np.array([tc0] + stamps)) * 1e6
+        print(f"bench.py debug: changing-overlay host us per step: median {np.median(d):.1f} mean {d.mean():.1f} "
+              f"p90 {np.percentile(d, 90):.1f} max {d.max():.1f}; slow steps {np.nonzero(d > 100)[0][:20].tolist()}",
+              file=sys.stderr)
+    if LANES > 1:
+        for s in lane_streams[:LANES]:
+            done = torch.cuda.Event()
+            done.record(s)
+            stream.wait_event(done)
     c1.record(stream)
     torch.cuda.synchronize()
     changing_s = time.perf_counter() - tc0               # until the last result is there
@@ -751,11 +768,13 @@ def run_gpu_arm(args):
             "value_changing_overlay": {"value": frames_changing / changing_s, "unit": "frames/s",
                                        "steps": changing_steps,
                                        "host_us_per_step": changing_host_s / changing_steps * 1e6,
-                                       "host_plan_us_per_step": plan_s[0] / changing_steps * 1e6,
+                                       "cuda_streams": LANES,
                                        "device_us_per_step": changing_device_ms / changing_steps * 1e3,
                                        "note": "same step, a different overlay dict every step (boxes move, label "
-                                               "text changes); host planning + upload inside the timed region, wall "
-                                               "clock with a final synchronize"},
+                                               "text changes); host planning + upload inside the timed region (plan + "
+                                               "resize + draw = one library call, OverlayRing.resize_draw), wall clock "
+                                               "with a final synchronize; warmed up on 400 other overlays (glyph "
+                                               "variants of border-clipped labels are rasterised once and cached)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": peak_src, "kernel": "resize3_staged",

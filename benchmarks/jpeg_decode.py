@@ -50,22 +50,31 @@ def main():
     # several batches in flight on separate CUDA streams: the entropy kernel of one 32-image batch keeps only
     # 68 warps busy (one thread per restart segment), so concurrent batches fill the rest of the GPU
     blobs = [pinned(blob(500 + k, restart_marker_rows=1)) for k in range(32)]
-    for lanes in (1, 2, 4, 8, 12):
-        streams = [torch.cuda.Stream(dev) for _ in range(lanes)]
-        decs = [jpeg.GpuJpegDecoder(dev) for _ in range(lanes)]
-        outs = [torch.empty((32, 1080, 1920, 3), dtype=torch.uint8, device=dev) for _ in range(lanes)]
-        for k in range(lanes):
-            decs[k].decode(blobs, out=outs[k], stream=streams[k])
-        torch.cuda.synchronize()
-        rounds = 4
-        t0 = time.perf_counter()
-        for r in range(rounds):
+    for stages, what in ((15, "all stages"), (3, "segments + entropy decode only"), (12, "IDCT + colour only")):
+        os.environ["AIKO_B200_JPEG_STAGES"] = str(stages)
+        for lanes in (1, 4, 8, 12, 16) if stages != 12 else (1, 8):
+            streams = [torch.cuda.Stream(dev) for _ in range(lanes)]
+            decs = [jpeg.GpuJpegDecoder(dev) for _ in range(lanes)]
+            outs = [torch.empty((32, 1080, 1920, 3), dtype=torch.uint8, device=dev) for _ in range(lanes)]
             for k in range(lanes):
                 decs[k].decode(blobs, out=outs[k], stream=streams[k])
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        print(f"own decoder, restart every MCU row, {lanes} batches in flight: {32 * lanes * rounds / dt:.0f} frames/s")
-        del outs
+            torch.cuda.synchronize()
+            rounds = 4
+            call_s = 0.0
+            t0 = time.perf_counter()
+            for r in range(rounds):
+                for k in range(lanes):
+                    if decs[k]._event is not None:
+                        decs[k]._event.synchronize()
+                    c0 = time.perf_counter()
+                    decs[k].decode(blobs, out=outs[k], stream=streams[k])
+                    call_s += time.perf_counter() - c0
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            print(f"own decoder, restart every MCU row, {what}, {lanes} batches in flight: "
+                  f"{32 * lanes * rounds / dt:.0f} frames/s, host {call_s / (lanes * rounds) * 1e3:.2f} ms per call")
+            del outs, decs
+    os.environ.pop("AIKO_B200_JPEG_STAGES")
     blobs = [pinned(blob(500 + k)) for k in range(32)]
     nv = jpeg.JpegDecoder(dev, 32)
     nv.decode(blobs, out=frames)

@@ -186,6 +186,24 @@ int aiko_b200_resize_linear_u8(const uint8_t* src, int n_frames, int src_h, int 
                                int dst_w, int64_t dst_row_stride, int64_t dst_frame_stride, int swap_rb,
                                const aiko_b200_overlay* overlay_host, void* stream);
 
+/* The per-frame call of a detection pipeline, ImageResize -> ImageOverlay (-> RGB2BGR) with an overlay that is
+ * new on every call (image_io.py:119-155 runs for every frame: boxes move, the label text carries the
+ * confidence): aiko_b200_overlay_plan_struct_host followed by aiko_b200_resize_linear_u8 as ONE call, so the
+ * host pays one crossing of the ABI per frame batch.  Arguments as in those two; the draw lists are planned for
+ * the dst_w x dst_h frames.  overlay_host->patch_ids / luts are the caller's device copy of the glyph atlas in
+ * the state (atlas_version, atlas_epoch); when planning had to grow the atlas past that state nothing is
+ * launched and AIKO_B200_ATLAS_GREW is returned: overlay_host is planned, the caller brings its device copy
+ * up to date (aiko_b200_overlay_atlas_host) and calls aiko_b200_resize_linear_u8 itself. */
+#define AIKO_B200_ATLAS_GREW 1
+int aiko_b200_resize_linear_objects_u8(const uint8_t* src, int n_frames, int src_h, int src_w, int channels,
+                                       int64_t src_row_stride, int64_t src_frame_stride, uint8_t* dst, int dst_h,
+                                       int dst_w, int64_t dst_row_stride, int64_t dst_frame_stride, int swap_rb,
+                                       int n_lists, const int32_t* object_offsets_host, const int32_t* rects_host,
+                                       const char* labels_host, int layout, const int32_t* list_of_frame_host,
+                                       void* buffer_host, size_t buffer_bytes, void* buffer_dev,
+                                       aiko_b200_overlay* overlay_host, aiko_b200_overlay_plan_info* info_host,
+                                       uint64_t atlas_version, uint64_t atlas_epoch, void* stream);
+
 /* ImageResize, PIL branch: PIL.Image.resize((W, H)) -- default BICUBIC filter   */
 /* with antialiasing, 8 bits per channel, horizontal pass then vertical pass on a  */
 /* uint8 intermediate -- R/elements/media/image_io.py:218.  Bit-exact.             */

@@ -485,6 +485,39 @@ def test_overlay_ring_changing_lists(cuda, atlas):
             np.testing.assert_array_equal(out[k], overlay_cpu(O.resize_linear(frames[k], W, H), overlay, atlas))
 
 
+def test_overlay_ring_resize_draw_one_call(cuda, atlas):
+    """OverlayRing.resize_draw = plan + resize + draw in ONE call of the library
+    (aiko_b200_resize_linear_objects_u8): a new overlay per call, shared or one per frame, with and
+    without the fused RGB->BGR; labels near the border make the planner grow the atlas in mid-run (the
+    ATLAS_GREW path).  Bit-exact with the oracle; the ring wraps several times."""
+    from aiko_services_b200.overlay_plan import build_ops
+    from util import replay_ops_cpu
+    rng = np.random.default_rng(89)
+    W, H = 160, 120
+    frames = np.stack([cases.frame(720 + k, 270, 480, 3) for k in range(2)])
+    d = dev(frames, cuda)
+    ring = ops.OverlayRing(cuda, capacity=1 << 14, slots=3)
+    for i in range(12):
+        swap = bool(i & 1)
+        per_frame = i % 3 == 2
+        overlays = [random_overlay(rng, W, H, n=3) for _ in range(2)] if per_frame else random_overlay(rng, W, H, n=3)
+        out = host(ring.resize_draw(d, overlays, W, H, swap_rb=swap))
+        for k in range(2):
+            small = O.resize_linear(frames[k], W, H)
+            o = overlays[k] if per_frame else overlays
+            if swap:
+                want = replay_ops_cpu(O.swap_rb(small), build_ops(o, W, H, "bgr", atlas), atlas)
+            else:
+                want = overlay_cpu(small, o, atlas)
+            np.testing.assert_array_equal(out[k], want)
+    # an empty overlay draws nothing; a list too long for a ring slot takes one-off buffers
+    np.testing.assert_array_equal(host(ring.resize_draw(d, {}, W, H))[0], O.resize_linear(frames[0], W, H))
+    big = random_overlay(rng, W, H, n=120)
+    small_ring = ops.OverlayRing(cuda, capacity=1 << 10, slots=2)
+    out = host(small_ring.resize_draw(d, big, W, H))
+    np.testing.assert_array_equal(out[1], overlay_cpu(O.resize_linear(frames[1], W, H), big, atlas))
+
+
 def _pil_array(im, mode):
     a = np.asarray(im)
     return a.astype(np.uint8) * 255 if mode == "1" else a
