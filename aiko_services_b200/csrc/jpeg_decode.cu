@@ -31,6 +31,7 @@ namespace aiko {
 
 constexpr int kLutBits = 9;
 constexpr int kMaxSegments = 65535;
+constexpr int kSyncMaxSegments = 512;   // images with more restart segments than this take jpeg_huffman_kernel
 
 struct HuffDev {                 // one Huffman table, ready for the device
   uint16_t lut[1 << kLutBits];   // next 9 bits -> (length << 8) | symbol, 0 = longer than 9 bits
@@ -361,6 +362,7 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
   __shared__ uint8_t s_zigzag[64];                        // (divergent indices: shared memory, not the constant cache)
   if (threadIdx.x < 64) s_zigzag[threadIdx.x] = kZigzag[threadIdx.x];
   const JpegImage im = images[blockIdx.y];
+  if (im.n_segments <= kSyncMaxSegments) return;          // (uniform) jpeg_sync_huffman_kernel's image
   const JpegTables& t = tables[im.table_set];
   // components use at most two DC and two AC tables in this subset (luma's and chroma's)
   if (threadIdx.x < 4) { s_slot_dc[threadIdx.x] = -1; s_slot_ac[threadIdx.x] = -1; }
@@ -443,6 +445,375 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
     }
   }
   if (bad) atomicExch(status, 2000 + (int)blockIdx.y);
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 2b: Huffman decoding of scans with few (or no) restart markers: one CTA per image, one thread per
+// SUBSEQUENCE of the scan (a run of B bytes inside one restart segment; B is chosen so that the image has at most
+// 1024 of them).  A thread that does not start a segment does not know where a codeword begins, which block
+// coefficient comes next or which component it belongs to, so the decoder state (bit position u, zigzag index
+// z, block-in-MCU c) at every subsequence boundary is found by iteration (self-synchronising Huffman decoding,
+// Klein & Wiseman 2003; on GPUs: Weissenberger & Schmidt 2018 / 2021): every thread first decodes its
+// subsequence from a guessed state, then again from the exit state of its predecessor, until no exit state
+// changes -- Huffman streams re-synchronise within a few dozen symbols, so two rounds settle almost every
+// boundary, and the loop is exact in any case (the first thread of a segment starts from the true state, and
+// each round extends the settled prefix).  Then the blocks completed per subsequence are prefix-summed into
+// block indices, a last pass writes the coefficients (DC as differences), and the DC predictions are resolved
+// with a prefix sum over the per-thread sums of differences.
+// Bit positions are counted in the UNSTUFFED stream (FF 00 -> FF) relative to the segment start.
+constexpr int kSyncThreads = 1024;
+
+struct SyncShared {
+  HuffDev dc[2], ac[2];
+  int slot_dc[4], slot_ac[4];
+  uint8_t zigzag[64];
+  uint8_t comp_of[8], bx_of[8], by_of[8], dc_of[8], ac_of[8];   // per block of an MCU
+  uint32_t seg_first[kSyncMaxSegments + 1];   // first subsequence of each segment
+  uint32_t start[kSyncThreads];               // raw byte offset of the subsequence in the scan
+  uint32_t ubits[kSyncThreads];               // unstuffed bit position of its first data byte, relative to its segment
+  uint32_t count[kSyncThreads];               // data bytes, later completed blocks
+  unsigned long long state[kSyncThreads];     // exit state (u << 16 | z << 4 | c)
+  uint16_t seg_of[kSyncThreads];
+  uint8_t changed[2][kSyncThreads];
+  int warp_sums[kSyncThreads / 32];
+};
+
+__device__ __forceinline__ int block_scan_excl(int v, int* warp_sums, int* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  int before = 0, all = 0;
+  for (int w = 0; w < (int)blockDim.x / 32; w++) {
+    const int s = warp_sums[w];
+    before += w < warp ? s : 0;
+    all += s;
+  }
+  __syncthreads();
+  *total = all;
+  return before + incl - v;
+}
+
+struct SpanReader {
+  BitReader b;
+  uint32_t loaded;       // bits fed into the accumulator so far
+  uint32_t base;         // position of the head bit = base + loaded - b.n
+};
+
+__device__ __forceinline__ void span_refill(SpanReader& r) {
+  while (r.b.n <= 56) {
+    unsigned byte = 0;
+    if (r.b.p < r.b.end) {
+      byte = *r.b.p;
+      if (byte == 0xffu) {
+        const unsigned next = (r.b.p + 1 < r.b.end) ? r.b.p[1] : 0xd9u;
+        if (next == 0u) r.b.p += 2;
+        else { byte = 0; r.b.end = r.b.p; }
+      } else {
+        r.b.p++;
+      }
+    }
+    r.b.acc |= (unsigned long long)byte << (56 - r.b.n);
+    r.b.n += 8;
+    r.loaded += 8;
+  }
+}
+
+// Decodes from (u, z, c) until the next codeword starts at or after `limit` (WRITE: or block `g_limit` is
+// reached).  -> exit state; *blocks = blocks completed.  WRITE stores the coefficients of blocks g, g + 1, ...
+template <bool WRITE>
+__device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, const JpegImage& im, const JpegGeometry& g,
+                                                         const uint8_t* seg_begin, const uint8_t* start,
+                                                         const uint8_t* seg_end, uint32_t ubits, uint32_t limit,
+                                                         unsigned long long entry, int* blocks, int16_t* image_coef,
+                                                         int bpm, int gi, int g_limit, int dsum[3], int* dc_first,
+                                                         int* dc_count, int* bad) {
+  uint32_t u = (uint32_t)(entry >> 16);
+  int z = (int)((entry >> 4) & 63u), c = (int)(entry & 15u);
+  SpanReader r;
+  r.b.p = start; r.b.end = seg_end; r.b.acc = 0; r.b.n = 0; r.loaded = 0;
+  if (start > seg_begin && start < seg_end && start[-1] == 0xffu && start[0] == 0u) r.b.p++;   // a stuffed zero
+  uint32_t skip = u - ubits;
+  span_refill(r);
+  while (skip) {
+    const uint32_t t = skip < 32u ? skip : 32u;
+    r.b.acc <<= t; r.b.n -= (int)t; skip -= t;
+    span_refill(r);
+  }
+  r.base = u - (r.loaded - (uint32_t)r.b.n);
+  int done = 0;
+  int16_t* blk = nullptr;
+  int mx = 0, my = 0;
+  if (WRITE) {
+    const int m = gi / bpm;
+    my = m / g.mcux; mx = m - my * g.mcux;
+    *dc_first = gi + (z > 0 ? 1 : 0);
+  }
+  auto block_ptr = [&](int q) -> int16_t* {
+    const int comp = S.comp_of[q];
+    return image_coef + g.coef_offset[comp] +
+           ((size_t)(my * g.v[comp] + S.by_of[q]) * g.bw[comp] + (mx * g.h[comp] + S.bx_of[q])) * 64;
+  };
+  if (WRITE && gi < g_limit) blk = block_ptr(c);
+  for (;;) {
+    if (r.b.n < 32) span_refill(r);
+    u = r.base + r.loaded - (uint32_t)r.b.n;
+    if (u >= limit) break;
+    if (WRITE && gi >= g_limit) break;
+    const int comp = S.comp_of[c];
+    const HuffDev& h = z == 0 ? S.dc[S.dc_of[c]] : S.ac[S.ac_of[c]];
+    const int sym = decode_symbol(r.b, h);
+    if (sym < 0) {                           // no such code: only in a wrong state or a corrupt file
+      r.b.acc <<= 1; r.b.n -= 1;
+      if (WRITE) *bad = 2000;
+      continue;
+    }
+    const int run = z == 0 ? 0 : sym >> 4, size = z == 0 ? sym : sym & 15;
+    if (size) {
+      const int v = extend_sign(take_bits(r.b, size), size);
+      const int k = z + run;
+      if (k > 63) {
+        if (WRITE) *bad = 3000;
+        z = 64;
+      } else {
+        if (WRITE) {
+          if (z == 0) {
+            dsum[0] += comp == 0 ? v : 0; dsum[1] += comp == 1 ? v : 0; dsum[2] += comp == 2 ? v : 0;
+            ++*dc_count;
+          }
+          blk[S.zigzag[k]] = (int16_t)v;
+        }
+        z = k + 1;
+      }
+    } else if (z == 0) {
+      if (WRITE) ++*dc_count;
+      z = 1;
+    } else {
+      z = run == 15 ? z + 16 : 64;
+    }
+    if (z >= 64) {
+      z = 0;
+      done++;
+      if (++c == bpm) {
+        c = 0;
+        if (WRITE && ++mx == g.mcux) { mx = 0; my++; }
+      }
+      if (WRITE) {
+        gi++;
+        if (gi < g_limit) blk = block_ptr(c);
+      }
+    }
+  }
+  *blocks = done;
+  return ((unsigned long long)u << 16) | (unsigned long long)((z << 4) | c);
+}
+
+__global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const uint8_t* __restrict__ compressed,
+                                                                         const JpegImage* __restrict__ images,
+                                                                         const JpegTables* __restrict__ tables,
+                                                                         const uint32_t* __restrict__ seg_offsets,
+                                                                         int seg_pitch, const JpegGeometry g,
+                                                                         int16_t* __restrict__ coef,
+                                                                         int* __restrict__ status) {
+  extern __shared__ __align__(16) uint8_t sync_smem[];
+  SyncShared& S = *reinterpret_cast<SyncShared*>(sync_smem);
+  const JpegImage im = images[blockIdx.x];
+  if (im.n_segments > kSyncMaxSegments) return;            // (uniform) jpeg_huffman_kernel's image
+  const JpegTables& t = tables[im.table_set];
+  const int tid = (int)threadIdx.x;
+  if (tid < 64) S.zigzag[tid] = kZigzag[tid];
+  if (tid < 4) { S.slot_dc[tid] = -1; S.slot_ac[tid] = -1; }
+  __syncthreads();
+  int bpm = 0;
+  for (int c = 0; c < g.ncomp; c++) bpm += g.h[c] * g.v[c];
+  if (tid == 0) {
+    int nd = 0, na = 0, q = 0;
+    for (int c = 0; c < g.ncomp; c++) {
+      if (S.slot_dc[im.td[c]] < 0 && nd < 2) S.slot_dc[im.td[c]] = nd++;
+      if (S.slot_ac[im.ta[c]] < 0 && na < 2) S.slot_ac[im.ta[c]] = na++;
+      for (int by = 0; by < g.v[c]; by++)
+        for (int bx = 0; bx < g.h[c]; bx++, q++) {
+          S.comp_of[q] = (uint8_t)c; S.bx_of[q] = (uint8_t)bx; S.by_of[q] = (uint8_t)by;
+          S.dc_of[q] = (uint8_t)max(S.slot_dc[im.td[c]], 0); S.ac_of[q] = (uint8_t)max(S.slot_ac[im.ta[c]], 0);
+        }
+    }
+  }
+  __syncthreads();
+  bool table_ok = true;
+  for (int c = 0; c < g.ncomp; c++) table_ok &= S.slot_dc[im.td[c]] >= 0 && S.slot_ac[im.ta[c]] >= 0;
+  if (!table_ok) {                                          // (uniform) three different tables
+    if (tid == 0) atomicExch(status, 1000 + (int)blockIdx.x);
+    return;
+  }
+  for (int id = 0; id < 4; id++) {
+    if (S.slot_dc[id] >= 0) {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(&t.dc[id]);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(&S.dc[S.slot_dc[id]]);
+      for (int i = tid; i < (int)(sizeof(HuffDev) / 4); i += kSyncThreads) dst[i] = __ldg(src + i);
+    }
+    if (S.slot_ac[id] >= 0) {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(&t.ac[id]);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(&S.ac[S.slot_ac[id]]);
+      for (int i = tid; i < (int)(sizeof(HuffDev) / 4); i += kSyncThreads) dst[i] = __ldg(src + i);
+    }
+  }
+  // ---- the subsequences: B bytes each, never across a restart marker
+  const uint32_t* offs = seg_offsets + (size_t)blockIdx.x * seg_pitch;
+  const uint8_t* base = compressed + im.scan_offset;
+  const int n_seg = im.n_segments;
+  const uint32_t scan_bytes = im.scan_bytes;
+  const uint32_t B = max(((scan_bytes + (uint32_t)(kSyncThreads - n_seg) - 1) / (uint32_t)(kSyncThreads - n_seg) + 63u) & ~63u, 64u);
+  int total;
+  {
+    int mine = 0;
+    if (tid < n_seg) {
+      const uint32_t lo = offs[tid], hi = tid + 1 < n_seg ? offs[tid + 1] : scan_bytes;
+      mine = (int)((hi - lo + B - 1) / B);
+    }
+    const int first = block_scan_excl(mine, S.warp_sums, &total);
+    if (tid < n_seg) S.seg_first[tid] = (uint32_t)first;
+    if (tid == 0) S.seg_first[n_seg] = (uint32_t)total;
+  }
+  __syncthreads();
+  const int n_sub = total;                                  // <= kSyncThreads by the choice of B
+  const bool active = tid < n_sub;
+  int seg = 0;
+  uint32_t seg_lo = 0, seg_hi = 0, sub_lo = 0, sub_hi = 0;
+  bool first_of_segment = false;
+  if (active) {
+    int lo = 0, hi = n_seg - 1;                             // last segment whose first subsequence is <= tid
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if ((int)S.seg_first[mid] <= tid) lo = mid; else hi = mid - 1;
+    }
+    seg = lo;
+    seg_lo = offs[seg];
+    seg_hi = seg + 1 < n_seg ? offs[seg + 1] : scan_bytes;
+    const uint32_t i = (uint32_t)tid - S.seg_first[seg];
+    first_of_segment = i == 0;
+    sub_lo = seg_lo + i * B;
+    sub_hi = min(sub_lo + B, seg_hi);
+    S.start[tid] = sub_lo;
+    S.seg_of[tid] = (uint16_t)seg;
+  }
+  // data bytes per subsequence (stuffed zeros and everything from a marker on do not count)
+  int data_bytes = 0;
+  if (active) {
+    uint32_t i = sub_lo;
+    if (sub_lo > seg_lo && base[sub_lo - 1] == 0xffu) {
+      if (base[sub_lo] == 0u) i++;                          // the stuffed zero of the FF before the boundary
+      else i = sub_hi;                                      // the second byte of the marker that ends the segment
+    }
+    while (i < sub_hi) {
+      if (base[i] == 0xffu) {
+        const unsigned next = i + 1 < seg_hi ? base[i + 1] : 0xd9u;
+        if (next != 0u) break;                              // a marker: the segment's data ends here
+        i++;                                                // FF 00 = one data byte
+      }
+      data_bytes++;
+      i++;
+    }
+  }
+  {
+    const int before = block_scan_excl(data_bytes, S.warp_sums, &total);
+    if (active) S.count[tid] = (uint32_t)before;
+  }
+  __syncthreads();
+  uint32_t ubits = 0, limit = 0;
+  if (active) {
+    ubits = 8u * (S.count[tid] - S.count[S.seg_first[seg]]);
+    limit = ubits + 8u * (uint32_t)data_bytes;
+    S.ubits[tid] = ubits;
+  }
+  __syncthreads();
+  // ---- the exit state of every subsequence, by iteration
+  int16_t* image_coef = coef + (size_t)blockIdx.x * g.coef_per_image;
+  int dsum[3] = {0, 0, 0};
+  int dc_first = 0, dc_count = 0;
+  int bad = 0;
+  int blocks = 0;
+  int cur = 0;
+  for (int iter = 0;; iter++) {
+    bool need = false;
+    unsigned long long entry = 0;
+    if (active) {
+      if (iter == 0) {
+        need = true;
+        entry = (unsigned long long)ubits << 16;           // guess: a block begins here (exact for a segment's first)
+      } else if (!first_of_segment && S.changed[cur ^ 1][tid - 1]) {
+        need = true;
+        entry = S.state[tid - 1];
+      }
+    }
+    unsigned long long exit_state = 0;
+    if (need)
+      exit_state = decode_span<false>(S, im, g, base + seg_lo, base + sub_lo, base + seg_hi, ubits, limit, entry, &blocks,
+                                      nullptr, bpm, 0, 0, dsum, &dc_first, &dc_count, &bad);
+    __syncthreads();
+    bool ch = false;
+    if (need) {
+      ch = iter == 0 || exit_state != S.state[tid];
+      S.state[tid] = exit_state;
+    }
+    if (active) S.changed[cur][tid] = ch ? 1 : 0;
+    const int any = __syncthreads_or(ch ? 1 : 0);
+    cur ^= 1;
+    if (!any) break;
+  }
+  // ---- block index of every subsequence, then the pass that writes
+  {
+    const int before = block_scan_excl(active ? blocks : 0, S.warp_sums, &total);
+    __syncthreads();
+    if (active) S.count[tid] = (uint32_t)before;
+  }
+  __syncthreads();
+  const int total_mcus = g.mcux * g.mcuy;
+  if (active) {
+    const int interval = im.restart_interval > 0 ? im.restart_interval : total_mcus;
+    const int g0 = seg * interval * bpm + (int)(S.count[tid] - S.count[S.seg_first[seg]]);
+    const int g_limit = min((seg + 1) * interval, total_mcus) * bpm;
+    const unsigned long long entry = first_of_segment ? 0ull : S.state[tid - 1];
+    const unsigned long long exit_state =
+        decode_span<true>(S, im, g, base + seg_lo, base + sub_lo, base + seg_hi, ubits, limit, entry, &blocks, image_coef, bpm,
+                          g0, g_limit, dsum, &dc_first, &dc_count, &bad);
+    const bool last_of_segment = tid + 1 == (int)S.seg_first[seg + 1];
+    if (last_of_segment && g0 + blocks != g_limit) bad = 4000;        // the segment ended early (or ran over)
+    // (cannot happen: the iteration settled; a thread that stopped at the segment's last block skipped the pad bits)
+    if (!last_of_segment && g0 + blocks < g_limit && exit_state != S.state[tid]) bad = 5000;
+  }
+  if (bad) atomicExch(status, bad + (int)blockIdx.x);
+  // ---- DC predictions: prefix sums of the differences per component, restarted at every segment
+  int pred[3];
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    __syncthreads();
+    const int before = block_scan_excl(active ? dsum[c] : 0, S.warp_sums, &total);
+    if (active) S.count[tid] = (uint32_t)before;
+    __syncthreads();
+    pred[c] = active ? (int)(S.count[tid] - S.count[S.seg_first[seg]]) : 0;
+  }
+  if (active && dc_count > 0) {
+    const int m = dc_first / bpm;
+    int q = dc_first - m * bpm;
+    int my = m / g.mcux, mx = m - my * g.mcux;
+    for (int i = 0; i < dc_count; i++) {
+      const int comp = S.comp_of[q];
+      int16_t* blk = image_coef + g.coef_offset[comp] +
+                     ((size_t)(my * g.v[comp] + S.by_of[q]) * g.bw[comp] + (mx * g.h[comp] + S.bx_of[q])) * 64;
+      const int v = (comp == 0 ? pred[0] : comp == 1 ? pred[1] : pred[2]) + (int)blk[0];
+      if (comp == 0) pred[0] = v; else if (comp == 1) pred[1] = v; else pred[2] = v;
+      blk[0] = (int16_t)v;
+      if (++q == bpm) {
+        q = 0;
+        if (++mx == g.mcux) { mx = 0; my++; }
+      }
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -723,6 +1094,7 @@ extern "C" int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host
   JpegGeometry g{};
   size_t scan_total = 0;
   int needed_segments = 1;
+  bool any_few = false, any_many = false;   // restart segments per image: which entropy kernels run
   for (int i = 0; i < n_images; i++) {
     const int rc = parse_jpeg(jpegs_host[i], lengths_host[i], &parsed[i], false);
     if (rc != AIKO_B200_OK) return rc;
@@ -735,11 +1107,9 @@ extern "C" int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host
                      gi.W, gi.H, gi.ncomp, gi.hmax, gi.vmax, g.W, g.H, g.ncomp, g.hmax, g.vmax);
       return AIKO_B200_ERR_INVALID_ARGUMENT;
     }
-    if (parsed[i].restart <= 0) {
-      set_last_error("jpeg_decode: image %d has no restart interval (the parallel entropy decoder needs one)", i);
-      return AIKO_B200_ERR_UNSUPPORTED;
-    }
-    const int segs = (g.mcux * g.mcuy + parsed[i].restart - 1) / parsed[i].restart;
+    const int segs = parsed[i].restart > 0 ? (g.mcux * g.mcuy + parsed[i].restart - 1) / parsed[i].restart : 1;
+    any_few |= segs <= kSyncMaxSegments;
+    any_many |= segs > kSyncMaxSegments;
     needed_segments = segs > needed_segments ? segs : needed_segments;
     scan_total += align_up(parsed[i].scan_bytes, 16);
   }
@@ -774,8 +1144,8 @@ extern "C" int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host
     memset(&d, 0, sizeof(d));
     d.scan_offset = (uint32_t)scan_at;
     d.scan_bytes = (uint32_t)im.scan_bytes;
-    d.restart_interval = im.restart;
-    d.n_segments = (g.mcux * g.mcuy + im.restart - 1) / im.restart;
+    d.restart_interval = im.restart > 0 ? im.restart : g.mcux * g.mcuy;
+    d.n_segments = (g.mcux * g.mcuy + d.restart_interval - 1) / d.restart_interval;
     d.table_set = set;
     for (int c = 0; c < g.ncomp; c++) { d.td[c] = (uint8_t)im.td[c]; d.ta[c] = (uint8_t)im.ta[c]; d.tq[c] = (uint8_t)im.tq[c]; }
     scan_at += align_up(im.scan_bytes, 16);
@@ -801,8 +1171,13 @@ extern "C" int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host
 
   if (stages & 1) jpeg_segments_kernel<<<(unsigned)n_images, kSegThreads, 0, st>>>(ws + L.compressed, d_images, d_seg, L.seg_pitch, d_status);
   AIKO_CUDA(cudaGetLastError());
-  if (stages & 2) jpeg_huffman_kernel<<<dim3((unsigned)((needed_segments + kHuffThreads - 1) / kHuffThreads), (unsigned)n_images),
-                        kHuffThreads, 0, st>>>(ws + L.compressed, d_images, d_tables, d_seg, L.seg_pitch, g, d_coef, d_status);
+  if ((stages & 2) && any_many)
+    jpeg_huffman_kernel<<<dim3((unsigned)((needed_segments + kHuffThreads - 1) / kHuffThreads), (unsigned)n_images),
+                          kHuffThreads, 0, st>>>(ws + L.compressed, d_images, d_tables, d_seg, L.seg_pitch, g, d_coef, d_status);
+  AIKO_CUDA(cudaGetLastError());
+  if ((stages & 2) && any_few)
+    jpeg_sync_huffman_kernel<<<(unsigned)n_images, kSyncThreads, sizeof(SyncShared), st>>>(
+        ws + L.compressed, d_images, d_tables, d_seg, L.seg_pitch, g, d_coef, d_status);
   AIKO_CUDA(cudaGetLastError());
   const long long blocks = g.coef_per_image / 64;
   if (stages & 4) jpeg_idct_kernel<<<dim3((unsigned)((blocks + kIdctThreads - 1) / kIdctThreads), (unsigned)n_images), kIdctThreads, 0, st>>>(
@@ -832,7 +1207,8 @@ extern "C" int aiko_b200_jpeg_gpu_status(const void* workspace, int n_images, in
   AIKO_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
   if (status != 0) {
     set_last_error("jpeg: corrupt entropy-coded data (code %d: 1+i restart markers of image i do not match its restart "
-                   "interval, 1000+i more than two Huffman tables, 2000+i invalid code in image i)", status);
+                   "interval, 1000+i more than two Huffman tables, 2000+i invalid code, 3000+i coefficient index past 63, "
+                   "4000+i a segment with too few or too many blocks)", status);
     return AIKO_B200_ERR_INVALID_ARGUMENT;
   }
   return AIKO_B200_OK;

@@ -122,9 +122,9 @@ def decoder_for(device, max_batch=64):
 class GpuJpegDecoder:
     """This library's own JPEG decoder (csrc/jpeg_decode.cu; include/aiko_b200.h, aiko_b200_jpeg_gpu_*):
     Huffman decoding, IDCT, upsampling and colour conversion all on the GPU, pixels bit-identical to
-    Pillow's decoder.  Needs baseline files with restart markers (entropy decoding runs one thread per
-    restart segment); for anything else ``decode`` raises NativeError(ERR_UNSUPPORTED) and the caller
-    keeps its other decoder (``JpegDecoder`` above, or Pillow).  One decoder per (GPU, CUDA stream)."""
+    Pillow's decoder.  Baseline files (gray, 4:4:4, 4:2:2, 4:2:0), with or without restart markers; for
+    anything else (progressive, arithmetic, 12 bit) ``decode`` raises NativeError(ERR_UNSUPPORTED) and the
+    caller keeps its other decoder (``JpegDecoder`` above, or Pillow).  One decoder per (GPU, CUDA stream)."""
 
     def __init__(self, device):
         self.device = torch.device(device)
@@ -163,34 +163,42 @@ class GpuJpegDecoder:
         first = buffers[0]
         head = bytes(first[:min(first.numel(), 1 << 16)].numpy().tobytes()) if isinstance(first, torch.Tensor) else bytes(first)
         w, h, comps, hmax, vmax, restart = self.info(head)
-        if restart <= 0:
-            raise NativeError(_native.ERR_UNSUPPORTED, "jpeg: no restart interval (the parallel entropy decoder needs one)")
         mcus = -(-w // (8 * hmax)) * -(-h // (8 * vmax))
-        segments = -(-mcus // restart)
+        segments = -(-mcus // restart) if restart > 0 else 1
         ptrs, lens, keep = self._pointers(buffers)
         total = sum(int(v) for v in lens)
         key = (n, w, h, comps, hmax, vmax)
         lib = _native.lib()
-        entry = self._buffers.get(key)
-        if entry is None or entry[2] < total or entry[3] < segments:
-            capacity = max(-(-total * 5 // 4 // (1 << 20)) * (1 << 20), 1 << 20)
-            nbytes = lib.aiko_b200_jpeg_gpu_workspace_bytes(n, w, h, comps, hmax, vmax, capacity, segments)
-            if nbytes == 0:
-                raise NativeError(_native.ERR_UNSUPPORTED, f"jpeg: unsupported layout ({comps} components, {hmax}x{vmax})")
-            with torch.cuda.device(self.device):
-                workspace = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
-            staging = torch.empty(lib.aiko_b200_jpeg_gpu_staging_bytes(n), dtype=torch.uint8).pin_memory()
-            entry = self._buffers[key] = (workspace, staging, capacity, segments)
-        workspace, staging, capacity, max_segments = entry
         if out is None:
             out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=self.device)
         s = stream if stream is not None else torch.cuda.current_stream(self.device)
         if self._event is not None:
-            self._event.synchronize()            # the previous call's descriptors have left the staging buffer
-        with torch.cuda.device(self.device):
-            _native.check(lib.aiko_b200_jpeg_gpu_decode_rgb_u8(
-                ptrs, lens, n, out.data_ptr(), h, w, h * w * 3, staging.data_ptr(), staging.numel(), workspace.data_ptr(),
-                workspace.numel(), capacity, max_segments, _vp(s.cuda_stream)))
+            self._event.synchronize()            # the previous call has left the staging buffer and the workspace
+        for attempt in range(2):
+            entry = self._buffers.get(key)
+            if entry is None or entry[2] < total or entry[3] < segments:
+                capacity = max(-(-total * 5 // 4 // (1 << 20)) * (1 << 20), 1 << 20)
+                nbytes = lib.aiko_b200_jpeg_gpu_workspace_bytes(n, w, h, comps, hmax, vmax, capacity, segments)
+                if nbytes == 0:
+                    raise NativeError(_native.ERR_UNSUPPORTED, f"jpeg: unsupported layout ({comps} components, {hmax}x{vmax})")
+                with torch.cuda.device(self.device):
+                    workspace = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+                staging = torch.empty(lib.aiko_b200_jpeg_gpu_staging_bytes(n), dtype=torch.uint8).pin_memory()
+                entry = self._buffers[key] = (workspace, staging, capacity, segments)
+            workspace, staging, capacity, max_segments = entry
+            with torch.cuda.device(self.device):
+                rc = lib.aiko_b200_jpeg_gpu_decode_rgb_u8(
+                    ptrs, lens, n, out.data_ptr(), h, w, h * w * 3, staging.data_ptr(), staging.numel(), workspace.data_ptr(),
+                    workspace.numel(), capacity, max_segments, _vp(s.cuda_stream))
+            if rc != _native.ERR_WORKSPACE or attempt:
+                _native.check(rc)
+                break
+            # the other images of the batch have more restart segments than the first: size for the largest
+            for k in range(n):
+                b = buffers[k]
+                head_k = bytes(b[:min(b.numel(), 1 << 16)].numpy().tobytes()) if isinstance(b, torch.Tensor) else bytes(b)
+                restart_k = self.info(head_k)[5]
+                segments = max(segments, -(-mcus // restart_k) if restart_k > 0 else 1)
         if self._event is None:
             self._event = torch.cuda.Event()
         self._event.record(s)

@@ -107,13 +107,15 @@ def test_image_read_file_decodes_on_the_gpu(cuda, tmp_path):
 
 
 # ---- this library's own decoder (csrc/jpeg_decode.cu): bit-exact with Pillow ------------------------------
-def encode_rst(frame, quality=90, subsampling=2, mode="RGB", **kw):
+def encode_rst(frame, quality=90, subsampling=2, mode="RGB", plain=False, **kw):
+    """Baseline JPEG; restart markers per MCU row unless ``kw`` says otherwise or ``plain`` (none at all)."""
     from PIL import Image
     buf = io.BytesIO()
     im = Image.fromarray(frame, "RGB")
     if mode == "L":
         im = im.convert("L")
-    im.save(buf, "JPEG", quality=quality, subsampling=subsampling if mode == "RGB" else -1, **(kw or {"restart_marker_rows": 1}))
+    extra = {} if plain else (kw or {"restart_marker_rows": 1})
+    im.save(buf, "JPEG", quality=quality, subsampling=subsampling if mode == "RGB" else -1, **extra)
     return buf.getvalue()
 
 
@@ -122,15 +124,16 @@ def pillow_rgb(blob):
     return np.asarray(Image.open(io.BytesIO(blob)).convert("RGB"))
 
 
+@pytest.mark.parametrize("plain", [False, True], ids=["restart_rows", "no_markers"])
 @pytest.mark.parametrize("subsampling", [0, 1, 2], ids=["444", "422", "420"])
-def test_own_decoder_is_bit_exact_with_pillow(cuda, subsampling):
+def test_own_decoder_is_bit_exact_with_pillow(cuda, subsampling, plain):
     from aiko_services_b200 import jpeg
     dec = jpeg.GpuJpegDecoder(cuda)
     rng = np.random.default_rng(40 + subsampling)
-    for h, w in ((270, 480), (64, 96), (67, 101), (8, 8), (1, 1), (17, 250)):
+    for h, w in ((270, 480), (64, 96), (67, 101), (8, 8), (1, 1), (17, 250), (600, 800)):
         frames = [natural_frame(int(rng.integers(1 << 30)), max(h, 2), max(w, 2))[:h, :w] for _ in range(3)]
         frames[1] = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)               # noise: long codes, big coefficients
-        blobs = [encode_rst(f, int(rng.integers(40, 100)), subsampling) for f in frames]
+        blobs = [encode_rst(f, int(rng.integers(40, 100)), subsampling, plain=plain) for f in frames]
         got = dec.decode(blobs, check=True).cpu().numpy()
         for k in range(3):
             np.testing.assert_array_equal(got[k], pillow_rgb(blobs[k]), err_msg=f"{w}x{h} image {k}")
@@ -146,10 +149,17 @@ def test_own_decoder_gray_restart_blocks_and_1080p(cuda):
         np.testing.assert_array_equal(dec.decode([blob], check=True).cpu().numpy()[0], pillow_rgb(blob))
     gray = encode_rst(frame, 80, 0, mode="L")
     np.testing.assert_array_equal(dec.decode([gray, gray], check=True).cpu().numpy()[1], pillow_rgb(gray))
-    big = [encode_rst(natural_frame(90 + k, 1080, 1920), 90, 2) for k in range(2)]       # BASELINE config 1 size
+    gray = encode_rst(frame, 80, 0, mode="L", plain=True)
+    np.testing.assert_array_equal(dec.decode([gray, gray], check=True).cpu().numpy()[0], pillow_rgb(gray))
+    # BASELINE config 1 size; one batch mixes every kind of scan: a marker per MCU row and no markers at all (one
+    # thread per 512-byte subsequence, states found by iteration), a marker every 8 MCUs (1020 segments: one thread
+    # per segment), and white noise at quality 100 (3 MB of scan, long codes)
+    big = [encode_rst(natural_frame(90, 1080, 1920), 90, 2), encode_rst(natural_frame(91, 1080, 1920), 90, 2, plain=True),
+           encode_rst(natural_frame(92, 1080, 1920), 75, 2, restart_marker_blocks=8),
+           encode_rst(np.random.default_rng(5).integers(0, 256, (1080, 1920, 3), dtype=np.uint8), 100, 2, plain=True)]
     got = dec.decode(big, check=True).cpu().numpy()
-    for k in range(2):
-        np.testing.assert_array_equal(got[k], pillow_rgb(big[k]))
+    for k in range(len(big)):
+        np.testing.assert_array_equal(got[k], pillow_rgb(big[k]), err_msg=f"image {k}")
 
 
 def test_own_decoder_refuses_what_it_cannot_do(cuda):
@@ -158,21 +168,23 @@ def test_own_decoder_refuses_what_it_cannot_do(cuda):
     from aiko_services_b200._native import ERR_UNSUPPORTED, NativeError
     dec = jpeg.GpuJpegDecoder(cuda)
     frame = natural_frame(3, 64, 96)
-    with pytest.raises(NativeError) as e:
-        dec.decode([encode(frame)])                          # no restart markers
-    assert e.value.code == ERR_UNSUPPORTED
     buf = io.BytesIO()
     Image.fromarray(frame, "RGB").save(buf, "JPEG", progressive=True)
-    with pytest.raises(NativeError):
+    with pytest.raises(NativeError) as e:
         dec.decode([buf.getvalue()])
+    assert e.value.code == ERR_UNSUPPORTED
     good = encode_rst(frame)
     with pytest.raises(NativeError):
         dec.decode([good, encode_rst(natural_frame(4, 48, 96))])      # sizes differ within a batch
     cut = good[:len(good) // 2]                                        # truncated scan: reported, no crash
     with pytest.raises(NativeError):
         dec.decode([cut], check=True)
-    frames, which = jpeg.decode_on_gpu([encode(frame)], cuda)          # falls back to nvJPEG for plain files
+    for cut in (good[:len(good) // 2], encode(frame)[:len(encode(frame)) // 2]):
+        with pytest.raises(NativeError):
+            dec.decode([cut], check=True)
+    frames, which = jpeg.decode_on_gpu([buf.getvalue()], cuda)         # progressive: falls back to nvJPEG
     assert which == "nvjpeg" and frames.shape == (1, 64, 96, 3)
-    frames, which = jpeg.decode_on_gpu([good], cuda)
-    assert which == "aiko"
-    np.testing.assert_array_equal(frames.cpu().numpy()[0], pillow_rgb(good))
+    for blob in (good, encode(frame)):                                 # with and without restart markers
+        frames, which = jpeg.decode_on_gpu([blob], cuda)
+        assert which == "aiko"
+        np.testing.assert_array_equal(frames.cpu().numpy()[0], pillow_rgb(blob))
