@@ -20,6 +20,7 @@
 // Subset: SOF0, 8 bit, one interleaved scan, gray or YCbCr with luma sampling 1x1 / 2x1 / 2x2 and chroma
 // 1x1, a restart interval (the parallel entropy decoder needs one), all images of a call of one geometry.
 // Everything else returns AIKO_B200_ERR_UNSUPPORTED and the caller keeps its other decoder.
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -763,7 +764,10 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const u
     if (active) S.changed[cur][tid] = ch ? 1 : 0;
     const int any = __syncthreads_or(ch ? 1 : 0);
     cur ^= 1;
-    if (!any) break;
+    if (!any) {
+      if (tid == 0) { atomicMax(status + 1, iter); atomicAdd(status + 2, iter); }    // diagnostics: rounds needed
+      break;
+    }
   }
   // ---- block index of every subsequence, then the pass that writes
   {
@@ -1185,6 +1189,13 @@ extern "C" int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host
   AIKO_CUDA(cudaGetLastError());
   const long long items = (long long)((g.W + 7) / 8) * g.H;
   const dim3 colour_grid((unsigned)((items + 255) / 256), (unsigned)n_images);
+  if (getenv("AIKO_B200_JPEG_DEBUG")) {                 // diagnostic: rounds of the state iteration (synchronises)
+    int dbg[4] = {0, 0, 0, 0};
+    AIKO_CUDA(cudaMemcpyAsync(dbg, ws + L.status, sizeof(dbg), cudaMemcpyDeviceToHost, st));
+    AIKO_CUDA(cudaStreamSynchronize(st));
+    fprintf(stderr, "jpeg_decode: status %d, state iteration rounds: max %d, mean %.2f over %d images\n", dbg[0], dbg[1],
+            (double)dbg[2] / n_images, n_images);
+  }
   if (!(stages & 8)) return AIKO_B200_OK;
   if (g.ncomp == 1) jpeg_colour_kernel<0><<<colour_grid, 256, 0, st>>>(d_planes, g, dst, frame_stride);
   else if (g.hmax == 1) jpeg_colour_kernel<1><<<colour_grid, 256, 0, st>>>(d_planes, g, dst, frame_stride);

@@ -82,9 +82,9 @@ def natural_frame(seed, h=SRC_H, w=SRC_W):
     return np.clip(up + rng.normal(0, 4, (h, w, 3)), 0, 255).astype(np.uint8)
 
 
-def jpeg_blob(seed, restart_rows=1):
-    """One 1080p baseline JPEG (quality 90, 4:2:0).  ``restart_rows`` = 1: a restart marker after every MCU row
-    (libjpeg's restart_in_rows, what cameras and MJPEG encoders emit); 0: none (Pillow's default)."""
+def jpeg_blob(seed, restart_rows=0):
+    """One 1080p baseline JPEG (quality 90, 4:2:0) as Pillow writes it by default: no restart markers
+    (``restart_rows`` = 1: one after every MCU row, libjpeg's restart_in_rows)."""
     import io
     from PIL import Image
     buf = io.BytesIO()
@@ -93,9 +93,9 @@ def jpeg_blob(seed, restart_rows=1):
     return buf.getvalue()
 
 
-JPEG_WORKLOAD = ("config1: JPEG bytes in host memory (1080p, quality 90, 4:2:0, a restart marker per MCU row) -> decode -> "
-                 "ImageResize PIL branch (antialiased bicubic 1920x1080->640x480) -> RGB frames in host memory, "
-                 "32-frame batches")
+JPEG_WORKLOAD = ("config1: JPEG bytes in host memory (1080p, quality 90, 4:2:0, Pillow's default encoder settings: no "
+                 "restart markers) -> decode -> ImageResize PIL branch (antialiased bicubic 1920x1080->640x480) -> RGB "
+                 "frames in host memory, 32-frame batches")
 JPEG_LANES = int(os.environ.get("AIKO_BENCH_JPEG_LANES", "8"))
 
 
@@ -655,10 +655,10 @@ def run_gpu_arm(args):
 
     # ---- end to end from JPEG bytes (BASELINE config 1): the frames are born on the device.  32 JPEG
     # blobs per step in page-locked host memory -> this library's decoder (csrc/jpeg_decode.cu: entropy decode
-    # one thread per restart segment, IDCT, upsampling, colour conversion; pixels bit-identical to Pillow's)
-    # -> antialiased bicubic resize (the reference's PIL branch) -> D2H of the 640x480 frames.  One batch
-    # keeps only ~68 warps busy in the entropy kernel, so JPEG_LANES batches are in flight on separate CUDA
-    # streams.  Files without restart markers take nvJPEG (second measurement, 2 lanes).
+    # one thread per subsequence of the scan, IDCT, upsampling, colour conversion; pixels bit-identical to
+    # Pillow's) -> antialiased bicubic resize (the reference's PIL branch) -> D2H of the 640x480 frames.  The
+    # entropy kernel runs one CTA per image (32 of the 148 SMs per batch), so JPEG_LANES batches are in flight on
+    # separate CUDA streams.
     jpeg_result = None
     try:
         from aiko_services_b200 import jpeg
@@ -711,16 +711,6 @@ def run_gpu_arm(args):
         jpeg_result = {"seconds": jpeg_s, "frames": BATCH * n_jpeg, "steps": n_jpeg, "lanes": JPEG_LANES,
                        "h2d": sum(len(b) for b in blobs), "checksum": int(lanes[0]["host"][0, 0, 0, 0])}
         del lanes
-        torch.cuda.empty_cache()
-        try:
-            plain = [jpeg_blob(JPEG_SEED + 100 * rank + k, restart_rows=0) for k in range(BATCH)]
-            n_plain = max(4, min(args.steps, 40))
-            plain_s, lanes = jpeg_leg([pin(b) for b in plain], lambda: jpeg.JpegDecoder(device, BATCH), 2, n_plain)
-            jpeg_result.update({"plain_seconds": plain_s, "plain_frames": BATCH * n_plain,
-                                "plain_h2d": sum(len(b) for b in plain), "hardware": lanes[0]["decoder"].hardware})
-            del lanes
-        except Exception as error:   # nvJPEG is optional (libaiko_b200_jpeg.so)
-            jpeg_result["plain_error"] = repr(error)
     except Exception as error:      # the headline does not depend on the JPEG leg
         jpeg_result = {"error": repr(error)}
 
@@ -733,9 +723,6 @@ def run_gpu_arm(args):
     ok_everywhere = sharding.combine([0.0 if (jpeg_result and "error" not in jpeg_result) else 1.0], [], device=device)[0][0] == 0.0
     if ok_everywhere:
         jpeg_totals = sharding.combine([jpeg_result["seconds"]], [jpeg_result["frames"]], device=device)
-        plain_ok = sharding.combine([0.0 if "plain_seconds" in jpeg_result else 1.0], [], device=device)[0][0] == 0.0
-        plain_totals = sharding.combine([jpeg_result["plain_seconds"]], [jpeg_result["plain_frames"]],
-                                        device=device) if plain_ok else None
     elif jpeg_result is not None and "error" not in jpeg_result:
         jpeg_result = {"error": "JPEG leg failed on another rank"}
 
@@ -809,21 +796,10 @@ def run_gpu_arm(args):
                                 "steps": jpeg_result["steps"], "batches_in_flight": jpeg_result["lanes"],
                                 "h2d_bytes_per_step": jpeg_result["h2d"], "d2h_bytes_per_step": d2h,
                                 "decoder": "this library's kernels (csrc/jpeg_decode.cu): jpeg_segments_kernel, "
-                                           "jpeg_huffman_kernel (one thread per restart segment), jpeg_idct_kernel, "
-                                           "jpeg_colour_kernel; resize = bicubic_mma_kernel",
-                                "note": "decoded pixels are bit-identical to Pillow's decoder (tests/test_gpu_jpeg.py); "
-                                        "the parallel entropy decoder needs restart markers"}
-            if plain_totals is not None:
-                (plain_s,), (plain_frames,) = plain_totals
-                line["e2e_jpeg"]["without_restart_markers"] = {
-                    "value": plain_frames / plain_s, "unit": "frames/s", "h2d_bytes_per_step": jpeg_result["plain_h2d"],
-                    "decoder": "nvJPEG, NVJPG hardware engines" if jpeg_result["hardware"]
-                    else "nvJPEG hybrid (hardware backend not offered by this driver): entropy decode on the host "
-                         "cores, IDCT / upsampling / colour conversion on the GPU",
-                    "note": "library code; pixels differ from Pillow's decoder within the tolerance of "
-                            "tests/test_gpu_jpeg.py"}
-            elif "plain_error" in jpeg_result:
-                line["e2e_jpeg"]["without_restart_markers"] = {"unavailable": jpeg_result["plain_error"]}
+                                           "jpeg_sync_huffman_kernel (one thread per 448-byte subsequence of the scan, "
+                                           "boundary states by iteration), jpeg_idct_kernel, jpeg_colour_kernel; "
+                                           "resize = bicubic_mma_kernel",
+                                "note": "decoded pixels are bit-identical to Pillow's decoder (tests/test_gpu_jpeg.py)"}
         elif jpeg_result is not None:
             line["e2e_jpeg"] = {"unavailable": jpeg_result["error"]}
         if world == 1 and not args.no_cpu_baseline:
