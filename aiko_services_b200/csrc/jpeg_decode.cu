@@ -9,16 +9,19 @@
 //             interval, where the entropy-coded scan starts); build 9-bit look-up tables for the Huffman
 //             codes; ship tables + compressed bytes (a few hundred KB per 1080p frame instead of 6.2 MB
 //             of pixels) with one copy.
-//   kernel 1: jpeg_segments_kernel -- find the restart markers of every scan (one CTA per image).
-//   kernel 2: jpeg_huffman_kernel  -- entropy decoding, ONE THREAD PER RESTART SEGMENT: a restart marker
-//             resets the DC predictors and byte-aligns the stream, so the segments of an image (one per
-//             MCU row for typical encoders) decode independently; quantised coefficients go to HBM.
+//   kernel 1: jpeg_unstuff_kernel  -- the scan without stuffed zeros and markers ("clean" stream) + where every
+//             restart segment starts in it (one CTA per image).
+//   kernel 2: entropy decoding into quantised coefficients in HBM.  jpeg_sync_huffman_kernel: one CTA per image,
+//             ONE THREAD PER SUBSEQUENCE of the stream; the decoder state at the subsequence boundaries is found
+//             by iteration (Huffman streams re-synchronise), so files WITHOUT restart markers decode in
+//             parallel too.  jpeg_huffman_kernel (images with more than 512 restart segments): one thread per
+//             segment -- a restart marker resets the DC predictors and byte-aligns the stream.
 //   kernel 3: jpeg_idct_kernel     -- dequantise + islow IDCT, one thread per 8x8 block, into planes.
 //   kernel 4: jpeg_colour_kernel   -- fancy upsampling of the chroma planes + YCbCr -> RGB, interleaved
 //             uint8 RGB frames: the layout np.asarray(PIL image) has.
 //
 // Subset: SOF0, 8 bit, one interleaved scan, gray or YCbCr with luma sampling 1x1 / 2x1 / 2x2 and chroma
-// 1x1, a restart interval (the parallel entropy decoder needs one), all images of a call of one geometry.
+// 1x1, with or without restart markers, all images of a call of one geometry.
 // Everything else returns AIKO_B200_ERR_UNSUPPORTED and the caller keeps its other decoder.
 #include <stdio.h>
 #include <stdlib.h>
@@ -215,144 +218,210 @@ static int make_geometry(const ParsedImage& im, JpegGeometry* g) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// kernel 1: where the restart segments of each scan begin (inside entropy-coded data FF is always followed by
-// 00, so FF D0..D7 can only be a restart marker).
+// kernel 1: the scan as a clean bit stream.  Inside entropy-coded data a byte FF is always followed by a stuffed
+// 00, so FF + non-zero can only be a marker (RSTn between restart segments, EOI at the end).  One CTA per image
+// copies the scan without stuffed zeros and markers ("clean" bytes: segments end on byte boundaries, so they
+// simply follow each other) and records where every restart segment begins in it.  A warp owns a contiguous run
+// of 16-byte vectors (lanes interleaved, so loads coalesce); pass 1 counts, pass 2 writes.
 constexpr int kSegThreads = 1024;
 
-// bit p set: a restart marker (FF D0..D7) starts at byte 16 * v + p of the scan
-__device__ __forceinline__ unsigned restart_marks(const uint8_t* __restrict__ data, int v, int bytes) {
+struct ByteClasses {
+  unsigned data;         // bit p: byte 16 v + p is entropy-coded data
+  unsigned rst_end;      // bit p: a restart marker ends with byte 16 v + p
+};
+
+__device__ __forceinline__ ByteClasses classify16(const uint8_t* __restrict__ data, int v, int bytes, uint4* vec) {
   const uint4 q = __ldg(reinterpret_cast<const uint4*>(data) + v);
+  *vec = q;
   const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+  const int at = 16 * v;
+  const unsigned valid = at + 16 <= bytes ? 0xffffu : (1u << (bytes - at)) - 1u;
   unsigned any_ff = 0;
 #pragma unroll
   for (int k = 0; k < 4; k++) any_ff |= (~w[k] - 0x01010101u) & w[k] & 0x80808080u;   // exact for "no FF byte at all"
-  if (any_ff == 0) return 0;
-  const int at = 16 * v;
-  const unsigned after = at + 16 < bytes ? (unsigned)__ldg(data + at + 16) : 0u;
-  unsigned m = 0;
+  const unsigned before = at > 0 ? (unsigned)__ldg(data + at - 1) : 0u;
+  ByteClasses c;
+  if (any_ff == 0 && before != 0xffu) {
+    c.data = valid;
+    c.rst_end = 0;
+    return c;
+  }
+  const unsigned after = at + 16 < bytes ? (unsigned)__ldg(data + at + 16) : 0xd9u;
+  unsigned d = 0, r = 0, prev = before;
 #pragma unroll
   for (int p = 0; p < 16; p++) {
     const unsigned b = (w[p >> 2] >> (8 * (p & 3))) & 0xffu;
     const unsigned n = p < 15 ? (w[(p + 1) >> 2] >> (8 * ((p + 1) & 3))) & 0xffu : after;
-    if (b == 0xffu && (n & 0xf8u) == 0xd0u && at + p + 1 < bytes) m |= 1u << p;
+    const bool stuffed = b == 0u && prev == 0xffu;
+    const bool marker = (b == 0xffu && n != 0u) || (prev == 0xffu && b != 0u);
+    if (!stuffed && !marker) d |= 1u << p;
+    if (prev == 0xffu && (b & 0xf8u) == 0xd0u) r |= 1u << p;
+    prev = b;
   }
-  return m;
+  c.data = d & valid;
+  c.rst_end = r & valid;
+  return c;
 }
 
-// kernel 1: one CTA per image finds the restart markers of the scan.  A warp owns a contiguous run of 16-byte
-// vectors (lanes interleaved, so loads coalesce); pass 1 counts, pass 2 writes the byte offset after each marker.
-__global__ void __launch_bounds__(kSegThreads) jpeg_segments_kernel(const uint8_t* __restrict__ compressed,
-                                                                    const JpegImage* __restrict__ images,
-                                                                    uint32_t* __restrict__ seg_offsets, int seg_pitch,
-                                                                    int* __restrict__ status) {
-  __shared__ int warp_count[kSegThreads / 32];
+__global__ void __launch_bounds__(kSegThreads) jpeg_unstuff_kernel(const uint8_t* __restrict__ compressed,
+                                                                   const JpegImage* __restrict__ images,
+                                                                   uint8_t* __restrict__ clean_all,
+                                                                   uint32_t* __restrict__ seg_offsets, int seg_pitch,
+                                                                   int* __restrict__ status) {
+  __shared__ int warp_data[kSegThreads / 32], warp_rst[kSegThreads / 32];
   const JpegImage im = images[blockIdx.x];
   const uint8_t* data = compressed + im.scan_offset;      // 16-byte aligned, padded to a multiple of 16
+  uint8_t* clean = clean_all + im.scan_offset;
   const int bytes = (int)im.scan_bytes;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int vecs = (bytes + 15) >> 4;
   const int per_warp = (vecs + kSegThreads / 32 - 1) / (kSegThreads / 32);
   const int v_lo = min(warp * per_warp, vecs), v_hi = min(v_lo + per_warp, vecs);
-  int count = 0;
-  for (int v = v_lo + lane; v < v_hi; v += 32) count += __popc(restart_marks(data, v, bytes));
+  int n_data = 0, n_rst = 0;
+  uint4 vec;
+  for (int v = v_lo + lane; v < v_hi; v += 32) {
+    const ByteClasses c = classify16(data, v, bytes, &vec);
+    n_data += __popc(c.data);
+    n_rst += __popc(c.rst_end);
+  }
 #pragma unroll
-  for (int d = 16; d > 0; d >>= 1) count += __shfl_xor_sync(0xffffffffu, count, d);
-  if (lane == 0) warp_count[warp] = count;
+  for (int d = 16; d > 0; d >>= 1) {
+    n_data += __shfl_xor_sync(0xffffffffu, n_data, d);
+    n_rst += __shfl_xor_sync(0xffffffffu, n_rst, d);
+  }
+  if (lane == 0) { warp_data[warp] = n_data; warp_rst[warp] = n_rst; }
   __syncthreads();
-  int before = 0, total = 0;
+  int data_before = 0, data_total = 0, rst_before = 0, rst_total = 0;
   for (int w = 0; w < kSegThreads / 32; w++) {
-    const int c = warp_count[w];
-    before += w < warp ? c : 0;
-    total += c;
+    const int a = warp_data[w], b = warp_rst[w];
+    data_before += w < warp ? a : 0;
+    data_total += a;
+    rst_before += w < warp ? b : 0;
+    rst_total += b;
   }
   uint32_t* out = seg_offsets + (size_t)blockIdx.x * seg_pitch;
   if (threadIdx.x == 0) {
     out[0] = 0;
-    if (total != im.n_segments - 1) atomicExch(status, 1 + (int)blockIdx.x);   // markers do not match the restart interval
-    for (int k = total + 1; k < im.n_segments; k++) out[k] = (uint32_t)bytes;   // (corrupt stream) such segments decode nothing
+    out[im.n_segments] = (uint32_t)data_total;            // end of the last segment
+    if (rst_total != im.n_segments - 1) atomicExch(status, 1 + (int)blockIdx.x);   // markers do not match the restart interval
+    for (int k = rst_total + 1; k < im.n_segments; k++) out[k] = (uint32_t)data_total;   // (corrupt) empty segments
   }
-  if (count == 0) return;                                  // (warp-uniform)
-  int running = before;
+  int run_data = data_before, run_rst = rst_before;
   for (int v0 = v_lo; v0 < v_hi; v0 += 32) {
     const int v = v0 + lane;
-    unsigned m = v < v_hi ? restart_marks(data, v, bytes) : 0u;
-    if (__ballot_sync(0xffffffffu, m != 0) == 0) continue;
-    const int c = __popc(m);
-    int incl = c;
+    ByteClasses c;
+    c.data = 0; c.rst_end = 0;
+    if (v < v_hi) c = classify16(data, v, bytes, &vec);
+    const int cd = __popc(c.data);
+    int incl = cd;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const int t = __shfl_up_sync(0xffffffffu, incl, d);
       if (lane >= d) incl += t;
     }
-    int at = running + incl - c;
-    while (m) {
-      const int p = __ffs(m) - 1;
-      m &= m - 1;
-      at++;
-      if (at < im.n_segments) out[at] = (uint32_t)(16 * v + p + 2);
+    int at = run_data + incl - cd;
+    run_data += __shfl_sync(0xffffffffu, incl, 31);
+    const uint32_t w[4] = {vec.x, vec.y, vec.z, vec.w};
+    if (c.data == 0xffffu) {
+#pragma unroll
+      for (int p = 0; p < 16; p++) clean[at + p] = (uint8_t)(w[p >> 2] >> (8 * (p & 3)));
+    } else {
+      unsigned m = c.data;
+      int o = at;
+      while (m) {
+        const int p = __ffs(m) - 1;
+        m &= m - 1;
+        clean[o++] = (uint8_t)(w[p >> 2] >> (8 * (p & 3)));
+      }
     }
-    running += __shfl_sync(0xffffffffu, incl, 31);
+    if (__ballot_sync(0xffffffffu, c.rst_end != 0) != 0) {
+      const int cr = __popc(c.rst_end);
+      int incl_r = cr;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl_r, d);
+        if (lane >= d) incl_r += t;
+      }
+      int k = run_rst + incl_r - cr;
+      run_rst += __shfl_sync(0xffffffffu, incl_r, 31);
+      unsigned m = c.rst_end;
+      while (m) {
+        const int p = __ffs(m) - 1;
+        m &= m - 1;
+        k++;
+        if (k < im.n_segments) out[k] = (uint32_t)(at + __popc(c.data & ((1u << p) - 1u)));
+      }
+    }
   }
 }
 
 // ---------------------------------------------------------------------------------------------
-// kernel 2: Huffman decoding (jdhuff.c), one thread per restart segment.
-struct BitReader {
-  const uint8_t* p;
-  const uint8_t* end;
-  unsigned long long acc;
-  int n;
+// Reading the clean stream: 64-bit accumulator, refilled with aligned big-endian 32-bit words.
+struct CleanReader {
+  const uint32_t* words;         // the image's clean stream (16-byte aligned)
+  int wi;                        // next word to load
+  unsigned long long acc;        // head bit = bit 63
+  int n;                         // valid bits in acc (after a refill: 33..64)
 };
 
-__device__ __forceinline__ void refill(BitReader& b) {
-  while (b.n <= 56) {
-    unsigned byte = 0;
-    if (b.p < b.end) {
-      byte = *b.p;
-      if (byte == 0xffu) {
-        const unsigned next = (b.p + 1 < b.end) ? b.p[1] : 0xd9u;
-        if (next == 0u) b.p += 2;          // a stuffed zero follows a data FF
-        else { byte = 0; b.end = b.p; }     // a marker: the segment ends here, feed zeros
-      } else {
-        b.p++;
-      }
-    }
-    b.acc |= (unsigned long long)byte << (56 - b.n);
-    b.n += 8;
+__device__ __forceinline__ uint32_t be32(uint32_t x) { return __byte_perm(x, 0, 0x0123); }
+
+__device__ __forceinline__ void reader_init(CleanReader& r, const uint32_t* words, uint32_t bit) {
+  r.words = words;
+  const int w = (int)(bit >> 5), drop = (int)(bit & 31u);
+  r.acc = (((unsigned long long)be32(__ldg(words + w)) << 32) | be32(__ldg(words + w + 1))) << drop;
+  r.n = 64 - drop;
+  r.wi = w + 2;
+}
+
+__device__ __forceinline__ void reader_refill(CleanReader& r) {
+  if (r.n <= 32) {
+    r.acc |= (unsigned long long)be32(__ldg(r.words + r.wi)) << (32 - r.n);
+    r.wi++;
+    r.n += 32;
   }
 }
 
-__device__ __forceinline__ int take_bits(BitReader& b, int s) {      // 1 <= s <= 16
-  const int v = (int)(b.acc >> (64 - s));
-  b.acc <<= s;
-  b.n -= s;
-  return v;
-}
+__device__ __forceinline__ uint32_t reader_position(const CleanReader& r) { return 32u * (uint32_t)r.wi - (uint32_t)r.n; }
 
-__device__ __forceinline__ int decode_symbol(BitReader& b, const HuffDev& h) {
-  const unsigned e = h.lut[(unsigned)(b.acc >> (64 - kLutBits))];
+// The Huffman code at the head of the stream (at least 16 valid bits): -> symbol, *len = its length; -1 = no such code.
+__device__ __forceinline__ int peek_symbol(const CleanReader& r, const HuffDev& h, int* len) {
+  const uint32_t hi = (uint32_t)(r.acc >> 32);
+  const unsigned e = h.lut[hi >> (32 - kLutBits)];
   if (e) {
-    const int len = (int)(e >> 8);
-    b.acc <<= len;
-    b.n -= len;
+    *len = (int)(e >> 8);
     return (int)(e & 0xffu);
   }
-  for (int len = kLutBits + 1; len <= 16; len++) {
-    const int code = (int)(b.acc >> (64 - len));
-    if (code <= h.maxcode[len]) {
-      b.acc <<= len;
-      b.n -= len;
-      return h.vals[(h.valptr[len] + code - h.mincode[len]) & 255];
+  for (int l = kLutBits + 1; l <= 16; l++) {
+    const int code = (int)(hi >> (32 - l));
+    if (code <= h.maxcode[l]) {
+      *len = l;
+      return h.vals[(h.valptr[l] + code - h.mincode[l]) & 255];
     }
   }
+  *len = 1;
   return -1;
 }
 
-__device__ __forceinline__ int extend_sign(int v, int s) { return v < (1 << (s - 1)) ? v - (1 << s) + 1 : v; }
+// Consumes a code of `len` bits and the `size` magnitude bits that follow it (len + size <= 31, all within the
+// top 32 bits of the accumulator).  -> the magnitude, sign-extended as jdhuff.c's HUFF_EXTEND does (0 for size 0).
+__device__ __forceinline__ int take_code_and_value(CleanReader& r, int len, int size) {
+  const uint32_t hi = (uint32_t)(r.acc >> 32);
+  int v = 0;
+  if (size) {
+    v = (int)((hi << len) >> (32 - size));
+    v = v < (1 << (size - 1)) ? v - (1 << size) + 1 : v;
+  }
+  r.acc <<= (len + size);
+  r.n -= len + size;
+  return v;
+}
 
+// ---------------------------------------------------------------------------------------------
+// kernel 2: Huffman decoding (jdhuff.c) of images with many restart segments, one thread per segment.
 constexpr int kHuffThreads = 64;
 
-__global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_t* __restrict__ compressed,
+__global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_t* __restrict__ clean_all,
                                                                     const JpegImage* __restrict__ images,
                                                                     const JpegTables* __restrict__ tables,
                                                                     const uint32_t* __restrict__ seg_offsets,
@@ -398,17 +467,13 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
     return;
   }
   const uint32_t* offs = seg_offsets + (size_t)blockIdx.y * seg_pitch;
-  const uint8_t* base = compressed + im.scan_offset;
-  BitReader b;
-  b.p = base + offs[seg];
-  b.end = base + ((seg + 1 < im.n_segments) ? offs[seg + 1] : im.scan_bytes);
-  b.acc = 0;
-  b.n = 0;
+  CleanReader r;
+  reader_init(r, reinterpret_cast<const uint32_t*>(clean_all + im.scan_offset), 8u * offs[seg]);
   int16_t* image_coef = coef + (size_t)blockIdx.y * g.coef_per_image;
   const int total_mcus = g.mcux * g.mcuy;
   const int first = seg * im.restart_interval, last = min(first + im.restart_interval, total_mcus);
   int pred[3] = {0, 0, 0};
-  bool bad = false;
+  int bad = 0;
   for (int m = first; m < last && !bad; m++) {
     const int my = m / g.mcux, mx = m - my * g.mcux;
 #pragma unroll 1
@@ -420,21 +485,23 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
       for (int q = 0; q < nblocks; q++) {
         const int by = q / g.h[c], bx = q - by * g.h[c];
         int16_t* blk = image_coef + g.coef_offset[c] + ((size_t)(my * g.v[c] + by) * g.bw[c] + (mx * g.h[c] + bx)) * 64;
-        if (b.n < 32) refill(b);
-        int s = decode_symbol(b, hd);
-        if (s < 0 || s > 15) { bad = true; break; }
-        if (s) pred[c] += extend_sign(take_bits(b, s), s);
+        reader_refill(r);
+        int len;
+        const int s = peek_symbol(r, hd, &len);
+        if (s < 0 || s > 15) { bad = 2000; break; }
+        pred[c] += take_code_and_value(r, len, s);
         if (pred[c]) blk[0] = (int16_t)pred[c];
         for (int k = 1; k < 64; k++) {
-          if (b.n < 32) refill(b);
-          const int rs = decode_symbol(b, ha);
-          if (rs < 0) { bad = true; break; }
-          const int r = rs >> 4, sz = rs & 15;
-          if (sz) {
-            k += r;
-            if (k > 63) { bad = true; break; }
-            blk[s_zigzag[k]] = (int16_t)extend_sign(take_bits(b, sz), sz);
-          } else if (r == 15) {
+          reader_refill(r);
+          const int rs = peek_symbol(r, ha, &len);
+          if (rs < 0) { bad = 2000; break; }
+          const int run = rs >> 4, size = rs & 15;
+          const int v = take_code_and_value(r, len, size);
+          if (size) {
+            k += run;
+            if (k > 63) { bad = 3000; break; }
+            blk[s_zigzag[k]] = (int16_t)v;
+          } else if (run == 15) {
             k += 15;
           } else {
             break;
@@ -445,23 +512,23 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
       if (bad) break;
     }
   }
-  if (bad) atomicExch(status, 2000 + (int)blockIdx.y);
+  if (!bad && reader_position(r) > 8u * offs[seg + 1]) bad = 4000;      // read past the segment's data
+  if (bad) atomicExch(status, bad + (int)blockIdx.y);
 }
 
 // ---------------------------------------------------------------------------------------------
 // kernel 2b: Huffman decoding of scans with few (or no) restart markers: one CTA per image, one thread per
-// SUBSEQUENCE of the scan (a run of B bytes inside one restart segment; B is chosen so that the image has at most
-// 1024 of them).  A thread that does not start a segment does not know where a codeword begins, which block
-// coefficient comes next or which component it belongs to, so the decoder state (bit position u, zigzag index
-// z, block-in-MCU c) at every subsequence boundary is found by iteration (self-synchronising Huffman decoding,
-// Klein & Wiseman 2003; on GPUs: Weissenberger & Schmidt 2018 / 2021): every thread first decodes its
+// SUBSEQUENCE of the clean stream (a run of B bytes inside one restart segment; B is chosen so that the image has
+// at most 1024 of them).  A thread that does not start a segment does not know where a codeword begins, which
+// block coefficient comes next or which component it belongs to, so the decoder state (bit position u, zigzag
+// index z, block-in-MCU c) at every subsequence boundary is found by iteration (self-synchronising Huffman
+// decoding, Klein & Wiseman 2003; on GPUs: Weissenberger & Schmidt 2018 / 2021): every thread first decodes its
 // subsequence from a guessed state, then again from the exit state of its predecessor, until no exit state
 // changes -- Huffman streams re-synchronise within a few dozen symbols, so two rounds settle almost every
 // boundary, and the loop is exact in any case (the first thread of a segment starts from the true state, and
 // each round extends the settled prefix).  Then the blocks completed per subsequence are prefix-summed into
 // block indices, a last pass writes the coefficients (DC as differences), and the DC predictions are resolved
 // with a prefix sum over the per-thread sums of differences.
-// Bit positions are counted in the UNSTUFFED stream (FF 00 -> FF) relative to the segment start.
 constexpr int kSyncThreads = 1024;
 
 struct SyncShared {
@@ -470,11 +537,8 @@ struct SyncShared {
   uint8_t zigzag[64];
   uint8_t comp_of[8], bx_of[8], by_of[8], dc_of[8], ac_of[8];   // per block of an MCU
   uint32_t seg_first[kSyncMaxSegments + 1];   // first subsequence of each segment
-  uint32_t start[kSyncThreads];               // raw byte offset of the subsequence in the scan
-  uint32_t ubits[kSyncThreads];               // unstuffed bit position of its first data byte, relative to its segment
-  uint32_t count[kSyncThreads];               // data bytes, later completed blocks
-  unsigned long long state[kSyncThreads];     // exit state (u << 16 | z << 4 | c)
-  uint16_t seg_of[kSyncThreads];
+  uint32_t count[kSyncThreads];               // scans: completed blocks, sums of DC differences
+  unsigned long long state[kSyncThreads];     // exit state (u << 16 | z << 4 | c), u = bit position in the clean stream
   uint8_t changed[2][kSyncThreads];
   int warp_sums[kSyncThreads / 32];
 };
@@ -500,53 +564,19 @@ __device__ __forceinline__ int block_scan_excl(int v, int* warp_sums, int* total
   return before + incl - v;
 }
 
-struct SpanReader {
-  BitReader b;
-  uint32_t loaded;       // bits fed into the accumulator so far
-  uint32_t base;         // position of the head bit = base + loaded - b.n
-};
-
-__device__ __forceinline__ void span_refill(SpanReader& r) {
-  while (r.b.n <= 56) {
-    unsigned byte = 0;
-    if (r.b.p < r.b.end) {
-      byte = *r.b.p;
-      if (byte == 0xffu) {
-        const unsigned next = (r.b.p + 1 < r.b.end) ? r.b.p[1] : 0xd9u;
-        if (next == 0u) r.b.p += 2;
-        else { byte = 0; r.b.end = r.b.p; }
-      } else {
-        r.b.p++;
-      }
-    }
-    r.b.acc |= (unsigned long long)byte << (56 - r.b.n);
-    r.b.n += 8;
-    r.loaded += 8;
-  }
-}
-
-// Decodes from (u, z, c) until the next codeword starts at or after `limit` (WRITE: or block `g_limit` is
-// reached).  -> exit state; *blocks = blocks completed.  WRITE stores the coefficients of blocks g, g + 1, ...
+// Decodes from the state `entry` until the next codeword starts at or after bit `limit` (WRITE: or block
+// `g_limit` is reached).  -> exit state; *blocks = blocks completed.  WRITE stores the coefficients of blocks
+// gi, gi + 1, ... (DC as the difference to the previous block of the component).
 template <bool WRITE>
-__device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, const JpegImage& im, const JpegGeometry& g,
-                                                         const uint8_t* seg_begin, const uint8_t* start,
-                                                         const uint8_t* seg_end, uint32_t ubits, uint32_t limit,
+__device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, const JpegGeometry& g,
+                                                         const uint32_t* words, uint32_t limit,
                                                          unsigned long long entry, int* blocks, int16_t* image_coef,
                                                          int bpm, int gi, int g_limit, int dsum[3], int* dc_first,
                                                          int* dc_count, int* bad) {
   uint32_t u = (uint32_t)(entry >> 16);
   int z = (int)((entry >> 4) & 63u), c = (int)(entry & 15u);
-  SpanReader r;
-  r.b.p = start; r.b.end = seg_end; r.b.acc = 0; r.b.n = 0; r.loaded = 0;
-  if (start > seg_begin && start < seg_end && start[-1] == 0xffu && start[0] == 0u) r.b.p++;   // a stuffed zero
-  uint32_t skip = u - ubits;
-  span_refill(r);
-  while (skip) {
-    const uint32_t t = skip < 32u ? skip : 32u;
-    r.b.acc <<= t; r.b.n -= (int)t; skip -= t;
-    span_refill(r);
-  }
-  r.base = u - (r.loaded - (uint32_t)r.b.n);
+  CleanReader r;
+  reader_init(r, words, u);
   int done = 0;
   int16_t* blk = nullptr;
   int mx = 0, my = 0;
@@ -562,21 +592,21 @@ __device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, c
   };
   if (WRITE && gi < g_limit) blk = block_ptr(c);
   for (;;) {
-    if (r.b.n < 32) span_refill(r);
-    u = r.base + r.loaded - (uint32_t)r.b.n;
+    reader_refill(r);
+    u = reader_position(r);
     if (u >= limit) break;
     if (WRITE && gi >= g_limit) break;
-    const int comp = S.comp_of[c];
     const HuffDev& h = z == 0 ? S.dc[S.dc_of[c]] : S.ac[S.ac_of[c]];
-    const int sym = decode_symbol(r.b, h);
+    int len;
+    const int sym = peek_symbol(r, h, &len);
     if (sym < 0) {                           // no such code: only in a wrong state or a corrupt file
-      r.b.acc <<= 1; r.b.n -= 1;
+      r.acc <<= 1; r.n -= 1;
       if (WRITE) *bad = 2000;
       continue;
     }
     const int run = z == 0 ? 0 : sym >> 4, size = z == 0 ? sym : sym & 15;
+    const int v = take_code_and_value(r, len, size);
     if (size) {
-      const int v = extend_sign(take_bits(r.b, size), size);
       const int k = z + run;
       if (k > 63) {
         if (WRITE) *bad = 3000;
@@ -584,6 +614,7 @@ __device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, c
       } else {
         if (WRITE) {
           if (z == 0) {
+            const int comp = S.comp_of[c];
             dsum[0] += comp == 0 ? v : 0; dsum[1] += comp == 1 ? v : 0; dsum[2] += comp == 2 ? v : 0;
             ++*dc_count;
           }
@@ -614,7 +645,7 @@ __device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, c
   return ((unsigned long long)u << 16) | (unsigned long long)((z << 4) | c);
 }
 
-__global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const uint8_t* __restrict__ compressed,
+__global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const uint8_t* __restrict__ clean_all,
                                                                          const JpegImage* __restrict__ images,
                                                                          const JpegTables* __restrict__ tables,
                                                                          const uint32_t* __restrict__ seg_offsets,
@@ -663,19 +694,16 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const u
       for (int i = tid; i < (int)(sizeof(HuffDev) / 4); i += kSyncThreads) dst[i] = __ldg(src + i);
     }
   }
-  // ---- the subsequences: B bytes each, never across a restart marker
+  // ---- the subsequences: B clean bytes each, never across a segment boundary
   const uint32_t* offs = seg_offsets + (size_t)blockIdx.x * seg_pitch;
-  const uint8_t* base = compressed + im.scan_offset;
+  const uint32_t* words = reinterpret_cast<const uint32_t*>(clean_all + im.scan_offset);
   const int n_seg = im.n_segments;
-  const uint32_t scan_bytes = im.scan_bytes;
-  const uint32_t B = max(((scan_bytes + (uint32_t)(kSyncThreads - n_seg) - 1) / (uint32_t)(kSyncThreads - n_seg) + 63u) & ~63u, 64u);
+  const uint32_t clean_bytes = offs[n_seg];
+  const uint32_t B = max(((clean_bytes + (uint32_t)(kSyncThreads - n_seg) - 1) / (uint32_t)(kSyncThreads - n_seg) + 63u) & ~63u, 64u);
   int total;
   {
     int mine = 0;
-    if (tid < n_seg) {
-      const uint32_t lo = offs[tid], hi = tid + 1 < n_seg ? offs[tid + 1] : scan_bytes;
-      mine = (int)((hi - lo + B - 1) / B);
-    }
+    if (tid < n_seg) mine = (int)((offs[tid + 1] - offs[tid] + B - 1) / B);
     const int first = block_scan_excl(mine, S.warp_sums, &total);
     if (tid < n_seg) S.seg_first[tid] = (uint32_t)first;
     if (tid == 0) S.seg_first[n_seg] = (uint32_t)total;
@@ -684,7 +712,7 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const u
   const int n_sub = total;                                  // <= kSyncThreads by the choice of B
   const bool active = tid < n_sub;
   int seg = 0;
-  uint32_t seg_lo = 0, seg_hi = 0, sub_lo = 0, sub_hi = 0;
+  uint32_t first_bit = 0, limit = 0;
   bool first_of_segment = false;
   if (active) {
     int lo = 0, hi = n_seg - 1;                             // last segment whose first subsequence is <= tid
@@ -693,45 +721,13 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const u
       if ((int)S.seg_first[mid] <= tid) lo = mid; else hi = mid - 1;
     }
     seg = lo;
-    seg_lo = offs[seg];
-    seg_hi = seg + 1 < n_seg ? offs[seg + 1] : scan_bytes;
+    const uint32_t seg_lo = offs[seg], seg_hi = offs[seg + 1];
     const uint32_t i = (uint32_t)tid - S.seg_first[seg];
     first_of_segment = i == 0;
-    sub_lo = seg_lo + i * B;
-    sub_hi = min(sub_lo + B, seg_hi);
-    S.start[tid] = sub_lo;
-    S.seg_of[tid] = (uint16_t)seg;
+    const uint32_t sub_lo = seg_lo + i * B;
+    first_bit = 8u * sub_lo;
+    limit = 8u * min(sub_lo + B, seg_hi);
   }
-  // data bytes per subsequence (stuffed zeros and everything from a marker on do not count)
-  int data_bytes = 0;
-  if (active) {
-    uint32_t i = sub_lo;
-    if (sub_lo > seg_lo && base[sub_lo - 1] == 0xffu) {
-      if (base[sub_lo] == 0u) i++;                          // the stuffed zero of the FF before the boundary
-      else i = sub_hi;                                      // the second byte of the marker that ends the segment
-    }
-    while (i < sub_hi) {
-      if (base[i] == 0xffu) {
-        const unsigned next = i + 1 < seg_hi ? base[i + 1] : 0xd9u;
-        if (next != 0u) break;                              // a marker: the segment's data ends here
-        i++;                                                // FF 00 = one data byte
-      }
-      data_bytes++;
-      i++;
-    }
-  }
-  {
-    const int before = block_scan_excl(data_bytes, S.warp_sums, &total);
-    if (active) S.count[tid] = (uint32_t)before;
-  }
-  __syncthreads();
-  uint32_t ubits = 0, limit = 0;
-  if (active) {
-    ubits = 8u * (S.count[tid] - S.count[S.seg_first[seg]]);
-    limit = ubits + 8u * (uint32_t)data_bytes;
-    S.ubits[tid] = ubits;
-  }
-  __syncthreads();
   // ---- the exit state of every subsequence, by iteration
   int16_t* image_coef = coef + (size_t)blockIdx.x * g.coef_per_image;
   int dsum[3] = {0, 0, 0};
@@ -745,7 +741,7 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const u
     if (active) {
       if (iter == 0) {
         need = true;
-        entry = (unsigned long long)ubits << 16;           // guess: a block begins here (exact for a segment's first)
+        entry = (unsigned long long)first_bit << 16;       // guess: a block begins here (exact for a segment's first)
       } else if (!first_of_segment && S.changed[cur ^ 1][tid - 1]) {
         need = true;
         entry = S.state[tid - 1];
@@ -753,8 +749,7 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const u
     }
     unsigned long long exit_state = 0;
     if (need)
-      exit_state = decode_span<false>(S, im, g, base + seg_lo, base + sub_lo, base + seg_hi, ubits, limit, entry, &blocks,
-                                      nullptr, bpm, 0, 0, dsum, &dc_first, &dc_count, &bad);
+      exit_state = decode_span<false>(S, g, words, limit, entry, &blocks, nullptr, bpm, 0, 0, dsum, &dc_first, &dc_count, &bad);
     __syncthreads();
     bool ch = false;
     if (need) {
@@ -772,7 +767,6 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const u
   // ---- block index of every subsequence, then the pass that writes
   {
     const int before = block_scan_excl(active ? blocks : 0, S.warp_sums, &total);
-    __syncthreads();
     if (active) S.count[tid] = (uint32_t)before;
   }
   __syncthreads();
@@ -781,10 +775,9 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_huffman_kernel(const u
     const int interval = im.restart_interval > 0 ? im.restart_interval : total_mcus;
     const int g0 = seg * interval * bpm + (int)(S.count[tid] - S.count[S.seg_first[seg]]);
     const int g_limit = min((seg + 1) * interval, total_mcus) * bpm;
-    const unsigned long long entry = first_of_segment ? 0ull : S.state[tid - 1];
-    const unsigned long long exit_state =
-        decode_span<true>(S, im, g, base + seg_lo, base + sub_lo, base + seg_hi, ubits, limit, entry, &blocks, image_coef, bpm,
-                          g0, g_limit, dsum, &dc_first, &dc_count, &bad);
+    const unsigned long long entry = first_of_segment ? (unsigned long long)first_bit << 16 : S.state[tid - 1];
+    const unsigned long long exit_state = decode_span<true>(S, g, words, limit, entry, &blocks, image_coef, bpm, g0, g_limit,
+                                                            dsum, &dc_first, &dc_count, &bad);
     const bool last_of_segment = tid + 1 == (int)S.seg_first[seg + 1];
     if (last_of_segment && g0 + blocks != g_limit) bad = 4000;        // the segment ended early (or ran over)
     // (cannot happen: the iteration settled; a thread that stopped at the segment's last block skipped the pad bits)
@@ -1020,7 +1013,7 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WorkspaceLayout {
   size_t images, tables, head_bytes;       // uploaded from the staging buffer in one copy
-  size_t seg_offsets, status, compressed, coef, planes, total;
+  size_t seg_offsets, status, compressed, clean, coef, planes, total;
   int seg_pitch;
 };
 
@@ -1034,6 +1027,7 @@ WorkspaceLayout layout_for(int n, const JpegGeometry& g, size_t compressed_capac
   L.seg_offsets = at; at = align_up(at + (size_t)n * L.seg_pitch * sizeof(uint32_t), 256);
   L.status = at; at += 256;
   L.compressed = at; at = align_up(at + compressed_capacity + 16 * (size_t)n + 64, 256);
+  L.clean = at; at = align_up(at + compressed_capacity + 16 * (size_t)n + 64, 256);       // the scans without stuffing and markers
   L.coef = at; at = align_up(at + (size_t)n * g.coef_per_image * sizeof(int16_t), 256);
   L.planes = at; at = align_up(at + (size_t)n * g.plane_per_image, 256);
   L.total = at;
@@ -1173,15 +1167,16 @@ extern "C" int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host
   int16_t* d_coef = reinterpret_cast<int16_t*>(ws + L.coef);
   uint8_t* d_planes = ws + L.planes;
 
-  if (stages & 1) jpeg_segments_kernel<<<(unsigned)n_images, kSegThreads, 0, st>>>(ws + L.compressed, d_images, d_seg, L.seg_pitch, d_status);
+  if (stages & 1)
+    jpeg_unstuff_kernel<<<(unsigned)n_images, kSegThreads, 0, st>>>(ws + L.compressed, d_images, ws + L.clean, d_seg, L.seg_pitch, d_status);
   AIKO_CUDA(cudaGetLastError());
   if ((stages & 2) && any_many)
     jpeg_huffman_kernel<<<dim3((unsigned)((needed_segments + kHuffThreads - 1) / kHuffThreads), (unsigned)n_images),
-                          kHuffThreads, 0, st>>>(ws + L.compressed, d_images, d_tables, d_seg, L.seg_pitch, g, d_coef, d_status);
+                          kHuffThreads, 0, st>>>(ws + L.clean, d_images, d_tables, d_seg, L.seg_pitch, g, d_coef, d_status);
   AIKO_CUDA(cudaGetLastError());
   if ((stages & 2) && any_few)
     jpeg_sync_huffman_kernel<<<(unsigned)n_images, kSyncThreads, sizeof(SyncShared), st>>>(
-        ws + L.compressed, d_images, d_tables, d_seg, L.seg_pitch, g, d_coef, d_status);
+        ws + L.clean, d_images, d_tables, d_seg, L.seg_pitch, g, d_coef, d_status);
   AIKO_CUDA(cudaGetLastError());
   const long long blocks = g.coef_per_image / 64;
   if (stages & 4) jpeg_idct_kernel<<<dim3((unsigned)((blocks + kIdctThreads - 1) / kIdctThreads), (unsigned)n_images), kIdctThreads, 0, st>>>(

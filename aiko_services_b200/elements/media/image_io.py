@@ -182,7 +182,7 @@ class _null:
 def logic_image_read_file(element, stream, paths):
     """ImageReadFile.process_frame (image_io.py:180-191): lazy PIL open, decode deferred into the
     consumer, exactly as the reference -- unless the parameter ``decode`` is "gpu": then baseline
-    colour JPEG files are decoded on the GPU (NVJPG engines / nvJPEG, aiko_services_b200.jpeg) and
+    colour baseline JPEG files are decoded on the GPU (csrc/jpeg_decode.cu through aiko_services_b200.jpeg) and
     handed on as device-resident frames that downstream elements treat as the RGB PIL images the
     reference would have produced (ImageResize takes its PIL branch).  Other files stay lazy PIL."""
     from PIL import Image
@@ -220,13 +220,14 @@ def _read_jpegs_on_gpu(stream, paths, images):
             continue                      # progressive, CMYK, 12-bit, ...: the reference's host path
         if components != 3:
             continue                      # gray JPEGs open as mode L in Pillow: keep the host path
-        groups.setdefault((width, height, hmax, vmax, restart > 0), []).append((k, data))
+        groups.setdefault((width, height, hmax, vmax), []).append((k, data))
     import torch
     for members in groups.values():
         lane = stager.next_lane()
         with torch.cuda.stream(lane):
-            # this library's decoder (bit-identical to Pillow) for files with restart markers, nvJPEG otherwise
-            frames, _ = jpeg.decode_on_gpu([data for _, data in members], stager.device, stream=lane)
+            # this library's decoder (bit-identical to Pillow); a truncated or corrupt file is an error of this
+            # element, as a failing Image.open / load is in the reference, not a frame of garbage
+            frames, _ = jpeg.decode_on_gpu([data for _, data in members], stager.device, stream=lane, check=True)
         batch = DeviceBatch(frames, lane)
         batch.stager = stager
         for image, (k, _) in zip(batch.images(), members):

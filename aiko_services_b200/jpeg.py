@@ -226,11 +226,12 @@ def gpu_decoder_for(device):
     return _gpu_decoders[key]
 
 
-def decode_on_gpu(buffers, device, stream=None):
+def decode_on_gpu(buffers, device, stream=None, check=False):
     """JPEG images of one size -> uint8 [n, h, w, 3] RGB on ``device``: this library's own decoder when the
-    files allow it (bit-identical to Pillow), nvJPEG otherwise.  -> (tensor, "aiko" | "nvjpeg")"""
+    files allow it (baseline; bit-identical to Pillow), nvJPEG otherwise.  ``check`` waits for the result and
+    raises on corrupt entropy-coded data (own decoder).  -> (tensor, "aiko" | "nvjpeg")"""
     try:
-        return gpu_decoder_for(device).decode(buffers, stream=stream), "aiko"
+        return gpu_decoder_for(device).decode(buffers, stream=stream, check=check), "aiko"
     except NativeError as error:
         if error.code != _native.ERR_UNSUPPORTED:
             raise

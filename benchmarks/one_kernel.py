@@ -66,6 +66,22 @@ def make(name, dev):
         src = [torch.randint(0, 256, shape, dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
         out = torch.empty((shape[0], size[1], size[0]) + shape[3:], dtype=torch.uint8, device=dev)
         return lambda i: ops.resize_linear(src[i % rot], size[0], size[1], out=out), shape[0]
+    if name == "norm":                     # BASELINE config 4: 4K -> 224x224 fp32 NCHW, normalised
+        src = [torch.randint(0, 256, (32, 2160, 3840, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(2)]
+        out = torch.empty((32, 3, 224, 224), dtype=torch.float32, device=dev)
+        return lambda i: ops.resize_norm_f32(src[i % 2], 224, 224, (0.485, 0.456, 0.406), (0.229, 0.224, 0.225), out=out), 32
+    if name == "jpeg":                     # 32 x 1080p JPEG files as Pillow writes them (no restart markers)
+        import bench
+        from aiko_services_b200 import jpeg
+        blobs = []
+        for k in range(32):
+            b = bench.jpeg_blob(500 + k)
+            t = torch.empty(len(b), dtype=torch.uint8).pin_memory()
+            t.numpy()[...] = np.frombuffer(b, np.uint8)
+            blobs.append(t)
+        dec = jpeg.GpuJpegDecoder(dev)
+        frames = torch.empty((32, 1080, 1920, 3), dtype=torch.uint8, device=dev)
+        return lambda i: dec.decode(blobs, out=frames), 32
     if name in ("audio", "fft"):
         t = np.arange(16000) / 16000.0
         freqs = np.geomspace(50, 7000, 1024)
