@@ -322,17 +322,11 @@ __global__ void __launch_bounds__(kSegThreads) jpeg_unstuff_kernel(const uint8_t
     int at = run_data + incl - cd;
     run_data += __shfl_sync(0xffffffffu, incl, 31);
     const uint32_t w[4] = {vec.x, vec.y, vec.z, vec.w};
-    if (c.data == 0xffffu) {
+    {
+      int o = at;                                          // (predicated, no divergence: most vectors are all data)
 #pragma unroll
-      for (int p = 0; p < 16; p++) clean[at + p] = (uint8_t)(w[p >> 2] >> (8 * (p & 3)));
-    } else {
-      unsigned m = c.data;
-      int o = at;
-      while (m) {
-        const int p = __ffs(m) - 1;
-        m &= m - 1;
-        clean[o++] = (uint8_t)(w[p >> 2] >> (8 * (p & 3)));
-      }
+      for (int p = 0; p < 16; p++)
+        if ((c.data >> p) & 1u) clean[o++] = (uint8_t)(w[p >> 2] >> (8 * (p & 3)));
     }
     if (__ballot_sync(0xffffffffu, c.rst_end != 0) != 0) {
       const int cr = __popc(c.rst_end);
@@ -569,17 +563,21 @@ __device__ __forceinline__ int block_scan_excl(int v, int* warp_sums, int* total
 // gi, gi + 1, ... (DC as the difference to the previous block of the component).
 template <bool WRITE>
 __device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, const JpegGeometry& g,
-                                                         const uint32_t* words, uint32_t limit,
+                                                         const uint32_t* words_in, uint32_t limit,
                                                          unsigned long long entry, int* blocks, int16_t* image_coef,
                                                          int bpm, int gi, int g_limit, int dsum[3], int* dc_first,
                                                          int* dc_count, int* bad) {
   uint32_t u = (uint32_t)(entry >> 16);
   int z = (int)((entry >> 4) & 63u), c = (int)(entry & 15u);
+  const uint32_t* words = words_in;
+  asm volatile("" : "+l"(words));            // keep the stream's base address in registers across the loop
   CleanReader r;
   reader_init(r, words, u);
   int done = 0;
   int16_t* blk = nullptr;
   int mx = 0, my = 0;
+  const HuffDev* hd = &S.dc[S.dc_of[c]];     // the tables of the block being decoded
+  const HuffDev* ha = &S.ac[S.ac_of[c]];
   if (WRITE) {
     const int m = gi / bpm;
     my = m / g.mcux; mx = m - my * g.mcux;
@@ -596,9 +594,8 @@ __device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, c
     u = reader_position(r);
     if (u >= limit) break;
     if (WRITE && gi >= g_limit) break;
-    const HuffDev& h = z == 0 ? S.dc[S.dc_of[c]] : S.ac[S.ac_of[c]];
     int len;
-    const int sym = peek_symbol(r, h, &len);
+    const int sym = peek_symbol(r, z == 0 ? *hd : *ha, &len);
     if (sym < 0) {                           // no such code: only in a wrong state or a corrupt file
       r.acc <<= 1; r.n -= 1;
       if (WRITE) *bad = 2000;
@@ -635,6 +632,8 @@ __device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, c
         c = 0;
         if (WRITE && ++mx == g.mcux) { mx = 0; my++; }
       }
+      hd = &S.dc[S.dc_of[c]];
+      ha = &S.ac[S.ac_of[c]];
       if (WRITE) {
         gi++;
         if (gi < g_limit) blk = block_ptr(c);
