@@ -369,6 +369,7 @@ def run_gpu_arm(args):
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=device)
 
     atlas = TextAtlas.shared()
@@ -795,7 +796,7 @@ def run_gpu_arm(args):
             line["e2e_jpeg"] = {"value": jpeg_frames / jpeg_s, "unit": "frames/s", "workload": JPEG_WORKLOAD,
                                 "steps": jpeg_result["steps"], "batches_in_flight": jpeg_result["lanes"],
                                 "h2d_bytes_per_step": jpeg_result["h2d"], "d2h_bytes_per_step": d2h,
-                                "decoder": "this library's kernels (csrc/jpeg_decode.cu): jpeg_segments_kernel, "
+                                "decoder": "this library's kernels (csrc/jpeg_decode.cu): jpeg_unstuff_kernel, "
                                            "jpeg_sync_huffman_kernel (one thread per 448-byte subsequence of the scan, "
                                            "boundary states by iteration), jpeg_idct_kernel, jpeg_colour_kernel; "
                                            "resize = bicubic_mma_kernel",
