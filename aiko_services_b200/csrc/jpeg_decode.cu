@@ -143,6 +143,7 @@ static int parse_jpeg(const uint8_t* data, size_t len, ParsedImage* out, bool he
       }
     } else if (m == 0xc4) {
       while (s < e) {
+        if (s + 17 > e) { set_last_error("jpeg: bad DHT"); return AIKO_B200_ERR_INVALID_ARGUMENT; }
         const int tc = s[0] >> 4, th = s[0] & 15;
         int total = 0;
         for (int k = 1; k <= 16; k++) total += s[k];
@@ -154,6 +155,7 @@ static int parse_jpeg(const uint8_t* data, size_t len, ParsedImage* out, bool he
         s += 17 + total;
       }
     } else if (m == 0xc0) {
+      if (seg < 8 || seg < 8 + 3 * s[5]) { set_last_error("jpeg: bad SOF0"); return AIKO_B200_ERR_INVALID_ARGUMENT; }
       if (s[0] != 8) { set_last_error("jpeg: %d-bit samples", s[0]); return AIKO_B200_ERR_UNSUPPORTED; }
       out->H = be16(s + 1); out->W = be16(s + 3); out->ncomp = s[5];
       if ((out->ncomp != 1 && out->ncomp != 3) || out->W <= 0 || out->H <= 0) {
@@ -170,9 +172,10 @@ static int parse_jpeg(const uint8_t* data, size_t len, ParsedImage* out, bool he
       set_last_error("jpeg: not baseline (SOF%d)", m - 0xc0);
       return AIKO_B200_ERR_UNSUPPORTED;
     } else if (m == 0xdd) {
+      if (seg < 4) { set_last_error("jpeg: bad DRI"); return AIKO_B200_ERR_INVALID_ARGUMENT; }
       out->restart = be16(s);
     } else if (m == 0xda) {
-      if (!have_sof || s[0] != out->ncomp) { set_last_error("jpeg: scan does not cover all components"); return AIKO_B200_ERR_UNSUPPORTED; }
+      if (!have_sof || seg < 6 + 2 * out->ncomp || s[0] != out->ncomp) { set_last_error("jpeg: scan does not cover all components"); return AIKO_B200_ERR_UNSUPPORTED; }
       for (int i = 0; i < out->ncomp; i++) {
         if (s[1 + 2 * i] != out->id[i]) { set_last_error("jpeg: component order"); return AIKO_B200_ERR_UNSUPPORTED; }
         out->td[i] = (s[2 + 2 * i] >> 4) & 3; out->ta[i] = s[2 + 2 * i] & 3;
@@ -463,6 +466,7 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
   const uint32_t* offs = seg_offsets + (size_t)blockIdx.y * seg_pitch;
   CleanReader r;
   reader_init(r, reinterpret_cast<const uint32_t*>(clean_all + im.scan_offset), 8u * offs[seg]);
+  const uint32_t end_bit = 8u * offs[seg + 1];
   int16_t* image_coef = coef + (size_t)blockIdx.y * g.coef_per_image;
   const int total_mcus = g.mcux * g.mcuy;
   const int first = seg * im.restart_interval, last = min(first + im.restart_interval, total_mcus);
@@ -480,6 +484,7 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
         const int by = q / g.h[c], bx = q - by * g.h[c];
         int16_t* blk = image_coef + g.coef_offset[c] + ((size_t)(my * g.v[c] + by) * g.bw[c] + (mx * g.h[c] + bx)) * 64;
         reader_refill(r);
+        if (reader_position(r) > end_bit) { bad = 4000; break; }          // (corrupt) ran past the segment's data
         int len;
         const int s = peek_symbol(r, hd, &len);
         if (s < 0 || s > 15) { bad = 2000; break; }
@@ -506,7 +511,7 @@ __global__ void __launch_bounds__(kHuffThreads) jpeg_huffman_kernel(const uint8_
       if (bad) break;
     }
   }
-  if (!bad && reader_position(r) > 8u * offs[seg + 1]) bad = 4000;      // read past the segment's data
+  if (!bad && reader_position(r) > end_bit) bad = 4000;                // read past the segment's data
   if (bad) atomicExch(status, bad + (int)blockIdx.y);
 }
 
@@ -596,7 +601,7 @@ __device__ __forceinline__ unsigned long long decode_span(const SyncShared& S, c
     if (WRITE && gi >= g_limit) break;
     int len;
     const int sym = peek_symbol(r, z == 0 ? *hd : *ha, &len);
-    if (sym < 0) {                           // no such code: only in a wrong state or a corrupt file
+    if (sym < 0 || (z == 0 && sym > 15)) {    // no such code / DC category: only in a wrong state or a corrupt file
       r.acc <<= 1; r.n -= 1;
       if (WRITE) *bad = 2000;
       continue;
@@ -1026,7 +1031,8 @@ WorkspaceLayout layout_for(int n, const JpegGeometry& g, size_t compressed_capac
   L.seg_offsets = at; at = align_up(at + (size_t)n * L.seg_pitch * sizeof(uint32_t), 256);
   L.status = at; at += 256;
   L.compressed = at; at = align_up(at + compressed_capacity + 16 * (size_t)n + 64, 256);
-  L.clean = at; at = align_up(at + compressed_capacity + 16 * (size_t)n + 64, 256);       // the scans without stuffing and markers
+  // the scans without stuffing and markers; a corrupt segment is read up to one block (64 x 31 bits) past its end
+  L.clean = at; at = align_up(at + compressed_capacity + 16 * (size_t)n + 512, 256);
   L.coef = at; at = align_up(at + (size_t)n * g.coef_per_image * sizeof(int16_t), 256);
   L.planes = at; at = align_up(at + (size_t)n * g.plane_per_image, 256);
   L.total = at;

@@ -50,3 +50,36 @@ def test_zero_copy_eligibility_rule():
     assert not ops.reads_source_rows_once((1080, 1918, 3), 640, 480)       # unaligned rows: gathers
     assert not ops.reads_source_rows_once((1080, 1920), 640, 480)          # gray: generic kernel
     assert not ops.reads_source_rows_once((2160, 3840, 3), 224, 224)       # scale x > 4: gathers
+
+
+def test_jpeg_header_parser_survives_hostile_input():
+    """aiko_b200_jpeg_gpu_info_host on damaged and truncated headers: an error code or the header's numbers,
+    never a crash (host code only -- runs without a GPU)."""
+    import ctypes
+    import io
+
+    import numpy as np
+    from PIL import Image
+    from aiko_services_b200 import _native
+    lib = _native.lib()
+    rng = np.random.default_rng(5)
+    frame = rng.integers(0, 256, (40, 56, 3), dtype=np.uint8)
+    blobs = []
+    for kw in ({}, {"restart_marker_rows": 1}, {"progressive": True}, {"subsampling": 0}):
+        buf = io.BytesIO()
+        Image.fromarray(frame, "RGB").save(buf, "JPEG", quality=80, **kw)
+        blobs.append(buf.getvalue())
+    vals = [ctypes.c_int() for _ in range(6)]
+    results = set()
+    for trial in range(3000):
+        blob = bytearray(blobs[trial % len(blobs)])
+        head = min(len(blob), 700)
+        for _ in range(int(rng.integers(1, 8))):
+            blob[int(rng.integers(0, head))] = int(rng.integers(256))
+        if trial % 3 == 0:
+            blob = blob[:int(rng.integers(0, head))]
+        raw = bytes(blob)
+        rc = lib.aiko_b200_jpeg_gpu_info_host(raw, len(raw), *[ctypes.byref(v) for v in vals])
+        results.add(rc)
+        assert rc in (_native.OK, _native.ERR_INVALID_ARGUMENT, _native.ERR_UNSUPPORTED)
+    assert _native.OK in results and _native.ERR_INVALID_ARGUMENT in results

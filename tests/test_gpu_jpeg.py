@@ -1,7 +1,8 @@
-"""GPU: JPEG frames decoded on the device (libaiko_b200_jpeg.so / nvJPEG) against Pillow's decoder.
-Two JPEG decoders never agree bit for bit (IDCT rounding; chroma upsampling for 4:2:0), so the decoded
-pixels are compared within a stated tolerance; everything AFTER the decode is compared bit-exact on
-the same decoded pixels."""
+"""GPU: JPEG frames decoded on the device against Pillow's decoder.
+This library's own decoder (csrc/jpeg_decode.cu) restates libjpeg-turbo's arithmetic and is compared BIT-EXACT.
+The nvJPEG path (libaiko_b200_jpeg.so; progressive files) is another decoder -- two JPEG decoders never agree
+bit for bit (IDCT rounding; chroma upsampling for 4:2:0) -- so there the decoded pixels are compared within a
+stated tolerance, and everything AFTER the decode bit-exact on the same decoded pixels."""
 import io
 
 import numpy as np
@@ -188,3 +189,39 @@ def test_own_decoder_refuses_what_it_cannot_do(cuda):
         frames, which = jpeg.decode_on_gpu([blob], cuda)
         assert which == "aiko"
         np.testing.assert_array_equal(frames.cpu().numpy()[0], pillow_rgb(blob))
+
+
+def test_own_decoder_survives_corrupt_files(cuda):
+    """Random damage to valid files (flipped bytes in tables and scan, truncation, inserted markers): every call
+    returns pixels or a NativeError -- no hang, no crash -- and a valid file decodes bit-exactly afterwards."""
+    from aiko_services_b200 import jpeg
+    from aiko_services_b200._native import NativeError
+    dec = jpeg.GpuJpegDecoder(cuda)
+    rng = np.random.default_rng(77)
+    frame = natural_frame(11, 120, 200)
+    sources = [encode_rst(frame, 85, 2, plain=True), encode_rst(frame, 85, 2), encode_rst(frame, 70, 0, restart_marker_blocks=1),
+               encode_rst(frame, 95, 1, plain=True)]
+    outcomes = {"pixels": 0, "error": 0}
+    for trial in range(160):
+        blob = bytearray(sources[trial % len(sources)])
+        kind = trial % 4
+        if kind == 0:                                   # damage anywhere after SOI (headers, tables, scan)
+            for _ in range(int(rng.integers(1, 6))):
+                blob[int(rng.integers(2, len(blob)))] = int(rng.integers(256))
+        elif kind == 1:                                 # damage inside the scan only
+            for _ in range(int(rng.integers(1, 20))):
+                blob[int(rng.integers(len(blob) // 2, len(blob)))] = int(rng.integers(256))
+        elif kind == 2:                                 # truncation
+            blob = blob[:int(rng.integers(4, len(blob)))]
+        else:                                           # stray markers in the scan
+            at = int(rng.integers(len(blob) // 2, len(blob) - 2))
+            blob[at:at + 2] = bytes([0xff, int(rng.choice([0xd0, 0xd3, 0xd9, 0xc4, 0xff, 0x01]))])
+        try:
+            out = dec.decode([bytes(blob)], check=True)
+            assert out.shape[0] == 1
+            outcomes["pixels"] += 1
+        except NativeError:
+            outcomes["error"] += 1
+    assert outcomes["error"] > 20 and outcomes["pixels"] + outcomes["error"] == 160
+    for blob in sources:
+        np.testing.assert_array_equal(dec.decode([blob], check=True).cpu().numpy()[0], pillow_rgb(blob))
