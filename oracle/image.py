@@ -217,3 +217,23 @@ def jpeg_decode(data):
     if rc != 0:
         raise ValueError(f"jpeg oracle: cannot decode this file (code {rc})")
     return out
+
+
+def jpeg_encode(img, quality=75, subsampling=(2, 2)):
+    """uint8 [H, W, 3] RGB or [H, W] gray -> the bytes PIL.Image.fromarray(img).save(f, "JPEG", quality=...,
+    subsampling=...) writes (libjpeg-turbo defaults: standard Huffman tables, JFIF header).
+    ``subsampling``: luma sampling factors (2, 2) = 4:2:0 (Pillow's default), (2, 1) = 4:2:2, (1, 1) = 4:4:4."""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape[:2]
+    channels = 1 if img.ndim == 2 else img.shape[2]
+    fn = lib().oracle_jpeg_encode
+    fn.restype = ctypes.c_size_t
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                   ctypes.c_void_p, ctypes.c_size_t]
+    cap = h * w * channels * 2 + 4096
+    out = np.empty(cap, np.uint8)
+    n = fn(img.ctypes.data, h, w, channels, int(quality), int(subsampling[0]), int(subsampling[1]), out.ctypes.data, cap)
+    if n > cap:
+        out = np.empty(n, np.uint8)
+        n = fn(img.ctypes.data, h, w, channels, int(quality), int(subsampling[0]), int(subsampling[1]), out.ctypes.data, n)
+    return out[:n].tobytes()

@@ -200,3 +200,35 @@ def test_jpeg_oracle_is_bit_exact_with_pillow():
     Image.fromarray(_natural(rng, 40, 40), "RGB").save(buf, "JPEG", progressive=True)
     with pytest.raises(ValueError):
         O.jpeg_decode(buf.getvalue())                 # progressive: outside the subset, refused
+
+
+def test_jpeg_encode_oracle_writes_pillows_bytes():
+    """oracle/jpeg_encode_oracle.c (restated libjpeg-turbo encoder: colour conversion, downsampling with edge
+    replication and dummy blocks, islow forward DCT, quantisation, Huffman coding, headers) against the bytes
+    Pillow writes -- what ImageWriteFile's image.save produces (R/elements/media/image_io.py:250): every
+    subsampling, qualities 1..100, gray, sizes that are not multiples of the MCU."""
+    import io
+    from PIL import Image
+    rng = np.random.default_rng(21)
+    sizes = [(16, 16), (8, 8), (24, 40), (1, 1), (17, 33), (7, 100), (100, 7), (67, 101), (270, 480), (15, 15), (9, 24),
+             (8, 24), (24, 8), (40, 24)]
+    for h, w in sizes:
+        for kind in ("noise", "natural"):
+            if kind == "noise":
+                a = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+            else:
+                a = _natural(rng, max(h, 2), max(w, 2))[:h, :w]
+            for quality in (75, 90, 30, 100, 1):
+                for sub, factors in ((2, (2, 2)), (1, (2, 1)), (0, (1, 1))):
+                    buf = io.BytesIO()
+                    Image.fromarray(a, "RGB").save(buf, "JPEG", quality=quality, subsampling=sub)
+                    assert O.jpeg_encode(a, quality, factors) == buf.getvalue(), (h, w, kind, quality, sub)
+            gray = np.ascontiguousarray(a[..., 1])
+            buf = io.BytesIO()
+            Image.fromarray(gray, "L").save(buf, "JPEG")
+            assert O.jpeg_encode(gray) == buf.getvalue(), (h, w, kind, "gray")
+    # the default call of the reference: image.save(path) = quality 75, 4:2:0
+    a = _natural(rng, 480, 640)
+    buf = io.BytesIO()
+    Image.fromarray(a, "RGB").save(buf, "JPEG")
+    assert O.jpeg_encode(a) == buf.getvalue()
