@@ -97,6 +97,8 @@ SIGNATURES = {
     "aiko_b200_jpeg_gpu_workspace_bytes": [_i, _i, _i, _i, _i, _i, _sz, _i],
     "aiko_b200_jpeg_gpu_decode_rgb_u8": [_vp, _vp, _i, _vp, _i, _i, _i64, _vp, _sz, _vp, _sz, _sz, _i, _vp],
     "aiko_b200_jpeg_gpu_status": [_vp, _i, _i, _i, _i, _i, _i, _sz, _i, _vp],
+    "aiko_b200_jpeg_gpu_encode_workspace_bytes": [_i, _i, _i, _i, _i, _i, _sz],
+    "aiko_b200_jpeg_gpu_encode_u8": [_vp, _i, _i, _i, _i, _i64, _i, _i, _i, _vp, _sz, _sz, _vp, _sz, _vp, _vp],
     "aiko_b200_overlay_u8": [_vp, _vp, _i, _i, _i, _i, _i64, _i64, _ovp, _vp],
     "aiko_b200_swap_rb_u8": [_vp, _vp, _i64, _vp],
     "aiko_b200_bgr2gray_u8": [_vp, _vp, _i64, _i, _vp],
@@ -108,7 +110,8 @@ SIGNATURES = {
 
 RESTYPES = {"aiko_b200_last_error": ctypes.c_char_p, "aiko_b200_resize_bicubic_workspace_bytes": ctypes.c_size_t,
             "aiko_b200_jpeg_gpu_staging_bytes": ctypes.c_size_t, "aiko_b200_jpeg_gpu_workspace_bytes": ctypes.c_size_t,
-            "aiko_b200_audio_workspace_bytes": ctypes.c_size_t}
+            "aiko_b200_audio_workspace_bytes": ctypes.c_size_t,
+            "aiko_b200_jpeg_gpu_encode_workspace_bytes": ctypes.c_size_t}
 
 _lib = None
 

@@ -216,6 +216,93 @@ class GpuJpegDecoder:
                                                                       capacity, segs, _vp(s.cuda_stream)))
 
 
+class GpuJpegEncoder:
+    """This library's JPEG encoder (csrc/jpeg_encode.cu; include/aiko_b200.h, aiko_b200_jpeg_gpu_encode_*):
+    colour conversion, downsampling, forward DCT, quantisation and Huffman coding on the GPU; the files are
+    byte-identical to what ``PIL.Image.fromarray(frame).save(f, "JPEG", quality=..., subsampling=...)`` writes.
+    One encoder per (GPU, CUDA stream)."""
+
+    SUBSAMPLING = {0: (1, 1), 1: (2, 1), 2: (2, 2), "4:4:4": (1, 1), "4:2:2": (2, 1), "4:2:0": (2, 2)}
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self._buffers = {}        # geometry key -> (workspace, out, sizes, scan_capacity, out_stride)
+        self._room = {}           # geometry key -> scan capacity as a multiple of half the raw frame
+
+    def _key(self, frames, subsampling):
+        gray = frames.dim() == 3
+        hs, vs = subsampling if isinstance(subsampling, tuple) else self.SUBSAMPLING[subsampling]
+        return (frames.shape[0], frames.shape[1], frames.shape[2], 1 if gray else frames.shape[3], hs, vs)
+
+    def encode_async(self, frames, quality=75, subsampling=2, stream=None):
+        """``frames``: uint8 CUDA tensor [n, h, w, 3] (RGB) or [n, h, w] (gray).  Enqueues the encoder on
+        ``stream``; -> (out uint8 [n, out_stride] on the device: file k = out[k, :sizes[k]]; sizes int32 [n] on
+        the device, -1 = did not fit).  Both belong to the encoder and are overwritten by its next call."""
+        if not (isinstance(frames, torch.Tensor) and frames.is_cuda and frames.dtype == torch.uint8 and frames.is_contiguous()):
+            raise RuntimeError("GpuJpegEncoder: frames must be a contiguous uint8 CUDA tensor")
+        key = self._key(frames, subsampling)
+        n, h, w, channels, hs, vs = key
+        if channels not in (1, 3):
+            raise NativeError(_native.ERR_UNSUPPORTED, f"jpeg encode: {channels} channels")
+        lib = _native.lib()
+        entry = self._buffers.get(key)
+        if entry is None:
+            scan_capacity = max(h * w * channels // 2 * self._room.get(key, 1), 4096)
+            out_stride = -(-(scan_capacity + scan_capacity // 16 + 1024) // 16) * 16
+            nbytes = lib.aiko_b200_jpeg_gpu_encode_workspace_bytes(n, w, h, channels, hs, vs, scan_capacity)
+            if nbytes == 0:
+                raise NativeError(_native.ERR_UNSUPPORTED, f"jpeg encode: unsupported layout ({channels} channels, {hs}x{vs})")
+            with torch.cuda.device(self.device):
+                workspace = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+                out = torch.empty((n, out_stride), dtype=torch.uint8, device=self.device)
+                sizes = torch.empty(n, dtype=torch.int32, device=self.device)
+            entry = self._buffers[key] = (workspace, out, sizes, scan_capacity, out_stride)
+        workspace, out, sizes, scan_capacity, out_stride = entry
+        s = stream if stream is not None else torch.cuda.current_stream(self.device)
+        with torch.cuda.device(self.device):
+            _native.check(lib.aiko_b200_jpeg_gpu_encode_u8(
+                frames.data_ptr(), n, h, w, channels, h * w * channels, int(quality), hs, vs, workspace.data_ptr(),
+                workspace.numel(), scan_capacity, out.data_ptr(), out_stride, sizes.data_ptr(), _vp(s.cuda_stream)))
+        return out, sizes
+
+    def encode(self, frames, quality=75, subsampling=2, stream=None):
+        """-> list of ``bytes``, one JPEG file per frame (waits for the result)."""
+        if frames.shape[0] == 0:
+            return []
+        s = stream if stream is not None else torch.cuda.current_stream(self.device)
+        key = self._key(frames, subsampling)
+        while True:
+            out, sizes = self.encode_async(frames, quality, subsampling, stream=s)
+            with torch.cuda.stream(s):
+                host_sizes = sizes.cpu()
+            s.synchronize()
+            lengths = host_sizes.tolist()
+            if min(lengths) >= 0:
+                break
+            # a scan did not fit (noise at high quality): four times the room, up to four raw frames
+            room = self._room.get(key, 1) * 4
+            if room > 16:
+                raise NativeError(_native.ERR_WORKSPACE, "jpeg encode: the compressed data does not fit its buffers")
+            self._room[key] = room
+            del self._buffers[key]
+        longest = max(lengths)
+        with torch.cuda.stream(s):
+            host = out[:, :longest].cpu()
+        s.synchronize()
+        data = host.numpy()
+        return [data[k, :lengths[k]].tobytes() for k in range(len(lengths))]
+
+
+_gpu_encoders = {}
+
+
+def gpu_encoder_for(device):
+    key = str(torch.device(device))
+    if key not in _gpu_encoders:
+        _gpu_encoders[key] = GpuJpegEncoder(device)
+    return _gpu_encoders[key]
+
+
 _gpu_decoders = {}
 
 

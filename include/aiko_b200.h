@@ -314,6 +314,23 @@ int aiko_b200_jpeg_gpu_decode_rgb_u8(const uint8_t* const* jpegs_host, const siz
 int aiko_b200_jpeg_gpu_status(const void* workspace, int n_images, int width, int height, int components, int hmax,
                               int vmax, size_t compressed_capacity, int max_segments, void* stream);
 
+/* ImageWriteFile: image.save(path) for a JPEG path -- R/elements/media/image_io.py:250 -- without the frames
+ * leaving the GPU uncompressed.  Baseline JPEG files byte-identical to what Pillow (libjpeg-turbo, standard Huffman
+ * tables, JFIF 1.01 header) writes for the same pixels: quality as Pillow's `quality` (the reference's default
+ * call: 75), luma sampling hs x vs = 2x2 (4:2:0, Pillow's default for RGB), 2x1 (4:2:2) or 1x1 (4:4:4);
+ * channels 3 = RGB frames, 1 = gray frames (mode L).  src: n_images frames of height x width x channels bytes on
+ * the device.  out (device): n_images slots of out_stride bytes, slot i receives file i; sizes_out (device,
+ * int32 per image): the file's length, or -1 when its scan did not fit scan_capacity bytes or the file did not
+ * fit the slot (call again with more room: a scan never needs more than twice the raw frame).  workspace:
+ * 256-byte aligned, aiko_b200_jpeg_gpu_encode_workspace_bytes for the same arguments (0 = unsupported).
+ * Asynchronous on `stream`. */
+size_t aiko_b200_jpeg_gpu_encode_workspace_bytes(int n_images, int width, int height, int channels, int hs, int vs,
+                                                 size_t scan_capacity);
+int aiko_b200_jpeg_gpu_encode_u8(const uint8_t* src, int n_images, int height, int width, int channels,
+                                 int64_t frame_stride, int quality, int hs, int vs, void* workspace,
+                                 size_t workspace_bytes, size_t scan_capacity, uint8_t* out, size_t out_stride,
+                                 int32_t* sizes_out, void* stream);
+
 /* ---------------------------------------------------------------------- */
 /* Colour conversion / flip / crop call sites.                              */
 

@@ -225,3 +225,49 @@ def test_own_decoder_survives_corrupt_files(cuda):
     assert outcomes["error"] > 20 and outcomes["pixels"] + outcomes["error"] == 160
     for blob in sources:
         np.testing.assert_array_equal(dec.decode([blob], check=True).cpu().numpy()[0], pillow_rgb(blob))
+
+
+# ---- this library's encoder (csrc/jpeg_encode.cu): the bytes Pillow writes ---------------------------------
+def pillow_bytes(frame, **kw):
+    from PIL import Image
+    buf = io.BytesIO()
+    Image.fromarray(frame, "RGB" if frame.ndim == 3 else "L").save(buf, "JPEG", **kw)
+    return buf.getvalue()
+
+
+@pytest.mark.parametrize("subsampling", [2, 1, 0], ids=["420", "422", "444"])
+def test_encoder_writes_pillows_bytes(cuda, subsampling):
+    """GpuJpegEncoder against PIL.Image.save (what ImageWriteFile calls, R/elements/media/image_io.py:250) and
+    against the oracle: identical files for natural frames and noise, any quality, sizes that are not multiples
+    of the MCU (replicated edges, dummy blocks), batches."""
+    from aiko_services_b200 import jpeg
+    enc = jpeg.GpuJpegEncoder(cuda)
+    rng = np.random.default_rng(60 + subsampling)
+    factors = {2: (2, 2), 1: (2, 1), 0: (1, 1)}[subsampling]
+    for h, w in ((480, 640), (16, 16), (8, 8), (1, 1), (17, 33), (7, 100), (100, 7), (67, 101), (9, 24), (24, 8), (270, 480)):
+        frames = np.stack([natural_frame(int(rng.integers(1 << 30)), max(h, 2), max(w, 2))[:h, :w] for _ in range(3)])
+        frames[1] = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        for quality in (75, int(rng.integers(1, 101))):
+            files = enc.encode(torch.from_numpy(frames).to(cuda), quality=quality, subsampling=subsampling)
+            for k in range(3):
+                want = pillow_bytes(frames[k], quality=quality, subsampling=subsampling)
+                assert files[k] == want, f"{w}x{h} image {k} quality {quality}: {len(files[k])} vs {len(want)} bytes"
+                assert files[k] == O.jpeg_encode(frames[k], quality, factors)
+
+
+def test_encoder_defaults_gray_and_round_trip(cuda):
+    from aiko_services_b200 import jpeg
+    enc, dec = jpeg.GpuJpegEncoder(cuda), jpeg.GpuJpegDecoder(cuda)
+    frames = np.stack([natural_frame(70 + k, 1080, 1920) for k in range(2)])        # BASELINE size, Pillow's defaults
+    files = enc.encode(torch.from_numpy(frames).to(cuda))
+    for k in range(2):
+        assert files[k] == pillow_bytes(frames[k])
+    back = dec.decode(files, check=True).cpu().numpy()                               # and back through the decoder
+    for k in range(2):
+        np.testing.assert_array_equal(back[k], pillow_rgb(files[k]))
+    gray = np.ascontiguousarray(frames[:, :203, :301, 1])
+    for k, f in enumerate(enc.encode(torch.from_numpy(gray).to(cuda), quality=90)):
+        assert f == pillow_bytes(gray[k], quality=90)
+    noise = np.random.default_rng(3).integers(0, 256, (1, 256, 256, 3), dtype=np.uint8)     # scan larger than the first buffers
+    assert enc.encode(torch.from_numpy(noise).to(cuda), quality=100, subsampling=0)[0] == pillow_bytes(noise[0], quality=100, subsampling=0)
+    assert enc.encode(torch.empty((0, 8, 8, 3), dtype=torch.uint8, device=cuda)) == []
