@@ -234,14 +234,31 @@ def _read_jpegs_on_gpu(stream, paths, images):
             images[k] = _LazyPil(image, "RGB")
 
 
+_JPEG_SUFFIXES = (".jpg", ".jpeg", ".jpe", ".jfif")
+
+
 def logic_image_write_file(element, stream, images):
-    """ImageWriteFile.process_frame (image_io.py:234-255)."""
+    """ImageWriteFile.process_frame (image_io.py:234-255).  With the parameter ``encode: gpu``, device-resident
+    RGB / gray frames that go to a JPEG path are encoded on the GPU (aiko_services_b200.jpeg.GpuJpegEncoder:
+    the bytes image.save(path) would write) and only the compressed files cross PCIe."""
     from PIL import Image
+    encode, _ = element.get_parameter("encode", default="host")
+    paths = []
     for image in images:
         path = stream.variables["target_path"]
         if contains_all(path, "{}"):
             path = path.format(stream.variables["target_file_id"])
             stream.variables["target_file_id"] += 1
+        paths.append(path)
+    written = set()
+    if str(encode).lower() == "gpu":
+        try:
+            written = _write_jpegs_on_gpu(images, paths)
+        except Exception as exception:
+            return StreamEvent.ERROR, {"diagnostic": f"Error saving image: {exception}"}
+    for k, (image, path) in enumerate(zip(images, paths)):
+        if k in written:
+            continue
         if isinstance(image, DeviceImage):
             image = image.to_pil()
         elif not isinstance(image, Image.Image):
@@ -254,6 +271,36 @@ def logic_image_write_file(element, stream, images):
         except Exception as exception:
             return StreamEvent.ERROR, {"diagnostic": f"Error saving image: {exception}"}
     return StreamEvent.OKAY, {}
+
+
+def _write_jpegs_on_gpu(images, paths):
+    """Encodes the device-resident RGB / L frames whose path is a JPEG path, one batch per DeviceBatch, and
+    writes the files.  -> indices written."""
+    import torch
+    from ... import jpeg
+    groups = {}
+    for k, (image, path) in enumerate(zip(images, paths)):
+        if not isinstance(image, DeviceImage) or not str(path).lower().endswith(_JPEG_SUFFIXES):
+            continue
+        shape = image.shape
+        mode = image.pil_mode or ("L" if len(shape) == 2 else "RGB" if shape[2] == 3 else None)
+        if mode not in ("RGB", "L"):
+            continue
+        groups.setdefault(id(image.batch), (image.batch, []))[1].append((k, image.index))
+    written = set()
+    for batch, members in groups.values():
+        frames = batch.tensor
+        indices = [i for _, i in members]
+        lane = batch.stream if batch.stream is not None else torch.cuda.current_stream(frames.device)
+        with torch.cuda.stream(lane):
+            if indices != list(range(frames.shape[0])):
+                frames = frames.index_select(0, torch.as_tensor(indices, device=frames.device))
+            files = jpeg.gpu_encoder_for(frames.device).encode(frames.contiguous(), stream=lane)
+        for (k, _), data in zip(members, files):
+            with open(paths[k], "wb") as f:
+                f.write(data)
+            written.add(k)
+    return written
 
 
 def _pipeline_stager(pipeline, device_index):

@@ -78,8 +78,7 @@ def test_bad_input_is_an_error_not_a_crash(cuda):
 
 def test_image_read_file_decodes_on_the_gpu(cuda, tmp_path):
     """ImageReadFile(decode=gpu) -> ImageResize -> ImageWriteFile: frames never exist as raw pixels on
-    the host before the resize; the written files match Pillow decode + resize within the decoder
-    tolerance, and a PNG in the same stream still takes the reference's host path."""
+    the host before the resize; the written files hold exactly the pixels of Pillow's decode + resize."""
     from PIL import Image
     from aiko_services_b200.pipeline import Pipeline
     mod = "aiko_services.elements.media.image_io"
@@ -104,7 +103,37 @@ def test_image_read_file_decodes_on_the_gpu(cuda, tmp_path):
         got = np.asarray(Image.open(tmp_path / f"out_{k:02d}.png")).astype(np.int32)
         want = np.asarray(Image.open(tmp_path / f"in_{k:02d}.jpeg").resize((160, 90))).astype(np.int32)
         assert got.shape == (90, 160, 3)
-        assert np.abs(got - want).mean() <= 1.0 and np.abs(got - want).max() <= 12, (k, np.abs(got - want).max())
+        np.testing.assert_array_equal(got, want)
+
+
+def test_jpeg_in_jpeg_out_files_are_the_references_bytes(cuda, tmp_path):
+    """ImageReadFile(decode=gpu) -> ImageResize -> ImageWriteFile(encode=gpu) with JPEG files on both sides: only
+    compressed bytes cross PCIe, and every written FILE is byte-identical to what the reference's chain writes
+    (Image.open(path) -> image.resize((w, h)) -> image.save(path), R/elements/media/image_io.py:184,218,250)."""
+    import io as _io
+    from PIL import Image
+    from aiko_services_b200.pipeline import Pipeline
+    mod = "aiko_services.elements.media.image_io"
+    for k in range(5):
+        (tmp_path / f"in_{k:02d}.jpg").write_bytes(encode(natural_frame(400 + k, 360, 640), 88, 2))
+    d = {"version": 0, "name": "p_jpeg2", "runtime": "python", "graph": ["(ImageReadFile ImageResize ImageWriteFile)"],
+         "parameters": {"resolution": "320x180"},
+         "elements": [
+             {"name": "ImageReadFile", "parameters": {"data_sources": f"(file://{tmp_path}/in_{{}}.jpg)",
+                                                      "data_batch_size": 3, "decode": "gpu"},
+              "input": [{"name": "paths", "type": "[Path]"}], "output": [{"name": "images", "type": "[image]"}],
+              "deploy": {"local": {"module": mod}}},
+             {"name": "ImageResize", "input": [{"name": "images", "type": "[image]"}],
+              "output": [{"name": "images", "type": "[image]"}], "deploy": {"local": {"module": mod}}},
+             {"name": "ImageWriteFile", "parameters": {"data_targets": f"file://{tmp_path}/out_{{:02d}}.jpg", "encode": "gpu"},
+              "input": [{"name": "images", "type": "[image]"}], "output": [], "deploy": {"local": {"module": mod}}}]}
+    p = Pipeline(d)
+    assert p.create_stream("1")
+    p.run()
+    for k in range(5):
+        buf = _io.BytesIO()
+        Image.open(tmp_path / f"in_{k:02d}.jpg").resize((320, 180)).save(buf, "JPEG")
+        assert (tmp_path / f"out_{k:02d}.jpg").read_bytes() == buf.getvalue(), k
 
 
 # ---- this library's own decoder (csrc/jpeg_decode.cu): bit-exact with Pillow ------------------------------
