@@ -4,11 +4,12 @@
 // defaults: quality 75, 4:2:0 for RGB images, standard Huffman tables, JFIF header.  This file restates that
 // pipeline (oracle: oracle/jpeg_encode_oracle.c, itself pinned against the bytes Pillow writes):
 //
-//   kernel 1: jpeg_fdct_kernel    -- one thread per 8x8 block in scan (MCU) order: RGB -> YCbCr (jccolor.c 16-bit
-//             fixed point), h2v1 / h2v2 box downsampling with libjpeg's alternating bias and replicated edges,
-//             level shift, the accurate integer forward DCT (jfdctint.c), quantisation (jcdctmgr.c); coefficients
-//             stored in zigzag order.  Blocks outside the component's real block grid ("dummy" blocks that
-//             complete an MCU) are zero apart from the DC they inherit in kernel 2.
+//   kernel 0: jpeg_planes_kernel  -- RGB -> YCbCr (jccolor.c 16-bit fixed point) and h2v1 / h2v2 box downsampling
+//             with libjpeg's alternating bias and replicated edges, into one plane per component.
+//   kernel 1: jpeg_fdct_kernel    -- one thread per 8x8 block in scan (MCU) order: level shift, the accurate integer
+//             forward DCT (jfdctint.c), quantisation (jcdctmgr.c: rounded division, done with an exact 40-bit
+//             reciprocal); coefficients stored in zigzag order.  Blocks outside the component's real block grid
+//             ("dummy" blocks that complete an MCU) are zero apart from the DC they inherit in kernel 2.
 //   kernel 2: jpeg_entropy_kernel -- one CTA per image, every thread owns a contiguous run of blocks: pass 1 sums
 //             the code lengths of its run (jchuff.c encode_one_block), a block scan turns them into bit offsets,
 //             pass 2 writes the codes at its offset (whole words with plain stores, the two words it shares with
@@ -34,10 +35,13 @@ struct EncGeometry {
   int comp_of[6], bx_of[6], by_of[6];
   int first_q[3];                // first block of the component inside an MCU
   int n_blocks;                  // per image, scan order
+  long long plane_offset[3];     // bytes from the start of an image's plane area; plane c is bh*8 rows of bw*8 bytes
+  long long plane_per_image;
 };
 
 struct EncTables {               // by value as a kernel argument
   uint16_t q8[2][64];            // quantisation divisors (table value * 8), natural order
+  unsigned long long recip[2][64];   // ceil(2^40 / divisor): n / d = (n * recip) >> 40 exactly for n < 2^18
   uint16_t dc_code[2][12];
   uint8_t dc_size[2][12];
   uint16_t ac_code[2][256];
@@ -75,19 +79,60 @@ struct EncHeader {               // by value as a kernel argument
     (d1) = AIKO_FDCT_DESCALE(tmp7 + z1 + z4, SH);                                                      \
   }
 
-constexpr int kFdctThreads = 128;
-
-__device__ __forceinline__ int ycc_sample(const uint8_t* __restrict__ px, int comp, int channels) {
-  if (channels == 1) return px[0];
+// kernel 0: component planes.  One thread per chroma sample position: its Cb and Cr samples and the hs x vs luma
+// samples it covers (gray frames: one thread per sample).  Planes hold the component's real blocks; samples
+// right of / below the image repeat the edge as libjpeg does (expand_right_edge on the source pixels,
+// expand_bottom_edge on the colour rows and on the downsampled rows).
+__device__ __forceinline__ int ycc_sample(const uint8_t* __restrict__ px, int comp) {
   const int r = px[0], g = px[1], b = px[2];
   if (comp == 0) return (19595 * r + 38470 * g + 7471 * b + 32768) >> 16;
   if (comp == 1) return (-11059 * r - 21709 * g + 32768 * b + (128 << 16) + 32767) >> 16;
   return (32768 * r - 27439 * g - 5329 * b + (128 << 16) + 32767) >> 16;
 }
 
-__global__ void __launch_bounds__(kFdctThreads) jpeg_fdct_kernel(const uint8_t* __restrict__ src, long long frame_stride,
-                                                                 int channels, const EncGeometry g, const EncTables t,
-                                                                 int16_t* __restrict__ coef) {
+template <int HS, int VS>
+__global__ void __launch_bounds__(256) jpeg_planes_kernel(const uint8_t* __restrict__ src, long long frame_stride,
+                                                          const EncGeometry g, uint8_t* __restrict__ planes_all) {
+  const uint8_t* frame = src + (size_t)blockIdx.y * frame_stride;
+  uint8_t* planes = planes_all + (size_t)blockIdx.y * g.plane_per_image;
+  const int cpw = g.bw[g.ncomp == 1 ? 0 : 1] * 8, cph = g.bh[g.ncomp == 1 ? 0 : 1] * 8;   // the grid: chroma plane (gray: luma)
+  const int item = (int)blockIdx.x * 256 + (int)threadIdx.x;
+  if (item >= cpw * cph) return;
+  const int Y = item / cpw, X = item - Y * cpw;
+  if (g.ncomp == 1) {
+    planes[(size_t)Y * cpw + X] = frame[(size_t)min(Y, g.H - 1) * g.W + min(X, g.W - 1)];
+    return;
+  }
+  const int lpw = g.bw[0] * 8, lph = g.bh[0] * 8;
+#pragma unroll
+  for (int dy = 0; dy < VS; dy++)
+#pragma unroll
+    for (int dx = 0; dx < HS; dx++) {
+      const int lx = X * HS + dx, ly = Y * VS + dy;
+      if (lx < lpw && ly < lph)
+        planes[g.plane_offset[0] + (size_t)ly * lpw + lx] =
+            (uint8_t)ycc_sample(frame + ((size_t)min(ly, g.H - 1) * g.W + min(lx, g.W - 1)) * 3, 0);
+    }
+  const int sy = min(Y, g.ch[1] - 1);                     // below the image: the last sample row again
+  int cb = 0, cr = 0;
+#pragma unroll
+  for (int dy = 0; dy < VS; dy++)
+#pragma unroll
+    for (int dx = 0; dx < HS; dx++) {
+      const uint8_t* px = frame + ((size_t)min(sy * VS + dy, g.H - 1) * g.W + min(X * HS + dx, g.W - 1)) * 3;
+      cb += ycc_sample(px, 1);
+      cr += ycc_sample(px, 2);
+    }
+  if (HS == 2 && VS == 1) { const int bias = X & 1; cb = (cb + bias) >> 1; cr = (cr + bias) >> 1; }          // h2v1: 0, 1, 0, 1
+  else if (HS == 2) { const int bias = (X & 1) ? 2 : 1; cb = (cb + bias) >> 2; cr = (cr + bias) >> 2; }      // h2v2: 1, 2, 1, 2
+  planes[g.plane_offset[1] + (size_t)Y * cpw + X] = (uint8_t)cb;
+  planes[g.plane_offset[2] + (size_t)Y * cpw + X] = (uint8_t)cr;
+}
+
+constexpr int kFdctThreads = 128;
+
+__global__ void __launch_bounds__(kFdctThreads) jpeg_fdct_kernel(const uint8_t* __restrict__ planes_all, const EncGeometry g,
+                                                                 const EncTables t, int16_t* __restrict__ coef) {
   const int blk = (int)blockIdx.x * kFdctThreads + (int)threadIdx.x;
   if (blk >= g.n_blocks) return;
   const int m = blk / g.bpm, q = blk - m * g.bpm;
@@ -100,27 +145,16 @@ __global__ void __launch_bounds__(kFdctThreads) jpeg_fdct_kernel(const uint8_t* 
     for (int k = 0; k < 8; k++) out[k] = make_uint4(0, 0, 0, 0);
     return;
   }
-  const uint8_t* frame = src + (size_t)blockIdx.y * frame_stride;
-  const int fx = g.hs / g.ph[c], fy = g.vs / g.pv[c];     // source pixels per sample
+  const int pitch = g.bw[c] * 8;
+  const uint8_t* plane = planes_all + (size_t)blockIdx.y * g.plane_per_image + g.plane_offset[c] + (size_t)gy * 8 * pitch + gx * 8;
   int x[64];
 #pragma unroll
   for (int yy = 0; yy < 8; yy++) {
-    const int sy = min(gy * 8 + yy, g.ch[c] - 1);         // below the image: the last sample row again
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(plane + (size_t)yy * pitch));
 #pragma unroll
-    for (int xx = 0; xx < 8; xx++) {
-      const int sx = gx * 8 + xx;
-      int sum = 0;
-      for (int dy = 0; dy < fy; dy++) {
-        const int py = min(sy * fy + dy, g.H - 1);
-        for (int dx = 0; dx < fx; dx++) {
-          const int px = min(sx * fx + dx, g.W - 1);      // right of the image: the last pixel again
-          sum += ycc_sample(frame + ((size_t)py * g.W + px) * channels, c, channels);
-        }
-      }
-      int s = sum;
-      if (fx == 2 && fy == 1) s = (sum + (sx & 1)) >> 1;          // h2v1: bias 0, 1, 0, 1
-      else if (fx == 2) s = (sum + ((sx & 1) ? 2 : 1)) >> 2;      // h2v2: bias 1, 2, 1, 2
-      x[8 * yy + xx] = s - 128;
+    for (int xx = 0; xx < 4; xx++) {
+      x[8 * yy + xx] = (int)((v.x >> (8 * xx)) & 0xffu) - 128;
+      x[8 * yy + 4 + xx] = (int)((v.y >> (8 * xx)) & 0xffu) - 128;
     }
   }
 #pragma unroll
@@ -130,6 +164,7 @@ __global__ void __launch_bounds__(kFdctThreads) jpeg_fdct_kernel(const uint8_t* 
   for (int col = 0; col < 8; col++)
     AIKO_FDCT_1D(x[col], x[8 + col], x[16 + col], x[24 + col], x[32 + col], x[40 + col], x[48 + col], x[56 + col], false)
   const uint16_t* q8 = t.q8[c == 0 ? 0 : 1];
+  const unsigned long long* recip = t.recip[c == 0 ? 0 : 1];
   uint32_t packed[32];
 #pragma unroll
   for (int k = 0; k < 64; k++) {
@@ -137,9 +172,10 @@ __global__ void __launch_bounds__(kFdctThreads) jpeg_fdct_kernel(const uint8_t* 
                                 41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
                                 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
     const int i = zz[k];
-    const int div = q8[i];
     const int v = x[i];
-    const int qv = v < 0 ? -((-v + (div >> 1)) / div) : (v + (div >> 1)) / div;
+    const unsigned n = (unsigned)(v < 0 ? -v : v) + (q8[i] >> 1);
+    const int mag = (int)(((unsigned long long)n * recip[i]) >> 40);       // n / q8[i]
+    const int qv = v < 0 ? -mag : mag;
     if (k & 1) packed[k >> 1] |= (uint32_t)(qv & 0xffff) << 16;
     else packed[k >> 1] = (uint32_t)(qv & 0xffff);
   }
@@ -418,6 +454,12 @@ int make_enc_geometry(int w, int h, int channels, int hs, int vs, EncGeometry* g
   const long long blocks = (long long)g->mcux * g->mcuy * g->bpm;
   if (blocks > (1ll << 26)) { set_last_error("jpeg_encode: image too large"); return AIKO_B200_ERR_UNSUPPORTED; }
   g->n_blocks = (int)blocks;
+  long long plane = 0;
+  for (int c = 0; c < g->ncomp; c++) {
+    g->plane_offset[c] = plane;
+    plane += (long long)g->bw[c] * 8 * g->bh[c] * 8;
+  }
+  g->plane_per_image = (plane + 15) & ~15ll;
   return AIKO_B200_OK;
 }
 
@@ -480,7 +522,7 @@ void build_header(const EncGeometry& g, const uint8_t q[2][64], EncHeader* hdr) 
   hdr->length = (int)(p - hdr->bytes);
 }
 
-struct EncLayout { size_t coef, scan, bits, total; long long scan_words; };
+struct EncLayout { size_t planes, coef, scan, bits, total; long long scan_words; };
 
 size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
@@ -488,6 +530,7 @@ EncLayout enc_layout(int n, const EncGeometry& g, size_t scan_capacity) {
   EncLayout L{};
   L.scan_words = (long long)((scan_capacity + 15) / 16 * 4);            // a multiple of 16 bytes per image
   size_t at = 0;
+  L.planes = at; at = align256(at + (size_t)n * g.plane_per_image);
   L.coef = at; at = align256(at + (size_t)n * g.n_blocks * 64 * sizeof(int16_t));
   L.scan = at; at = align256(at + (size_t)n * (size_t)L.scan_words * 4 + 64);
   L.bits = at; at = align256(at + (size_t)n * sizeof(long long));
@@ -531,7 +574,10 @@ extern "C" int aiko_b200_jpeg_gpu_encode_u8(const uint8_t* src, int n_images, in
   EncTables t;
   memset(&t, 0, sizeof(t));
   for (int k = 0; k < 2; k++)
-    for (int i = 0; i < 64; i++) t.q8[k][i] = (uint16_t)(q[k][i] * 8);
+    for (int i = 0; i < 64; i++) {
+      t.q8[k][i] = (uint16_t)(q[k][i] * 8);
+      t.recip[k][i] = ((1ull << 40) + t.q8[k][i] - 1) / t.q8[k][i];
+    }
   {
     uint16_t code[256];
     uint8_t size[256];
@@ -555,9 +601,19 @@ extern "C" int aiko_b200_jpeg_gpu_encode_u8(const uint8_t* src, int n_images, in
   uint32_t* d_scan = reinterpret_cast<uint32_t*>(ws + L.scan);
   long long* d_bits = reinterpret_cast<long long*>(ws + L.bits);
   AIKO_CUDA(cudaMemsetAsync(d_scan, 0, (size_t)n_images * (size_t)L.scan_words * 4, st));
-  jpeg_fdct_kernel<<<dim3((unsigned)((g.n_blocks + kFdctThreads - 1) / kFdctThreads), (unsigned)n_images), kFdctThreads, 0, st>>>(
-      src, frame_stride, channels, g, t, d_coef);
-  AIKO_CUDA(cudaGetLastError());
+  {
+    uint8_t* d_planes = ws + L.planes;
+    const int cc = g.ncomp == 1 ? 0 : 1;
+    const long long items = (long long)g.bw[cc] * 8 * g.bh[cc] * 8;
+    const dim3 grid((unsigned)((items + 255) / 256), (unsigned)n_images);
+    if (g.hs == 1) jpeg_planes_kernel<1, 1><<<grid, 256, 0, st>>>(src, frame_stride, g, d_planes);
+    else if (g.vs == 1) jpeg_planes_kernel<2, 1><<<grid, 256, 0, st>>>(src, frame_stride, g, d_planes);
+    else jpeg_planes_kernel<2, 2><<<grid, 256, 0, st>>>(src, frame_stride, g, d_planes);
+    AIKO_CUDA(cudaGetLastError());
+    jpeg_fdct_kernel<<<dim3((unsigned)((g.n_blocks + kFdctThreads - 1) / kFdctThreads), (unsigned)n_images), kFdctThreads, 0, st>>>(
+        d_planes, g, t, d_coef);
+    AIKO_CUDA(cudaGetLastError());
+  }
   jpeg_entropy_kernel<<<(unsigned)n_images, kEntropyThreads, 0, st>>>(d_coef, g, t, d_scan, L.scan_words, d_bits);
   AIKO_CUDA(cudaGetLastError());
   jpeg_finish_kernel<<<(unsigned)n_images, kFinishThreads, 0, st>>>(reinterpret_cast<const uint8_t*>(d_scan), L.scan_words * 4,
