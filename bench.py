@@ -93,9 +93,10 @@ def jpeg_blob(seed, restart_rows=0):
     return buf.getvalue()
 
 
-JPEG_WORKLOAD = ("config1: JPEG bytes in host memory (1080p, quality 90, 4:2:0, Pillow's default encoder settings: no "
-                 "restart markers) -> decode -> ImageResize PIL branch (antialiased bicubic 1920x1080->640x480) -> RGB "
-                 "frames in host memory, 32-frame batches")
+JPEG_WORKLOAD = ("config1: ImageReadFile -> ImageResize -> ImageWriteFile on JPEG files held in host memory: 1080p, quality "
+                 "90, 4:2:0, Pillow's default encoder settings (no restart markers) -> decode -> ImageResize PIL branch "
+                 "(antialiased bicubic 1920x1080->640x480) -> image.save as JPEG (Pillow's defaults: quality 75, 4:2:0) "
+                 "-> file bytes in host memory, 32-frame batches")
 JPEG_LANES = int(os.environ.get("AIKO_BENCH_JPEG_LANES", "8"))
 
 
@@ -203,15 +204,16 @@ def cpu_reference_rate(steps, warmup, frames_per_step=BATCH):
 
 
 def _ref_worker_jpeg(idx, seeds, warmup, steps, rounds, barrier, results):
-    """One host core of the JPEG leg: Image.open + resize (R/elements/media/image_io.py:184,218; the
-    decode runs lazily inside resize, as in the reference) on its share of every 32-blob batch."""
+    """One host core of the JPEG leg: Image.open + resize + save (R/elements/media/image_io.py:184,218,250;
+    the decode runs lazily inside resize, as in the reference) on its share of every 32-blob batch."""
     import io
     from PIL import Image
     blobs = [jpeg_blob(s) for s in seeds]
     def step():
         out = None
         for b in blobs:
-            out = np.asarray(Image.open(io.BytesIO(b)).resize((DST_W, DST_H)))
+            out = io.BytesIO()
+            Image.open(io.BytesIO(b)).resize((DST_W, DST_H)).save(out, "JPEG")
         return out
     for _ in range(max(warmup, 1)):
         step()
@@ -265,7 +267,7 @@ def cpu_jpeg_object(args):
     rate, workers, rounds = cpu_reference_rate_jpeg(jpeg_steps(args), min(args.warmup, 2))
     return {"value": rate, "unit": "frames/s", "cores": workers, "kind": "reference library calls",
             "workload": JPEG_WORKLOAD, "rounds_frames_per_s": [round(r, 1) for r in rounds],
-            "sample": f"{CPU_ROUNDS} rounds x {jpeg_steps(args)} steps x {BATCH} frames: PIL.Image.open(bytes).resize "
+            "sample": f"{CPU_ROUNDS} rounds x {jpeg_steps(args)} steps x {BATCH} frames: PIL.Image.open(bytes).resize(...).save(BytesIO, JPEG) "
                       f"(Pillow {PIL.__version__}), one process per core"}
 
 
@@ -669,48 +671,80 @@ def run_gpu_arm(args):
             t.numpy()[...] = np.frombuffer(b, np.uint8)
             return t
 
-        def jpeg_leg(pinned_blobs, make_decoder, n_lanes, n_steps):
+        JPEG_OUT_SLOT = 96 * 1024       # bytes copied back per file (a 640x480 file of this content is ~32 KB)
+
+        def jpeg_leg(pinned_blobs, n_lanes, n_steps, jpeg_out):
             lanes = []
             for k in range(n_lanes):
                 st = torch.cuda.Stream(device)
-                lanes.append({"stream": st, "decoder": make_decoder(),
-                              "frames": torch.empty((BATCH, SRC_H, SRC_W, 3), dtype=torch.uint8, device=device),
-                              "small": torch.empty((BATCH, DST_H, DST_W, 3), dtype=torch.uint8, device=device),
-                              "host": torch.empty((BATCH, DST_H, DST_W, 3), dtype=torch.uint8).pin_memory(),
-                              "busy": False})
+                lane = {"stream": st, "decoder": jpeg.GpuJpegDecoder(device), "busy": False, "oversize": 0,
+                        "frames": torch.empty((BATCH, SRC_H, SRC_W, 3), dtype=torch.uint8, device=device),
+                        "small": torch.empty((BATCH, DST_H, DST_W, 3), dtype=torch.uint8, device=device)}
+                if jpeg_out:
+                    lane["encoder"] = jpeg.GpuJpegEncoder(device)
+                    lane["files"] = torch.empty((BATCH, JPEG_OUT_SLOT), dtype=torch.uint8).pin_memory()
+                    lane["sizes"] = torch.empty(BATCH, dtype=torch.int32).pin_memory()
+                else:
+                    lane["host"] = torch.empty((BATCH, DST_H, DST_W, 3), dtype=torch.uint8).pin_memory()
+                lanes.append(lane)
+
+            def collect(lane):
+                lane["stream"].synchronize()
+                if jpeg_out and lane["busy"]:
+                    sizes = lane["sizes"].numpy()
+                    if sizes.min() < 0 or sizes.max() > JPEG_OUT_SLOT:     # (not with this content) a second, larger copy
+                        lane["oversize"] += 1
 
             def submit(i):
                 lane = lanes[i % n_lanes]
                 if lane["busy"]:
-                    lane["stream"].synchronize()
+                    collect(lane)
                 with torch.cuda.stream(lane["stream"]):
                     lane["decoder"].decode(pinned_blobs, out=lane["frames"], stream=lane["stream"])
                     ops.resize_bicubic_aa(lane["frames"], DST_W, DST_H, out=lane["small"], stream=lane["stream"])
-                    lane["host"].copy_(lane["small"], non_blocking=True)
+                    if jpeg_out:
+                        files, sizes = lane["encoder"].encode_async(lane["small"], stream=lane["stream"])
+                        lane["sizes"].copy_(sizes, non_blocking=True)
+                        lane["files"].copy_(files[:, :JPEG_OUT_SLOT], non_blocking=True)
+                    else:
+                        lane["host"].copy_(lane["small"], non_blocking=True)
                 lane["busy"] = True
 
             for i in range(2 * n_lanes):
                 submit(i)
             for lane in lanes:
-                lane["stream"].synchronize()
+                collect(lane)
             barrier()
             t0 = time.perf_counter()
             for i in range(n_steps):
                 submit(i)
             for lane in lanes:
-                lane["stream"].synchronize()
+                collect(lane)
             seconds = time.perf_counter() - t0
             barrier()
             for lane in lanes:
-                if hasattr(lane["decoder"], "check"):
-                    lane["decoder"].check()              # corrupt entropy data would raise here
+                lane["decoder"].check()                  # corrupt entropy data would raise here
             return seconds, lanes
 
         blobs = [jpeg_blob(JPEG_SEED + 100 * rank + k) for k in range(BATCH)]
+        pinned_blobs = [pin(b) for b in blobs]
         n_jpeg = max(2 * JPEG_LANES, min(4 * args.steps, 160))
-        jpeg_s, lanes = jpeg_leg([pin(b) for b in blobs], lambda: jpeg.GpuJpegDecoder(device), JPEG_LANES, n_jpeg)
+        jpeg_s, lanes = jpeg_leg(pinned_blobs, JPEG_LANES, n_jpeg, jpeg_out=True)
+        sizes = lanes[0]["sizes"].numpy()
+        first_file = lanes[0]["files"][0, :int(sizes[0])].numpy().tobytes()
         jpeg_result = {"seconds": jpeg_s, "frames": BATCH * n_jpeg, "steps": n_jpeg, "lanes": JPEG_LANES,
-                       "h2d": sum(len(b) for b in blobs), "checksum": int(lanes[0]["host"][0, 0, 0, 0])}
+                       "h2d": sum(len(b) for b in blobs), "d2h": BATCH * JPEG_OUT_SLOT + 4 * BATCH,
+                       "file_bytes": float(sizes.mean()), "oversize": sum(lane["oversize"] for lane in lanes),
+                       "checksum": int(np.frombuffer(first_file, np.uint8).sum())}
+        if rank == 0:                                    # the first file against the reference chain's (not timed)
+            import io
+            from PIL import Image
+            ref = io.BytesIO()
+            Image.open(io.BytesIO(blobs[0])).resize((DST_W, DST_H)).save(ref, "JPEG")
+            jpeg_result["identical_to_reference_file"] = ref.getvalue() == first_file
+        del lanes
+        rgb_s, lanes = jpeg_leg(pinned_blobs, JPEG_LANES, n_jpeg, jpeg_out=False)
+        jpeg_result.update({"rgb_seconds": rgb_s})
         del lanes
     except Exception as error:      # the headline does not depend on the JPEG leg
         jpeg_result = {"error": repr(error)}
@@ -723,7 +757,8 @@ def run_gpu_arm(args):
     c3_totals = sharding.combine([config3["seconds"]], [config3["frames"], config3["streams"]], device=device) if c3_ok else None
     ok_everywhere = sharding.combine([0.0 if (jpeg_result and "error" not in jpeg_result) else 1.0], [], device=device)[0][0] == 0.0
     if ok_everywhere:
-        jpeg_totals = sharding.combine([jpeg_result["seconds"]], [jpeg_result["frames"]], device=device)
+        jpeg_totals = sharding.combine([jpeg_result["seconds"], jpeg_result["rgb_seconds"]], [jpeg_result["frames"]],
+                                       device=device)
     elif jpeg_result is not None and "error" not in jpeg_result:
         jpeg_result = {"error": "JPEG leg failed on another rank"}
 
@@ -792,15 +827,21 @@ def run_gpu_arm(args):
         elif config3 is not None:
             line["config3"] = {"unavailable": config3.get("error", "failed on another rank")}
         if jpeg_result is not None and "error" not in jpeg_result:
-            (jpeg_s,), (jpeg_frames,) = jpeg_totals
+            (jpeg_s, rgb_s), (jpeg_frames,) = jpeg_totals
             line["e2e_jpeg"] = {"value": jpeg_frames / jpeg_s, "unit": "frames/s", "workload": JPEG_WORKLOAD,
                                 "steps": jpeg_result["steps"], "batches_in_flight": jpeg_result["lanes"],
-                                "h2d_bytes_per_step": jpeg_result["h2d"], "d2h_bytes_per_step": d2h,
-                                "decoder": "this library's kernels (csrc/jpeg_decode.cu): jpeg_unstuff_kernel, "
-                                           "jpeg_sync_huffman_kernel (one thread per 448-byte subsequence of the scan, "
-                                           "boundary states by iteration), jpeg_idct_kernel, jpeg_colour_kernel; "
-                                           "resize = bicubic_mma_kernel",
-                                "note": "decoded pixels are bit-identical to Pillow's decoder (tests/test_gpu_jpeg.py)"}
+                                "h2d_bytes_per_step": jpeg_result["h2d"], "d2h_bytes_per_step": jpeg_result["d2h"],
+                                "written_file_bytes_mean": jpeg_result["file_bytes"],
+                                "files_larger_than_the_copied_slot": jpeg_result["oversize"],
+                                "first_file_identical_to_the_reference_chain": jpeg_result.get("identical_to_reference_file"),
+                                "value_rgb_out": jpeg_frames / rgb_s,
+                                "kernels": "csrc/jpeg_decode.cu: jpeg_unstuff_kernel, jpeg_sync_huffman_kernel (one thread "
+                                           "per 448-byte subsequence of the scan, boundary states by iteration), "
+                                           "jpeg_idct_kernel, jpeg_colour_kernel; bicubic_mma_kernel; csrc/jpeg_encode.cu: "
+                                           "jpeg_planes_kernel, jpeg_fdct_kernel, jpeg_entropy_kernel, jpeg_finish_kernel",
+                                "note": "decoded pixels bit-identical to Pillow's decoder, written files byte-identical to "
+                                        "Pillow's (tests/test_gpu_jpeg.py); value_rgb_out: the same without the encoder, "
+                                        "640x480 RGB frames copied to host memory instead (29.5 MB per step)"}
         elif jpeg_result is not None:
             line["e2e_jpeg"] = {"unavailable": jpeg_result["error"]}
         if world == 1 and not args.no_cpu_baseline:
