@@ -19,6 +19,7 @@
 // from global memory.
 #include <atomic>
 #include <math.h>
+#include <vector>
 
 #include "overlay.cuh"
 
@@ -769,19 +770,59 @@ extern "C" int aiko_b200_resize_linear_rows_host(int src_h, int dst_h, uint8_t* 
 }
 
 // Host -> device copy of the listed row runs of every frame of a batch (runs_host: first row, row count
-// pairs): one strided copy per run across all frames.  The rows in between are left as they are.
+// pairs, ascending).  The frames are contiguous, so the batch is one long list of rows: runs that touch across a
+// frame boundary are merged, and consecutive runs of equal length at equal distance become ONE strided copy
+// (1080 -> 480 rows: every ninth source row carries no weight, the whole 32-frame batch is a head run, one
+// strided copy of 3839 runs of 8 rows, and a tail run).  Patterns that would need more than 8 copies are copied
+// whole.  Rows that are not listed are left as they are.
 extern "C" int aiko_b200_copy_rows_h2d(uint8_t* dst, const uint8_t* src_host, int n_frames, int64_t frame_bytes,
                                        int64_t row_bytes, const int32_t* runs_host, int n_runs, void* stream) {
   AIKO_CHECK_ARG(n_frames >= 0 && n_runs >= 0 && frame_bytes > 0 && row_bytes > 0, "copy_rows: bad size");
   if (n_frames == 0 || n_runs == 0) return AIKO_B200_OK;
   AIKO_CHECK_ARG(dst && src_host && runs_host, "copy_rows: null pointer");
+  AIKO_CHECK_ARG(frame_bytes % row_bytes == 0, "copy_rows: frames must be whole rows (contiguous frames)");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  for (int r = 0; r < n_runs; r++) {
-    const int64_t first = runs_host[2 * r], count = runs_host[2 * r + 1];
-    AIKO_CHECK_ARG(first >= 0 && count > 0 && (first + count) * row_bytes <= frame_bytes, "copy_rows: run %d outside the frame", r);
-    AIKO_CUDA(cudaMemcpy2DAsync(dst + first * row_bytes, (size_t)frame_bytes, src_host + first * row_bytes,
-                                (size_t)frame_bytes, (size_t)(count * row_bytes), (size_t)n_frames,
-                                cudaMemcpyHostToDevice, st));
+  const int64_t rows = frame_bytes / row_bytes;
+  struct Piece { int64_t first, count, stride, repeats; };
+  std::vector<Piece> pieces;
+  int64_t run_first = -1, run_count = 0;               // the run being assembled, in batch rows
+  auto close_run = [&]() {
+    if (run_count == 0) return;
+    if (!pieces.empty()) {
+      Piece& p = pieces.back();
+      const int64_t last_first = p.first + (p.repeats - 1) * p.stride;
+      if (p.count == run_count && (p.repeats == 1 || run_first - last_first == p.stride)) {
+        if (p.repeats == 1) p.stride = run_first - p.first;
+        p.repeats++;
+        run_count = 0;
+        return;
+      }
+    }
+    pieces.push_back({run_first, run_count, 0, 1});
+    run_count = 0;
+  };
+  for (int f = 0; f < n_frames; f++)
+    for (int r = 0; r < n_runs; r++) {
+      const int64_t first = runs_host[2 * r], count = runs_host[2 * r + 1];
+      AIKO_CHECK_ARG(first >= 0 && count > 0 && first + count <= rows, "copy_rows: run %d outside the frame", r);
+      const int64_t at = (int64_t)f * rows + first;
+      if (run_count > 0 && at == run_first + run_count) { run_count += count; continue; }
+      close_run();
+      run_first = at;
+      run_count = count;
+    }
+  close_run();
+  if (pieces.size() > 8) {                              // too fragmented: one contiguous copy of everything
+    AIKO_CUDA(cudaMemcpyAsync(dst, src_host, (size_t)(frame_bytes * n_frames), cudaMemcpyHostToDevice, st));
+    return AIKO_B200_OK;
+  }
+  for (const Piece& p : pieces) {
+    const size_t offset = (size_t)(p.first * row_bytes), width = (size_t)(p.count * row_bytes);
+    if (p.repeats == 1)
+      AIKO_CUDA(cudaMemcpyAsync(dst + offset, src_host + offset, width, cudaMemcpyHostToDevice, st));
+    else
+      AIKO_CUDA(cudaMemcpy2DAsync(dst + offset, (size_t)(p.stride * row_bytes), src_host + offset, (size_t)(p.stride * row_bytes),
+                                  width, (size_t)p.repeats, cudaMemcpyHostToDevice, st));
   }
   return AIKO_B200_OK;
 }

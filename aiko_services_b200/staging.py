@@ -130,14 +130,13 @@ class FrameStager:
 
     def upload_pinned(self, pinned_tensor, slot=None, resize_to=None):
         """A tensor already in pinned host memory -> DeviceBatch (one cudaMemcpyAsync).  ``resize_to``
-        = (width, height) says that a bilinear resize is all that will read the frames; with
-        AIKO_B200_COPY_NEEDED_ROWS=1 only the source rows that carry weight then cross PCIe (8 of 9 for
-        1080 -> 480), as one strided copy per run of rows.  Off by default: measured on B200 the 121
-        strided copies of a 32-frame batch (46 KB per row run and frame) run the copy engine at a lower
-        rate than one contiguous 199 MB copy -- 7.8 k against 8.7 k frames/s end to end."""
+        = (width, height) says that a bilinear resize is all that will read the frames: then only the
+        source rows that carry weight cross PCIe (8 of 9 for 1080 -> 480; the library turns the periodic
+        pattern into three copies per batch, one of them strided; AIKO_B200_COPY_NEEDED_ROWS=0 copies
+        everything)."""
         lane = self.next_lane()
         runs = None
-        if resize_to is not None and pinned_tensor.dim() == 4 and os.environ.get("AIKO_B200_COPY_NEEDED_ROWS") == "1":
+        if resize_to is not None and pinned_tensor.dim() == 4 and os.environ.get("AIKO_B200_COPY_NEEDED_ROWS", "1") == "1":
             runs = needed_row_runs(pinned_tensor.shape[1], resize_to[1])
         with torch.cuda.stream(lane):
             dev = torch.empty(pinned_tensor.shape, dtype=torch.uint8, device=self.device)

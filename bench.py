@@ -611,7 +611,12 @@ def run_gpu_arm(args):
     checksum += e2e_collect(pending)
     barrier()
     e2e_s = time.perf_counter() - t0
-    h2d = BATCH * SRC_H * SRC_W * 3
+    # bytes that cross PCIe per step: the stager ships only the source rows that carry weight in the resize
+    # (8 of every 9 for 1080 -> 480), unless AIKO_B200_COPY_NEEDED_ROWS=0
+    from aiko_services_b200.staging import needed_row_runs
+    runs = needed_row_runs(SRC_H, DST_H) if os.environ.get("AIKO_B200_COPY_NEEDED_ROWS", "1") == "1" else None
+    rows_copied = sum(runs[0][1::2]) if runs is not None else SRC_H
+    h2d = BATCH * rows_copied * SRC_W * 3
     d2h = BATCH * DST_H * DST_W * 3
 
     # ---- BASELINE config 3: 64 concurrent 1080p streams sharded by stream_id across the ranks
@@ -810,9 +815,10 @@ def run_gpu_arm(args):
                          "kernels_per_step": ["resize3_staged", OVERLAY_KERNEL]},
             "e2e": {"value": frames_e2e / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                    "h2d_rows_per_frame": rows_copied,
                     "note": "Pipeline.process_frame over ImageResize -> ImageOverlay -> ImageConvert(RGB2BGR) -> "
-                            "ImageOutput; pinned host frames -> cudaMemcpyAsync -> fused kernel -> D2H, 2 aiko streams "
-                            "alternating"},
+                            "ImageOutput; pinned host frames -> cudaMemcpyAsync (only the source rows the resize reads: "
+                            "three copies per batch, one strided) -> fused kernel -> D2H, 2 aiko streams alternating"},
             "gpu_launches": 2 * args.steps * world,
             "clocks": clocks,
         }
