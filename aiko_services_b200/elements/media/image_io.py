@@ -218,20 +218,21 @@ def _read_jpegs_on_gpu(stream, paths, images):
             width, height, components, hmax, vmax, restart = jpeg.GpuJpegDecoder.info(data)
         except Exception:
             continue                      # progressive, CMYK, 12-bit, ...: the reference's host path
-        if components != 3:
-            continue                      # gray JPEGs open as mode L in Pillow: keep the host path
-        groups.setdefault((width, height, hmax, vmax), []).append((k, data))
+        groups.setdefault((width, height, components, hmax, vmax), []).append((k, data))
     import torch
-    for members in groups.values():
+    for key, members in groups.items():
         lane = stager.next_lane()
         with torch.cuda.stream(lane):
             # this library's decoder (bit-identical to Pillow); a truncated or corrupt file is an error of this
             # element, as a failing Image.open / load is in the reference, not a frame of garbage
             frames, _ = jpeg.decode_on_gpu([data for _, data in members], stager.device, stream=lane, check=True)
+            mode = "RGB"
+            if key[2] == 1:               # a gray file opens as mode L in Pillow: one channel (the decoder wrote R = G = B)
+                frames, mode = frames[..., 0].contiguous(), "L"
         batch = DeviceBatch(frames, lane)
         batch.stager = stager
         for image, (k, _) in zip(batch.images(), members):
-            images[k] = _LazyPil(image, "RGB")
+            images[k] = _LazyPil(image, mode)
 
 
 _JPEG_SUFFIXES = (".jpg", ".jpeg", ".jpe", ".jfif")

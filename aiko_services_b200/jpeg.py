@@ -259,10 +259,8 @@ class GpuJpegEncoder:
             entry = self._buffers[key] = (workspace, out, sizes, scan_capacity, out_stride)
         workspace, out, sizes, scan_capacity, out_stride = entry
         s = stream if stream is not None else torch.cuda.current_stream(self.device)
-        with torch.cuda.device(self.device):
-            _native.check(lib.aiko_b200_jpeg_gpu_encode_u8(
-                frames.data_ptr(), n, h, w, channels, h * w * channels, int(quality), hs, vs, workspace.data_ptr(),
-                workspace.numel(), scan_capacity, out.data_ptr(), out_stride, sizes.data_ptr(), _vp(s.cuda_stream)))
+        from .torch_ops import OPS
+        OPS.jpeg_encode_u8(frames, int(quality), hs, vs, workspace, scan_capacity, out, sizes, s.cuda_stream)
         return out, sizes
 
     def encode(self, frames, quality=75, subsampling=2, stream=None):

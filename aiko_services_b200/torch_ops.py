@@ -195,4 +195,14 @@ def audio_bands_f64(amplitudes, frequencies, band_freq, band_amp, stream):
                                                       band_amp.data_ptr(), _vp(stream)))
 
 
+@_op("jpeg_encode_u8(Tensor src, int quality, int hs, int vs, Tensor workspace, int scan_capacity, Tensor(a!) out, "
+     "Tensor(b!) sizes, int stream) -> ()")
+def jpeg_encode_u8(src, quality, hs, vs, workspace, scan_capacity, out, sizes, stream):
+    n, h, w, c = _geometry(src)
+    with _current(src):
+        check(_native.lib().aiko_b200_jpeg_gpu_encode_u8(
+            src.data_ptr(), n, h, w, c, h * w * c, int(quality), int(hs), int(vs), workspace.data_ptr(), workspace.numel(),
+            int(scan_capacity), out.data_ptr(), out.shape[1], sizes.data_ptr(), _vp(stream)))
+
+
 OPS = torch.ops.aiko_b200

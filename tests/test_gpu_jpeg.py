@@ -116,6 +116,7 @@ def test_jpeg_in_jpeg_out_files_are_the_references_bytes(cuda, tmp_path):
     mod = "aiko_services.elements.media.image_io"
     for k in range(5):
         (tmp_path / f"in_{k:02d}.jpg").write_bytes(encode(natural_frame(400 + k, 360, 640), 88, 2))
+    (tmp_path / "in_05.jpg").write_bytes(encode_rst(natural_frame(405, 360, 640), 80, mode="L", plain=True))   # a gray file
     d = {"version": 0, "name": "p_jpeg2", "runtime": "python", "graph": ["(ImageReadFile ImageResize ImageWriteFile)"],
          "parameters": {"resolution": "320x180"},
          "elements": [
@@ -130,10 +131,11 @@ def test_jpeg_in_jpeg_out_files_are_the_references_bytes(cuda, tmp_path):
     p = Pipeline(d)
     assert p.create_stream("1")
     p.run()
-    for k in range(5):
+    for k in range(6):
         buf = _io.BytesIO()
         Image.open(tmp_path / f"in_{k:02d}.jpg").resize((320, 180)).save(buf, "JPEG")
         assert (tmp_path / f"out_{k:02d}.jpg").read_bytes() == buf.getvalue(), k
+    assert Image.open(tmp_path / "out_05.jpg").mode == "L"
 
 
 # ---- this library's own decoder (csrc/jpeg_decode.cu): bit-exact with Pillow ------------------------------

@@ -158,3 +158,13 @@ def test_torch_custom_ops(cuda):
     np.testing.assert_array_equal(out[0].cpu().numpy(), O.resize_bicubic_aa(frames[0], 60, 45))
     with pytest.raises(Exception):
         T.flip_u8(src, src, 1, stream)           # aliased pointers: the library's error, not a crash
+    # JPEG files of the frames (image.save's bytes), straight through the op
+    from aiko_services_b200 import _native
+    capacity = 90 * 150 * 3
+    nbytes = _native.lib().aiko_b200_jpeg_gpu_encode_workspace_bytes(3, 150, 90, 3, 2, 2, capacity)
+    workspace = torch.empty(nbytes, dtype=torch.uint8, device=cuda)
+    files = torch.empty((3, 2 * capacity), dtype=torch.uint8, device=cuda)
+    sizes = torch.empty(3, dtype=torch.int32, device=cuda)
+    T.jpeg_encode_u8(src, 75, 2, 2, workspace, capacity, files, sizes, stream)
+    for k in range(3):
+        assert files[k, :int(sizes[k])].cpu().numpy().tobytes() == O.jpeg_encode(frames[k])
