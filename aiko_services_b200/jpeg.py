@@ -1,7 +1,11 @@
-"""JPEG frames decoded on the GPU (libaiko_b200_jpeg.so, include/aiko_b200_jpeg.h): the decode half of
-``PIL.Image.open(path)`` ... ``image.resize(...)`` (R/elements/media/image_io.py:184,218) so that
-frames are born device-resident instead of crossing PCIe as raw pixels.  The decoder is nvJPEG (the
-NVJPG hardware engines when available).  torch only provides the destination tensor and the stream."""
+"""JPEG at the file edges of the path, on the GPU: the decode half of ``PIL.Image.open(path)`` ...
+``image.resize(...)`` (R/elements/media/image_io.py:184,218) and the encode inside ``image.save(path)``
+(image_io.py:250), so that frames are born and leave device-resident instead of crossing PCIe as raw pixels.
+
+``GpuJpegDecoder`` / ``GpuJpegEncoder``: this library's own kernels (csrc/jpeg_decode.cu, csrc/jpeg_encode.cu in
+libaiko_b200.so; include/aiko_b200.h): baseline files, pixels and file bytes identical to Pillow's.
+``JpegDecoder``: nvJPEG behind libaiko_b200_jpeg.so (include/aiko_b200_jpeg.h) for what the own decoder refuses
+(progressive files).  torch only provides the tensors and the streams; there is no CPU decoder here."""
 import ctypes
 import os
 
