@@ -205,10 +205,25 @@ class FrameStager:
                         # or cameras' own buffers): one asynchronous copy per frame straight into
                         # the batch on the device -- no staging copy on the host
                         lane = self.next_lane()
+                        runs = None
+                        if resize_to is not None and arrs[0].ndim == 3 and os.environ.get("AIKO_B200_COPY_NEEDED_ROWS", "1") == "1":
+                            runs = needed_row_runs(arrs[0].shape[0], resize_to[1])
                         with torch.cuda.stream(lane):
                             dev = torch.empty((len(arrs),) + arrs[0].shape, dtype=torch.uint8, device=self.device)
-                            for k, t in enumerate(sources):
-                                dev[k].copy_(t, non_blocking=True)
+                            if runs is not None:      # only the rows the resize reads: three copies per frame
+                                import ctypes
+
+                                from . import _native
+                                h, w, c = arrs[0].shape
+                                copy, st = _native.lib().aiko_b200_copy_rows_h2d, ctypes.c_void_p(lane.cuda_stream)
+                                base, runs_ptr = dev.data_ptr(), runs[0].buffer_info()[0]
+                                with torch.cuda.device(self.device):
+                                    for k, t in enumerate(sources):
+                                        _native.check(copy(base + k * h * w * c, t.data_ptr(), 1, h * w * c, w * c, runs_ptr,
+                                                           runs[1], st))
+                            else:
+                                for k, t in enumerate(sources):
+                                    dev[k].copy_(t, non_blocking=True)
                         batch = DeviceBatch(dev, lane)
                         batch.stager = self
                         out.append((batch, positions))
