@@ -302,3 +302,15 @@ def test_encoder_defaults_gray_and_round_trip(cuda):
     noise = np.random.default_rng(3).integers(0, 256, (1, 256, 256, 3), dtype=np.uint8)     # scan larger than the first buffers
     assert enc.encode(torch.from_numpy(noise).to(cuda), quality=100, subsampling=0)[0] == pillow_bytes(noise[0], quality=100, subsampling=0)
     assert enc.encode(torch.empty((0, 8, 8, 3), dtype=torch.uint8, device=cuda)) == []
+
+
+def test_codec_on_large_and_extreme_shapes(cuda):
+    """4K frames (BASELINE config 4's source size), a very wide strip and a very tall one: encoder bytes and decoder
+    pixels against Pillow."""
+    from aiko_services_b200 import jpeg
+    enc, dec = jpeg.GpuJpegEncoder(cuda), jpeg.GpuJpegDecoder(cuda)
+    for h, w in ((2160, 3840), (9, 4100), (4100, 9)):
+        frame = natural_frame(h + w, max(h, 41), max(w, 41))[:h, :w]
+        files = enc.encode(torch.from_numpy(np.ascontiguousarray(frame[None])).to(cuda), quality=85)
+        assert files[0] == pillow_bytes(frame, quality=85), (h, w)
+        np.testing.assert_array_equal(dec.decode(files, check=True).cpu().numpy()[0], pillow_rgb(files[0]))
