@@ -103,6 +103,7 @@ SIGNATURES = {
     "aiko_b200_swap_rb_u8": [_vp, _vp, _i64, _vp],
     "aiko_b200_bgr2gray_u8": [_vp, _vp, _i64, _i, _vp],
     "aiko_b200_yuv_u8": [_vp, _vp, _i64, _i, _i, _vp],
+    "aiko_b200_alpha_paste_u8": [_vp, _i, _i, _i, _i64, _vp, _i, _i, _i, _i, _vp],
     "aiko_b200_gray2bgr_u8": [_vp, _vp, _i64, _vp],
     "aiko_b200_flip_u8": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "aiko_b200_crop_u8": [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _vp],

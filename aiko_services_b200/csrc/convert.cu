@@ -323,6 +323,74 @@ extern "C" int aiko_b200_yuv_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixe
   return cuda_status(cudaGetLastError(), "yuv launch");
 }
 
+// Alpha blending (extension: named by BASELINE.json's north_star, no call site in the reference): an RGBA image
+// composited onto every RGB frame of a batch the way PIL's frame.paste(image, (x, y), image) does it -- per byte
+// t = dst * (255 - a) + src * a + 128; out = ((t >> 8) + t) >> 8 (Paste.c, BLEND8).  One thread per 4 pixels of
+// a row of the covered region; the 1.2 MB of a frame-sized RGBA image stay L2-resident across the batch.
+__global__ void alpha_paste_kernel(uint8_t* __restrict__ frames, long long frame_stride, int width,
+                                   const uint8_t* __restrict__ rgba, int sticker_w, int sx0, int sy0, int dx0, int dy0,
+                                   int region_w, int region_h) {
+  const int groups = (region_w + 3) >> 2;
+  const int item = (int)blockIdx.x * kThreads + (int)threadIdx.x;
+  if (item >= groups * region_h) return;
+  const int r = item / groups, x = (item - r * groups) * 4;
+  const int npx = min(4, region_w - x);
+  const uint8_t* s = rgba + ((size_t)(sy0 + r) * sticker_w + sx0 + x) * 4;
+  uint8_t* d = frames + (size_t)blockIdx.y * frame_stride + ((size_t)(dy0 + r) * width + dx0 + x) * 3;
+  uint32_t sp[4] = {0, 0, 0, 0};
+  if (npx == 4 && (reinterpret_cast<uintptr_t>(s) & 15) == 0) {
+    const uint4 q = __ldg(reinterpret_cast<const uint4*>(s));
+    sp[0] = q.x; sp[1] = q.y; sp[2] = q.z; sp[3] = q.w;
+  } else {
+    for (int k = 0; k < npx; k++) sp[k] = __ldg(reinterpret_cast<const uint32_t*>(s) + k);
+  }
+  const bool words = npx == 4 && (reinterpret_cast<uintptr_t>(d) & 3) == 0;
+  uint32_t dw[3] = {0, 0, 0};
+  if (words) {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(d);
+    dw[0] = p[0]; dw[1] = p[1]; dw[2] = p[2];
+  } else {
+    for (int q = 0; q < npx * 3; q++) dw[q >> 2] |= (uint32_t)d[q] << (8 * (q & 3));
+  }
+  uint32_t out[3] = {0, 0, 0};
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const unsigned a = sp[k] >> 24;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const int at = 3 * k + c;
+      const unsigned old = (dw[at >> 2] >> (8 * (at & 3))) & 0xffu, src = (sp[k] >> (8 * c)) & 0xffu;
+      const unsigned t = old * (255u - a) + src * a + 128u;
+      out[at >> 2] |= ((((t >> 8) + t) >> 8) & 0xffu) << (8 * (at & 3));
+    }
+  }
+  if (words) {
+    uint32_t* p = reinterpret_cast<uint32_t*>(d);
+    p[0] = out[0]; p[1] = out[1]; p[2] = out[2];
+  } else {
+    for (int q = 0; q < npx * 3; q++) d[q] = (uint8_t)(out[q >> 2] >> (8 * (q & 3)));
+  }
+}
+
+extern "C" int aiko_b200_alpha_paste_u8(uint8_t* frames, int n_frames, int height, int width, int64_t frame_stride,
+                                        const uint8_t* rgba, int image_h, int image_w, int x, int y, void* stream) {
+  AIKO_CHECK_ARG(n_frames >= 0 && height > 0 && width > 0 && image_h >= 0 && image_w >= 0, "alpha_paste: bad size");
+  AIKO_CHECK_ARG(frame_stride >= (int64_t)height * width * 3, "alpha_paste: frame stride smaller than a frame");
+  // the part of the image that lands on the frame (PIL clips the box to the frame)
+  const long long x0 = x < 0 ? 0 : x, y0 = y < 0 ? 0 : y;
+  const long long x1 = (long long)x + image_w < width ? (long long)x + image_w : width;
+  const long long y1 = (long long)y + image_h < height ? (long long)y + image_h : height;
+  if (n_frames == 0 || x1 <= x0 || y1 <= y0) return AIKO_B200_OK;
+  AIKO_CHECK_ARG(frames && rgba, "alpha_paste: null pointer");
+  AIKO_CHECK_ARG((reinterpret_cast<uintptr_t>(rgba) & 3) == 0, "alpha_paste: the RGBA image must be 4-byte aligned");
+  const int region_w = (int)(x1 - x0), region_h = (int)(y1 - y0);
+  const long long items = (long long)((region_w + 3) / 4) * region_h;
+  alpha_paste_kernel<<<dim3((unsigned)((items + kThreads - 1) / kThreads), (unsigned)n_frames), kThreads, 0,
+                       (cudaStream_t)stream>>>(frames, frame_stride, width, rgba, image_w, (int)(x0 - x), (int)(y0 - y), (int)x0,
+                                               (int)y0, region_w, region_h);
+  return cuda_status(cudaGetLastError(), "alpha_paste launch");
+}
+
 extern "C" int aiko_b200_bgr2gray_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, int rgb_order,
                                      void* stream) {
   AIKO_CHECK_ARG(n_pixels >= 0, "bgr2gray: n_pixels < 0");

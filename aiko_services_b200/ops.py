@@ -478,6 +478,24 @@ def yuv(src, *, bgr_order=False, inverse=False, out=None, stream=None):
     return out
 
 
+def alpha_paste(frames, rgba, x=0, y=0, *, out=None, stream=None):
+    """PIL's ``frame.paste(image, (x, y), image)`` for every RGB frame of ``frames`` [N, H, W, 3]: the RGBA image
+    ``rgba`` [h, w, 4] (CUDA tensor) blended over the frames by its own alpha.  In place unless ``out`` is given."""
+    _require_cuda(frames, "alpha_paste frames")
+    _require_cuda(rgba, "alpha_paste rgba")
+    if frames.dim() != 4 or frames.shape[3] != 3 or rgba.dim() != 3 or rgba.shape[2] != 4:
+        raise ValueError("alpha_paste: frames [N, H, W, 3] and an RGBA image [h, w, 4] are needed")
+    if out is not None:
+        out = _out(out, frames.shape, frames.device, "alpha_paste out")
+        if out.data_ptr() != frames.data_ptr():
+            with torch.cuda.stream(stream) if stream is not None else contextlib.nullcontext():
+                out.copy_(frames)
+        frames = out
+    with _on_device(frames.device):
+        _T().alpha_paste_u8(frames, rgba, int(x), int(y), _stream_int(stream))
+    return frames
+
+
 def gray2bgr(src, *, out=None, stream=None):
     _require_cuda(src, "gray2bgr src")
     out = _out(out, tuple(src.shape) + (3,), src.device, "gray2bgr out")

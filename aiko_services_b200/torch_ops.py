@@ -118,6 +118,14 @@ def yuv_u8(src, out, bgr_order, inverse, stream):
                                              int(inverse), _vp(stream)))
 
 
+@_op("alpha_paste_u8(Tensor(a!) frames, Tensor rgba, int x, int y, int stream) -> ()")
+def alpha_paste_u8(frames, rgba, x, y, stream):
+    n, h, w, _ = _geometry(frames)
+    with _current(frames):
+        check(_native.lib().aiko_b200_alpha_paste_u8(frames.data_ptr(), n, h, w, h * w * 3, rgba.data_ptr(), rgba.shape[0],
+                                                     rgba.shape[1], int(x), int(y), _vp(stream)))
+
+
 @_op("gray2bgr_u8(Tensor src, Tensor(a!) out, int stream) -> ()")
 def gray2bgr_u8(src, out, stream):
     with _current(src):

@@ -66,6 +66,10 @@ def make(name, dev):
         src = [torch.randint(0, 256, shape, dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
         out = torch.empty((shape[0], size[1], size[0]) + shape[3:], dtype=torch.uint8, device=dev)
         return lambda i: ops.resize_linear(src[i % rot], size[0], size[1], out=out), shape[0]
+    if name == "alpha":                    # a frame-sized RGBA image blended over 32 x 640x480 frames, in place
+        frames = [torch.randint(0, 256, (32, 480, 640, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+        rgba = torch.randint(0, 256, (480, 640, 4), dtype=torch.uint8, device=dev, generator=g)
+        return lambda i: ops.alpha_paste(frames[i % rot], rgba), 32
     if name == "norm":                     # BASELINE config 4: 4K -> 224x224 fp32 NCHW, normalised
         src = [torch.randint(0, 256, (32, 2160, 3840, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(2)]
         out = torch.empty((32, 3, 224, 224), dtype=torch.float32, device=dev)

@@ -348,6 +348,12 @@ int aiko_b200_bgr2gray_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, in
 /* inverse = 1 (bgr_order picks the BGR variants), 14-bit fixed point, bit-exact with OpenCV   */
 /* over all 2^24 colours.  n_pixels 3-byte pixels.                                            */
 int aiko_b200_yuv_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, int bgr_order, int inverse, void* stream);
+/* Alpha blending (extension: BASELINE.json's north_star names it, the reference has no call   */
+/* site): the RGBA image rgba[image_h][image_w][4] (device, 4-byte aligned) composited onto every  */
+/* RGB frame at (x, y), in place, with the arithmetic of PIL's frame.paste(image, (x, y), image):  */
+/* t = dst * (255 - a) + src * a + 128, out = ((t >> 8) + t) >> 8; the box is clipped to the frame. */
+int aiko_b200_alpha_paste_u8(uint8_t* frames, int n_frames, int height, int width, int64_t frame_stride,
+                             const uint8_t* rgba, int image_h, int image_w, int x, int y, void* stream);
 /* cv2.cvtColor(.., COLOR_GRAY2BGR): image_io.py:115.                        */
 int aiko_b200_gray2bgr_u8(const uint8_t* src, uint8_t* dst, int64_t n_pixels, void* stream);
 /* cv2.flip(image, flip_code): webcam_io.py:127 (1, horizontal), :129 (0,    */

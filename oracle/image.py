@@ -237,3 +237,19 @@ def jpeg_encode(img, quality=75, subsampling=(2, 2)):
         out = np.empty(n, np.uint8)
         n = fn(img.ctypes.data, h, w, channels, int(quality), int(subsampling[0]), int(subsampling[1]), out.ctypes.data, n)
     return out[:n].tobytes()
+
+
+def pil_paste(img, rgba, x, y):
+    """PIL's ``Image.paste(image, (x, y), image)`` of an RGBA image onto an RGB frame (Paste.c BLEND8): per byte
+    t = dst * (255 - a) + src * a + 128, out = ((t >> 8) + t) >> 8; the box is clipped to the frame."""
+    out = np.array(img, dtype=np.uint8, copy=True)
+    h, w = out.shape[:2]
+    sh, sw = rgba.shape[:2]
+    x0, y0, x1, y1 = max(x, 0), max(y, 0), min(x + sw, w), min(y + sh, h)
+    if x1 <= x0 or y1 <= y0:
+        return out
+    part = rgba[y0 - y:y1 - y, x0 - x:x1 - x].astype(np.int32)
+    a = part[..., 3:4]
+    t = out[y0:y1, x0:x1].astype(np.int32) * (255 - a) + part[..., :3] * a + 128
+    out[y0:y1, x0:x1] = (((t >> 8) + t) >> 8).astype(np.uint8)
+    return out

@@ -564,3 +564,25 @@ def test_yuv_conversions_vs_oracle(cuda):
     out = torch.empty(3 * 1000 + 1, dtype=torch.uint8, device=cuda)[1:].view(1, 10, 100, 3)
     torch.ops.aiko_b200.yuv_u8(src, out, False, False, torch.cuda.current_stream().cuda_stream)
     np.testing.assert_array_equal(host(out), O.yuv(host(src)))
+
+
+def test_alpha_paste_vs_oracle(cuda):
+    """ops.alpha_paste (PIL's paste of an RGBA image by its own alpha; extension named by north_star) against the
+    oracle pinned on Pillow: random sizes and offsets, clipped by every border, frame-sized images, batches; in
+    place and into ``out``; also straight through torch.ops.aiko_b200."""
+    rng = np.random.default_rng(93)
+    for t in range(40):
+        n, h, w = int(rng.integers(1, 4)), int(rng.integers(1, 90)), int(rng.integers(1, 130))
+        sh, sw = int(rng.integers(1, 100)), int(rng.integers(1, 140))
+        if t % 8 == 0:
+            sh, sw = h, w
+        frames = rng.integers(0, 256, (n, h, w, 3), dtype=np.uint8)
+        rgba = rng.integers(0, 256, (sh, sw, 4), dtype=np.uint8)
+        x, y = (0, 0) if t % 8 == 0 else (int(rng.integers(-sw - 2, w + 2)), int(rng.integers(-sh - 2, h + 2)))
+        d, s = dev(frames, cuda), dev(rgba, cuda)
+        out = ops.alpha_paste(d, s, x, y, out=torch.empty_like(d))
+        np.testing.assert_array_equal(host(d), frames)                      # the source is untouched
+        for k in range(n):
+            np.testing.assert_array_equal(host(out)[k], O.pil_paste(frames[k], rgba, x, y), err_msg=f"case {t} frame {k}")
+        torch.ops.aiko_b200.alpha_paste_u8(d, s, x, y, torch.cuda.current_stream().cuda_stream)       # in place
+        np.testing.assert_array_equal(host(d), host(out))

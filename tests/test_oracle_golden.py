@@ -232,3 +232,22 @@ def test_jpeg_encode_oracle_writes_pillows_bytes():
     buf = io.BytesIO()
     Image.fromarray(a, "RGB").save(buf, "JPEG")
     assert O.jpeg_encode(a) == buf.getvalue()
+
+
+def test_alpha_paste_oracle_is_pillows_paste():
+    """oracle.pil_paste (extension: alpha blending is named by north_star, the reference has no call site) against
+    PIL.Image.paste(image, (x, y), image) for RGBA images at random offsets, clipped by every border."""
+    from PIL import Image
+    rng = np.random.default_rng(31)
+    for t in range(200):
+        h, w = int(rng.integers(1, 90)), int(rng.integers(1, 120))
+        sh, sw = int(rng.integers(1, 100)), int(rng.integers(1, 130))
+        frame = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        rgba = rng.integers(0, 256, (sh, sw, 4), dtype=np.uint8)
+        if t % 5 == 0:
+            rgba[..., 3] = rng.choice([0, 255, 128], size=(sh, sw))
+        x, y = int(rng.integers(-sw - 2, w + 2)), int(rng.integers(-sh - 2, h + 2))
+        ref = Image.fromarray(frame, "RGB")
+        sticker = Image.fromarray(rgba, "RGBA")
+        ref.paste(sticker, (x, y), sticker)
+        np.testing.assert_array_equal(O.pil_paste(frame, rgba, x, y), np.asarray(ref), err_msg=f"case {t}")
