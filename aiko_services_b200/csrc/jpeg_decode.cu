@@ -925,6 +925,14 @@ __device__ __forceinline__ void chroma_eight(const uint8_t* __restrict__ plane, 
     return;
   }
   const int sx0 = x0 >> 1;
+  if (dw <= 2) {
+    // jdsample.c jinit_upsampler installs the fancy filters only for downsampled_width > 2: narrower components
+    // are upsampled by replication (h2v1_upsample / h2v2_upsample); such an image is at most 4 pixels wide
+    const uint8_t* row = plane + (size_t)(MODE == 3 ? y >> 1 : y) * pitch;
+#pragma unroll
+    for (int k = 0; k < 8; k++) out[k] = row[min(sx0 + (k >> 1), pitch - 1)];
+    return;
+  }
   int c[6];
   if (MODE == 2) {
     chroma_six(plane + (size_t)y * pitch, sx0, pitch, c);

@@ -166,6 +166,13 @@ static void upsample(const Comp* c, int hmax, int vmax, int W, int H, uint8_t* o
     return;
   }
   const int dw = c->dw;
+  if (dw <= 2) {
+    /* jdsample.c jinit_upsampler: the fancy filters are only installed for downsampled_width > 2; narrower
+     * components are upsampled by replication (h2v1_upsample / h2v2_upsample) */
+    for (int y = 0; y < H; y++)
+      for (int x = 0; x < W; x++) out[(size_t)y * W + x] = c->plane[(size_t)(vs == 2 ? y >> 1 : y) * c->pw + (x >> 1)];
+    return;
+  }
   int* sums = (int*)malloc(sizeof(int) * (size_t)dw);
   for (int y = 0; y < H; y++) {
     const int sy = vs == 2 ? y >> 1 : y;
