@@ -121,7 +121,7 @@ static int parse_jpeg(const uint8_t* data, size_t len, ParsedImage* out, bool he
     return AIKO_B200_ERR_INVALID_ARGUMENT;
   }
   memset(&out->tables, 0, sizeof(out->tables));
-  bool have_sof = false;
+  bool have_sof = false, saw_jfif = false;
   size_t pos = 2;
   while (pos + 4 <= len) {
     if (data[pos] != 0xff) { set_last_error("jpeg: marker expected at byte %zu", pos); return AIKO_B200_ERR_INVALID_ARGUMENT; }
@@ -171,6 +171,14 @@ static int parse_jpeg(const uint8_t* data, size_t len, ParsedImage* out, bool he
     } else if (m >= 0xc1 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc) {
       set_last_error("jpeg: not baseline (SOF%d)", m - 0xc0);
       return AIKO_B200_ERR_UNSUPPORTED;
+    } else if (m == 0xee) {
+      // APP14 "Adobe": its transform flag can declare the three components RGB (or CMYK / YCCK) instead of YCbCr
+      if (seg >= 14 && memcmp(s, "Adobe", 5) == 0 && s[11] != 1) {
+        set_last_error("jpeg: Adobe marker with colour transform %d", s[11]);
+        return AIKO_B200_ERR_UNSUPPORTED;
+      }
+    } else if (m == 0xe0) {
+      if (seg >= 7 && memcmp(s, "JFIF", 5) == 0) saw_jfif = true;
     } else if (m == 0xdd) {
       if (seg < 4) { set_last_error("jpeg: bad DRI"); return AIKO_B200_ERR_INVALID_ARGUMENT; }
       out->restart = be16(s);
@@ -179,6 +187,11 @@ static int parse_jpeg(const uint8_t* data, size_t len, ParsedImage* out, bool he
       for (int i = 0; i < out->ncomp; i++) {
         if (s[1 + 2 * i] != out->id[i]) { set_last_error("jpeg: component order"); return AIKO_B200_ERR_UNSUPPORTED; }
         out->td[i] = (s[2 + 2 * i] >> 4) & 3; out->ta[i] = s[2 + 2 * i] & 3;
+      }
+      // without a JFIF marker libjpeg takes component ids 'R', 'G', 'B' for RGB data (jdapimin.c default_decompress_parms)
+      if (out->ncomp == 3 && !saw_jfif && out->id[0] == 'R' && out->id[1] == 'G' && out->id[2] == 'B') {
+        set_last_error("jpeg: RGB components (no colour transform)");
+        return AIKO_B200_ERR_UNSUPPORTED;
       }
       out->scan = e;
       out->scan_bytes = len - (size_t)(e - data);

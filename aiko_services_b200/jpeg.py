@@ -144,6 +144,22 @@ class GpuJpegDecoder:
         _native.check(_native.lib().aiko_b200_jpeg_gpu_info_host(raw, len(raw), *[ctypes.byref(v) for v in vals]))
         return tuple(v.value for v in vals)
 
+    @classmethod
+    def _header(cls, buffer):
+        """``info`` of a file given as bytes or as a uint8 host tensor (only as much of a tensor is copied as the
+        header needs: 64 KB, or more when EXIF / ICC segments push the frame header further back)."""
+        if not isinstance(buffer, torch.Tensor):
+            return cls.info(bytes(buffer))
+        size = 1 << 16
+        while True:
+            size = min(size, buffer.numel())
+            try:
+                return cls.info(buffer[:size].numpy().tobytes())
+            except NativeError as error:
+                if size == buffer.numel() or error.code == _native.ERR_UNSUPPORTED:
+                    raise
+                size *= 16
+
     def _pointers(self, buffers):
         n = len(buffers)
         ptrs, lens, keep = (_vp * n)(), (_sz * n)(), []
@@ -164,9 +180,7 @@ class GpuJpegDecoder:
         n = len(buffers)
         if n == 0:
             return torch.empty((0, 0, 0, 3), dtype=torch.uint8, device=self.device)
-        first = buffers[0]
-        head = bytes(first[:min(first.numel(), 1 << 16)].numpy().tobytes()) if isinstance(first, torch.Tensor) else bytes(first)
-        w, h, comps, hmax, vmax, restart = self.info(head)
+        w, h, comps, hmax, vmax, restart = self._header(buffers[0])
         mcus = -(-w // (8 * hmax)) * -(-h // (8 * vmax))
         segments = -(-mcus // restart) if restart > 0 else 1
         ptrs, lens, keep = self._pointers(buffers)
@@ -199,9 +213,7 @@ class GpuJpegDecoder:
                 break
             # the other images of the batch have more restart segments than the first: size for the largest
             for k in range(n):
-                b = buffers[k]
-                head_k = bytes(b[:min(b.numel(), 1 << 16)].numpy().tobytes()) if isinstance(b, torch.Tensor) else bytes(b)
-                restart_k = self.info(head_k)[5]
+                restart_k = self._header(buffers[k])[5]
                 segments = max(segments, -(-mcus // restart_k) if restart_k > 0 else 1)
         if self._event is None:
             self._event = torch.cuda.Event()

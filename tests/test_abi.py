@@ -83,3 +83,29 @@ def test_jpeg_header_parser_survives_hostile_input():
         results.add(rc)
         assert rc in (_native.OK, _native.ERR_INVALID_ARGUMENT, _native.ERR_UNSUPPORTED)
     assert _native.OK in results and _native.ERR_INVALID_ARGUMENT in results
+
+
+def test_jpeg_header_parser_refuses_rgb_coded_files():
+    """A JPEG whose three components are RGB (Adobe marker, colour transform 0) is not YCbCr: the own decoder
+    must refuse it (the caller keeps its other decoder) rather than decode wrong colours."""
+    import ctypes
+    import io
+
+    import numpy as np
+    from PIL import Image
+    from aiko_services_b200 import _native
+    frame = np.random.default_rng(0).integers(0, 256, (40, 56, 3), dtype=np.uint8)
+    vals = [ctypes.c_int() for _ in range(6)]
+    buf = io.BytesIO()
+    try:
+        Image.fromarray(frame, "RGB").save(buf, "JPEG", keep_rgb=True)
+    except TypeError:                       # a Pillow without keep_rgb
+        return
+    raw = buf.getvalue()
+    assert _native.lib().aiko_b200_jpeg_gpu_info_host(raw, len(raw), *[ctypes.byref(v) for v in vals]) == _native.ERR_UNSUPPORTED
+    buf = io.BytesIO()                      # comment, EXIF and ICC segments are skipped
+    Image.fromarray(frame, "RGB").save(buf, "JPEG", comment=b"hello", icc_profile=b"x" * 3000,
+                                       exif=b"Exif\x00\x00II*\x00\x08\x00\x00\x00\x00\x00")
+    raw = buf.getvalue()
+    assert _native.lib().aiko_b200_jpeg_gpu_info_host(raw, len(raw), *[ctypes.byref(v) for v in vals]) == _native.OK
+    assert [v.value for v in vals[:5]] == [56, 40, 3, 2, 2]

@@ -215,6 +215,12 @@ def test_own_decoder_refuses_what_it_cannot_do(cuda):
     for cut in (good[:len(good) // 2], encode(frame)[:len(encode(frame)) // 2]):
         with pytest.raises(NativeError):
             dec.decode([cut], check=True)
+    extras = io.BytesIO()                                              # comment / EXIF / ICC segments: skipped
+    Image.fromarray(frame, "RGB").save(extras, "JPEG", comment=b"hello", icc_profile=b"x" * 70000,
+                                       exif=b"Exif\x00\x00II*\x00\x08\x00\x00\x00\x00\x00")
+    np.testing.assert_array_equal(dec.decode([extras.getvalue()], check=True).cpu().numpy()[0], pillow_rgb(extras.getvalue()))
+    pinned = torch.frombuffer(bytearray(extras.getvalue()), dtype=torch.uint8).pin_memory()      # header beyond the first 64 KB
+    np.testing.assert_array_equal(dec.decode([pinned], check=True).cpu().numpy()[0], pillow_rgb(extras.getvalue()))
     frames, which = jpeg.decode_on_gpu([buf.getvalue()], cuda)         # progressive: falls back to nvJPEG
     assert which == "nvjpeg" and frames.shape == (1, 64, 96, 3)
     for blob in (good, encode(frame)):                                 # with and without restart markers
