@@ -188,6 +188,14 @@ static int parse_jpeg(const uint8_t* data, size_t len, ParsedImage* out, bool he
         if (s[1 + 2 * i] != out->id[i]) { set_last_error("jpeg: component order"); return AIKO_B200_ERR_UNSUPPORTED; }
         out->td[i] = (s[2 + 2 * i] >> 4) & 3; out->ta[i] = s[2 + 2 * i] & 3;
       }
+      {                                       // the entropy kernels keep two DC and two AC tables in shared memory
+        int dcs = 0, acs = 0;
+        for (int i = 0; i < out->ncomp; i++) { dcs |= 1 << out->td[i]; acs |= 1 << out->ta[i]; }
+        if (__builtin_popcount(dcs) > 2 || __builtin_popcount(acs) > 2) {
+          set_last_error("jpeg: more than two Huffman tables of a kind in one scan");
+          return AIKO_B200_ERR_UNSUPPORTED;
+        }
+      }
       // without a JFIF marker libjpeg takes component ids 'R', 'G', 'B' for RGB data (jdapimin.c default_decompress_parms)
       if (out->ncomp == 3 && !saw_jfif && out->id[0] == 'R' && out->id[1] == 'G' && out->id[2] == 'B') {
         set_last_error("jpeg: RGB components (no colour transform)");
