@@ -327,3 +327,36 @@ def test_staging_only_the_rows_a_resize_reads(cuda, monkeypatch):
     out = batch.then("resize_linear", 160, 120).host()
     for k in range(3):
         np.testing.assert_array_equal(out[k], O.resize_linear(frames[k], 160, 120))
+
+
+def test_needed_rows_staging_random_shapes(cuda):
+    """The stager ships only the rows a bilinear resize reads, as strided copies when the pattern is periodic and
+    as one whole copy when it is too fragmented (aiko_b200_copy_rows_h2d): random source / destination heights,
+    batches, both entry routes (one pinned block; one pinned buffer per frame).  The device buffer is poisoned
+    first, so a row that should have been copied and was not would show."""
+    from aiko_services_b200.staging import FrameStager
+    rng = np.random.default_rng(77)
+    stager = FrameStager(cuda)
+    for trial in range(24):
+        sh, dh = int(rng.integers(8, 400)), int(rng.integers(1, 200))
+        if trial % 4 == 0:
+            dh = max(1, sh * 4 // 9)                       # the periodic 2.25x pattern of the headline shape
+        sw, dw, n = int(rng.integers(4, 200)), int(rng.integers(1, 100)), int(rng.integers(1, 5))
+        frames = [cases.frame(7000 + 10 * trial + k, sh, sw, 3) for k in range(n)]
+        poison = torch.full((n, sh, sw, 3), 0xA5, dtype=torch.uint8, device=cuda)      # next torch.empty of this size
+        del poison
+        if trial % 2:
+            views = stager.allocate(n, (sh, sw, 3))        # one pinned block owned by the stager
+            for v, f in zip(views, frames):
+                v[...] = f
+            (batch, _), = stager.upload(views, resize_to=(dw, dh))
+        else:
+            pinned = []
+            for f in frames:                               # one pinned buffer per frame (frames of several streams)
+                t = torch.empty(f.shape, dtype=torch.uint8).pin_memory()
+                t.numpy()[...] = f
+                pinned.append(t.numpy())
+            (batch, _), = stager.upload(pinned, resize_to=(dw, dh))
+        out = batch.then("resize_linear", dw, dh).host()
+        for k in range(n):
+            np.testing.assert_array_equal(out[k], O.resize_linear(frames[k], dw, dh), err_msg=f"trial {trial}: {sw}x{sh} -> {dw}x{dh}")
