@@ -75,6 +75,9 @@ SIGNATURES = {
     "aiko_b200_overlay_cells_host": [_vp, _i, _i, _i, ctypes.POINTER(_i), ctypes.POINTER(ctypes.c_longlong)],
     "aiko_b200_overlay_marks_host": [_vp, _i, _i, _vp],
     "aiko_b200_overlay_atlas_host": [ctypes.POINTER(AtlasView)],
+    "aiko_b200_overlay_glyph_metrics_host": [_vp, _vp, _vp],
+    "aiko_b200_overlay_boxes_workspace_bytes": [_i, _i, _i],
+    "aiko_b200_overlay_boxes_u8": [_vp, _i, _i, _i, _i64, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp, _vp],
     "aiko_b200_resize_linear_u8": [_vp, _i, _i, _i, _i, _i64, _i64, _vp, _i, _i, _i64, _i64, _i, _ovp, _vp],
     "aiko_b200_resize_linear_rows_host": [_i, _i, _vp],
     "aiko_b200_copy_rows_h2d": [_vp, _vp, _i, _i64, _i64, _vp, _i, _vp],
@@ -112,7 +115,8 @@ SIGNATURES = {
 RESTYPES = {"aiko_b200_last_error": ctypes.c_char_p, "aiko_b200_resize_bicubic_workspace_bytes": ctypes.c_size_t,
             "aiko_b200_jpeg_gpu_staging_bytes": ctypes.c_size_t, "aiko_b200_jpeg_gpu_workspace_bytes": ctypes.c_size_t,
             "aiko_b200_audio_workspace_bytes": ctypes.c_size_t,
-            "aiko_b200_jpeg_gpu_encode_workspace_bytes": ctypes.c_size_t}
+            "aiko_b200_jpeg_gpu_encode_workspace_bytes": ctypes.c_size_t,
+            "aiko_b200_overlay_boxes_workspace_bytes": ctypes.c_size_t}
 
 _lib = None
 

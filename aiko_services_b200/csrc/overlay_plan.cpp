@@ -266,6 +266,36 @@ int op_marks(const aiko_b200_overlay_op& op, int W, int H, long long* cells) {
 
 }  // namespace
 
+// What a planner needs to know about the 95 x 4 interior glyphs, for the device-side planner of
+// aiko_b200_overlay_boxes_u8 (csrc/overlay_boxes.cu): advance per character in glyph units, and per
+// (character, pen phase) the inclusive box x0, y0, x1, y1 of the pixels its two patches touch inside the patch
+// window (x1 < x0: blank), plus the planner's constants.
+extern "C" int aiko_b200_overlay_glyph_metrics_host(uint8_t* advance_out_host /* [95] */, int16_t* boxes_out_host /* [95*4][4] */,
+                                                    int32_t* constants_out_host /* [8] */) {
+  if (!advance_out_host || !boxes_out_host || !constants_out_host) {
+    aiko::set_last_error("glyph_metrics: null argument");
+    return AIKO_B200_ERR_INVALID_ARGUMENT;
+  }
+  std::lock_guard<std::mutex> lock(g_mutex);
+  Atlas* a = atlas();
+  if (!a) return AIKO_B200_ERR_UNSUPPORTED;
+  for (int ci = 0; ci < 95; ci++) {
+    advance_out_host[ci] = (uint8_t)aiko_text::glyph_advance((unsigned char)(32 + ci));
+    for (int q = 0; q < 4; q++) {
+      const int base = interior_patch((unsigned char)(32 + ci), q, 0);
+      Box u = a->bbox[base];
+      const Box& b1 = a->bbox[base + 1];
+      if (u.empty()) u = b1;
+      else if (!b1.empty()) { u.x0 = std::min(u.x0, b1.x0); u.y0 = std::min(u.y0, b1.y0); u.x1 = std::max(u.x1, b1.x1); u.y1 = std::max(u.y1, b1.y1); }
+      int16_t* o = boxes_out_host + (ci * 4 + q) * 4;
+      o[0] = (int16_t)u.x0; o[1] = (int16_t)u.y0; o[2] = (int16_t)u.x1; o[3] = (int16_t)u.y1;
+    }
+  }
+  const int32_t constants[8] = {kPatchW, kPatchH, kPadX, kPadY, kBorderMargin, kTextHeight, kThickness, 0};
+  std::memcpy(constants_out_host, constants, sizeof(constants));
+  return AIKO_B200_OK;
+}
+
 extern "C" int aiko_b200_overlay_text_size_host(const char* text_host, int* width_host, int* height_host) {
   if (!text_host || !width_host || !height_host) { aiko::set_last_error("text_size: null argument"); return AIKO_B200_ERR_INVALID_ARGUMENT; }
   text_size(text_host, width_host, height_host);

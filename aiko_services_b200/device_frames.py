@@ -146,7 +146,8 @@ class DeviceBatch:
                 w, h = step[1], step[2]
                 ov, swap, used = None, False, 1
                 # fuse what the library runs in the same pass: [overlay] [RGB<->BGR]
-                if colour and i + used < len(recipe) and recipe[i + used][0] == "overlay":
+                if (colour and i + used < len(recipe) and recipe[i + used][0] == "overlay"
+                        and not isinstance(recipe[i + used][1], ops.DeviceDetections)):
                     ov_spec = recipe[i + used][1]
                     used += 1
                     if i + used < len(recipe) and recipe[i + used] in (("convert", "RGB2BGR"), ("convert", "BGR2RGB")):
@@ -173,6 +174,10 @@ class DeviceBatch:
                 t = ops.resize_bicubic_aa(t, step[1], step[2])
             elif kind == "resize_pil":
                 t = ops.resize_pil(t, step[3], step[1], step[2])
+            elif kind == "overlay" and isinstance(step[1], ops.DeviceDetections):
+                if not colour:
+                    raise ValueError("ImageOverlay from device-resident detections needs RGB frames")
+                t = ops.overlay_boxes(t, step[1], out=t if owned else torch.empty_like(t))    # planned and drawn on the GPU
             elif kind == "overlay":
                 gray = t.dim() == 3
                 h, w = t.shape[1:3]

@@ -120,7 +120,8 @@ class _LazyPil(DeviceImage):
 
 
 def logic_image_overlay(element, stream, images, overlay):
-    """ImageOverlay.process_frame (image_io.py:107-163)."""
+    """ImageOverlay.process_frame (image_io.py:107-163).  ``overlay``: the reference's dict, or -- from a detector
+    element that keeps its output on the GPU -- an ``ops.DeviceDetections``, planned and drawn on the device."""
     for image in images:
         if not isinstance(image, (np.ndarray, DeviceImage)) or isinstance(image, _LazyPil):
             # the reference indexes image.shape, which PIL images lack -> its frame errors out
@@ -373,6 +374,9 @@ def _prepare_overlay(element, stream, images, overlay):
     for image in images:
         if not isinstance(image, (np.ndarray, DeviceImage)) or isinstance(image, _LazyPil):
             return StreamEvent.ERROR, {"diagnostic": "ImageOverlay: images must be numpy arrays"}
+    from ... import ops
+    if isinstance(overlay, ops.DeviceDetections):
+        return logic_image_overlay(element, stream, images, overlay)    # device-resident detections: per-stream path
     return images, ("overlay", overlay), "overlay"
 
 

@@ -292,6 +292,113 @@ class OverlayRing:
         return out
 
 
+class DeviceDetections:
+    """A detector's output as it sits on the GPU, in place of the overlay dict the reference builds on the host
+    (R/examples/yolo/yolo.py:56-87): ``boxes`` int32 [L, K, 4] (x, y, w, h), ``class_ids`` int32 [L, K],
+    ``confidences`` float32 [L, K]; L = 1 (one overlay for all frames of the call, as in the reference) or one
+    list per frame; unused slots carry confidence 0.  ``names``: class names (index = class id)."""
+
+    _name_tables = {}
+
+    def __init__(self, boxes, class_ids, confidences, names):
+        for t, dtype, what in ((boxes, torch.int32, "boxes"), (class_ids, torch.int32, "class_ids"),
+                               (confidences, torch.float32, "confidences")):
+            if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == dtype and t.is_contiguous()):
+                raise RuntimeError(f"DeviceDetections {what}: a contiguous {dtype} CUDA tensor is needed")
+        if boxes.dim() == 2:
+            boxes, class_ids, confidences = boxes[None], class_ids[None], confidences[None]
+        if boxes.dim() != 3 or boxes.shape[2] != 4 or class_ids.shape != boxes.shape[:2] or confidences.shape != boxes.shape[:2]:
+            raise ValueError("DeviceDetections: boxes [L, K, 4], class_ids [L, K], confidences [L, K]")
+        self.boxes, self.class_ids, self.confidences, self.names = boxes, class_ids, confidences, tuple(names)
+
+    def name_table(self, device):
+        """(device char table [n_names, stride], stride), cached per (names, device)."""
+        from .text_atlas import _encode
+        key = (self.names, str(device))
+        entry = self._name_tables.get(key)
+        if entry is None:
+            raw = [_encode(n) if n else b"" for n in self.names]
+            stride = max([len(r) for r in raw] + [1]) + 1
+            if stride > 40:
+                raise ValueError("DeviceDetections: class names longer than 39 characters")
+            table = torch.zeros((max(len(raw), 1), stride), dtype=torch.uint8)
+            for k, r in enumerate(raw):
+                table[k, :len(r)] = torch.frombuffer(bytearray(r), dtype=torch.uint8) if r else table[k, :0]
+            entry = self._name_tables[key] = (table.to(device), stride)
+        return entry
+
+    def to_overlay_dicts(self):
+        """The overlay dict(s) the reference would have built (reads the tensors back: the host path)."""
+        boxes, cls, conf = self.boxes.cpu().numpy(), self.class_ids.cpu().numpy(), self.confidences.cpu().numpy()
+        dicts = []
+        for li in range(boxes.shape[0]):
+            objects, rectangles = [], []
+            for k in range(boxes.shape[1]):
+                c = int(cls[li, k])
+                name = self.names[c] if 0 <= c < len(self.names) and self.names[c] else None
+                objects.append({"name": name, "confidence": float(conf[li, k])})
+                x, y, w, h = (int(v) for v in boxes[li, k])
+                rectangles.append({"x": x, "y": y, "w": w, "h": h})
+            dicts.append({"objects": objects, "rectangles": rectangles})
+        return dicts
+
+
+_boxes_workspaces = {}
+
+
+def overlay_boxes(frames, detections, *, layout="rgb", out=None, stream=None, check=True):
+    """ImageOverlay drawn from a detector's device-resident output (``DeviceDetections``) on RGB frames
+    [N, H, W, 3]: planning and drawing both run on the GPU (aiko_b200_overlay_boxes_u8).  In place unless ``out``
+    is given.  A label that comes within the border margin of the frame needs a glyph variant only the host
+    rasteriser makes: with ``check`` (the default) the 4-byte status is read back and such a call is redone
+    through the host planner; without it the status tensor is returned next to the frames for the caller to look
+    at later (status 1: nothing was drawn).  -> frames, or (frames, status) when ``check`` is false."""
+    from .overlay_plan import LAYOUTS
+    from .text_atlas import TextAtlas
+    _require_cuda(frames, "overlay_boxes frames")
+    if frames.dim() != 4 or frames.shape[3] != 3:
+        raise ValueError("overlay_boxes: RGB frames [N, H, W, 3] are needed")
+    n, h, w, _ = frames.shape
+    d = detections
+    lists, slots = d.boxes.shape[0], d.boxes.shape[1]
+    if lists not in (1, n):
+        raise ValueError(f"overlay_boxes: {lists} lists for {n} frames (1, or one per frame)")
+    dev = frames.device
+    s = stream if stream is not None else torch.cuda.current_stream(dev)
+    if out is not None:
+        out = _out(out, frames.shape, dev, "overlay_boxes out")
+        if out.data_ptr() != frames.data_ptr():
+            with torch.cuda.stream(s):
+                out.copy_(frames)
+        frames = out
+    lib = _native.lib()
+    key = (str(dev), lists, slots, n)
+    entry = _boxes_workspaces.get(key)
+    if entry is None:
+        nbytes = lib.aiko_b200_overlay_boxes_workspace_bytes(lists, slots, n)
+        entry = _boxes_workspaces[key] = (torch.empty(nbytes, dtype=torch.uint8, device=dev),
+                                          torch.zeros(1, dtype=torch.int32, device=dev))
+    workspace, status = entry
+    names, stride = d.name_table(dev)
+    atlas = TextAtlas.shared().device(dev)
+    if atlas.ready is not None:
+        s.wait_event(atlas.ready)
+    _T().overlay_boxes_u8(frames, LAYOUTS[layout], d.boxes, d.class_ids, d.confidences, names, len(d.names), atlas.patch_ids,
+                          atlas.luts, workspace, status, s.cuda_stream)
+    if not check:
+        return frames, status
+    with torch.cuda.stream(s):
+        code = int(status.cpu()[0])
+    if code != 0:
+        # border-clipped labels (or an unusual value): this call through the host planner, boxes read back
+        from .overlay_plan import plan
+        dicts = d.to_overlay_dicts()
+        planned = plan(dicts[0] if lists == 1 else dicts, w, h, layout, n_frames=n)
+        ov = DeviceOverlay.from_plan(planned, dev, TextAtlas.shared().device(dev), stream=s)
+        overlay_draw(frames, ov, out=frames, stream=s)
+    return frames
+
+
 def reads_source_rows_once(frame_shape, width, height):
     """True when ``resize_linear`` to (width, height) fetches every source row it needs exactly once
     with bulk row copies (RGB, 16-byte aligned rows, horizontal scale <= 4, vertical scale >= 2):

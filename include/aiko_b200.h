@@ -172,6 +172,34 @@ typedef struct aiko_b200_atlas_view {
 } aiko_b200_atlas_view;
 int aiko_b200_overlay_atlas_host(aiko_b200_atlas_view* view_host);
 
+/* What a planner needs to know about the 95 x 4 interior glyphs of the atlas (used by the device-side planner
+ * below): advance per character 32..126 in glyph units (pixels = units x 0.75), per (character, pen phase) the
+ * inclusive box x0, y0, x1, y1 of the touched pixels inside the patch window (x1 < x0: blank), and the
+ * planner's constants {patch_w, patch_h, pad_x, pad_y, border_margin, text_height, thickness, 0}. */
+int aiko_b200_overlay_glyph_metrics_host(uint8_t* advance_out_host, int16_t* boxes_out_host, int32_t* constants_out_host);
+
+/* ImageOverlay for detections that never leave the GPU (a detector element's output tensors instead of the
+ * overlay dict that R/examples/yolo/yolo.py:56-87 builds on the host with six .item() calls per box): one
+ * kernel plans the draw lists on the device -- confidence threshold (image_io.py:131), label
+ * f"{name}: {confidence:0.2f}" (image_io.py:139), label size and placement (image_io.py:140-150), one op per
+ * glyph, the rectangle (image_io.py:154-155) -- and the lists are drawn on the RGB frames in place.
+ * boxes: int32 [n_lists][max_objects][4] = x, y, w, h; class_ids: int32 [n_lists][max_objects], an index into
+ * names (outside 0..n_names-1 or an empty name: no label); confidences: float32 [n_lists][max_objects],
+ * slots with confidence <= 0 (or NaN) are skipped, as the reference skips them; n_lists = 1 (the reference: one
+ * overlay for all images of a call) or n_frames (one list per frame).  names: char [n_names][name_stride], NUL
+ * padded; patch_ids / luts: the caller's device copy of the glyph atlas (aiko_b200_overlay_atlas_host).  All of
+ * these are DEVICE pointers.  layout as in aiko_b200_overlay_plan_host.  workspace: 16-byte aligned device
+ * memory of aiko_b200_overlay_boxes_workspace_bytes.  *status (device int32) receives 0 = drawn, or -- with
+ * nothing drawn at all -- 1 = a label comes within the border margin of the frame and needs a glyph variant
+ * only the host rasteriser makes (take the host path for this call), 2 = more ops than the workspace holds,
+ * 3 = a confidence that is not finite or >= 1e9. */
+size_t aiko_b200_overlay_boxes_workspace_bytes(int n_lists, int max_objects, int n_frames);
+int aiko_b200_overlay_boxes_u8(uint8_t* frames, int n_frames, int height, int width, int64_t frame_stride, int layout,
+                               const int32_t* boxes, const int32_t* class_ids, const float* confidences, int n_lists,
+                               int max_objects, const char* names, int n_names, int name_stride,
+                               const uint16_t* patch_ids, const uint8_t* luts, void* workspace, size_t workspace_bytes,
+                               int32_t* status, void* stream);
+
 /* ---------------------------------------------------------------------- */
 /* ImageResize, ndarray branch: cv2.resize(image, (W, H)), INTER_LINEAR,   */
 /* bit-exact fixed-point arithmetic -- R/elements/media/image_io.py:216.   */

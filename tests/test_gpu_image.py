@@ -586,3 +586,55 @@ def test_alpha_paste_vs_oracle(cuda):
             np.testing.assert_array_equal(host(out)[k], O.pil_paste(frames[k], rgba, x, y), err_msg=f"case {t} frame {k}")
         torch.ops.aiko_b200.alpha_paste_u8(d, s, x, y, torch.cuda.current_stream().cuda_stream)       # in place
         np.testing.assert_array_equal(host(d), host(out))
+
+
+def _random_detections(rng, lists, slots, w, h, names, interior):
+    boxes = np.zeros((lists, slots, 4), np.int32)
+    cls = rng.integers(-1, len(names), (lists, slots)).astype(np.int32)
+    conf = rng.random((lists, slots)).astype(np.float32)
+    special = np.array([0.125, 0.875, 0.005, 0.995, 0.999, 1.0, 0.0, -0.3, 12.345, 0.015, 0.025, 0.5], np.float32)
+    pick = rng.random((lists, slots)) < 0.3
+    conf[pick] = rng.choice(special, size=int(pick.sum()))
+    for li in range(lists):
+        for k in range(slots):
+            if interior:          # label and box well inside the frame: the device planner has every glyph
+                bw, bh = int(rng.integers(10, w // 3)), int(rng.integers(10, h // 3))
+                boxes[li, k] = (int(rng.integers(20, w - bw - 200)), int(rng.integers(60, h - bh - 60)), bw, bh)
+            else:
+                boxes[li, k] = (int(rng.integers(-30, w)), int(rng.integers(-30, h)), int(rng.integers(0, w)), int(rng.integers(0, h)))
+    return boxes, cls, conf
+
+
+def test_overlay_from_device_resident_detections(cuda, atlas):
+    """ops.overlay_boxes: the draw lists are planned ON THE GPU from a detector's output tensors (boxes, class
+    ids, float32 confidences) -- label text incl. the correctly rounded confidence, size, placement, glyph ops --
+    and must equal the host planner's result (itself pinned on cv2) pixel for pixel: shared and per-frame lists,
+    skipped slots, unnamed classes, ties in the rounding.  Labels cut by the frame border take the host path."""
+    from aiko_services_b200.overlay_plan import plan
+    names = ["person", "bicycle", "car", "", "traffic light", "Zq{|}~", "x"]
+    rng = np.random.default_rng(2031)
+    W, H = 640, 480
+    for trial in range(12):
+        n = int(rng.integers(1, 4))
+        lists = 1 if trial % 2 == 0 else n
+        slots = int(rng.integers(1, 9))
+        interior = trial % 3 != 2
+        boxes, cls, conf = _random_detections(rng, lists, slots, W, H, names, interior)
+        frames = np.stack([cases.frame(9300 + 7 * trial + k, H, W, 3) for k in range(n)])
+        det = ops.DeviceDetections(torch.from_numpy(boxes).to(cuda), torch.from_numpy(cls).to(cuda),
+                                   torch.from_numpy(conf).to(cuda), names)
+        dicts = det.to_overlay_dicts()
+        for layout in ("rgb", "bgr"):
+            d = dev(frames, cuda)
+            got, status = ops.overlay_boxes(d, det, layout=layout, out=torch.empty_like(d), check=False)
+            code = int(status.cpu()[0])
+            planned = plan(dicts[0] if lists == 1 else dicts, W, H, layout, n_frames=n)
+            want = host(ops.overlay_draw(d, ops.DeviceOverlay.from_plan(planned, cuda, atlas.device(cuda))))
+            if interior:
+                assert code == 0, f"trial {trial}: status {code}"
+            if code == 0:
+                np.testing.assert_array_equal(host(got), want, err_msg=f"trial {trial} {layout}")
+            else:
+                np.testing.assert_array_equal(host(got), frames)                       # nothing drawn, status says why
+            checked = ops.overlay_boxes(d, det, layout=layout, out=torch.empty_like(d))   # falls back when needed
+            np.testing.assert_array_equal(host(checked), want, err_msg=f"trial {trial} {layout} (checked)")

@@ -360,3 +360,27 @@ def test_needed_rows_staging_random_shapes(cuda):
         out = batch.then("resize_linear", dw, dh).host()
         for k in range(n):
             np.testing.assert_array_equal(out[k], O.resize_linear(frames[k], dw, dh), err_msg=f"trial {trial}: {sw}x{sh} -> {dw}x{dh}")
+
+
+def test_image_overlay_element_takes_device_resident_detections(cuda, tmp_path):
+    """A detector element that keeps its output on the GPU hands ImageOverlay an ops.DeviceDetections instead of
+    the overlay dict: ImageResize -> ImageOverlay through the pipeline, same pixels as with the dict."""
+    from aiko_services_b200 import ops
+    names = ["person", "car"]
+    boxes = torch.tensor([[[30, 40, 60, 30], [90, 60, 40, 30], [0, 0, 0, 0]]], dtype=torch.int32, device=cuda)
+    cls = torch.tensor([[0, 1, 0]], dtype=torch.int32, device=cuda)
+    conf = torch.tensor([[0.875, 0.33, 0.0]], dtype=torch.float32, device=cuda)
+    det = ops.DeviceDetections(boxes, cls, conf, names)
+    frames = [cases.frame(9500 + k, 270, 480, 3) for k in range(2)]
+    results = []
+    for overlay in (det, det.to_overlay_dicts()[0]):
+        p = Pipeline(definition(tmp_path, ["Feed", "ImageResize", "ImageOverlay", "ImageOutput"], "240x135"))
+        assert p.create_stream("s")
+        okay, swag = p.process_frame({"stream_id": "s", "frame_id": 0}, {"images": list(frames), "overlay": overlay})
+        assert okay
+        results.append([np.asarray(im) for im in swag["images"]])
+    for a, b in zip(*results):
+        np.testing.assert_array_equal(a, b)
+    ref = reference_port.image_overlay(reference_port.image_resize(frames, "240x135"), det.to_overlay_dicts()[0])
+    for a, r in zip(results[0], ref):                       # and the reference's own cv2 calls on the same dict
+        np.testing.assert_array_equal(a, r)
