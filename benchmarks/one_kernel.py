@@ -66,6 +66,17 @@ def make(name, dev):
         src = [torch.randint(0, 256, shape, dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
         out = torch.empty((shape[0], size[1], size[0]) + shape[3:], dtype=torch.uint8, device=dev)
         return lambda i: ops.resize_linear(src[i % rot], size[0], size[1], out=out), shape[0]
+    if name == "boxes":                    # ImageOverlay planned and drawn on the GPU from device-resident detections
+        import bench
+        frames = [torch.randint(0, 256, (32, 480, 640, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+        rects, objs = bench.OVERLAY["rectangles"], bench.OVERLAY["objects"]
+        names = sorted({o["name"] for o in objs})
+        det = ops.DeviceDetections(
+            torch.tensor([[[r["x"], r["y"], r["w"], r["h"]] for r in rects]], dtype=torch.int32, device=dev),
+            torch.tensor([[names.index(o["name"]) for o in objs]], dtype=torch.int32, device=dev),
+            torch.tensor([[o["confidence"] for o in objs]], dtype=torch.float32, device=dev), names)
+        assert int(ops.overlay_boxes(frames[0], det, layout="bgr", check=False)[1].cpu()[0]) == 0
+        return lambda i: ops.overlay_boxes(frames[i % rot], det, layout="bgr", check=False), 32
     if name == "alpha":                    # a frame-sized RGBA image blended over 32 x 640x480 frames, in place
         frames = [torch.randint(0, 256, (32, 480, 640, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
         rgba = torch.randint(0, 256, (480, 640, 4), dtype=torch.uint8, device=dev, generator=g)
