@@ -51,6 +51,32 @@ def main():
                   f"{len(blob)} bytes, {len(ys)} pixels differ, first at y={ys[0]} x={xs[0]}, max |diff| "
                   f"{np.abs(got.astype(int) - want.astype(int)).max()}")
     print(f"stress_jpeg: {cases} cases, encoder mismatches {bad_enc}, decoder mismatches {bad_dec}")
+    # batches: several files of one geometry but different content, quality, tables and restart layout in ONE call
+    bad_batch = 0
+    for t in range(cases // 10):
+        h, w, n = int(rng.integers(1, 300)), int(rng.integers(1, 300)), int(rng.integers(2, 7))
+        sub = int(rng.integers(0, 3))
+        blobs, frames = [], []
+        for k in range(n):
+            frame = rng.integers(0, 256, (h, w, 3), dtype=np.uint8) if rng.random() < 0.3 else \
+                np.clip(np.asarray(Image.fromarray((rng.random((h // 16 + 2, w // 16 + 2, 3)) * 255).astype(np.uint8), "RGB")
+                                   .resize((w, h), Image.BICUBIC)).astype(np.float32) + rng.normal(0, 5, (h, w, 3)), 0, 255).astype(np.uint8)
+            kw = [{}, {"restart_marker_rows": 1}, {"restart_marker_blocks": int(rng.integers(1, 10))}, {"optimize": True}][int(rng.integers(0, 4))]
+            buf = io.BytesIO()
+            Image.fromarray(frame, "RGB").save(buf, "JPEG", quality=int(rng.integers(5, 100)), subsampling=sub, **kw)
+            blobs.append(buf.getvalue())
+            frames.append(frame)
+        got = dec.decode(blobs, check=True).cpu().numpy()
+        for k in range(n):
+            if not np.array_equal(got[k], np.asarray(Image.open(io.BytesIO(blobs[k])).convert("RGB"))):
+                bad_batch += 1
+                print(f"batch mismatch: batch {t}, image {k}, {w}x{h}, subsampling {sub}")
+        files = enc.encode(torch.from_numpy(np.stack(frames)).to(dev), quality=77, subsampling=sub)
+        for k in range(n):
+            buf = io.BytesIO()
+            Image.fromarray(frames[k], "RGB").save(buf, "JPEG", quality=77, subsampling=sub)
+            bad_batch += files[k] != buf.getvalue()
+    print(f"stress_jpeg: {cases // 10} batches, mismatches {bad_batch}")
 
 
 if __name__ == "__main__":
