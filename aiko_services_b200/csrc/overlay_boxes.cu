@@ -155,11 +155,12 @@ __global__ void __launch_bounds__(kPlanThreads) overlay_boxes_plan_kernel(const 
   const int tid = (int)threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int total = p.n_lists * p.max_objects;
   if (tid == 0) s_carry = 0;
-  for (int i = tid; i < p.n_frames; i += kPlanThreads) p.list_of_frame[i] = p.n_lists == 1 ? 0 : i;
+  const int nthreads = (int)blockDim.x;
+  for (int i = tid; i < p.n_frames; i += nthreads) p.list_of_frame[i] = p.n_lists == 1 ? 0 : i;
   __syncthreads();
   // pass 1: does any label need the host?  do the ops fit?
   int flag = 0, mine = 0;
-  for (int base = 0; base < total; base += kPlanThreads) {
+  for (int base = 0; base < total; base += nthreads) {
     const int object = base + tid;
     if (object < total) mine += plan_object<false>(p, gm, object, nullptr, &flag);
   }
@@ -170,19 +171,20 @@ __global__ void __launch_bounds__(kPlanThreads) overlay_boxes_plan_kernel(const 
   if (lane == 0) warp_sums[warp] = sum;
   __syncthreads();
   int all = 0;
-  for (int w = 0; w < kPlanThreads / 32; w++) all += warp_sums[w];
+  for (int w = 0; w < nthreads / 32; w++) all += warp_sums[w];
   if (flag == 0 && all > p.ops_capacity) flag = 2;
   __syncthreads();
   if (flag != 0) {                                         // (uniform) nothing is drawn: empty lists
-    for (int i = tid; i <= p.n_lists; i += kPlanThreads) p.op_offsets[i] = 0;
+    for (int i = tid; i <= p.n_lists; i += nthreads) p.op_offsets[i] = 0;
     if (tid == 0) *p.status = flag;
     return;
   }
   // pass 2: objects in order, kPlanThreads at a time
-  for (int base = 0; base < total; base += kPlanThreads) {
+  for (int base = 0; base < total; base += nthreads) {
     const int object = base + tid;
     int unused = 0;
-    const int count = object < total ? plan_object<false>(p, gm, object, nullptr, &unused) : 0;
+    // (a call that fits one round of the CTA counted its objects in pass 1 already)
+    const int count = total <= nthreads ? mine : (object < total ? plan_object<false>(p, gm, object, nullptr, &unused) : 0);
     int incl = count;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -192,7 +194,7 @@ __global__ void __launch_bounds__(kPlanThreads) overlay_boxes_plan_kernel(const 
     if (lane == 31) warp_sums[warp] = incl;
     __syncthreads();
     int before = s_carry, chunk = 0;
-    for (int w = 0; w < kPlanThreads / 32; w++) {
+    for (int w = 0; w < nthreads / 32; w++) {
       const int v = warp_sums[w];
       before += w < warp ? v : 0;
       chunk += v;
@@ -285,7 +287,9 @@ extern "C" int aiko_b200_overlay_boxes_u8(uint8_t* frames, int n_frames, int hei
   p.list_of_frame = reinterpret_cast<int32_t*>(ws + L.frames);
   p.status = status;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  overlay_boxes_plan_kernel<<<1, kPlanThreads, 0, st>>>(p, metrics);
+  const int total_objects = n_lists * max_objects;
+  const int threads = total_objects <= 32 ? 32 : total_objects <= 128 ? 128 : kPlanThreads;     // one CTA; small calls: fewer warps at the barriers
+  overlay_boxes_plan_kernel<<<1, threads, 0, st>>>(p, metrics);
   AIKO_CUDA(cudaGetLastError());
   aiko_b200_overlay ov;
   memset(&ov, 0, sizeof(ov));

@@ -97,6 +97,13 @@ def make(name, dev):
         dec = jpeg.GpuJpegDecoder(dev)
         frames = torch.empty((32, 1080, 1920, 3), dtype=torch.uint8, device=dev)
         return lambda i: dec.decode(blobs, out=frames), 32
+    if name == "jpegenc":                  # 32 x 640x480 frames -> JPEG files (Pillow's default settings)
+        import bench
+        from aiko_services_b200 import jpeg
+        host = np.stack([bench.natural_frame(900 + k, 480, 640) for k in range(32)])
+        frames = torch.from_numpy(host).to(dev)
+        enc = jpeg.GpuJpegEncoder(dev)
+        return lambda i: enc.encode_async(frames), 32
     if name in ("audio", "fft"):
         t = np.arange(16000) / 16000.0
         freqs = np.geomspace(50, 7000, 1024)
