@@ -317,16 +317,19 @@ int aiko_b200_resize_norm_f32_nchw(const uint8_t* src, int n_frames, int src_h, 
 /* frames are born device-resident and only the compressed bytes cross PCIe.  The kernels restate      */
 /* libjpeg-turbo's default decoder (Huffman decoding, accurate integer IDCT, "fancy" chroma             */
 /* upsampling, fixed-point YCbCr -> RGB): the decoded pixels are BIT-IDENTICAL to Pillow's.             */
-/* Subset: SOF0, 8 bit, one interleaved scan, gray or YCbCr (4:4:4, 4:2:2, 4:2:0), and a restart        */
-/* interval -- entropy decoding runs one thread per restart segment; files without restart markers      */
-/* return AIKO_B200_ERR_UNSUPPORTED (use another decoder for those, e.g. libaiko_b200_jpeg.so).         */
+/* Subset: SOF0, 8 bit, one interleaved scan, gray or YCbCr (4:4:4, 4:2:2, 4:2:0), with or without      */
+/* restart markers -- entropy decoding runs one thread per subsequence of the scan and finds the         */
+/* decoder state at the subsequence boundaries by iteration (images with more than 512 restart           */
+/* segments: one thread per segment).  Progressive / arithmetic / 12-bit files, RGB- or CMYK-coded       */
+/* files and other sampling layouts return AIKO_B200_ERR_UNSUPPORTED (use another decoder for those,     */
+/* e.g. libaiko_b200_jpeg.so).                                                                           */
 /* All images of a call have one geometry.  dst: uint8 [n][height][width][3] RGB at frame_stride.        */
 /*   info_host       : width, height, components (1 / 3), luma sampling, restart interval of one file    */
 /*   staging_bytes   : page-locked host buffer the call fills with descriptors and tables                */
 /*   workspace_bytes : device workspace for n images of that geometry holding up to compressed_capacity  */
 /*                     bytes of entropy-coded data in all and max_segments restart segments per image    */
 /*                     (quantised coefficients and component planes live there: ~9.4 MB per 1080p        */
-/*                     4:2:0 frame); 0 for an unsupported geometry                                      */
+/*                     4:2:0 frame, plus two copies of the compressed data); 0 for an unsupported geometry;                                      */
 /*   decode_rgb_u8   : everything is enqueued on `stream`; the compressed scans are copied straight      */
 /*                     from jpegs_host (asynchronously when that memory is page-locked; they and the     */
 /*                     staging buffer must stay untouched until the copies have run)                     */
