@@ -98,6 +98,35 @@ def main():
     report("resize_norm_f32 4K->224x224 NCHW (config 4, batch 32)", 32, "frames", 4_272_128, ms)
     del uhd
 
+    # round 2: YUV, alpha blending, and the JPEG codec (algorithmic bytes: compressed file + RGB frame)
+    yuv = torch.empty_like(hd[0])
+    ms = timed(lambda i: ops.yuv(hd[i % rot], out=yuv), args.steps)
+    report("yuv (RGB2YUV) 1080p", 32, "frames", 2 * 6_220_800, ms)
+    del yuv
+    small = [torch.randint(0, 256, (32, 480, 640, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+    rgba = torch.randint(0, 256, (480, 640, 4), dtype=torch.uint8, device=dev, generator=g)
+    ms = timed(lambda i: ops.alpha_paste(small[i % rot], rgba), args.steps)
+    report("alpha_paste, frame-sized RGBA image over 640x480 frames, in place", 32, "frames", 2 * 921_600, ms)
+    sys.path.insert(0, ROOT)
+    import bench
+    from aiko_services_b200 import jpeg
+    blobs = []
+    for k in range(32):
+        b = bench.jpeg_blob(500 + k)
+        pinned = torch.empty(len(b), dtype=torch.uint8).pin_memory()
+        pinned.numpy()[...] = np.frombuffer(b, np.uint8)
+        blobs.append(pinned)
+    file_bytes = int(np.mean([b.numel() for b in blobs]))
+    dec, enc = jpeg.GpuJpegDecoder(dev), jpeg.GpuJpegEncoder(dev)
+    frames = torch.empty((32, 1080, 1920, 3), dtype=torch.uint8, device=dev)
+    ms = timed(lambda i: dec.decode(blobs, out=frames), max(args.steps // 5, 5))
+    report("jpeg decode 1080p 4:2:0 quality 90, no restart markers (one batch at a time, H2D of the files included)", 32,
+           "frames", file_bytes + 6_220_800, ms)
+    natural = torch.from_numpy(np.stack([bench.natural_frame(900 + k, 480, 640) for k in range(32)])).to(dev)
+    ms = timed(lambda i: enc.encode_async(natural), args.steps)
+    report("jpeg encode 640x480, quality 75 4:2:0 (one batch at a time)", 32, "frames", 921_600 + 44_000, ms)
+    del frames, small
+
     t = np.arange(16000) / 16000.0
     freqs = np.geomspace(50, 7000, 1024)
     rng = np.random.default_rng(5000)
