@@ -586,6 +586,13 @@ def test_alpha_paste_vs_oracle(cuda):
             np.testing.assert_array_equal(host(out)[k], O.pil_paste(frames[k], rgba, x, y), err_msg=f"case {t} frame {k}")
         torch.ops.aiko_b200.alpha_paste_u8(d, s, x, y, torch.cuda.current_stream().cuda_stream)       # in place
         np.testing.assert_array_equal(host(d), host(out))
+    # rows that are 16-byte aligned in both images take the 16-pixel kernel
+    for (h, w, sh, sw, x, y) in ((48, 64, 48, 64, 0, 0), (50, 96, 20, 32, 16, 5), (480, 640, 480, 640, 0, 0)):
+        frames = rng.integers(0, 256, (3, h, w, 3), dtype=np.uint8)
+        rgba = rng.integers(0, 256, (sh, sw, 4), dtype=np.uint8)
+        got = host(ops.alpha_paste(dev(frames, cuda), dev(rgba, cuda), x, y))
+        for k in range(3):
+            np.testing.assert_array_equal(got[k], O.pil_paste(frames[k], rgba, x, y))
 
 
 def _random_detections(rng, lists, slots, w, h, names, interior):
