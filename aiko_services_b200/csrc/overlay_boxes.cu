@@ -13,6 +13,8 @@
 #include <math.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "overlay.cuh"
 
 extern "C" int aiko_b200_overlay_glyph_metrics_host(uint8_t* advance_out_host, int16_t* boxes_out_host,
@@ -258,24 +260,23 @@ extern "C" int aiko_b200_overlay_boxes_u8(uint8_t* frames, int n_frames, int hei
     set_last_error("overlay_boxes: workspace of %zu bytes, need %zu", workspace_bytes, L.total);
     return AIKO_B200_ERR_WORKSPACE;
   }
-  static GlyphMetrics metrics;                           // the interior glyphs never change
-  static bool have_metrics = false;
-  if (!have_metrics) {
+  static GlyphMetrics metrics;                           // the interior glyphs never change: fetched once per process
+  static std::once_flag metrics_once;
+  static int metrics_rc = AIKO_B200_OK;
+  std::call_once(metrics_once, [] {
     uint8_t advance[95];
     int16_t glyph_boxes[95 * 4 * 4];
     int32_t constants[8];
-    const int rc = aiko_b200_overlay_glyph_metrics_host(advance, glyph_boxes, constants);
-    if (rc != AIKO_B200_OK) return rc;
-    GlyphMetrics m;
-    memset(&m, 0, sizeof(m));
-    memcpy(m.advance, advance, 95);
+    metrics_rc = aiko_b200_overlay_glyph_metrics_host(advance, glyph_boxes, constants);
+    if (metrics_rc != AIKO_B200_OK) return;
+    memset(&metrics, 0, sizeof(metrics));
+    memcpy(metrics.advance, advance, 95);
     for (int i = 0; i < 95 * 4; i++)
-      m.box[i] = make_short4(glyph_boxes[4 * i], glyph_boxes[4 * i + 1], glyph_boxes[4 * i + 2], glyph_boxes[4 * i + 3]);
-    m.patch_w = constants[0]; m.patch_h = constants[1]; m.pad_x = constants[2]; m.pad_y = constants[3];
-    m.margin = constants[4]; m.text_height = constants[5]; m.thickness = constants[6];
-    metrics = m;
-    have_metrics = true;
-  }
+      metrics.box[i] = make_short4(glyph_boxes[4 * i], glyph_boxes[4 * i + 1], glyph_boxes[4 * i + 2], glyph_boxes[4 * i + 3]);
+    metrics.patch_w = constants[0]; metrics.patch_h = constants[1]; metrics.pad_x = constants[2]; metrics.pad_y = constants[3];
+    metrics.margin = constants[4]; metrics.text_height = constants[5]; metrics.thickness = constants[6];
+  });
+  if (metrics_rc != AIKO_B200_OK) return metrics_rc;
   uint8_t* ws = static_cast<uint8_t*>(workspace);
   BoxesParams p{};
   p.boxes = boxes; p.class_ids = class_ids; p.confidences = confidences; p.names = names;
