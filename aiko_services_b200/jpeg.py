@@ -92,6 +92,9 @@ class JpegDecoder:
         w, h, _, _ = self.info(head)
         if out is None:
             out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=self.device)
+        elif not (out.is_cuda and out.dtype == torch.uint8 and out.is_contiguous() and tuple(out.shape) == (n, h, w, 3)):
+            raise RuntimeError(f"jpeg decode out: a contiguous uint8 CUDA tensor of shape {(n, h, w, 3)} is needed, "
+                               f"got {tuple(out.shape)}")
         s = stream if stream is not None else torch.cuda.current_stream(self.device)
         with torch.cuda.device(self.device):
             for start in range(0, n, self.max_batch):
@@ -189,6 +192,9 @@ class GpuJpegDecoder:
         lib = _native.lib()
         if out is None:
             out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=self.device)
+        elif not (out.is_cuda and out.dtype == torch.uint8 and out.is_contiguous() and tuple(out.shape) == (n, h, w, 3)):
+            raise RuntimeError(f"jpeg decode out: a contiguous uint8 CUDA tensor of shape {(n, h, w, 3)} is needed, "
+                               f"got {tuple(out.shape)}")
         s = stream if stream is not None else torch.cuda.current_stream(self.device)
         if self._event is not None:
             self._event.synchronize()            # the previous call has left the staging buffer and the workspace

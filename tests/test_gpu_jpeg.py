@@ -209,6 +209,8 @@ def test_own_decoder_refuses_what_it_cannot_do(cuda):
     good = encode_rst(frame)
     with pytest.raises(NativeError):
         dec.decode([good, encode_rst(natural_frame(4, 48, 96))])      # sizes differ within a batch
+    with pytest.raises(RuntimeError):
+        dec.decode([good], out=torch.empty((1, 32, 96, 3), dtype=torch.uint8, device=cuda))     # a destination of the wrong shape
     cut = good[:len(good) // 2]                                        # truncated scan: reported, no crash
     with pytest.raises(NativeError):
         dec.decode([cut], check=True)
