@@ -32,6 +32,8 @@ def _op(schema):
 
 def _geometry(t):
     """uint8 frames [N, H, W, C] or [N, H, W] -> (n, h, w, c)"""
+    if t.dtype != torch.uint8 or not t.is_contiguous() or not (t.is_cuda or t.is_pinned()):
+        raise ValueError("aiko_b200 ops take contiguous uint8 frames on a CUDA device (or in page-locked host memory)")
     if t.dim() == 4:
         return t.shape[0], t.shape[1], t.shape[2], t.shape[3]
     if t.dim() == 3:
