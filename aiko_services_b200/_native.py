@@ -77,7 +77,9 @@ SIGNATURES = {
     "aiko_b200_overlay_atlas_host": [ctypes.POINTER(AtlasView)],
     "aiko_b200_overlay_glyph_metrics_host": [_vp, _vp, _vp],
     "aiko_b200_overlay_boxes_workspace_bytes": [_i, _i, _i],
-    "aiko_b200_overlay_boxes_u8": [_vp, _i, _i, _i, _i64, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp, _vp],
+    "aiko_b200_overlay_boxes_u8": [_vp, _i, _i, _i, _i64, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i,
+                                   _vp, _sz, _vp, _vp],
+    "aiko_b200_overlay_variants_host": [_vp, _vp, _vp, _i, _vp, _vp],
     "aiko_b200_resize_linear_u8": [_vp, _i, _i, _i, _i, _i64, _i64, _vp, _i, _i, _i64, _i64, _i, _ovp, _vp],
     "aiko_b200_resize_linear_rows_host": [_i, _i, _vp],
     "aiko_b200_copy_rows_h2d": [_vp, _vp, _i, _i64, _i64, _vp, _i, _vp],

@@ -6,10 +6,11 @@
 // f"{name}: {confidence:0.2f}", label size and placement rule, one GLYPH op per character, the RECT op -- and
 // writes the 32-byte op records straight into device memory, where the drawing kernels read them.
 //
-// The glyph atlas on the device holds the 95 x 4 interior glyphs; a glyph whose strokes come within the border
-// margin of the frame needs a variant rasterised against that border, which only the host rasteriser makes.  When
-// any label of the call needs one, the planner draws NOTHING and reports status 1: the caller then takes the host
-// path (boxes read back, aiko_b200_overlay_plan_host) for that call.
+// A glyph whose strokes come within the border margin of the frame needs a variant rasterised against that border
+// geometry, which only the host rasteriser makes.  The variants made so far travel to the device as a sorted key
+// table (aiko_b200_overlay_variants_host); when a label of the call needs one that is not there yet, the planner
+// draws NOTHING and reports status 1: the caller takes the host path for that call (boxes read back,
+// aiko_b200_overlay_plan_host -- which rasterises the missing variants, so the next call finds them).
 #include <math.h>
 #include <string.h>
 
@@ -40,6 +41,10 @@ struct BoxesParams {
   const char* names;                          // [n_names][name_stride], NUL padded
   int n_lists, max_objects, n_names, name_stride;
   int W, H, layout, n_frames;
+  const unsigned long long* variant_keys;     // the border variants the host has rasterised so far, sorted by key
+  const int32_t* variant_firsts;
+  const short4* variant_boxes;
+  int n_variants;
   aiko_b200_overlay_op* ops;
   int ops_capacity;
   int32_t* op_offsets;                        // [n_lists + 1]
@@ -118,18 +123,49 @@ __device__ int plan_object(const BoxesParams& p, const GlyphMetrics& gm, int obj
       const int px = (int)pxl, py = (int)pyl;
       const short4 u = gm.box[slot * 4 + q];
       if (u.z < u.x) continue;                            // blank
+      int first = 1 + (slot * 4 + q) * 2;
+      short4 box = u;
       if (!(px + u.x >= gm.margin && py + u.y >= gm.margin && px + u.z < W - gm.margin && py + u.w < H - gm.margin)) {
-        *needs_host = 1;                                  // only the host rasteriser makes border variants
-        continue;
+        // near a border: the variant rasterised against this border geometry, if the host has made it already
+        // (csrc/overlay_plan.cpp glyph_patches: the same key)
+        const int far = 1 << 20;
+        const int left = (px + u.x < gm.margin) ? px : -far, top = (py + u.y < gm.margin) ? py : -far;
+        const int right = (px + u.z >= W - gm.margin) ? W - px : far, bottom = (py + u.w >= H - gm.margin) ? H - py : far;
+        const bool ok = (left == -far || (left >= -127 && left <= 126)) && (top == -far || (top >= -127 && top <= 126)) &&
+                        (right == far || (right >= -127 && right <= 126)) && (bottom == far || (bottom >= -127 && bottom <= 126));
+        int found = -1;
+        if (ok) {
+          const unsigned long long key = ((unsigned long long)slot << 34) | ((unsigned long long)q << 32) |
+                                         ((unsigned long long)(left == -far ? 0 : left + 128) << 24) |
+                                         ((unsigned long long)(top == -far ? 0 : top + 128) << 16) |
+                                         ((unsigned long long)(right == far ? 255 : right + 128) << 8) |
+                                         (unsigned long long)(bottom == far ? 255 : bottom + 128);
+          int lo = 0, hi = p.n_variants - 1;
+          while (lo <= hi) {
+            const int mid = (lo + hi) >> 1;
+            const unsigned long long k = p.variant_keys[mid];
+            if (k == key) { found = mid; break; }
+            if (k < key) lo = mid + 1; else hi = mid - 1;
+          }
+        }
+        if (found < 0) {
+          *needs_host = 1;                                // not rasterised yet: only the host rasteriser can
+          continue;
+        }
+        first = p.variant_firsts[found];
+        if (first == 0) continue;                         // nothing of the glyph lands on the image
+        box = p.variant_boxes[found];
+        if (box.z < box.x) continue;
       }
+      const int cx0 = max(px + box.x, 0), cy0 = max(py + box.y, 0), cx1 = min(px + box.z, W - 1), cy1 = min(py + box.w, H - 1);
+      if (cx1 < cx0 || cy1 < cy0) continue;
       if (EMIT) {
-        const int first = 1 + (slot * 4 + q) * 2;
         aiko_b200_overlay_op op;
         op.kind = AIKO_B200_OP_GLYPH;
-        op.x0 = px + u.x; op.y0 = py + u.y; op.x1 = px + u.z; op.y1 = py + u.w;
+        op.x0 = cx0; op.y0 = cy0; op.x1 = cx1; op.y1 = cy1;
         op.p0 = (uint32_t)(first + comp[0]) | ((uint32_t)(first + comp[1]) << 16);
         op.p1 = (uint32_t)(first + comp[2]);
-        op.p2 = (uint32_t)u.x | ((uint32_t)u.y << 16);
+        op.p2 = (uint32_t)(cx0 - px) | ((uint32_t)(cy0 - py) << 16);
         out[n_ops] = op;
       }
       n_ops++;
@@ -245,7 +281,9 @@ extern "C" int aiko_b200_overlay_boxes_u8(uint8_t* frames, int n_frames, int hei
                                           int layout, const int32_t* boxes, const int32_t* class_ids,
                                           const float* confidences, int n_lists, int max_objects, const char* names,
                                           int n_names, int name_stride, const uint16_t* patch_ids, const uint8_t* luts,
-                                          void* workspace, size_t workspace_bytes, int32_t* status, void* stream) {
+                                          int n_patches, const uint64_t* variant_keys, const int32_t* variant_firsts,
+                                          const int16_t* variant_boxes, int n_variants, void* workspace,
+                                          size_t workspace_bytes, int32_t* status, void* stream) {
   AIKO_CHECK_ARG(n_frames >= 0 && height > 0 && width > 0 && (layout == 0 || layout == 1), "overlay_boxes: bad size / layout");
   if (n_frames == 0) return AIKO_B200_OK;
   AIKO_CHECK_ARG(n_lists == 1 || n_lists == n_frames, "overlay_boxes: %d lists for %d frames (1 or one per frame)", n_lists,
@@ -254,6 +292,8 @@ extern "C" int aiko_b200_overlay_boxes_u8(uint8_t* frames, int n_frames, int hei
   AIKO_CHECK_ARG(frames && boxes && class_ids && confidences && workspace && status && patch_ids && luts && (names || n_names == 0),
                  "overlay_boxes: null pointer");
   AIKO_CHECK_ARG(frame_stride >= (int64_t)height * width * 3, "overlay_boxes: frame stride smaller than a frame");
+  AIKO_CHECK_ARG(n_variants == 0 || (variant_keys && variant_firsts && variant_boxes), "overlay_boxes: null variant table");
+  AIKO_CHECK_ARG(n_patches >= 1 + 95 * 4 * 2 && n_variants >= 0, "overlay_boxes: the atlas must hold the interior glyphs");
   AIKO_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "overlay_boxes: workspace must be 16-byte aligned");
   const BoxesLayout L = boxes_layout(n_lists, max_objects, n_frames);
   if (workspace_bytes < L.total) {
@@ -282,6 +322,10 @@ extern "C" int aiko_b200_overlay_boxes_u8(uint8_t* frames, int n_frames, int hei
   p.boxes = boxes; p.class_ids = class_ids; p.confidences = confidences; p.names = names;
   p.n_lists = n_lists; p.max_objects = max_objects; p.n_names = n_names; p.name_stride = name_stride;
   p.W = width; p.H = height; p.layout = layout; p.n_frames = n_frames;
+  p.variant_keys = reinterpret_cast<const unsigned long long*>(variant_keys);
+  p.variant_firsts = variant_firsts;
+  p.variant_boxes = reinterpret_cast<const short4*>(variant_boxes);
+  p.n_variants = n_variants;
   p.ops = reinterpret_cast<aiko_b200_overlay_op*>(ws + L.ops);
   p.ops_capacity = L.ops_capacity;
   p.op_offsets = reinterpret_cast<int32_t*>(ws + L.offsets);
@@ -297,7 +341,7 @@ extern "C" int aiko_b200_overlay_boxes_u8(uint8_t* frames, int n_frames, int hei
   ov.ops = p.ops; ov.op_offsets = p.op_offsets; ov.list_of_frame = p.list_of_frame;
   ov.patch_ids = patch_ids; ov.luts = luts;
   ov.patch_w = metrics.patch_w; ov.patch_h = metrics.patch_h;
-  ov.n_patches = 1 + 95 * 4 * 2;
+  ov.n_patches = n_patches;
   ov.n_lists = n_lists; ov.n_frames = n_frames;
   ov.frame_width = width; ov.frame_height = height;      // op counts are only known on the device: the tile kernel culls the lists
   return aiko_b200_overlay_u8(frames, frames, n_frames, height, width, 3, (int64_t)width * 3, frame_stride, &ov, stream);

@@ -296,6 +296,48 @@ extern "C" int aiko_b200_overlay_glyph_metrics_host(uint8_t* advance_out_host /*
   return AIKO_B200_OK;
 }
 
+// The border variants rasterised so far, for the device-side planner: per variant a 64-bit key -- glyph slot, pen
+// phase and where the image borders lie relative to the patch window, packed so that unsigned order is the order
+// of the planner's own map (slot << 34 | phase << 32 | left << 24 | top << 16 | right << 8 | bottom, every border
+// distance biased by 128, "far" = 0 for left / top and 255 for right / bottom) --, its first patch (0: nothing of
+// the glyph lands on the image) and the inclusive box of the pixels its patches touch.  Sorted by key.
+// -> number of variants (only the first `capacity` are written).
+extern "C" int aiko_b200_overlay_variants_host(uint64_t* keys_out_host, int32_t* firsts_out_host, int16_t* boxes_out_host,
+                                               int capacity, uint64_t* version_out_host, uint64_t* epoch_out_host) {
+  std::lock_guard<std::mutex> lock(g_mutex);
+  Atlas* a = atlas();
+  if (!a) return AIKO_B200_ERR_UNSUPPORTED;
+  if (version_out_host) *version_out_host = a->version;
+  if (epoch_out_host) *epoch_out_host = a->epoch;
+  int n = 0;
+  for (const auto& kv : a->variants) {
+    const int slot = std::get<0>(kv.first), q = std::get<1>(kv.first);
+    const int l = std::get<2>(kv.first), t = std::get<3>(kv.first), r = std::get<4>(kv.first), b = std::get<5>(kv.first);
+    const bool lf = l <= -kFar, tf = t <= -kFar, rf = r >= kFar, bf = b >= kFar;
+    if ((!lf && (l < -127 || l > 126)) || (!tf && (t < -127 || t > 126)) || (!rf && (r < -127 || r > 126)) ||
+        (!bf && (b < -127 || b > 126)))
+      continue;                                            // (not representable in the key: the device asks the host)
+    if (n < capacity && keys_out_host && firsts_out_host && boxes_out_host) {
+      const uint64_t L = lf ? 0 : (uint64_t)(l + 128), T = tf ? 0 : (uint64_t)(t + 128);
+      const uint64_t R = rf ? 255 : (uint64_t)(r + 128), B = bf ? 255 : (uint64_t)(b + 128);
+      keys_out_host[n] = ((uint64_t)slot << 34) | ((uint64_t)q << 32) | (L << 24) | (T << 16) | (R << 8) | B;
+      const int first = kv.second;
+      firsts_out_host[n] = first;
+      Box u;
+      if (first > 0) {
+        u = a->bbox[first];
+        const Box& b1 = a->bbox[first + 1];
+        if (u.empty()) u = b1;
+        else if (!b1.empty()) { u.x0 = std::min(u.x0, b1.x0); u.y0 = std::min(u.y0, b1.y0); u.x1 = std::max(u.x1, b1.x1); u.y1 = std::max(u.y1, b1.y1); }
+      }
+      boxes_out_host[4 * n] = (int16_t)u.x0; boxes_out_host[4 * n + 1] = (int16_t)u.y0;
+      boxes_out_host[4 * n + 2] = (int16_t)u.x1; boxes_out_host[4 * n + 3] = (int16_t)u.y1;
+    }
+    n++;
+  }
+  return n;
+}
+
 extern "C" int aiko_b200_overlay_text_size_host(const char* text_host, int* width_host, int* height_host) {
   if (!text_host || !width_host || !height_host) { aiko::set_last_error("text_size: null argument"); return AIKO_B200_ERR_INVALID_ARGUMENT; }
   text_size(text_host, width_host, height_host);

@@ -349,10 +349,11 @@ _boxes_workspaces = {}
 def overlay_boxes(frames, detections, *, layout="rgb", out=None, stream=None, check=True):
     """ImageOverlay drawn from a detector's device-resident output (``DeviceDetections``) on RGB frames
     [N, H, W, 3]: planning and drawing both run on the GPU (aiko_b200_overlay_boxes_u8).  In place unless ``out``
-    is given.  A label that comes within the border margin of the frame needs a glyph variant only the host
-    rasteriser makes: with ``check`` (the default) the 4-byte status is read back and such a call is redone
-    through the host planner; without it the status tensor is returned next to the frames for the caller to look
-    at later (status 1: nothing was drawn).  -> frames, or (frames, status) when ``check`` is false."""
+    is given.  A label that comes within the border margin of the frame needs a glyph variant rasterised against
+    that border; the variants the host has made so far are mirrored on the device.  When one is missing, nothing is
+    drawn and the status says so: with ``check`` (the default) the 4-byte status is read back and the call is redone
+    through the host planner (which rasterises the variant: the next call finds it on the device); without it the
+    status tensor is returned next to the frames for the caller to look at later.  -> frames, or (frames, status) when ``check`` is false."""
     from .overlay_plan import LAYOUTS
     from .text_atlas import TextAtlas
     _require_cuda(frames, "overlay_boxes frames")
@@ -380,11 +381,15 @@ def overlay_boxes(frames, detections, *, layout="rgb", out=None, stream=None, ch
                                           torch.zeros(1, dtype=torch.int32, device=dev))
     workspace, status = entry
     names, stride = d.name_table(dev)
-    atlas = TextAtlas.shared().device(dev)
+    shared = TextAtlas.shared()
+    atlas = shared.device(dev)
     if atlas.ready is not None:
         s.wait_event(atlas.ready)
+    with torch.cuda.stream(s):
+        keys, firsts, variant_boxes, n_variants = shared.variants(dev)     # (a copy only when the host made new variants)
     _T().overlay_boxes_u8(frames, LAYOUTS[layout], d.boxes, d.class_ids, d.confidences, names, len(d.names), atlas.patch_ids,
-                          atlas.luts, workspace, status, s.cuda_stream)
+                          atlas.luts, atlas.n_patches, keys, firsts, variant_boxes, n_variants, workspace, status,
+                          s.cuda_stream)
     if not check:
         return frames, status
     with torch.cuda.stream(s):

@@ -31,6 +31,7 @@ class TextAtlas:
 
     def __init__(self):
         self._device = {}               # torch.device -> _DeviceAtlas
+        self._variants = {}             # torch.device -> ((epoch, version), variant tensors)
         self._view = AtlasView()
 
     @classmethod
@@ -66,6 +67,27 @@ class TextAtlas:
         w, h = ctypes.c_int(), ctypes.c_int()
         check(_native.lib().aiko_b200_overlay_text_size_host(_encode(text), ctypes.byref(w), ctypes.byref(h)))
         return w.value, h.value
+
+    def variants(self, device):
+        """The border variants rasterised so far as device tensors for the device-side planner
+        (aiko_b200_overlay_variants_host): (keys int64 [n], firsts int32 [n], boxes int16 [n, 4], n); refreshed when
+        the atlas has grown."""
+        import torch
+        device = torch.device(device)
+        v = self.view()
+        cached = self._variants.get(device)
+        if cached is not None and cached[0] == (v.epoch, v.version):
+            return cached[1]
+        lib = _native.lib()
+        n = lib.aiko_b200_overlay_variants_host(None, None, None, 0, None, None)
+        keys = np.zeros(max(n, 1), np.uint64)
+        firsts = np.zeros(max(n, 1), np.int32)
+        boxes = np.zeros((max(n, 1), 4), np.int16)
+        n = min(n, lib.aiko_b200_overlay_variants_host(keys.ctypes.data, firsts.ctypes.data, boxes.ctypes.data, len(keys), None, None))
+        tensors = (torch.from_numpy(keys.view(np.int64)).to(device), torch.from_numpy(firsts).to(device),
+                   torch.from_numpy(boxes).to(device), n)
+        self._variants[device] = ((v.epoch, v.version), tensors)
+        return tensors
 
     def device(self, device):
         import torch

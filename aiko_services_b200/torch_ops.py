@@ -101,14 +101,17 @@ def overlay_u8(src, out, overlay, stream):
 
 
 @_op("overlay_boxes_u8(Tensor(a!) frames, int layout, Tensor boxes, Tensor class_ids, Tensor confidences, Tensor names, "
-     "int n_names, Tensor patch_ids, Tensor luts, Tensor workspace, Tensor(b!) status, int stream) -> ()")
-def overlay_boxes_u8(frames, layout, boxes, class_ids, confidences, names, n_names, patch_ids, luts, workspace, status, stream):
+     "int n_names, Tensor patch_ids, Tensor luts, int n_patches, Tensor variant_keys, Tensor variant_firsts, "
+     "Tensor variant_boxes, int n_variants, Tensor workspace, Tensor(b!) status, int stream) -> ()")
+def overlay_boxes_u8(frames, layout, boxes, class_ids, confidences, names, n_names, patch_ids, luts, n_patches, variant_keys,
+                     variant_firsts, variant_boxes, n_variants, workspace, status, stream):
     n, h, w, _ = _geometry(frames)
     with _current(frames):
         check(_native.lib().aiko_b200_overlay_boxes_u8(
             frames.data_ptr(), n, h, w, h * w * 3, int(layout), boxes.data_ptr(), class_ids.data_ptr(), confidences.data_ptr(),
             boxes.shape[0], boxes.shape[1], names.data_ptr(), int(n_names), names.shape[1], patch_ids.data_ptr(),
-            luts.data_ptr(), workspace.data_ptr(), workspace.numel(), status.data_ptr(), _vp(stream)))
+            luts.data_ptr(), int(n_patches), variant_keys.data_ptr(), variant_firsts.data_ptr(), variant_boxes.data_ptr(),
+            int(n_variants), workspace.data_ptr(), workspace.numel(), status.data_ptr(), _vp(stream)))
 
 
 @_op("swap_rb_u8(Tensor src, Tensor(a!) out, int stream) -> ()")

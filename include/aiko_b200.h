@@ -187,18 +187,26 @@ int aiko_b200_overlay_glyph_metrics_host(uint8_t* advance_out_host, int16_t* box
  * names (outside 0..n_names-1 or an empty name: no label); confidences: float32 [n_lists][max_objects],
  * slots with confidence <= 0 (or NaN) are skipped, as the reference skips them; n_lists = 1 (the reference: one
  * overlay for all images of a call) or n_frames (one list per frame).  names: char [n_names][name_stride], NUL
- * padded; patch_ids / luts: the caller's device copy of the glyph atlas (aiko_b200_overlay_atlas_host).  All of
- * these are DEVICE pointers.  layout as in aiko_b200_overlay_plan_host.  workspace: 16-byte aligned device
+ * padded; patch_ids / luts / n_patches: the caller's device copy of the glyph atlas (aiko_b200_overlay_atlas_host);
+ * variant_*: its border variants (aiko_b200_overlay_variants_host, below; n_variants may be 0).  All of these are
+ * DEVICE pointers.  layout as in aiko_b200_overlay_plan_host.  workspace: 16-byte aligned device
  * memory of aiko_b200_overlay_boxes_workspace_bytes.  *status (device int32) receives 0 = drawn, or -- with
- * nothing drawn at all -- 1 = a label comes within the border margin of the frame and needs a glyph variant
- * only the host rasteriser makes (take the host path for this call), 2 = more ops than the workspace holds,
+ * nothing drawn at all -- 1 = a label comes within the border margin of the frame and needs a glyph variant that
+ * is not in the table yet (take the host path for this call: it rasterises the variant, refresh the table after), 2 = more ops than the workspace holds,
  * 3 = a confidence that is not finite or >= 1e9. */
 size_t aiko_b200_overlay_boxes_workspace_bytes(int n_lists, int max_objects, int n_frames);
 int aiko_b200_overlay_boxes_u8(uint8_t* frames, int n_frames, int height, int width, int64_t frame_stride, int layout,
                                const int32_t* boxes, const int32_t* class_ids, const float* confidences, int n_lists,
                                int max_objects, const char* names, int n_names, int name_stride,
-                               const uint16_t* patch_ids, const uint8_t* luts, void* workspace, size_t workspace_bytes,
-                               int32_t* status, void* stream);
+                               const uint16_t* patch_ids, const uint8_t* luts, int n_patches,
+                               const uint64_t* variant_keys, const int32_t* variant_firsts, const int16_t* variant_boxes,
+                               int n_variants, void* workspace, size_t workspace_bytes, int32_t* status, void* stream);
+/* The border variants of the glyph atlas rasterised so far, as the table aiko_b200_overlay_boxes_u8 takes (device
+ * copies of the three arrays): keys sorted ascending, first patch per variant (0 = the glyph does not reach the
+ * image), inclusive box of the touched pixels inside the patch window.  -> number of variants (only the first
+ * `capacity` are written; the arrays may be NULL to just count); version / epoch: the atlas state they belong to. */
+int aiko_b200_overlay_variants_host(uint64_t* keys_out_host, int32_t* firsts_out_host, int16_t* boxes_out_host,
+                                    int capacity, uint64_t* version_out_host, uint64_t* epoch_out_host);
 
 /* ---------------------------------------------------------------------- */
 /* ImageResize, ndarray branch: cv2.resize(image, (W, H)), INTER_LINEAR,   */

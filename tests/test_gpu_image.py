@@ -645,3 +645,8 @@ def test_overlay_from_device_resident_detections(cuda, atlas):
                 np.testing.assert_array_equal(host(got), frames)                       # nothing drawn, status says why
             checked = ops.overlay_boxes(d, det, layout=layout, out=torch.empty_like(d))   # falls back when needed
             np.testing.assert_array_equal(host(checked), want, err_msg=f"trial {trial} {layout} (checked)")
+            # the host path rasterised the border variants this call needs; they are mirrored on the device now, so
+            # the same detections (the next frame of a video) are planned on the GPU
+            again, status = ops.overlay_boxes(d, det, layout=layout, out=torch.empty_like(d), check=False)
+            assert int(status.cpu()[0]) == 0, f"trial {trial} {layout}: still status {int(status.cpu()[0])}"
+            np.testing.assert_array_equal(host(again), want, err_msg=f"trial {trial} {layout} (second call)")
