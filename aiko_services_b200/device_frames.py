@@ -18,11 +18,9 @@ import torch
 
 from . import ops
 from .metrics import current_tag
-from .overlay_plan import plan
-from .text_atlas import TextAtlas
 
 
-_overlay_cache = OrderedDict()       # (overlay content, size, layout, frames, device) -> DeviceOverlay
+_overlay_rings = OrderedDict()       # (device, CUDA stream) -> ops.OverlayRing: page-locked slots for the draw lists
 
 
 class DeviceBatch:
@@ -100,26 +98,18 @@ class DeviceBatch:
         return self._tensor
 
     def _overlay(self, overlays, width, height, gray, swapped, n):
-        """Plan the draw lists of this call on the host (libaiko_b200's planner: microseconds) and
-        ship them with one copy.  ``overlays``: one dict for all frames, or one per frame."""
+        """Plan the draw lists of this call on the host (libaiko_b200's planner: microseconds) into a page-locked
+        ring slot; the bytes travel with the call that draws them (no blocking copy on the frames' stream).
+        ``overlays``: one dict for all frames, or one per frame."""
         layout = "bgr" if (gray or swapped) else "rgb"
-        if isinstance(overlays, dict):
-            # the most recent static overlay stays on the device (a fixed banner, a benchmark)
-            key = (repr(overlays), width, height, layout, n, str(self.device),
-                   TextAtlas.shared().version[0])
-            cached = _overlay_cache.get(key)
-            if cached is not None:
-                _overlay_cache.move_to_end(key)
-                return cached
-        else:
-            key = None
-        planned = plan(overlays, width, height, layout, n_frames=n)
-        dev = ops.DeviceOverlay.from_plan(planned, self.device, TextAtlas.shared().device(self.device))
-        if key is not None:
-            _overlay_cache[key] = dev
-            if len(_overlay_cache) > 16:
-                _overlay_cache.popitem(last=False)
-        return dev
+        stream = self.stream if self.stream is not None else torch.cuda.current_stream(self.device)
+        key = (str(self.device), stream.cuda_stream)
+        ring = _overlay_rings.get(key)
+        if ring is None:
+            ring = _overlay_rings[key] = ops.OverlayRing(self.device)
+            if len(_overlay_rings) > 64:                  # streams come and go: forget the oldest ring
+                _overlay_rings.pop(next(iter(_overlay_rings)))
+        return ring.plan(overlays, width, height, layout, n_frames=n, stream=stream)
 
     def _source_read(self):
         if self._on_source_read is not None:
