@@ -198,8 +198,8 @@ class FrameStager:
                     batch.stager = self
                     out.append((batch, positions))
                     continue
-                if len(arrs) > 1 and all(a.flags.c_contiguous and a.dtype == np.uint8 for a in arrs):
-                    sources = [torch.from_numpy(a) for a in arrs]
+                if len(arrs) > 1 and all(a.flags.c_contiguous and a.flags.writeable and a.dtype == np.uint8 for a in arrs):
+                    sources = [torch.from_numpy(a) for a in arrs]     # (read-only arrays -- np.asarray(PIL image) -- are never pinned)
                     if all(t.is_pinned() for t in sources):
                         # frames of several streams, each already in page-locked memory (decoders'
                         # or cameras' own buffers): one asynchronous copy per frame straight into
