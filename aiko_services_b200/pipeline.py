@@ -568,7 +568,11 @@ class Pipeline:
             batch, held = held, []
             try:
                 if not batch:
-                    batch.append(self._pending.get(timeout=idle_timeout))
+                    # (nobody can queue any more once the last frame generator has finished: do not wait then)
+                    if self._generators == 0:
+                        batch.append(self._pending.get_nowait())
+                    else:
+                        batch.append(self._pending.get(timeout=idle_timeout))
                 while len(batch) < max_batch:
                     batch.append(self._pending.get_nowait())
             except queue.Empty:

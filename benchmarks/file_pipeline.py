@@ -37,6 +37,23 @@ def main():
         for k in range(n_files):
             with open(os.path.join(root, f"in_{k:04d}.jpg"), "wb") as f:
                 f.write(bench.jpeg_blob(7000 + k % 32))
+        if os.environ.get("PROFILE"):
+            import cProfile
+            import pstats
+            p = Pipeline(definition(root, True, 32))
+            assert p.create_stream("1")
+            p.run()
+            for f in os.listdir(root):
+                if f.startswith("out_"):
+                    os.remove(os.path.join(root, f))
+            p = Pipeline(definition(root, True, 32))
+            assert p.create_stream("1")
+            prof = cProfile.Profile()
+            prof.enable()
+            p.run()
+            prof.disable()
+            pstats.Stats(prof).sort_stats("tottime").print_stats(16)
+            return
         for gpu in (True, False, True):
             p = Pipeline(definition(root, gpu, 32))
             assert p.create_stream("1")
