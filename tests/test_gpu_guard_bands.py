@@ -105,3 +105,45 @@ def test_encoder_writes_stay_inside_its_buffers(cuda):
         assert all(v == -1 or 0 < v <= out_stride for v in lengths), lengths
         if room < 0.1:
             assert lengths == [-1] * n
+
+
+def test_overlay_boxes_and_alpha_paste_stay_inside_the_frames(cuda):
+    """The device-side overlay planner (op records, offsets, status) and the alpha paste with boxes far outside
+    the frame, huge boxes and pastes clipped by every border."""
+    from aiko_services_b200 import ops
+    from aiko_services_b200.text_atlas import TextAtlas
+    lib = _native.lib()
+    rng = np.random.default_rng(14)
+    stream = torch.cuda.current_stream().cuda_stream
+    atlas = TextAtlas.shared().device(cuda)
+    keys, firsts, vboxes, n_variants = TextAtlas.shared().variants(cuda)
+    names = ["person", "a much longer class name, 39 chars.."]
+    det_names, stride = ops.DeviceDetections(torch.zeros((1, 1, 4), dtype=torch.int32, device=cuda),
+                                             torch.zeros((1, 1), dtype=torch.int32, device=cuda),
+                                             torch.zeros((1, 1), dtype=torch.float32, device=cuda), names).name_table(cuda)
+    for trial in range(12):
+        n, h, w = int(rng.integers(1, 4)), int(rng.integers(20, 300)), int(rng.integers(20, 400))
+        lists, slots = (1 if trial % 2 else n), int(rng.integers(1, 40))
+        boxes = torch.from_numpy(rng.integers(-5000, 5000, (lists, slots, 4)).astype(np.int32)).to(cuda)
+        if trial % 3 == 0:
+            boxes[..., 2:] = 1 << 30                                            # absurd sizes
+        cls = torch.from_numpy(rng.integers(-3, 5, (lists, slots)).astype(np.int32)).to(cuda)
+        conf = torch.from_numpy((rng.random((lists, slots)) * 3 - 1).astype(np.float32)).to(cuda)
+        frames = Guarded(n * h * w * 3, cuda)
+        workspace = Guarded(lib.aiko_b200_overlay_boxes_workspace_bytes(lists, slots, n), cuda)
+        status = Guarded(4, cuda)
+        rc = lib.aiko_b200_overlay_boxes_u8(frames.ptr, n, h, w, h * w * 3, trial & 1, boxes.data_ptr(), cls.data_ptr(),
+                                            conf.data_ptr(), lists, slots, det_names.data_ptr(), len(names), stride,
+                                            atlas.patch_ids.data_ptr(), atlas.luts.data_ptr(), atlas.n_patches, keys.data_ptr(),
+                                            firsts.data_ptr(), vboxes.data_ptr(), n_variants, workspace.ptr, workspace.nbytes,
+                                            status.ptr, ctypes.c_void_p(stream))
+        torch.cuda.synchronize()
+        assert rc == 0
+        assert frames.intact() and workspace.intact() and status.intact(), f"trial {trial}: overlay_boxes wrote outside its buffers"
+        # alpha paste at offsets that clip the image by every border (and miss the frame altogether)
+        sh, sw = int(rng.integers(1, 200)), int(rng.integers(1, 300))
+        rgba = torch.from_numpy(rng.integers(0, 256, (sh, sw, 4), dtype=np.uint8)).to(cuda)
+        for (x, y) in ((-sw + 1, -sh + 1), (w - 1, h - 1), (-sw, 0), (0, h), (int(rng.integers(-sw, w)), int(rng.integers(-sh, h)))):
+            rc = lib.aiko_b200_alpha_paste_u8(frames.ptr, n, h, w, h * w * 3, rgba.data_ptr(), sh, sw, x, y, ctypes.c_void_p(stream))
+            torch.cuda.synchronize()
+            assert rc == 0 and frames.intact(), f"trial {trial}: alpha_paste at ({x}, {y}) wrote outside the frames"
