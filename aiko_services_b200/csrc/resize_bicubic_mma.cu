@@ -24,7 +24,9 @@
 //
 // tcgen05 is not used on purpose: the weight matrices are banded (12 taps wide at scale 3), and
 // the band fills 19 % of a 16-output x 64-pixel block but only 3-5 % of the 64/128-row blocks
-// tcgen05.mma works on, which costs more than its higher rate returns.
+// tcgen05.mma works on, which costs more than its higher rate returns: measured on B200
+// (benchmarks/tcgen05_i8_rate.cu) kind::i8 runs at 2.1x (M = 64) / 4.2x (M = 128) the rate of
+// mma.sync.m16n8k32, i.e. 50-55 us of tensor-pipe time for this batch against 31 us here.
 #include "bicubic.cuh"
 
 namespace aiko {
