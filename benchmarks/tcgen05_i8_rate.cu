@@ -144,6 +144,105 @@ __global__ void __launch_bounds__(128) umma_i8_kernel(const uint8_t* __restrict_
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem_d));
 }
 
+// The issue pattern of benchmarks/bicubic_h_umma.cu without its loads and epilogue: M = 128, N = 48, seven K = 32 steps
+// into each of ACCS accumulators in turn (B from a different plane each), optionally while the other three warps
+// read a second TMEM region with tcgen05.ld all the time (READERS).
+template <int ACCS, int READERS, int COMMIT_EACH_ROUND>
+__global__ void __launch_bounds__(128) umma_pattern_kernel(int iters, long long* __restrict__ clocks, int* __restrict__ sink) {
+  constexpr int M = 128, N = 48, K = 224;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sa = smem;
+  uint8_t* sb = smem + M * K;                           // ACCS planes of N x K
+  __shared__ __align__(8) unsigned long long bar, round_bar;
+  __shared__ uint32_t tmem_base_slot;
+  __shared__ volatile int stop;
+  const int tid = (int)threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < (M + ACCS * N) * K; i += 128) smem[i] = (uint8_t)(i * 37 + 11);
+  if (tid == 0) {
+    stop = 0;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&round_bar)));
+    asm volatile("fence.mbarrier_init.release.cluster;");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&tmem_base_slot)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;");
+  const uint32_t tmem_d = tmem_base_slot;
+  if (warp == 0) {
+    if (tid == 0) {
+      const uint32_t idesc = umma_idesc(M, N);
+      const uint32_t a0 = smem_u32(sa), b0 = smem_u32(sb);
+      const long long t0 = clock64();
+      for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int p = 0; p < ACCS; p++) {
+#pragma unroll
+          for (int k = 0; k < K / 32; k++) {
+            const uint64_t da = umma_desc(a0 + k * 2 * (M * 16), M * 16, 128);
+            const uint64_t db = umma_desc(b0 + p * N * K + k * 2 * (N * 16), N * 16, 128);
+            umma_i8(tmem_d + p * 64, da, db, idesc, k ? 1u : 0u);
+          }
+        }
+        if (COMMIT_EACH_ROUND)      // as a kernel with an epilogue does once per tile; nobody waits on this barrier
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&round_bar)) : "memory");
+      }
+      asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
+      uint32_t done = 0;
+      while (!done && clock64() - t0 < 4000000000ll) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}\n"
+            : "=r"(done)
+            : "r"(smem_u32(&bar)), "r"(0u)
+            : "memory");
+      }
+      clocks[blockIdx.x] = clock64() - t0;
+      stop = 1;
+    }
+  } else if (READERS) {
+    uint32_t acc = 0;
+    while (!stop) {
+      uint32_t v[16];
+      const uint32_t taddr = tmem_d + ((uint32_t)(warp * 32) << 16) + 256u;
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+            "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+          : "r"(taddr));
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      for (int j = 0; j < 16; j++) acc += v[j];
+    }
+    if (acc == 0x12345u) sink[0] = (int)acc;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_d));
+}
+
+template <int ACCS, int READERS, int COMMIT_EACH_ROUND>
+void run_pattern(int n_sms, long long* d_clocks, int* d_sink) {
+  const size_t smem = (size_t)(128 + ACCS * 48) * 224;
+  CHECK(cudaFuncSetAttribute(umma_pattern_kernel<ACCS, READERS, COMMIT_EACH_ROUND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int iters = 512;
+  for (int rep = 0; rep < 2; rep++) {
+    umma_pattern_kernel<ACCS, READERS, COMMIT_EACH_ROUND><<<n_sms, 128, smem>>>(iters, d_clocks, d_sink);
+    CHECK(cudaDeviceSynchronize());
+  }
+  long long* h = (long long*)malloc(sizeof(long long) * n_sms);
+  CHECK(cudaMemcpy(h, d_clocks, sizeof(long long) * n_sms, cudaMemcpyDeviceToHost));
+  long long worst = 0;
+  for (int i = 0; i < n_sms; i++) worst = h[i] > worst ? h[i] : worst;
+  free(h);
+  printf("{\"kernel\": \"tcgen05.mma kind::i8 pattern\", \"M\": 128, \"N\": 48, \"accumulators_in_turn\": %d, \"tmem_readers\": %d, \"commit_after_each_round\": %d, "
+         "\"clocks_per_instruction\": %.2f}\n", ACCS, READERS, COMMIT_EACH_ROUND, (double)worst / (iters * ACCS * 7));
+}
+
 // The legacy path: every warp keeps ACC independent m16n8k32 accumulators going.
 template <int ACC>
 __global__ void __launch_bounds__(256) imma_rate_kernel(int iters, int* __restrict__ sink) {
@@ -273,10 +372,20 @@ int main() {
   if (!bad) {                                  // a wrong or hung first shape: stop, nothing else is worth the box time
     bad |= run_umma<128, 128>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
     bad |= run_umma<128, 64>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
+    bad |= run_umma<128, 192>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
+    bad |= run_umma<128, 96>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
+    bad |= run_umma<128, 48>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
+    bad |= run_umma<128, 32>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
+    bad |= run_umma<128, 16>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
     bad |= run_umma<64, 256>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
     bad |= run_umma<64, 128>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
     bad |= run_umma<64, 64>(n_sms, sm_hz, dA, dB, dD, d_clocks, d_flag, hA, hB);
   }
+  run_pattern<1, 0, 0>(n_sms, d_clocks, d_flag + 1);
+  run_pattern<3, 0, 0>(n_sms, d_clocks, d_flag + 1);
+  run_pattern<3, 1, 0>(n_sms, d_clocks, d_flag + 1);
+  run_pattern<3, 0, 1>(n_sms, d_clocks, d_flag + 1);
+  run_pattern<3, 1, 1>(n_sms, d_clocks, d_flag + 1);
   run_imma<8>(n_sms, 1, d_flag + 1);
   run_imma<8>(n_sms, 2, d_flag + 1);
   run_imma<8>(n_sms, 4, d_flag + 1);
