@@ -25,7 +25,9 @@
 // kernel does BOTH passes in 87 us, so it stays.  Versions on the way: 16-byte cp.async staging 152-170 us (LDGSTS
 // issue-bound), 3-D TMA boxes with 16-byte rows 115 us, three N = 48 instructions per K step 92 us (shared-memory
 // operand bandwidth: an M = 128 K = 32 A tile is 4 KB = 32 clocks of the 128 B/clk shared memory per instruction,
-// whatever N is).  What is left is in the epilogue / accumulator hand-off, not in the tensor pipe (37 k of ~125 k clocks; the issuer waits for a free accumulator slot 47 % of the time).
+// whatever N is).  What is left is the epilogue's integer arithmetic (three 32-bit planes per output byte: ~1,560 warp
+// instructions per tile at ~1.2 per clock), not the tensor pipe (37 k of ~125 k clocks): the issuer waits for a free
+// accumulator slot about half of the time (-DEPILOGUE_CLOCKS prints the counters of one epilogue warp).
 //
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o benchmarks/_build/bicubic_h_umma benchmarks/bicubic_h_umma.cu
 #include <cuda.h>
@@ -225,7 +227,13 @@ bicubic_h_umma_kernel(const __grid_constant__ CUtensorMap src_map,   // (5760 by
       const int rb = item / kItemsPerRow, tile = (item % kItemsPerRow) * kTilesPerItem + q;
       const size_t row = (size_t)rb * kRowsPerBlock + quarter * 32 + lane;
       const int slot = t % kSlots;
+#ifdef EPILOGUE_CLOCKS
+      const long long e0 = clock64();
+#endif
       if (!bar_wait(&bars->acc_full[slot], (t / kSlots) & 1, gave_up)) goto out;
+#ifdef EPILOGUE_CLOCKS
+      const long long e1 = clock64();
+#endif
       asm volatile("tcgen05.fence::after_thread_sync;");
       uint32_t packed[4];
 #pragma unroll
@@ -259,6 +267,14 @@ bicubic_h_umma_kernel(const __grid_constant__ CUtensorMap src_map,   // (5760 by
       }
       uint8_t* out = dst + row * kOutRowBytes + (size_t)tile * kTileN + third * 16;
       *reinterpret_cast<uint4*>(out) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+#ifdef EPILOGUE_CLOCKS
+      if (stats && (warp == 5 || warp == 17) && lane == 0) {      // one warp of each group
+        const long long e2 = clock64();
+        atomicAdd((unsigned long long*)&stats[blockIdx.x * 8 + 3], (unsigned long long)(e1 - e0));
+        atomicAdd((unsigned long long*)&stats[blockIdx.x * 8 + 4], (unsigned long long)(e2 - e1));
+        atomicAdd((unsigned long long*)&stats[blockIdx.x * 8 + 5], 1ull);
+      }
+#endif
     }
   } else if (warp == kEpilogueWarps) {
     // ---- MMA issuer: the whole warp walks the loop (uniform control flow, so the descriptors are computed on the
@@ -507,6 +523,7 @@ int main(int argc, char** argv) {
     long long worst = 0;
     for (int i = 0; i < grid; i++) worst = h[i * 8] > worst ? h[i * 8] : worst;
     fprintf(stderr, "issuer clocks per CTA: total %.0f (slowest CTA %lld), waiting for data %.0f, waiting for a slot %.0f\n", a[0], worst, a[1], a[2]);
+    if (a[5] > 0) fprintf(stderr, "an epilogue warp, per tile of its own: waiting for the accumulator %.0f clocks, TMEM read + arithmetic + store issue %.0f\n", a[3] / a[5], a[4] / a[5]);
     free(h);
   }
   const double bytes = (double)src_bytes + (double)dst_bytes;
