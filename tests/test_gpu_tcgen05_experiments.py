@@ -1,0 +1,38 @@
+"""The two stand-alone tcgen05 programs behind DESIGN.md section 8 (why the bicubic resize stays on mma.sync) still
+run and still compute the right numbers: the kind::i8 rate program checks its M = 128 tiles against a host product, the
+horizontal-pass program checks its output bytes against Pillow's arithmetic (R/elements/media/image_io.py:218 ->
+ImagingResampleHorizontal_8bpc).  They are measurements, not product code: nothing in aiko_services_b200 uses them."""
+import json
+import os
+import subprocess
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(program, *args):
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "benchmarks")], stdout=subprocess.DEVNULL)
+    done = subprocess.run([os.path.join(ROOT, "benchmarks", "_build", program), *args], capture_output=True, text=True, timeout=120)
+    lines = [json.loads(line) for line in done.stdout.splitlines() if line.startswith("{")]
+    assert done.returncode == 0, (done.returncode, done.stdout[-2000:], done.stderr[-2000:])
+    return lines
+
+
+def test_tcgen05_i8_tiles_match_a_host_product_and_beat_mma_sync_only_fourfold():
+    lines = _run("tcgen05_i8_rate")
+    umma = [line for line in lines if line.get("kernel") == "tcgen05.mma kind::i8"]
+    assert len(umma) >= 6 and all(line["timed_out"] == 0 for line in umma)
+    assert all(line["wrong_elements_vs_host"] == 0 for line in umma if line["M"] == 128)
+    best = max(line["mac_per_clk_per_sm"] for line in umma)
+    legacy = max(line["chip_tmac_per_s"] for line in lines if line.get("kernel", "").startswith("mma.sync"))
+    full = max(line["chip_tmac_per_s_from_clocks"] for line in umma)
+    assert 7000 < best < 8300                        # 8,192 MAC / clock / SM is the dense 8-bit rate
+    assert 3.0 < full / legacy < 5.5                 # 4.2x, not an order of magnitude
+
+
+def test_bicubic_horizontal_pass_on_tcgen05_is_bit_exact():
+    (line,) = [line for line in _run("bicubic_h_umma", "16") if "wrong_bytes" in line]
+    assert line["gave_up"] == 0 and line["wrong_bytes"] == 0 and line["checked_bytes"] > 500000
