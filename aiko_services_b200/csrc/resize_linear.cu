@@ -281,6 +281,9 @@ __device__ __forceinline__ void consume_rows_fast_g(const ResizeParams& p, bool 
 
 // Gray frames on the same ring: a thread owns 4 consecutive output pixels = one output word; a tap
 // pair is two adjacent bytes (one dp2a), taken from two aligned words with a funnel shift.
+// DECIM (every horizontal weight pair is (2048, 0), e.g. 1920 -> 640): the tap is ONE byte per row, read as a
+// byte, and the vertical blend is (b * tap) >> 9 as in vblend_decim.
+template <bool DECIM>
 __device__ __forceinline__ void consume_rows_gray(const ResizeParams& p, uint64_t* full, uint64_t* empty, const int* recs,
                                                   const uint8_t* stage, int my_items, const int* xw, const int* xs,
                                                   const uint32_t* xcoef, int g, bool on, int lane) {
@@ -305,11 +308,15 @@ __device__ __forceinline__ void consume_rows_gray(const ResizeParams& p, uint64_
     const uint8_t* r0 = stage + (size_t)(slot * R + sub) * 2 * p.seg_stride;
     const uint8_t* r1 = r0 + p.seg_stride;
     if (on) {
-      const uint32_t b0s = (uint32_t)bb.x << 16, b1s = (uint32_t)bb.y << 16;
+      const uint32_t b0s = (uint32_t)bb.x << (DECIM ? 15 : 16), b1s = (uint32_t)bb.y << (DECIM ? 15 : 16);
       uint32_t out = 0;
 #pragma unroll
       for (int k = 0; k < 4; k++) {
         const int e0 = exact[k] + delta.x, e1 = exact[k] + delta.y;
+        if (DECIM) {
+          out |= vblend_decim((uint32_t)r0[e0] << 8, (uint32_t)r1[e1] << 8, b0s, b1s) << (8 * k);
+          continue;
+        }
         const uint32_t* w0 = reinterpret_cast<const uint32_t*>(r0 + (e0 & ~3));
         const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1 + (e1 & ~3));
         const uint32_t u = __funnelshift_r(w0[0], w0[1], (e0 & 3) * 8), v = __funnelshift_r(w1[0], w1[1], (e1 & 3) * 8);
@@ -438,7 +445,8 @@ __global__ void __launch_bounds__(352) resize3_staged(const ResizeParams p) {
     const int g = warp * 32 + lane;
     const bool on = g < groups;
     if (p.ch == 1) {
-      consume_rows_gray(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, lane);
+      if (decim) consume_rows_gray<true>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, lane);
+      else consume_rows_gray<false>(p, full, empty, recs, stage, my_items, xw, xs, xcoef, g, on, lane);
     } else {
       const int gstep = ncons * 32, per_thread = (groups + gstep - 1) / gstep;
       if (per_thread <= 1) consume_rows_fast_g<1>(p, decim, full, empty, recs, stage, my_items, xw, xs, xcoef, g, gstep, groups, sel_rgb, lane);
