@@ -781,8 +781,8 @@ extern "C" int aiko_b200_resize_linear_rows_host(int src_h, int dst_h, uint8_t* 
 // pairs, ascending).  The frames are contiguous, so the batch is one long list of rows: runs that touch across a
 // frame boundary are merged, and consecutive runs of equal length at equal distance become ONE strided copy
 // (1080 -> 480 rows: every ninth source row carries no weight, the whole 32-frame batch is a head run, one
-// strided copy of 3839 runs of 8 rows, and a tail run).  Patterns that would need more than 8 copies are copied
-// whole.  Rows that are not listed are left as they are.
+// strided copy of 3839 runs of 8 rows, and a tail run -- the last two lone runs of equal length again as one strided
+// copy of two runs).  Patterns that would need more than 8 copies are copied whole.  Rows that are not listed are left as they are.
 extern "C" int aiko_b200_copy_rows_h2d(uint8_t* dst, const uint8_t* src_host, int n_frames, int64_t frame_bytes,
                                        int64_t row_bytes, const int32_t* runs_host, int n_runs, void* stream) {
   AIKO_CHECK_ARG(n_frames >= 0 && n_runs >= 0 && frame_bytes > 0 && row_bytes > 0, "copy_rows: bad size");
@@ -820,6 +820,17 @@ extern "C" int aiko_b200_copy_rows_h2d(uint8_t* dst, const uint8_t* src_host, in
       run_count = count;
     }
   close_run();
+  // Two lone runs of equal length (typically the head and the tail run either side of the strided piece) are one
+  // strided copy of two runs: every copy command costs the DMA engine a few microseconds, which counts when the
+  // frames of 64 streams are uploaded one by one.
+  for (size_t i = 0; i < pieces.size(); i++)
+    for (size_t j = i + 1; j < pieces.size(); j++)
+      if (pieces[i].repeats == 1 && pieces[j].repeats == 1 && pieces[i].count == pieces[j].count) {
+        pieces[i].stride = pieces[j].first - pieces[i].first;
+        pieces[i].repeats = 2;
+        pieces.erase(pieces.begin() + (long)j);
+        break;
+      }
   if (pieces.size() > 8) {                              // too fragmented: one contiguous copy of everything
     AIKO_CUDA(cudaMemcpyAsync(dst, src_host, (size_t)(frame_bytes * n_frames), cudaMemcpyHostToDevice, st));
     return AIKO_B200_OK;

@@ -132,7 +132,7 @@ class FrameStager:
         """A tensor already in pinned host memory -> DeviceBatch (one cudaMemcpyAsync).  ``resize_to``
         = (width, height) says that a bilinear resize is all that will read the frames: then only the
         source rows that carry weight cross PCIe (8 of 9 for 1080 -> 480; the library turns the periodic
-        pattern into three copies per batch, one of them strided; AIKO_B200_COPY_NEEDED_ROWS=0 copies
+        pattern into two strided copies per batch; AIKO_B200_COPY_NEEDED_ROWS=0 copies
         everything)."""
         lane = self.next_lane()
         runs = None
@@ -210,7 +210,7 @@ class FrameStager:
                             runs = needed_row_runs(arrs[0].shape[0], resize_to[1])
                         with torch.cuda.stream(lane):
                             dev = torch.empty((len(arrs),) + arrs[0].shape, dtype=torch.uint8, device=self.device)
-                            if runs is not None:      # only the rows the resize reads: three copies per frame
+                            if runs is not None:      # only the rows the resize reads: two copies per frame
                                 import ctypes
 
                                 from . import _native

@@ -824,7 +824,7 @@ def run_gpu_arm(args):
                     "h2d_rows_per_frame": rows_copied,
                     "note": "Pipeline.process_frame over ImageResize -> ImageOverlay -> ImageConvert(RGB2BGR) -> "
                             "ImageOutput; pinned host frames -> cudaMemcpyAsync (only the source rows the resize reads: "
-                            "three copies per batch, one strided) -> fused kernel -> D2H, 2 aiko streams alternating"},
+                            "two strided copies per batch) -> fused kernel -> D2H, 2 aiko streams alternating"},
             "gpu_launches": 2 * args.steps * world,
             "clocks": clocks,
         }

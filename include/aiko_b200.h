@@ -266,7 +266,7 @@ int aiko_b200_resize_bicubic_aa_u8(const uint8_t* src, int n_frames, int src_h, 
 /* vertical reduction touches 8 rows of every 9.  With aiko_b200_copy_rows_h2d a caller that stages    */
 /* frames for a resize ships only the rows that carry weight over PCIe: the frames of a batch are      */
 /* contiguous (frame_bytes = rows x row_bytes), runs of equal length at equal distance travel as one   */
-/* cudaMemcpy2DAsync (1080 -> 480: three copies per batch), patterns needing more than 8 copies are    */
+/* cudaMemcpy2DAsync (1080 -> 480: two copies per batch), patterns needing more than 8 copies are      */
 /* copied whole.                                                                                        */
 int aiko_b200_resize_linear_rows_host(int src_h, int dst_h, uint8_t* needed_host);
 int aiko_b200_copy_rows_h2d(uint8_t* dst, const uint8_t* src_host, int n_frames, int64_t frame_bytes, int64_t row_bytes,
